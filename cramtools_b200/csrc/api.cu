@@ -1,0 +1,255 @@
+// api.cu -- context management and the host-memory entry points of the C ABI (include/cramgpu.h).
+#include "internal.cuh"
+
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+static thread_local std::string g_init_error;
+
+int ctx_fail(cramgpu_ctx *ctx, int code, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->err = buf; else g_init_error = buf;
+    return code;
+}
+
+int ctx_cuda(cramgpu_ctx *ctx, cudaError_t e, const char *what)
+{
+    return ctx_fail(ctx, CRAMGPU_ERR_CUDA, "CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+}
+
+int pool_reserve(cramgpu_ctx *ctx, DevPool &pool, size_t bytes)
+{
+    if (bytes <= pool.cap) return CRAMGPU_OK;
+    // the old buffer may still be in use by enqueued work
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    CUDA_TRY(ctx, cudaDeviceSynchronize());
+    if (pool.p) CUDA_TRY(ctx, cudaFree(pool.p));
+    pool.p = nullptr; pool.cap = 0;
+    size_t want = rup(bytes + bytes / 8, 1 << 20);
+    cudaError_t e = cudaMalloc(&pool.p, want);
+    if (e != cudaSuccess) { want = rup(bytes, 1 << 20); e = cudaMalloc(&pool.p, want); }
+    if (e != cudaSuccess) return ctx_cuda(ctx, e, "cudaMalloc(scratch)");
+    pool.cap = want;
+    return CRAMGPU_OK;
+}
+
+int pinned_reserve(cramgpu_ctx *ctx, void **p, size_t *cap, size_t bytes)
+{
+    if (bytes <= *cap) return CRAMGPU_OK;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    if (*p) CUDA_TRY(ctx, cudaFreeHost(*p));
+    *p = nullptr; *cap = 0;
+    size_t want = rup(bytes + bytes / 8, 1 << 16);
+    CUDA_TRY(ctx, cudaHostAlloc(p, want, cudaHostAllocDefault));
+    *cap = want;
+    return CRAMGPU_OK;
+}
+
+extern "C" {
+
+int cramgpu_init(int device, cramgpu_ctx **out)
+{
+    if (!out) return ctx_fail(nullptr, CRAMGPU_ERR_ARG, "null ctx pointer");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+        return ctx_fail(nullptr, CRAMGPU_ERR_CUDA, "no usable CUDA device (%s); libcramgpu has no CPU fallback",
+                        e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= n) return ctx_fail(nullptr, CRAMGPU_ERR_ARG, "device %d out of range [0,%d)", device, n);
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return ctx_cuda(nullptr, e, "cudaSetDevice");
+    cramgpu_ctx *ctx = new cramgpu_ctx();
+    ctx->device = device;
+    e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming);
+    if (e != cudaSuccess) { delete ctx; return ctx_cuda(nullptr, e, "stream/event creation"); }
+    *out = ctx;
+    return CRAMGPU_OK;
+}
+
+void cramgpu_destroy(cramgpu_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaDeviceSynchronize();
+    if (ctx->scratch.p) cudaFree(ctx->scratch.p);
+    if (ctx->dev_in.p) cudaFree(ctx->dev_in.p);
+    if (ctx->dev_out.p) cudaFree(ctx->dev_out.p);
+    if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
+    if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
+    if (ctx->pin_meta) cudaFreeHost(ctx->pin_meta);
+    if (ctx->ev) cudaEventDestroy(ctx->ev);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *cramgpu_last_error(const cramgpu_ctx *ctx)
+{
+    return ctx ? ctx->err.c_str() : g_init_error.c_str();
+}
+
+int cramgpu_sync(cramgpu_ctx *ctx)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return CRAMGPU_OK;
+}
+
+uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int cramgpu_rans_encode_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
+                            const uint32_t *in_len, const uint8_t *order, uint8_t *d_out, uint64_t out_cap,
+                            uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!d_out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return rans_encode_device(ctx, nblocks, d_in, in_off, in_len, order, d_out, out_cap, d_out_off, d_out_len, d_status,
+                              stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+int cramgpu_rans_decode_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
+                            const uint32_t *in_len, const uint8_t *in_prefix, uint8_t *d_out, uint64_t out_cap,
+                            uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return rans_decode_device(ctx, nblocks, d_in, in_off, in_len, in_prefix, d_out, out_cap, d_out_off, d_out_len, d_status,
+                              stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+int cramgpu_rans_raw_sizes(uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len, uint32_t *raw_len,
+                           int32_t *status)
+{
+    int first = CRAMGPU_OK;
+    for (uint32_t i = 0; i < nblocks; i++) {
+        uint32_t ord;
+        int rc = rans_parse_prefix(in[i], in_len[i], &ord, &raw_len[i]);
+        if (rc != CRAMGPU_OK) raw_len[i] = 0;
+        if (status) status[i] = rc;
+        if (rc != CRAMGPU_OK && first == CRAMGPU_OK) first = rc;
+    }
+    return first;
+}
+
+static const char *status_text(int rc)
+{
+    switch (rc) {
+    case CRAMGPU_ERR_INPUT_LENGTH: return "Incorrect input length.";
+    case CRAMGPU_ERR_OUT_TOO_SMALL: return "Output buffer too small";
+    case CRAMGPU_ERR_UNKNOWN_ORDER: return "Unknown rANS order";
+    case CRAMGPU_ERR_CORRUPT: return "Corrupt rANS block";
+    default: return "error";
+    }
+}
+
+// Shared by the two host entry points: stage inputs in pinned memory, one H2D copy, run the device
+// pipeline, one D2H copy of the packed results, scatter into the caller's buffers.
+static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len,
+                      const uint8_t *order, uint8_t *const *out, const uint32_t *out_cap, uint32_t *out_len,
+                      int32_t *status)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (nblocks == 0) return CRAMGPU_OK;
+    if (!in || !in_len || !out || !out_cap || !out_len || (encode && !order)) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+
+    std::vector<uint64_t> off(nblocks);
+    std::vector<uint8_t> prefix(encode ? 0 : 9 * (size_t)nblocks, 0);
+    uint64_t total_in = 0, total_out_cap = 0;
+    for (uint32_t i = 0; i < nblocks; i++) {
+        if (in_len[i] && !in[i]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in[%u] is null", i);
+        off[i] = total_in;
+        total_in += rup(in_len[i], 16);
+        if (!encode) {
+            memcpy(&prefix[9 * (size_t)i], in[i], in_len[i] < 9 ? in_len[i] : 9);
+            uint32_t ord, raw;
+            if (rans_parse_prefix(in[i], in_len[i], &ord, &raw) == CRAMGPU_OK) total_out_cap += rup(raw, 16);
+        }
+    }
+    // results header: out_off (nblocks+1 u64) | out_len (u32) | status (i32)
+    size_t hdr_bytes = 8 * (size_t)(nblocks + 1) + 8 * (size_t)nblocks;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, total_in + 16)) return rc;
+    if (int rc = pool_reserve(ctx, ctx->dev_in, total_in + hdr_bytes + 64)) return rc;
+    uint8_t *pin = (uint8_t *)ctx->pin_in;
+    for (uint32_t i = 0; i < nblocks; i++)
+        if (in_len[i]) memcpy(pin + off[i], in[i], in_len[i]);
+    uint8_t *d_in = (uint8_t *)ctx->dev_in.p;
+    uint8_t *d_hdr = d_in + rup(total_in, 16) + 16;
+    uint64_t *d_out_off = (uint64_t *)d_hdr;
+    uint32_t *d_out_len = (uint32_t *)(d_hdr + 8 * (size_t)(nblocks + 1));
+    int32_t *d_status = (int32_t *)(d_hdr + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
+    if (total_in) CUDA_TRY(ctx, cudaMemcpyAsync(d_in, pin, total_in, cudaMemcpyHostToDevice, st));
+
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, hdr_bytes + 64)) return rc;
+    if (encode) {
+        if (int rc = rans_encode_device(ctx, nblocks, d_in, off.data(), in_len, order, nullptr, ~0ull, d_out_off, d_out_len,
+                                        d_status, st))
+            return rc;
+        // the packed size is only known on the device: fetch it, then size the output buffers
+        CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pin_out, d_out_off + nblocks, 8, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        total_out_cap = *(uint64_t *)ctx->pin_out;
+        if (int rc = pool_reserve(ctx, ctx->dev_out, total_out_cap + 64)) return rc;
+        if (int rc = rans_encode_pack(ctx, (uint8_t *)ctx->dev_out.p, st)) return rc;
+    } else {
+        if (int rc = pool_reserve(ctx, ctx->dev_out, total_out_cap + 64)) return rc;
+        if (int rc = rans_decode_device(ctx, nblocks, d_in, off.data(), in_len, prefix.data(), (uint8_t *)ctx->dev_out.p,
+                                        total_out_cap, d_out_off, d_out_len, d_status, st))
+            return rc;
+    }
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, hdr_bytes + 64 + total_out_cap)) return rc;
+    uint8_t *pout = (uint8_t *)ctx->pin_out;
+    uint8_t *pdata = pout + rup(hdr_bytes, 64);
+    CUDA_TRY(ctx, cudaMemcpyAsync(pout, d_hdr, hdr_bytes, cudaMemcpyDeviceToHost, st));
+    if (total_out_cap) CUDA_TRY(ctx, cudaMemcpyAsync(pdata, ctx->dev_out.p, total_out_cap, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+
+    const uint64_t *h_off = (const uint64_t *)pout;
+    const uint32_t *h_len = (const uint32_t *)(pout + 8 * (size_t)(nblocks + 1));
+    const int32_t *h_status = (const int32_t *)(pout + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
+    int first = CRAMGPU_OK;
+    for (uint32_t i = 0; i < nblocks; i++) {
+        int rc = h_status[i];
+        out_len[i] = 0;
+        if (rc == CRAMGPU_OK) {
+            if (h_len[i] > out_cap[i]) rc = CRAMGPU_ERR_OUT_TOO_SMALL;
+            else {
+                if (h_len[i]) memcpy(out[i], pdata + h_off[i], h_len[i]);
+                out_len[i] = h_len[i];
+            }
+        }
+        if (status) status[i] = rc;
+        if (rc != CRAMGPU_OK && first == CRAMGPU_OK) {
+            first = rc;
+            if (rc == CRAMGPU_ERR_OUT_TOO_SMALL) ctx_fail(ctx, rc, "Output buffer too small to fit %u bytes. (block %u)", h_len[i], i);
+            else if (rc == CRAMGPU_ERR_UNKNOWN_ORDER) ctx_fail(ctx, rc, "Unknown rANS order: %d (block %u)", encode ? (int)order[i] : (int)in[i][0], i);
+            else ctx_fail(ctx, rc, "%s (block %u)", status_text(rc), i);
+        }
+    }
+    return first;
+}
+
+int cramgpu_rans_encode_batch(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len,
+                              const uint8_t *order, uint8_t *const *out, const uint32_t *out_cap, uint32_t *out_len,
+                              int32_t *status)
+{
+    return host_batch(ctx, true, nblocks, in, in_len, order, out, out_cap, out_len, status);
+}
+
+int cramgpu_rans_decode_batch(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len,
+                              uint8_t *const *out, const uint32_t *out_cap, uint32_t *out_len, int32_t *status)
+{
+    return host_batch(ctx, false, nblocks, in, in_len, nullptr, out, out_cap, out_len, status);
+}
+
+}  // extern "C"

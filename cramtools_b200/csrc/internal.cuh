@@ -1,0 +1,104 @@
+// internal.cuh -- shared declarations of libcramgpu (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include <vector>
+
+#include "../../include/cramgpu.h"
+
+#define TF_SHIFT 12
+#define TOTFREQ 4096u
+#define RANS_L (1u << 23)
+
+#define HIST_CHUNK (128u * 1024u)   // bytes of one block handled by one histogram CTA
+#define PACK_CHUNK (64u * 1024u)    // bytes of one block copied by one pack CTA
+#define O0_TAB_CAP 1040u            // >= 256*(1+1+2)+1
+#define O1_TAB_CAP 263936u          // >= 256*(2+1025)+1, multiple of 256
+#define O1_SMEM_ENTRIES 12032u      // compact (ctx x sym) histogram cells kept in shared memory per CTA
+
+static inline uint64_t rup(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+// One rANS block of the batch, as the kernels see it.
+struct BlockDesc {
+    uint64_t in_off;      // offset of the raw (encode) or compressed (decode) bytes in the input buffer
+    uint64_t work_off;    // encode: offset of this block's table+payload work area in scratch
+    uint64_t out_off;     // decode: offset of the decoded bytes in the output buffer
+    uint32_t in_len;      // encode: raw size; decode: compressed size
+    uint32_t out_len;     // decode: raw size
+    uint32_t work_cap;    // encode: bytes of work area (table region first, payload grows down from the end)
+    uint32_t tab_cap;     // encode: bytes reserved for the table at the start of the work area
+    uint32_t order;       // effective order (0 when n < 4), or 0xFF = skip (empty / rejected on host)
+    uint32_t o1_index;    // rank among the order-1 blocks of this call (selects F1 / syms1 / lut1 slabs)
+    uint32_t pad0, pad1;
+};
+
+// Alphabet of an order-1 block: contexts = bytes that occur, plus 0; symbols = bytes that occur.
+struct O1Meta {
+    uint8_t cmap[256];    // byte -> context rank
+    uint8_t smap[256];    // byte -> symbol rank
+    uint8_t calpha[256];  // context rank -> byte
+    uint8_t salpha[256];  // symbol rank -> byte
+    uint32_t nctx, nsym;
+};
+
+struct DevPool {
+    void *p = nullptr;
+    size_t cap = 0;
+};
+
+struct EncodePending {     // what k_pack needs once the output buffer exists
+    const BlockDesc *desc = nullptr;
+    const uint8_t *work = nullptr;
+    const uint32_t *tlen = nullptr, *plen = nullptr;
+    const uint64_t *out_off = nullptr;
+    const uint32_t *out_len = nullptr;
+    uint32_t nblocks = 0;
+    uint64_t max_out = 0;
+};
+
+struct cramgpu_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    DevPool scratch;          // carved anew by every call
+    DevPool dev_in, dev_out;  // device staging of the host entry points
+    void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
+    size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
+    cudaEvent_t ev = nullptr;
+    EncodePending pend;
+};
+
+int ctx_fail(cramgpu_ctx *ctx, int code, const char *fmt, ...);
+int ctx_cuda(cramgpu_ctx *ctx, cudaError_t e, const char *what);
+int pool_reserve(cramgpu_ctx *ctx, DevPool &pool, size_t bytes);
+int pinned_reserve(cramgpu_ctx *ctx, void **p, size_t *cap, size_t bytes);
+
+#define CUDA_TRY(ctx, call)                                            \
+    do {                                                               \
+        cudaError_t e__ = (call);                                      \
+        if (e__ != cudaSuccess) return ctx_cuda((ctx), e__, #call);    \
+    } while (0)
+
+// bump allocator over the context scratch pool (sizes first, then pointers)
+struct Carver {
+    size_t off = 0;
+    size_t take(size_t bytes, size_t align = 256) {
+        off = rup(off, align);
+        size_t o = off;
+        off += bytes;
+        return o;
+    }
+};
+
+// rans.cu
+int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
+                       const uint32_t *in_len, const uint8_t *order, uint8_t *d_out, uint64_t out_cap,
+                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st);
+int rans_encode_pack(cramgpu_ctx *ctx, uint8_t *d_out, cudaStream_t st);
+int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
+                       const uint32_t *in_len, const uint8_t *in_prefix, uint8_t *d_out, uint64_t out_cap,
+                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st);
+int rans_parse_prefix(const uint8_t *p, uint32_t len, uint32_t *order, uint32_t *raw);

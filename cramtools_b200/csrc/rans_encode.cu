@@ -1,0 +1,770 @@
+// rans_encode.cu -- htsjdk-compatible rANS order-0 / order-1 ENCODE for sm_100a.
+//
+// Byte-identical restatement of RANS.compress [RANS.java:60-73] as a batch pipeline:
+//
+//   k_hist0    byte histogram of every block                  Frequencies.calcFrequencies_o0 [:109-117]
+//   k_prep_o1  alphabet of each order-1 block, zero its (ctx x sym) cells
+//   k_hist1    order-1 pair counts                            Frequencies.calcFrequencies_o1 [:149-166]
+//   k_tables0  normalise to 4095, symbol table, freq table    [:118-145], buildSyms_o0 [:197-211], writeFrequencies_o0 [:215-244]
+//   k_tables1  same per context (IEEE double scaling)         [:167-193], buildSyms_o1 [:248-265], writeFrequencies_o1 [:269-328]
+//   k_enc0     4-way interleaved coder, one lane per state    E04.compress [E04.java:12-57], RansEncPutSymbol [Encoding.java:46-71]
+//   k_enc1     4 quarter-lanes, context = previous byte       E14.compress [E14.java:13-86]
+//   k_scan_out output offsets (16-byte aligned, back to back)
+//   k_pack     prefix + table + payload into the output       RANS.finalizeCompressed [RANS.java:132-142]
+//
+// The coder is a strict recurrence per state, so a block offers exactly 4 lanes of parallelism;
+// the kernels pack 8 blocks into a warp (one lane per state) and rely on many blocks per call.
+// Renormalisation bytes of the 4 lanes share one output cursor: per step the lanes emit in the order
+// 3,2,1,0 [E04.java:41-44] and the whole buffer is reversed at the end [rans/Utils.java:7-33]; here the
+// bytes are written downwards from the end of the block's work area, positions coming from two
+// ballots + popc per step, so no reversal pass is needed.
+#include "internal.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// device helpers
+
+// Encoding.RansEncSymbolInit [Encoding.java:21-43], packed into 8 bytes:
+//   .x = rcp_freq,  .y = bias (13 bits) | freq << 13 (12 bits) | (rcp_shift - 32) << 25
+// x_max = freq << 19 and cmpl_freq = 4096 - freq are recomputed in the coder (off the critical chain).
+__device__ __forceinline__ uint2 make_enc_sym(uint32_t start, uint32_t freq)
+{
+    uint32_t rcp, sh, bias;
+    if (freq < 2) {
+        rcp = 0xFFFFFFFFu; sh = 0; bias = start + TOTFREQ - 1;
+    } else {
+        uint32_t shift = 32 - __clz(freq - 1);   // smallest shift with freq <= 1 << shift
+        rcp = (uint32_t)(((1ull << (shift + 31)) + freq - 1) / freq);
+        sh = shift - 1; bias = start;
+    }
+    return make_uint2(rcp, bias | (freq << 13) | (sh << 25));
+}
+
+__device__ __forceinline__ uint32_t warp_sum(uint32_t v)
+{
+    return __reduce_add_sync(0xFFFFFFFFu, v);
+}
+__device__ __forceinline__ uint32_t warp_excl_scan(uint32_t v, uint32_t lane)
+{
+    uint32_t s = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xFFFFFFFFu, s, d);
+        if (lane >= (uint32_t)d) s += t;
+    }
+    return s - v;
+}
+__device__ __forceinline__ unsigned long long warp_max64(unsigned long long v)
+{
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        unsigned long long t = __shfl_xor_sync(0xFFFFFFFFu, v, d);
+        v = t > v ? t : v;
+    }
+    return v;
+}
+
+// One warp serialises one frequency row (Frequencies.writeFrequencies_o0 [:215-244]; rows of _o1 [:297-324]).
+//   rowF   256 normalised frequencies in shared memory (0 = symbol absent)
+//   mask   8 words of shared memory scratch private to this warp
+//   dst    destination, or nullptr to only measure
+// Run-length rule restated position-locally: inside a maximal run [a..b] of consecutive present symbols,
+// a writes its symbol byte, a+1 writes its symbol byte and the count b-a-1 of further symbols, the rest
+// write no symbol byte.  Every present symbol then writes its frequency in 1 byte (<128) or 2 bytes.
+__device__ uint32_t warp_write_row(const uint16_t *rowF, uint32_t *mask, uint8_t *dst, uint32_t lane)
+{
+#pragma unroll
+    for (int w = 0; w < 8; w++) {
+        uint32_t b = __ballot_sync(0xFFFFFFFFu, rowF[w * 32 + lane] != 0);
+        if (lane == 0) mask[w] = b;
+    }
+    __syncwarp();
+    uint32_t nb = 0;
+    uint8_t buf[8 * 4];
+    for (int i = 0; i < 8; i++) {
+        int j = lane * 8 + i;
+        uint32_t f = rowF[j];
+        if (!f) continue;
+        bool p1 = j > 0 && ((mask[(j - 1) >> 5] >> ((j - 1) & 31)) & 1);
+        bool p2 = j > 1 && ((mask[(j - 2) >> 5] >> ((j - 2) & 31)) & 1);
+        if (!p1) {
+            buf[nb++] = (uint8_t)j;
+        } else if (!p2) {
+            // end of the run that contains j
+            int w = j >> 5;
+            uint32_t inv = ~mask[w] & (0xFFFFFFFFu << (j & 31));
+            while (inv == 0 && w < 7) { w++; inv = ~mask[w]; }
+            int end = inv ? (w * 32 + __ffs(inv) - 2) : 255;
+            buf[nb++] = (uint8_t)j;
+            buf[nb++] = (uint8_t)(end - j);
+        }
+        if (f < 128) buf[nb++] = (uint8_t)f;
+        else { buf[nb++] = (uint8_t)(128 | (f >> 8)); buf[nb++] = (uint8_t)(f & 0xFF); }
+    }
+    uint32_t off = warp_excl_scan(nb, lane);
+    uint32_t total = __shfl_sync(0xFFFFFFFFu, off + nb, 31);
+    if (dst) {
+        for (uint32_t i = 0; i < nb; i++) dst[off + i] = buf[i];
+        if (lane == 0) dst[total] = 0;
+    }
+    __syncwarp();
+    return total + 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_hist0: grid (nblocks, chunks); 256 threads; per-warp private 256-bin histograms in shared memory.
+__global__ void __launch_bounds__(256) k_hist0(const BlockDesc *__restrict__ desc, const uint8_t *__restrict__ d_in,
+                                               uint32_t *__restrict__ F0)
+{
+    const BlockDesc d = desc[blockIdx.x];
+    uint64_t start = (uint64_t)blockIdx.y * HIST_CHUNK;
+    if (d.order > 1 || start >= d.in_len) return;
+    uint32_t len = min((uint64_t)HIST_CHUNK, d.in_len - start);
+    const uint8_t *in = d_in + d.in_off + start;
+
+    __shared__ uint32_t h[8][256];
+    for (int i = threadIdx.x; i < 8 * 256; i += 256) (&h[0][0])[i] = 0;
+    __syncthreads();
+    uint32_t *hw = h[threadIdx.x >> 5];
+    uint32_t nvec = len >> 4;
+    const uint4 *v = reinterpret_cast<const uint4 *>(in);
+    for (uint32_t i = threadIdx.x; i < nvec; i += 256) {
+        uint4 q = __ldg(v + i);
+        uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            atomicAdd(&hw[w[k] & 0xFF], 1u);
+            atomicAdd(&hw[(w[k] >> 8) & 0xFF], 1u);
+            atomicAdd(&hw[(w[k] >> 16) & 0xFF], 1u);
+            atomicAdd(&hw[w[k] >> 24], 1u);
+        }
+    }
+    for (uint32_t i = (nvec << 4) + threadIdx.x; i < len; i += 256) atomicAdd(&hw[in[i]], 1u);
+    __syncthreads();
+    uint32_t s = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) s += h[w][threadIdx.x];
+    if (s) atomicAdd(&F0[(size_t)blockIdx.x * 256 + threadIdx.x], s);
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_prep_o1: one CTA (256 threads) per order-1 block.
+__global__ void __launch_bounds__(256) k_prep_o1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o1_blocks,
+                                                 const uint32_t *__restrict__ F0, O1Meta *__restrict__ meta,
+                                                 uint32_t *__restrict__ F1)
+{
+    uint32_t blk = o1_blocks[blockIdx.x];
+    uint32_t j = threadIdx.x, lane = j & 31, w = j >> 5;
+    bool present = F0[(size_t)blk * 256 + j] != 0;
+    bool isctx = present || j == 0;
+    __shared__ uint32_t cntS[8], cntC[8];
+    uint32_t bs = __ballot_sync(0xFFFFFFFFu, present), bc = __ballot_sync(0xFFFFFFFFu, isctx);
+    if (lane == 0) { cntS[w] = __popc(bs); cntC[w] = __popc(bc); }
+    __syncthreads();
+    uint32_t baseS = 0, baseC = 0, totS = 0, totC = 0;
+    for (int k = 0; k < 8; k++) {
+        if (k < (int)w) { baseS += cntS[k]; baseC += cntC[k]; }
+        totS += cntS[k]; totC += cntC[k];
+    }
+    uint32_t rs = baseS + __popc(bs & ((1u << lane) - 1)), rc = baseC + __popc(bc & ((1u << lane) - 1));
+    O1Meta *m = meta + blockIdx.x;
+    m->smap[j] = present ? (uint8_t)rs : 0;
+    m->cmap[j] = isctx ? (uint8_t)rc : 0;
+    if (present) m->salpha[rs] = (uint8_t)j;
+    if (isctx) m->calpha[rc] = (uint8_t)j;
+    if (j == 0) { m->nsym = totS; m->nctx = totC; }
+    uint32_t *f1 = F1 + (size_t)blockIdx.x * 65536;
+    for (uint32_t i = j; i < totS * totC; i += 256) f1[i] = 0;
+    (void)desc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_hist1: grid (n_o1, chunks); 256 threads.  Counts (previous byte, byte) pairs of one chunk into a compact
+// (ctx rank x sym rank) table in shared memory, then adds the non-zero cells to the block's global table.
+__global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o1_blocks,
+                                               const uint8_t *__restrict__ d_in, const O1Meta *__restrict__ meta,
+                                               uint32_t *__restrict__ F1)
+{
+    const BlockDesc d = desc[o1_blocks[blockIdx.x]];
+    uint64_t start = (uint64_t)blockIdx.y * HIST_CHUNK;
+    if (start >= d.in_len) return;
+    uint32_t len = min((uint64_t)HIST_CHUNK, d.in_len - start);
+    const uint8_t *base = d_in + d.in_off;
+    const uint8_t *in = base + start;
+    const O1Meta *m = meta + blockIdx.x;
+    uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
+
+    __shared__ uint8_t cmap[256], smap[256];
+    __shared__ uint32_t cells[O1_SMEM_ENTRIES];
+    cmap[threadIdx.x] = m->cmap[threadIdx.x];
+    smap[threadIdx.x] = m->smap[threadIdx.x];
+    const uint32_t ns = m->nsym, ncell = m->nsym * m->nctx;
+    const bool in_smem = ncell <= O1_SMEM_ENTRIES;
+    if (in_smem) for (uint32_t i = threadIdx.x; i < ncell; i += 256) cells[i] = 0;
+    __syncthreads();
+    uint32_t *t = in_smem ? cells : g;
+
+    uint32_t nvec = len >> 4;
+    const uint4 *v = reinterpret_cast<const uint4 *>(in);
+    for (uint32_t i = threadIdx.x; i < nvec; i += 256) {
+        uint4 q = __ldg(v + i);
+        uint32_t w[4] = {q.x, q.y, q.z, q.w};
+        uint64_t gpos = start + ((uint64_t)i << 4);
+        uint32_t prev = gpos ? in[((int64_t)i << 4) - 1] : 0;   // last = 0 before the first byte [:152]
+        uint32_t row = cmap[prev] * ns;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                uint32_t c = (w[k] >> (8 * b)) & 0xFF;
+                atomicAdd(&t[row + smap[c]], 1u);
+                row = cmap[c] * ns;
+            }
+        }
+    }
+    for (uint32_t i = (nvec << 4) + threadIdx.x; i < len; i += 256) {
+        uint64_t gpos = start + i;
+        uint32_t prev = gpos ? base[gpos - 1] : 0;
+        atomicAdd(&t[cmap[prev] * ns + smap[in[i]]], 1u);
+    }
+    if (blockIdx.y == 0 && threadIdx.x < 3) {
+        // start symbols of lanes 1..3 are coded in context 0 [:163-166]
+        uint32_t q = d.in_len >> 2;
+        atomicAdd(&t[cmap[0] * ns + smap[base[(uint64_t)(threadIdx.x + 1) * q]]], 1u);
+    }
+    if (in_smem) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < ncell; i += 256) {
+            uint32_t c = cells[i];
+            if (c) atomicAdd(&g[i], c);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_tables0: one CTA (256 threads, thread j = symbol j) per order-0 block.
+__global__ void __launch_bounds__(256) k_tables0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o0_blocks,
+                                                 const uint32_t *__restrict__ F0, uint2 *__restrict__ syms0,
+                                                 uint8_t *__restrict__ work, uint32_t *__restrict__ tlen)
+{
+    uint32_t blk = o0_blocks[blockIdx.x];
+    const BlockDesc d = desc[blk];
+    uint32_t j = threadIdx.x, lane = j & 31, w = j >> 5;
+    uint32_t f = F0[(size_t)blk * 256 + j];
+    uint64_t T = d.in_len;
+    uint64_t tr = ((uint64_t)TOTFREQ << 31) / T + (1ull << 30) / T;              // [:118]
+
+    __shared__ unsigned long long redk[8];
+    __shared__ uint32_t reds[8];
+    __shared__ uint16_t rowF[256];
+    __shared__ uint32_t mask[8];
+    // M = first index of the maximum raw count [:123-126]
+    unsigned long long key = f ? (((unsigned long long)f << 32) | (255u - j)) : 0ull;
+    key = warp_max64(key);
+    uint32_t nf = f ? (uint32_t)(((uint64_t)f * tr) >> 31) : 0;                  // [:127]
+    if (f && nf == 0) nf = 1;
+    uint32_t s = warp_sum(nf);
+    if (lane == 0) { redk[w] = key; reds[w] = s; }
+    __syncthreads();
+    unsigned long long bk = 0; uint32_t fsum = 1;                                // fsum++ [:131]
+    for (int k = 0; k < 8; k++) { bk = redk[k] > bk ? redk[k] : bk; fsum += reds[k]; }
+    uint32_t M = 255u - (uint32_t)(bk & 0xFFFFFFFFu);
+    if (j == M) nf = (uint32_t)((int)nf + ((int)TOTFREQ - (int)fsum));           // [:132-135]
+    // cumulative start [buildSyms_o0 :197-211]
+    uint32_t ex = warp_excl_scan(nf, lane);
+    uint32_t wtot = __shfl_sync(0xFFFFFFFFu, ex + nf, 31);
+    __syncthreads();
+    if (lane == 0) reds[w] = wtot;
+    __syncthreads();
+    uint32_t base = 0;
+    for (int k = 0; k < (int)w; k++) base += reds[k];
+    if (nf) syms0[(size_t)blk * 256 + j] = make_enc_sym(base + ex, nf);
+    rowF[j] = (uint16_t)nf;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t n = warp_write_row(rowF, mask, work + d.work_off, lane);
+        if (lane == 0) tlen[blk] = n;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_tables1: one CTA (8 warps) per order-1 block; a warp owns one context row at a time.
+// Pass 1 normalises each row, writes its coder symbols and measures its serialised length; thread 0 then
+// lays out the table (context bytes use the same run-length rule over contexts with T != 0 [:275-296]);
+// pass 2 serialises the rows in place.
+__global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o1_blocks,
+                                                 const O1Meta *__restrict__ meta, uint32_t *__restrict__ F1,
+                                                 uint2 *__restrict__ syms1, uint8_t *__restrict__ work,
+                                                 uint32_t *__restrict__ tlen)
+{
+    uint32_t blk = o1_blocks[blockIdx.x];
+    const BlockDesc d = desc[blk];
+    const O1Meta *m = meta + blockIdx.x;
+    uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
+    uint2 *sy = syms1 + (size_t)blockIdx.x * 65536;
+    uint8_t *tab = work + d.work_off;
+    uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+
+    __shared__ uint8_t salpha[256], calpha[256];
+    __shared__ uint16_t rowF[8][256];
+    __shared__ uint32_t mask[8][8];
+    __shared__ uint32_t rowlen[256];   // 0 = context absent (T == 0)
+    __shared__ uint32_t rowoff[256];
+    __shared__ uint32_t total;
+    salpha[tid] = m->salpha[tid];
+    calpha[tid] = m->calpha[tid];
+    const uint32_t ns = m->nsym, nc = m->nctx;
+    __syncthreads();
+
+    for (int pass = 0; pass < 2; pass++) {
+        for (uint32_t r = w; r < nc; r += 8) {
+            if (pass == 1 && rowlen[r] == 0) continue;
+            for (int i = lane; i < 256; i += 32) rowF[w][i] = 0;
+            __syncwarp();
+            uint32_t *row = g + (size_t)r * ns;
+            uint32_t f[8];
+            uint32_t a0 = lane * 8;
+#pragma unroll
+            for (int i = 0; i < 8; i++) f[i] = (a0 + i < ns) ? row[a0 + i] : 0;
+            if (pass == 0) {
+                uint32_t T = 0;
+                unsigned long long key = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    T += f[i];
+                    unsigned long long k = f[i] ? (((unsigned long long)f[i] << 32) | (0xFFFFu - (a0 + i))) : 0ull;
+                    key = k > key ? k : key;
+                }
+                T = warp_sum(T);
+                if (T == 0) { if (lane == 0) rowlen[r] = 0; continue; }
+                key = warp_max64(key);
+                uint32_t M = 0xFFFFu - (uint32_t)(key & 0xFFFFFFFFu);
+                // double p = 4096.0 / T; F = (int)(F * p), IEEE double, no contraction [:170,181]
+                double p = __ddiv_rn(4096.0, (double)T);
+                uint32_t t2 = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    if (f[i]) {
+                        uint32_t nf = (uint32_t)__double2int_rz(__dmul_rn((double)f[i], p));
+                        f[i] = nf ? nf : 1;
+                        t2 += f[i];
+                    }
+                }
+                t2 = warp_sum(t2) + 1;                                            // t2++ [:186]
+                if (M >= a0 && M < a0 + 8) {
+#pragma unroll
+                    for (int i = 0; i < 8; i++)
+                        if (a0 + i == M) f[i] = (uint32_t)((int)f[i] + ((int)TOTFREQ - (int)t2));
+                }
+                uint32_t ls = 0;
+#pragma unroll
+                for (int i = 0; i < 8; i++) ls += f[i];
+                uint32_t x = warp_excl_scan(ls, lane);
+                uint2 *srow = sy + (size_t)calpha[r] * 256;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    if (a0 + i < ns) {
+                        row[a0 + i] = f[i];
+                        if (f[i]) { srow[salpha[a0 + i]] = make_enc_sym(x, f[i]); x += f[i]; }
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; i++)
+                if (a0 + i < ns && f[i]) rowF[w][salpha[a0 + i]] = (uint16_t)f[i];
+            __syncwarp();
+            uint32_t n = warp_write_row(rowF[w], mask[w], pass ? tab + rowoff[r] : nullptr, lane);
+            if (pass == 0 && lane == 0) rowlen[r] = n;
+        }
+        __syncthreads();
+        if (pass == 0 && tid == 0) {
+            uint32_t off = 0;
+            int rle = 0;
+            for (uint32_t r = 0; r < nc; r++) {
+                if (!rowlen[r]) continue;
+                uint32_t i = calpha[r];
+                if (rle > 0) rle--;
+                else {
+                    tab[off++] = (uint8_t)i;
+                    bool prev = r > 0 && rowlen[r - 1] && calpha[r - 1] + 1u == i;
+                    if (i > 0 && prev) {
+                        uint32_t e = r;
+                        while (e + 1 < nc && rowlen[e + 1] && calpha[e + 1] == calpha[e] + 1u) e++;
+                        rle = (int)(e - r);
+                        tab[off++] = (uint8_t)rle;
+                    }
+                }
+                rowoff[r] = off;
+                off += rowlen[r];
+            }
+            tab[off++] = 0;
+            total = off;
+        }
+        __syncthreads();
+    }
+    if (tid == 0) tlen[blk] = total;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The coder step.  Returns the new state; nb = renormalisation bytes (0..2), low byte of `bytes` is emitted first.
+__device__ __forceinline__ uint32_t put_symbol(uint32_t x, uint2 s, uint32_t &nb, uint32_t &bytes)
+{
+    uint32_t F = (s.y >> 13) & 0xFFFu, bias = s.y & 0x1FFFu, sh = s.y >> 25;
+    uint32_t x_max = F << 19;
+    bool c1 = x >= x_max;
+    bool c2 = (x >> 8) >= x_max;            // implies c1
+    bytes = x;
+    nb = (uint32_t)c1 + (uint32_t)c2;
+    x = c2 ? (x >> 16) : (c1 ? (x >> 8) : x);
+    uint32_t q = __umulhi(x, s.x) >> sh;
+    return x + bias + q * (TOTFREQ - F);
+}
+
+// Shared tail of both coders: place this step's bytes below the cursor and advance it.
+// Lanes of a 4-lane group emit in the order 3,2,1,0.
+__device__ __forceinline__ void emit_step(uint8_t *end, uint32_t &p, uint32_t cap, uint32_t nb, uint32_t bytes,
+                                          uint32_t lane, bool &overflow)
+{
+    uint32_t b1 = __ballot_sync(0xFFFFFFFFu, nb >= 1), b2 = __ballot_sync(0xFFFFFFFFu, nb == 2);
+    uint32_t g4 = lane & ~3u, k = lane & 3u;
+    uint32_t gm = 0xFu << g4;
+    uint32_t hm = (0xEu << k) & 0xFu;       // lanes above k inside the group
+    hm <<= g4;
+    uint32_t before = __popc(b1 & hm) + __popc(b2 & hm);
+    uint32_t tot = __popc(b1 & gm) + __popc(b2 & gm);
+    if (p + tot > cap) overflow = true;
+    if (nb && !overflow) {
+        uint32_t e = p + before;            // emission index of the first byte
+        end[-1 - (int64_t)e] = (uint8_t)bytes;
+        if (nb == 2) end[-2 - (int64_t)e] = (uint8_t)(bytes >> 8);
+    }
+    p += tot;
+}
+
+__device__ __forceinline__ void finish_block(uint8_t *end, uint32_t p, uint32_t cap, uint32_t x, uint32_t k,
+                                             bool overflow, uint32_t blk, uint32_t *plen, int32_t *status)
+{
+    // states 3,2,1,0 big-endian then reversed == states 0..3 little-endian in front of the payload [E04.java:46-50]
+    if (p + 16 > cap) overflow = true;
+    if (!overflow) {
+        uint8_t *s = end - p - 16 + 4 * k;
+        s[0] = (uint8_t)x; s[1] = (uint8_t)(x >> 8); s[2] = (uint8_t)(x >> 16); s[3] = (uint8_t)(x >> 24);
+    }
+    if (k == 0) {
+        plen[blk] = overflow ? 0 : p + 16;
+        if (overflow) status[blk] = CRAMGPU_ERR_OUT_TOO_SMALL;
+    }
+}
+
+// k_enc0: 1 warp per CTA, 8 blocks per warp, lane k of a group owns state k (symbols k, k+4, k+8, ...).
+__global__ void __launch_bounds__(32) k_enc0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                             const uint2 *__restrict__ syms0, uint8_t *__restrict__ work,
+                                             uint32_t *__restrict__ plen, int32_t *__restrict__ status)
+{
+    uint32_t lane = threadIdx.x, k = lane & 3u;
+    uint32_t slot = blockIdx.x * 8 + (lane >> 2);
+    bool have = slot < nslots;
+    uint32_t blk = have ? slots[slot] : 0;
+    BlockDesc d = desc[blk];
+    uint32_t n = have ? d.in_len : 0;
+    const uint8_t *in = d_in + d.in_off;
+    const uint2 *st = syms0 + (size_t)blk * 256;
+    uint32_t cap = d.work_cap - d.tab_cap;
+    uint8_t *end = work + d.work_off + d.work_cap;
+
+    uint32_t steps = (n + 3) >> 2;
+    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    uint32_t x = RANS_L, p = 0;
+    bool overflow = false;
+
+    // software pipeline: byte two steps ahead, symbol one step ahead (neither depends on the state)
+    auto idx_of = [&](uint32_t t) -> int64_t {      // symbol index handled by this lane in loop step t, or -1
+        if (t >= steps) return -1;
+        uint64_t i = (uint64_t)(steps - 1 - t) * 4 + k;
+        return i < n ? (int64_t)i : -1;
+    };
+    int64_t i0 = idx_of(0), i1 = idx_of(1);
+    uint2 sym_next = make_uint2(0, 0);
+    bool act_next = i0 >= 0;
+    if (act_next) sym_next = __ldg(st + __ldg(in + i0));
+    uint32_t c_next = i1 >= 0 ? __ldg(in + i1) : 0;
+    bool act_next2 = i1 >= 0;
+
+    for (uint32_t t = 0; t < max_steps; t++) {
+        uint2 s = sym_next;
+        bool act = act_next;
+        act_next = act_next2;
+        if (act_next) sym_next = __ldg(st + c_next);
+        int64_t i2 = idx_of(t + 2);
+        act_next2 = i2 >= 0;
+        if (act_next2) c_next = __ldg(in + i2);
+
+        uint32_t nb = 0, bytes = 0;
+        if (act) x = put_symbol(x, s, nb, bytes);
+        emit_step(end, p, cap, nb, bytes, lane, overflow);
+    }
+    if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
+}
+
+// k_enc1: lane k owns the quarter [k*q, (k+1)*q), lane 3 also the remainder; coded backwards,
+// symbol = in[j], context = in[j-1] (0 for the first byte of the quarter) [E14.java:24-71].
+__global__ void __launch_bounds__(32) k_enc1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                             const uint2 *__restrict__ syms1, uint8_t *__restrict__ work,
+                                             uint32_t *__restrict__ plen, int32_t *__restrict__ status)
+{
+    uint32_t lane = threadIdx.x, k = lane & 3u;
+    uint32_t slot = blockIdx.x * 8 + (lane >> 2);
+    bool have = slot < nslots;
+    uint32_t blk = have ? slots[slot] : 0;
+    BlockDesc d = desc[blk];
+    uint32_t n = have ? d.in_len : 0;
+    uint32_t q = n >> 2;
+    const uint8_t *in = d_in + d.in_off + (uint64_t)k * q;          // this lane's quarter
+    uint32_t mylen = (k == 3) ? n - 3 * q : q;
+    const uint2 *st = syms1 + (size_t)d.o1_index * 65536;
+    uint32_t cap = d.work_cap - d.tab_cap;
+    uint8_t *end = work + d.work_off + d.work_cap;
+
+    uint32_t steps = n - 3 * q;                                     // lane 3's length = longest
+    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    uint32_t x = RANS_L, p = 0;
+    bool overflow = false;
+
+    // step t codes local index j = steps-1-t; pipeline: bytes two steps ahead, symbol one step ahead
+    auto j_of = [&](uint32_t t) -> int64_t {
+        if (t >= steps) return -1;
+        uint32_t j = steps - 1 - t;
+        return j < mylen ? (int64_t)j : -1;
+    };
+    auto pair_of = [&](int64_t j) -> uint32_t {                     // ctx*256 + sym
+        uint32_t l = __ldg(in + j);
+        uint32_t c = j > 0 ? __ldg(in + j - 1) : 0;
+        return c * 256 + l;
+    };
+    int64_t j0 = j_of(0), j1 = j_of(1);
+    bool act_next = j0 >= 0, act_next2 = j1 >= 0;
+    uint2 sym_next = make_uint2(0, 0);
+    if (act_next) sym_next = __ldg(st + pair_of(j0));
+    uint32_t pr_next = act_next2 ? pair_of(j1) : 0;
+
+    for (uint32_t t = 0; t < max_steps; t++) {
+        uint2 s = sym_next;
+        bool act = act_next;
+        act_next = act_next2;
+        if (act_next) sym_next = __ldg(st + pr_next);
+        int64_t j2 = j_of(t + 2);
+        act_next2 = j2 >= 0;
+        if (act_next2) pr_next = pair_of(j2);
+
+        uint32_t nb = 0, bytes = 0;
+        if (act) x = put_symbol(x, s, nb, bytes);
+        emit_step(end, p, cap, nb, bytes, lane, overflow);
+    }
+    if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_scan_out: one CTA; out_off[i] = sum of roundup16(len) of the blocks before i.
+__global__ void __launch_bounds__(1024) k_scan_out(const BlockDesc *__restrict__ desc, uint32_t nblocks,
+                                                   const uint32_t *__restrict__ tlen, const uint32_t *__restrict__ plen,
+                                                   uint64_t out_cap, uint64_t *__restrict__ out_off,
+                                                   uint32_t *__restrict__ out_len, int32_t *__restrict__ status)
+{
+    __shared__ uint64_t wsum[32];
+    __shared__ uint64_t carry;
+    uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < nblocks; base += 1024) {
+        uint32_t i = base + tid;
+        uint32_t len = 0;
+        if (i < nblocks && desc[i].order <= 1 && status[i] == 0) len = 9 + tlen[i] + plen[i];
+        uint64_t a = (len + 15u) & ~15ull;
+        uint64_t s = a;
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            uint64_t t = __shfl_up_sync(0xFFFFFFFFu, s, dlt);
+            if (lane >= (uint32_t)dlt) s += t;
+        }
+        if (lane == 31) wsum[w] = s;
+        __syncthreads();
+        uint64_t off = carry;
+        for (uint32_t k = 0; k < w; k++) off += wsum[k];
+        off += s - a;
+        if (i < nblocks) {
+            if (off + a > out_cap && len) { status[i] = CRAMGPU_ERR_OUT_TOO_SMALL; len = 0; }
+            out_off[i] = off;
+            out_len[i] = len;
+        }
+        __syncthreads();
+        if (tid == 1023) carry = off + a;
+        __syncthreads();
+    }
+    if (tid == 0) out_off[nblocks] = carry;
+}
+
+// k_pack: grid (nblocks, chunks): prefix [RANS.java:132-142] + table + payload -> output.
+__global__ void __launch_bounds__(256) k_pack(const BlockDesc *__restrict__ desc, const uint8_t *__restrict__ work,
+                                              const uint32_t *__restrict__ tlen, const uint32_t *__restrict__ plen,
+                                              const uint64_t *__restrict__ out_off, const uint32_t *__restrict__ out_len,
+                                              uint8_t *__restrict__ d_out)
+{
+    uint32_t blk = blockIdx.x;
+    uint32_t total = out_len[blk];
+    uint64_t start = (uint64_t)blockIdx.y * PACK_CHUNK;
+    if (start >= total) return;
+    const BlockDesc d = desc[blk];
+    uint32_t tl = tlen[blk], pl = plen[blk];
+    const uint8_t *tab = work + d.work_off;
+    const uint8_t *pay = work + d.work_off + d.work_cap - pl;
+    uint8_t *out = d_out + out_off[blk];
+    uint32_t stop = min((uint64_t)total, start + PACK_CHUNK);
+    uint32_t csize = tl + pl;
+    for (uint32_t i = start + threadIdx.x; i < stop; i += 256) {
+        uint8_t b;
+        if (i >= 9 + tl) b = pay[i - 9 - tl];
+        else if (i >= 9) b = tab[i - 9];
+        else if (i == 0) b = (uint8_t)d.order;
+        else if (i < 5) b = (uint8_t)(csize >> (8 * (i - 1)));
+        else b = (uint8_t)(d.in_len >> (8 * (i - 5)));
+        out[i] = b;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host launcher
+
+uint32_t cramgpu_rans_bound(uint32_t n)
+{
+    return (uint32_t)(int)(1.05 * (double)n + 257 * 257 * 3 + 4);
+}
+
+#include <algorithm>
+
+int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
+                       const uint32_t *in_len, const uint8_t *order, uint8_t *d_out, uint64_t out_cap,
+                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st)
+{
+    if (nblocks == 0) return CRAMGPU_OK;
+    if (!d_in || !in_off || !in_len || !order || !d_out_off || !d_out_len || !d_status)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+
+    // ---- plan (host): effective order, work areas, length-sorted slot lists
+    std::vector<BlockDesc> desc(nblocks);
+    std::vector<int32_t> hstatus(nblocks, 0);
+    std::vector<uint32_t> o0, o1;
+    uint64_t work_total = 0;
+    uint32_t max_len = 0;
+    for (uint32_t i = 0; i < nblocks; i++) {
+        BlockDesc &d = desc[i];
+        d = BlockDesc();
+        d.in_off = in_off[i];
+        d.in_len = in_len[i];
+        if (in_off[i] & 15) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in_off[%u] is not a multiple of 16", i);
+        uint32_t ord = order[i];
+        if (d.in_len == 0) { d.order = 0xFF; continue; }                       // empty -> empty [RANS.java:60-61]
+        if (ord > 1) { d.order = 0xFF; hstatus[i] = CRAMGPU_ERR_UNKNOWN_ORDER; continue; }
+        if (d.in_len < 4) ord = 0;                                             // [RANS.java:63-64]
+        d.order = ord;
+        d.tab_cap = ord ? O1_TAB_CAP : O0_TAB_CAP;
+        uint64_t pay_cap = rup((uint64_t)d.in_len + d.in_len / 4 + 64, 16);
+        d.work_cap = (uint32_t)(d.tab_cap + pay_cap);
+        d.work_off = work_total;
+        work_total += rup(d.work_cap, 256);
+        if (ord) { d.o1_index = (uint32_t)o1.size(); o1.push_back(i); } else o0.push_back(i);
+        max_len = std::max(max_len, d.in_len);
+    }
+    auto by_len = [&](uint32_t a, uint32_t b) { return desc[a].in_len > desc[b].in_len; };
+    std::vector<uint32_t> s0 = o0, s1 = o1;
+    std::stable_sort(s0.begin(), s0.end(), by_len);
+    std::stable_sort(s1.begin(), s1.end(), by_len);
+    const uint32_t n0 = (uint32_t)o0.size(), n1 = (uint32_t)o1.size();
+
+    // ---- carve scratch
+    Carver c;
+    size_t o_desc = c.take(sizeof(BlockDesc) * nblocks);
+    size_t o_o0 = c.take(4 * (size_t)std::max(n0, 1u)), o_o1 = c.take(4 * (size_t)std::max(n1, 1u));
+    size_t o_s0 = c.take(4 * (size_t)std::max(n0, 1u)), o_s1 = c.take(4 * (size_t)std::max(n1, 1u));
+    size_t o_F0 = c.take(1024 * (size_t)nblocks);
+    size_t o_tlen = c.take(4 * (size_t)nblocks), o_plen = c.take(4 * (size_t)nblocks);
+    size_t o_zero_end = c.off;                                                  // [o_F0, here) is zeroed
+    size_t o_syms0 = c.take(2048 * (size_t)nblocks);
+    size_t o_meta = c.take(sizeof(O1Meta) * (size_t)std::max(n1, 1u));
+    size_t o_F1 = c.take(262144 * (size_t)n1 + 16);
+    size_t o_syms1 = c.take(524288 * (size_t)n1 + 16);
+    size_t o_work = c.take(work_total + 256);
+    if (int rc = pool_reserve(ctx, ctx->scratch, c.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->scratch.p;
+
+    // ---- upload the plan through pinned memory
+    size_t meta_bytes = sizeof(BlockDesc) * nblocks + 4 * (size_t)(2 * n0 + 2 * n1) + 4 * (size_t)nblocks + 64;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, meta_bytes)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev));       // previous call may still be reading the pinned plan
+    uint8_t *pm = (uint8_t *)ctx->pin_meta;
+    size_t po = 0;
+    auto up = [&](const void *src, size_t bytes, void *dst) -> cudaError_t {
+        if (!bytes) return cudaSuccess;
+        memcpy(pm + po, src, bytes);
+        cudaError_t e = cudaMemcpyAsync(dst, pm + po, bytes, cudaMemcpyHostToDevice, st);
+        po += rup(bytes, 16);
+        return e;
+    };
+    CUDA_TRY(ctx, up(desc.data(), sizeof(BlockDesc) * nblocks, S + o_desc));
+    CUDA_TRY(ctx, up(o0.data(), 4 * (size_t)n0, S + o_o0));
+    CUDA_TRY(ctx, up(o1.data(), 4 * (size_t)n1, S + o_o1));
+    CUDA_TRY(ctx, up(s0.data(), 4 * (size_t)n0, S + o_s0));
+    CUDA_TRY(ctx, up(s1.data(), 4 * (size_t)n1, S + o_s1));
+    CUDA_TRY(ctx, up(hstatus.data(), 4 * (size_t)nblocks, d_status));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_F0, 0, o_zero_end - o_F0, st));
+
+    const BlockDesc *dd = (const BlockDesc *)(S + o_desc);
+    uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
+    uint2 *syms0 = (uint2 *)(S + o_syms0), *syms1 = (uint2 *)(S + o_syms1);
+    O1Meta *meta = (O1Meta *)(S + o_meta);
+    uint32_t *F1 = (uint32_t *)(S + o_F1);
+    uint8_t *work = S + o_work;
+    const uint32_t *d_o0 = (const uint32_t *)(S + o_o0), *d_o1 = (const uint32_t *)(S + o_o1);
+    const uint32_t *d_s0 = (const uint32_t *)(S + o_s0), *d_s1 = (const uint32_t *)(S + o_s1);
+
+    if (n0 + n1) {
+        uint32_t chunks = (max_len + HIST_CHUNK - 1) / HIST_CHUNK;
+        k_hist0<<<dim3(nblocks, chunks), 256, 0, st>>>(dd, d_in, F0);
+        ctx->launches++;
+        if (n1) {
+            uint32_t max1 = desc[s1[0]].in_len;
+            k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1);
+            k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1);
+            k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen);
+            k_enc1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, d_s1, n1, d_in, syms1, work, plen, d_status);
+            ctx->launches += 4;
+        }
+        if (n0) {
+            k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen);
+            k_enc0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, d_s0, n0, d_in, syms0, work, plen, d_status);
+            ctx->launches += 2;
+        }
+    }
+    k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    ctx->pend = EncodePending{dd, work, tlen, plen, d_out_off, d_out_len, nblocks,
+                              (n0 + n1) ? 9 + (uint64_t)(n1 ? O1_TAB_CAP : O0_TAB_CAP) + max_len + max_len / 4 + 80 : 0};
+    if (d_out) return rans_encode_pack(ctx, d_out, st);
+    return CRAMGPU_OK;
+}
+
+// second half of the encode pipeline: needs the output buffer (the host entry point sizes it from the
+// device-computed total before calling this)
+int rans_encode_pack(cramgpu_ctx *ctx, uint8_t *d_out, cudaStream_t st)
+{
+    const EncodePending &p = ctx->pend;
+    if (p.max_out) {
+        k_pack<<<dim3(p.nblocks, (uint32_t)((p.max_out + PACK_CHUNK - 1) / PACK_CHUNK)), 256, 0, st>>>(
+            p.desc, p.work, p.tlen, p.plen, p.out_off, p.out_len, d_out);
+        ctx->launches++;
+        CUDA_TRY(ctx, cudaGetLastError());
+    }
+    return CRAMGPU_OK;
+}

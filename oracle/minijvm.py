@@ -1,0 +1,1098 @@
+"""oracle/minijvm.py -- TEST INFRASTRUCTURE ONLY.
+
+A deliberately small Java bytecode interpreter, just large enough to EXECUTE the
+reference's own rANS classes (htsjdk/samtools/cram/encoding/rans/*.class and a few
+other leaf classes) straight out of /root/reference/cramtools-3.0.jar.  There is no
+JVM in the build container, so this is how golden vectors for the hot path are
+produced from the reference itself rather than from a restatement:
+
+    python oracle/make_golden.py      # runs the jar's bytecode, writes tests/golden/*.json
+
+It is slow (pure Python, ~1 M bytecodes/s), so vectors are small.  Nothing at run time
+(tests on the GPU box, smoke(), bench.py) imports this module or needs the jar: the
+vectors are committed.
+
+Supported: the class-file format (constant pool, fields, methods, Code attribute,
+exception tables), ints/longs/doubles/floats with Java wrap-around semantics, arrays, objects,
+static init, enums, tableswitch/lookupswitch, exceptions thrown by `athrow` (surfaced
+as JavaThrow), and emulations of the handful of JDK classes the rANS code touches
+(java.nio.ByteBuffer/ByteOrder, System.arraycopy, Arrays.fill, StringBuilder, Math).
+"""
+import struct
+import zipfile
+
+# ----------------------------------------------------------------------------- class file
+
+
+class ClassFile:
+    def __init__(self, data):
+        self.data = data
+        self.pos = 0
+        magic = self.u4()
+        assert magic == 0xCAFEBABE
+        self.u2(); self.u2()
+        n = self.u2()
+        self.cp = [None] * n
+        i = 1
+        while i < n:
+            tag = self.u1()
+            if tag == 1:
+                ln = self.u2()
+                self.cp[i] = ('utf8', self.data[self.pos:self.pos + ln].decode('utf-8', 'replace'))
+                self.pos += ln
+            elif tag == 3:
+                self.cp[i] = ('int', struct.unpack('>i', self.raw(4))[0])
+            elif tag == 4:
+                self.cp[i] = ('float', struct.unpack('>f', self.raw(4))[0])
+            elif tag == 5:
+                self.cp[i] = ('long', struct.unpack('>q', self.raw(8))[0]); i += 1
+            elif tag == 6:
+                self.cp[i] = ('double', struct.unpack('>d', self.raw(8))[0]); i += 1
+            elif tag == 7:
+                self.cp[i] = ('class', self.u2())
+            elif tag == 8:
+                self.cp[i] = ('string', self.u2())
+            elif tag in (9, 10, 11):
+                self.cp[i] = ({9: 'field', 10: 'method', 11: 'imethod'}[tag], self.u2(), self.u2())
+            elif tag == 12:
+                self.cp[i] = ('nat', self.u2(), self.u2())
+            elif tag == 15:
+                self.cp[i] = ('mh', self.u1(), self.u2())
+            elif tag == 16:
+                self.cp[i] = ('mt', self.u2())
+            elif tag == 18:
+                self.cp[i] = ('indy', self.u2(), self.u2())
+            else:
+                raise ValueError('cp tag %d' % tag)
+            i += 1
+        self.access = self.u2()
+        self.name = self.class_name(self.u2())
+        sup = self.u2()
+        self.super_name = self.class_name(sup) if sup else None
+        self.interfaces = [self.class_name(self.u2()) for _ in range(self.u2())]
+        self.fields = []
+        for _ in range(self.u2()):
+            acc, nm, ds = self.u2(), self.utf(self.u2()), self.utf(self.u2())
+            attrs = self.attrs()
+            self.fields.append((acc, nm, ds, attrs))
+        self.methods = {}
+        for _ in range(self.u2()):
+            acc, nm, ds = self.u2(), self.utf(self.u2()), self.utf(self.u2())
+            attrs = self.attrs()
+            self.methods[(nm, ds)] = Method(self, acc, nm, ds, attrs)
+
+    def raw(self, n):
+        b = self.data[self.pos:self.pos + n]; self.pos += n; return b
+
+    def u1(self):
+        v = self.data[self.pos]; self.pos += 1; return v
+
+    def u2(self):
+        v = struct.unpack_from('>H', self.data, self.pos)[0]; self.pos += 2; return v
+
+    def u4(self):
+        v = struct.unpack_from('>I', self.data, self.pos)[0]; self.pos += 4; return v
+
+    def utf(self, i):
+        return self.cp[i][1]
+
+    def class_name(self, i):
+        return self.utf(self.cp[i][1])
+
+    def attrs(self):
+        out = {}
+        for _ in range(self.u2()):
+            nm = self.utf(self.u2()); ln = self.u4()
+            out[nm] = self.raw(ln)
+        return out
+
+    def member_ref(self, i):
+        _, ci, nti = self.cp[i]
+        _, ni, di = self.cp[nti]
+        return self.class_name(ci), self.utf(ni), self.utf(di)
+
+
+class Method:
+    def __init__(self, cf, acc, name, desc, attrs):
+        self.cf, self.acc, self.name, self.desc = cf, acc, name, desc
+        self.static = bool(acc & 0x0008)
+        self.code = None
+        self.lines = []
+        if 'Code' in attrs:
+            a = attrs['Code']
+            self.max_stack, self.max_locals, cl = struct.unpack_from('>HHI', a, 0)
+            self.code = a[8:8 + cl]
+            p = 8 + cl
+            n = struct.unpack_from('>H', a, p)[0]; p += 2
+            self.extable = []
+            for _ in range(n):
+                self.extable.append(struct.unpack_from('>HHHH', a, p)); p += 8
+            na = struct.unpack_from('>H', a, p)[0]; p += 2
+            for _ in range(na):
+                ni, ln = struct.unpack_from('>HI', a, p); p += 6
+                if cf.utf(ni) == 'LineNumberTable':
+                    k = struct.unpack_from('>H', a, p)[0]
+                    for t in range(k):
+                        self.lines.append(struct.unpack_from('>HH', a, p + 2 + 4 * t))
+                p += ln
+        self.nargs = self._count_args(desc)
+
+    @staticmethod
+    def _count_args(desc):
+        """list of slot widths of the parameters"""
+        out = []; i = 1
+        while desc[i] != ')':
+            c = desc[i]
+            if c in 'JD':
+                out.append(2); i += 1
+            elif c == 'L':
+                out.append(1); i = desc.index(';', i) + 1
+            elif c == '[':
+                while desc[i] == '[':
+                    i += 1
+                if desc[i] == 'L':
+                    i = desc.index(';', i) + 1
+                else:
+                    i += 1
+                out.append(1)
+            else:
+                out.append(1); i += 1
+        return out
+
+    def line_of(self, pc):
+        best = None
+        for spc, ln in self.lines:
+            if spc <= pc:
+                best = ln
+        return best
+
+
+# ----------------------------------------------------------------------------- runtime objects
+
+
+class JavaThrow(Exception):
+    def __init__(self, obj):
+        self.obj = obj
+        Exception.__init__(self, '%s: %s' % (obj.cls, obj.fields.get('message')))
+
+
+class JObject:
+    __slots__ = ('cls', 'fields')
+
+    def __init__(self, cls):
+        self.cls = cls
+        self.fields = {}
+
+    def __repr__(self):
+        return '<%s %r>' % (self.cls, self.fields)
+
+
+class JArray:
+    __slots__ = ('kind', 'a')
+
+    def __init__(self, kind, a):
+        self.kind, self.a = kind, a
+
+
+def i32(v):
+    v &= 0xFFFFFFFF
+    return v - 0x100000000 if v & 0x80000000 else v
+
+
+def i64(v):
+    v &= 0xFFFFFFFFFFFFFFFF
+    return v - 0x10000000000000000 if v & 0x8000000000000000 else v
+
+
+def i8(v):
+    v &= 0xFF
+    return v - 256 if v & 0x80 else v
+
+
+def i16(v):
+    v &= 0xFFFF
+    return v - 65536 if v & 0x8000 else v
+
+
+def d2i(d, bits):
+    if d != d:
+        return 0
+    lo, hi = -(1 << (bits - 1)), (1 << (bits - 1)) - 1
+    if d >= hi:
+        return hi
+    if d <= lo:
+        return lo
+    return int(d)
+
+
+class ByteOrder:
+    def __init__(self, name):
+        self.name = name
+
+
+BIG = ByteOrder('BIG_ENDIAN')
+LITTLE = ByteOrder('LITTLE_ENDIAN')
+
+
+class ByteBuffer:
+    """java.nio.HeapByteBuffer semantics, the subset the CRAM code uses."""
+
+    def __init__(self, arr, offset, cap):
+        self.arr = arr          # python bytearray shared with JArray('B')
+        self.offset = offset
+        self.cap = cap
+        self.position = 0
+        self.limit = cap
+        self.order = BIG
+        self.jarray = None
+
+    def _chk(self, vm, n):
+        if self.limit - self.position < n:
+            vm.throw('java/nio/BufferUnderflowException' , None)
+
+    def _chkw(self, vm, n):
+        if self.limit - self.position < n:
+            vm.throw('java/nio/BufferOverflowException', None)
+
+
+# ----------------------------------------------------------------------------- the VM
+
+
+class MiniJVM:
+    def __init__(self, jar_paths):
+        self.jars = [zipfile.ZipFile(p) for p in jar_paths]
+        self.classes = {}
+        self.statics = {}
+        self.initialized = set()
+        self.nbytecodes = 0
+        self.strings = {}
+
+    # ---- loading
+    def load(self, name):
+        cf = self.classes.get(name)
+        if cf is None:
+            data = None
+            for z in self.jars:
+                try:
+                    data = z.read(name + '.class'); break
+                except KeyError:
+                    pass
+            if data is None:
+                raise KeyError('class not in jar: ' + name)
+            cf = ClassFile(data)
+            self.classes[name] = cf
+        if name not in self.initialized:
+            self.initialized.add(name)
+            if cf.super_name and not cf.super_name.startswith('java/'):
+                self.load(cf.super_name)
+            for acc, nm, ds, attrs in cf.fields:
+                if acc & 0x0008:
+                    v = 0.0 if ds in 'DF' else (0 if ds in 'IJSBCZ' else None)
+                    if 'ConstantValue' in attrs:
+                        ci = struct.unpack('>H', attrs['ConstantValue'])[0]
+                        v = cf.cp[ci][1]
+                    self.statics[(name, nm)] = v
+            m = cf.methods.get(('<clinit>', '()V'))
+            if m:
+                self.invoke(m, [])
+        return cf
+
+    def is_jdk(self, name):
+        return name.startswith('java/')
+
+    def find_method(self, cname, name, desc):
+        c = cname
+        while c and not self.is_jdk(c):
+            cf = self.load(c)
+            m = cf.methods.get((name, desc))
+            if m:
+                return m
+            c = cf.super_name
+        return None
+
+    def find_static_owner(self, cname, fname):
+        c = cname
+        while c and not self.is_jdk(c):
+            if (c, fname) in self.statics:
+                return c
+            cf = self.load(c)
+            if (c, fname) in self.statics:
+                return c
+            c = cf.super_name
+        raise KeyError((cname, fname))
+
+    def instance_of(self, obj, cname):
+        if obj is None:
+            return False
+        c = obj.cls if isinstance(obj, JObject) else None
+        if isinstance(obj, ByteBuffer):
+            return cname in ('java/nio/ByteBuffer', 'java/nio/Buffer', 'java/lang/Object')
+        if isinstance(obj, JArray):
+            return True
+        while c:
+            if c == cname:
+                return True
+            if self.is_jdk(c):
+                return JDK_SUPERS.get(c) is not None and self.instance_of_jdk(c, cname)
+            cf = self.load(c)
+            if cname in cf.interfaces:
+                return True
+            c = cf.super_name
+        return False
+
+    def instance_of_jdk(self, c, cname):
+        while c:
+            if c == cname:
+                return True
+            c = JDK_SUPERS.get(c)
+        return False
+
+    # ---- helpers
+    def new_string(self, s):
+        return s  # java.lang.String modelled as python str
+
+    def throw(self, cname, msg):
+        o = JObject(cname)
+        o.fields['message'] = msg
+        raise JavaThrow(o)
+
+    def new_array(self, atype, n):
+        if n < 0:
+            self.throw('java/lang/NegativeArraySizeException', None)
+        if atype in ('B',):
+            return JArray('B', bytearray(n))
+        if atype in ('Z',):
+            return JArray('Z', [0] * n)
+        if atype in ('D', 'F'):
+            return JArray(atype, [0.0] * n)
+        if atype in ('I', 'J', 'S', 'C'):
+            return JArray(atype, [0] * n)
+        return JArray('L', [None] * n)
+
+    def multi_array(self, desc, dims):
+        # desc like [[I
+        if len(dims) == 1:
+            return self.new_array(desc[1] if desc[1] != 'L' and desc[1] != '[' else 'L', dims[0])
+        arr = JArray('L', [None] * dims[0])
+        for i in range(dims[0]):
+            arr.a[i] = self.multi_array(desc[1:], dims[1:])
+        return arr
+
+    # ---- interpreter
+    def call(self, cname, name, desc, args):
+        self.load(cname)
+        m = self.find_method(cname, name, desc)
+        if m is None:
+            raise KeyError((cname, name, desc))
+        return self.invoke(m, args)
+
+    def invoke(self, m, args):
+        if m.code is None:
+            raise NotImplementedError('native/abstract %s.%s%s' % (m.cf.name, m.name, m.desc))
+        loc = [None] * m.max_locals
+        i = 0
+        if not m.static:
+            loc[0] = args[0]; i = 1
+            args = args[1:]
+        for w, a in zip(m.nargs, args):
+            loc[i] = a; i += w
+        return self.run(m, loc)
+
+    def run(self, m, loc):
+        code = m.code
+        cf = m.cf
+        cp = cf.cp
+        st = []
+        push = st.append
+        pop = st.pop
+        pc = 0
+        up = struct.unpack_from
+        while True:
+            try:
+                while True:
+                    op = code[pc]
+                    self.nbytecodes += 1
+                    # --- constants
+                    if op == 0:
+                        pc += 1
+                    elif op == 1:
+                        push(None); pc += 1
+                    elif 2 <= op <= 8:
+                        push(op - 3); pc += 1
+                    elif op in (9, 10):
+                        push(op - 9); pc += 1
+                    elif 11 <= op <= 13:
+                        push(float(op - 11)); pc += 1
+                    elif op in (14, 15):
+                        push(float(op - 14)); pc += 1
+                    elif op == 16:
+                        push(i8(code[pc + 1])); pc += 2
+                    elif op == 17:
+                        push(up('>h', code, pc + 1)[0]); pc += 3
+                    elif op in (18, 19, 20):
+                        if op == 18:
+                            idx = code[pc + 1]; pc += 2
+                        else:
+                            idx = up('>H', code, pc + 1)[0]; pc += 3
+                        e = cp[idx]
+                        if e[0] == 'string':
+                            push(cf.utf(e[1]))
+                        elif e[0] == 'class':
+                            push(('class', cf.utf(e[1])))
+                        else:
+                            push(e[1])
+                    # --- loads
+                    elif 21 <= op <= 25:
+                        push(loc[code[pc + 1]]); pc += 2
+                    elif 26 <= op <= 45:
+                        push(loc[(op - 26) & 3]); pc += 1
+                    elif 46 <= op <= 53:   # array loads
+                        idx = pop(); arr = pop()
+                        if arr is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        if idx < 0 or idx >= len(arr.a):
+                            self.throw('java/lang/ArrayIndexOutOfBoundsException', str(idx))
+                        v = arr.a[idx]
+                        if op == 51 and arr.kind == 'B':
+                            v = v - 256 if v & 0x80 else v
+                        push(v); pc += 1
+                    # --- stores
+                    elif 54 <= op <= 58:
+                        loc[code[pc + 1]] = pop(); pc += 2
+                    elif 59 <= op <= 78:
+                        loc[(op - 59) & 3] = pop(); pc += 1
+                    elif 79 <= op <= 86:   # array stores
+                        v = pop(); idx = pop(); arr = pop()
+                        if arr is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        if idx < 0 or idx >= len(arr.a):
+                            self.throw('java/lang/ArrayIndexOutOfBoundsException', str(idx))
+                        if op == 84:
+                            v = v & 0xFF if arr.kind == 'B' else (1 if v & 1 else 0)
+                        elif op == 85:
+                            v &= 0xFFFF
+                        elif op == 86:
+                            v = i16(v)
+                        arr.a[idx] = v; pc += 1
+                    # --- stack
+                    elif op == 87:
+                        pop(); pc += 1
+                    elif op == 88:
+                        v = pop()
+                        if not self._is_wide(m, v):
+                            pop()
+                        pc += 1
+                    elif op == 89:
+                        push(st[-1]); pc += 1
+                    elif op == 90:
+                        v1 = pop(); v2 = pop(); push(v1); push(v2); push(v1); pc += 1
+                    elif op == 91:  # dup_x2 (treat wide values as single python items)
+                        v1 = pop(); v2 = pop()
+                        if isinstance(v2, WIDE):
+                            push(v1); push(v2); push(v1)
+                        else:
+                            v3 = pop(); push(v1); push(v3); push(v2); push(v1)
+                        pc += 1
+                    elif op == 92:  # dup2
+                        v1 = st[-1]
+                        if isinstance(v1, WIDE):
+                            push(v1)
+                        else:
+                            v2 = st[-2]; push(v2); push(v1)
+                        pc += 1
+                    elif op == 93:  # dup2_x1
+                        v1 = pop()
+                        if isinstance(v1, WIDE):
+                            v2 = pop(); push(v1); push(v2); push(v1)
+                        else:
+                            v2 = pop(); v3 = pop(); push(v2); push(v1); push(v3); push(v2); push(v1)
+                        pc += 1
+                    elif op == 95:
+                        v1 = pop(); v2 = pop(); push(v1); push(v2); pc += 1
+                    # --- int arithmetic
+                    elif op == 96:
+                        b = pop(); a = pop(); push(i32(a + b)); pc += 1
+                    elif op == 97:
+                        b = pop(); a = pop(); push(L(i64(a + b))); pc += 1
+                    elif op in (98, 99):
+                        b = pop(); a = pop(); push(D(a + b) if op == 99 else a + b); pc += 1
+                    elif op == 100:
+                        b = pop(); a = pop(); push(i32(a - b)); pc += 1
+                    elif op == 101:
+                        b = pop(); a = pop(); push(L(i64(a - b))); pc += 1
+                    elif op in (102, 103):
+                        b = pop(); a = pop(); push(D(a - b) if op == 103 else a - b); pc += 1
+                    elif op == 104:
+                        b = pop(); a = pop(); push(i32(a * b)); pc += 1
+                    elif op == 105:
+                        b = pop(); a = pop(); push(L(i64(a * b))); pc += 1
+                    elif op in (106, 107):
+                        b = pop(); a = pop(); push(D(a * b) if op == 107 else a * b); pc += 1
+                    elif op in (108, 109):
+                        b = pop(); a = pop()
+                        if b == 0:
+                            self.throw('java/lang/ArithmeticException', '/ by zero')
+                        q = abs(a) // abs(b)
+                        if (a < 0) != (b < 0):
+                            q = -q
+                        push(i32(q) if op == 108 else L(i64(q))); pc += 1
+                    elif op in (110, 111):
+                        b = pop(); a = pop()
+                        if b == 0.0:
+                            r = float('nan') if a == 0.0 or a != a else (float('inf') if (a > 0) == (str(b)[0] != '-') else float('-inf'))
+                        else:
+                            r = a / b
+                        push(D(r) if op == 111 else r); pc += 1
+                    elif op in (112, 113):
+                        b = pop(); a = pop()
+                        if b == 0:
+                            self.throw('java/lang/ArithmeticException', '/ by zero')
+                        r = abs(a) % abs(b)
+                        if a < 0:
+                            r = -r
+                        push(i32(r) if op == 112 else L(i64(r))); pc += 1
+                    elif op == 116:
+                        push(i32(-pop())); pc += 1
+                    elif op == 117:
+                        push(L(i64(-pop()))); pc += 1
+                    elif op in (118, 119):
+                        v = -pop(); push(D(v) if op == 119 else v); pc += 1
+                    elif op == 120:
+                        b = pop(); a = pop(); push(i32(a << (b & 31))); pc += 1
+                    elif op == 121:
+                        b = pop(); a = pop(); push(L(i64(a << (b & 63)))); pc += 1
+                    elif op == 122:
+                        b = pop(); a = pop(); push(a >> (b & 31)); pc += 1
+                    elif op == 123:
+                        b = pop(); a = pop(); push(L(a >> (b & 63))); pc += 1
+                    elif op == 124:
+                        b = pop(); a = pop(); push(i32((a & 0xFFFFFFFF) >> (b & 31))); pc += 1
+                    elif op == 125:
+                        b = pop(); a = pop(); push(L(i64((a & 0xFFFFFFFFFFFFFFFF) >> (b & 63)))); pc += 1
+                    elif op == 126:
+                        b = pop(); a = pop(); push(a & b); pc += 1
+                    elif op == 127:
+                        b = pop(); a = pop(); push(L(a & b)); pc += 1
+                    elif op == 128:
+                        b = pop(); a = pop(); push(a | b); pc += 1
+                    elif op == 129:
+                        b = pop(); a = pop(); push(L(a | b)); pc += 1
+                    elif op == 130:
+                        b = pop(); a = pop(); push(a ^ b); pc += 1
+                    elif op == 131:
+                        b = pop(); a = pop(); push(L(a ^ b)); pc += 1
+                    elif op == 132:
+                        idx = code[pc + 1]; loc[idx] = i32(loc[idx] + i8(code[pc + 2])); pc += 3
+                    # --- conversions
+                    elif op == 133:
+                        push(L(pop())); pc += 1
+                    elif op == 134:
+                        push(struct.unpack('f', struct.pack('f', float(pop())))[0]); pc += 1
+                    elif op == 135:
+                        push(D(float(pop()))); pc += 1
+                    elif op == 136:
+                        push(i32(pop())); pc += 1
+                    elif op == 137:
+                        push(struct.unpack('f', struct.pack('f', float(pop())))[0]); pc += 1
+                    elif op == 138:
+                        push(D(float(pop()))); pc += 1
+                    elif op == 139:
+                        push(d2i(pop(), 32)); pc += 1
+                    elif op == 140:
+                        push(L(d2i(pop(), 64))); pc += 1
+                    elif op == 141:
+                        push(D(float(pop()))); pc += 1
+                    elif op == 142:
+                        push(d2i(pop(), 32)); pc += 1
+                    elif op == 143:
+                        push(L(d2i(pop(), 64))); pc += 1
+                    elif op == 144:
+                        push(struct.unpack('f', struct.pack('f', float(pop())))[0]); pc += 1
+                    elif op == 145:
+                        push(i8(pop())); pc += 1
+                    elif op == 146:
+                        push(pop() & 0xFFFF); pc += 1
+                    elif op == 147:
+                        push(i16(pop())); pc += 1
+                    # --- compares
+                    elif op == 148:
+                        b = pop(); a = pop(); push((a > b) - (a < b)); pc += 1
+                    elif 149 <= op <= 152:
+                        b = pop(); a = pop()
+                        if a != a or b != b:
+                            push(1 if op in (150, 152) else -1)
+                        else:
+                            push((a > b) - (a < b))
+                        pc += 1
+                    elif 153 <= op <= 158:
+                        v = pop()
+                        t = (v == 0, v != 0, v < 0, v >= 0, v > 0, v <= 0)[op - 153]
+                        pc = pc + up('>h', code, pc + 1)[0] if t else pc + 3
+                    elif 159 <= op <= 164:
+                        b = pop(); a = pop()
+                        t = (a == b, a != b, a < b, a >= b, a > b, a <= b)[op - 159]
+                        pc = pc + up('>h', code, pc + 1)[0] if t else pc + 3
+                    elif op in (165, 166):
+                        b = pop(); a = pop()
+                        t = (a is b) if op == 165 else (a is not b)
+                        if isinstance(a, str) and isinstance(b, str):
+                            t = (a == b) if op == 165 else (a != b)
+                        pc = pc + up('>h', code, pc + 1)[0] if t else pc + 3
+                    elif op == 167:
+                        pc += up('>h', code, pc + 1)[0]
+                    elif op == 170:   # tableswitch
+                        base = pc
+                        p = (pc + 4) & ~3
+                        dflt, lo, hi = up('>iii', code, p)
+                        v = pop()
+                        if lo <= v <= hi:
+                            pc = base + up('>i', code, p + 12 + 4 * (v - lo))[0]
+                        else:
+                            pc = base + dflt
+                    elif op == 171:   # lookupswitch
+                        base = pc
+                        p = (pc + 4) & ~3
+                        dflt, n = up('>ii', code, p)
+                        v = pop()
+                        tgt = dflt
+                        for k in range(n):
+                            mv, off = up('>ii', code, p + 8 + 8 * k)
+                            if mv == v:
+                                tgt = off; break
+                        pc = base + tgt
+                    elif 172 <= op <= 176:
+                        return pop()
+                    elif op == 177:
+                        return None
+                    # --- fields
+                    elif op == 178:
+                        cn, fn, ds = cf.member_ref(up('>H', code, pc + 1)[0])
+                        if self.is_jdk(cn):
+                            push(self.jdk_static(cn, fn))
+                        else:
+                            self.load(cn)
+                            v = self.statics[(self.find_static_owner(cn, fn), fn)]
+                            push(self._wrap(ds, v))
+                        pc += 3
+                    elif op == 179:
+                        cn, fn, ds = cf.member_ref(up('>H', code, pc + 1)[0])
+                        self.load(cn)
+                        self.statics[(self.find_static_owner(cn, fn), fn)] = pop()
+                        pc += 3
+                    elif op == 180:
+                        cn, fn, ds = cf.member_ref(up('>H', code, pc + 1)[0])
+                        o = pop()
+                        if o is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        v = o.fields.get(fn, _DEFAULT)
+                        if v is _DEFAULT:
+                            v = 0.0 if ds in 'DF' else (0 if ds in 'IJSBCZ' else None)
+                        push(self._wrap(ds, v)); pc += 3
+                    elif op == 181:
+                        cn, fn, ds = cf.member_ref(up('>H', code, pc + 1)[0])
+                        v = pop(); o = pop()
+                        if o is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        o.fields[fn] = v; pc += 3
+                    # --- invokes
+                    elif op in (182, 183, 184, 185):
+                        cn, mn, ds = cf.member_ref(up('>H', code, pc + 1)[0])
+                        widths = Method._count_args(ds)
+                        nargs = len(widths) + (0 if op == 184 else 1)
+                        args = st[len(st) - nargs:] if nargs else []
+                        if nargs:
+                            del st[len(st) - nargs:]
+                        pc += 5 if op == 185 else 3
+                        ret = self.dispatch(op, cn, mn, ds, args)
+                        if not ds.endswith(')V'):
+                            push(self._wrap(ds[ds.index(')') + 1:], ret))
+                    elif op == 187:
+                        cn = cf.class_name(up('>H', code, pc + 1)[0])
+                        if not self.is_jdk(cn):
+                            self.load(cn)
+                        push(JObject(cn)); pc += 3
+                    elif op == 188:
+                        t = {4: 'Z', 5: 'C', 6: 'F', 7: 'D', 8: 'B', 9: 'S', 10: 'I', 11: 'J'}[code[pc + 1]]
+                        push(self.new_array(t, pop())); pc += 2
+                    elif op == 189:
+                        push(self.new_array('L', pop())); pc += 3
+                    elif op == 190:
+                        a = pop()
+                        if a is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        push(len(a.a)); pc += 1
+                    elif op == 191:
+                        o = pop()
+                        if o is None:
+                            self.throw('java/lang/NullPointerException', None)
+                        raise JavaThrow(o)
+                    elif op == 192:   # checkcast: trust
+                        pc += 3
+                    elif op == 193:
+                        cn = cf.class_name(up('>H', code, pc + 1)[0])
+                        push(1 if self.instance_of(pop(), cn) else 0); pc += 3
+                    elif op in (194, 195):
+                        pop(); pc += 1
+                    elif op == 196:   # wide
+                        op2 = code[pc + 1]; idx = up('>H', code, pc + 2)[0]
+                        if op2 == 132:
+                            loc[idx] = i32(loc[idx] + up('>h', code, pc + 4)[0]); pc += 6
+                        elif 21 <= op2 <= 25:
+                            push(loc[idx]); pc += 4
+                        else:
+                            loc[idx] = pop(); pc += 4
+                    elif op == 197:
+                        desc = cf.class_name(up('>H', code, pc + 1)[0]); nd = code[pc + 3]
+                        dims = st[len(st) - nd:]; del st[len(st) - nd:]
+                        push(self.multi_array(desc, dims)); pc += 4
+                    elif op == 198:
+                        pc = pc + up('>h', code, pc + 1)[0] if pop() is None else pc + 3
+                    elif op == 199:
+                        pc = pc + up('>h', code, pc + 1)[0] if pop() is not None else pc + 3
+                    elif op == 200:
+                        pc += up('>i', code, pc + 1)[0]
+                    else:
+                        raise NotImplementedError('opcode %d in %s.%s' % (op, cf.name, m.name))
+            except JavaThrow as t:
+                handler = None
+                for s, e, h, ct in m.extable:
+                    if s <= pc < e:
+                        if ct == 0 or self.instance_of(t.obj, cf.class_name(ct)):
+                            handler = h; break
+                if handler is None:
+                    raise
+                del st[:]
+                push(t.obj)
+                pc = handler
+
+    @staticmethod
+    def _is_wide(m, v):
+        return isinstance(v, WIDE)
+
+    @staticmethod
+    def _wrap(ds, v):
+        if ds == 'J' and not isinstance(v, L):
+            return L(v)
+        if ds == 'D' and not isinstance(v, D):
+            return D(v)
+        return v
+
+    # ---- method dispatch incl. JDK emulation
+    def dispatch(self, op, cn, mn, ds, args):
+        if op == 184:
+            if self.is_jdk(cn):
+                return self.jdk_static_call(cn, mn, ds, args)
+            self.load(cn)
+            m = self.find_method(cn, mn, ds)
+            return self.invoke(m, args)
+        recv = args[0]
+        if recv is None:
+            self.throw('java/lang/NullPointerException', None)
+        if op == 183:  # invokespecial: exact class
+            if self.is_jdk(cn):
+                return self.jdk_special(cn, mn, ds, args)
+            m = self.find_method(cn, mn, ds)
+            return self.invoke(m, args)
+        # virtual / interface
+        if isinstance(recv, JObject) and not self.is_jdk(recv.cls):
+            m = self.find_method(recv.cls, mn, ds)
+            if m is not None:
+                return self.invoke(m, args)
+        return self.jdk_virtual(cn, mn, ds, args)
+
+    def jdk_static(self, cn, fn):
+        if cn == 'java/nio/ByteOrder':
+            return LITTLE if fn == 'LITTLE_ENDIAN' else BIG
+        if cn == 'java/lang/System' and fn in ('out', 'err'):
+            return JObject('java/io/PrintStream')
+        raise NotImplementedError('static field %s.%s' % (cn, fn))
+
+    def jdk_special(self, cn, mn, ds, args):
+        o = args[0]
+        if mn == '<init>':
+            if cn in ('java/lang/Object',):
+                return None
+            if cn == 'java/lang/Enum':
+                o.fields['name'] = args[1]; o.fields['ordinal'] = args[2]; return None
+            if cn == 'java/lang/StringBuilder':
+                o.fields['s'] = args[1] if len(args) > 1 and isinstance(args[1], str) else ''
+                return None
+            if cn in JDK_SUPERS and self.instance_of_jdk(cn, 'java/lang/Throwable'):
+                o.fields['message'] = args[1] if len(args) > 1 and isinstance(args[1], str) else None
+                return None
+        raise NotImplementedError('special %s.%s%s' % (cn, mn, ds))
+
+    def jdk_static_call(self, cn, mn, ds, args):
+        if cn == 'java/lang/System' and mn == 'arraycopy':
+            src, sp, dst, dp, n = args
+            if src is None or dst is None:
+                self.throw('java/lang/NullPointerException', None)
+            if sp < 0 or dp < 0 or n < 0 or sp + n > len(src.a) or dp + n > len(dst.a):
+                self.throw('java/lang/ArrayIndexOutOfBoundsException', None)
+            dst.a[dp:dp + n] = src.a[sp:sp + n]
+            return None
+        if cn == 'java/util/Arrays' and mn == 'fill':
+            if len(args) == 4:
+                a, lo, hi, v = args
+                if lo > hi:
+                    self.throw('java/lang/IllegalArgumentException', 'fromIndex > toIndex')
+                if lo < 0 or hi > len(a.a):
+                    self.throw('java/lang/ArrayIndexOutOfBoundsException', None)
+            else:
+                a, v = args; lo, hi = 0, len(a.a)
+            if a.kind == 'B':
+                v &= 0xFF
+                a.a[lo:hi] = bytes([v]) * (hi - lo)
+            else:
+                a.a[lo:hi] = [v] * (hi - lo)
+            return None
+        if cn == 'java/util/Arrays' and mn in ('copyOf', 'copyOfRange'):
+            if mn == 'copyOf':
+                a, n = args; lo = 0; hi = n
+            else:
+                a, lo, hi = args
+            out = self.new_array(a.kind, hi - lo)
+            k = max(0, min(hi, len(a.a)) - lo)
+            out.a[0:k] = a.a[lo:lo + k]
+            return out
+        if cn == 'java/nio/ByteBuffer':
+            if mn == 'allocate':
+                arr = self.new_array('B', args[0])
+                bb = ByteBuffer(arr.a, 0, args[0]); bb.jarray = arr
+                return bb
+            if mn == 'wrap':
+                arr = args[0]
+                if len(args) == 1:
+                    bb = ByteBuffer(arr.a, 0, len(arr.a))
+                else:
+                    bb = ByteBuffer(arr.a, 0, len(arr.a)); bb.position = args[1]; bb.limit = args[1] + args[2]
+                bb.jarray = arr
+                return bb
+        if cn == 'java/lang/Math':
+            if mn == 'min':
+                return min(args)
+            if mn == 'max':
+                return max(args)
+            if mn == 'abs':
+                return abs(args[0])
+        if cn == 'java/lang/System' and mn == 'getProperty':
+            return args[1] if len(args) > 1 else None   # no -D properties set: defaults apply
+        if cn == 'java/lang/Integer' and mn == 'parseInt':
+            return i32(int(args[0]))
+        if cn == 'java/lang/Integer' and mn == 'valueOf':
+            o = JObject('java/lang/Integer'); o.fields['value'] = args[0]; return o
+        if cn == 'java/lang/String' and mn == 'valueOf':
+            return self.to_jstring(args[0], ds)
+        if cn == 'java/lang/Enum' and mn == 'valueOf':
+            _, cname = args[0]
+            for v in self.statics[(cname, '$VALUES')].a:
+                if v.fields['name'] == args[1]:
+                    return v
+            self.throw('java/lang/IllegalArgumentException', args[1])
+        raise NotImplementedError('static %s.%s%s' % (cn, mn, ds))
+
+    def to_jstring(self, v, ds):
+        p = ds[1:ds.index(')')]
+        if p == 'C':
+            return chr(v)
+        if p == 'Z':
+            return 'true' if v else 'false'
+        if v is None:
+            return 'null'
+        if isinstance(v, JObject):
+            if 'name' in v.fields and 'ordinal' in v.fields:
+                return v.fields['name']
+            return str(v)
+        if isinstance(v, float):
+            return repr(float(v))
+        return str(int(v)) if not isinstance(v, str) else v
+
+    def jdk_virtual(self, cn, mn, ds, args):
+        o = args[0]
+        if isinstance(o, ByteBuffer):
+            return self.bb_call(o, mn, ds, args[1:])
+        if isinstance(o, tuple) and o[0] == 'class':
+            if mn == 'desiredAssertionStatus':
+                return 0       # plain `java` without -ea
+            if mn == 'getName':
+                return o[1].replace('/', '.')
+        if isinstance(o, JArray) and mn == 'clone':
+            return JArray(o.kind, o.a[:])
+        if isinstance(o, str):
+            if mn == 'length':
+                return len(o)
+            if mn == 'charAt':
+                return ord(o[args[1]])
+            if mn == 'equals':
+                return 1 if o == args[1] else 0
+            if mn == 'hashCode':
+                h = 0
+                for ch in o:
+                    h = i32(31 * h + ord(ch))
+                return h
+            if mn == 'toString':
+                return o
+        if isinstance(o, JObject):
+            if mn == 'ordinal':
+                return o.fields['ordinal']
+            if mn == 'name' or (mn == 'toString' and 'name' in o.fields and 'ordinal' in o.fields):
+                return o.fields['name']
+            if o.cls == 'java/lang/StringBuilder':
+                if mn == 'append':
+                    o.fields['s'] += self.to_jstring(args[1], ds); return o
+                if mn == 'toString':
+                    return o.fields['s']
+            if mn == 'getMessage':
+                return o.fields.get('message')
+            if mn == 'hashCode':
+                return id(o) & 0x7FFFFFFF
+            if mn == 'equals':
+                return 1 if o is args[1] else 0
+            if mn == 'getClass':
+                return ('class', o.cls)
+            if o.cls == 'java/io/PrintStream':
+                return None
+            if o.cls == 'java/lang/Integer' and mn == 'intValue':
+                return o.fields['value']
+        raise NotImplementedError('virtual %s.%s%s on %r' % (cn, mn, ds, type(o)))
+
+    def bb_call(self, b, mn, ds, a):
+        arr, off = b.arr, b.offset
+        if mn == 'get':
+            if ds == '()B':
+                b._chk(self, 1); v = arr[off + b.position]; b.position += 1; return i8(v)
+            if ds == '(I)B':
+                if a[0] < 0 or a[0] >= b.limit:
+                    self.throw('java/lang/IndexOutOfBoundsException', None)
+                return i8(arr[off + a[0]])
+            if ds == '([B)Ljava/nio/ByteBuffer;':
+                dst = a[0]; n = len(dst.a)
+                b._chk(self, n); dst.a[0:n] = arr[off + b.position: off + b.position + n]; b.position += n; return b
+            if ds == '([BII)Ljava/nio/ByteBuffer;':
+                dst, dp, n = a
+                b._chk(self, n); dst.a[dp:dp + n] = arr[off + b.position: off + b.position + n]; b.position += n; return b
+        if mn == 'put':
+            if ds == '(B)Ljava/nio/ByteBuffer;':
+                b._chkw(self, 1); arr[off + b.position] = a[0] & 0xFF; b.position += 1; return b
+            if ds == '(IB)Ljava/nio/ByteBuffer;':
+                if a[0] < 0 or a[0] >= b.limit:
+                    self.throw('java/lang/IndexOutOfBoundsException', None)
+                arr[off + a[0]] = a[1] & 0xFF; return b
+            if ds == '([B)Ljava/nio/ByteBuffer;':
+                src = a[0]; n = len(src.a)
+                b._chkw(self, n); arr[off + b.position: off + b.position + n] = src.a; b.position += n; return b
+            if ds == '([BII)Ljava/nio/ByteBuffer;':
+                src, sp, n = a
+                b._chkw(self, n); arr[off + b.position: off + b.position + n] = src.a[sp:sp + n]; b.position += n; return b
+            if ds == '(Ljava/nio/ByteBuffer;)Ljava/nio/ByteBuffer;':
+                s = a[0]; n = s.limit - s.position
+                b._chkw(self, n)
+                arr[off + b.position: off + b.position + n] = s.arr[s.offset + s.position: s.offset + s.limit]
+                b.position += n; s.position = s.limit; return b
+        if mn == 'getInt':
+            fmt = '<i' if b.order is LITTLE else '>i'
+            if ds == '()I':
+                b._chk(self, 4); v = struct.unpack_from(fmt, arr, off + b.position)[0]; b.position += 4; return v
+            if ds == '(I)I':
+                if a[0] < 0 or a[0] + 4 > b.limit:
+                    self.throw('java/lang/IndexOutOfBoundsException', None)
+                return struct.unpack_from(fmt, arr, off + a[0])[0]
+        if mn == 'putInt':
+            fmt = '<i' if b.order is LITTLE else '>i'
+            if ds == '(I)Ljava/nio/ByteBuffer;':
+                b._chkw(self, 4); struct.pack_into(fmt, arr, off + b.position, i32(a[0])); b.position += 4; return b
+            if ds == '(II)Ljava/nio/ByteBuffer;':
+                if a[0] < 0 or a[0] + 4 > b.limit:
+                    self.throw('java/lang/IndexOutOfBoundsException', None)
+                struct.pack_into(fmt, arr, off + a[0], i32(a[1])); return b
+        if mn == 'position':
+            if ds == '()I':
+                return b.position
+            if a[0] < 0 or a[0] > b.limit:
+                self.throw('java/lang/IllegalArgumentException', None)
+            b.position = a[0]; return b
+        if mn == 'limit':
+            if ds == '()I':
+                return b.limit
+            if a[0] < 0 or a[0] > b.cap:
+                self.throw('java/lang/IllegalArgumentException', None)
+            b.limit = a[0]
+            if b.position > b.limit:
+                b.position = b.limit
+            return b
+        if mn == 'remaining':
+            return b.limit - b.position
+        if mn == 'hasRemaining':
+            return 1 if b.position < b.limit else 0
+        if mn == 'capacity':
+            return b.cap
+        if mn == 'order':
+            if ds == '()Ljava/nio/ByteOrder;':
+                return b.order
+            b.order = a[0]; return b
+        if mn == 'rewind':
+            b.position = 0; return b
+        if mn == 'flip':
+            b.limit = b.position; b.position = 0; return b
+        if mn == 'clear':
+            b.position = 0; b.limit = b.cap; return b
+        if mn == 'slice':
+            n = ByteBuffer(arr, off + b.position, b.limit - b.position)
+            n.jarray = b.jarray    # order resets to BIG_ENDIAN, as in Java
+            return n
+        if mn == 'duplicate':
+            n = ByteBuffer(arr, off, b.cap); n.position = b.position; n.limit = b.limit; n.jarray = b.jarray
+            return n
+        if mn == 'array':
+            return b.jarray
+        if mn == 'arrayOffset':
+            return off
+        if mn == 'hasArray':
+            return 1
+        raise NotImplementedError('ByteBuffer.%s%s' % (mn, ds))
+
+
+class L(int):
+    """marker for category-2 long values on the operand stack"""
+    __slots__ = ()
+
+
+class D(float):
+    """marker for category-2 double values on the operand stack"""
+    __slots__ = ()
+
+
+WIDE = (L, D)
+_DEFAULT = object()
+
+JDK_SUPERS = {
+    'java/lang/Object': None,
+    'java/lang/Throwable': 'java/lang/Object',
+    'java/lang/Exception': 'java/lang/Throwable',
+    'java/lang/Error': 'java/lang/Throwable',
+    'java/lang/LinkageError': 'java/lang/Error',
+    'java/lang/IncompatibleClassChangeError': 'java/lang/LinkageError',
+    'java/lang/NoSuchFieldError': 'java/lang/IncompatibleClassChangeError',
+    'java/lang/RuntimeException': 'java/lang/Exception',
+    'java/lang/IllegalArgumentException': 'java/lang/RuntimeException',
+    'java/lang/IllegalStateException': 'java/lang/RuntimeException',
+    'java/lang/ArithmeticException': 'java/lang/RuntimeException',
+    'java/lang/NullPointerException': 'java/lang/RuntimeException',
+    'java/lang/NegativeArraySizeException': 'java/lang/RuntimeException',
+    'java/lang/IndexOutOfBoundsException': 'java/lang/RuntimeException',
+    'java/lang/ArrayIndexOutOfBoundsException': 'java/lang/IndexOutOfBoundsException',
+    'java/nio/BufferUnderflowException': 'java/lang/RuntimeException',
+    'java/nio/BufferOverflowException': 'java/lang/RuntimeException',
+}
+
+REFERENCE_JAR = '/root/reference/cramtools-3.0.jar'
+
+
+def disassemble_refs(vm, cname):
+    """names of every member the class references -- handy when extending the JDK emulation"""
+    cf = vm.load(cname) if not vm.is_jdk(cname) else None
+    out = set()
+    for i, e in enumerate(cf.cp):
+        if e and e[0] in ('field', 'method', 'imethod'):
+            out.add((e[0],) + cf.member_ref(i))
+    return sorted(out)

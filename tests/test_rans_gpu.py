@@ -1,0 +1,162 @@
+"""GPU parity tests for the rANS block codec, through the C ABI (libcramgpu.so)."""
+import numpy as np
+import pytest
+
+from cramtools_b200 import synth, _lib
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope='module')
+def EC():
+    from cramtools_b200 import ExternalCompression
+    return ExternalCompression
+
+
+def test_golden_vectors_encode_byte_identical(EC, rans_golden, gpu_ctx):
+    vec, _ = rans_golden
+    got = EC.rans_batch([v[2] for v in vec], [v[1] for v in vec], gpu_ctx)
+    for (name, order, data, blob), g in zip(vec, got):
+        assert g == blob, (name, order)
+
+
+def test_golden_vectors_decode(EC, rans_golden, gpu_ctx):
+    vec, _ = rans_golden
+    got = EC.unrans_batch([v[3] for v in vec], gpu_ctx)
+    for (name, order, data, blob), g in zip(vec, got):
+        assert g == data, (name, order)
+
+
+def test_single_block_calls_like_the_reference(EC, rans_golden, gpu_ctx):
+    vec, _ = rans_golden
+    for name, order, data, blob in vec[:12]:
+        assert EC.rans(data, order, gpu_ctx) == blob
+        assert EC.unrans(blob, gpu_ctx) == data
+
+
+def test_error_behaviour_matches_reference(EC, rans_golden, gpu_ctx):
+    _, err = rans_golden
+    for name, blob, throws in err:
+        with pytest.raises(_lib.CramGpuError) as e:
+            EC.unrans(blob, gpu_ctx)
+        msg = throws.split(': ', 1)[1]
+        assert msg in str(e.value), (name, str(e.value))
+    with pytest.raises(_lib.CramGpuError):
+        EC.rans(b'abcdef', 2, gpu_ctx)
+
+
+def _oracle():
+    from oracle import rans as orans
+    return orans
+
+
+@pytest.mark.parametrize('order', [0, 1])
+def test_parity_with_oracle_size_sweep(EC, gpu_ctx, order):
+    orans = _oracle()
+    blocks = []
+    for kind in sorted(synth.STREAM_KINDS):
+        for n in (4, 5, 63, 64, 65, 4095, 4096, 4097, 65536, 65537, 131072 + 1, 262144 + 2, 1 << 20):
+            blocks.append(synth.STREAM_KINDS[kind](n, 7 * n + order))
+    got = EC.rans_batch(blocks, [order] * len(blocks), gpu_ctx)
+    for b, g in zip(blocks, got):
+        assert g == orans.compress(b, order), (len(b), order)
+    back = EC.unrans_batch(got, gpu_ctx)
+    for b, r in zip(blocks, back):
+        assert r == b.tobytes()
+
+
+def test_parity_adversarial_alphabets(EC, gpu_ctx):
+    orans = _oracle()
+    rng = np.random.default_rng(5)
+    blocks = [
+        rng.integers(0, 256, size=300000, dtype=np.uint8),                    # all 256 symbols, 256 contexts
+        np.repeat(np.arange(256, dtype=np.uint8), 40),                        # long runs, every symbol
+        np.tile(np.arange(256, dtype=np.uint8), 50),                          # every (i, i+1) pair
+        np.zeros(100000, dtype=np.uint8),                                     # single symbol 0
+        np.full(77777, 255, dtype=np.uint8),                                  # single symbol 255
+        (rng.random(500000) < 0.001).astype(np.uint8) * 3,                    # very skewed
+        np.minimum(rng.geometric(0.02, size=200000), 255).astype(np.uint8),   # ~200 symbols, skewed
+        rng.integers(0, 130, size=100000, dtype=np.uint8),                    # alphabet just above the smem limit
+    ]
+    for order in (0, 1):
+        got = EC.rans_batch(blocks, [order] * len(blocks), gpu_ctx)
+        for i, (b, g) in enumerate(zip(blocks, got)):
+            assert g == orans.compress(b, order), (i, order)
+        back = EC.unrans_batch(got, gpu_ctx)
+        for b, r in zip(blocks, back):
+            assert r == b.tobytes()
+
+
+def test_mixed_batch_with_empty_and_tiny_blocks(EC, gpu_ctx):
+    orans = _oracle()
+    blocks = [b'', b'A', b'AC', b'ACG', b'ACGT', b'', synth.qs_stream(150000, 1).tobytes(), b'\x00' * 7,
+              synth.rn_stream(30000, 2).tobytes(), b'', synth.itf8_stream(10000, 3).tobytes()]
+    orders = [1, 1, 0, 1, 1, 0, 1, 0, 1, 0, 0]
+    got = EC.rans_batch(blocks, orders, gpu_ctx)
+    for b, o, g in zip(blocks, orders, got):
+        assert g == orans.compress(b, o)
+    assert EC.unrans_batch(got, gpu_ctx) == [bytes(b) for b in blocks]
+
+
+def test_gpu_decodes_oracle_blocks_and_oracle_decodes_gpu_blocks(EC, gpu_ctx):
+    orans = _oracle()
+    data = [synth.STREAM_KINDS[k](200000 + i, 50 + i) for i, k in enumerate(sorted(synth.STREAM_KINDS))]
+    for order in (0, 1):
+        blobs = [orans.compress(d, order) for d in data]
+        assert EC.unrans_batch(blobs, gpu_ctx) == [d.tobytes() for d in data]
+        for d, g in zip(data, EC.rans_batch(data, [order] * len(data), gpu_ctx)):
+            assert orans.uncompress(g) == d.tobytes()
+
+
+def test_corrupt_blocks_are_reported_not_crashing(EC, gpu_ctx):
+    orans = _oracle()
+    good = bytearray(orans.compress(synth.qs_stream(20000, 9), 1))
+    # keep the prefix consistent but scribble over the frequency table
+    bad = bytearray(good)
+    for i in range(9, 60):
+        bad[i] = 0xFF
+    with pytest.raises(_lib.CramGpuError) as e:
+        EC.unrans(bytes(bad), gpu_ctx)
+    assert e.value.status == _lib.ERR_CORRUPT
+    # the context still works afterwards
+    assert EC.unrans(bytes(good), gpu_ctx) == synth.qs_stream(20000, 9).tobytes()
+
+
+def test_large_many_block_round_trip_checksum(EC, gpu_ctx):
+    """Full-size property check: many slice-sized QS blocks, decode(encode(x)) == x and block sizes
+    equal the oracle's on a sample."""
+    orans = _oracle()
+    q = synth.qualities(10000 * 12, 150, 77).reshape(12, -1)     # 12 slices' QS blocks of 1.5 MB
+    blocks = [np.ascontiguousarray(q[i]) for i in range(12)]
+    got = EC.rans_batch(blocks, [1] * 12, gpu_ctx)
+    assert got[0] == orans.compress(blocks[0], 1)
+    assert got[11] == orans.compress(blocks[11], 1)
+    back = EC.unrans_batch(got, gpu_ctx)
+    for b, r in zip(blocks, back):
+        assert r == b.tobytes()
+
+
+def test_device_resident_entry_points(gpu_ctx):
+    import torch
+    from cramtools_b200 import device as dv
+    orans = _oracle()
+    blocks = [synth.qs_stream(100000 + 17 * i, i) for i in range(20)] + [synth.ba_stream(5000, 3), np.zeros(0, np.uint8)]
+    orders = [i % 2 for i in range(len(blocks))]
+    d_in, off, ln = dv.pack_blocks(blocks, 'cuda:0')
+    res = dv.rans_encode_dev(gpu_ctx, d_in, off, ln, orders)
+    torch.cuda.synchronize()
+    blobs, st = res.to_host()
+    assert (st == 0).all()
+    for b, o, g in zip(blocks, orders, blobs):
+        assert g == orans.compress(b, o)
+    # decode straight from the encoder's device output
+    off2 = res.off.cpu().numpy().view(np.uint64)[:-1]
+    ln2 = res.len.cpu().numpy().view(np.uint32)
+    pre = np.zeros((len(blocks), 9), dtype=np.uint8)
+    for i, g in enumerate(blobs):
+        pre[i, :min(9, len(g))] = np.frombuffer(g[:9], dtype=np.uint8)
+    res2 = dv.rans_decode_dev(gpu_ctx, res.out, off2, ln2, pre)
+    torch.cuda.synchronize()
+    raws, st2 = res2.to_host()
+    assert (st2 == 0).all()
+    assert raws == [b.tobytes() for b in blocks]
