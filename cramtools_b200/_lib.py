@@ -33,6 +33,9 @@ SIGNATURES = {
     'cramgpu_last_error': (ctypes.c_char_p, [vp]),
     'cramgpu_sync': (ctypes.c_int, [vp]),
     'cramgpu_launch_count': (ctypes.c_uint64, [vp]),
+    'cramgpu_profile_enable': (ctypes.c_int, [vp, ctypes.c_int]),
+    'cramgpu_profile_read': (ctypes.c_int, [vp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_char_p),
+                                            ctypes.POINTER(ctypes.c_float)]),
     'cramgpu_rans_bound': (ctypes.c_uint32, [ctypes.c_uint32]),
     'cramgpu_rans_encode_batch': (ctypes.c_int, [vp, ctypes.c_uint32, u8pp, u32p, u8p, u8pp, u32p, u32p, i32p]),
     'cramgpu_rans_raw_sizes': (ctypes.c_int, [ctypes.c_uint32, u8pp, u32p, u32p, i32p]),
@@ -94,6 +97,17 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.cramgpu_launch_count(self.handle))
+
+    def profile_enable(self, on=True):
+        self.check(self.lib.cramgpu_profile_enable(self.handle, 1 if on else 0))
+
+    def profile_read(self, cap=65536):
+        """[(kernel name, milliseconds)] since the last read; synchronise the stream first"""
+        names = (ctypes.c_char_p * cap)()
+        ms = (ctypes.c_float * cap)()
+        n = self.lib.cramgpu_profile_read(self.handle, cap, names, ms)
+        n = min(max(n, 0), cap)
+        return [(names[i].decode(), float(ms[i])) for i in range(n)]
 
     def close(self):
         if self.handle:

@@ -51,7 +51,46 @@ int pinned_reserve(cramgpu_ctx *ctx, void **p, size_t *cap, size_t bytes)
     return CRAMGPU_OK;
 }
 
+static cudaEvent_t ev_get(cramgpu_ctx *ctx)
+{
+    if (!ctx->ev_pool.empty()) { cudaEvent_t e = ctx->ev_pool.back(); ctx->ev_pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+void prof_begin(cramgpu_ctx *ctx, cudaStream_t st, const char *name)
+{
+    cramgpu_ctx::Span s{name, ev_get(ctx), ev_get(ctx)};
+    cudaEventRecord(s.a, st);
+    ctx->spans.push_back(s);
+}
+void prof_end(cramgpu_ctx *ctx, cudaStream_t st) { cudaEventRecord(ctx->spans.back().b, st); }
+
 extern "C" {
+
+int cramgpu_profile_enable(cramgpu_ctx *ctx, int on)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    ctx->profiling = on != 0;
+    return CRAMGPU_OK;
+}
+
+// Drain the recorded spans: the caller must have synchronised the stream(s) the work ran on.
+// Writes up to cap entries; returns the number of spans recorded since the last call.
+int cramgpu_profile_read(cramgpu_ctx *ctx, uint32_t cap, const char **names, float *ms)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    uint32_t n = (uint32_t)ctx->spans.size();
+    for (uint32_t i = 0; i < n; i++) {
+        cramgpu_ctx::Span &s = ctx->spans[i];
+        float t = 0.f;
+        cudaEventElapsedTime(&t, s.a, s.b);
+        if (i < cap) { if (names) names[i] = s.name; if (ms) ms[i] = t; }
+        ctx->ev_pool.push_back(s.a); ctx->ev_pool.push_back(s.b);
+    }
+    ctx->spans.clear();
+    return (int)n;
+}
 
 int cramgpu_init(int device, cramgpu_ctx **out)
 {
@@ -87,6 +126,8 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
     if (ctx->pin_meta) cudaFreeHost(ctx->pin_meta);
     if (ctx->ev) cudaEventDestroy(ctx->ev);
+    for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
+    for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

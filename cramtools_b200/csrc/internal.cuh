@@ -69,7 +69,23 @@ struct cramgpu_ctx {
     size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
     cudaEvent_t ev = nullptr;
     EncodePending pend;
+    // optional per-kernel timing (cramgpu_profile_*): CUDA events around every launch
+    bool profiling = false;
+    struct Span { const char *name; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> ev_pool;
 };
+
+// LAUNCH(ctx, stream, "name", kernel<<<...>>>(...)) counts the launch and, when profiling, brackets it with events
+void prof_begin(cramgpu_ctx *ctx, cudaStream_t st, const char *name);
+void prof_end(cramgpu_ctx *ctx, cudaStream_t st);
+#define LAUNCH(ctx, st, name, ...)              \
+    do {                                        \
+        if ((ctx)->profiling) prof_begin((ctx), (st), (name)); \
+        __VA_ARGS__;                            \
+        (ctx)->launches++;                      \
+        if ((ctx)->profiling) prof_end((ctx), (st)); \
+    } while (0)
 
 int ctx_fail(cramgpu_ctx *ctx, int code, const char *fmt, ...);
 int ctx_cuda(cramgpu_ctx *ctx, cudaError_t e, const char *what);

@@ -312,15 +312,12 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     uint8_t *lut0 = S + o_lut0, *lut1 = S + o_lut1;
     uint32_t *fc0 = (uint32_t *)(S + o_fc0), *fc1 = (uint32_t *)(S + o_fc1);
     if (n0 + n1) {
-        k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, meta, d_status);
-        ctx->launches++;
+        LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, meta, d_status));
         if (n1) {
-            k_dec1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status);
-            ctx->launches++;
+            LAUNCH(ctx, st, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
         }
         if (n0) {
-            k_dec0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s0), n0, d_in, lut0, fc0, meta, d_out, d_status);
-            ctx->launches++;
+            LAUNCH(ctx, st, "k_dec0", k_dec0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s0), n0, d_in, lut0, fc0, meta, d_out, d_status));
         }
     }
     CUDA_TRY(ctx, cudaGetLastError());

@@ -730,24 +730,20 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
 
     if (n0 + n1) {
         uint32_t chunks = (max_len + HIST_CHUNK - 1) / HIST_CHUNK;
-        k_hist0<<<dim3(nblocks, chunks), 256, 0, st>>>(dd, d_in, F0);
-        ctx->launches++;
+        LAUNCH(ctx, st, "k_hist0", k_hist0<<<dim3(nblocks, chunks), 256, 0, st>>>(dd, d_in, F0));
         if (n1) {
             uint32_t max1 = desc[s1[0]].in_len;
-            k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1);
-            k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1);
-            k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen);
-            k_enc1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, d_s1, n1, d_in, syms1, work, plen, d_status);
-            ctx->launches += 4;
+            LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
+            LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
+            LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
+            LAUNCH(ctx, st, "k_enc1", k_enc1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, d_s1, n1, d_in, syms1, work, plen, d_status));
         }
         if (n0) {
-            k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen);
-            k_enc0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, d_s0, n0, d_in, syms0, work, plen, d_status);
-            ctx->launches += 2;
+            LAUNCH(ctx, st, "k_tables0", k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen));
+            LAUNCH(ctx, st, "k_enc0", k_enc0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, d_s0, n0, d_in, syms0, work, plen, d_status));
         }
     }
-    k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status);
-    ctx->launches++;
+    LAUNCH(ctx, st, "k_scan_out", k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status));
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->pend = EncodePending{dd, work, tlen, plen, d_out_off, d_out_len, nblocks,
                               (n0 + n1) ? 9 + (uint64_t)(n1 ? O1_TAB_CAP : O0_TAB_CAP) + max_len + max_len / 4 + 80 : 0};
@@ -761,9 +757,8 @@ int rans_encode_pack(cramgpu_ctx *ctx, uint8_t *d_out, cudaStream_t st)
 {
     const EncodePending &p = ctx->pend;
     if (p.max_out) {
-        k_pack<<<dim3(p.nblocks, (uint32_t)((p.max_out + PACK_CHUNK - 1) / PACK_CHUNK)), 256, 0, st>>>(
-            p.desc, p.work, p.tlen, p.plen, p.out_off, p.out_len, d_out);
-        ctx->launches++;
+        LAUNCH(ctx, st, "k_pack", k_pack<<<dim3(p.nblocks, (uint32_t)((p.max_out + PACK_CHUNK - 1) / PACK_CHUNK)), 256, 0, st>>>(
+            p.desc, p.work, p.tlen, p.plen, p.out_off, p.out_len, d_out));
         CUDA_TRY(ctx, cudaGetLastError());
     }
     return CRAMGPU_OK;

@@ -61,6 +61,16 @@ int cramgpu_sync(cramgpu_ctx *ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches claim). */
 uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx);
 
+/*
+ * Per-kernel device timing, the CUDA-event counterpart of the reference's System.nanoTime() stage
+ * counters (Cram2Bam.java:172-178,291-294; Container.buildHeaderTime/buildSlicesTime).  While enabled,
+ * every kernel the context launches is bracketed by events on the launching stream.
+ * cramgpu_profile_read drains them: synchronise the stream first; names[i] / ms[i] receive up to `cap`
+ * spans in launch order; returns the number of spans recorded since the previous read.
+ */
+int cramgpu_profile_enable(cramgpu_ctx *ctx, int on);
+int cramgpu_profile_read(cramgpu_ctx *ctx, uint32_t cap, const char **names, float *ms);
+
 /* ------------------------------------------------------------------ rANS block codec */
 
 /* Worst-case compressed size the reference allocates for n raw bytes:

@@ -412,3 +412,42 @@ int rans_oracle_uncompress(const uint8_t *in, uint32_t in_len, uint8_t *out, uin
     if (order == 1) return uncompress_o1(&s, out, out_sz);
     return RANS_ERR_UNKNOWN_ORDER;
 }
+
+/* ---------------------------------------------------------------- multi-threaded driver
+ * Runs the single-threaded codec above over independent blocks on `nthreads` host threads (the
+ * reference's own concurrency model: one container / block per pool thread,
+ * paralell/BamToCram_OBA_Function.java:51-94).  Used by bench.py for the CPU baseline only. */
+#include <pthread.h>
+
+typedef struct {
+    int encode, nthreads, tid;
+    uint32_t nblocks;
+    const uint8_t *const *in; const uint32_t *in_len; const uint8_t *order;
+    uint8_t *const *out; const uint32_t *out_cap; uint32_t *out_len; int *rc;
+} many_t;
+
+static void *many_worker(void *arg)
+{
+    many_t *m = (many_t *)arg;
+    for (uint32_t i = (uint32_t)m->tid; i < m->nblocks; i += (uint32_t)m->nthreads) {
+        if (m->encode) m->rc[i] = rans_oracle_compress(m->in[i], m->in_len[i], m->order[i], m->out[i], m->out_cap[i], &m->out_len[i]);
+        else m->rc[i] = rans_oracle_uncompress(m->in[i], m->in_len[i], m->out[i], m->out_cap[i], &m->out_len[i]);
+    }
+    return NULL;
+}
+
+int rans_oracle_many(int encode, int nthreads, uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len,
+                     const uint8_t *order, uint8_t *const *out, const uint32_t *out_cap, uint32_t *out_len, int *rc)
+{
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    pthread_t th[256];
+    many_t a[256];
+    for (int t = 0; t < nthreads; t++) {
+        a[t] = (many_t){encode, nthreads, t, nblocks, in, in_len, order, out, out_cap, out_len, rc};
+        pthread_create(&th[t], NULL, many_worker, &a[t]);
+    }
+    for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+    for (uint32_t i = 0; i < nblocks; i++) if (rc[i]) return rc[i];
+    return 0;
+}
