@@ -3,26 +3,58 @@
 // Restatement of RANS.uncompress [RANS.java:29-55] as a batch pipeline:
 //
 //   (host)        9-byte prefix: order, compressed size check, raw size        [RANS.java:31-44]
-//   k_dec_tables  frequency table -> slot->symbol LUT + {freq, start} per symbol Frequencies.readStats_o0 [:13-46], _o1 [:50-106]
+//   k_dec_tables  frequency table -> decoder tables                             Frequencies.readStats_o0 [:13-46], _o1 [:50-106]
 //   k_dec0        4-way interleaved decoder, one lane per state                 D04.uncompress [D04.java:9-85]
 //   k_dec1        4 quarter-lanes, context = previously decoded byte            D14.uncompress [D14.java:9-70]
+//   k_dec1_big    same, for blocks whose alphabet does not fit the shared-memory tables
 //
 // The four states of a block renormalise from ONE byte cursor in the order 0,1,2,3
 // [D04.java:36-39, Decoding.java:84-90]; per step each lane needs 0..2 bytes, and its read position is
 // the cursor plus the bytes taken by the lower lanes of its group (two ballots + popc).
+//
+// Every table lookup of the decoder depends on the state, so nothing can be prefetched: the tables must be
+// on-chip.  Order 0: the 4 KB slot->symbol table and 1 KB {freq,start} table of each of the warp's 8 blocks
+// are copied to shared memory.  Order 1 would need 4 KB per context (168 KB for a 42-symbol quality block),
+// so it uses a compact form instead: per context the 64 cumulative frequencies of the (<= 64) bytes the block
+// uses, searched in two 8-way steps with SWAR compares (144 B per context).  The compressed stream is staged
+// through a per-group shared-memory ring by cp.async and consumed from an 8-byte register window.
 #include "internal.cuh"
+
+#define DEC_MAXU 64          // alphabet limit of the shared-memory order-1 path
+#define DEC_ROW 72           // u16 per context row: 64 cumulative ends + 8 group ends
+#define DEC_CHUNK 16         // decoder steps per stream-staging round (<= 8 bytes per step and group)
+#define DEC_RING 128         // stream ring words per group
 
 struct DecMeta {
     uint32_t pay_off;   // offset of the 16 state bytes inside the compressed block
+    uint32_t small;     // order-1: 1 when the compact tables were built
 };
+
+// compact order-1 decoder tables of one block (global scratch; copied to shared memory by k_dec1)
+struct DecCompact {
+    uint16_t rows[DEC_MAXU][DEC_ROW];   // rows[ctx rank][r] = end of symbol rank r's slot range; [64+g] = rows[.][8g+7]
+    uint8_t ualpha[DEC_MAXU];           // rank -> byte
+    uint32_t nU, pad[3];
+};
+
+__device__ __forceinline__ void cp_async4(void *smem, const void *g)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(g));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // grid nblocks, 128 threads.  Thread 0 walks the table bytes (inherently sequential: every field's
 // position depends on the previous ones); all threads then expand each row.
-//   lut [ctx][4096] u8   slot -> symbol                (Arrays.fill(R, x, x+F, j), [Frequencies.java:31])
-//   fc  [ctx][256]  u32  freq << 16 | cumulative start
+//   order 0 and large-alphabet order 1:
+//     lut [ctx][4096] u8   slot -> symbol                (Arrays.fill(R, x, x+F, j), [Frequencies.java:31])
+//     fc  [ctx][256]  u32  freq << 16 | cumulative start
+//   order 1 with <= 64 distinct bytes (contexts and symbols together): DecCompact
 __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict__ desc, const uint8_t *__restrict__ d_in,
                                                     uint8_t *__restrict__ lut0, uint32_t *__restrict__ fc0,
                                                     uint8_t *__restrict__ lut1, uint32_t *__restrict__ fc1,
+                                                    DecCompact *__restrict__ compact,
                                                     DecMeta *__restrict__ meta, int32_t *__restrict__ status)
 {
     uint32_t blk = blockIdx.x;
@@ -33,69 +65,358 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
     const bool o1 = d.order == 1;
     uint8_t *lut = o1 ? lut1 + (size_t)d.o1_index * (256 * 4096) : lut0 + (size_t)blk * 4096;
     uint32_t *fc = o1 ? fc1 + (size_t)d.o1_index * 65536 : fc0 + (size_t)blk * 256;
+    DecCompact *cp = compact + d.o1_index;
 
     __shared__ uint16_t F[256];
     __shared__ uint16_t C[257];
     __shared__ uint8_t symlist[256];
-    __shared__ uint32_t s_nsym, s_pos, s_ctx, s_more, s_bad;
-    uint32_t tid = threadIdx.x;
+    __shared__ uint8_t present[256];
+    __shared__ uint8_t rank[256];
+    __shared__ uint32_t wcnt[4];
+    __shared__ uint32_t s_nsym, s_pos, s_ctx, s_more, s_bad, s_nU;
+    uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     // parser state (thread 0 only)
     uint32_t pos = 9, ctx = 0;
     int rle_i = 0;
     bool bad = false;
     auto getb = [&]() -> uint32_t { if (pos >= len) { bad = true; return 0; } return in[pos++]; };
     auto peekb = [&]() -> int { if (pos >= len) { bad = true; return -1; } return in[pos]; };
-    if (tid == 0 && o1) ctx = getb();
+    // one row: readStats_o0 [:13-46] / inner loop of readStats_o1 [:62-94].  collect: only mark the bytes seen.
+    auto parse_row = [&](bool collect) -> uint32_t {
+        uint32_t x = 0, ns = 0;
+        int rle = 0;
+        uint32_t j = getb();
+        do {
+            uint32_t f = getb();
+            if (f >= 128) f = ((f & 127) << 8) | getb();
+            if (o1 && f == 0) f = TOTFREQ;                                   // [:68-69]
+            if (x + f > TOTFREQ || ns >= 256) { bad = true; break; }          // Java: AIOOBE in Arrays.fill
+            if (collect) present[j] = 1;
+            else { F[j] = (uint16_t)f; C[j] = (uint16_t)x; symlist[ns] = (uint8_t)j; }
+            ns++;
+            x += f;
+            if (rle == 0 && peekb() == (int)j + 1) { j = getb(); rle = (int)getb(); }
+            else if (rle != 0) { rle--; j++; if (j > 255) { bad = true; break; } }
+            else j = getb();
+            if (bad) break;
+        } while (j != 0);
+        return ns;
+    };
+    auto next_ctx = [&]() {                                                   // [:96-105]
+        if (rle_i == 0 && peekb() == (int)ctx + 1) { ctx = getb(); rle_i = (int)getb(); }
+        else if (rle_i != 0) { rle_i--; ctx++; if (ctx > 255) bad = true; }
+        else ctx = getb();
+    };
 
-    for (;;) {
+    // ---- order 1, pass A: which bytes occur (as context or symbol)?  -> ranks
+    bool small = false;
+    if (o1) {
+        present[tid] = 0; present[tid + 128] = 0;
+        __syncthreads();
+        if (tid == 0) {
+            ctx = getb();
+            do {
+                present[ctx] = 1;
+                parse_row(true);
+                if (bad) break;
+                next_ctx();
+            } while (!bad && ctx != 0);
+            s_bad = bad ? 1u : 0u;
+            pos = 9; ctx = 0; rle_i = 0;      // rewind for pass B
+        }
+        __syncthreads();
+        if (!s_bad) {
+            // rank of byte b = number of present bytes below b; thread handles bytes 2*tid, 2*tid+1
+            uint32_t p0 = present[2 * tid], p1 = present[2 * tid + 1];
+            uint32_t c = p0 + p1;
+            uint32_t ex = c;
+            for (int dlt = 1; dlt < 32; dlt <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, ex, dlt); if (lane >= (uint32_t)dlt) ex += t; }
+            if (lane == 31) wcnt[w] = ex;
+            __syncthreads();
+            uint32_t b0 = ex - c;
+            for (uint32_t k = 0; k < w; k++) b0 += wcnt[k];
+            rank[2 * tid] = (uint8_t)b0; rank[2 * tid + 1] = (uint8_t)(b0 + p0);
+            if (tid == 127) s_nU = b0 + c;
+            __syncthreads();
+            small = s_nU <= DEC_MAXU;
+            if (small) {
+                if (p0) cp->ualpha[b0] = (uint8_t)(2 * tid);
+                if (p1) cp->ualpha[b0 + p0] = (uint8_t)(2 * tid + 1);
+                if (tid == 0) cp->nU = s_nU;
+                // contexts that never get a row keep all-zero (never selected) cumulative ends
+                for (uint32_t i = tid; i < DEC_MAXU * DEC_ROW; i += 128) (&cp->rows[0][0])[i] = 0;
+            }
+        }
+        __syncthreads();
+        if (tid == 0 && !s_bad) ctx = getb();
+    }
+
+    // ---- pass B: parse each row, expand it
+    if (!(o1 && s_bad)) for (;;) {
         F[tid] = 0; F[tid + 128] = 0;
         __syncthreads();
         if (tid == 0) {
-            // one row: readStats_o0 [:13-46] / inner loop of readStats_o1 [:62-94]
-            uint32_t x = 0, ns = 0;
-            int rle = 0;
-            uint32_t j = getb();
-            do {
-                uint32_t f = getb();
-                if (f >= 128) f = ((f & 127) << 8) | getb();
-                if (o1 && f == 0) f = TOTFREQ;                                   // [:68-69]
-                if (x + f > TOTFREQ || ns >= 256) { bad = true; break; }          // Java: AIOOBE in Arrays.fill
-                F[j] = (uint16_t)f; C[j] = (uint16_t)x; symlist[ns++] = (uint8_t)j;
-                x += f;
-                if (rle == 0 && peekb() == (int)j + 1) { j = getb(); rle = (int)getb(); }
-                else if (rle != 0) { rle--; j++; if (j > 255) { bad = true; break; } }
-                else j = getb();
-                if (bad) break;
-            } while (j != 0);
+            uint32_t ns = parse_row(false);
             s_nsym = ns; s_ctx = ctx;
-            if (o1 && !bad) {
-                // next context [:96-105]
-                if (rle_i == 0 && peekb() == (int)ctx + 1) { ctx = getb(); rle_i = (int)getb(); }
-                else if (rle_i != 0) { rle_i--; ctx++; if (ctx > 255) bad = true; }
-                else ctx = getb();
-            }
+            if (o1 && !bad) next_ctx();
             s_more = (o1 && !bad && ctx != 0) ? 1u : 0u;
             s_bad = bad ? 1u : 0u;
             s_pos = pos;
         }
         __syncthreads();
         if (s_bad) break;
-        // expand the row: every symbol fills its slots
-        uint8_t *row_lut = lut + (size_t)s_ctx * 4096 * (o1 ? 1 : 0);
-        uint32_t *row_fc = fc + (size_t)s_ctx * 256 * (o1 ? 1 : 0);
-        uint32_t ns = s_nsym;
-        for (uint32_t a = tid >> 5; a < ns; a += 4) {       // one warp per symbol
-            uint32_t j = symlist[a], f = F[j], c = C[j];
-            if ((tid & 31) == 0) row_fc[j] = (f << 16) | c;
-            for (uint32_t s = tid & 31; s < f; s += 32) row_lut[c + s] = (uint8_t)j;
+        if (small) {
+            // cumulative ends over byte ranks: warp 0, lane owns ranks 2*lane, 2*lane+1
+            if (w == 0) {
+                uint32_t r0 = 2 * lane, r1 = r0 + 1, nU = s_nU;
+                uint32_t f0 = r0 < nU ? F[cp->ualpha[r0]] : 0, f1 = r1 < nU ? F[cp->ualpha[r1]] : 0;
+                uint32_t s = f0 + f1, inc = s;
+                for (int dlt = 1; dlt < 32; dlt <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, dlt); if (lane >= (uint32_t)dlt) inc += t; }
+                uint16_t *row = cp->rows[rank[s_ctx]];
+                row[r0] = (uint16_t)(inc - f1);
+                row[r1] = (uint16_t)inc;
+                if ((lane & 3) == 3) row[64 + (lane >> 2)] = (uint16_t)inc;   // end of ranks 8g..8g+7
+            }
+        } else {
+            uint8_t *row_lut = lut + (size_t)s_ctx * 4096 * (o1 ? 1 : 0);
+            uint32_t *row_fc = fc + (size_t)s_ctx * 256 * (o1 ? 1 : 0);
+            uint32_t ns = s_nsym;
+            for (uint32_t a = w; a < ns; a += 4) {       // one warp per symbol
+                uint32_t j = symlist[a], f = F[j], c = C[j];
+                if (lane == 0) row_fc[j] = (f << 16) | c;
+                for (uint32_t s = lane; s < f; s += 32) row_lut[c + s] = (uint8_t)j;
+            }
         }
         __syncthreads();
         if (!s_more) break;
     }
     if (tid == 0) {
         meta[blk].pay_off = s_pos;
+        meta[blk].small = small ? 1u : 0u;
         if (s_bad) status[blk] = CRAMGPU_ERR_CORRUPT;
     }
+}
+
+// ---- the compressed stream of a group, staged in shared memory -----------------------------------------
+// ring[word index & (DEC_RING-1)][group]; all offsets are relative to the block start (16-byte aligned).
+struct Stream {
+    const uint8_t *base;      // block start in global memory
+    uint32_t len4;            // block length rounded up to 4
+    uint32_t wfetch;          // first word not yet requested
+};
+
+__device__ __forceinline__ void stream_fetch(Stream &s, uint32_t (*ring)[8], uint32_t g, uint32_t k, uint32_t cur)
+{
+    // A chunk consumes at most DEC_CHUNK * 8 bytes = 32 words and its window reads 2 words further; what is
+    // requested now is only waited for at the start of the NEXT chunk, so stay 72 words ahead of the cursor.
+    uint32_t tgt = ((cur >> 2) + 72 + 3) & ~3u;
+    uint32_t lim = s.len4 >> 2;
+    for (uint32_t w = s.wfetch + k; w < tgt; w += 4)       // the 4 lanes cover [wfetch, tgt) in strides of 4
+        if (w < lim) cp_async4(&ring[w & (DEC_RING - 1)][g], s.base + 4ull * w);
+    if (tgt > s.wfetch) s.wfetch = tgt;
+}
+
+// 8 bytes of the stream starting at byte offset cur
+__device__ __forceinline__ unsigned long long stream_window(uint32_t (*ring)[8], uint32_t g, uint32_t cur)
+{
+    uint32_t w = cur >> 2, sh = (cur & 3) * 8;
+    uint32_t a = ring[w & (DEC_RING - 1)][g], b = ring[(w + 1) & (DEC_RING - 1)][g], c = ring[(w + 2) & (DEC_RING - 1)][g];
+    uint32_t lo = __funnelshift_r(a, b, sh), hi = __funnelshift_r(b, c, sh);
+    return ((unsigned long long)hi << 32) | lo;
+}
+
+// Renormalise the 4 states of every group from the group's cursor, lanes in the order 0,1,2,3.
+// win = 8 stream bytes at the cursor.  Returns the new state and advances the cursor.
+__device__ __forceinline__ uint32_t renorm_win(uint32_t x, bool act, unsigned long long win, uint32_t &cur, uint32_t lane)
+{
+    bool n1 = act && x < RANS_L;
+    bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
+    uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1), b2 = __ballot_sync(0xFFFFFFFFu, n2);
+    uint32_t g4 = lane & ~3u, k = lane & 3u;
+    uint32_t gm = 0xFu << g4;
+    uint32_t lm = ((1u << k) - 1u) << g4;  // lower lanes of the group
+    uint32_t off = __popc(b1 & lm) + __popc(b2 & lm);
+    uint32_t v = (uint32_t)(win >> (8 * off));
+    if (n2) x = (x << 16) | ((v & 0xFF) << 8) | ((v >> 8) & 0xFF);
+    else if (n1) x = (x << 8) | (v & 0xFF);
+    cur += __popc(b1 & gm) + __popc(b2 & gm);
+    return x;
+}
+
+// number of the 8 sorted u16 in v that are <= m (all values < 2^15)
+__device__ __forceinline__ uint32_t count_le8(uint4 v, uint32_t m)
+{
+    uint32_t mm = (m + 1) * 0x00010001u;
+    const uint32_t K = 0x80008000u;
+    // bit 15 of each half survives iff half >= m+1, i.e. half > m
+    uint32_t t0 = ((v.x | K) - mm) & K, t1 = ((v.y | K) - mm) & K, t2 = ((v.z | K) - mm) & K, t3 = ((v.w | K) - mm) & K;
+    uint32_t gt = __popc(t0 | (t1 >> 1) | (t2 >> 2) | (t3 >> 3));
+    return 8 - gt;
+}
+// element e (0..7) of the 8 u16 in v
+__device__ __forceinline__ uint32_t elem8(uint4 v, uint32_t e)
+{
+    unsigned long long lo = ((unsigned long long)v.y << 32) | v.x, hi = ((unsigned long long)v.w << 32) | v.z;
+    unsigned long long h = (e & 4) ? hi : lo;
+    return (uint32_t)(h >> ((e & 3) * 16)) & 0xFFFFu;
+}
+
+// k_dec0: 1 warp per CTA, 8 blocks per warp; tables in shared memory.
+__global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                             const uint8_t *__restrict__ lut0, const uint32_t *__restrict__ fc0,
+                                             const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
+                                             int32_t *__restrict__ status)
+{
+    __shared__ __align__(16) uint8_t s_lut[8][4096];
+    __shared__ uint32_t s_fc[256][8];
+    __shared__ uint32_t ring[DEC_RING][8];
+    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
+    uint32_t slot = blockIdx.x * 8 + g;
+    bool have = slot < nslots;
+    uint32_t blk = have ? slots[slot] : 0;
+    BlockDesc d = desc[blk];
+    have = have && status[blk] == 0;
+    uint32_t n = have ? d.out_len : 0;
+    uint8_t *out = d_out + d.out_off;
+
+    for (uint32_t gg = 0; gg < 8; gg++) {
+        uint32_t b = __shfl_sync(0xFFFFFFFFu, blk, gg * 4);
+        const uint4 *src = reinterpret_cast<const uint4 *>(lut0 + (size_t)b * 4096);
+        uint4 *dst = reinterpret_cast<uint4 *>(s_lut[gg]);
+        for (uint32_t i = lane; i < 256; i += 32) dst[i] = __ldg(src + i);
+        for (uint32_t i = lane; i < 256; i += 32) s_fc[i][gg] = __ldg(fc0 + (size_t)b * 256 + i);
+    }
+    Stream st;
+    st.base = d_in + d.in_off;
+    st.len4 = have ? (d.in_len + 3) & ~3u : 0;
+    uint32_t cur = have ? meta[blk].pay_off : 0;
+    st.wfetch = (cur >> 2) & ~3u;
+    stream_fetch(st, ring, g, k, cur);
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncwarp();
+    uint32_t x = (uint32_t)(stream_window(ring, g, cur + 4 * k) & 0xFFFFFFFFu);
+    cur += 16;
+    bool under = false;
+
+    uint32_t steps = n >> 2;
+    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    const uint8_t *lut = s_lut[g];
+    unsigned long long win = stream_window(ring, g, cur);
+    for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
+        cp_async_wait_all();
+        __syncwarp();
+        stream_fetch(st, ring, g, k, cur);
+        cp_async_commit();
+        win = stream_window(ring, g, cur);
+#pragma unroll 4
+        for (uint32_t u = 0; u < DEC_CHUNK; u++) {
+            uint32_t t = t0 + u;
+            bool act = t < steps;
+            if (act) {
+                uint32_t m = x & (TOTFREQ - 1);
+                uint32_t s = lut[m];
+                uint32_t e = s_fc[s][g];
+                out[(uint64_t)t * 4 + k] = (uint8_t)s;
+                x = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFF);                 // [Decoding.java:35-48]
+            }
+            x = renorm_win(x, act, win, cur, lane);
+            win = stream_window(ring, g, cur);
+        }
+        if (cur > d.in_len) under = true;
+    }
+    if (have && k < (n & 3u)) out[(uint64_t)steps * 4 + k] = lut[x & (TOTFREQ - 1)];   // tail [D04.java:60-83]
+    if (have && (under || cur > d.in_len)) status[blk] = CRAMGPU_ERR_CORRUPT;
+}
+
+// k_dec1: lane k decodes the quarter starting at k*(n>>2); lane 3 also the remainder [D14.java:62-68].
+// Shared-memory path for blocks with <= 64 distinct bytes.  Dynamic shared memory:
+//   uint16_t rows[8][DEC_MAXU][DEC_ROW] | uint32_t ring[DEC_RING][8] | uint8_t ualpha[8][DEC_MAXU]
+#define DEC1_SMEM (8 * DEC_MAXU * DEC_ROW * 2 + DEC_RING * 8 * 4 + 8 * DEC_MAXU)
+__global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                             const DecCompact *__restrict__ compact,
+                                             const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
+                                             int32_t *__restrict__ status)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint16_t (*rows)[DEC_MAXU][DEC_ROW] = reinterpret_cast<uint16_t (*)[DEC_MAXU][DEC_ROW]>(smem);
+    uint32_t (*ring)[8] = reinterpret_cast<uint32_t (*)[8]>(smem + 8 * DEC_MAXU * DEC_ROW * 2);
+    uint8_t (*ualpha)[DEC_MAXU] = reinterpret_cast<uint8_t (*)[DEC_MAXU]>(smem + 8 * DEC_MAXU * DEC_ROW * 2 + DEC_RING * 8 * 4);
+
+    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
+    uint32_t slot = blockIdx.x * 8 + g;
+    bool have = slot < nslots;
+    uint32_t blk = have ? slots[slot] : 0;
+    BlockDesc d = desc[blk];
+    have = have && status[blk] == 0 && meta[blk].small == 1;
+    if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;
+    uint32_t n = have ? d.out_len : 0;
+    uint32_t q = n >> 2;
+    uint8_t *out = d_out + d.out_off + (uint64_t)k * q;
+    uint32_t mylen = (k == 3) ? n - 3 * q : q;
+
+    for (uint32_t gg = 0; gg < 8; gg++) {
+        uint32_t hv = __shfl_sync(0xFFFFFFFFu, (uint32_t)have, gg * 4);
+        uint32_t oi = __shfl_sync(0xFFFFFFFFu, d.o1_index, gg * 4);
+        if (!hv) continue;
+        const DecCompact *cp = compact + oi;
+        const uint4 *src = reinterpret_cast<const uint4 *>(&cp->rows[0][0]);
+        uint4 *dst = reinterpret_cast<uint4 *>(&rows[gg][0][0]);
+        for (uint32_t i = lane; i < DEC_MAXU * DEC_ROW * 2 / 16; i += 32) dst[i] = __ldg(src + i);
+        for (uint32_t i = lane; i < DEC_MAXU; i += 32) ualpha[gg][i] = cp->ualpha[i];
+    }
+    Stream st;
+    st.base = d_in + d.in_off;
+    st.len4 = have ? (d.in_len + 3) & ~3u : 0;
+    uint32_t cur = have ? meta[blk].pay_off : 0;
+    st.wfetch = (cur >> 2) & ~3u;
+    stream_fetch(st, ring, g, k, cur);
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncwarp();
+    uint32_t x = (uint32_t)(stream_window(ring, g, cur + 4 * k) & 0xFFFFFFFFu);
+    cur += 16;
+    bool under = false;
+
+    uint32_t steps = n - 3 * q;
+    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    const uint16_t (*myrows)[DEC_ROW] = rows[g];
+    const uint8_t *myalpha = ualpha[g];
+    // context 0 is byte 0; its rank is 0 whenever the block has a context-0 row (it always does)
+    uint32_t ctx = 0;
+    uint4 l1v = *reinterpret_cast<const uint4 *>(&myrows[ctx][64]);
+    unsigned long long win = 0;
+    for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
+        cp_async_wait_all();
+        __syncwarp();
+        stream_fetch(st, ring, g, k, cur);
+        cp_async_commit();
+        win = stream_window(ring, g, cur);
+#pragma unroll 4
+        for (uint32_t u = 0; u < DEC_CHUNK; u++) {
+            uint32_t t = t0 + u;
+            bool act = t < mylen;
+            if (act) {
+                uint32_t m = x & (TOTFREQ - 1);
+                uint32_t grp = min(count_le8(l1v, m), 7u);
+                uint4 gv = *reinterpret_cast<const uint4 *>(&myrows[ctx][grp * 8]);
+                uint32_t cnt = min(count_le8(gv, m), 7u);
+                uint32_t s = grp * 8 + cnt;
+                uint32_t hi = elem8(gv, cnt);
+                uint32_t lo = cnt ? elem8(gv, cnt - 1) : (grp ? elem8(l1v, grp - 1) : 0);
+                ctx = s;
+                l1v = *reinterpret_cast<const uint4 *>(&myrows[ctx][64]);       // next step's first level, early
+                out[t] = myalpha[s];
+                x = (hi - lo) * (x >> TF_SHIFT) + m - lo;
+            }
+            x = renorm_win(x, act, win, cur, lane);
+            win = stream_window(ring, g, cur);
+        }
+        if (cur > d.in_len) under = true;
+    }
+    if (have && (under || cur > d.in_len)) status[blk] = CRAMGPU_ERR_CORRUPT;
 }
 
 __device__ __forceinline__ uint32_t ld_byte(const uint8_t *p, uint32_t pos, uint32_t len, bool &under)
@@ -104,83 +425,20 @@ __device__ __forceinline__ uint32_t ld_byte(const uint8_t *p, uint32_t pos, uint
     return p[pos];
 }
 
-// Renormalise the 4 states of every group from the group's shared cursor, lanes in the order 0,1,2,3.
-__device__ __forceinline__ uint32_t renorm_step(uint32_t x, bool act, const uint8_t *in, uint32_t len, uint32_t &cur,
-                                                uint32_t lane, bool &under)
-{
-    bool n1 = act && x < RANS_L;
-    bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
-    uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1), b2 = __ballot_sync(0xFFFFFFFFu, n2);
-    uint32_t g4 = lane & ~3u, k = lane & 3u;
-    uint32_t gm = 0xFu << g4;
-    uint32_t lm = ((1u << k) - 1u) << g4;  // lower lanes of the group
-    uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
-    if (n1) {
-        x = (x << 8) | ld_byte(in, at, len, under);
-        if (n2) x = (x << 8) | ld_byte(in, at + 1, len, under);
-    }
-    cur += __popc(b1 & gm) + __popc(b2 & gm);
-    return x;
-}
-
-// k_dec0: 1 warp per CTA, 8 blocks per warp.
-__global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
-                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
-                                             const uint8_t *__restrict__ lut0, const uint32_t *__restrict__ fc0,
-                                             const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
-                                             int32_t *__restrict__ status)
+// k_dec1_big: general order-1 path (tables in global memory / L2), for alphabets above DEC_MAXU.
+__global__ void __launch_bounds__(32) k_dec1_big(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                                 uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                                 const uint8_t *__restrict__ lut1, const uint32_t *__restrict__ fc1,
+                                                 const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
+                                                 int32_t *__restrict__ status)
 {
     uint32_t lane = threadIdx.x, k = lane & 3u;
     uint32_t slot = blockIdx.x * 8 + (lane >> 2);
     bool have = slot < nslots;
     uint32_t blk = have ? slots[slot] : 0;
     BlockDesc d = desc[blk];
-    have = have && status[blk] == 0;
-    uint32_t n = have ? d.out_len : 0;
-    const uint8_t *in = d_in + d.in_off;
-    uint32_t len = d.in_len;
-    const uint8_t *lut = lut0 + (size_t)blk * 4096;
-    const uint32_t *fc = fc0 + (size_t)blk * 256;
-    uint8_t *out = d_out + d.out_off;
-    bool under = false;
-
-    uint32_t cur = have ? meta[blk].pay_off : 0;
-    uint32_t x = 0;
-    if (have) {
-        x = ld_byte(in, cur + 4 * k, len, under) | (ld_byte(in, cur + 4 * k + 1, len, under) << 8) |
-            (ld_byte(in, cur + 4 * k + 2, len, under) << 16) | (ld_byte(in, cur + 4 * k + 3, len, under) << 24);
-        cur += 16;
-    }
-    uint32_t steps = n >> 2;
-    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    for (uint32_t t = 0; t < max_steps; t++) {
-        bool act = t < steps;
-        if (act) {
-            uint32_t m = x & (TOTFREQ - 1);
-            uint32_t s = lut[m];
-            uint32_t e = fc[s];
-            out[(uint64_t)t * 4 + k] = (uint8_t)s;
-            x = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFF);                 // [Decoding.java:35-48]
-        }
-        x = renorm_step(x, act, in, len, cur, lane, under);
-    }
-    if (have && k < (n & 3u)) out[(uint64_t)steps * 4 + k] = lut[x & (TOTFREQ - 1)];   // tail [D04.java:60-83]
-    if (have && under) status[blk] = CRAMGPU_ERR_CORRUPT;
-}
-
-// k_dec1: lane k decodes the quarter starting at k*(n>>2); lane 3 also the remainder [D14.java:62-68].
-__global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
-                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
-                                             const uint8_t *__restrict__ lut1, const uint32_t *__restrict__ fc1,
-                                             const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
-                                             int32_t *__restrict__ status)
-{
-    uint32_t lane = threadIdx.x, k = lane & 3u;
-    uint32_t slot = blockIdx.x * 8 + (lane >> 2);
-    bool have = slot < nslots;
-    uint32_t blk = have ? slots[slot] : 0;
-    BlockDesc d = desc[blk];
-    have = have && status[blk] == 0;
+    have = have && status[blk] == 0 && meta[blk].small == 0;
+    if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;
     uint32_t n = have ? d.out_len : 0;
     const uint8_t *in = d_in + d.in_off;
     uint32_t len = d.in_len;
@@ -211,7 +469,18 @@ __global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc,
             x = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFF);
             l = s;
         }
-        x = renorm_step(x, act, in, len, cur, lane, under);
+        bool n1 = act && x < RANS_L;
+        bool n2 = act && x < (1u << 15);
+        uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1), b2 = __ballot_sync(0xFFFFFFFFu, n2);
+        uint32_t g4 = lane & ~3u;
+        uint32_t gm = 0xFu << g4;
+        uint32_t lm = ((1u << k) - 1u) << g4;
+        uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
+        if (n1) {
+            x = (x << 8) | ld_byte(in, at, len, under);
+            if (n2) x = (x << 8) | ld_byte(in, at + 1, len, under);
+        }
+        cur += __popc(b1 & gm) + __popc(b2 & gm);
     }
     if (have && under) status[blk] = CRAMGPU_ERR_CORRUPT;
 }
@@ -284,6 +553,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     size_t o_meta = c.take(sizeof(DecMeta) * (size_t)nblocks);
     size_t o_lut0 = c.take(4096 * (size_t)nblocks), o_fc0 = c.take(1024 * (size_t)nblocks);
     size_t o_lut1 = c.take((size_t)n1 * 256 * 4096 + 16), o_fc1 = c.take((size_t)n1 * 65536 * 4 + 16);
+    size_t o_compact = c.take(sizeof(DecCompact) * (size_t)std::max(n1, 1u));
     if (int rc = pool_reserve(ctx, ctx->scratch, c.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->scratch.p;
 
@@ -311,10 +581,17 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     DecMeta *meta = (DecMeta *)(S + o_meta);
     uint8_t *lut0 = S + o_lut0, *lut1 = S + o_lut1;
     uint32_t *fc0 = (uint32_t *)(S + o_fc0), *fc1 = (uint32_t *)(S + o_fc1);
+    DecCompact *compact = (DecCompact *)(S + o_compact);
+    static bool attr_done = false;
+    if (!attr_done) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(k_dec1, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC1_SMEM));
+        attr_done = true;
+    }
     if (n0 + n1) {
-        LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, meta, d_status));
+        LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, compact, meta, d_status));
         if (n1) {
-            LAUNCH(ctx, st, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
+            LAUNCH(ctx, st, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, DEC1_SMEM, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, compact, meta, d_out, d_status));
+            LAUNCH(ctx, st, "k_dec1_big", k_dec1_big<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
         }
         if (n0) {
             LAUNCH(ctx, st, "k_dec0", k_dec0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s0), n0, d_in, lut0, fc0, meta, d_out, d_status));

@@ -455,64 +455,106 @@ __device__ __forceinline__ void finish_block(uint8_t *end, uint32_t p, uint32_t 
     }
 }
 
+// ---- asynchronous global->shared copies (LDGSTS): they keep global-memory latency off the coder's recurrence
+__device__ __forceinline__ void cp_async4(void *smem, const void *g)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(g));
+}
+__device__ __forceinline__ void cp_async8(void *smem, const void *g)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+#define ENC_CHUNK 32   // coder steps per staging round
+
 // k_enc0: 1 warp per CTA, 8 blocks per warp, lane k of a group owns state k (symbols k, k+4, k+8, ...).
+// The 8 symbol tables (2 KB each) live in shared memory; input words are staged through a per-group ring by
+// cp.async two chunks ahead, so the recurrence touches only registers and shared memory.
 __global__ void __launch_bounds__(32) k_enc0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
                                              const uint2 *__restrict__ syms0, uint8_t *__restrict__ work,
                                              uint32_t *__restrict__ plen, int32_t *__restrict__ status)
 {
-    uint32_t lane = threadIdx.x, k = lane & 3u;
-    uint32_t slot = blockIdx.x * 8 + (lane >> 2);
+    __shared__ uint2 stab[256][8];          // [symbol][group]
+    __shared__ uint32_t wring[128][8];      // [input word index & 127][group]
+    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
+    uint32_t slot = blockIdx.x * 8 + g;
     bool have = slot < nslots;
     uint32_t blk = have ? slots[slot] : 0;
     BlockDesc d = desc[blk];
     uint32_t n = have ? d.in_len : 0;
-    const uint8_t *in = d_in + d.in_off;
-    const uint2 *st = syms0 + (size_t)blk * 256;
+    const uint8_t *in = d_in + d.in_off;    // 16-byte aligned
     uint32_t cap = d.work_cap - d.tab_cap;
     uint8_t *end = work + d.work_off + d.work_cap;
 
-    uint32_t steps = (n + 3) >> 2;
+    for (uint32_t i = lane; i < 2048; i += 32) {
+        uint32_t gg = i & 7, sym = i >> 3;
+        uint32_t b = __shfl_sync(0xFFFFFFFFu, blk, gg * 4);
+        stab[sym][gg] = __ldg(syms0 + (size_t)b * 256 + sym);
+    }
+    uint32_t steps = (n + 3) >> 2;          // step s codes symbols 4s..4s+3 == input word s
     uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    uint32_t nchunks = (max_steps + ENC_CHUNK - 1) / ENC_CHUNK;
+    // loop step t handles word s = steps-1-t.  Words of chunk c: s in (steps-1-32c-32, steps-1-32c]
+    auto fetch_chunk = [&](uint32_t c) {
+        // each lane of the group fetches 8 of the chunk's 32 words
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            uint32_t t = c * ENC_CHUNK + i * 4 + k;
+            if (t < steps) {
+                uint32_t s = steps - 1 - t;
+                cp_async4(&wring[s & 127][g], in + 4ull * s);
+            }
+        }
+    };
+    fetch_chunk(0); fetch_chunk(1);
+    cp_async_commit();
     uint32_t x = RANS_L, p = 0;
     bool overflow = false;
-
-    // software pipeline: byte two steps ahead, symbol one step ahead (neither depends on the state)
-    auto idx_of = [&](uint32_t t) -> int64_t {      // symbol index handled by this lane in loop step t, or -1
-        if (t >= steps) return -1;
-        uint64_t i = (uint64_t)(steps - 1 - t) * 4 + k;
-        return i < n ? (int64_t)i : -1;
-    };
-    int64_t i0 = idx_of(0), i1 = idx_of(1);
-    uint2 sym_next = make_uint2(0, 0);
-    bool act_next = i0 >= 0;
-    if (act_next) sym_next = __ldg(st + __ldg(in + i0));
-    uint32_t c_next = i1 >= 0 ? __ldg(in + i1) : 0;
-    bool act_next2 = i1 >= 0;
-
-    for (uint32_t t = 0; t < max_steps; t++) {
-        uint2 s = sym_next;
-        bool act = act_next;
-        act_next = act_next2;
-        if (act_next) sym_next = __ldg(st + c_next);
-        int64_t i2 = idx_of(t + 2);
-        act_next2 = i2 >= 0;
-        if (act_next2) c_next = __ldg(in + i2);
-
-        uint32_t nb = 0, bytes = 0;
-        if (act) x = put_symbol(x, s, nb, bytes);
-        emit_step(end, p, cap, nb, bytes, lane, overflow);
+    for (uint32_t c = 0; c < nchunks; c++) {
+        cp_async_wait_all();
+        __syncwarp();
+        fetch_chunk(c + 2);
+        cp_async_commit();
+        uint32_t t0 = c * ENC_CHUNK;
+        // two-stage register pipeline over shared memory: word -> byte -> symbol entry
+        auto sym_at = [&](uint32_t t) -> uint2 {
+            uint32_t s = steps - 1 - t;
+            uint32_t w = wring[s & 127][g];
+            return stab[(w >> (8 * k)) & 0xFF][g];
+        };
+        uint2 s_next = (t0 < steps) ? sym_at(t0) : make_uint2(0, 0);
+#pragma unroll 4
+        for (uint32_t u = 0; u < ENC_CHUNK; u++) {
+            uint32_t t = t0 + u;
+            uint2 s = s_next;
+            if (u + 1 < ENC_CHUNK && t + 1 < steps) s_next = sym_at(t + 1);
+            bool act = t < steps && (uint64_t)(steps - 1 - t) * 4 + k < n;
+            uint32_t nb = 0, bytes = 0;
+            if (act) x = put_symbol(x, s, nb, bytes);
+            emit_step(end, p, cap, nb, bytes, lane, overflow);
+        }
     }
     if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
 }
 
 // k_enc1: lane k owns the quarter [k*q, (k+1)*q), lane 3 also the remainder; coded backwards,
 // symbol = in[j], context = in[j-1] (0 for the first byte of the quarter) [E14.java:24-71].
+// Neither the input bytes nor the (context, symbol) table entries depend on the coder state, so both are
+// fetched asynchronously: input words two chunks ahead into a per-lane ring, table entries one chunk ahead
+// into a double-buffered descriptor ring (cp.async 8 B each).  The recurrence then reads one uint2 per step
+// from shared memory.
 __global__ void __launch_bounds__(32) k_enc1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
                                              const uint2 *__restrict__ syms1, uint8_t *__restrict__ work,
                                              uint32_t *__restrict__ plen, int32_t *__restrict__ status)
 {
+    __shared__ uint2 dring[2][ENC_CHUNK][32];   // [buffer][step in chunk][lane]
+    __shared__ uint32_t bring[32][32];          // [input word index & 31][lane]
     uint32_t lane = threadIdx.x, k = lane & 3u;
     uint32_t slot = blockIdx.x * 8 + (lane >> 2);
     bool have = slot < nslots;
@@ -520,46 +562,78 @@ __global__ void __launch_bounds__(32) k_enc1(const BlockDesc *__restrict__ desc,
     BlockDesc d = desc[blk];
     uint32_t n = have ? d.in_len : 0;
     uint32_t q = n >> 2;
-    const uint8_t *in = d_in + d.in_off + (uint64_t)k * q;          // this lane's quarter
+    const uint8_t *base = d_in + d.in_off;      // 16-byte aligned
+    uint32_t o0 = k * q;                        // this lane's quarter starts at byte o0 of the block
     uint32_t mylen = (k == 3) ? n - 3 * q : q;
     const uint2 *st = syms1 + (size_t)d.o1_index * 65536;
     uint32_t cap = d.work_cap - d.tab_cap;
     uint8_t *end = work + d.work_off + d.work_cap;
 
-    uint32_t steps = n - 3 * q;                                     // lane 3's length = longest
+    uint32_t steps = n - 3 * q;                 // lane 3's length = longest
     uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    uint32_t nchunks = (max_steps + ENC_CHUNK - 1) / ENC_CHUNK;
+
+    // loop step t codes local index j = steps-1-t (active when j < mylen)
+    int64_t wnext = mylen ? (int64_t)((o0 + mylen - 1) >> 2) : -1;   // next input word to fetch, descending
+    const int64_t wmin = o0 >> 2;
+    auto fetch_bytes = [&](uint32_t c) {
+        // make the ring cover every byte chunk c will look up: down to (context of) j_lo
+        int64_t jlo = (int64_t)steps - 1 - ((int64_t)c * ENC_CHUNK + ENC_CHUNK - 1);
+        if (jlo < 1) jlo = 1;
+        int64_t wneed = (int64_t)((o0 + (uint64_t)jlo - 1) >> 2);
+#pragma unroll
+        for (int i = 0; i < 10; i++) {
+            if (wnext >= wneed && wnext >= wmin) {
+                cp_async4(&bring[wnext & 31][lane], base + 4 * wnext);
+                wnext--;
+            }
+        }
+    };
+    auto ring_byte = [&](uint32_t o) -> uint32_t { return (bring[(o >> 2) & 31][lane] >> ((o & 3) * 8)) & 0xFF; };
+    auto issue_desc = [&](uint32_t c) {
+        uint32_t t0 = c * ENC_CHUNK;
+        if (t0 >= steps) return;
+        uint32_t j = steps - 1 - t0;
+        uint32_t l = j < mylen ? ring_byte(o0 + j) : 0;
+#pragma unroll 8
+        for (uint32_t u = 0; u < ENC_CHUNK; u++, j--) {
+            if (t0 + u >= steps) break;
+            bool act = j < mylen;
+            bool actn = j >= 1 && j - 1 < mylen;
+            uint32_t cx = actn ? ring_byte(o0 + j - 1) : 0;          // context = previous byte, 0 at j == 0
+            if (act) cp_async8(&dring[c & 1][u][lane], st + cx * 256 + l);
+            l = cx;
+        }
+    };
+
+    fetch_bytes(0); fetch_bytes(1);
+    cp_async_commit();
+    cp_async_wait_all();
+    __syncwarp();
+    issue_desc(0);
+    cp_async_commit();
+
     uint32_t x = RANS_L, p = 0;
     bool overflow = false;
-
-    // step t codes local index j = steps-1-t; pipeline: bytes two steps ahead, symbol one step ahead
-    auto j_of = [&](uint32_t t) -> int64_t {
-        if (t >= steps) return -1;
-        uint32_t j = steps - 1 - t;
-        return j < mylen ? (int64_t)j : -1;
-    };
-    auto pair_of = [&](int64_t j) -> uint32_t {                     // ctx*256 + sym
-        uint32_t l = __ldg(in + j);
-        uint32_t c = j > 0 ? __ldg(in + j - 1) : 0;
-        return c * 256 + l;
-    };
-    int64_t j0 = j_of(0), j1 = j_of(1);
-    bool act_next = j0 >= 0, act_next2 = j1 >= 0;
-    uint2 sym_next = make_uint2(0, 0);
-    if (act_next) sym_next = __ldg(st + pair_of(j0));
-    uint32_t pr_next = act_next2 ? pair_of(j1) : 0;
-
-    for (uint32_t t = 0; t < max_steps; t++) {
-        uint2 s = sym_next;
-        bool act = act_next;
-        act_next = act_next2;
-        if (act_next) sym_next = __ldg(st + pr_next);
-        int64_t j2 = j_of(t + 2);
-        act_next2 = j2 >= 0;
-        if (act_next2) pr_next = pair_of(j2);
-
-        uint32_t nb = 0, bytes = 0;
-        if (act) x = put_symbol(x, s, nb, bytes);
-        emit_step(end, p, cap, nb, bytes, lane, overflow);
+    for (uint32_t c = 0; c < nchunks; c++) {
+        cp_async_wait_all();
+        __syncwarp();
+        fetch_bytes(c + 2);
+        issue_desc(c + 1);
+        cp_async_commit();
+        uint32_t t0 = c * ENC_CHUNK;
+        const uint2 *dr = &dring[c & 1][0][lane];
+        uint2 s_next = dr[0];
+#pragma unroll 4
+        for (uint32_t u = 0; u < ENC_CHUNK; u++) {
+            uint32_t t = t0 + u;
+            uint2 s = s_next;
+            if (u + 1 < ENC_CHUNK) s_next = dr[(u + 1) * 32];
+            bool act = t < steps && (steps - 1 - t) < mylen;
+            uint32_t nb = 0, bytes = 0;
+            if (act) x = put_symbol(x, s, nb, bytes);
+            emit_step(end, p, cap, nb, bytes, lane, overflow);
+        }
     }
     if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
 }
