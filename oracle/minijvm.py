@@ -779,6 +779,9 @@ class MiniJVM:
 
     # ---- method dispatch incl. JDK emulation
     def dispatch(self, op, cn, mn, ds, args):
+        if not (mn == '<init>' and cn == 'java/lang/String'):
+            # `new String(...)` objects behave as python strings everywhere they are used
+            args = [a.fields['s'] if isinstance(a, JObject) and a.cls == 'java/lang/String' else a for a in args]
         if op == 184:
             if self.is_jdk(cn):
                 return self.jdk_static_call(cn, mn, ds, args)
@@ -800,9 +803,18 @@ class MiniJVM:
                 return self.invoke(m, args)
         return self.jdk_virtual(cn, mn, ds, args)
 
+    def empty_list(self):
+        # Collections.EMPTY_LIST / emptyList(): one shared immutable instance, compared by identity in the reference
+        if not hasattr(self, '_empty_list'):
+            self._empty_list = JObject('java/util/ArrayList')
+            self._empty_list.fields['list'] = []
+        return self._empty_list
+
     def jdk_static(self, cn, fn):
         if cn == 'java/nio/ByteOrder':
             return LITTLE if fn == 'LITTLE_ENDIAN' else BIG
+        if cn == 'java/util/Collections' and fn == 'EMPTY_LIST':
+            return self.empty_list()
         if cn == 'java/lang/System' and fn in ('out', 'err'):
             return JObject('java/io/PrintStream')
         raise NotImplementedError('static field %s.%s' % (cn, fn))
@@ -815,6 +827,30 @@ class MiniJVM:
             if cn == 'java/lang/Enum':
                 o.fields['name'] = args[1]; o.fields['ordinal'] = args[2]; return None
             if cn == 'java/lang/StringBuilder':
+                o.fields['s'] = args[1] if len(args) > 1 and isinstance(args[1], str) else ''
+                return None
+            if cn == 'java/lang/String':
+                a = args[1:]
+                if not a:
+                    o.fields['s'] = ''
+                elif isinstance(a[0], JArray) and a[0].kind == 'C':
+                    chars = a[0].a if len(a) == 1 else a[0].a[a[1]:a[1] + a[2]]
+                    o.fields['s'] = ''.join(chr(c) for c in chars)
+                elif isinstance(a[0], JArray) and a[0].kind == 'B':
+                    o.fields['s'] = bytes(a[0].a).decode('latin-1')
+                else:
+                    o.fields['s'] = a[0] if isinstance(a[0], str) else a[0].fields['s']
+                return None
+            if cn in JDK_LISTS:
+                o.fields['list'] = list(args[1].fields['list']) if len(args) > 1 and isinstance(args[1], JObject) and 'list' in args[1].fields else []
+                return None
+            if cn in JDK_MAPS:
+                o.fields['map'] = {}
+                return None
+            if cn in JDK_SETS:
+                o.fields['map'] = {}
+                return None
+            if cn in ('java/lang/StringBuffer',):
                 o.fields['s'] = args[1] if len(args) > 1 and isinstance(args[1], str) else ''
                 return None
             if cn in JDK_SUPERS and self.instance_of_jdk(cn, 'java/lang/Throwable'):
@@ -875,6 +911,43 @@ class MiniJVM:
                 return max(args)
             if mn == 'abs':
                 return abs(args[0])
+        if cn == 'java/util/Collections':
+            if mn == 'emptyList':
+                return self.empty_list()
+            if mn == 'sort':
+                lst = args[0].fields['list']
+                if len(args) == 2 and args[1] is not None:
+                    import functools
+                    cmpo = args[1]
+                    m = self.find_method(cmpo.cls, 'compare', '(Ljava/lang/Object;Ljava/lang/Object;)I')
+                    lst.sort(key=functools.cmp_to_key(lambda a, b: self.invoke(m, [cmpo, a, b])))   # stable, like Java
+                else:
+                    lst.sort(key=lambda v: v.fields['value'] if isinstance(v, JObject) else v)
+                return None
+            if mn in ('unmodifiableList', 'unmodifiableMap', 'unmodifiableSet', 'unmodifiableCollection'):
+                return args[0]
+        if cn in ('java/lang/Character', 'java/lang/Byte', 'java/lang/Short', 'java/lang/Long', 'java/lang/Boolean') and mn == 'valueOf':
+            o = JObject(cn); o.fields['value'] = args[0]; return o
+        if cn == 'java/lang/Character' and mn == 'isDigit':
+            return 1 if 48 <= args[0] <= 57 else 0
+        if cn == 'java/util/Arrays' and mn == 'sort':
+            import functools
+            arr = args[0]
+            lo, hi = (args[1], args[2]) if len(args) == 4 else (0, len(arr.a))
+            cmpo = args[-1] if isinstance(args[-1], JObject) else None
+            part = list(arr.a[lo:hi])
+            if cmpo is not None:
+                m = self.find_method(cmpo.cls, 'compare', '(Ljava/lang/Object;Ljava/lang/Object;)I')
+                part.sort(key=functools.cmp_to_key(lambda a, b: self.invoke(m, [cmpo, a, b])))   # stable (TimSort)
+            else:
+                part.sort()
+            arr.a[lo:hi] = part
+            return None
+        if cn == 'java/util/Arrays' and mn == 'asList':
+            o = JObject('java/util/ArrayList'); o.fields['list'] = list(args[0].a); return o
+        if cn == 'java/util/Arrays' and mn == 'equals':
+            a, b = args
+            return 1 if (a is None and b is None) or (a is not None and b is not None and list(a.a) == list(b.a)) else 0
         if cn == 'java/lang/System' and mn == 'getProperty':
             return args[1] if len(args) > 1 else None   # no -D properties set: defaults apply
         if cn == 'java/lang/Integer' and mn == 'parseInt':
@@ -916,6 +989,8 @@ class MiniJVM:
                 return 0       # plain `java` without -ea
             if mn == 'getName':
                 return o[1].replace('/', '.')
+            if mn == 'getSimpleName':
+                return o[1].split('/')[-1].split('$')[-1]
         if isinstance(o, JArray) and mn == 'clone':
             return JArray(o.kind, o.a[:])
         if isinstance(o, str):
@@ -932,11 +1007,108 @@ class MiniJVM:
                 return h
             if mn == 'toString':
                 return o
+            if mn == 'split':
+                import re as _re
+                parts = o.split(args[1]) if len(args[1]) == 1 and args[1] not in '.$|()[{^?*+\\' else _re.split(args[1], o)
+                while parts and parts[-1] == '':
+                    parts.pop()
+                return JArray('L', parts)
+            if mn == 'toCharArray':
+                return JArray('C', [ord(ch) for ch in o])
+            if mn == 'getBytes':
+                return JArray('B', bytearray(o.encode('latin-1')))
+            if mn == 'isEmpty':
+                return 1 if not o else 0
+            if mn == 'intern':
+                return o
+            if mn == 'startsWith':
+                return 1 if o.startswith(args[1]) else 0
+            if mn == 'substring':
+                return o[args[1]:] if len(args) == 2 else o[args[1]:args[2]]
         if isinstance(o, JObject):
             if mn == 'ordinal':
                 return o.fields['ordinal']
             if mn == 'name' or (mn == 'toString' and 'name' in o.fields and 'ordinal' in o.fields):
                 return o.fields['name']
+            if 'list' in o.fields and o.cls in JDK_LISTS + ('java/util/List', 'java/util/Collection'):
+                lst = o.fields['list']
+                if mn == 'add':
+                    if ds.startswith('(I'):
+                        lst.insert(args[1], args[2]); return None
+                    lst.append(args[1]); return 1
+                if mn == 'addAll':
+                    lst.extend(args[1].fields['list']); return 1
+                if mn in ('addLast',):
+                    lst.append(args[1]); return None
+                if mn == 'get':
+                    if args[1] < 0 or args[1] >= len(lst):
+                        self.throw('java/lang/IndexOutOfBoundsException', str(args[1]))
+                    return lst[args[1]]
+                if mn == 'size':
+                    return len(lst)
+                if mn == 'isEmpty':
+                    return 1 if not lst else 0
+                if mn == 'clear':
+                    del lst[:]; return None
+                if mn in ('iterator', 'listIterator'):
+                    it = JObject('java/util/Iterator'); it.fields['it'] = lst; it.fields['i'] = 0; return it
+                if mn in ('getFirst', 'peekFirst', 'peek'):
+                    if not lst and mn == 'getFirst':
+                        self.throw('java/util/NoSuchElementException', None)
+                    return lst[0] if lst else None
+                if mn in ('removeFirst', 'poll', 'pollFirst'):
+                    if not lst and mn == 'removeFirst':
+                        self.throw('java/util/NoSuchElementException', None)
+                    return lst.pop(0) if lst else None
+                if mn == 'remove' and ds.startswith('(I'):
+                    return lst.pop(args[1])
+                if mn == 'contains':
+                    k = _key(args[1]); return 1 if any(_key(v) == k for v in lst) else 0
+                if mn == 'toArray':
+                    return JArray('L', list(lst))
+            if o.cls == 'java/util/Iterator':
+                if mn == 'hasNext':
+                    return 1 if o.fields['i'] < len(o.fields['it']) else 0
+                if mn == 'next':
+                    v = o.fields['it'][o.fields['i']]; o.fields['i'] += 1; return v
+            if 'map' in o.fields and o.cls in JDK_MAPS:
+                mp = o.fields['map']
+                if mn == 'put':
+                    k = _key(args[1]); old = mp.get(k, (None, None))[1]; mp[k] = (args[1], args[2]); return old
+                if mn == 'get':
+                    return mp.get(_key(args[1]), (None, None))[1]
+                if mn == 'containsKey':
+                    return 1 if _key(args[1]) in mp else 0
+                if mn == 'size':
+                    return len(mp)
+                if mn == 'isEmpty':
+                    return 1 if not mp else 0
+                if mn == 'clear':
+                    mp.clear(); return None
+                if mn == 'values':
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [v for _, v in mp.values()]; return r
+                if mn == 'keySet':
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [k for k, _ in mp.values()]; return r
+            if 'map' in o.fields and o.cls in JDK_SETS:
+                mp = o.fields['map']
+                if mn == 'add':
+                    k = _key(args[1]); had = k in mp; mp[k] = args[1]; return 0 if had else 1
+                if mn == 'contains':
+                    return 1 if _key(args[1]) in mp else 0
+                if mn == 'isEmpty':
+                    return 1 if not mp else 0
+                if mn == 'size':
+                    return len(mp)
+                if mn == 'iterator':
+                    it = JObject('java/util/Iterator'); it.fields['it'] = list(mp.values()); it.fields['i'] = 0; return it
+            if o.cls.startswith('java/lang/') and 'value' in o.fields and mn in (
+                    'intValue', 'charValue', 'byteValue', 'shortValue', 'longValue', 'booleanValue'):
+                return o.fields['value']
+            if o.cls in ('java/lang/StringBuffer',):
+                if mn == 'append':
+                    o.fields['s'] += self.to_jstring(args[1], ds); return o
+                if mn == 'toString':
+                    return o.fields['s']
             if o.cls == 'java/lang/StringBuilder':
                 if mn == 'append':
                     o.fields['s'] += self.to_jstring(args[1], ds); return o
@@ -1052,6 +1224,20 @@ class MiniJVM:
         raise NotImplementedError('ByteBuffer.%s%s' % (mn, ds))
 
 
+JDK_LISTS = ('java/util/ArrayList', 'java/util/LinkedList')
+JDK_MAPS = ('java/util/HashMap', 'java/util/TreeMap', 'java/util/LinkedHashMap')
+JDK_SETS = ('java/util/HashSet', 'java/util/TreeSet', 'java/util/LinkedHashSet')
+
+
+def _key(v):
+    """dictionary key for a Java object used in a HashMap / HashSet"""
+    if isinstance(v, JObject) and 'value' in v.fields and v.cls.startswith('java/lang/'):
+        return (v.cls, v.fields['value'])
+    if isinstance(v, (str, int, float)) or v is None:
+        return v
+    return id(v)
+
+
 class L(int):
     """marker for category-2 long values on the operand stack"""
     __slots__ = ()
@@ -1082,6 +1268,7 @@ JDK_SUPERS = {
     'java/lang/IndexOutOfBoundsException': 'java/lang/RuntimeException',
     'java/lang/ArrayIndexOutOfBoundsException': 'java/lang/IndexOutOfBoundsException',
     'java/nio/BufferUnderflowException': 'java/lang/RuntimeException',
+    'java/util/NoSuchElementException': 'java/lang/RuntimeException',
     'java/nio/BufferOverflowException': 'java/lang/RuntimeException',
 }
 
@@ -1096,3 +1283,86 @@ def disassemble_refs(vm, cname):
         if e and e[0] in ('field', 'method', 'imethod'):
             out.add((e[0],) + cf.member_ref(i))
     return sorted(out)
+
+
+# ----------------------------------------------------------------------------- disassembler (for reading the jar)
+
+_OPNAMES = {
+    0: 'nop', 1: 'aconst_null', 16: 'bipush', 17: 'sipush', 18: 'ldc', 19: 'ldc_w', 20: 'ldc2_w',
+    21: 'iload', 22: 'lload', 23: 'fload', 24: 'dload', 25: 'aload', 46: 'iaload', 47: 'laload', 50: 'aaload',
+    51: 'baload', 52: 'caload', 53: 'saload', 54: 'istore', 55: 'lstore', 58: 'astore', 79: 'iastore', 80: 'lastore',
+    83: 'aastore', 84: 'bastore', 87: 'pop', 88: 'pop2', 89: 'dup', 90: 'dup_x1', 91: 'dup_x2', 92: 'dup2', 95: 'swap',
+    96: 'iadd', 97: 'ladd', 100: 'isub', 101: 'lsub', 104: 'imul', 105: 'lmul', 107: 'dmul', 108: 'idiv', 109: 'ldiv',
+    111: 'ddiv', 112: 'irem', 116: 'ineg', 120: 'ishl', 121: 'lshl', 122: 'ishr', 123: 'lshr', 124: 'iushr', 125: 'lushr',
+    126: 'iand', 127: 'land', 128: 'ior', 129: 'lor', 130: 'ixor', 132: 'iinc', 133: 'i2l', 135: 'i2d', 136: 'l2i',
+    138: 'l2d', 142: 'd2i', 145: 'i2b', 146: 'i2c', 147: 'i2s', 148: 'lcmp', 153: 'ifeq', 154: 'ifne', 155: 'iflt',
+    156: 'ifge', 157: 'ifgt', 158: 'ifle', 159: 'if_icmpeq', 160: 'if_icmpne', 161: 'if_icmplt', 162: 'if_icmpge',
+    163: 'if_icmpgt', 164: 'if_icmple', 165: 'if_acmpeq', 166: 'if_acmpne', 167: 'goto', 170: 'tableswitch',
+    171: 'lookupswitch', 172: 'ireturn', 173: 'lreturn', 176: 'areturn', 177: 'return', 178: 'getstatic',
+    179: 'putstatic', 180: 'getfield', 181: 'putfield', 182: 'invokevirtual', 183: 'invokespecial', 184: 'invokestatic',
+    185: 'invokeinterface', 187: 'new', 188: 'newarray', 189: 'anewarray', 190: 'arraylength', 191: 'athrow',
+    192: 'checkcast', 193: 'instanceof', 196: 'wide', 197: 'multianewarray', 198: 'ifnull', 199: 'ifnonnull',
+}
+for _i, _n in enumerate(['iconst_m1', 'iconst_0', 'iconst_1', 'iconst_2', 'iconst_3', 'iconst_4', 'iconst_5', 'lconst_0',
+                         'lconst_1', 'fconst_0', 'fconst_1', 'fconst_2', 'dconst_0', 'dconst_1']):
+    _OPNAMES[2 + _i] = _n
+for _b, _p in ((26, 'iload_'), (30, 'lload_'), (34, 'fload_'), (38, 'dload_'), (42, 'aload_'), (59, 'istore_'),
+               (63, 'lstore_'), (67, 'fstore_'), (71, 'dstore_'), (75, 'astore_')):
+    for _k in range(4):
+        _OPNAMES[_b + _k] = _p + str(_k)
+
+
+def disassemble(cf, name, desc=None):
+    """javap -c style listing of one method (with source line numbers) -- used to read htsjdk's bytecode"""
+    out = []
+    for (nm, ds), m in cf.methods.items():
+        if nm != name or (desc and ds != desc) or m.code is None:
+            continue
+        out.append('%s%s' % (nm, ds))
+        code = m.code
+        pc = 0
+        up = struct.unpack_from
+        while pc < len(code):
+            op = code[pc]
+            nmn = _OPNAMES.get(op, 'op%d' % op)
+            arg = ''
+            ln = 1
+            if op in (16, 188):
+                arg = str(i8(code[pc + 1]) if op == 16 else code[pc + 1]); ln = 2
+            elif op == 17:
+                arg = str(up('>h', code, pc + 1)[0]); ln = 3
+            elif op == 18 or op in (19, 20):
+                idx = code[pc + 1] if op == 18 else up('>H', code, pc + 1)[0]
+                e = cf.cp[idx]
+                arg = repr(cf.utf(e[1])) if e[0] in ('string', 'class') else repr(e[1])
+                ln = 2 if op == 18 else 3
+            elif 21 <= op <= 25 or 54 <= op <= 58:
+                arg = str(code[pc + 1]); ln = 2
+            elif op == 132:
+                arg = '%d %d' % (code[pc + 1], i8(code[pc + 2])); ln = 3
+            elif 153 <= op <= 167 or op in (198, 199):
+                arg = '-> %d' % (pc + up('>h', code, pc + 1)[0]); ln = 3
+            elif op in (178, 179, 180, 181, 182, 183, 184):
+                arg = '%s.%s %s' % cf.member_ref(up('>H', code, pc + 1)[0]); ln = 3
+            elif op == 185:
+                arg = '%s.%s %s' % cf.member_ref(up('>H', code, pc + 1)[0]); ln = 5
+            elif op in (187, 189, 192, 193):
+                arg = cf.class_name(up('>H', code, pc + 1)[0]); ln = 3
+            elif op == 197:
+                arg = cf.class_name(up('>H', code, pc + 1)[0]) + ' dims=%d' % code[pc + 3]; ln = 4
+            elif op == 170:
+                p = (pc + 4) & ~3
+                dflt, lo, hi = up('>iii', code, p)
+                arg = 'default->%d ' % (pc + dflt) + ' '.join('%d->%d' % (lo + k, pc + up('>i', code, p + 12 + 4 * k)[0]) for k in range(hi - lo + 1))
+                ln = p + 12 + 4 * (hi - lo + 1) - pc
+            elif op == 171:
+                p = (pc + 4) & ~3
+                dflt, n = up('>ii', code, p)
+                arg = 'default->%d ' % (pc + dflt) + ' '.join('%d->%d' % (up('>i', code, p + 8 + 8 * k)[0], pc + up('>i', code, p + 12 + 8 * k)[0]) for k in range(n))
+                ln = p + 8 + 8 * n - pc
+            elif op == 196:
+                ln = 6 if code[pc + 1] == 132 else 4
+                arg = str(up('>H', code, pc + 2)[0])
+            out.append('  %4d [L%s] %-16s %s' % (pc, m.line_of(pc), nmn, arg))
+            pc += ln
+    return '\n'.join(out)

@@ -1,0 +1,209 @@
+"""ctypes front-end of oracle/records_oracle.c.  TEST INFRASTRUCTURE ONLY."""
+import ctypes
+
+import numpy as np
+
+from . import rans as _rans
+
+_c = ctypes
+u8p = _c.POINTER(_c.c_uint8)
+i32p = _c.POINTER(_c.c_int32)
+i64p = _c.POINTER(_c.c_int64)
+u32p = _c.POINTER(_c.c_uint32)
+u16p = _c.POINTER(_c.c_uint16)
+
+
+class RecFeatures(_c.Structure):
+    _fields_ = [('n_feat', _c.c_int64), ('f_op', u8p), ('f_pos', i32p), ('f_val', i32p), ('f_aux', i32p),
+                ('feat_off', i64p), ('payload', u8p), ('payload_len', _c.c_int64),
+                ('subst_counts', (_c.c_int64 * 5) * 5), ('matrix', _c.c_uint8 * 5)]
+
+
+class QsPolicy(_c.Structure):
+    _fields_ = [('read_cat', _c.c_int32), ('read_param', _c.c_int32), ('n_base_cats', _c.c_int32),
+                ('base_cat', _c.c_int32 * 8), ('treatment', _c.c_int32), ('treat_param', _c.c_int32)]
+
+
+STREAMS = ['FN', 'FC', 'FP', 'BS', 'DL', 'BA', 'SC', 'QS', 'RS', 'HC', 'PD', 'MQ']
+
+_done = False
+
+
+def lib():
+    global _done
+    L = _rans.lib()
+    if not _done:
+        L.rec_oracle_normalize_base.restype = _c.c_uint8
+        L.rec_oracle_normalize_base.argtypes = [_c.c_uint8]
+        L.rec_oracle_itf8.restype = _c.c_int
+        L.rec_oracle_itf8.argtypes = [_c.c_int32, u8p]
+        L.rec_oracle_extract.restype = _c.c_int
+        L.rec_oracle_extract.argtypes = [_c.c_int64, u8p, i64p, u32p, i64p, i32p, u16p, u8p, _c.c_int64, _c.POINTER(RecFeatures)]
+        L.rec_oracle_free.argtypes = [_c.POINTER(RecFeatures)]
+        L.rec_oracle_subst_matrix.argtypes = [(_c.c_int64 * 5) * 5, _c.c_uint8 * 5, (_c.c_uint8 * 5) * 5]
+        L.rec_oracle_parse_policies.restype = _c.c_int
+        L.rec_oracle_parse_policies.argtypes = [_c.c_char_p, _c.POINTER(QsPolicy), _c.c_int]
+        L.rec_oracle_quality.restype = _c.c_int
+        L.rec_oracle_quality.argtypes = [u8p, u8p, _c.c_int64, _c.c_int, u32p, _c.c_int64, _c.c_int32, _c.c_uint16,
+                                         _c.c_uint8, u8p, _c.c_int64, _c.POINTER(QsPolicy), _c.c_int, u8p]
+        L.rec_oracle_restore_bases.restype = _c.c_int
+        L.rec_oracle_restore_bases.argtypes = [_c.c_int32, _c.c_int64, _c.c_int64, u8p, i32p, i32p, i32p, u8p, u8p,
+                                               _c.c_int64, _c.c_int64, _c.c_uint8 * 5, u8p]
+        L.rec_oracle_restore_quals.restype = _c.c_int
+        L.rec_oracle_restore_quals.argtypes = [_c.c_int, _c.c_int64, _c.c_int64, u8p, i32p, i32p, i32p, u8p]
+        L.rec_oracle_write_streams.argtypes = [_c.c_int64, u8p, i64p, u16p, u8p, i32p, _c.POINTER(RecFeatures), u8p, u8p,
+                                               _c.POINTER(u8p), i64p]
+        _done = True
+    return L
+
+
+def _p(a, t):
+    return a.ctypes.data_as(t)
+
+
+def itf8(v):
+    buf = np.zeros(8, np.uint8)
+    n = lib().rec_oracle_itf8(int(v), _p(buf, u8p))
+    return buf[:n].tobytes()
+
+
+def parse_policies(spec):
+    """-> list of QsPolicy (sorted as the reference sorts), or raises ValueError"""
+    if spec is None or spec == 'lossless':
+        return None
+    arr = (QsPolicy * 16)()
+    n = lib().rec_oracle_parse_policies(spec.encode(), arr, 16)
+    if n == -1:
+        raise ValueError('Unknown read or base category')
+    if n == -2:
+        raise ValueError('selector needs ReferenceTracks counters (X/P): not restated')
+    return arr, n
+
+
+def subst_matrix(counts):
+    """counts: dict 'AC' -> n (ref, read).  -> (5 matrix bytes, codes dict)"""
+    C = ((_c.c_int64 * 5) * 5)()
+    B = 'ACGTN'
+    for k, v in counts.items():
+        C[B.index(k[0])][B.index(k[1])] = v
+    M = (_c.c_uint8 * 5)()
+    K = ((_c.c_uint8 * 5) * 5)()
+    lib().rec_oracle_subst_matrix(C, M, K)
+    return bytes(M), {B[r] + B[b]: K[r][b] for r in range(5) for b in range(5) if r != b}
+
+
+class Extracted(object):
+    """numpy views (copied) of rec_features_t"""
+
+    def __init__(self, rf, n_reads):
+        n = rf.n_feat
+        self.n_feat = n
+        self.f_op = np.ctypeslib.as_array(rf.f_op, (max(n, 1),))[:n].copy()
+        self.f_pos = np.ctypeslib.as_array(rf.f_pos, (max(n, 1),))[:n].copy()
+        self.f_val = np.ctypeslib.as_array(rf.f_val, (max(n, 1),))[:n].copy()
+        self.f_aux = np.ctypeslib.as_array(rf.f_aux, (max(n, 1),))[:n].copy()
+        self.feat_off = np.ctypeslib.as_array(rf.feat_off, (n_reads + 1,)).copy()
+        pl = rf.payload_len
+        self.payload = np.ctypeslib.as_array(rf.payload, (max(pl, 1),))[:pl].copy() if pl else np.zeros(0, np.uint8)
+        self.matrix = bytes(rf.matrix)
+        self.subst_counts = {'ACGTN'[r] + 'ACGTN'[b]: rf.subst_counts[r][b] for r in range(5) for b in range(5)
+                             if rf.subst_counts[r][b]}
+
+
+def extract(rd, ref):
+    """rows F2-F5 for one container.  rd = SoA dict (cramtools_b200.synth.reads layout)."""
+    n = len(rd['pos'])
+    rf = RecFeatures()
+    bases = np.ascontiguousarray(rd['bases'], np.uint8) if len(rd['bases']) else np.zeros(1, np.uint8)
+    cigar = np.ascontiguousarray(rd['cigar'], np.uint32) if len(rd['cigar']) else np.zeros(1, np.uint32)
+    ref = np.ascontiguousarray(ref, np.uint8)
+    rc = lib().rec_oracle_extract(n, _p(bases, u8p), _p(np.ascontiguousarray(rd['read_off'], np.int64), i64p),
+                                  _p(cigar, u32p), _p(np.ascontiguousarray(rd['cigar_off'], np.int64), i64p),
+                                  _p(np.ascontiguousarray(rd['pos'], np.int32), i32p),
+                                  _p(np.ascontiguousarray(rd['flag'], np.uint16), u16p), _p(ref, u8p), ref.size, _c.byref(rf))
+    if rc:
+        raise RuntimeError('Unsupported cigar operator')
+    out = Extracted(rf, n)
+    lib().rec_oracle_free(_c.byref(rf))
+    return out
+
+
+def quality(rd, ref, spec):
+    """row Q for every read.  -> (force_qs u8[n] (bit0 force, bit1 has array), scores u8[sum len] 0xFF = absent)"""
+    n = len(rd['pos'])
+    pol = parse_policies(spec)
+    arr, npol = (None, -1) if pol is None else pol
+    bases = np.ascontiguousarray(rd['bases'], np.uint8)
+    quals = np.ascontiguousarray(rd['quals'], np.uint8)
+    ref = np.ascontiguousarray(ref, np.uint8)
+    cigar = np.ascontiguousarray(rd['cigar'], np.uint32)
+    scores = np.full(max(bases.size, 1), 0xFF, np.uint8)
+    force = np.zeros(n, np.uint8)
+    rflags = rd.get('rflags', np.zeros(n, np.uint8))
+    dummy = np.zeros(1, np.uint8)
+    dummyc = np.zeros(1, np.uint32)
+    for r in range(n):
+        lo, hi = int(rd['read_off'][r]), int(rd['read_off'][r + 1])
+        c0, c1 = int(rd['cigar_off'][r]), int(rd['cigar_off'][r + 1])
+        rb = bases[lo:hi] if hi > lo else dummy
+        q = quals[lo:hi] if hi > lo else dummy
+        cg = cigar[c0:c1] if c1 > c0 else dummyc
+        sc = scores[lo:hi] if hi > lo else dummy
+        force[r] = lib().rec_oracle_quality(_p(rb, u8p), _p(q, u8p), hi - lo, 0 if (rflags[r] & 1) else 1, _p(cg, u32p),
+                                            c1 - c0, int(rd['pos'][r]), int(rd['flag'][r]), int(rd['mapq'][r]),
+                                            _p(ref, u8p), ref.size, arr, npol, _p(sc, u8p))
+    return force, scores[:bases.size]
+
+
+def restore_bases(pos, rlen, ex, r, window, window_off0, matrix):
+    """row N1 for read r of an Extracted feature set.  -> bytes or None (Java would throw)"""
+    a, b = int(ex.feat_off[r]), int(ex.feat_off[r + 1])
+    out = np.zeros(max(rlen, 1), np.uint8)
+    window = np.ascontiguousarray(window, np.uint8)
+    M = (_c.c_uint8 * 5)(*matrix)
+    op = ex.f_op[a:b] if b > a else np.zeros(1, np.uint8)
+    fp = ex.f_pos[a:b] if b > a else np.zeros(1, np.int32)
+    fv = ex.f_val[a:b] if b > a else np.zeros(1, np.int32)
+    fa = ex.f_aux[a:b] if b > a else np.zeros(1, np.int32)
+    pl = ex.payload if ex.payload.size else np.zeros(1, np.uint8)
+    rc = lib().rec_oracle_restore_bases(int(pos), rlen, b - a, _p(np.ascontiguousarray(op), u8p), _p(np.ascontiguousarray(fp), i32p),
+                                        _p(np.ascontiguousarray(fv), i32p), _p(np.ascontiguousarray(fa), i32p), _p(pl, u8p),
+                                        _p(window, u8p), window.size, window_off0, M, _p(out, u8p))
+    return None if rc else out[:rlen].tobytes()
+
+
+def restore_quals(force, rlen, scores, q_pos, q_val):
+    """row N2.  scores: stored array (forced) ; q_pos/q_val: Q features otherwise.  -> bytes or '*'"""
+    sc = np.array(scores, np.uint8).copy() if force else np.zeros(max(rlen, 1), np.uint8)
+    if sc.size == 0:
+        sc = np.zeros(1, np.uint8)
+    n = len(q_pos)
+    op = np.full(max(n, 1), ord('Q'), np.uint8)
+    fp = np.array(list(q_pos) + [0] * (1 if n == 0 else 0), np.int32)
+    fv = np.array(list(q_val) + [0] * (1 if n == 0 else 0), np.int32)
+    fa = np.zeros(max(n, 1), np.int32)
+    star = lib().rec_oracle_restore_quals(1 if force else 0, rlen, n, _p(op, u8p), _p(fp, i32p), _p(fv, i32p), _p(fa, i32p), _p(sc, u8p))
+    return '*' if star else sc[:rlen].tobytes()
+
+
+def write_streams(rd, ex, force, scores):
+    """row W: -> dict series name -> bytes"""
+    n = len(rd['pos'])
+    total = int(rd['read_off'][-1])
+    cap = 8 * total + 16 * int(ex.n_feat) + 16 * n + 64
+    bufs = [np.zeros(cap, np.uint8) for _ in STREAMS]
+    ptrs = (u8p * len(STREAMS))(*[_p(b, u8p) for b in bufs])
+    lens = np.zeros(len(STREAMS), np.int64)
+    rf = RecFeatures()
+    keep = [np.ascontiguousarray(x) if len(x) else np.zeros(1, x.dtype) for x in (ex.f_op, ex.f_pos, ex.f_val, ex.f_aux, ex.feat_off, ex.payload)]
+    rf.n_feat = ex.n_feat
+    rf.f_op = _p(keep[0], u8p); rf.f_pos = _p(keep[1], i32p); rf.f_val = _p(keep[2], i32p); rf.f_aux = _p(keep[3], i32p)
+    rf.feat_off = _p(keep[4], i64p); rf.payload = _p(keep[5], u8p); rf.payload_len = ex.payload.size
+    bases = np.ascontiguousarray(rd['bases'], np.uint8) if total else np.zeros(1, np.uint8)
+    sc = np.ascontiguousarray(scores, np.uint8) if total else np.zeros(1, np.uint8)
+    lib().rec_oracle_write_streams(n, _p(bases, u8p), _p(np.ascontiguousarray(rd['read_off'], np.int64), i64p),
+                                   _p(np.ascontiguousarray(rd['flag'], np.uint16), u16p),
+                                   _p(np.ascontiguousarray(rd['mapq'], np.uint8), u8p),
+                                   _p(np.ascontiguousarray(rd['pos'], np.int32), i32p), _c.byref(rf),
+                                   _p(np.ascontiguousarray(force, np.uint8), u8p), _p(sc, u8p), ptrs, _p(lens, i64p))
+    return {nm: bufs[i][:int(lens[i])].tobytes() for i, nm in enumerate(STREAMS)}
