@@ -150,6 +150,10 @@ def test_streams_consistent_with_features(G):
             v = st[name][cur[name]]; cur[name] += 1; return v
         for i in range(n):
             if rd['flag'][i] & 4:
+                rl = int(rd['read_off'][i + 1] - rd['read_off'][i])
+                cur['BA'] += rl                      # unmapped: bases go to BA one by one [Writer.java:254-258]
+                if force[i] & 1:
+                    cur['QS'] += rl
                 continue
             nf = itf8('FN')
             prev = 0
@@ -183,3 +187,5 @@ def test_streams_consistent_with_features(G):
             elif spec in g['lossy']:
                 exp = [[f[0], f[1]] for f in (g['lossy'][spec][i].get('features') or [])]
                 assert [[f[0], f[1]] for f in row] == exp, (spec, i)
+        for k in st:
+            assert cur[k] == len(st[k]), (spec, k)      # every byte of every stream accounted for
