@@ -6,3 +6,5 @@ tests and the benchmark exactly the way the Java shim of INTEGRATION.md uses the
 """
 from ._lib import Context, CramGpuError, default_context  # noqa: F401
 from .external_compression import ExternalCompression, ExternalCompressor, rans_bound  # noqa: F401
+from . import records  # noqa: F401,E402  (registers the record-feature entry points)
+from .records import QualityScorePreservation  # noqa: F401,E402

@@ -122,6 +122,9 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->scratch.p) cudaFree(ctx->scratch.p);
     if (ctx->dev_in.p) cudaFree(ctx->dev_in.p);
     if (ctx->dev_out.p) cudaFree(ctx->dev_out.p);
+    if (ctx->rec_scratch.p) cudaFree(ctx->rec_scratch.p);
+    if (ctx->rec_out.p) cudaFree(ctx->rec_out.p);
+    if (ctx->pin_rec) cudaFreeHost(ctx->pin_rec);
     if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
     if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
     if (ctx->pin_meta) cudaFreeHost(ctx->pin_meta);

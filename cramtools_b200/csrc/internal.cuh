@@ -65,6 +65,8 @@ struct cramgpu_ctx {
     uint64_t launches = 0;
     DevPool scratch;          // carved anew by every call
     DevPool dev_in, dev_out;  // device staging of the host entry points
+    DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
+    void *pin_rec = nullptr; size_t pin_rec_cap = 0;
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
     size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
     cudaEvent_t ev = nullptr;

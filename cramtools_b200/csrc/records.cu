@@ -1,1 +1,1015 @@
+// records.cu -- per-record work of the CRAM slice hot path for sm_100a.
+//
+// Encode (one warp per read, lanes over consecutive bases so every load of bases / qualities / reference is coalesced):
+//   k_rec_walk<false>  count pass: features per read, bytes per series, substitution histogram, force-preserve flag
+//   k_rec_matrix       SubstitutionMatrix ranking per container            [SubstitutionMatrix.java:42-57,141-169]
+//   k_rec_scan         per-container exclusive scans of the 14 per-read counters
+//   k_rec_layout       absolute offsets of every (container, series) region, feature / payload bases
+//   k_rec_walk<true>   write pass: feature arrays + the series bytes       [Writer.java:180-258]
+// Both passes run the same walk over the CIGAR, restating
+//   Sam2CramRecordFactory.createVariations / addSubstitutionsAndMaskedBases [Sam2CramRecordFactory.java:205-335]
+//   QualityScorePreservation.addQualityScores / addQS     (lossy/QualityScorePreservation.java:276-301,332-489)
+// Mismatch positions come from __ballot_sync; positions inside the feature list and inside each series come from
+// popc of the ballots (warp compaction), FP byte offsets from a warp prefix sum of the ITF8 lengths.
+//
+// Decode:
+//   k_norm             CramNormalizer.restoreReadBases / restoreQualityScores (build/CramNormalizer.java:287-434)
 #include "internal.cuh"
+
+#define NCNT 14
+enum { C_FN = 0, C_FC, C_FP, C_BS, C_DL, C_BA, C_SC, C_QS, C_RS, C_HC, C_PD, C_MQ, C_NFEAT, C_PAYLOAD };
+enum { OP_M = 0, OP_I, OP_D, OP_N, OP_S, OP_H, OP_P, OP_EQ, OP_X };
+#define SAM_UNMAPPED 4
+#define MAX_POL 16
+
+struct PolSet {
+    int n;                       // < 0: lossless
+    int per_base;                // any policy with base categories
+    cramgpu_qs_policy p[MAX_POL];
+};
+
+struct RecArgs {
+    // inputs
+    const uint8_t *ref, *bases, *quals;
+    const uint64_t *read_off, *cigar_off;
+    const uint32_t *cigar;
+    const int32_t *pos;
+    const uint16_t *flag;
+    const uint8_t *mapq, *rflags;
+    const uint64_t *cont_off, *ref_off, *ref_len;    // device copies of the host tables
+    uint32_t n_containers;
+    uint64_t n_reads;
+    // pass-1 outputs / pass-2 inputs
+    uint32_t *cnt;               // [NCNT][n_reads]: counts, then container-local exclusive offsets
+    uint8_t *force;              // [n_reads]
+    unsigned long long *subst;   // [n_containers][25]
+    const uint8_t *codes;        // [n_containers][32]: 25 codes + pad
+    const uint64_t *base;        // [n_containers][NCNT] absolute bases (series: byte offset in streams)
+    int32_t *status;             // [1] first error
+    // pass-2 outputs
+    uint8_t *f_op; int32_t *f_pos, *f_val, *f_aux; uint64_t *feat_off;
+    uint8_t *payload, *streams;
+    uint64_t *read_qs_off, *read_ba_off;
+};
+
+__device__ __forceinline__ uint8_t norm_base(uint8_t b)      // cram/build/Utils.normalizeBase [Utils.java:31-49]
+{
+    uint8_t u = b & 0xDF;                                     // upper-case letters
+    bool letter = (b | 0x20) == 'a' || (b | 0x20) == 'c' || (b | 0x20) == 'g' || (b | 0x20) == 't';
+    return letter ? u : (uint8_t)'N';
+}
+__device__ __forceinline__ int base_index(uint8_t b)
+{
+    return b == 'A' ? 0 : b == 'C' ? 1 : b == 'G' ? 2 : b == 'T' ? 3 : b == 'N' ? 4 : -1;
+}
+__device__ __forceinline__ uint32_t itf8_len(uint32_t v)     // ITF8.writeUnsignedITF8 [ITF8.java:53-84]
+{
+    return v < (1u << 7) ? 1 : v < (1u << 14) ? 2 : v < (1u << 21) ? 3 : v < (1u << 28) ? 4 : 5;
+}
+__device__ __forceinline__ void itf8_put(uint8_t *p, uint32_t v)
+{
+    if (v < (1u << 7)) { p[0] = (uint8_t)v; }
+    else if (v < (1u << 14)) { p[0] = (uint8_t)((v >> 8) | 0x80); p[1] = (uint8_t)v; }
+    else if (v < (1u << 21)) { p[0] = (uint8_t)((v >> 16) | 0xC0); p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)v; }
+    else if (v < (1u << 28)) { p[0] = (uint8_t)((v >> 24) | 0xE0); p[1] = (uint8_t)(v >> 16); p[2] = (uint8_t)(v >> 8); p[3] = (uint8_t)v; }
+    else { p[0] = (uint8_t)((v >> 28) | 0xF0); p[1] = (uint8_t)(v >> 20); p[2] = (uint8_t)(v >> 12); p[3] = (uint8_t)(v >> 4); p[4] = (uint8_t)v; }
+}
+__device__ __forceinline__ bool consumes_read(int op) { return op == OP_M || op == OP_I || op == OP_S || op == OP_EQ || op == OP_X; }
+__device__ __forceinline__ bool consumes_ref(int op) { return op == OP_M || op == OP_D || op == OP_N || op == OP_EQ || op == OP_X; }
+
+// Binning.Illumina_binning_matrix (lossy/Binning.java:63-71), as the closed form of its 110 entries
+__device__ __forceinline__ uint8_t illumina_bin(uint8_t q)
+{
+    return q < 2 ? q : q < 10 ? 6 : q < 20 ? 15 : q < 25 ? 22 : q < 30 ? 27 : q < 35 ? 33 : q < 40 ? 37 : 40;
+}
+__device__ __forceinline__ uint8_t treat(uint8_t q, int treatment)
+{
+    return treatment == 1 ? illumina_bin(q) : treatment == 2 ? (uint8_t)0xFF : q;
+}
+__device__ __forceinline__ bool read_in_category(const cramgpu_qs_policy &p, uint16_t flag, uint8_t mapq)
+{
+    switch (p.read_cat) {
+    case 0: case 1: return true;
+    case 2: return (flag & SAM_UNMAPPED) != 0;
+    case 3: return (int)mapq < p.read_param;
+    default: return (int)mapq > p.read_param;
+    }
+}
+// mask value of one per-base policy at one base (QualityScorePreservation.java:398-476)
+__device__ __forceinline__ bool base_mask(const cramgpu_qs_policy &p, bool match, bool is_ins, bool dmark)
+{
+    bool m = false;
+    for (int b = 0; b < p.n_base_cats; b++) {
+        switch (p.base_cat[b]) {
+        case 1: m = match; break;          // MATCH: assignment for every read-consuming position
+        case 2: m = !match; break;         // MISMATCH
+        case 3: m = m || dmark; break;     // FLANKING_DELETION: only sets
+        case 4: m = m || is_ins; break;    // INSERTION: only sets
+        }
+    }
+    return m;
+}
+// the score addQualityScores leaves at one base (0xFF = -1 = none), policies in their sorted order
+__device__ __forceinline__ uint8_t score_at(const PolSet &ps, uint8_t q, uint16_t flag, uint8_t mapq, int32_t pos,
+                                            bool match, bool is_ins, bool dmark)
+{
+    uint8_t s = 0xFF;
+    for (int k = 0; k < ps.n; k++) {
+        const cramgpu_qs_policy &p = ps.p[k];
+        if (!read_in_category(p, flag, mapq)) continue;
+        if (p.n_base_cats == 0) { if (p.treatment != 2) s = treat(q, p.treatment); }
+        else if (pos != 0 && base_mask(p, match, is_ins, dmark)) s = treat(q, p.treatment);
+    }
+    return s;
+}
+
+__device__ __forceinline__ uint32_t warp_excl_scan_u32(uint32_t v, uint32_t lane, uint32_t &total)
+{
+    uint32_t s = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xFFFFFFFFu, s, d);
+        if (lane >= (uint32_t)d) s += t;
+    }
+    total = __shfl_sync(0xFFFFFFFFu, s, 31);
+    return s - v;
+}
+
+// container of read r: binary search over cont_off
+__device__ __forceinline__ uint32_t container_of(const uint64_t *cont_off, uint32_t nc, uint64_t r)
+{
+    uint32_t lo = 0, hi = nc;              // cont_off[lo] <= r < cont_off[hi]
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (cont_off[mid] <= r) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.n_reads) return;
+    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    const uint8_t *ref = a.ref + a.ref_off[c];
+    const int64_t ref_len = (int64_t)a.ref_len[c];
+    const uint64_t lo = a.read_off[r];
+    const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
+    const uint8_t *rb = a.bases + lo, *rq = a.quals + lo;
+    const uint64_t c0 = a.cigar_off[r], c1 = a.cigar_off[r + 1];
+    const int32_t pos = a.pos[r];
+    const uint16_t flag = a.flag[r];
+    const uint8_t mapq = a.mapq[r];
+    const uint8_t rfl = a.rflags ? a.rflags[r] : 0;
+    const bool has_quals = !(rfl & CRAMGPU_RF_NO_QUALS);
+    const bool mapped = !(flag & SAM_UNMAPPED);
+    const bool hasfeat = mapped && pos != 0;
+
+    // ---- force-preserve flag (count pass); bit1 = record carries a score array
+    uint8_t force;
+    if (!WRITE) {
+        if (ps.n < 0) force = has_quals ? 3 : 0;                                   // CramSerilization.java:160-161
+        else if (!has_quals) force = 0;                                            // QualityScorePreservation.java:277-281
+        else {
+            bool f = false;
+            uint32_t masked[MAX_POL];
+            for (int k = 0; k < MAX_POL; k++) masked[k] = 0;
+            if (ps.per_base && pos != 0) {
+                int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
+                for (uint64_t ci = c0; ci < c1; ci++) {
+                    uint32_t cw = a.cigar[ci]; int op = cw & 15; int64_t len = cw >> 4;
+                    if (op == OP_D) { if (d_a != z) { d_b = d_a; d_a = z; } }
+                    if (consumes_read(op)) {
+                        for (int64_t i0 = 0; i0 < len; i0 += 32) {
+                            int64_t i = i0 + lane;
+                            bool in = i < len && z + i < rlen;
+                            int64_t zi = z + i;
+                            uint8_t b = in ? rb[zi] : 0;
+                            int64_t rp = (int64_t)pos - 1 + aoff + i;
+                            uint8_t tb = (in && rp >= 0 && rp < ref_len) ? ref[rp] : 0;   // tracks.baseAt(refPos + i)
+                            bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
+                            for (int k = 0; k < ps.n; k++)
+                                if (ps.p[k].n_base_cats) {
+                                    bool m = in && base_mask(ps.p[k], b == tb, op == OP_I, dm);
+                                    masked[k] += __popc(__ballot_sync(0xFFFFFFFFu, m));
+                                }
+                        }
+                        z += len;
+                    }
+                    if (consumes_ref(op)) aoff += len;
+                }
+            }
+            for (int k = 0; k < ps.n; k++) {
+                const cramgpu_qs_policy &p = ps.p[k];
+                if (!read_in_category(p, flag, mapq)) continue;
+                if (p.n_base_cats == 0) f = p.treatment != 2;                      // BIN / PRESERVE force, DROP clears
+                else if (pos != 0 && (int64_t)masked[k] > rlen / 2) f = true;      // safety latch [:487-488]
+            }
+            force = (f ? 1 : 0) | 2;
+        }
+        if (lane == 0) a.force[r] = force;
+    } else {
+        force = a.force[r];
+    }
+    const bool forced = force & 1;
+    const bool q_feats = !forced && (force & 2) && ps.n >= 0;        // sparse Q features possible
+
+    // ---- running series cursors (uniform across the warp)
+    uint32_t n_feat = 0, n_fp = 0, n_bs = 0, n_dl = 0, n_ba = 0, n_sc = 0, n_qs = 0, n_rs = 0, n_hc = 0, n_pd = 0, n_pay = 0;
+    int32_t prev = 0;
+    // write-pass bases
+    uint64_t fbase = 0, paybase = 0;
+    uint8_t *sFC = nullptr, *sFP = nullptr, *sBS = nullptr, *sDL = nullptr, *sBA = nullptr, *sSC = nullptr, *sQS = nullptr,
+            *sRS = nullptr, *sHC = nullptr, *sPD = nullptr;
+    if (WRITE) {
+        const uint64_t *B = a.base + (size_t)c * NCNT;
+        auto at = [&](int k) -> uint64_t { return B[k] + a.cnt[(size_t)k * a.n_reads + r]; };
+        fbase = at(C_NFEAT); paybase = at(C_PAYLOAD);
+        sFC = a.streams + at(C_FC); sFP = a.streams + at(C_FP); sBS = a.streams + at(C_BS); sDL = a.streams + at(C_DL);
+        sBA = a.streams + at(C_BA); sSC = a.streams + at(C_SC); sQS = a.streams + at(C_QS); sRS = a.streams + at(C_RS);
+        sHC = a.streams + at(C_HC); sPD = a.streams + at(C_PD);
+        if (lane == 0) {
+            a.feat_off[r] = fbase;                      // feat_off[n_reads] is filled in by the launcher
+            a.read_qs_off[r] = ~0ull;
+            a.read_ba_off[r] = ~0ull;
+        }
+    }
+
+    if (!mapped) {
+        // unmapped: bases one by one into BA (unless unknown), then the preserved scores [Writer.java:254-258]
+        if (!(rfl & CRAMGPU_RF_NO_BASES)) {
+            if (WRITE) {
+                for (int64_t i = lane; i < rlen; i += 32) sBA[i] = rb[i];
+                if (lane == 0) a.read_ba_off[r] = (uint64_t)(sBA - a.streams);
+            }
+            n_ba += (uint32_t)rlen;
+        }
+    } else if (hasfeat) {
+        const uint8_t *codes = WRITE ? a.codes + (size_t)c * 32 : nullptr;
+        int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
+        for (uint64_t ci = c0; ci < c1; ci++) {
+            uint32_t cw = a.cigar[ci]; int op = cw & 15; int64_t len = cw >> 4;
+            if (op > OP_X) { if (lane == 0) atomicCAS(a.status, 0, CRAMGPU_ERR_ARG); break; }   // "Unsupported cigar operator"
+            if (op == OP_D) { if (d_a != z) { d_b = d_a; d_a = z; } }
+            if (!consumes_read(op)) {
+                // D, N, H, P: one feature at the next read position [:228-240]
+                int32_t fpos = (int32_t)z + 1;
+                uint32_t dl = itf8_len((uint32_t)(fpos - prev)), vl = itf8_len((uint32_t)len);
+                if (WRITE && lane == 0) {
+                    uint64_t fi = fbase + n_feat;
+                    uint8_t opc = op == OP_D ? 'D' : op == OP_N ? 'N' : op == OP_H ? 'H' : 'P';
+                    a.f_op[fi] = opc; a.f_pos[fi] = fpos; a.f_val[fi] = (int32_t)len; a.f_aux[fi] = 0;
+                    sFC[n_feat] = opc;
+                    itf8_put(sFP + n_fp, (uint32_t)(fpos - prev));
+                    uint8_t *dst = op == OP_D ? sDL + n_dl : op == OP_N ? sRS + n_rs : op == OP_H ? sHC + n_hc : sPD + n_pd;
+                    itf8_put(dst, (uint32_t)len);
+                }
+                n_feat++; n_fp += dl; prev = fpos;
+                if (op == OP_D) n_dl += vl; else if (op == OP_N) n_rs += vl; else if (op == OP_H) n_hc += vl; else n_pd += vl;
+            } else {
+                const bool isM = op == OP_M || op == OP_EQ || op == OP_X;
+                if (op == OP_S) {
+                    // SoftClip(pos, bases[pos .. pos+len)) [:268-272]; bytes + TAB into SC, bytes into the payload
+                    if (WRITE) {
+                        for (int64_t i = lane; i < len; i += 32) {
+                            uint8_t b = rlen ? rb[z + i] : (uint8_t)'N';
+                            sSC[n_sc + i] = b; a.payload[paybase + n_pay + i] = b;
+                        }
+                        if (lane == 0) sSC[n_sc + len] = '\t';
+                    }
+                }
+                for (int64_t i0 = 0; i0 < len; i0 += 32) {
+                    int64_t i = i0 + lane;
+                    bool in = i < len;
+                    int64_t zi = z + i;
+                    uint8_t b = in ? (rlen ? rb[zi] : (uint8_t)'N') : 0;                      // empty bases -> 'N' x cigarLen [:218-220]
+                    int64_t rp = (int64_t)pos - 1 + aoff + i;
+                    uint8_t rraw = (in && rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                    uint8_t refb = norm_base((in && rp < ref_len) ? rraw : (uint8_t)'N');     // [:306-308]
+                    bool isX = in && isM && b != refb;
+                    bool hasF = in && (isX || op == OP_I || (op == OP_S && i == 0));
+                    uint8_t sc = 0xFF;
+                    if (q_feats && in && zi < rlen) {
+                        bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
+                        sc = score_at(ps, rq[zi], flag, mapq, pos, b == rraw, op == OP_I, dm);
+                    }
+                    bool hasQ = sc < 128;                                                     // scores[i] > -1 [:290]
+                    uint32_t bF = __ballot_sync(0xFFFFFFFFu, hasF), bQ = __ballot_sync(0xFFFFFFFFu, hasQ);
+                    uint32_t bAny = bF | bQ;
+                    if (bAny) {
+                        uint32_t lt = (1u << lane) - 1u;
+                        int32_t mypos = (int32_t)zi + 1;
+                        // position of the previous feature: nearest lower lane with a feature, else the carried one
+                        uint32_t below = bAny & lt;
+                        int32_t pprev = below ? (int32_t)(z + i0 + (31 - __clz(below))) + 1 : prev;
+                        uint32_t dF = hasF ? (uint32_t)(mypos - pprev) : 0;
+                        uint32_t dQ = hasQ ? (hasF ? 0u : (uint32_t)(mypos - pprev)) : 0;
+                        uint32_t lF = hasF ? itf8_len(dF) : 0, lQ = hasQ ? itf8_len(dQ) : 0;
+                        uint32_t fp_tot, fp_off = warp_excl_scan_u32(lF + lQ, lane, fp_tot);
+                        uint32_t fidx = n_feat + __popc(bF & lt) + __popc(bQ & lt);
+                        uint32_t bX = __ballot_sync(0xFFFFFFFFu, isX), bI = __ballot_sync(0xFFFFFFFFu, in && op == OP_I);
+                        if (!WRITE) {
+                            if (isX) {
+                                int ri = base_index(refb), bi = base_index(b);
+                                if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
+                            }
+                        } else {
+                            if (hasF) {
+                                uint64_t fi = fbase + fidx;
+                                uint8_t opc = isX ? 'X' : op == OP_I ? 'i' : 'S';
+                                a.f_op[fi] = opc; a.f_pos[fi] = mypos;
+                                sFC[fidx] = opc;
+                                itf8_put(sFP + n_fp + fp_off, dF);
+                                if (isX) {
+                                    int ri = base_index(refb), bi = base_index(b);
+                                    uint8_t code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;  // codes[][] default 0 [:39]
+                                    a.f_val[fi] = code; a.f_aux[fi] = (int32_t)b | ((int32_t)refb << 8);
+                                    sBS[n_bs + __popc(bX & lt)] = code;
+                                } else if (op == OP_I) {
+                                    a.f_val[fi] = b; a.f_aux[fi] = 0;
+                                    sBA[n_ba + __popc(bI & lt)] = b;
+                                } else {
+                                    a.f_val[fi] = (int32_t)(paybase + n_pay); a.f_aux[fi] = (int32_t)len;
+                                }
+                            }
+                            if (hasQ) {
+                                uint64_t fi = fbase + fidx + (hasF ? 1 : 0);
+                                a.f_op[fi] = 'Q'; a.f_pos[fi] = mypos; a.f_val[fi] = sc; a.f_aux[fi] = 0;
+                                sFC[fidx + (hasF ? 1 : 0)] = 'Q';
+                                itf8_put(sFP + n_fp + fp_off + lF, dQ);
+                                sQS[n_qs + __popc(bQ & lt)] = sc;
+                            }
+                        }
+                        n_feat += __popc(bF) + __popc(bQ);
+                        n_fp += fp_tot;
+                        n_bs += __popc(bX); n_ba += __popc(bI); n_qs += __popc(bQ);
+                        prev = (int32_t)(z + i0 + (31 - __clz(bAny))) + 1;
+                    }
+                }
+                if (op == OP_S) { n_sc += (uint32_t)len + 1; n_pay += (uint32_t)len; }
+                z += len;
+            }
+            if (consumes_ref(op)) aoff += len;
+        }
+    }
+    // preserved score array after the features (mapped) or after the bases (unmapped) [Writer.java:250-251,257-258]
+    if (forced) {
+        if (WRITE) {
+            // lossless: the array is the record's own qualities; under a lossy model k_rec_forced_scores fills it in
+            if (ps.n < 0) for (int64_t i = lane; i < rlen; i += 32) sQS[n_qs + i] = rq[i];
+            if (lane == 0) a.read_qs_off[r] = (uint64_t)(sQS + n_qs - a.streams);
+        }
+        n_qs += (uint32_t)rlen;
+    }
+    if (!WRITE && lane == 0) {
+        uint32_t *cn = a.cnt + r;
+        const uint64_t N = a.n_reads;
+        cn[C_FN * N] = mapped ? itf8_len(n_feat) : 0;
+        cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_BS * N] = n_bs; cn[C_DL * N] = n_dl; cn[C_BA * N] = n_ba;
+        cn[C_SC * N] = n_sc; cn[C_QS * N] = n_qs; cn[C_RS * N] = n_rs; cn[C_HC * N] = n_hc; cn[C_PD * N] = n_pd;
+        cn[C_MQ * N] = mapped ? itf8_len(mapq) : 0;
+        cn[C_NFEAT * N] = n_feat; cn[C_PAYLOAD * N] = n_pay;
+    }
+    if (WRITE && lane == 0 && mapped) {
+        const uint64_t *B = a.base + (size_t)c * NCNT;
+        itf8_put(a.streams + B[C_FN] + a.cnt[(size_t)C_FN * a.n_reads + r], n_feat);
+        itf8_put(a.streams + B[C_MQ] + a.cnt[(size_t)C_MQ * a.n_reads + r], mapq);
+    }
+}
+
+// Forced arrays under a lossy model need the per-base scores again; done by a second small kernel so that the walk above
+// stays simple: one warp per read, same CIGAR walk, writes into the already reserved QS slot.
+__global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.n_reads) return;
+    if (!(a.force[r] & 1)) return;
+    uint64_t qoff = a.read_qs_off[r];
+    if (qoff == ~0ull) return;
+    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    const uint8_t *ref = a.ref + a.ref_off[c];
+    const int64_t ref_len = (int64_t)a.ref_len[c];
+    const uint64_t lo = a.read_off[r];
+    const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
+    const uint8_t *rb = a.bases + lo, *rq = a.quals + lo;
+    const int32_t pos = a.pos[r];
+    const uint16_t flag = a.flag[r];
+    const uint8_t mapq = a.mapq[r];
+    uint8_t *dst = a.streams + qoff;
+    // read-level part of every base (bases not covered by a read-consuming CIGAR op see only these policies)
+    for (int64_t i = lane; i < rlen; i += 32) dst[i] = score_at(ps, rq[i], flag, mapq, 0, false, false, false);
+    if (!ps.per_base || pos == 0) return;
+    __syncwarp();
+    int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
+    for (uint64_t ci = a.cigar_off[r]; ci < a.cigar_off[r + 1]; ci++) {
+        uint32_t cw = a.cigar[ci]; int op = cw & 15; int64_t len = cw >> 4;
+        if (op == OP_D) { if (d_a != z) { d_b = d_a; d_a = z; } }
+        if (consumes_read(op)) {
+            for (int64_t i = lane; i < len; i += 32) {
+                int64_t zi = z + i;
+                if (zi >= rlen) break;
+                int64_t rp = (int64_t)pos - 1 + aoff + i;
+                uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
+                dst[zi] = score_at(ps, rq[zi], flag, mapq, pos, rb[zi] == tb, op == OP_I, dm);
+            }
+            z += len;
+        }
+        if (consumes_ref(op)) aoff += len;
+    }
+}
+
+// SubstitutionMatrix.<init>(long[][]) / rank [SubstitutionMatrix.java:42-57,129-169]: one thread per container
+__global__ void k_rec_matrix(const unsigned long long *__restrict__ subst, uint32_t nc, uint8_t *__restrict__ codes,
+                             uint8_t *__restrict__ matrix)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= nc) return;
+    const unsigned long long *cnt = subst + (size_t)c * 25;
+    for (int r = 0; r < 5; r++) {
+        int base[4]; long long freq[4]; int k = 0;
+        for (int b = 0; b < 5; b++) if (b != r) { base[k] = b; freq[k] = (long long)cnt[r * 5 + b]; k++; }
+        for (int i = 1; i < 4; i++) {                       // stable insertion sort with the reference's comparator
+            int bb = base[i]; long long ff = freq[i]; int j = i - 1;
+            while (j >= 0) {
+                int cmp = (freq[j] != ff) ? (int)(unsigned int)(unsigned long long)(ff - freq[j]) : (base[j] - bb);
+                if (cmp > 0) { base[j + 1] = base[j]; freq[j + 1] = freq[j]; j--; } else break;
+            }
+            base[j + 1] = bb; freq[j + 1] = ff;
+        }
+        int rank_of[5] = {0, 0, 0, 0, 0};
+        for (int i = 0; i < 4; i++) rank_of[base[i]] = i;
+        uint8_t byte = 0;
+        for (int b = 0; b < 5; b++) {
+            codes[(size_t)c * 32 + r * 5 + b] = (b == r) ? 0 : (uint8_t)rank_of[b];
+            if (b != r) byte = (uint8_t)((byte << 2) | rank_of[b]);
+        }
+        matrix[(size_t)c * 8 + r] = byte;
+    }
+    matrix[(size_t)c * 8 + 5] = matrix[(size_t)c * 8 + 6] = matrix[(size_t)c * 8 + 7] = 0;
+}
+
+// per-container exclusive scans of the per-read counters: grid (n_containers, NCNT), 256 threads
+__global__ void __launch_bounds__(256) k_rec_scan(uint32_t *__restrict__ cnt, const uint64_t *__restrict__ cont_off,
+                                                  uint64_t n_reads, uint64_t *__restrict__ totals)
+{
+    uint32_t c = blockIdx.x, k = blockIdx.y;
+    uint64_t r0 = cont_off[c], r1 = cont_off[c + 1];
+    uint32_t *v = cnt + (size_t)k * n_reads;
+    __shared__ uint32_t wsum[8];
+    __shared__ unsigned long long carry;
+    uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (uint64_t base = r0; base < r1; base += 256) {
+        uint64_t r = base + tid;
+        uint32_t x = r < r1 ? v[r] : 0;
+        uint32_t tot, ex = warp_excl_scan_u32(x, lane, tot);
+        if (lane == 0) wsum[w] = tot;
+        __syncthreads();
+        uint32_t off = 0, all = 0;
+        for (uint32_t j = 0; j < 8; j++) { if (j < w) off += wsum[j]; all += wsum[j]; }
+        unsigned long long cbase = carry;
+        if (r < r1) v[r] = (uint32_t)(cbase + off + ex);
+        __syncthreads();
+        if (tid == 0) carry = cbase + all;
+        __syncthreads();
+    }
+    if (tid == 0) totals[(size_t)c * NCNT + k] = carry;
+}
+
+// absolute bases: one thread walks the (container, counter) totals.  Series regions start at multiples of 16.
+// grand[0] = bytes of streams, grand[1] = features, grand[2] = payload bytes
+__global__ void k_rec_layout(const uint64_t *__restrict__ totals, uint32_t nc, uint64_t *__restrict__ base,
+                             uint64_t *__restrict__ stream_off, uint64_t *__restrict__ stream_len, uint64_t *__restrict__ grand)
+{
+    if (blockIdx.x || threadIdx.x) return;
+    uint64_t sbytes = 0, feats = 0, pay = 0;
+    for (uint32_t c = 0; c < nc; c++) {
+        for (int k = 0; k < CRAMGPU_S_COUNT; k++) {
+            uint64_t t = totals[(size_t)c * NCNT + k];
+            base[(size_t)c * NCNT + k] = sbytes;
+            stream_off[(size_t)c * CRAMGPU_S_COUNT + k] = sbytes;
+            stream_len[(size_t)c * CRAMGPU_S_COUNT + k] = t;
+            sbytes += (t + 15) & ~15ull;
+        }
+        base[(size_t)c * NCNT + C_NFEAT] = feats; feats += totals[(size_t)c * NCNT + C_NFEAT];
+        base[(size_t)c * NCNT + C_PAYLOAD] = pay; pay += totals[(size_t)c * NCNT + C_PAYLOAD];
+    }
+    grand[0] = sbytes; grand[1] = feats; grand[2] = pay;
+}
+
+// ------------------------------------------------------------------------------------------------ decode
+
+struct NormArgs {
+    uint64_t n_reads; uint32_t n_containers;
+    const uint64_t *cont_off, *win_off, *win_len; const int64_t *win_start0;      // device copies
+    const uint8_t *ref, *matrix;
+    const int32_t *pos; const uint64_t *read_off; const uint8_t *rflags; const uint64_t *feat_off;
+    const uint8_t *f_op; const int32_t *f_pos, *f_val, *f_aux; const uint8_t *payload;
+    const uint8_t *qs; const uint64_t *read_qs_off; const uint8_t *ba; const uint64_t *read_ba_off;
+    uint8_t *bases, *quals, *qual_star; int32_t *status;
+};
+
+// base with rank `code` for normalised reference base r: SubstitutionMatrix(byte[]) / base() [:59-..,177]
+__device__ __forceinline__ uint8_t matrix_base(const uint8_t *m, uint8_t refb, int code)
+{
+    int r = base_index(refb);
+    const char B[5] = {'A', 'C', 'G', 'T', 'N'};
+    int k = 0;
+    uint8_t out = 'N';
+    for (int b = 0; b < 5; b++) {
+        if (b == r) continue;
+        int rank = (m[r] >> (2 * (3 - k))) & 3;
+        if (rank == code) out = (uint8_t)B[b];
+        k++;
+    }
+    return out;
+}
+
+// one warp per record
+__global__ void __launch_bounds__(128) k_norm(NormArgs a)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.n_reads) return;
+    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    const uint8_t *ref = a.ref + a.win_off[c];
+    const int64_t ref_len = (int64_t)a.win_len[c], off0 = a.win_start0[c];
+    const uint8_t *mtx = a.matrix + (size_t)c * 8;
+    const uint64_t lo = a.read_off[r];
+    const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
+    const uint8_t rfl = a.rflags[r];
+    const uint64_t f0 = a.feat_off[r], f1 = a.feat_off[r + 1];
+    uint8_t *bases = a.bases + lo, *quals = a.quals + lo;
+    int bad = 0;
+
+    // ---- bases: CramNormalizer.restoreBases / restoreReadBases (build/CramNormalizer.java:208-244,335-434)
+    if (rfl & CRAMGPU_NF_UNKNOWN_BASES) {
+        // NULL_SEQUENCE: nothing to write (readLength bytes stay as they are; callers treat the read as '*')
+    } else if (rfl & CRAMGPU_NF_UNMAPPED) {
+        uint64_t bo = a.read_ba_off[r];
+        if (bo != ~0ull) for (int64_t i = lane; i < rlen; i += 32) bases[i] = a.ba[bo + i];
+    } else if (rlen > 0) {
+        const int64_t al0 = (int64_t)a.pos[r] - 1;
+        if (f0 == f1) {
+            // no features: straight copy, 'N' fill when the record overhangs the region (:346-362); no normalizeBase here
+            if (ref_len + off0 < al0 + rlen) {
+                int64_t o = al0 - off0, avail = ref_len - o;
+                int64_t ncopy = (o > 0 && avail > 0) ? (rlen < avail ? rlen : avail) : 0;
+                for (int64_t i = lane; i < rlen; i += 32) bases[i] = i < ncopy ? ref[o + i] : (uint8_t)'N';
+            } else if (al0 - off0 < 0) {
+                bad = 1;
+            } else {
+                for (int64_t i = lane; i < rlen; i += 32) bases[i] = ref[al0 - off0 + i];
+            }
+        } else {
+            int64_t pir = 1, pis = 0;      // posInRead (1-based), posInSeq
+            for (uint64_t f = f0; f < f1 && !bad; f++) {
+                int64_t fpos = a.f_pos[f];
+                uint8_t op = a.f_op[f];
+                // reference bases up to the feature (:365-373)
+                int64_t n = fpos - pir;
+                if (n > 0) {
+                    if (al0 + pis - off0 < 0 || fpos - 1 > rlen) { bad = 1; break; }
+                    for (int64_t i = lane; i < n; i += 32) {
+                        int64_t rp = al0 + pis + i - off0;
+                        bases[pir - 1 + i] = norm_base(rp >= ref_len ? (uint8_t)'N' : ref[rp]);
+                    }
+                    pir += n; pis += n;
+                }
+                switch (op) {
+                case 'X': {
+                    int64_t rp = al0 + pis - off0;
+                    if (rp < 0 || pir > rlen) { bad = 1; break; }
+                    uint8_t refb = norm_base(rp >= ref_len ? (uint8_t)'N' : ref[rp]);
+                    if (lane == 0) bases[pir - 1] = norm_base(matrix_base(mtx, refb, a.f_val[f]));
+                    pir++; pis++;
+                    break;
+                }
+                case 'S': case 'I': {
+                    int64_t ln = a.f_aux[f];
+                    if (pir - 1 + ln > rlen) { bad = 1; break; }
+                    for (int64_t i = lane; i < ln; i += 32) bases[pir - 1 + i] = norm_base(a.payload[a.f_val[f] + i]);
+                    pir += ln;
+                    break;
+                }
+                case 'D': case 'N': pis += a.f_val[f]; break;
+                case 'i':
+                    if (pir > rlen) { bad = 1; break; }
+                    if (lane == 0) bases[pir - 1] = norm_base((uint8_t)a.f_val[f]);
+                    pir++;
+                    break;
+                default: break;            // H, P, Q, B consume nothing here
+                }
+            }
+            if (!bad) {
+                // tail from the reference while it lasts (:412-415); what is left stays 0 -> normalizeBase -> 'N'
+                int64_t n = rlen - pir + 1;
+                if (n > 0 && al0 + pis - off0 < 0) bad = 1;
+                for (int64_t i = lane; i < n && !bad; i += 32) {
+                    int64_t rp = al0 + pis + i - off0;
+                    bases[pir - 1 + i] = rp < ref_len ? norm_base(ref[rp]) : (uint8_t)'N';
+                }
+                __syncwarp();
+                for (uint64_t f = f0; f < f1; f++)          // ReadBase overwrites (:418-427)
+                    if (a.f_op[f] == 'B' && lane == 0) bases[a.f_pos[f] - 1] = norm_base((uint8_t)a.f_val[f]);
+            }
+        }
+    }
+
+    // ---- qualities: restoreQualityScores (:287-333)
+    const uint8_t dflt = '?' - '!';
+    uint32_t star;
+    if (!(rfl & CRAMGPU_NF_FORCE_QS)) {
+        for (int64_t i = lane; i < rlen; i += 32) quals[i] = dflt;
+        __syncwarp();
+        uint32_t any = 0;
+        for (uint64_t f = f0 + lane; f < f1; f += 32) {
+            uint8_t op = a.f_op[f];
+            if (op == 'Q') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_val[f]; any = 1; }
+            else if (op == 'B') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_aux[f]; any = 1; }
+        }
+        star = __ballot_sync(0xFFFFFFFFu, any) == 0;
+    } else {
+        uint64_t qo = a.read_qs_off[r];
+        uint32_t present = 0;
+        for (int64_t i = lane; i < rlen; i += 32) {
+            uint8_t s = qo != ~0ull ? a.qs[qo + i] : (uint8_t)0xFF;
+            if (s == 0xFF) s = dflt; else present = 1;
+            quals[i] = s;
+        }
+        star = __ballot_sync(0xFFFFFFFFu, present) == 0;     // missingScores == scores.length
+    }
+    if (lane == 0) {
+        a.qual_star[r] = (uint8_t)star;
+        a.status[r] = bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ host side
+
+#include <string.h>
+
+// QualityScorePreservation.parsePolicies / parseSinglePolicy / readParam / readTreatment
+// (src/main/java/htsjdk/samtools/cram/lossy/QualityScorePreservation.java:141-256)
+extern "C" int cramgpu_parse_lossy_spec(const char *spec, cramgpu_qs_policy *out, int cap)
+{
+    if (!spec || !out || cap <= 0) return CRAMGPU_ERR_ARG;
+    int n = 0;
+    size_t pos = 0, total = strlen(spec);
+    while (pos <= total) {
+        const char *dash = strchr(spec + pos, '-');
+        size_t end = dash ? (size_t)(dash - spec) : total;
+        if (end > pos) {
+            if (n == cap) return CRAMGPU_ERR_ARG;
+            cramgpu_qs_policy p;
+            memset(&p, 0, sizeof p);
+            bool have_treatment = false;
+            size_t i = pos;
+            auto read_param = [&]() { int v = 0; while (i < end && spec[i] >= '0' && spec[i] <= '9') v = v * 10 + (spec[i++] - '0'); return v; };
+            auto read_treatment = [&]() {
+                int prm = read_param();
+                have_treatment = true;
+                p.treat_param = prm;
+                p.treatment = prm == 0 ? 2 : prm == 40 ? 0 : 1;        // 0 -> drop, 40 -> preserve, else bin(param)
+            };
+            auto add_cat = [&](int cat) { if (p.n_base_cats < 8) p.base_cat[p.n_base_cats++] = cat; };
+            while (i < end) {
+                char code = spec[i++];
+                switch (code) {
+                case 'R': add_cat(1); read_treatment(); break;
+                case 'N': add_cat(2); read_treatment(); break;
+                case 'D': add_cat(3); read_treatment(); break;
+                case 'I': add_cat(4); read_treatment(); break;
+                case 'M': p.read_cat = 4; p.read_param = read_param(); break;
+                case 'm': p.read_cat = 3; p.read_param = read_param(); break;
+                case 'U': p.read_cat = 2; read_treatment(); break;
+                case '_': read_treatment(); break;
+                case '*': p.read_cat = 1; read_treatment(); break;
+                case 'X': case 'P': return CRAMGPU_ERR_UNSUPPORTED;
+                default: return CRAMGPU_ERR_ARG;                        // "Unknown read or base category: " + code
+                }
+                if (!have_treatment) { p.treatment = 0; p.treat_param = 40; have_treatment = true; }
+            }
+            out[n++] = p;
+        }
+        if (!dash) break;
+        pos = end + 1;
+    }
+    // Collections.sort by treatment ordinal, descending (stable): DROP, BIN, PRESERVE
+    for (int i = 1; i < n; i++) {
+        cramgpu_qs_policy p = out[i];
+        int j = i - 1;
+        while (j >= 0 && out[j].treatment < p.treatment) { out[j + 1] = out[j]; j--; }
+        out[j + 1] = p;
+    }
+    return n;
+}
+
+static int make_polset(cramgpu_ctx *ctx, const cramgpu_qs_policy *pol, int n, PolSet &ps)
+{
+    memset(&ps, 0, sizeof ps);
+    ps.n = n < 0 ? -1 : n;
+    if (n > MAX_POL) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "more than %d lossy policies", MAX_POL);
+    for (int k = 0; k < n; k++) {
+        if (!pol) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null policies");
+        ps.p[k] = pol[k];
+        if (pol[k].n_base_cats < 0 || pol[k].n_base_cats > 8) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "bad policy");
+        if (pol[k].n_base_cats) ps.per_base = 1;
+    }
+    return CRAMGPU_OK;
+}
+
+// upload a small host table through the pinned plan buffer
+struct Uploader {
+    cramgpu_ctx *ctx; cudaStream_t st; size_t po = 0;
+    cudaError_t up(const void *src, size_t bytes, void *dst)
+    {
+        if (!bytes) return cudaSuccess;
+        memcpy((uint8_t *)ctx->pin_meta + po, src, bytes);
+        cudaError_t e = cudaMemcpyAsync(dst, (uint8_t *)ctx->pin_meta + po, bytes, cudaMemcpyHostToDevice, st);
+        po += rup(bytes, 16);
+        return e;
+    }
+};
+
+// device-pointer implementation shared by both encode entry points.  R holds device pointers for the big arrays.
+static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *pol, int npol,
+                                cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len, cudaStream_t st)
+{
+    if (!R || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    memset(out, 0, sizeof *out);
+    const uint64_t n = R->n_reads;
+    const uint32_t nc = R->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!R->cont_off || !R->ref_off || !R->ref_len || !R->ref || !R->bases || !R->quals || !R->read_off || !R->cigar_off ||
+        !R->pos || !R->flag || !R->mapq)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (R->cont_off[0] != 0 || R->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
+    for (uint32_t c = 0; c < nc; c++) {
+        if (R->cont_off[c] > R->cont_off[c + 1]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off not monotonic");
+        if (R->ref_off[c] + R->ref_len[c] > R->ref_total) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "reference window of container %u outside ref", c);
+    }
+    PolSet ps;
+    if (int rc = make_polset(ctx, pol, npol, ps)) return rc;
+
+    Carver cv;
+    size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_roff = cv.take(8 * (size_t)nc), o_rlen = cv.take(8 * (size_t)nc);
+    size_t o_cnt = cv.take(4 * (size_t)NCNT * n), o_force = cv.take(n);
+    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16);
+    size_t o_zero_end = cv.off;
+    size_t o_codes = cv.take(32 * (size_t)nc), o_matrix = cv.take(8 * (size_t)nc);
+    size_t o_totals = cv.take(8 * (size_t)NCNT * nc), o_base = cv.take(8 * (size_t)NCNT * nc);
+    size_t o_soff = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc), o_slen = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc);
+    size_t o_grand = cv.take(64);
+    if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
+
+    size_t plan_bytes = 8 * (size_t)(3 * nc + 1) + 256;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, plan_bytes)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev));
+    Uploader U{ctx, st};
+    CUDA_TRY(ctx, U.up(R->cont_off, 8 * (size_t)(nc + 1), S + o_cont));
+    CUDA_TRY(ctx, U.up(R->ref_off, 8 * (size_t)nc, S + o_roff));
+    CUDA_TRY(ctx, U.up(R->ref_len, 8 * (size_t)nc, S + o_rlen));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_subst, 0, o_zero_end - o_subst, st));
+
+    RecArgs a;
+    memset(&a, 0, sizeof a);
+    a.ref = R->ref; a.bases = R->bases; a.quals = R->quals; a.read_off = R->read_off; a.cigar_off = R->cigar_off;
+    a.cigar = R->cigar; a.pos = R->pos; a.flag = R->flag; a.mapq = R->mapq; a.rflags = R->rflags;
+    a.cont_off = (const uint64_t *)(S + o_cont); a.ref_off = (const uint64_t *)(S + o_roff); a.ref_len = (const uint64_t *)(S + o_rlen);
+    a.n_containers = nc; a.n_reads = n;
+    a.cnt = (uint32_t *)(S + o_cnt); a.force = S + o_force; a.subst = (unsigned long long *)(S + o_subst);
+    a.codes = S + o_codes; a.base = (const uint64_t *)(S + o_base); a.status = (int32_t *)(S + o_status);
+    uint64_t *d_totals = (uint64_t *)(S + o_totals), *d_soff = (uint64_t *)(S + o_soff), *d_slen = (uint64_t *)(S + o_slen);
+    uint64_t *d_grand = (uint64_t *)(S + o_grand);
+
+    const uint32_t grid = (uint32_t)((n + 3) / 4);
+    LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<grid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
+    LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
+    LAUNCH(ctx, st, "k_rec_layout", k_rec_layout<<<1, 32, 0, st>>>(d_totals, nc, (uint64_t *)(S + o_base), d_soff, d_slen, d_grand));
+    CUDA_TRY(ctx, cudaGetLastError());
+
+    // totals (and the per-container tables the caller needs) come back to the host
+    size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_rec, &ctx->pin_rec_cap, 2 * tab + 128)) return rc;
+    uint8_t *pr = (uint8_t *)ctx->pin_rec;
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr, d_grand, 32, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 32, S + o_status, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 64, d_soff, tab, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 64 + tab, d_slen, tab, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t *grand = (const uint64_t *)pr;
+    int32_t dstatus = *(const int32_t *)(pr + 32);
+    if (dstatus) return ctx_fail(ctx, dstatus, "Unsupported cigar operator");
+    const uint64_t sbytes = grand[0], nfeat = grand[1], paylen = grand[2];
+    if (h_stream_off) memcpy(h_stream_off, pr + 64, tab);
+    if (h_stream_len) memcpy(h_stream_len, pr + 64 + tab, tab);
+
+    Carver co;
+    size_t q_op = co.take(nfeat + 16), q_pos = co.take(4 * nfeat + 16), q_val = co.take(4 * nfeat + 16), q_aux = co.take(4 * nfeat + 16);
+    size_t q_foff = co.take(8 * (size_t)(n + 1)), q_pay = co.take(paylen + 16), q_str = co.take(sbytes + 16);
+    size_t q_qso = co.take(8 * (size_t)n), q_bao = co.take(8 * (size_t)n);
+    if (int rc = pool_reserve(ctx, ctx->rec_out, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->rec_out.p;
+    a.f_op = O + q_op; a.f_pos = (int32_t *)(O + q_pos); a.f_val = (int32_t *)(O + q_val); a.f_aux = (int32_t *)(O + q_aux);
+    a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.streams = O + q_str;
+    a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
+    LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<grid, 128, 0, st>>>(a, ps));
+    if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
+    CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
+    CUDA_TRY(ctx, cudaGetLastError());
+
+    out->n_feat = nfeat; out->f_op = a.f_op; out->f_pos = a.f_pos; out->f_val = a.f_val; out->f_aux = a.f_aux;
+    out->feat_off = a.feat_off; out->payload = a.payload; out->payload_len = paylen; out->force_qs = a.force;
+    out->matrix = S + o_matrix; out->streams = a.streams; out->streams_len = sbytes; out->stream_off = d_soff;
+    out->stream_len = d_slen; out->read_qs_off = a.read_qs_off; out->read_ba_off = a.read_ba_off;
+    return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
+                                           int n_policies, cramgpu_features *out, uint64_t *h_stream_off,
+                                           uint64_t *h_stream_len, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    if (int rc = features_encode_impl(ctx, reads, policies, n_policies, out, h_stream_off, h_stream_len, st)) return rc;
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CRAMGPU_OK;
+}
+
+// copy helper for the host entry points: place host arrays back to back in one pinned buffer / one device buffer
+struct Stager {
+    std::vector<const void *> src; std::vector<size_t> bytes, off; size_t total = 0;
+    size_t add(const void *p, size_t b) { off.push_back(total); src.push_back(p); bytes.push_back(b); total += rup(b ? b : 1, 256); return off.back(); }
+};
+
+extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies,
+                                       int n_policies, cramgpu_features *out)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!R || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    memset(out, 0, sizeof *out);
+    const uint64_t n = R->n_reads;
+    const uint32_t nc = R->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!R->read_off || !R->cigar_off || !R->bases || !R->quals || !R->pos || !R->flag || !R->mapq || !R->ref)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    const uint64_t nb = R->read_off[n], ncig = R->cigar_off[n];
+    Stager sg;
+    size_t i_ref = sg.add(R->ref, R->ref_total), i_bases = sg.add(R->bases, nb), i_quals = sg.add(R->quals, nb);
+    size_t i_roff = sg.add(R->read_off, 8 * (n + 1)), i_cig = sg.add(R->cigar, 4 * ncig), i_coff = sg.add(R->cigar_off, 8 * (n + 1));
+    size_t i_pos = sg.add(R->pos, 4 * n), i_flag = sg.add(R->flag, 2 * n), i_mapq = sg.add(R->mapq, n);
+    size_t i_rfl = R->rflags ? sg.add(R->rflags, n) : 0;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
+    if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
+    uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
+    for (size_t k = 0; k < sg.src.size(); k++) if (sg.bytes[k]) memcpy(pin + sg.off[k], sg.src[k], sg.bytes[k]);
+    CUDA_TRY(ctx, cudaMemcpyAsync(D, pin, sg.total, cudaMemcpyHostToDevice, st));
+    cramgpu_reads dev = *R;
+    dev.ref = D + i_ref; dev.bases = D + i_bases; dev.quals = D + i_quals; dev.read_off = (const uint64_t *)(D + i_roff);
+    dev.cigar = (const uint32_t *)(D + i_cig); dev.cigar_off = (const uint64_t *)(D + i_coff); dev.pos = (const int32_t *)(D + i_pos);
+    dev.flag = (const uint16_t *)(D + i_flag); dev.mapq = D + i_mapq; dev.rflags = R->rflags ? D + i_rfl : nullptr;
+    cramgpu_features df;
+    if (int rc = features_encode_impl(ctx, &dev, policies, n_policies, &df, nullptr, nullptr, st)) return rc;
+
+    // results to pinned host memory owned by the context
+    const size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
+    Stager so;
+    size_t r_op = so.add(df.f_op, df.n_feat), r_pos = so.add(df.f_pos, 4 * df.n_feat), r_val = so.add(df.f_val, 4 * df.n_feat);
+    size_t r_aux = so.add(df.f_aux, 4 * df.n_feat), r_foff = so.add(df.feat_off, 8 * (n + 1)), r_pay = so.add(df.payload, df.payload_len);
+    size_t r_force = so.add(df.force_qs, n), r_mtx = so.add(df.matrix, 8 * (size_t)nc), r_str = so.add(df.streams, df.streams_len);
+    size_t r_soff = so.add(df.stream_off, tab), r_slen = so.add(df.stream_len, tab);
+    size_t r_qso = so.add(df.read_qs_off, 8 * n), r_bao = so.add(df.read_ba_off, 8 * n);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, so.total)) return rc;
+    uint8_t *po = (uint8_t *)ctx->pin_out;
+    for (size_t k = 0; k < so.src.size(); k++)
+        if (so.bytes[k]) CUDA_TRY(ctx, cudaMemcpyAsync(po + so.off[k], so.src[k], so.bytes[k], cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *out = df;
+    out->f_op = po + r_op; out->f_pos = (const int32_t *)(po + r_pos); out->f_val = (const int32_t *)(po + r_val);
+    out->f_aux = (const int32_t *)(po + r_aux); out->feat_off = (const uint64_t *)(po + r_foff); out->payload = po + r_pay;
+    out->force_qs = po + r_force; out->matrix = po + r_mtx; out->streams = po + r_str;
+    out->stream_off = (const uint64_t *)(po + r_soff); out->stream_len = (const uint64_t *)(po + r_slen);
+    out->read_qs_off = (const uint64_t *)(po + r_qso); out->read_ba_off = (const uint64_t *)(po + r_bao);
+    return CRAMGPU_OK;
+}
+
+static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *d_bases, uint8_t *d_quals,
+                          uint8_t *d_star, int32_t *d_status, cudaStream_t st)
+{
+    if (!in) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!in->cont_off || !in->win_off || !in->win_len || !in->win_start0 || !in->pos || !in->read_off || !in->rflags ||
+        !in->feat_off || !d_bases || !d_quals || !d_star || !d_status)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (in->cont_off[0] != 0 || in->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
+    for (uint32_t c = 0; c < nc; c++)
+        if (in->win_off[c] + in->win_len[c] > in->ref_total) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "reference region of container %u outside ref", c);
+    Carver cv;
+    size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_woff = cv.take(8 * (size_t)nc), o_wlen = cv.take(8 * (size_t)nc), o_ws = cv.take(8 * (size_t)nc);
+    if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, 8 * (size_t)(4 * nc + 1) + 256)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev));
+    Uploader U{ctx, st};
+    CUDA_TRY(ctx, U.up(in->cont_off, 8 * (size_t)(nc + 1), S + o_cont));
+    CUDA_TRY(ctx, U.up(in->win_off, 8 * (size_t)nc, S + o_woff));
+    CUDA_TRY(ctx, U.up(in->win_len, 8 * (size_t)nc, S + o_wlen));
+    CUDA_TRY(ctx, U.up(in->win_start0, 8 * (size_t)nc, S + o_ws));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev, st));
+    NormArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_reads = n; a.n_containers = nc;
+    a.cont_off = (const uint64_t *)(S + o_cont); a.win_off = (const uint64_t *)(S + o_woff); a.win_len = (const uint64_t *)(S + o_wlen);
+    a.win_start0 = (const int64_t *)(S + o_ws);
+    a.ref = in->ref; a.matrix = in->matrix; a.pos = in->pos; a.read_off = in->read_off; a.rflags = in->rflags; a.feat_off = in->feat_off;
+    a.f_op = in->f_op; a.f_pos = in->f_pos; a.f_val = in->f_val; a.f_aux = in->f_aux; a.payload = in->payload;
+    a.qs = in->qs; a.read_qs_off = in->read_qs_off; a.ba = in->ba; a.read_ba_off = in->read_ba_off;
+    a.bases = d_bases; a.quals = d_quals; a.qual_star = d_star; a.status = d_status;
+    LAUNCH(ctx, st, "k_norm", k_norm<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_normalize_decode_dev(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *d_bases, uint8_t *d_quals,
+                                            uint8_t *d_qual_star, int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return normalize_impl(ctx, in, d_bases, d_quals, d_qual_star, d_status, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *bases, uint8_t *quals,
+                                        uint8_t *qual_star, int32_t *status)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !bases || !quals || !qual_star || !status) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!in->read_off || !in->feat_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    const uint64_t nb = in->read_off[n], nf = in->feat_off[n];
+    // extents of the side buffers: the furthest byte any record refers to
+    uint64_t qs_len = 0, ba_len = 0, pay_len = 0;
+    for (uint64_t r = 0; r < n; r++) {
+        uint64_t len = in->read_off[r + 1] - in->read_off[r];
+        if (in->read_qs_off && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
+        if (in->read_ba_off && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
+    }
+    for (uint64_t f = 0; f < nf; f++)
+        if (in->f_op[f] == 'S' || in->f_op[f] == 'I') pay_len = std::max(pay_len, (uint64_t)in->f_val[f] + (uint64_t)in->f_aux[f]);
+    Stager sg;
+    size_t i_ref = sg.add(in->ref, in->ref_total), i_mtx = sg.add(in->matrix, 8 * (size_t)nc), i_pos = sg.add(in->pos, 4 * n);
+    size_t i_roff = sg.add(in->read_off, 8 * (n + 1)), i_rfl = sg.add(in->rflags, n), i_foff = sg.add(in->feat_off, 8 * (n + 1));
+    size_t i_op = sg.add(in->f_op, nf), i_fp = sg.add(in->f_pos, 4 * nf), i_fv = sg.add(in->f_val, 4 * nf), i_fa = sg.add(in->f_aux, 4 * nf);
+    size_t i_pay = sg.add(in->payload, pay_len), i_qs = sg.add(in->qs, qs_len), i_qso = sg.add(in->read_qs_off, 8 * n);
+    size_t i_ba = sg.add(in->ba, ba_len), i_bao = sg.add(in->read_ba_off, 8 * n);
+    size_t o_bases = sg.add(nullptr, 0); sg.total += rup(nb + 16, 256);
+    size_t o_quals = sg.add(nullptr, 0); sg.total += rup(nb + 16, 256);
+    size_t o_star = sg.add(nullptr, 0); sg.total += rup(n, 256);
+    size_t o_stat = sg.add(nullptr, 0); sg.total += rup(4 * n, 256);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
+    if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
+    uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
+    for (size_t k = 0; k < sg.src.size(); k++) if (sg.bytes[k] && sg.src[k]) memcpy(pin + sg.off[k], sg.src[k], sg.bytes[k]);
+    CUDA_TRY(ctx, cudaMemcpyAsync(D, pin, o_bases, cudaMemcpyHostToDevice, st));
+    // records without a stored array / BA bases still need valid offset tables
+    if (!in->read_qs_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_qso, 0xFF, 8 * n, st));
+    if (!in->read_ba_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_bao, 0xFF, 8 * n, st));
+    cramgpu_norm_in dev = *in;
+    dev.ref = D + i_ref; dev.matrix = D + i_mtx; dev.pos = (const int32_t *)(D + i_pos); dev.read_off = (const uint64_t *)(D + i_roff);
+    dev.rflags = D + i_rfl; dev.feat_off = (const uint64_t *)(D + i_foff); dev.f_op = D + i_op; dev.f_pos = (const int32_t *)(D + i_fp);
+    dev.f_val = (const int32_t *)(D + i_fv); dev.f_aux = (const int32_t *)(D + i_fa); dev.payload = D + i_pay; dev.qs = D + i_qs;
+    dev.read_qs_off = (const uint64_t *)(D + i_qso); dev.ba = D + i_ba; dev.read_ba_off = (const uint64_t *)(D + i_bao);
+    if (int rc = normalize_impl(ctx, &dev, D + o_bases, D + o_quals, D + o_star, (int32_t *)(D + o_stat), st)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256))) return rc;
+    uint8_t *po = (uint8_t *)ctx->pin_out;
+    size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256);
+    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(po, D + o_bases, nb, cudaMemcpyDeviceToHost, st));
+    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(po + p_q, D + o_quals, nb, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, D + o_star, n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_t, D + o_stat, 4 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (nb) { memcpy(bases, po, nb); memcpy(quals, po + p_q, nb); }
+    memcpy(qual_star, po + p_s, n);
+    memcpy(status, po + p_t, 4 * n);
+    for (uint64_t r = 0; r < n; r++)
+        if (status[r]) return ctx_fail(ctx, status[r], "record %llu lies outside its reference region (ArrayIndexOutOfBoundsException in the reference)", (unsigned long long)r);
+    return CRAMGPU_OK;
+}

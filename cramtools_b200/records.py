@@ -1,0 +1,204 @@
+"""Host-side mirror of the reference's record-feature plug-in points, on top of the C ABI.
+
+Mirrors, with the reference's names:
+  QualityScorePreservation.lossyFromSpec / parsePolicies   (lossy/QualityScorePreservation.java:64,167-191)
+  CramSerilization.convert's per-record loop               (cram/CramSerilization.java:144-166) -> features_encode
+  CramNormalizer.restoreBases / restoreQualityScores       (cram/build/CramNormalizer.java:208-244,287-333) -> normalize_decode
+Records are passed as structure-of-arrays dicts (the layout cramtools_b200.synth.reads produces), which is what the
+Java shim of INTEGRATION.md builds from List<SAMRecord> before calling the same exported symbols.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import CramGpuError
+
+u8p, u16p, u32p, i32p, i64p, u64p = (C.POINTER(t) for t in (C.c_uint8, C.c_uint16, C.c_uint32, C.c_int32, C.c_int64, C.c_uint64))
+
+SERIES = ['FN', 'FC', 'FP', 'BS', 'DL', 'BA', 'SC', 'QS', 'RS', 'HC', 'PD', 'MQ']
+SERIES_CONTENT_ID = {'FN': 15, 'FC': 3, 'FP': 2, 'BS': 16, 'DL': 5, 'BA': 6, 'SC': 27, 'QS': 4, 'RS': 26, 'HC': 28, 'PD': 29, 'MQ': 11}
+NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+class QsPolicy(C.Structure):
+    _fields_ = [('read_cat', C.c_int32), ('read_param', C.c_int32), ('n_base_cats', C.c_int32),
+                ('base_cat', C.c_int32 * 8), ('treatment', C.c_int32), ('treat_param', C.c_int32)]
+
+
+class Reads(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('ref_off', u64p), ('ref_len', u64p),
+                ('ref', C.c_void_p), ('ref_total', C.c_uint64), ('bases', C.c_void_p), ('quals', C.c_void_p), ('read_off', C.c_void_p),
+                ('cigar', C.c_void_p), ('cigar_off', C.c_void_p), ('pos', C.c_void_p), ('flag', C.c_void_p), ('mapq', C.c_void_p),
+                ('rflags', C.c_void_p)]
+
+
+class Features(C.Structure):
+    _fields_ = [('n_feat', C.c_uint64), ('f_op', C.c_void_p), ('f_pos', C.c_void_p), ('f_val', C.c_void_p), ('f_aux', C.c_void_p),
+                ('feat_off', C.c_void_p), ('payload', C.c_void_p), ('payload_len', C.c_uint64), ('force_qs', C.c_void_p),
+                ('matrix', C.c_void_p), ('streams', C.c_void_p), ('streams_len', C.c_uint64), ('stream_off', C.c_void_p),
+                ('stream_len', C.c_void_p), ('read_qs_off', C.c_void_p), ('read_ba_off', C.c_void_p)]
+
+
+class NormIn(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('win_off', u64p), ('win_len', u64p),
+                ('win_start0', i64p), ('ref', C.c_void_p), ('ref_total', C.c_uint64), ('matrix', C.c_void_p), ('pos', C.c_void_p),
+                ('read_off', C.c_void_p), ('rflags', C.c_void_p), ('feat_off', C.c_void_p), ('f_op', C.c_void_p), ('f_pos', C.c_void_p),
+                ('f_val', C.c_void_p), ('f_aux', C.c_void_p), ('payload', C.c_void_p), ('qs', C.c_void_p), ('read_qs_off', C.c_void_p),
+                ('ba', C.c_void_p), ('read_ba_off', C.c_void_p)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_parse_lossy_spec': (C.c_int, [C.c_char_p, C.POINTER(QsPolicy), C.c_int]),
+    'cramgpu_features_encode': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features)]),
+    'cramgpu_features_encode_dev': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features),
+                                              u64p, u64p, C.c_void_p]),
+    'cramgpu_normalize_decode': (C.c_int, [C.c_void_p, C.POINTER(NormIn), u8p, u8p, u8p, i32p]),
+    'cramgpu_normalize_decode_dev': (C.c_int, [C.c_void_p, C.POINTER(NormIn), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p]),
+})
+
+
+class QualityScorePreservation(object):
+    """lossy/QualityScorePreservation.java: spec -> policy list (sorted DROP, BIN, PRESERVE)"""
+
+    def __init__(self, policies, n):
+        self.policies, self.n = policies, n
+
+    @staticmethod
+    def lossyFromSpec(spec):
+        lib = _lib.load()
+        arr = (QsPolicy * 16)()
+        n = lib.cramgpu_parse_lossy_spec(spec.encode(), arr, 16)
+        if n == _lib.ERR_ARG:
+            raise CramGpuError(n, 'Unknown read or base category')
+        if n == _lib.ERR_UNSUPPORTED:
+            raise CramGpuError(n, 'The quality score lossy model requires reference tracks.')
+        return QualityScorePreservation(arr, n)
+
+    def getPreservationPolicies(self):
+        return [self.policies[i] for i in range(self.n)]
+
+
+def _policy_args(spec):
+    """None / 'lossless' -> lossless; else parse"""
+    if spec is None or spec == 'lossless':
+        return None, -1
+    q = spec if isinstance(spec, QualityScorePreservation) else QualityScorePreservation.lossyFromSpec(spec)
+    return q.policies, q.n
+
+
+def _vp(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else None
+
+
+def _arr(x, dt, minlen=1):
+    if isinstance(x, (bytes, bytearray)):
+        x = np.frombuffer(bytes(x), dtype=np.uint8)
+    a = np.ascontiguousarray(x, dtype=dt)
+    if a.size < minlen:
+        a = np.concatenate([a, np.zeros(minlen - a.size, dt)])
+    return a
+
+
+def _view(ptr, n, dt):
+    n = int(n)
+    if n == 0 or not ptr:
+        return np.zeros(0, dt)
+    buf = (C.c_uint8 * (n * np.dtype(dt).itemsize)).from_address(ptr)
+    return np.frombuffer(buf, dtype=dt, count=n).copy()
+
+
+class EncodedFeatures(object):
+    """host copy of a cramgpu_features result"""
+
+    def __init__(self, f, n_reads, n_containers):
+        nf = int(f.n_feat)
+        self.n_feat = nf
+        self.f_op = _view(f.f_op, nf, np.uint8); self.f_pos = _view(f.f_pos, nf, np.int32)
+        self.f_val = _view(f.f_val, nf, np.int32); self.f_aux = _view(f.f_aux, nf, np.int32)
+        self.feat_off = _view(f.feat_off, n_reads + 1, np.uint64)
+        self.payload = _view(f.payload, f.payload_len, np.uint8)
+        self.force_qs = _view(f.force_qs, n_reads, np.uint8)
+        self.matrix = _view(f.matrix, 8 * n_containers, np.uint8).reshape(n_containers, 8)
+        self.streams = _view(f.streams, f.streams_len, np.uint8)
+        self.stream_off = _view(f.stream_off, 12 * n_containers, np.uint64).reshape(n_containers, 12)
+        self.stream_len = _view(f.stream_len, 12 * n_containers, np.uint64).reshape(n_containers, 12)
+        self.read_qs_off = _view(f.read_qs_off, n_reads, np.uint64)
+        self.read_ba_off = _view(f.read_ba_off, n_reads, np.uint64)
+
+    def series(self, container, name):
+        k = SERIES.index(name)
+        o, ln = int(self.stream_off[container, k]), int(self.stream_len[container, k])
+        return self.streams[o:o + ln].tobytes()
+
+
+def _reads_struct(rd, ref, cont_off, ref_off, ref_len, keep):
+    n = len(rd['pos'])
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    ref = _arr(ref, np.uint8)
+    ref_off = _arr(np.zeros(nc) if ref_off is None else ref_off, np.uint64)
+    ref_len = _arr(np.full(nc, ref.size) if ref_len is None else ref_len, np.uint64)
+    arrs = dict(bases=_arr(rd['bases'], np.uint8), quals=_arr(rd['quals'], np.uint8), read_off=_arr(rd['read_off'], np.uint64),
+                cigar=_arr(rd['cigar'], np.uint32), cigar_off=_arr(rd['cigar_off'], np.uint64), pos=_arr(rd['pos'], np.int32),
+                flag=_arr(rd['flag'], np.uint16), mapq=_arr(rd['mapq'], np.uint8),
+                rflags=_arr(rd['rflags'], np.uint8) if rd.get('rflags') is not None else None)
+    keep.extend([cont_off, ref_off, ref_len, ref] + list(arrs.values()))
+    R = Reads()
+    R.n_reads = n; R.n_containers = nc
+    R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
+    R.ref = _vp(ref); R.ref_total = ref.size
+    for k, v in arrs.items():
+        setattr(R, k, _vp(v))
+    return R, n, nc
+
+
+def features_encode(rd, ref, spec=None, cont_off=None, ref_off=None, ref_len=None, ctx=None):
+    """Feature extraction + quality preservation + series packing through cramgpu_features_encode (host buffers).
+    rd: SoA dict; ref: reference bytes; spec: None/'lossless' or a lossy model string such as '*8', 'm5', 'N40-D8'."""
+    ctx = ctx or _lib.default_context()
+    keep = []
+    R, n, nc = _reads_struct(rd, ref, cont_off, ref_off, ref_len, keep)
+    pol, npol = _policy_args(spec)
+    F = Features()
+    rc = ctx.lib.cramgpu_features_encode(ctx.handle, C.byref(R), pol, npol, C.byref(F))
+    ctx.check(rc)
+    return EncodedFeatures(F, n, nc)
+
+
+def normalize_decode(pos, read_off, rflags, enc, window, window_start0, matrix, cont_off=None, win_off=None, win_len=None,
+                     qs=None, read_qs_off=None, ba=None, read_ba_off=None, ctx=None, check=True):
+    """CramNormalizer base + quality restoration through cramgpu_normalize_decode (host buffers).
+    enc supplies the feature arrays (f_op, f_pos, f_val, f_aux, feat_off, payload); window/window_start0 describe the
+    reference region(s).  Returns (bases u8, quals u8, qual_star u8, status i32)."""
+    ctx = ctx or _lib.default_context()
+    n = len(pos)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    window = _arr(window, np.uint8)
+    win_off = _arr(np.zeros(nc) if win_off is None else win_off, np.uint64)
+    win_len = _arr(np.full(nc, window.size) if win_len is None else win_len, np.uint64)
+    ws0 = _arr(np.full(nc, window_start0) if np.isscalar(window_start0) else window_start0, np.int64)
+    matrix = _arr(np.asarray(matrix, np.uint8).reshape(nc, -1)[:, :8] if np.asarray(matrix).size == 8 * nc else
+                  np.pad(np.asarray(matrix, np.uint8).reshape(nc, -1), ((0, 0), (0, 8 - np.asarray(matrix).size // nc))), np.uint8)
+    a = dict(pos=_arr(pos, np.int32), read_off=_arr(read_off, np.uint64), rflags=_arr(rflags, np.uint8),
+             feat_off=_arr(enc.feat_off, np.uint64), f_op=_arr(enc.f_op, np.uint8), f_pos=_arr(enc.f_pos, np.int32),
+             f_val=_arr(enc.f_val, np.int32), f_aux=_arr(enc.f_aux, np.int32), payload=_arr(enc.payload, np.uint8),
+             qs=_arr(qs if qs is not None else [], np.uint8), ba=_arr(ba if ba is not None else [], np.uint8),
+             read_qs_off=_arr(read_qs_off, np.uint64) if read_qs_off is not None else None,
+             read_ba_off=_arr(read_ba_off, np.uint64) if read_ba_off is not None else None)
+    I = NormIn()
+    I.n_reads = n; I.n_containers = nc
+    I.cont_off = cont_off.ctypes.data_as(u64p); I.win_off = win_off.ctypes.data_as(u64p); I.win_len = win_len.ctypes.data_as(u64p)
+    I.win_start0 = ws0.ctypes.data_as(i64p); I.ref = _vp(window); I.ref_total = window.size; I.matrix = _vp(matrix)
+    for k, v in a.items():
+        setattr(I, k, _vp(v))
+    total = int(a['read_off'][n])
+    bases = np.zeros(max(total, 1), np.uint8); quals = np.zeros(max(total, 1), np.uint8)
+    star = np.zeros(max(n, 1), np.uint8); status = np.zeros(max(n, 1), np.int32)
+    rc = ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(I), bases.ctypes.data_as(u8p), quals.ctypes.data_as(u8p),
+                                          star.ctypes.data_as(u8p), status.ctypes.data_as(i32p))
+    if rc != _lib.OK and (check or rc != _lib.ERR_CORRUPT):
+        ctx.check(rc)
+    return bases[:total], quals[:total], star[:n], status[:n]

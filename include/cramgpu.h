@@ -148,6 +148,169 @@ int cramgpu_rans_decode_dev(cramgpu_ctx *ctx, uint32_t nblocks,
                             uint8_t *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_out_len,
                             int32_t *d_status, void *stream);
 
+
+/* ------------------------------------------------------------------ record-feature work
+ *
+ * Encode side  (replaces the per-record loop of CramSerilization.convert,
+ *               src/main/java/htsjdk/samtools/cram/CramSerilization.java:144-166):
+ *   Sam2CramRecordFactory.createCramRecord / createVariations / addSubstitutionsAndMaskedBases
+ *                                                       [Sam2CramRecordFactory.java:108-335]
+ *   QualityScorePreservation.addQualityScores           lossy/QualityScorePreservation.java:276-301,332-489
+ *   CompressionHeaderFactory.buildFrequencies, SubstitutionMatrix(long[][]), updateSubstitutionCodes
+ *                                                       [CompressionHeaderFactory.java:171-209]
+ *   Writer.write for the series fed by the feature work [Writer.java:180-258]
+ * Decode side  (replaces CramNormalizer.restoreBases / restoreQualityScores,
+ *               src/main/java/htsjdk/samtools/cram/build/CramNormalizer.java:208-244,287-434).
+ *
+ * Records travel as structure-of-arrays over one or more containers (a container = the <= 10 000 records
+ * CRAMContainerStreamWriter flushes together, all on one reference sequence).  The Java shim flattens
+ * List<SAMRecord> into this layout once per call.
+ */
+
+/* one parsed lossy-quality policy (lossy/PreservationPolicy + ReadCategory + BaseCategory + QualityScoreTreatment) */
+typedef struct cramgpu_qs_policy {
+    int32_t read_cat;      /* 0 none, 1 ALL (*), 2 UNPLACED (U), 3 LOWER_MAPPING_SCORE (m), 4 HIGHER_MAPPING_SCORE (M) */
+    int32_t read_param;
+    int32_t n_base_cats;   /* base categories in spec order (they overwrite one another exactly as in the reference) */
+    int32_t base_cat[8];   /* 1 MATCH (R), 2 MISMATCH (N), 3 FLANKING_DELETION (D), 4 INSERTION (I) */
+    int32_t treatment;     /* 0 PRESERVE, 1 BIN (Illumina 8-binning), 2 DROP */
+    int32_t treat_param;
+} cramgpu_qs_policy;
+
+/*
+ * Replaces QualityScorePreservation.parsePolicies(String) (lossy/QualityScorePreservation.java:167-256):
+ * "-"-separated policies, sorted DROP, BIN, PRESERVE (stable).  Host only.
+ * Returns the number of policies written, CRAMGPU_ERR_ARG for "Unknown read or base category", or
+ * CRAMGPU_ERR_UNSUPPORTED for the X / P selectors (they need ReferenceTracks coverage / pile-up counters that
+ * carry state across containers; the reference itself throws unless tracks were set up).
+ */
+int cramgpu_parse_lossy_spec(const char *spec, cramgpu_qs_policy *out, int cap);
+
+/* series produced by cramgpu_features_encode; values of the index into stream_off / stream_len */
+enum {
+    CRAMGPU_S_FN = 0, /* number of read features, ITF8                       content id 15 */
+    CRAMGPU_S_FC,     /* feature operator byte                                content id 3  */
+    CRAMGPU_S_FP,     /* feature position delta, ITF8                         content id 2  */
+    CRAMGPU_S_BS,     /* substitution code byte                               content id 16 */
+    CRAMGPU_S_DL,     /* deletion length, ITF8                                content id 5  */
+    CRAMGPU_S_BA,     /* bases: InsertBase features and unmapped reads        content id 6  */
+    CRAMGPU_S_SC,     /* soft clip bases, TAB terminated                      content id 27 */
+    CRAMGPU_S_QS,     /* quality scores: Q features and preserved arrays      content id 4  */
+    CRAMGPU_S_RS,     /* reference skip length, ITF8                          content id 26 */
+    CRAMGPU_S_HC,     /* hard clip length, ITF8                               content id 28 */
+    CRAMGPU_S_PD,     /* padding length, ITF8                                 content id 29 */
+    CRAMGPU_S_MQ,     /* mapping quality, ITF8                                content id 11 */
+    CRAMGPU_S_COUNT
+};
+
+#define CRAMGPU_RF_NO_QUALS 1u   /* rflags bit: SAMRecord.NULL_QUALS ('*') */
+#define CRAMGPU_RF_NO_BASES 2u   /* rflags bit: SAMRecord.NULL_SEQUENCE ('*'); read_off gives length 0 */
+
+/* input records, structure of arrays.  cont_off, ref_off, ref_len are always HOST arrays. */
+typedef struct cramgpu_reads {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;  /* [n_containers+1] container c holds reads cont_off[c] .. cont_off[c+1]-1 */
+    const uint64_t *ref_off;   /* [n_containers] start of the container's reference sequence inside `ref` */
+    const uint64_t *ref_len;   /* [n_containers] its length (bases beyond it read as 'N', [:306]) */
+    const uint8_t *ref;        /* reference bases as ReferenceSource hands them out (upper-cased or not) */
+    uint64_t ref_total;        /* bytes in `ref` */
+    const uint8_t *bases;      /* SAMRecord.getReadBases(), concatenated */
+    const uint8_t *quals;      /* SAMRecord.getBaseQualities(), same offsets as bases */
+    const uint64_t *read_off;  /* [n_reads+1] */
+    const uint32_t *cigar;     /* BAM-packed: length << 4 | op, ops MIDNSHP=X */
+    const uint64_t *cigar_off; /* [n_reads+1] */
+    const int32_t *pos;        /* SAMRecord.getAlignmentStart(), 1-based, 0 = none */
+    const uint16_t *flag;      /* SAM flags (0x4 = read unmapped) */
+    const uint8_t *mapq;
+    const uint8_t *rflags;     /* CRAMGPU_RF_* per read; NULL = all 0 */
+} cramgpu_reads;
+
+/*
+ * Result of feature extraction.  Every pointer refers to memory owned by the context (device memory for
+ * cramgpu_features_encode_dev, host memory for cramgpu_features_encode) and stays valid until the next
+ * record call on the same context.
+ *   features: f_op (operator byte as in ReadFeature.getOperator()), f_pos (1-based position in read),
+ *     'X': f_val = substitution code (after ranking), f_aux = read base | reference base << 8
+ *     'i': f_val = base      'D','N','H','P': f_val = length      'Q': f_val = score
+ *     'S': f_val = offset into payload, f_aux = length
+ *   Q features are already merged in by position, after the other features of the same position, exactly
+ *   as Collections.sort leaves them (QualityScorePreservation.java:288-299).
+ */
+typedef struct cramgpu_features {
+    uint64_t n_feat;
+    const uint8_t *f_op;
+    const int32_t *f_pos, *f_val, *f_aux;
+    const uint64_t *feat_off;     /* [n_reads+1] */
+    const uint8_t *payload;
+    uint64_t payload_len;
+    const uint8_t *force_qs;      /* [n_reads] bit0 = CramCompressionRecord.isForcePreserveQualityScores(), bit1 = has a score array */
+    const uint8_t *matrix;        /* [n_containers][8]: 5 bytes of SubstitutionMatrix.getEncodedMatrix(), 3 pad */
+    const uint8_t *streams;       /* all series bytes; every (container, series) region starts at a multiple of 16 */
+    uint64_t streams_len;
+    const uint64_t *stream_off;   /* [n_containers][CRAMGPU_S_COUNT] */
+    const uint64_t *stream_len;   /* [n_containers][CRAMGPU_S_COUNT] */
+    const uint64_t *read_qs_off;  /* [n_reads] offset in `streams` of the read's preserved score array, ~0 = none */
+    const uint64_t *read_ba_off;  /* [n_reads] offset in `streams` of an unmapped read's bases, ~0 = none */
+} cramgpu_features;
+
+/*
+ * Feature extraction + quality preservation + series packing for a batch of containers.
+ *   n_policies < 0          lossless (CramSerilization.java:160-161: preserve iff quals != NULL_QUALS)
+ *   n_policies >= 0         the parsed lossy model; 0 policies = drop all
+ * Host variant: `reads` holds host pointers; results are host pointers.
+ * Device variant: the big arrays of `reads` (ref, bases, quals, read_off, cigar, cigar_off, pos, flag, mapq,
+ * rflags) are device pointers; results are device pointers, except that the small per-container tables
+ * stream_off / stream_len and the scalars are also mirrored on the host (h_stream_off, h_stream_len) so that
+ * the caller can hand the series straight to cramgpu_rans_encode_dev.  The call returns after the device
+ * has finished (it needs the totals).
+ * Reads longer than 4096 bases are rejected with CRAMGPU_ERR_UNSUPPORTED when a per-base policy (R/N/D/I) is present.
+ */
+int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
+                            int n_policies, cramgpu_features *out);
+int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
+                                int n_policies, cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len,
+                                void *stream);
+
+/* input of the decode-side normaliser: records as CramRecordReader leaves them, structure of arrays */
+typedef struct cramgpu_norm_in {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    const uint64_t *win_off;      /* HOST [n_containers] start of the container's reference region inside `ref` */
+    const uint64_t *win_len;      /* HOST [n_containers] region.array.length */
+    const int64_t *win_start0;    /* HOST [n_containers] refOffsetZeroBased = region.alignmentStart - 1 */
+    const uint8_t *ref;           /* region bytes of all containers */
+    uint64_t ref_total;
+    const uint8_t *matrix;        /* [n_containers][8] substitution matrix bytes */
+    const int32_t *pos;           /* [n_reads] alignmentStart */
+    const uint64_t *read_off;     /* [n_reads+1] output offsets = cumulative readLength */
+    const uint8_t *rflags;        /* [n_reads] bit0 forcePreserveQualityScores, bit1 segment unmapped, bit2 unknownBases */
+    const uint64_t *feat_off;     /* [n_reads+1] */
+    const uint8_t *f_op;
+    const int32_t *f_pos, *f_val, *f_aux;
+    const uint8_t *payload;
+    const uint8_t *qs;            /* decoded QS series (or any buffer holding the preserved arrays) */
+    const uint64_t *read_qs_off;  /* [n_reads] offset of the read's preserved array in qs; ~0 = none */
+    const uint8_t *ba;            /* decoded BA series */
+    const uint64_t *read_ba_off;  /* [n_reads] offset of an unmapped read's bases in ba; ~0 = none */
+} cramgpu_norm_in;
+
+#define CRAMGPU_NF_FORCE_QS 1u
+#define CRAMGPU_NF_UNMAPPED 2u
+#define CRAMGPU_NF_UNKNOWN_BASES 4u
+
+/*
+ * Base and quality restoration.  bases / quals receive read_off[n_reads] bytes; qual_star[r] = 1 where the
+ * reference yields SAMRecord.NULL_QUALS; status[r] = CRAMGPU_ERR_CORRUPT where the reference would throw
+ * ArrayIndexOutOfBoundsException (record outside its region).  Host variant takes/returns host memory; the
+ * device variant takes device pointers for everything not marked HOST and enqueues on `stream`.
+ */
+int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *bases, uint8_t *quals,
+                             uint8_t *qual_star, int32_t *status);
+int cramgpu_normalize_decode_dev(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *d_bases, uint8_t *d_quals,
+                                 uint8_t *d_qual_star, int32_t *d_status, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
