@@ -118,12 +118,17 @@ class EncodedFeatures(object):
         self.f_op = _view(f.f_op, nf, np.uint8); self.f_pos = _view(f.f_pos, nf, np.int32)
         self.f_val = _view(f.f_val, nf, np.int32); self.f_aux = _view(f.f_aux, nf, np.int32)
         self.feat_off = _view(f.feat_off, n_reads + 1, np.uint64)
+        if self.feat_off.size == 0:
+            self.feat_off = np.zeros(n_reads + 1, np.uint64)
         self.payload = _view(f.payload, f.payload_len, np.uint8)
         self.force_qs = _view(f.force_qs, n_reads, np.uint8)
-        self.matrix = _view(f.matrix, 8 * n_containers, np.uint8).reshape(n_containers, 8)
+        def table(ptr, cols, dt):
+            v = _view(ptr, cols * n_containers, dt)
+            return v.reshape(n_containers, cols) if v.size else np.zeros((n_containers, cols), dt)
+        self.matrix = table(f.matrix, 8, np.uint8)
         self.streams = _view(f.streams, f.streams_len, np.uint8)
-        self.stream_off = _view(f.stream_off, 12 * n_containers, np.uint64).reshape(n_containers, 12)
-        self.stream_len = _view(f.stream_len, 12 * n_containers, np.uint64).reshape(n_containers, 12)
+        self.stream_off = table(f.stream_off, 12, np.uint64)
+        self.stream_len = table(f.stream_len, 12, np.uint64)
         self.read_qs_off = _view(f.read_qs_off, n_reads, np.uint64)
         self.read_ba_off = _view(f.read_ba_off, n_reads, np.uint64)
 
