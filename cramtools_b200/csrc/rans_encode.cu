@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
 // ------------------------------------------------------------------------------------------------
 // k_tables0: one CTA (256 threads, thread j = symbol j) per order-0 block.
 __global__ void __launch_bounds__(256) k_tables0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o0_blocks,
-                                                 const uint32_t *__restrict__ F0, uint2 *__restrict__ syms0,
+                                                 const uint32_t *__restrict__ F0, uint32_t *__restrict__ tab0,
                                                  uint8_t *__restrict__ work, uint32_t *__restrict__ tlen)
 {
     uint32_t blk = o0_blocks[blockIdx.x];
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(256) k_tables0(const BlockDesc *__restrict__ d
     __syncthreads();
     uint32_t base = 0;
     for (int k = 0; k < (int)w; k++) base += reds[k];
-    if (nf) syms0[(size_t)blk * 256 + j] = make_enc_sym(base + ex, nf);
+    tab0[(size_t)blk * 256 + j] = nf ? (nf | ((base + ex) << 12)) : 0u;      // {freq, cumulative start} [buildSyms_o0 :197-211]
     rowF[j] = (uint16_t)nf;
     __syncthreads();
     if (w == 0) {
@@ -293,14 +293,14 @@ __global__ void __launch_bounds__(256) k_tables0(const BlockDesc *__restrict__ d
 // pass 2 serialises the rows in place.
 __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o1_blocks,
                                                  const O1Meta *__restrict__ meta, uint32_t *__restrict__ F1,
-                                                 uint2 *__restrict__ syms1, uint8_t *__restrict__ work,
+                                                 uint32_t *__restrict__ tab1, uint8_t *__restrict__ work,
                                                  uint32_t *__restrict__ tlen)
 {
     uint32_t blk = o1_blocks[blockIdx.x];
     const BlockDesc d = desc[blk];
     const O1Meta *m = meta + blockIdx.x;
     uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
-    uint2 *sy = syms1 + (size_t)blockIdx.x * 65536;
+    uint32_t *sy = tab1 + (size_t)blockIdx.x * 65536;          // compact [ctx rank][sym rank] {freq | start << 12}
     uint8_t *tab = work + d.work_off;
     uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
@@ -359,12 +359,13 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
 #pragma unroll
                 for (int i = 0; i < 8; i++) ls += f[i];
                 uint32_t x = warp_excl_scan(ls, lane);
-                uint2 *srow = sy + (size_t)calpha[r] * 256;
+                uint32_t *srow = sy + (size_t)r * ns;
 #pragma unroll
                 for (int i = 0; i < 8; i++) {
                     if (a0 + i < ns) {
                         row[a0 + i] = f[i];
-                        if (f[i]) { srow[salpha[a0 + i]] = make_enc_sym(x, f[i]); x += f[i]; }
+                        srow[a0 + i] = f[i] ? (f[i] | (x << 12)) : 0u;                 // [buildSyms_o1 :248-265]
+                        x += f[i];
                     }
                 }
             }
@@ -405,238 +406,311 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
 }
 
 // ------------------------------------------------------------------------------------------------
-// The coder step.  Returns the new state; nb = renormalisation bytes (0..2), low byte of `bytes` is emitted first.
-__device__ __forceinline__ uint32_t put_symbol(uint32_t x, uint2 s, uint32_t &nb, uint32_t &bytes)
-{
-    uint32_t F = (s.y >> 13) & 0xFFFu, bias = s.y & 0x1FFFu, sh = s.y >> 25;
-    uint32_t x_max = F << 19;
-    bool c1 = x >= x_max;
-    bool c2 = (x >> 8) >= x_max;            // implies c1
-    bytes = x;
-    nb = (uint32_t)c1 + (uint32_t)c2;
-    x = c2 ? (x >> 16) : (c1 ? (x >> 8) : x);
-    uint32_t q = __umulhi(x, s.x) >> sh;
-    return x + bias + q * (TOTFREQ - F);
-}
+// ------------------------------------------------------------------------------------------------
+// The coder kernel.  A CTA codes 8 blocks (32 states) with four warps that form a software pipeline over
+// chunks of 32 coder steps, handing work over through shared-memory rings:
+//
+//   warps 0-7  PRODUCERS (4 states each)  for every (state, step) of chunk I: input byte(s) -> {freq, start} cell of
+//                     the block's table (shared memory when it fits, else global) -> packed coder descriptor
+//                     {rcp_freq, bias | freq << 13 | (rcp_shift - 32) << 25}  [Encoding.RansEncSymbolInit, Encoding.java:21-43].
+//                     Threads run over the 32 steps of one state at a time, so input reads are contiguous; the input
+//                     words themselves arrive two chunks ahead by cp.async.  rcp_freq comes from a 4096-entry table
+//                     built in shared memory when the CTA starts.
+//   warp 8     CODER  lane = state: 32 dependent steps of chunk I-1; nothing but the recurrence of
+//                     RansEncPutSymbol [Encoding.java:46-71], no global memory
+//   warps 9,10 EMITTERS (4 blocks each)  chunk I-2: positions of the renormalisation bytes (lanes emit in the order 3,2,1,0 within a
+//                     step, [E04.java:41-44]) by a prefix sum over the steps; bytes stored downwards from the end of the
+//                     block's work area == the reversed buffer of [rans/Utils.java:7-33]
+//
+// A single warp alone on an SM issues one dependent instruction every ~4 cycles (ncu: profiles/r1_k_enc1_v2_hotloop.txt),
+// so the states' recurrence is kept as short as possible and everything else runs beside it on other warps.
+#define EC 32
+#define ENC_TAB_ENTRIES 1792u     // order-1 {freq,start} cells per block kept in shared memory (ctx x sym <= 1792, e.g. 42 x 42)
+#define ENC_PROD 8                 // producer warps (4 states each)
+#define ENC_THREADS ((ENC_PROD + 3) * 32)   // + 1 coder warp + 2 emitter warps (4 blocks each)
 
-// Shared tail of both coders: place this step's bytes below the cursor and advance it.
-// Lanes of a 4-lane group emit in the order 3,2,1,0.
-__device__ __forceinline__ void emit_step(uint8_t *end, uint32_t &p, uint32_t cap, uint32_t nb, uint32_t bytes,
-                                          uint32_t lane, bool &overflow)
-{
-    uint32_t b1 = __ballot_sync(0xFFFFFFFFu, nb >= 1), b2 = __ballot_sync(0xFFFFFFFFu, nb == 2);
-    uint32_t g4 = lane & ~3u, k = lane & 3u;
-    uint32_t gm = 0xFu << g4;
-    uint32_t hm = (0xEu << k) & 0xFu;       // lanes above k inside the group
-    hm <<= g4;
-    uint32_t before = __popc(b1 & hm) + __popc(b2 & hm);
-    uint32_t tot = __popc(b1 & gm) + __popc(b2 & gm);
-    if (p + tot > cap) overflow = true;
-    if (nb && !overflow) {
-        uint32_t e = p + before;            // emission index of the first byte
-        end[-1 - (int64_t)e] = (uint8_t)bytes;
-        if (nb == 2) end[-2 - (int64_t)e] = (uint8_t)(bytes >> 8);
-    }
-    p += tot;
-}
-
-__device__ __forceinline__ void finish_block(uint8_t *end, uint32_t p, uint32_t cap, uint32_t x, uint32_t k,
-                                             bool overflow, uint32_t blk, uint32_t *plen, int32_t *status)
-{
-    // states 3,2,1,0 big-endian then reversed == states 0..3 little-endian in front of the payload [E04.java:46-50]
-    if (p + 16 > cap) overflow = true;
-    if (!overflow) {
-        uint8_t *s = end - p - 16 + 4 * k;
-        s[0] = (uint8_t)x; s[1] = (uint8_t)(x >> 8); s[2] = (uint8_t)(x >> 16); s[3] = (uint8_t)(x >> 24);
-    }
-    if (k == 0) {
-        plen[blk] = overflow ? 0 : p + 16;
-        if (overflow) status[blk] = CRAMGPU_ERR_OUT_TOO_SMALL;
-    }
-}
-
-// ---- asynchronous global->shared copies (LDGSTS): they keep global-memory latency off the coder's recurrence
 __device__ __forceinline__ void cp_async4(void *smem, const void *g)
 {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(g));
 }
-__device__ __forceinline__ void cp_async8(void *smem, const void *g)
-{
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(g));
-}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-#define ENC_CHUNK 32   // coder steps per staging round
+struct EncStream {                // one per state lane of the CTA, in shared memory (32 bytes)
+    const uint8_t *in;            // o1: first byte of the lane's quarter; o0: first byte of the block
+    const uint32_t *gtab;         // block's compact table in global memory
+    uint32_t len;                 // o1: symbols owned by this lane; o0: block length
+    uint32_t steps;               // steps of the lane's block (longest lane)
+    uint32_t ns;                  // o1: symbols per context row of the compact table
+    uint32_t in_smem;             // table copy in shared memory?
+};
 
-// k_enc0: 1 warp per CTA, 8 blocks per warp, lane k of a group owns state k (symbols k, k+4, k+8, ...).
-// The 8 symbol tables (2 KB each) live in shared memory; input words are staged through a per-group ring by
-// cp.async two chunks ahead, so the recurrence touches only registers and shared memory.
-__global__ void __launch_bounds__(32) k_enc0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
-                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
-                                             const uint2 *__restrict__ syms0, uint8_t *__restrict__ work,
-                                             uint32_t *__restrict__ plen, int32_t *__restrict__ status)
+template <int ORDER>
+__global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                                     uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                                     const uint32_t *__restrict__ tabs, const O1Meta *__restrict__ meta,
+                                                     uint8_t *__restrict__ work, uint32_t *__restrict__ plen,
+                                                     int32_t *__restrict__ status)
 {
-    __shared__ uint2 stab[256][8];          // [symbol][group]
-    __shared__ uint32_t wring[128][8];      // [input word index & 127][group]
-    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
-    uint32_t slot = blockIdx.x * 8 + g;
-    bool have = slot < nslots;
-    uint32_t blk = have ? slots[slot] : 0;
-    BlockDesc d = desc[blk];
-    uint32_t n = have ? d.in_len : 0;
-    const uint8_t *in = d_in + d.in_off;    // 16-byte aligned
-    uint32_t cap = d.work_cap - d.tab_cap;
-    uint8_t *end = work + d.work_off + d.work_cap;
+    extern __shared__ __align__(16) uint8_t smem[];
+    constexpr uint32_t TABE = ORDER ? ENC_TAB_ENTRIES : 256u;
+    constexpr uint32_t RW = ORDER ? 32u : 128u;                                   // input ring words per state (o1) / per block (o0)
+    uint2 *dring = reinterpret_cast<uint2 *>(smem);                               // [2][32 lanes][32 slots], slot = (u + lane) & 31
+    uint32_t *oring = reinterpret_cast<uint32_t *>(smem + 2 * 1024 * 8);          // [2][32 steps][32 cols], col = (lane + 4u) & 31
+    uint32_t *rcp_lut = oring + 2 * 1024;                                         // [4096] ceil(2^(31+shift) / F)
+    uint32_t *iring = rcp_lut + 4096;                                             // input staging, 1024 words
+    uint32_t *tab = iring + 1024;                                                 // [8][TABE]
+    uint8_t *maps = reinterpret_cast<uint8_t *>(tab + 8 * TABE);                  // o1: [8][2][256] cmap | smap
+    __shared__ EncStream strm[32];
+    __shared__ uint8_t *g_end[8];
+    __shared__ uint32_t g_cap[8], g_p[8], g_blk[8], g_ovf[8], xfin[32];
+    __shared__ uint32_t s_max_steps;
 
-    for (uint32_t i = lane; i < 2048; i += 32) {
-        uint32_t gg = i & 7, sym = i >> 3;
-        uint32_t b = __shfl_sync(0xFFFFFFFFu, blk, gg * 4);
-        stab[sym][gg] = __ldg(syms0 + (size_t)b * 256 + sym);
+    const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+    // ---- set-up: every warp helps
+    if (tid < 32) {
+        uint32_t g = tid >> 2, k = tid & 3;
+        uint32_t slot = blockIdx.x * 8 + g;
+        bool have = slot < nslots;
+        uint32_t blk = have ? slots[slot] : 0;
+        BlockDesc d = desc[blk];
+        uint32_t n = have ? d.in_len : 0;
+        EncStream s;
+        if (ORDER) {
+            uint32_t q = n >> 2;
+            s.in = d_in + d.in_off + (uint64_t)k * q;
+            s.len = (k == 3) ? n - 3 * q : q;
+            s.steps = n - 3 * q;
+            const O1Meta *m = meta + d.o1_index;
+            s.ns = have ? m->nsym : 1;
+            s.gtab = tabs + (size_t)d.o1_index * 65536;
+            s.in_smem = have && (m->nsym * m->nctx <= ENC_TAB_ENTRIES);
+        } else {
+            s.in = d_in + d.in_off;
+            s.len = n;
+            s.steps = (n + 3) >> 2;
+            s.ns = 0;
+            s.gtab = tabs + (size_t)blk * 256;
+            s.in_smem = 1;
+        }
+        strm[tid] = s;
+        if (k == 0) {
+            g_end[g] = work + d.work_off + d.work_cap;
+            g_cap[g] = have && n ? d.work_cap - d.tab_cap : 0;
+            g_p[g] = 0; g_blk[g] = have && n ? blk : 0xFFFFFFFFu; g_ovf[g] = 0;
+        }
+        uint32_t ms = __reduce_max_sync(0xFFFFFFFFu, s.steps);
+        if (tid == 0) s_max_steps = ms;
     }
-    uint32_t steps = (n + 3) >> 2;          // step s codes symbols 4s..4s+3 == input word s
-    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    uint32_t nchunks = (max_steps + ENC_CHUNK - 1) / ENC_CHUNK;
-    // loop step t handles word s = steps-1-t.  Words of chunk c: s in (steps-1-32c-32, steps-1-32c]
-    auto fetch_chunk = [&](uint32_t c) {
-        // each lane of the group fetches 8 of the chunk's 32 words
+    // rcp_freq of every frequency: ((1 << (shift+31)) + F - 1) / F == ceil(2^(31+shift) / F).  The double division
+    // rounded up, then ceil, is exact: the quotient is < 2^32 and its fractional part is a multiple of 1/F (>= 2^-12),
+    // far above the 2^-21 granularity of a double near 2^32.
+    for (uint32_t F = tid; F < 4096; F += ENC_THREADS) {
+        uint32_t r = 0xFFFFFFFFu;
+        if (F >= 2) {
+            uint32_t shift = 32 - __clz(F - 1);
+            double num = __hiloint2double((int)((1023u + 31u + shift) << 20), 0);
+            r = __double2uint_ru(__ddiv_ru(num, (double)F));
+        }
+        rcp_lut[F] = r;
+    }
+    __syncthreads();
+    for (uint32_t g = 0; g < 8; g++) {
+        const EncStream &s = strm[g * 4];
+        if (g_blk[g] == 0xFFFFFFFFu) continue;
+        if (ORDER) {
+            const O1Meta *m = meta + desc[g_blk[g]].o1_index;
+            for (uint32_t i = tid; i < 256; i += ENC_THREADS) { maps[g * 512 + i] = m->cmap[i]; maps[g * 512 + 256 + i] = m->smap[i]; }
+            if (s.in_smem) {
+                uint32_t cells = m->nsym * m->nctx;
+                for (uint32_t i = tid; i < cells; i += ENC_THREADS) tab[g * TABE + i] = __ldg(s.gtab + i);
+            }
+        } else {
+            for (uint32_t i = tid; i < 256; i += ENC_THREADS) tab[g * TABE + i] = __ldg(s.gtab + i);
+        }
+    }
+    __syncthreads();
+
+    const uint32_t max_steps = s_max_steps;
+    const uint32_t nchunks = (max_steps + EC - 1) / EC;
+    uint32_t x = RANS_L;                       // coder state (warp 2)
+
+    // Input staging (producer warps).  Order 1: one ring of 32 words per state lane (a chunk reads 33 consecutive
+    // bytes of the lane's quarter); order 0: one ring of 128 words per block (a chunk reads 128 consecutive bytes).
+    // Slots are addressed by the global word address, so the three chunks in flight never collide.
+    auto ring_byte = [&](uint32_t r, const uint8_t *p) -> uint32_t {
+        uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        return (iring[r * RW + ((a >> 2) & (RW - 1))] >> ((a & 3) * 8)) & 0xFFu;
+    };
+    // each producer warp owns the 4 states of one block: keep their parameters in registers
+    EncStream mine[4];
+    if (wid < ENC_PROD) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            uint32_t t = c * ENC_CHUNK + i * 4 + k;
-            if (t < steps) {
-                uint32_t s = steps - 1 - t;
-                cp_async4(&wring[s & 127][g], in + 4ull * s);
+        for (int si = 0; si < 4; si++) mine[si] = strm[wid * 4 + si];
+    }
+    auto prefetch_chunk = [&](uint32_t c) {          // called by the producer warps, each for its own block
+        if (ORDER) {
+#pragma unroll
+            for (uint32_t si = 0; si < 4; si++) {
+                const uint32_t s = wid * 4 + si;
+                const EncStream &st = mine[si];
+                uint32_t t0 = c * EC;
+                if (t0 >= st.steps || st.len == 0) continue;
+                int64_t jhi = (int64_t)st.steps - 1 - t0, jlo = jhi - (EC - 1) - 1;     // -1: the context byte
+                if (jhi > (int64_t)st.len - 1) jhi = (int64_t)st.len - 1;
+                if (jlo < 0) jlo = 0;
+                if (jhi < jlo) continue;
+                uintptr_t w0 = reinterpret_cast<uintptr_t>(st.in + jlo) >> 2, w1 = reinterpret_cast<uintptr_t>(st.in + jhi) >> 2;
+                uintptr_t w = w0 + lane;
+                if (w <= w1) cp_async4(&iring[s * RW + (w & (RW - 1))], reinterpret_cast<const void *>(w << 2));
+            }
+        } else {
+            {
+                const uint32_t g = wid;
+                const EncStream &st = mine[0];
+                uint32_t t = c * EC + lane;
+                if (t < st.steps) {
+                    const uint8_t *p = st.in + (uint64_t)(st.steps - 1 - t) * 4;         // word of step t (block start is 16-byte aligned)
+                    uintptr_t w = reinterpret_cast<uintptr_t>(p) >> 2;
+                    cp_async4(&iring[g * RW + (w & (RW - 1))], p);
+                }
             }
         }
     };
-    fetch_chunk(0); fetch_chunk(1);
-    cp_async_commit();
-    uint32_t x = RANS_L, p = 0;
-    bool overflow = false;
-    for (uint32_t c = 0; c < nchunks; c++) {
-        cp_async_wait_all();
-        __syncwarp();
-        fetch_chunk(c + 2);
+    if (wid < ENC_PROD) {
+        prefetch_chunk(0);
+        if (nchunks > 1) prefetch_chunk(1);
         cp_async_commit();
-        uint32_t t0 = c * ENC_CHUNK;
-        // two-stage register pipeline over shared memory: word -> byte -> symbol entry
-        auto sym_at = [&](uint32_t t) -> uint2 {
-            uint32_t s = steps - 1 - t;
-            uint32_t w = wring[s & 127][g];
-            return stab[(w >> (8 * k)) & 0xFF][g];
-        };
-        uint2 s_next = (t0 < steps) ? sym_at(t0) : make_uint2(0, 0);
-#pragma unroll 4
-        for (uint32_t u = 0; u < ENC_CHUNK; u++) {
-            uint32_t t = t0 + u;
-            uint2 s = s_next;
-            if (u + 1 < ENC_CHUNK && t + 1 < steps) s_next = sym_at(t + 1);
-            bool act = t < steps && (uint64_t)(steps - 1 - t) * 4 + k < n;
-            uint32_t nb = 0, bytes = 0;
-            if (act) x = put_symbol(x, s, nb, bytes);
-            emit_step(end, p, cap, nb, bytes, lane, overflow);
-        }
     }
-    if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
-}
 
-// k_enc1: lane k owns the quarter [k*q, (k+1)*q), lane 3 also the remainder; coded backwards,
-// symbol = in[j], context = in[j-1] (0 for the first byte of the quarter) [E14.java:24-71].
-// Neither the input bytes nor the (context, symbol) table entries depend on the coder state, so both are
-// fetched asynchronously: input words two chunks ahead into a per-lane ring, table entries one chunk ahead
-// into a double-buffered descriptor ring (cp.async 8 B each).  The recurrence then reads one uint2 per step
-// from shared memory.
-__global__ void __launch_bounds__(32) k_enc1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
-                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
-                                             const uint2 *__restrict__ syms1, uint8_t *__restrict__ work,
-                                             uint32_t *__restrict__ plen, int32_t *__restrict__ status)
-{
-    __shared__ uint2 dring[2][ENC_CHUNK][32];   // [buffer][step in chunk][lane]
-    __shared__ uint32_t bring[32][32];          // [input word index & 31][lane]
-    uint32_t lane = threadIdx.x, k = lane & 3u;
-    uint32_t slot = blockIdx.x * 8 + (lane >> 2);
-    bool have = slot < nslots;
-    uint32_t blk = have ? slots[slot] : 0;
-    BlockDesc d = desc[blk];
-    uint32_t n = have ? d.in_len : 0;
-    uint32_t q = n >> 2;
-    const uint8_t *base = d_in + d.in_off;      // 16-byte aligned
-    uint32_t o0 = k * q;                        // this lane's quarter starts at byte o0 of the block
-    uint32_t mylen = (k == 3) ? n - 3 * q : q;
-    const uint2 *st = syms1 + (size_t)d.o1_index * 65536;
-    uint32_t cap = d.work_cap - d.tab_cap;
-    uint8_t *end = work + d.work_off + d.work_cap;
-
-    uint32_t steps = n - 3 * q;                 // lane 3's length = longest
-    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    uint32_t nchunks = (max_steps + ENC_CHUNK - 1) / ENC_CHUNK;
-
-    // loop step t codes local index j = steps-1-t (active when j < mylen)
-    int64_t wnext = mylen ? (int64_t)((o0 + mylen - 1) >> 2) : -1;   // next input word to fetch, descending
-    const int64_t wmin = o0 >> 2;
-    auto fetch_bytes = [&](uint32_t c) {
-        // make the ring cover every byte chunk c will look up: down to (context of) j_lo
-        int64_t jlo = (int64_t)steps - 1 - ((int64_t)c * ENC_CHUNK + ENC_CHUNK - 1);
-        if (jlo < 1) jlo = 1;
-        int64_t wneed = (int64_t)((o0 + (uint64_t)jlo - 1) >> 2);
+    for (uint32_t I = 0; I < nchunks + 2; I++) {
+        if (wid < ENC_PROD) {
+            // ================= PRODUCERS: descriptors of chunk I; input words of chunk I+2 on their way
+            cp_async_wait_all();
+            __syncwarp();
+            if (I + 2 < nchunks) prefetch_chunk(I + 2);
+            cp_async_commit();
+            if (I < nchunks) {
+                uint2 *dbuf = dring + (I & 1) * 1024;
+                const uint32_t t = I * EC + lane;               // this thread's step
 #pragma unroll
-        for (int i = 0; i < 10; i++) {
-            if (wnext >= wneed && wnext >= wmin) {
-                cp_async4(&bring[wnext & 31][lane], base + 4 * wnext);
-                wnext--;
+                for (uint32_t si = 0; si < 4; si++) {
+                    const uint32_t s = wid * 4 + si;
+                    const EncStream &st = mine[si];
+                    uint32_t e = 0;
+                    if (t < st.steps) {
+                        const uint32_t g = s >> 2;
+                        if (ORDER) {
+                            uint32_t j = st.steps - 1 - t;
+                            if (j < st.len) {
+                                uint32_t l = ring_byte(s, st.in + j);
+                                uint32_t c = j ? ring_byte(s, st.in + j - 1) : 0;   // context 0 at the lane's first byte
+                                uint32_t cell = maps[g * 512 + c] * st.ns + maps[g * 512 + 256 + l];
+                                e = st.in_smem ? tab[g * TABE + cell] : __ldg(st.gtab + cell);
+                            }
+                        } else {
+                            uint64_t i = (uint64_t)(st.steps - 1 - t) * 4 + (s & 3);
+                            if (i < st.len) e = tab[g * TABE + ring_byte(g, st.in + i)];
+                        }
+                    }
+                    // e = freq | start << 12 (0 = no symbol for this state in this step)
+                    uint32_t F = e & 0xFFFu, C = e >> 12;
+                    uint32_t sh = F >= 2 ? 31 - __clz(F - 1) : 0;                    // rcp_shift - 32
+                    uint32_t bias = F >= 2 ? C : C + TOTFREQ - 1;
+                    uint2 dsc = F ? make_uint2(rcp_lut[F], bias | (F << 13) | (sh << 25)) : make_uint2(0u, 0u);
+                    dbuf[s * 32 + ((lane + s) & 31)] = dsc;
+                }
             }
-        }
-    };
-    auto ring_byte = [&](uint32_t o) -> uint32_t { return (bring[(o >> 2) & 31][lane] >> ((o & 3) * 8)) & 0xFF; };
-    auto issue_desc = [&](uint32_t c) {
-        uint32_t t0 = c * ENC_CHUNK;
-        if (t0 >= steps) return;
-        uint32_t j = steps - 1 - t0;
-        uint32_t l = j < mylen ? ring_byte(o0 + j) : 0;
+        } else if (wid == ENC_PROD) {
+            // ================= CODER: chunk I-1
+            if (I >= 1 && I <= nchunks) {
+                const uint2 *dbuf = dring + ((I - 1) & 1) * 1024 + lane * 32;
+                uint32_t *obuf = oring + ((I - 1) & 1) * 1024;
+                uint2 d = dbuf[lane & 31];
 #pragma unroll 8
-        for (uint32_t u = 0; u < ENC_CHUNK; u++, j--) {
-            if (t0 + u >= steps) break;
-            bool act = j < mylen;
-            bool actn = j >= 1 && j - 1 < mylen;
-            uint32_t cx = actn ? ring_byte(o0 + j - 1) : 0;          // context = previous byte, 0 at j == 0
-            if (act) cp_async8(&dring[c & 1][u][lane], st + cx * 256 + l);
-            l = cx;
+                for (uint32_t u = 0; u < EC; u++) {
+                    uint2 dn = dbuf[(u + 1 + lane) & 31];      // next step's descriptor (wraps harmlessly on the last step)
+                    uint32_t F = (d.y >> 13) & 0xFFFu;
+                    uint32_t x_max = F ? (F << 19) : 0xFFFFFFFFu;                    // F == 0: null step, state unchanged
+                    uint32_t x8 = x >> 8, x16 = x >> 16;
+                    bool c1 = x >= x_max, c2 = x8 >= x_max;
+                    uint32_t xn = c2 ? x16 : (c1 ? x8 : x);
+                    uint32_t q = __umulhi(xn, d.x) >> (d.y >> 25);
+                    obuf[u * 32 + ((lane + 4 * u) & 31)] = (x & 0xFFFFu) | (((uint32_t)c1 + (uint32_t)c2) << 16);
+                    x = xn + (d.y & 0x1FFFu) + q * (F ? TOTFREQ - F : 0u);
+                    d = dn;
+                }
+            }
+        } else {
+            // ================= EMITTER: chunk I-2
+            if (I >= 2) {
+                const uint32_t *obuf = oring + (I & 1) * 1024;
+                const uint32_t u = lane;
+                const uint32_t gfirst = (wid - ENC_PROD - 1) * 4;
+#pragma unroll 2
+                for (uint32_t g = gfirst; g < gfirst + 4; g++) {
+                    uint4 v = *reinterpret_cast<const uint4 *>(obuf + u * 32 + ((4 * g + 4 * u) & 31));
+                    uint32_t nb0 = v.x >> 16, nb1 = v.y >> 16, nb2 = v.z >> 16, nb3 = v.w >> 16;
+                    uint32_t tot = nb0 + nb1 + nb2 + nb3;
+                    uint32_t total, ex = 0;
+                    {
+                        uint32_t sc = tot;
+#pragma unroll
+                        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                            uint32_t tt = __shfl_up_sync(0xFFFFFFFFu, sc, dlt);
+                            if (lane >= (uint32_t)dlt) sc += tt;
+                        }
+                        total = __shfl_sync(0xFFFFFFFFu, sc, 31);
+                        ex = sc - tot;
+                    }
+                    uint32_t p0 = g_p[g], cap = g_cap[g];
+                    uint8_t *end = g_end[g];
+                    bool ovf = p0 + total > cap;
+                    if (!ovf && tot) {
+                        uint32_t off = p0 + ex;                                      // emission index of this step's first byte
+                        uint32_t w[4] = {v.w, v.z, v.y, v.x};                        // lanes 3,2,1,0
+                        uint32_t nb[4] = {nb3, nb2, nb1, nb0};
+#pragma unroll
+                        for (int k = 0; k < 4; k++) {
+                            if (nb[k]) {
+                                end[-1 - (int64_t)off] = (uint8_t)w[k];
+                                if (nb[k] == 2) end[-2 - (int64_t)off] = (uint8_t)(w[k] >> 8);
+                                off += nb[k];
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) { if (ovf) g_ovf[g] = 1; else g_p[g] = p0 + total; }
+                    __syncwarp();
+                }
+            }
         }
-    };
-
-    fetch_bytes(0); fetch_bytes(1);
-    cp_async_commit();
-    cp_async_wait_all();
-    __syncwarp();
-    issue_desc(0);
-    cp_async_commit();
-
-    uint32_t x = RANS_L, p = 0;
-    bool overflow = false;
-    for (uint32_t c = 0; c < nchunks; c++) {
-        cp_async_wait_all();
-        __syncwarp();
-        fetch_bytes(c + 2);
-        issue_desc(c + 1);
-        cp_async_commit();
-        uint32_t t0 = c * ENC_CHUNK;
-        const uint2 *dr = &dring[c & 1][0][lane];
-        uint2 s_next = dr[0];
-#pragma unroll 4
-        for (uint32_t u = 0; u < ENC_CHUNK; u++) {
-            uint32_t t = t0 + u;
-            uint2 s = s_next;
-            if (u + 1 < ENC_CHUNK) s_next = dr[(u + 1) * 32];
-            bool act = t < steps && (steps - 1 - t) < mylen;
-            uint32_t nb = 0, bytes = 0;
-            if (act) x = put_symbol(x, s, nb, bytes);
-            emit_step(end, p, cap, nb, bytes, lane, overflow);
+        __syncthreads();
+    }
+    if (wid == ENC_PROD) xfin[lane] = x;
+    __syncthreads();
+    if (wid == ENC_PROD + 1) {
+        // states 3,2,1,0 big-endian then reversed == states 0..3 little-endian in front of the payload [E04.java:46-50]
+        uint32_t g = lane >> 2, k = lane & 3;
+        uint32_t blk = g_blk[g];
+        if (blk != 0xFFFFFFFFu) {
+            uint32_t p = g_p[g], cap = g_cap[g];
+            bool ovf = g_ovf[g] || p + 16 > cap;
+            if (!ovf) {
+                uint32_t xs = xfin[lane];
+                uint8_t *s = g_end[g] - p - 16 + 4 * k;
+                s[0] = (uint8_t)xs; s[1] = (uint8_t)(xs >> 8); s[2] = (uint8_t)(xs >> 16); s[3] = (uint8_t)(xs >> 24);
+            }
+            if (k == 0) {
+                plen[blk] = ovf ? 0 : p + 16;
+                if (ovf) status[blk] = CRAMGPU_ERR_OUT_TOO_SMALL;
+            }
         }
     }
-    if (have && n) finish_block(end, p, cap, x, k, overflow, blk, plen, status);
 }
+#define ENC_SMEM(ORDER) (2 * 1024 * 8 + 2 * 1024 * 4 + 4096 * 4 + 4096 + 8 * ((ORDER) ? ENC_TAB_ENTRIES : 256u) * 4 + ((ORDER) ? 8 * 512 : 0))
 
 // ------------------------------------------------------------------------------------------------
 // k_scan_out: one CTA; out_off[i] = sum of roundup16(len) of the blocks before i.
@@ -763,10 +837,10 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     size_t o_F0 = c.take(1024 * (size_t)nblocks);
     size_t o_tlen = c.take(4 * (size_t)nblocks), o_plen = c.take(4 * (size_t)nblocks);
     size_t o_zero_end = c.off;                                                  // [o_F0, here) is zeroed
-    size_t o_syms0 = c.take(2048 * (size_t)nblocks);
+    size_t o_syms0 = c.take(1024 * (size_t)nblocks);
     size_t o_meta = c.take(sizeof(O1Meta) * (size_t)std::max(n1, 1u));
     size_t o_F1 = c.take(262144 * (size_t)n1 + 16);
-    size_t o_syms1 = c.take(524288 * (size_t)n1 + 16);
+    size_t o_syms1 = c.take(262144 * (size_t)n1 + 16);
     size_t o_work = c.take(work_total + 256);
     if (int rc = pool_reserve(ctx, ctx->scratch, c.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->scratch.p;
@@ -795,7 +869,13 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
 
     const BlockDesc *dd = (const BlockDesc *)(S + o_desc);
     uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
-    uint2 *syms0 = (uint2 *)(S + o_syms0), *syms1 = (uint2 *)(S + o_syms1);
+    uint32_t *syms0 = (uint32_t *)(S + o_syms0), *syms1 = (uint32_t *)(S + o_syms1);
+    static bool attr_done = false;
+    if (!attr_done) {
+        CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(1)));
+        CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(0)));
+        attr_done = true;
+    }
     O1Meta *meta = (O1Meta *)(S + o_meta);
     uint32_t *F1 = (uint32_t *)(S + o_F1);
     uint8_t *work = S + o_work;
@@ -810,11 +890,11 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
             LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
             LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
             LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
-            LAUNCH(ctx, st, "k_enc1", k_enc1<<<(n1 + 7) / 8, 32, 0, st>>>(dd, d_s1, n1, d_in, syms1, work, plen, d_status));
+            LAUNCH(ctx, st, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), st>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status));
         }
         if (n0) {
             LAUNCH(ctx, st, "k_tables0", k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen));
-            LAUNCH(ctx, st, "k_enc0", k_enc0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, d_s0, n0, d_in, syms0, work, plen, d_status));
+            LAUNCH(ctx, st, "k_enc0", k_enc<0><<<(n0 + 7) / 8, ENC_THREADS, ENC_SMEM(0), st>>>(dd, d_s0, n0, d_in, syms0, meta, work, plen, d_status));
         }
     }
     LAUNCH(ctx, st, "k_scan_out", k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status));
