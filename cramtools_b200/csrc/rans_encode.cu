@@ -19,24 +19,21 @@
 // bytes are written downwards from the end of the block's work area, positions coming from two
 // ballots + popc per step, so no reversal pass is needed.
 #include "internal.cuh"
+#include <stdlib.h>
+#include <stdio.h>
 
 // ------------------------------------------------------------------------------------------------
 // device helpers
 
-// Encoding.RansEncSymbolInit [Encoding.java:21-43], packed into 8 bytes:
-//   .x = rcp_freq,  .y = bias (13 bits) | freq << 13 (12 bits) | (rcp_shift - 32) << 25
-// x_max = freq << 19 and cmpl_freq = 4096 - freq are recomputed in the coder (off the critical chain).
-__device__ __forceinline__ uint2 make_enc_sym(uint32_t start, uint32_t freq)
+// Encoding.RansEncSymbolInit [Encoding.java:21-43]: everything of a coder symbol except rcp_freq, in one word
+//   bias (13 bits) | freq << 13 (13 bits) | (rcp_shift - 32) << 26
+// x_max = freq << 19 and cmpl_freq = 4096 - freq are recomputed in the coder (off the critical chain); rcp_freq
+// depends on freq alone and comes from a 4096-entry table the coder kernel builds in shared memory.
+__device__ __forceinline__ uint32_t enc_cell(uint32_t start, uint32_t freq)
 {
-    uint32_t rcp, sh, bias;
-    if (freq < 2) {
-        rcp = 0xFFFFFFFFu; sh = 0; bias = start + TOTFREQ - 1;
-    } else {
-        uint32_t shift = 32 - __clz(freq - 1);   // smallest shift with freq <= 1 << shift
-        rcp = (uint32_t)(((1ull << (shift + 31)) + freq - 1) / freq);
-        sh = shift - 1; bias = start;
-    }
-    return make_uint2(rcp, bias | (freq << 13) | (sh << 25));
+    uint32_t sh = freq >= 2 ? 31 - __clz(freq - 1) : 0;             // shift - 1, shift = ceil(log2 freq)
+    uint32_t bias = freq >= 2 ? start : start + TOTFREQ - 1;
+    return bias | (freq << 13) | (sh << 26);
 }
 
 __device__ __forceinline__ uint32_t warp_sum(uint32_t v)
@@ -277,7 +274,7 @@ __global__ void __launch_bounds__(256) k_tables0(const BlockDesc *__restrict__ d
     __syncthreads();
     uint32_t base = 0;
     for (int k = 0; k < (int)w; k++) base += reds[k];
-    tab0[(size_t)blk * 256 + j] = nf ? (nf | ((base + ex) << 12)) : 0u;      // {freq, cumulative start} [buildSyms_o0 :197-211]
+    tab0[(size_t)blk * 256 + j] = nf ? enc_cell(base + ex, nf) : 0u;         // [buildSyms_o0 :197-211]
     rowF[j] = (uint16_t)nf;
     __syncthreads();
     if (w == 0) {
@@ -364,7 +361,7 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
                 for (int i = 0; i < 8; i++) {
                     if (a0 + i < ns) {
                         row[a0 + i] = f[i];
-                        srow[a0 + i] = f[i] ? (f[i] | (x << 12)) : 0u;                 // [buildSyms_o1 :248-265]
+                        srow[a0 + i] = f[i] ? enc_cell(x, f[i]) : 0u;                   // [buildSyms_o1 :248-265]
                         x += f[i];
                     }
                 }
@@ -407,27 +404,32 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
 
 // ------------------------------------------------------------------------------------------------
 // ------------------------------------------------------------------------------------------------
-// The coder kernel.  A CTA codes 8 blocks (32 states) with four warps that form a software pipeline over
-// chunks of 32 coder steps, handing work over through shared-memory rings:
+// The coder kernel.  A CTA of 12 warps codes 8 blocks (32 states) as a software pipeline over chunks of 32 coder
+// steps; the warps hand work over through shared-memory rings and meet at one __syncthreads per chunk:
 //
-//   warps 0-7  PRODUCERS (4 states each)  for every (state, step) of chunk I: input byte(s) -> {freq, start} cell of
-//                     the block's table (shared memory when it fits, else global) -> packed coder descriptor
-//                     {rcp_freq, bias | freq << 13 | (rcp_shift - 32) << 25}  [Encoding.RansEncSymbolInit, Encoding.java:21-43].
+//   8 PRODUCER warps (one block = 4 states each)  for every (state, step) of chunk I: input byte(s) -> {freq, start}
+//                     cell of the block's table (shared memory when it fits, else global) -> packed coder descriptor
+//                     {rcp_freq, bias | freq << 13 | (rcp_shift - 32) << 26}  [Encoding.RansEncSymbolInit, Encoding.java:21-43].
 //                     Threads run over the 32 steps of one state at a time, so input reads are contiguous; the input
 //                     words themselves arrive two chunks ahead by cp.async.  rcp_freq comes from a 4096-entry table
 //                     built in shared memory when the CTA starts.
-//   warp 8     CODER  lane = state: 32 dependent steps of chunk I-1; nothing but the recurrence of
-//                     RansEncPutSymbol [Encoding.java:46-71], no global memory
-//   warps 9,10 EMITTERS (4 blocks each)  chunk I-2: positions of the renormalisation bytes (lanes emit in the order 3,2,1,0 within a
-//                     step, [E04.java:41-44]) by a prefix sum over the steps; bytes stored downwards from the end of the
-//                     block's work area == the reversed buffer of [rans/Utils.java:7-33]
+//   1 CODER warp      lane = state: 32 dependent steps of chunk I-1; nothing but the recurrence of
+//                     RansEncPutSymbol [Encoding.java:46-71], ~20 instructions per step, no global memory.  It sits
+//                     shares its SM sub-partition with one producer only.
+//   2 EMITTER warps (4 blocks each)  chunk I-2: positions of the renormalisation bytes (lanes emit in the order 3,2,1,0
+//                     within a step, [E04.java:41-44]) by a prefix sum over the steps; bytes stored downwards from the
+//                     end of the block's work area == the reversed buffer of [rans/Utils.java:7-33]
 //
-// A single warp alone on an SM issues one dependent instruction every ~4 cycles (ncu: profiles/r1_k_enc1_v2_hotloop.txt),
-// so the states' recurrence is kept as short as possible and everything else runs beside it on other warps.
+// Why: a warp alone on an SM issues one dependent instruction every ~4 cycles and a sub-partition sustains ~0.6 IPC on
+// this code (ncu: profiles/r1_k_enc1_v2_hotloop.txt, profiles/r1_k_enc_v3_roles.txt), so the states' recurrence is kept
+// as short as possible and everything that does not depend on the state runs beside it on other warps.
+// A step in which a state has no symbol (tails, shorter blocks of the CTA) gets freq = 4096: x_max = 2^31 (never
+// renormalises), cmpl_freq = 0, bias = 0 -- the recurrence maps x to x without any special case.
 #define EC 32
 #define ENC_TAB_ENTRIES 1792u     // order-1 {freq,start} cells per block kept in shared memory (ctx x sym <= 1792, e.g. 42 x 42)
-#define ENC_PROD 8                 // producer warps (4 states each)
-#define ENC_THREADS ((ENC_PROD + 3) * 32)   // + 1 coder warp + 2 emitter warps (4 blocks each)
+#define ENC_THREADS 384
+#define DR_STRIDE 33              // descriptor ring: uint2 per (state row, step), padded: conflict-free for both sides
+#define OR_STRIDE 36              // byte ring: u32 per (step row, state), padded so the emitter's 16-byte reads spread over the banks
 
 __device__ __forceinline__ void cp_async4(void *smem, const void *g)
 {
@@ -438,36 +440,54 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 struct EncStream {                // one per state lane of the CTA, in shared memory (32 bytes)
-    const uint8_t *in;            // o1: first byte of the lane's quarter; o0: first byte of the block
+    const uint8_t *base;          // first byte of the block (16-byte aligned)
     const uint32_t *gtab;         // block's compact table in global memory
+    uint32_t off;                 // o1: offset of the lane's quarter inside the block; o0: 0
     uint32_t len;                 // o1: symbols owned by this lane; o0: block length
     uint32_t steps;               // steps of the lane's block (longest lane)
-    uint32_t ns;                  // o1: symbols per context row of the compact table
-    uint32_t in_smem;             // table copy in shared memory?
+    uint32_t ns_smem;             // o1: symbols per context row of the compact table | in-shared-memory flag << 31
 };
+
+#define NULL_DESC make_uint2(0u, 4096u << 13)
+__device__ unsigned long long g_enc_dbg[16];   // CRAMGPU_DBG bit 4: busy cycles per warp of CTA 0
 
 template <int ORDER>
 __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                                      uint32_t nslots, const uint8_t *__restrict__ d_in,
                                                      const uint32_t *__restrict__ tabs, const O1Meta *__restrict__ meta,
                                                      uint8_t *__restrict__ work, uint32_t *__restrict__ plen,
-                                                     int32_t *__restrict__ status)
+                                                     int32_t *__restrict__ status, int dbg)
 {
     extern __shared__ __align__(16) uint8_t smem[];
     constexpr uint32_t TABE = ORDER ? ENC_TAB_ENTRIES : 256u;
     constexpr uint32_t RW = ORDER ? 32u : 128u;                                   // input ring words per state (o1) / per block (o0)
-    uint2 *dring = reinterpret_cast<uint2 *>(smem);                               // [2][32 lanes][32 slots], slot = (u + lane) & 31
-    uint32_t *oring = reinterpret_cast<uint32_t *>(smem + 2 * 1024 * 8);          // [2][32 steps][32 cols], col = (lane + 4u) & 31
-    uint32_t *rcp_lut = oring + 2 * 1024;                                         // [4096] ceil(2^(31+shift) / F)
-    uint32_t *iring = rcp_lut + 4096;                                             // input staging, 1024 words
-    uint32_t *tab = iring + 1024;                                                 // [8][TABE]
-    uint8_t *maps = reinterpret_cast<uint8_t *>(tab + 8 * TABE);                  // o1: [8][2][256] cmap | smap
+    // Every ring is addressed as an offset from `smem` so that the compiler keeps the accesses in the shared state
+    // space (pointers that travel through lambdas become generic and cost an S2R + address rebuild per access).
+    constexpr uint32_t OFF_DR = 0;                                                // uint2 [2][32 states][DR_STRIDE]
+    constexpr uint32_t OFF_OR = OFF_DR + 2 * 32 * DR_STRIDE * 8;                  // u32   [2][32 steps][OR_STRIDE]
+    constexpr uint32_t OFF_RCP = OFF_OR + 2 * 32 * OR_STRIDE * 4;                 // u32   [4096] ceil(2^(31+shift) / F)
+    constexpr uint32_t OFF_IR = OFF_RCP + 4096 * 4;                               // u32   [1024] input staging
+    constexpr uint32_t OFF_TAB = OFF_IR + 1024 * 4;                               // u32   [8][TABE]
+    constexpr uint32_t OFF_MAPS = OFF_TAB + 8 * TABE * 4;                         // u8    o1: [8][2][256] cmap | smap
+#define DRING(i) (reinterpret_cast<uint2 *>(smem + OFF_DR)[i])
+#define ORING(i) (reinterpret_cast<uint32_t *>(smem + OFF_OR)[i])
+#define RCPLUT(i) (reinterpret_cast<uint32_t *>(smem + OFF_RCP)[i])
+#define IRING(i) (reinterpret_cast<uint32_t *>(smem + OFF_IR)[i])
+#define TAB(i) (reinterpret_cast<uint32_t *>(smem + OFF_TAB)[i])
+#define MAPS(i) (smem[OFF_MAPS + (i)])
+#define RING_BYTE(r, o) ((uint32_t)smem[OFF_IR + (r) * (RW * 4) + ((o) & (RW * 4 - 1))])     /* input byte at offset o of the block */
     __shared__ EncStream strm[32];
     __shared__ uint8_t *g_end[8];
     __shared__ uint32_t g_cap[8], g_p[8], g_blk[8], g_ovf[8], xfin[32];
     __shared__ uint32_t s_max_steps;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    // roles, balanced over the 4 SM sub-partitions (warp w runs on sub-partition w % 4; each sustains ~0.5 IPC here):
+    //   0: coder(0) + producer(4) + emitter(8)   1: emitter(1) + producers(5, 9)
+    //   2: emitter(2) + producers(6, 10)         3: producers(3, 7, 11)
+    const bool is_coder = wid == 0, is_emit = wid == 1 || wid == 2 || wid == 8, is_prod = wid >= 3 && wid != 8;
+    const uint32_t prod_id = wid < 8 ? wid - 3 : wid - 4;                        // 3,4,5,6,7,9,10,11 -> 0..7
+    const uint32_t emit_first = wid == 1 ? 0 : wid == 2 ? 3 : 6, emit_last = wid == 1 ? 3 : wid == 2 ? 6 : 8;
 
     // ---- set-up: every warp helps
     if (tid < 32) {
@@ -478,22 +498,21 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
         BlockDesc d = desc[blk];
         uint32_t n = have ? d.in_len : 0;
         EncStream s;
+        s.base = d_in + d.in_off;
         if (ORDER) {
             uint32_t q = n >> 2;
-            s.in = d_in + d.in_off + (uint64_t)k * q;
+            s.off = k * q;
             s.len = (k == 3) ? n - 3 * q : q;
             s.steps = n - 3 * q;
             const O1Meta *m = meta + d.o1_index;
-            s.ns = have ? m->nsym : 1;
             s.gtab = tabs + (size_t)d.o1_index * 65536;
-            s.in_smem = have && (m->nsym * m->nctx <= ENC_TAB_ENTRIES);
+            s.ns_smem = (have ? m->nsym : 1) | ((have && m->nsym * m->nctx <= ENC_TAB_ENTRIES) ? 0x80000000u : 0u);
         } else {
-            s.in = d_in + d.in_off;
+            s.off = 0;
             s.len = n;
             s.steps = (n + 3) >> 2;
-            s.ns = 0;
             s.gtab = tabs + (size_t)blk * 256;
-            s.in_smem = 1;
+            s.ns_smem = 0x80000000u;
         }
         strm[tid] = s;
         if (k == 0) {
@@ -514,7 +533,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
             double num = __hiloint2double((int)((1023u + 31u + shift) << 20), 0);
             r = __double2uint_ru(__ddiv_ru(num, (double)F));
         }
-        rcp_lut[F] = r;
+        RCPLUT(F) = r;
     }
     __syncthreads();
     for (uint32_t g = 0; g < 8; g++) {
@@ -522,176 +541,168 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
         if (g_blk[g] == 0xFFFFFFFFu) continue;
         if (ORDER) {
             const O1Meta *m = meta + desc[g_blk[g]].o1_index;
-            for (uint32_t i = tid; i < 256; i += ENC_THREADS) { maps[g * 512 + i] = m->cmap[i]; maps[g * 512 + 256 + i] = m->smap[i]; }
-            if (s.in_smem) {
+            for (uint32_t i = tid; i < 256; i += ENC_THREADS) { MAPS(g * 512 + i) = m->cmap[i]; MAPS(g * 512 + 256 + i) = m->smap[i]; }
+            if (s.ns_smem >> 31) {
                 uint32_t cells = m->nsym * m->nctx;
-                for (uint32_t i = tid; i < cells; i += ENC_THREADS) tab[g * TABE + i] = __ldg(s.gtab + i);
+                for (uint32_t i = tid; i < cells; i += ENC_THREADS) TAB(g * TABE + i) = __ldg(s.gtab + i);
             }
         } else {
-            for (uint32_t i = tid; i < 256; i += ENC_THREADS) tab[g * TABE + i] = __ldg(s.gtab + i);
+            for (uint32_t i = tid; i < 256; i += ENC_THREADS) TAB(g * TABE + i) = __ldg(s.gtab + i);
         }
     }
     __syncthreads();
 
     const uint32_t max_steps = s_max_steps;
     const uint32_t nchunks = (max_steps + EC - 1) / EC;
-    uint32_t x = RANS_L;                       // coder state (warp 2)
+    uint32_t x = RANS_L;                       // coder state
 
     // Input staging (producer warps).  Order 1: one ring of 32 words per state lane (a chunk reads 33 consecutive
     // bytes of the lane's quarter); order 0: one ring of 128 words per block (a chunk reads 128 consecutive bytes).
-    // Slots are addressed by the global word address, so the three chunks in flight never collide.
-    auto ring_byte = [&](uint32_t r, const uint8_t *p) -> uint32_t {
-        uintptr_t a = reinterpret_cast<uintptr_t>(p);
-        return (iring[r * RW + ((a >> 2) & (RW - 1))] >> ((a & 3) * 8)) & 0xFFu;
-    };
-    // each producer warp owns the 4 states of one block: keep their parameters in registers
-    EncStream mine[4];
-    if (wid < ENC_PROD) {
+    // Slots are addressed by the word offset inside the block, so the three chunks in flight never collide.
+    EncStream mine[4];                         // a producer warp owns the 4 states of one block
+    const uint32_t g_mine = prod_id & 7;
+    if (is_prod) {
 #pragma unroll
-        for (int si = 0; si < 4; si++) mine[si] = strm[wid * 4 + si];
+        for (int si = 0; si < 4; si++) mine[si] = strm[g_mine * 4 + si];
     }
-    auto prefetch_chunk = [&](uint32_t c) {          // called by the producer warps, each for its own block
-        if (ORDER) {
-#pragma unroll
-            for (uint32_t si = 0; si < 4; si++) {
-                const uint32_t s = wid * 4 + si;
-                const EncStream &st = mine[si];
-                uint32_t t0 = c * EC;
-                if (t0 >= st.steps || st.len == 0) continue;
-                int64_t jhi = (int64_t)st.steps - 1 - t0, jlo = jhi - (EC - 1) - 1;     // -1: the context byte
-                if (jhi > (int64_t)st.len - 1) jhi = (int64_t)st.len - 1;
-                if (jlo < 0) jlo = 0;
-                if (jhi < jlo) continue;
-                uintptr_t w0 = reinterpret_cast<uintptr_t>(st.in + jlo) >> 2, w1 = reinterpret_cast<uintptr_t>(st.in + jhi) >> 2;
-                uintptr_t w = w0 + lane;
-                if (w <= w1) cp_async4(&iring[s * RW + (w & (RW - 1))], reinterpret_cast<const void *>(w << 2));
-            }
-        } else {
-            {
-                const uint32_t g = wid;
-                const EncStream &st = mine[0];
-                uint32_t t = c * EC + lane;
-                if (t < st.steps) {
-                    const uint8_t *p = st.in + (uint64_t)(st.steps - 1 - t) * 4;         // word of step t (block start is 16-byte aligned)
-                    uintptr_t w = reinterpret_cast<uintptr_t>(p) >> 2;
-                    cp_async4(&iring[g * RW + (w & (RW - 1))], p);
-                }
-            }
-        }
-    };
-    if (wid < ENC_PROD) {
-        prefetch_chunk(0);
-        if (nchunks > 1) prefetch_chunk(1);
+    // Input prefetch of one chunk for this producer warp's block, two cp.async instructions per warp:
+    // order 1: lane -> (state = lane >> 3, word = lane & 7) and a second round for words 8, 9 (33 bytes span <= 10 words);
+    // order 0: lane -> word of step t.  The lane's own state parameters stay in registers for the whole kernel.
+    uint32_t pf_off = 0, pf_len = 0, pf_steps = 0, pf_slot = 0;
+    const uint8_t *pf_base = nullptr;
+    if (is_prod) {
+        const EncStream &ps = strm[g_mine * 4 + (ORDER ? (lane >> 3) : 0)];
+        pf_off = ps.off; pf_len = ps.len; pf_steps = ps.steps; pf_base = ps.base;
+        pf_slot = ORDER ? (g_mine * 4 + (lane >> 3)) * RW : g_mine * RW;
+    }
+#define PREFETCH_CHUNK(c)                                                                                          \
+    do {                                                                                                           \
+        const uint32_t t0_ = (c) * EC;                                                                             \
+        if (ORDER) {                                                                                               \
+            if (t0_ < pf_steps && pf_len) {                                                                        \
+                uint32_t jhi_ = pf_steps - 1 - t0_;                   /* first symbol of the chunk */               \
+                uint32_t jlo_ = jhi_ >= EC ? jhi_ - EC : 0;           /* down to the last symbol's context byte */  \
+                if (jhi_ > pf_len - 1) jhi_ = pf_len - 1;                                                          \
+                if (jhi_ >= jlo_) {                                                                                \
+                    uint32_t w0_ = (pf_off + jlo_) >> 2, w1_ = (pf_off + jhi_) >> 2;                               \
+                    uint32_t w_ = w0_ + (lane & 7);                                                                \
+                    if (w_ <= w1_) cp_async4(&IRING(pf_slot + (w_ & (RW - 1))), pf_base + 4ull * w_);              \
+                    w_ += 8;                                                                                       \
+                    if ((lane & 7) < 2 && w_ <= w1_) cp_async4(&IRING(pf_slot + (w_ & (RW - 1))), pf_base + 4ull * w_); \
+                }                                                                                                  \
+            }                                                                                                      \
+        } else {                                                                                                   \
+            uint32_t t_ = t0_ + lane;                                                                              \
+            if (t_ < pf_steps) {                                                                                   \
+                uint32_t w_ = pf_steps - 1 - t_;                      /* word of step t */                          \
+                cp_async4(&IRING(pf_slot + (w_ & (RW - 1))), pf_base + 4ull * w_);                                 \
+            }                                                                                                      \
+        }                                                                                                          \
+    } while (0)
+    if (is_prod) {
+        PREFETCH_CHUNK(0u);
+        cp_async_commit();
+        if (nchunks > 1) PREFETCH_CHUNK(1u);
         cp_async_commit();
     }
 
+    unsigned long long busy = 0, t_start = clock64();
     for (uint32_t I = 0; I < nchunks + 2; I++) {
-        if (wid < ENC_PROD) {
+        unsigned long long t_in = clock64();
+        if (is_prod) {
             // ================= PRODUCERS: descriptors of chunk I; input words of chunk I+2 on their way
-            cp_async_wait_all();
-            __syncwarp();
-            if (I + 2 < nchunks) prefetch_chunk(I + 2);
+            // one cp.async group per chunk; chunk I was requested two iterations ago, so only it has to have landed
+            if (I + 2 < nchunks && !(dbg & 8)) PREFETCH_CHUNK(I + 2);
             cp_async_commit();
-            if (I < nchunks) {
-                uint2 *dbuf = dring + (I & 1) * 1024;
+            asm volatile("cp.async.wait_group 2;" ::: "memory");
+            __syncwarp();
+            if (I < nchunks && !(dbg & 2)) {
+                const uint32_t dbase = (I & 1) * 32 * DR_STRIDE + lane;
                 const uint32_t t = I * EC + lane;               // this thread's step
 #pragma unroll
                 for (uint32_t si = 0; si < 4; si++) {
-                    const uint32_t s = wid * 4 + si;
+                    const uint32_t s = g_mine * 4 + si;
                     const EncStream &st = mine[si];
                     uint32_t e = 0;
                     if (t < st.steps) {
-                        const uint32_t g = s >> 2;
                         if (ORDER) {
                             uint32_t j = st.steps - 1 - t;
                             if (j < st.len) {
-                                uint32_t l = ring_byte(s, st.in + j);
-                                uint32_t c = j ? ring_byte(s, st.in + j - 1) : 0;   // context 0 at the lane's first byte
-                                uint32_t cell = maps[g * 512 + c] * st.ns + maps[g * 512 + 256 + l];
-                                e = st.in_smem ? tab[g * TABE + cell] : __ldg(st.gtab + cell);
+                                uint32_t o = st.off + j;
+                                uint32_t l = RING_BYTE(s, o);
+                                uint32_t c = j ? RING_BYTE(s, o - 1) : 0;            // context 0 at the lane's first byte
+                                uint32_t cell = MAPS(g_mine * 512 + c) * (st.ns_smem & 0xFFFFu) + MAPS(g_mine * 512 + 256 + l);
+                                e = (st.ns_smem >> 31) ? TAB(g_mine * TABE + cell) : __ldg(st.gtab + cell);
                             }
                         } else {
-                            uint64_t i = (uint64_t)(st.steps - 1 - t) * 4 + (s & 3);
-                            if (i < st.len) e = tab[g * TABE + ring_byte(g, st.in + i)];
+                            uint32_t w = st.steps - 1 - t;
+                            if ((uint64_t)w * 4 + si < st.len) e = TAB(g_mine * TABE + RING_BYTE(g_mine, w * 4 + si));
                         }
                     }
-                    // e = freq | start << 12 (0 = no symbol for this state in this step)
-                    uint32_t F = e & 0xFFFu, C = e >> 12;
-                    uint32_t sh = F >= 2 ? 31 - __clz(F - 1) : 0;                    // rcp_shift - 32
-                    uint32_t bias = F >= 2 ? C : C + TOTFREQ - 1;
-                    uint2 dsc = F ? make_uint2(rcp_lut[F], bias | (F << 13) | (sh << 25)) : make_uint2(0u, 0u);
-                    dbuf[s * 32 + ((lane + s) & 31)] = dsc;
+                    // e = packed symbol word (0 = no symbol for this state in this step)
+                    DRING(dbase + s * DR_STRIDE) = e ? make_uint2(RCPLUT((e >> 13) & 0xFFFu), e) : NULL_DESC;
                 }
             }
-        } else if (wid == ENC_PROD) {
+        } else if (is_coder) {
             // ================= CODER: chunk I-1
-            if (I >= 1 && I <= nchunks) {
-                const uint2 *dbuf = dring + ((I - 1) & 1) * 1024 + lane * 32;
-                uint32_t *obuf = oring + ((I - 1) & 1) * 1024;
-                uint2 d = dbuf[lane & 31];
-#pragma unroll 8
+            if (I >= 1 && I <= nchunks && !(dbg & 4)) {
+                const uint32_t dbase = ((I - 1) & 1) * 32 * DR_STRIDE + lane * DR_STRIDE;
+                const uint32_t obase = ((I - 1) & 1) * 32 * OR_STRIDE + lane;
+                uint2 d = DRING(dbase);
+#pragma unroll
                 for (uint32_t u = 0; u < EC; u++) {
-                    uint2 dn = dbuf[(u + 1 + lane) & 31];      // next step's descriptor (wraps harmlessly on the last step)
-                    uint32_t F = (d.y >> 13) & 0xFFFu;
-                    uint32_t x_max = F ? (F << 19) : 0xFFFFFFFFu;                    // F == 0: null step, state unchanged
+                    uint2 dn = DRING(dbase + u + 1);           // next step's descriptor (slot 32 is padding)
+                    uint32_t F = (d.y >> 13) & 0x1FFFu;
+                    uint32_t x_max = F << 19;
                     uint32_t x8 = x >> 8, x16 = x >> 16;
                     bool c1 = x >= x_max, c2 = x8 >= x_max;
                     uint32_t xn = c2 ? x16 : (c1 ? x8 : x);
-                    uint32_t q = __umulhi(xn, d.x) >> (d.y >> 25);
-                    obuf[u * 32 + ((lane + 4 * u) & 31)] = (x & 0xFFFFu) | (((uint32_t)c1 + (uint32_t)c2) << 16);
-                    x = xn + (d.y & 0x1FFFu) + q * (F ? TOTFREQ - F : 0u);
+                    uint32_t q = __umulhi(xn, d.x) >> (d.y >> 26);
+                    ORING(obase + u * OR_STRIDE) = (x & 0xFFFFu) | (((uint32_t)c1 + (uint32_t)c2) << 16);
+                    x = xn + (d.y & 0x1FFFu) + q * (TOTFREQ - F);
                     d = dn;
                 }
             }
-        } else {
-            // ================= EMITTER: chunk I-2
-            if (I >= 2) {
-                const uint32_t *obuf = oring + (I & 1) * 1024;
-                const uint32_t u = lane;
-                const uint32_t gfirst = (wid - ENC_PROD - 1) * 4;
-#pragma unroll 2
-                for (uint32_t g = gfirst; g < gfirst + 4; g++) {
-                    uint4 v = *reinterpret_cast<const uint4 *>(obuf + u * 32 + ((4 * g + 4 * u) & 31));
+        } else if (is_emit) {
+            // ================= EMITTERS: chunk I-2
+            if (I >= 2 && !(dbg & 1)) {
+                const uint32_t obase = (I & 1) * 32 * OR_STRIDE + lane * OR_STRIDE;
+                const uint32_t lt = (1u << lane) - 1u;
+                for (uint32_t g = emit_first; g < emit_last; g++) {
+                    uint4 v = *reinterpret_cast<const uint4 *>(&ORING(obase + 4 * g));
                     uint32_t nb0 = v.x >> 16, nb1 = v.y >> 16, nb2 = v.z >> 16, nb3 = v.w >> 16;
-                    uint32_t tot = nb0 + nb1 + nb2 + nb3;
-                    uint32_t total, ex = 0;
-                    {
-                        uint32_t sc = tot;
-#pragma unroll
-                        for (int dlt = 1; dlt < 32; dlt <<= 1) {
-                            uint32_t tt = __shfl_up_sync(0xFFFFFFFFu, sc, dlt);
-                            if (lane >= (uint32_t)dlt) sc += tt;
-                        }
-                        total = __shfl_sync(0xFFFFFFFFu, sc, 31);
-                        ex = sc - tot;
-                    }
+                    uint32_t tot = nb0 + nb1 + nb2 + nb3;                           // 0..8 bytes in this step
+                    // prefix over the 32 steps from four ballots of the bit planes (short dependency chain)
+                    uint32_t b0 = __ballot_sync(0xFFFFFFFFu, tot & 1), b1 = __ballot_sync(0xFFFFFFFFu, tot & 2);
+                    uint32_t b2 = __ballot_sync(0xFFFFFFFFu, tot & 4), b3 = __ballot_sync(0xFFFFFFFFu, tot & 8);
+                    uint32_t ex = __popc(b0 & lt) + 2 * __popc(b1 & lt) + 4 * __popc(b2 & lt) + 8 * __popc(b3 & lt);
+                    uint32_t total = __popc(b0) + 2 * __popc(b1) + 4 * __popc(b2) + 8 * __popc(b3);
                     uint32_t p0 = g_p[g], cap = g_cap[g];
-                    uint8_t *end = g_end[g];
                     bool ovf = p0 + total > cap;
-                    if (!ovf && tot) {
-                        uint32_t off = p0 + ex;                                      // emission index of this step's first byte
-                        uint32_t w[4] = {v.w, v.z, v.y, v.x};                        // lanes 3,2,1,0
-                        uint32_t nb[4] = {nb3, nb2, nb1, nb0};
+                    // this step's bytes in emission order (lanes 3,2,1,0; low byte of each state first), branch-free
+                    unsigned long long pk = v.w & ((1u << (8 * nb3)) - 1u);
+                    uint32_t acc = nb3;
+                    pk |= (unsigned long long)(v.z & ((1u << (8 * nb2)) - 1u)) << (8 * acc); acc += nb2;
+                    pk |= (unsigned long long)(v.y & ((1u << (8 * nb1)) - 1u)) << (8 * acc); acc += nb1;
+                    pk |= (unsigned long long)(v.x & ((1u << (8 * nb0)) - 1u)) << (8 * acc);
+                    uint8_t *dst = g_end[g] - 1 - (p0 + ex);                         // emission index e lives at end - 1 - e
+                    uint32_t n = ovf ? 0 : tot;
 #pragma unroll
-                        for (int k = 0; k < 4; k++) {
-                            if (nb[k]) {
-                                end[-1 - (int64_t)off] = (uint8_t)w[k];
-                                if (nb[k] == 2) end[-2 - (int64_t)off] = (uint8_t)(w[k] >> 8);
-                                off += nb[k];
-                            }
-                        }
-                    }
+                    for (int i = 0; i < 8; i++)
+                        if ((uint32_t)i < n) dst[-i] = (uint8_t)(pk >> (8 * i));
                     __syncwarp();
                     if (lane == 0) { if (ovf) g_ovf[g] = 1; else g_p[g] = p0 + total; }
                     __syncwarp();
                 }
             }
         }
+        busy += clock64() - t_in;
         __syncthreads();
     }
-    if (wid == ENC_PROD) xfin[lane] = x;
+    if ((dbg & 16) && blockIdx.x == 0 && lane == 0) { g_enc_dbg[wid] = busy; if (wid == 0) g_enc_dbg[12] = clock64() - t_start; }
+    if (is_coder) xfin[lane] = x;
     __syncthreads();
-    if (wid == ENC_PROD + 1) {
+    if (wid == 2) {
         // states 3,2,1,0 big-endian then reversed == states 0..3 little-endian in front of the payload [E04.java:46-50]
         uint32_t g = lane >> 2, k = lane & 3;
         uint32_t blk = g_blk[g];
@@ -710,7 +721,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
         }
     }
 }
-#define ENC_SMEM(ORDER) (2 * 1024 * 8 + 2 * 1024 * 4 + 4096 * 4 + 4096 + 8 * ((ORDER) ? ENC_TAB_ENTRIES : 256u) * 4 + ((ORDER) ? 8 * 512 : 0))
+#define ENC_SMEM(ORDER) (2 * 32 * DR_STRIDE * 8 + 2 * 32 * OR_STRIDE * 4 + 4096 * 4 + 4096 + 8 * ((ORDER) ? ENC_TAB_ENTRIES : 256u) * 4 + ((ORDER) ? 8 * 512 : 0))
 
 // ------------------------------------------------------------------------------------------------
 // k_scan_out: one CTA; out_off[i] = sum of roundup16(len) of the blocks before i.
@@ -870,6 +881,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     const BlockDesc *dd = (const BlockDesc *)(S + o_desc);
     uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
     uint32_t *syms0 = (uint32_t *)(S + o_syms0), *syms1 = (uint32_t *)(S + o_syms1);
+    const int dbg = getenv("CRAMGPU_DBG") ? atoi(getenv("CRAMGPU_DBG")) : 0;   // timing experiments only (wrong output)
     static bool attr_done = false;
     if (!attr_done) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(1)));
@@ -890,14 +902,22 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
             LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
             LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
             LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
-            LAUNCH(ctx, st, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), st>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status));
+            LAUNCH(ctx, st, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), st>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status, dbg));
         }
         if (n0) {
             LAUNCH(ctx, st, "k_tables0", k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen));
-            LAUNCH(ctx, st, "k_enc0", k_enc<0><<<(n0 + 7) / 8, ENC_THREADS, ENC_SMEM(0), st>>>(dd, d_s0, n0, d_in, syms0, meta, work, plen, d_status));
+            LAUNCH(ctx, st, "k_enc0", k_enc<0><<<(n0 + 7) / 8, ENC_THREADS, ENC_SMEM(0), st>>>(dd, d_s0, n0, d_in, syms0, meta, work, plen, d_status, dbg));
         }
     }
     LAUNCH(ctx, st, "k_scan_out", k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status));
+    if (dbg & 16) {
+        unsigned long long h[16];
+        cudaStreamSynchronize(st);
+        cudaMemcpyFromSymbol(h, g_enc_dbg, sizeof h);
+        fprintf(stderr, "k_enc busy cycles per warp (CTA 0), total %llu:", h[12]);
+        for (int w = 0; w < 12; w++) fprintf(stderr, " %llu", h[w]);
+        fprintf(stderr, "\n");
+    }
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->pend = EncodePending{dd, work, tlen, plen, d_out_off, d_out_len, nblocks,
                               (n0 + n1) ? 9 + (uint64_t)(n1 ? O1_TAB_CAP : O0_TAB_CAP) + max_len + max_len / 4 + 80 : 0};
