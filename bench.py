@@ -1,17 +1,21 @@
 #!/usr/bin/env python
-"""bench.py -- headline benchmark of the CRAM slice-codec hot path (see DESIGN.md, "Measurement").
+"""bench.py -- headline benchmark of the CRAM slice-codec hot path (DESIGN.md, "Measurement").
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--containers C]
 
-A "step" is one pass of the hot path over this GPU's containers (synthetic, seeded):
-encode then decode of every container.  Containers are independent and are dealt round-robin to the
-ranks (weak scaling: --containers is PER GPU); the only collective is an all-gather of per-container
-compressed sizes from which every rank computes its containers' output offsets.
+Workload (BASELINE.json configs[2], "chr20-scale"): C containers PER GPU of 10 000 simulated 150 bp reads each at
+~45x over a random reference, lossless quality scores.  A "step" is one pass of the whole hot path over this GPU's
+containers:
+    encode  feature extraction + substitution matrix + series packing  ->  rANS of the slice's rANS-coded series
+            (QS, BA from the device; BF, CF, RL, RG, NS, TS order 1 and AP order 0 as the Java host hands them over)
+    decode  rANS decode of the same blocks  ->  base and quality restoration of every record
+Containers are independent and dealt round-robin to the ranks (weak scaling); the only collective is an all-gather
+of per-container compressed sizes, from which every rank derives its containers' output offsets.
 
-One JSON line is printed by rank 0; its keys are described in DESIGN.md.
+One JSON line is printed by rank 0; the keys are explained in DESIGN.md.
 """
 import argparse
-import ctypes
+import ctypes as C
 import json
 import os
 import subprocess
@@ -27,7 +31,11 @@ if ROOT not in sys.path:
 
 READS_PER_CONTAINER = 10000     # CRAMContainerStreamWriter.java:45, CramContext.java:33
 READ_LEN = 150
-UNIQUE_CONTAINERS = 32          # distinct synthetic containers; tiled to --containers (all copies live in HBM)
+COVERAGE = 45
+UNIQUE = 32                     # distinct synthetic containers; tiled to --containers (every copy lives in HBM)
+METRIC = 'cram_encode_decode_reads_per_s'
+UNIT = 'reads/s'
+EXTRA = [('BF', 1), ('CF', 1), ('RL', 1), ('RG', 1), ('NS', 1), ('TS', 1), ('AP', 0)]   # host-produced rANS series (R0)
 
 
 def measured_peaks():
@@ -41,32 +49,66 @@ def measured_peaks():
 # ------------------------------------------------------------------------------------------- workload
 
 
-def slice_series(container_id):
-    """The external data series of one lossless slice that htsjdk codes with rANS
-    (CompressionHeaderFactory.build [CompressionHeaderFactory.java:84-113]): (name, order, bytes)."""
+def itf8_pack_np(v):
+    v = np.asarray(v, np.int64) & 0xFFFFFFFF
+    out = []
+    n1 = v < (1 << 7); n2 = (~n1) & (v < (1 << 14)); n3 = (~n1) & (~n2) & (v < (1 << 21)); n4 = (~n1) & (~n2) & (~n3) & (v < (1 << 28))
+    n5 = ~(n1 | n2 | n3 | n4)
+    ln = n1 * 1 + n2 * 2 + n3 * 3 + n4 * 4 + n5 * 5
+    off = np.concatenate([[0], np.cumsum(ln)])
+    buf = np.zeros(int(off[-1]), np.uint8)
+    o = off[:-1]
+    buf[o[n1]] = v[n1]
+    buf[o[n2]] = (v[n2] >> 8) | 0x80; buf[o[n2] + 1] = v[n2] & 0xFF
+    buf[o[n3]] = (v[n3] >> 16) | 0xC0; buf[o[n3] + 1] = (v[n3] >> 8) & 0xFF; buf[o[n3] + 2] = v[n3] & 0xFF
+    buf[o[n4]] = (v[n4] >> 24) | 0xE0; buf[o[n4] + 1] = (v[n4] >> 16) & 0xFF; buf[o[n4] + 2] = (v[n4] >> 8) & 0xFF; buf[o[n4] + 3] = v[n4] & 0xFF
+    buf[o[n5]] = ((v[n5] >> 28) | 0xF0) & 0xFF; buf[o[n5] + 1] = (v[n5] >> 20) & 0xFF; buf[o[n5] + 2] = (v[n5] >> 12) & 0xFF
+    buf[o[n5] + 3] = (v[n5] >> 4) & 0xFF; buf[o[n5] + 4] = v[n5] & 0xFF
+    return buf
+
+
+def unique_containers(n_unique, seed):
+    """n_unique coordinate-sorted containers over one synthetic contig; returns (ref, rd, extra) where extra[c] is the list of
+    host-produced series of container c in EXTRA order (what htsjdk's Writer would hand to the rANS block codec)."""
     from cramtools_b200 import synth
-    seed = 1000 + container_id
-    n = READS_PER_CONTAINER
-    return [
-        ('QS', 1, synth.qs_stream(n * READ_LEN, seed)),          # 1.5 MB, byte series
-        ('BA', 1, synth.ba_stream(1500, seed + 1)),              # inserted bases
-        ('BF', 1, synth.itf8_stream(n, seed + 2)),
-        ('CF', 1, synth.itf8_stream(n, seed + 3)),
-        ('RL', 1, synth.itf8_stream(2 * n, seed + 4)),
-        ('NS', 1, synth.itf8_stream(n, seed + 5)),
-        ('RG', 1, synth.itf8_stream(5 * n, seed + 6)),           # -1 -> 5-byte ITF8
-        ('TS', 1, synth.itf8_stream(n, seed + 7)),
-        ('AP', 0, synth.itf8_stream(n, seed + 8)),
-    ]
+    n = n_unique * READS_PER_CONTAINER
+    ref_len = n * READ_LEN // COVERAGE + 4096
+    ref = synth.reference(ref_len, seed)
+    rd = synth.reads(ref, n, seed + 1, read_len=READ_LEN, with_names=False)
+    extra = []
+    for c in range(n_unique):
+        a, b = c * READS_PER_CONTAINER, (c + 1) * READS_PER_CONTAINER
+        flag, pos = rd['flag'][a:b].astype(np.int64), rd['pos'][a:b].astype(np.int64)
+        bf = np.where(flag & 16, 0x10, 0)                                   # CRAM BF: negative strand bit
+        cf = np.full(b - a, 3, np.uint8)                                    # force-preserve QS | detached
+        rl = np.full(b - a, READ_LEN)
+        rg = np.full(b - a, -1)                                             # no read group -> 5-byte ITF8
+        ns = np.full(b - a, -1)
+        ts = np.zeros(b - a, np.int64)
+        ap = np.diff(np.concatenate([[pos[0]], pos]))                       # AP delta vs previous record
+        extra.append([itf8_pack_np(bf), cf, itf8_pack_np(rl), itf8_pack_np(rg), itf8_pack_np(ns), itf8_pack_np(ts), itf8_pack_np(ap)])
+    return ref, rd, extra
 
 
-def build_blocks(n_containers, rank):
-    uniq = [slice_series(rank * UNIQUE_CONTAINERS + c) for c in range(min(UNIQUE_CONTAINERS, n_containers))]
-    blocks, orders, names = [], [], []
-    for c in range(n_containers):
-        for name, order, data in uniq[c % len(uniq)]:
-            blocks.append(data); orders.append(order); names.append(name)
-    return blocks, np.array(orders, dtype=np.uint8), names
+def tile_reads(rd, n_unique, n_cont):
+    """host arrays for n_cont containers by tiling the unique ones"""
+    reps = (n_cont + n_unique - 1) // n_unique
+    nr = n_cont * READS_PER_CONTAINER
+    nb = int(rd['read_off'][-1])
+    ncg = int(rd['cigar_off'][-1])
+    out = {}
+    for k in ('bases', 'quals', 'cigar', 'pos', 'flag', 'mapq'):
+        out[k] = np.tile(rd[k], reps)
+    ro = (rd['read_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * nb)[:, None]).reshape(-1)
+    co = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg)[:, None]).reshape(-1)
+    out['read_off'] = np.concatenate([ro[:nr], [ro[nr] if nr < ro.size else reps * nb]])
+    out['cigar_off'] = np.concatenate([co[:nr], [co[nr] if nr < co.size else reps * ncg]])
+    for k in ('pos', 'flag', 'mapq'):
+        out[k] = out[k][:nr]
+    out['bases'] = out['bases'][:int(out['read_off'][-1])]
+    out['quals'] = out['quals'][:int(out['read_off'][-1])]
+    out['cigar'] = out['cigar'][:int(out['cigar_off'][-1])]
+    return out
 
 
 # ------------------------------------------------------------------------------------------- helpers
@@ -80,9 +122,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         threading.Thread.__init__(self, daemon=True)
-        self.index = index
-        self.samples = []
-        self.stop_flag = False
+        self.index, self.samples, self.stop_flag = index, [], False
 
     def run(self):
         while not self.stop_flag:
@@ -102,93 +142,96 @@ class ClockSampler(threading.Thread):
         if not self.samples:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['unavailable']}
         sm = sorted(float(s[0]) for s in self.samples)
-        reasons = []
-        for i, nm in enumerate(['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']):
-            if any(s[2 + i].lower().startswith('active') for s in self.samples):
-                reasons.append(nm)
-        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.samples[0][1]), 'reasons': reasons,
-                'samples': len(sm)}
+        reasons = [nm for i, nm in enumerate(['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'])
+                   if any(s[2 + i].lower().startswith('active') for s in self.samples)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(self.samples[0][1]), 'reasons': reasons, 'samples': len(sm)}
 
 
-def ptr_array(arrs):
-    from cramtools_b200._lib import u8p
-    pa = (u8p * len(arrs))()
-    for i, a in enumerate(arrs):
-        pa[i] = a.ctypes.data_as(u8p)
-    return pa
+def workload_config(args, n_cont, note=''):
+    return {'workload': 'chr20-scale slices (BASELINE configs[2]): %d containers/GPU x 10000 simulated 150 bp reads at %dx, '
+                        'lossless QS; encode = features + series packing + rANS (QS, BA, BF, CF, RL, RG, NS, TS o1; AP o0), '
+                        'decode = rANS + base/quality restoration' % (n_cont, COVERAGE),
+            'containers_per_gpu': n_cont, 'reads_per_container': READS_PER_CONTAINER, 'read_len': READ_LEN,
+            'unique_containers': min(UNIQUE, n_cont), 'quality_model': 'lossless',
+            'l2': 'inputs larger than L2 (no flush needed)' if n_cont >= 64 else 'inputs may fit L2',
+            'sharding': 'containers round-robin over ranks; all-gather of compressed sizes', 'note': note}
 
 
-# ------------------------------------------------------------------------------------------- reference arm
+# ------------------------------------------------------------------------------------------- CPU arm
+
+
+def cpu_step_setup(n_cont, seed):
+    from oracle import rans as orans
+    lib = orans.lib()
+    nu = min(UNIQUE, n_cont)
+    ref, rd, extra = unique_containers(nu, seed)
+    trd = tile_reads(rd, nu, n_cont)
+    i64 = C.POINTER(C.c_int64)
+    keep = dict(cont=np.arange(n_cont + 1, dtype=np.int64) * READS_PER_CONTAINER, bases=trd['bases'], quals=trd['quals'],
+                ro=trd['read_off'].astype(np.int64), cg=trd['cigar'], co=trd['cigar_off'].astype(np.int64), pos=trd['pos'].astype(np.int32),
+                flag=trd['flag'].astype(np.uint16), mapq=trd['mapq'].astype(np.uint8), ref=ref)
+    ex = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
+    ex_ptr = np.array([e.ctypes.data for e in ex], np.uint64)
+    ex_len = np.array([e.size for e in ex], np.uint32)
+    ex_ord = np.array([o for _, o in EXTRA], np.uint8)
+    keep.update(ex=ex, ex_ptr=ex_ptr, ex_len=ex_len, ex_ord=ex_ord)
+    lib.oracle_cram_step.restype = C.c_int
+    comp = C.c_int64(0); chk = C.c_uint64(0)
+
+    def step(threads):
+        rc = lib.oracle_cram_step(
+            C.c_int(threads), C.c_int(n_cont), keep['cont'].ctypes.data_as(i64), C.c_void_p(keep['bases'].ctypes.data),
+            C.c_void_p(keep['quals'].ctypes.data), keep['ro'].ctypes.data_as(i64), C.c_void_p(keep['cg'].ctypes.data),
+            keep['co'].ctypes.data_as(i64), C.c_void_p(keep['pos'].ctypes.data), C.c_void_p(keep['flag'].ctypes.data),
+            C.c_void_p(keep['mapq'].ctypes.data), C.c_void_p(keep['ref'].ctypes.data), C.c_int64(keep['ref'].size), C.c_int(len(EXTRA)),
+            C.c_void_p(keep['ex_ptr'].ctypes.data), C.c_void_p(keep['ex_len'].ctypes.data), C.c_void_p(keep['ex_ord'].ctypes.data),
+            C.c_char_p(b'lossless'), C.byref(comp), C.byref(chk))
+        assert rc == 0, 'CPU oracle round trip failed (%d)' % rc
+        return comp.value
+    return step, keep
+
+
+def cpu_baseline(args, seconds=12.0):
+    """the oracle (C restatement of the reference's Java, pinned to the jar by tests/golden) on all host cores, bounded sample"""
+    cores = os.cpu_count() or 1
+    n_cont = max(2, min(args.containers, cores))
+    step, _ = cpu_step_setup(n_cont, 1000)
+    step(cores)
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        step(cores); reps += 1
+        if time.perf_counter() - t0 > seconds or reps >= 50:
+            break
+    dt = (time.perf_counter() - t0) / reps
+    return {'value': n_cont * READS_PER_CONTAINER / dt, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+            'sample': '%d containers (%d reads) x %d repetitions, one container per thread, %d threads; C restatement of the Java '
+                      'reference (no JVM in the image)' % (n_cont, n_cont * READS_PER_CONTAINER, reps, cores)}
 
 
 def run_reference(args):
-    """CPU implementation of the same step on the host cores.  No JVM exists in this image, so the reference
-    arm is the C restatement of htsjdk's rANS (oracle/, pinned to the jar by tests/golden) run on all host
-    threads over a bounded sample of the workload."""
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    from oracle import rans as orans
-    lib = orans.lib()
     cores = os.cpu_count() or 1
-    n_cont = min(args.containers, max(4, cores // 2))
-    blocks, orders, _ = build_blocks(n_cont, 0)
-    n = len(blocks)
-    ins = [np.ascontiguousarray(b) for b in blocks]
-    in_len = np.array([b.size for b in ins], dtype=np.uint32)
-    caps = np.array([orans.bound(int(x)) for x in in_len], dtype=np.uint32)
-    outs = [np.empty(int(c), dtype=np.uint8) for c in caps]
-    out_len = np.zeros(n, dtype=np.uint32)
-    rc = np.zeros(n, dtype=np.int32)
-    back = [np.empty(max(int(x), 1), dtype=np.uint8) for x in in_len]
-    back_len = np.zeros(n, dtype=np.uint32)
-    u32 = ctypes.POINTER(ctypes.c_uint32)
-    u8 = ctypes.POINTER(ctypes.c_uint8)
-    pin, pout, pback = ptr_array(ins), ptr_array(outs), ptr_array(back)
-
-    def step():
-        r = lib.rans_oracle_many(1, cores, n, pin, in_len.ctypes.data_as(u32), orders.ctypes.data_as(u8), pout,
-                                 caps.ctypes.data_as(u32), out_len.ctypes.data_as(u32),
-                                 rc.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
-        assert r == 0
-        r = lib.rans_oracle_many(0, cores, n, pout, out_len.ctypes.data_as(u32), orders.ctypes.data_as(u8), pback,
-                                 in_len.ctypes.data_as(u32), back_len.ctypes.data_as(u32),
-                                 rc.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
-        assert r == 0
-
+    n_cont = max(2, min(args.containers, 2 * cores))
+    step, _ = cpu_step_setup(n_cont, 1000)
     for _ in range(min(args.warmup, 1)):
-        step()
+        step(cores)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step()
+        step(cores)
     dt = (time.perf_counter() - t0) / args.steps
-    raw = float(in_len.sum())
-    value = raw / dt / 1e9
-    sample = '%d containers (%d rANS blocks, %.1f MB raw) per step, oracle C port on %d threads' % (
-        n_cont, n, raw / 1e6, cores)
-    line = {
-        'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak',
-        'vs_baseline': None, 'dtype': 'u8/u32 integer (+f64 for order-1 normalisation)', 'data': 'synthetic',
-        'config': workload_config(args, n_cont),
-        'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
-        'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
-        'note': 'no JVM in this image: reference arm = C restatement of htsjdk 2.4.1 rANS, byte-identical to the jar '
-                'on tests/golden/rans_jvm.json',
-    }
+    value = n_cont * READS_PER_CONTAINER / dt
+    sample = '%d containers (%d reads) per step, one container per thread, %d threads' % (n_cont, n_cont * READS_PER_CONTAINER, cores)
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': dt * 1e3, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+            'dtype': 'u8/i32 integer (+f64 in the order-1 frequency normalisation)', 'data': 'synthetic',
+            'config': workload_config(args, n_cont, 'bounded sample of the same workload'),
+            'cpu_baseline': {'value': value, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'note': 'no JVM in this image: the reference arm is the C restatement of cramtools/htsjdk (oracle/), byte-identical to '
+                    'the jar on tests/golden/*.json, run the way paralell/BamToCram + CramToBam do: one container per host thread'}
     print(json.dumps(line))
-
-
-METRIC = 'rans_o0o1_encode_decode_GBps'
-UNIT = 'GB/s of raw series bytes through encode+decode'
-
-
-def workload_config(args, n_cont):
-    return {'workload': 'rANS-coded external series of lossless CRAM slices (QS o1 1.5 MB + BA/BF/CF/RL/NS/RG/TS o1 + '
-                        'AP o0 per 10k-read container), BASELINE configs[1]/[2] block mix',
-            'containers_per_gpu': n_cont, 'reads_per_container': READS_PER_CONTAINER, 'read_len': READ_LEN,
-            'unique_containers': min(UNIQUE_CONTAINERS, n_cont), 'l2': 'inputs larger than L2 (no flush needed)',
-            'sharding': 'containers round-robin over ranks; all-gather of compressed sizes'}
 
 
 # ------------------------------------------------------------------------------------------- our arm
@@ -198,7 +241,8 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     import cramtools_b200
-    from cramtools_b200 import device as dv, sharding
+    from cramtools_b200 import device as dv, sharding, records as rec, _lib
+    from cramtools_b200._lib import u8p, u32p, u64p, i32p
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -209,45 +253,137 @@ def run_ours(args):
     dev = torch.device('cuda', local)
     ctx = cramtools_b200.Context(local)
     peaks, peak_kind = measured_peaks()
+    vp = C.c_void_p
 
     n_cont = args.containers
-    blocks, orders, names = build_blocks(n_cont, rank)
-    n = len(blocks)
-    per_cont = n // n_cont
-    raw_bytes = float(sum(b.size for b in blocks))
-    d_in, in_off, in_len = dv.pack_blocks(blocks, dev)
+    nu = min(UNIQUE, n_cont)
+    ref, rd, extra = unique_containers(nu, 1000 + 17 * rank)
+    reps = (n_cont + nu - 1) // nu
+    n_reads = n_cont * READS_PER_CONTAINER
+    nb_u, ncg_u = int(rd['read_off'][-1]), int(rd['cigar_off'][-1])
 
-    # --- device-resident step -----------------------------------------------------------------
-    enc_cap = int(sum(((9 + 1040 + int(l) + int(l) // 4 + 96 + 15) & ~15) for l in in_len)) + n_cont * 9 * 4096
+    # ---- resident inputs: upload the unique containers once, tile on the device
+    def up(a, dt):
+        return torch.from_numpy(np.ascontiguousarray(a, dt).view(np.uint8)).to(dev)
+
+    def tile_u8(a, dt, n_elems):
+        t = up(a, dt)
+        return t.repeat(reps)[:n_elems * np.dtype(dt).itemsize].contiguous()
+    t_bases = tile_u8(rd['bases'], np.uint8, n_reads * READ_LEN)
+    t_quals = tile_u8(rd['quals'], np.uint8, n_reads * READ_LEN)
+    t_pos = tile_u8(rd['pos'], np.int32, n_reads); t_flag = tile_u8(rd['flag'], np.uint16, n_reads); t_mapq = tile_u8(rd['mapq'], np.uint8, n_reads)
+    cig_all = np.tile(rd['cigar'], reps)
+    co_all = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg_u)[:, None]).reshape(-1)
+    co_all = np.concatenate([co_all[:n_reads], [co_all[n_reads] if n_reads < co_all.size else reps * ncg_u]]).astype(np.uint64)
+    t_cigar = up(cig_all[:int(co_all[-1])], np.uint32)
+    t_coff = up(co_all, np.uint64)
+    t_roff = up(np.arange(n_reads + 1, dtype=np.uint64) * READ_LEN, np.uint64)
+    t_ref = up(ref, np.uint8)
+    cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
+    ref_off = np.zeros(n_cont, np.uint64); ref_len = np.full(n_cont, ref.size, np.uint64)
+    R = rec.Reads()
+    R.n_reads = n_reads; R.n_containers = n_cont
+    R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
+    R.ref = vp(t_ref.data_ptr()); R.ref_total = ref.size
+    R.bases = vp(t_bases.data_ptr()); R.quals = vp(t_quals.data_ptr()); R.read_off = vp(t_roff.data_ptr())
+    R.cigar = vp(t_cigar.data_ptr()); R.cigar_off = vp(t_coff.data_ptr()); R.pos = vp(t_pos.data_ptr()); R.flag = vp(t_flag.data_ptr())
+    R.mapq = vp(t_mapq.data_ptr()); R.rflags = None
+
+    # host-produced series, resident: one buffer, 16-byte aligned blocks
+    ex_blocks = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
+    t_extra, ex_off, ex_len = dv.pack_blocks(ex_blocks, dev)
+    ex_addr = ex_off + np.uint64(t_extra.data_ptr())
+    NX = len(EXTRA)
+    NB = 2 + NX                                         # rANS blocks per container: QS, BA, then EXTRA
+    order = np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont)
+    stream = vp(torch.cuda.current_stream().cuda_stream)
+    KQS, KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
+    soff = np.zeros((n_cont, 12), np.uint64); slen = np.zeros((n_cont, 12), np.uint64)
+    F = rec.Features()
+    in_addr = np.zeros(n_cont * NB, np.uint64); in_len = np.zeros(n_cont * NB, np.uint32)
+    in_addr.reshape(n_cont, NB)[:, 2:] = ex_addr.reshape(n_cont, NX)
+    in_len.reshape(n_cont, NB)[:, 2:] = ex_len.reshape(n_cont, NX)
+    enc_cap = int(n_reads * READ_LEN * 0.6) + n_cont * NB * 4096 + int(ex_len.sum())
     enc_out = torch.empty(enc_cap, dtype=torch.uint8, device=dev)
-    res = dv.rans_encode_dev(ctx, d_in, in_off, in_len, orders, out=enc_out)
+    nblk = n_cont * NB
+    e_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); e_len = torch.empty(nblk, dtype=torch.int32, device=dev)
+    e_st = torch.empty(nblk, dtype=torch.int32, device=dev)
+    # region per container = [min start, max end] of its records (CramNormalizer.java:212-225)
+    p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
+    ws = (p.min(axis=1) - 1)
+    we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
+    win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
+    win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
+    o_bases = torch.empty(n_reads * READ_LEN, dtype=torch.uint8, device=dev); o_quals = torch.empty_like(o_bases)
+    o_star = torch.empty(n_reads, dtype=torch.uint8, device=dev); o_stat = torch.empty(n_reads, dtype=torch.int32, device=dev)
+    t_rfl = torch.ones(n_reads, dtype=torch.uint8, device=dev)          # lossless, mapped: force-preserve QS
+
+    def encode_dev():
+        ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(R), None, -1, C.byref(F), soff.ctypes.data_as(u64p),
+                                                      slen.ctypes.data_as(u64p), stream))
+        base = np.uint64(F.streams)
+        v = in_addr.reshape(n_cont, NB); w = in_len.reshape(n_cont, NB)
+        v[:, 0] = base + soff[:, KQS]; w[:, 0] = slen[:, KQS]
+        v[:, 1] = base + soff[:, KBA]; w[:, 1] = slen[:, KBA]
+        ctx.check(ctx.lib.cramgpu_rans_encode_dev(ctx.handle, nblk, None, in_addr.ctypes.data_as(u64p), in_len.ctypes.data_as(u32p),
+                                                  order.ctypes.data_as(u8p), vp(enc_out.data_ptr()), C.c_uint64(enc_cap),
+                                                  vp(e_off.data_ptr()), vp(e_len.data_ptr()), vp(e_st.data_ptr()), stream))
+        sizes = e_len.view(n_cont, NB).sum(dim=1, dtype=torch.int64)
+        return sharding.allgather_offsets(sizes, rank, world)             # the path's only collective
+
+    # ---- one verified pass to learn what the Java host would know on the decode side (block sizes, prefixes, offsets)
+    offs = encode_dev()
     torch.cuda.synchronize()
-    blobs, st = res.to_host()
-    assert (st == 0).all(), 'encode status'
-    comp_bytes = float(sum(len(b) for b in blobs))
-    c_off = res.off.cpu().numpy().view(np.uint64)[:-1].copy()
-    c_len = res.len.cpu().numpy().view(np.uint32).copy()
-    prefixes = np.zeros((n, 9), dtype=np.uint8)
-    for i, b in enumerate(blobs):
-        prefixes[i, :min(9, len(b))] = np.frombuffer(b[:9], dtype=np.uint8)
-    dec_out = torch.empty(int(sum((int(l) + 15) & ~15 for l in in_len)) + 16, dtype=torch.uint8, device=dev)
+    assert int(e_st.abs().sum()) == 0, 'rANS encode status'
+    c_off = e_off.cpu().numpy().view(np.uint64)[:-1].copy(); c_len = e_len.cpu().numpy().view(np.uint32).copy()
+    comp_bytes = float(c_len.sum())
+    enc_host = enc_out[:int(c_off[-1]) + int(c_len[-1])].cpu().numpy()
+    prefixes = np.zeros((nblk, 9), np.uint8)
+    idx = c_off[:, None].astype(np.int64) + np.arange(9)[None, :]
+    ok = c_len >= 9
+    prefixes[ok] = enc_host[idx[ok]]
+    del enc_host
+    raw = in_len.astype(np.int64)
+    d_off = np.concatenate([[0], np.cumsum((raw + 15) & ~15)]).astype(np.uint64)
+    dec_out = torch.empty(int(d_off[-1]) + 64, dtype=torch.uint8, device=dev)
+    dd_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); dd_len = torch.empty(nblk, dtype=torch.int32, device=dev)
+    dd_st = torch.empty(nblk, dtype=torch.int32, device=dev)
+    # per-read offset of its score array inside the decoded QS block (what CramRecordReader knows while parsing)
+    rq = dv.dev_to_numpy(ctx, F.read_qs_off, n_reads, np.uint64)
+    cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
+    rq_new = rq - soff[cidx, KQS] + d_off[cidx * NB + 0]
+    t_rq = up(rq_new, np.uint64)
+    t_rba = torch.full((n_reads,), -1, dtype=torch.int64, device=dev)
+    raw_bytes = float(raw.sum())
+    qs_bytes = float(slen[:, KQS].sum())
+
+    N = rec.NormIn()
+    N.n_reads = n_reads; N.n_containers = n_cont
+    N.cont_off = cont_off.ctypes.data_as(u64p); N.win_off = win_off.ctypes.data_as(u64p); N.win_len = win_len.ctypes.data_as(u64p)
+    N.win_start0 = win_s0.ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(t_ref.data_ptr()); N.ref_total = ref.size
+    N.pos = vp(t_pos.data_ptr()); N.read_off = vp(t_roff.data_ptr()); N.rflags = vp(t_rfl.data_ptr())
+    N.qs = vp(dec_out.data_ptr()); N.read_qs_off = vp(t_rq.data_ptr()); N.ba = vp(dec_out.data_ptr()); N.read_ba_off = vp(t_rba.data_ptr())
+
+    def decode_dev():
+        ctx.check(ctx.lib.cramgpu_rans_decode_dev(ctx.handle, nblk, vp(enc_out.data_ptr()), c_off.ctypes.data_as(u64p),
+                                                  c_len.ctypes.data_as(u32p), prefixes.ctypes.data_as(u8p), vp(dec_out.data_ptr()),
+                                                  C.c_uint64(dec_out.numel()), vp(dd_off.data_ptr()), vp(dd_len.data_ptr()),
+                                                  vp(dd_st.data_ptr()), stream))
+        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
+        N.payload = F.payload
+        ctx.check(ctx.lib.cramgpu_normalize_decode_dev(ctx.handle, C.byref(N), vp(o_bases.data_ptr()), vp(o_quals.data_ptr()),
+                                                       vp(o_star.data_ptr()), vp(o_stat.data_ptr()), stream))
 
     def step_dev():
-        r = dv.rans_encode_dev(ctx, d_in, in_off, in_len, orders, out=enc_out)
-        # per-container compressed size -> global output offsets (the path's only collective)
-        sizes = r.len.view(n_cont, per_cont).sum(dim=1, dtype=torch.int64)
-        offs = sharding.allgather_offsets(sizes, rank, world)
-        r2 = dv.rans_decode_dev(ctx, enc_out, c_off, c_len, prefixes, out=dec_out)
-        return r, r2, offs
+        o = encode_dev()
+        decode_dev()
+        return o
 
-    # correctness of what is being timed: decode(encode(x)) == x on device, sizes vs oracle on a sample
-    r, r2, offs = step_dev()
+    # correctness of what is timed: the round trip restores every base and quality of every read
+    decode_dev()
     torch.cuda.synchronize()
-    assert int(r.status.abs().sum()) == 0 and int(r2.status.abs().sum()) == 0
-    raws, _ = r2.to_host()
-    for i in range(0, n, max(1, n // 37)):
-        assert raws[i] == blocks[i].tobytes(), 'round trip mismatch in block %d' % i
-    del raws
+    assert int(dd_st.abs().sum()) == 0 and int(o_stat.abs().sum()) == 0 and int(o_star.sum()) == 0
+    assert torch.equal(o_bases, t_bases) and torch.equal(o_quals, t_quals), 'round trip mismatch'
 
     def barrier():
         if world > 1:
@@ -276,80 +412,42 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-
-    # per-kernel average duration inside the timed region
     kt = {}
     for name, m in spans:
         kt.setdefault(name, []).append(m)
-    kavg = {k: float(np.mean(v)) for k, v in kt.items()}
+    kavg = {k: float(np.sum(v)) / args.steps for k, v in kt.items()}       # per step (a kernel may launch more than once per step)
     top = max(kavg, key=kavg.get)
 
-    # --- end-to-end step through the host-buffer C ABI ------------------------------------------
-    ins = [np.ascontiguousarray(b) for b in blocks]
-    from cramtools_b200 import rans_bound
-    caps = np.array([rans_bound(b.size) for b in ins], dtype=np.uint32)
-    outs = [np.empty(int(c), dtype=np.uint8) for c in caps]
-    out_len = np.zeros(n, dtype=np.uint32)
-    status = np.zeros(n, dtype=np.int32)
-    back = [np.empty(max(b.size, 1), dtype=np.uint8) for b in ins]
-    back_len = np.zeros(n, dtype=np.uint32)
-    in_len32 = np.array([b.size for b in ins], dtype=np.uint32)
-    from cramtools_b200._lib import u32p, u8p, i32p
-    pin, pout, pback = ptr_array(ins), ptr_array(outs), ptr_array(back)
-
-    def step_e2e():
-        rc = ctx.lib.cramgpu_rans_encode_batch(ctx.handle, n, pin, in_len32.ctypes.data_as(u32p), orders.ctypes.data_as(u8p),
-                                               pout, caps.ctypes.data_as(u32p), out_len.ctypes.data_as(u32p),
-                                               status.ctypes.data_as(i32p))
-        ctx.check(rc)
-        rc = ctx.lib.cramgpu_rans_decode_batch(ctx.handle, n, pout, out_len.ctypes.data_as(u32p), pback,
-                                               in_len32.ctypes.data_as(u32p), back_len.ctypes.data_as(u32p),
-                                               status.ctypes.data_as(i32p))
-        ctx.check(rc)
-
-    step_e2e()
-    assert bytes(back[0][:back_len[0]]) == blocks[0].tobytes()
-    barrier()
-    t0 = time.perf_counter()
-    e2e_steps = max(1, min(args.steps, 3))
-    for _ in range(e2e_steps):
-        step_e2e()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
-    t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item())
+    # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
+    n_e2e = min(n_cont, args.e2e_containers)
+    e2e = run_e2e(ctx, args, ref, rd, extra, nu, n_e2e, world, barrier)
 
     if rank == 0:
-        value = raw_bytes * world / (ms * 1e-3) / 1e9
-        # roofline of the dominant kernel: algorithmic bytes per launch / its average duration
-        algo = {'k_enc1': None}
-        raw1 = float(sum(b.size for b, o in zip(blocks, orders) if o == 1 and b.size >= 4))
-        raw0 = raw_bytes - raw1
-        comp1 = float(sum(len(b) for b, o in zip(blobs, orders) if o == 1))
-        comp0 = comp_bytes - comp1
-        algo_bytes = {'k_enc1': raw1 + comp1, 'k_enc0': raw0 + comp0, 'k_dec1': raw1 + comp1, 'k_dec0': raw0 + comp0,
-                      'k_hist0': raw_bytes, 'k_hist1': raw1, 'k_pack': 2 * comp_bytes}
-        ab = algo_bytes.get(top)
+        value = n_reads * world / (ms * 1e-3)
+        o1_raw = raw_bytes - float(in_len.reshape(n_cont, NB)[:, -1].sum())
+        comp1 = comp_bytes * (o1_raw / raw_bytes)
+        algo = {'k_enc1': o1_raw + comp1, 'k_dec1': o1_raw + comp1, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
+                'k_rec_walk_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_walk_write': n_reads * (3 * READ_LEN + 40.0),
+                'k_norm': n_reads * (3 * READ_LEN + 20.0), 'k_pack': 2 * comp_bytes}
+        ab = algo.get(top)
         achieved = ab / (kavg[top] * 1e-3) / 1e9 if ab else None
         peak = float(peaks['hbm_gbs'])
-        lanes1 = 4 * sum(1 for o in orders if o == 1)
+        rans_ms_enc = sum(v for k, v in kavg.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
+        rans_ms_dec = sum(v for k, v in kavg.items() if k in ('k_dec_tables', 'k_dec0', 'k_dec1', 'k_dec1_big'))
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
-            'dtype': 'u8/u32 integer (+f64 for order-1 normalisation)', 'data': 'synthetic',
+            'dtype': 'u8/i32 integer (+f64 in the order-1 frequency normalisation)', 'data': 'synthetic',
             'config': workload_config(args, n_cont),
-            'compression_ratio': comp_bytes / raw_bytes,
-            'kernels_ms': kavg, 'gpu_launches': int(launches),
+            'rans': {'raw_GB_per_step_per_gpu': raw_bytes / 1e9, 'compressed_ratio': comp_bytes / raw_bytes,
+                     'encode_GBps_per_gpu': raw_bytes / (rans_ms_enc * 1e-3) / 1e9, 'decode_GBps_per_gpu': raw_bytes / (rans_ms_dec * 1e-3) / 1e9,
+                     'qs_block_bytes': qs_bytes / n_cont, 'state_lanes_in_flight': int(4 * nblk)},
+            'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak if achieved else None, 'traffic': None, 'peak_kind': peak_kind,
-                         'lanes_in_flight': lanes1,
-                         'note': 'rANS is a per-state recurrence: attainable rate = lanes x clock / cycles-per-symbol, see DESIGN.md'},
-            'e2e': {'value': raw_bytes * world / (e2e_ms * 1e-3) / 1e9, 'unit': UNIT,
-                    'h2d_bytes_per_step': int(raw_bytes + comp_bytes), 'd2h_bytes_per_step': int(comp_bytes + raw_bytes),
-                    'ms_per_step': e2e_ms},
-            'clocks': clocks,
+                         'note': 'rANS is a recurrence per state: attainable rate = resident states x clock / cycles per step '
+                                 '(DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
+            'e2e': e2e, 'clocks': clocks,
         }
         if world == 1 and not args.no_cpu:
             line['cpu_baseline'] = cpu_baseline(args)
@@ -358,40 +456,104 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
-def cpu_baseline(args):
-    """the oracle (C port of htsjdk's rANS) timed on this box's host cores on a bounded sample"""
-    from oracle import rans as orans
-    lib = orans.lib()
-    cores = os.cpu_count() or 1
-    n_cont = max(2, min(args.containers, cores // 2))
-    blocks, orders, _ = build_blocks(n_cont, 0)
-    n = len(blocks)
-    ins = [np.ascontiguousarray(b) for b in blocks]
-    in_len = np.array([b.size for b in ins], dtype=np.uint32)
-    caps = np.array([orans.bound(int(x)) for x in in_len], dtype=np.uint32)
-    outs = [np.empty(int(c), dtype=np.uint8) for c in caps]
-    out_len = np.zeros(n, dtype=np.uint32)
-    rc = np.zeros(n, dtype=np.int32)
-    back = [np.empty(max(int(x), 1), dtype=np.uint8) for x in in_len]
-    back_len = np.zeros(n, dtype=np.uint32)
-    u32 = ctypes.POINTER(ctypes.c_uint32)
-    u8 = ctypes.POINTER(ctypes.c_uint8)
-    pin, pout, pback = ptr_array(ins), ptr_array(outs), ptr_array(back)
-    reps = 0
+def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
+    """the same step through the host-memory entry points: every byte crosses PCIe inside the timed region"""
+    from cramtools_b200 import records as rec, rans_bound
+    from cramtools_b200._lib import u8p, u32p, u64p, i32p, u8pp
+    import torch
+    vp = C.c_void_p
+    trd = tile_reads(rd, nu, n_cont)
+    n_reads = n_cont * READS_PER_CONTAINER
+    cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
+    ref_off = np.zeros(n_cont, np.uint64); ref_len = np.full(n_cont, ref.size, np.uint64)
+    a = dict(bases=trd['bases'], quals=trd['quals'], read_off=trd['read_off'].astype(np.uint64), cigar=trd['cigar'].astype(np.uint32),
+             cigar_off=trd['cigar_off'].astype(np.uint64), pos=trd['pos'].astype(np.int32), flag=trd['flag'].astype(np.uint16),
+             mapq=trd['mapq'].astype(np.uint8))
+    R = rec.Reads()
+    R.n_reads = n_reads; R.n_containers = n_cont
+    R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
+    R.ref = vp(ref.ctypes.data); R.ref_total = ref.size
+    for k, v in a.items():
+        setattr(R, k, vp(v.ctypes.data))
+    R.rflags = None
+    F = rec.Features()
+    NX = len(EXTRA); NB = 2 + NX; nblk = n_cont * NB
+    ex = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
+    in_ptr = np.zeros(nblk, np.uint64); in_len = np.zeros(nblk, np.uint32)
+    in_ptr.reshape(n_cont, NB)[:, 2:] = np.array([e.ctypes.data for e in ex], np.uint64).reshape(n_cont, NX)
+    in_len.reshape(n_cont, NB)[:, 2:] = np.array([e.size for e in ex], np.uint32).reshape(n_cont, NX)
+    order = np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont)
+    KQS, KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
+    # output buffers: generous fixed slots (the reference allocates rans_bound(n) per block)
+    cap_qs = rans_bound(READS_PER_CONTAINER * READ_LEN)
+    caps = np.tile(np.array([cap_qs] + [rans_bound(60000)] * (NB - 1), np.uint32), n_cont)
+    cap_off = np.concatenate([[0], np.cumsum(caps.astype(np.int64))])
+    comp = np.empty(int(cap_off[-1]), np.uint8)
+    out_ptr = (np.uint64(comp.ctypes.data) + cap_off[:-1].astype(np.uint64))
+    out_len = np.zeros(nblk, np.uint32); status = np.zeros(nblk, np.int32)
+    back = np.empty(int(cap_off[-1]), np.uint8)                     # decoded series, same slots
+    back_ptr = (np.uint64(back.ctypes.data) + cap_off[:-1].astype(np.uint64))
+    back_len = np.zeros(nblk, np.uint32)
+    p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
+    reps = (n_cont + nu - 1) // nu
+    ws = (p.min(axis=1) - 1); we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
+    win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
+    win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
+    rfl = np.ones(n_reads, np.uint8)
+    o_b = np.empty(n_reads * READ_LEN, np.uint8); o_q = np.empty_like(o_b); o_s = np.empty(n_reads, np.uint8); o_t = np.empty(n_reads, np.int32)
+    cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
+    rba = np.full(n_reads, 0xFFFFFFFFFFFFFFFF, np.uint64)
+    N = rec.NormIn()
+    N.n_reads = n_reads; N.n_containers = n_cont
+    N.cont_off = cont_off.ctypes.data_as(u64p); N.win_off = win_off.ctypes.data_as(u64p); N.win_len = win_len.ctypes.data_as(u64p)
+    N.win_start0 = win_s0.ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(ref.ctypes.data); N.ref_total = ref.size
+    N.pos = vp(a['pos'].ctypes.data); N.read_off = vp(a['read_off'].ctypes.data); N.rflags = vp(rfl.ctypes.data)
+    N.ba = vp(back.ctypes.data); N.read_ba_off = vp(rba.ctypes.data); N.qs = vp(back.ctypes.data)
+    h2d = d2h = 0
+
+    def step():
+        nonlocal h2d, d2h
+        ctx.check(ctx.lib.cramgpu_features_encode(ctx.handle, C.byref(R), None, -1, C.byref(F)))
+        soff = np.ctypeslib.as_array(C.cast(F.stream_off, u64p), (n_cont, 12)); slen = np.ctypeslib.as_array(C.cast(F.stream_len, u64p), (n_cont, 12))
+        v = in_ptr.reshape(n_cont, NB); w = in_len.reshape(n_cont, NB)
+        v[:, 0] = np.uint64(F.streams) + soff[:, KQS]; w[:, 0] = slen[:, KQS]
+        v[:, 1] = np.uint64(F.streams) + soff[:, KBA]; w[:, 1] = slen[:, KBA]
+        ctx.check(ctx.lib.cramgpu_rans_encode_batch(ctx.handle, nblk, C.cast(in_ptr.ctypes.data, u8pp), in_len.ctypes.data_as(u32p),
+                                                    order.ctypes.data_as(u8p), C.cast(out_ptr.ctypes.data, u8pp), caps.ctypes.data_as(u32p),
+                                                    out_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+        ctx.check(ctx.lib.cramgpu_rans_decode_batch(ctx.handle, nblk, C.cast(out_ptr.ctypes.data, u8pp), out_len.ctypes.data_as(u32p),
+                                                    C.cast(back_ptr.ctypes.data, u8pp), caps.ctypes.data_as(u32p),
+                                                    back_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+        # records as CramRecordReader would hand them over: features from the encoder, score arrays inside the decoded QS series
+        rq = np.ctypeslib.as_array(C.cast(F.read_qs_off, u64p), (n_reads,))
+        rq_new = rq - soff[cidx, KQS] + cap_off[cidx * NB].astype(np.uint64)
+        N.read_qs_off = vp(rq_new.ctypes.data)
+        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
+        N.payload = F.payload
+        ctx.check(ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(N), o_b.ctypes.data_as(u8p), o_q.ctypes.data_as(u8p),
+                                                   o_s.ctypes.data_as(u8p), o_t.ctypes.data_as(i32p)))
+        nf = int(F.n_feat)
+        h2d = int(2 * n_reads * READ_LEN + ref.size + 20 * n_reads + a['cigar'].nbytes + in_len.sum() + out_len.sum()
+                  + ref.size + 17 * nf + 33 * n_reads + in_len.sum())
+        d2h = int(F.streams_len + 17 * nf + 25 * n_reads + out_len.sum() + in_len.sum() + 2 * n_reads * READ_LEN + 5 * n_reads)
+    step()
+    assert np.array_equal(o_b, a['bases']) and np.array_equal(o_q, a['quals']), 'e2e round trip mismatch'
+    barrier()
+    k = max(1, min(args.steps, 3))
     t0 = time.perf_counter()
-    while True:
-        lib.rans_oracle_many(1, cores, n, pin, in_len.ctypes.data_as(u32), orders.ctypes.data_as(u8), pout,
-                             caps.ctypes.data_as(u32), out_len.ctypes.data_as(u32), rc.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
-        lib.rans_oracle_many(0, cores, n, pout, out_len.ctypes.data_as(u32), orders.ctypes.data_as(u8), pback,
-                             in_len.ctypes.data_as(u32), back_len.ctypes.data_as(u32), rc.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
-        reps += 1
-        if time.perf_counter() - t0 > 10.0 or reps >= 20:
-            break
-    dt = (time.perf_counter() - t0) / reps
-    raw = float(in_len.sum())
-    return {'value': raw / dt / 1e9, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-            'sample': '%d containers (%d blocks, %.1f MB raw) x %d repetitions, oracle C port, %d threads'
-                      % (n_cont, n, raw / 1e6, reps, cores)}
+    for _ in range(k):
+        step()
+    barrier()
+    ms = (time.perf_counter() - t0) / k * 1e3
+    t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {'value': n_reads * world / (ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
+            'ms_per_step': ms, 'containers_per_gpu': n_cont,
+            'path': 'cramgpu_features_encode -> cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_normalize_decode, '
+                    'host buffers in and out, every copy inside the timed region'}
 
 
 def main():
@@ -400,7 +562,8 @@ def main():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--containers', type=int, default=1024, help='containers PER GPU (10 000 reads each)')
+    ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
+    ap.add_argument('--e2e-containers', type=int, default=512, help='containers per GPU of the end-to-end (host buffer) leg')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -33,6 +33,7 @@ SIGNATURES = {
     'cramgpu_last_error': (ctypes.c_char_p, [vp]),
     'cramgpu_sync': (ctypes.c_int, [vp]),
     'cramgpu_launch_count': (ctypes.c_uint64, [vp]),
+    'cramgpu_copy_to_host': (ctypes.c_int, [vp, vp, vp, ctypes.c_uint64, vp]),
     'cramgpu_profile_enable': (ctypes.c_int, [vp, ctypes.c_int]),
     'cramgpu_profile_read': (ctypes.c_int, [vp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_char_p),
                                             ctypes.POINTER(ctypes.c_float)]),

@@ -149,6 +149,18 @@ int cramgpu_sync(cramgpu_ctx *ctx)
 
 uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+int cramgpu_copy_to_host(cramgpu_ctx *ctx, void *dst_host, const void *src_dev, uint64_t bytes, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!bytes) return CRAMGPU_OK;
+    if (!dst_host || !src_dev) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    CUDA_TRY(ctx, cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CRAMGPU_OK;
+}
+
 int cramgpu_rans_encode_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
                             const uint32_t *in_len, const uint8_t *order, uint8_t *d_out, uint64_t out_cap,
                             uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, void *stream)

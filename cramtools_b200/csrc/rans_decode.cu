@@ -15,13 +15,16 @@
 // Every table lookup of the decoder depends on the state, so nothing can be prefetched: the tables must be
 // on-chip.  Order 0: the 4 KB slot->symbol table and 1 KB {freq,start} table of each of the warp's 8 blocks
 // are copied to shared memory.  Order 1 would need 4 KB per context (168 KB for a 42-symbol quality block),
-// so it uses a compact form instead: per context the 64 cumulative frequencies of the (<= 64) bytes the block
-// uses, searched in two 8-way steps with SWAR compares (144 B per context).  The compressed stream is staged
-// through a per-group shared-memory ring by cp.async and consumed from an 8-byte register window.
+// so it uses a compact form instead (232 B per context, blocks with <= 48 distinct bytes): a 128-entry table
+// slot >> 5 -> first candidate symbol rank, plus the cumulative frequencies of the ranks; the symbol is the
+// candidate advanced by the number of range ends <= slot among the next three (a loop finishes the rare longer
+// runs).  One profile-driven rule shaped the kernel: a warp alone on its SM issues one dependent instruction every
+// ~4 cycles, so the step was cut from 135 to ~65 instructions (profiles/r1_k_dec1_v2_mix.txt).  The compressed
+// stream is staged through a per-group byte ring in shared memory by cp.async.
 #include "internal.cuh"
 
-#define DEC_MAXU 64          // alphabet limit of the shared-memory order-1 path
-#define DEC_ROW 72           // u16 per context row: 64 cumulative ends + 8 group ends
+#define DEC_MAXU 48          // alphabet limit of the shared-memory order-1 path
+#define DEC_ROWB 232         // bytes per context row: coarse[128] u8 | cum[52] u16 (cum[0] = 0, cum[r+1] = end of rank r, rest 0xFFFF)
 #define DEC_CHUNK 16         // decoder steps per stream-staging round (<= 8 bytes per step and group)
 #define DEC_RING 128         // stream ring words per group
 
@@ -32,7 +35,7 @@ struct DecMeta {
 
 // compact order-1 decoder tables of one block (global scratch; copied to shared memory by k_dec1)
 struct DecCompact {
-    uint16_t rows[DEC_MAXU][DEC_ROW];   // rows[ctx rank][r] = end of symbol rank r's slot range; [64+g] = rows[.][8g+7]
+    uint8_t rows[DEC_MAXU][DEC_ROWB];   // per context rank: coarse | cum
     uint8_t ualpha[DEC_MAXU];           // rank -> byte
     uint32_t nU, pad[3];
 };
@@ -143,8 +146,11 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
                 if (p0) cp->ualpha[b0] = (uint8_t)(2 * tid);
                 if (p1) cp->ualpha[b0 + p0] = (uint8_t)(2 * tid + 1);
                 if (tid == 0) cp->nU = s_nU;
-                // contexts that never get a row keep all-zero (never selected) cumulative ends
-                for (uint32_t i = tid; i < DEC_MAXU * DEC_ROW; i += 128) (&cp->rows[0][0])[i] = 0;
+                // contexts that never get a row: coarse 0, cumulative ends 0xFFFF except cum[0] = 0 (only corrupt streams get here)
+                for (uint32_t i = tid; i < DEC_MAXU * DEC_ROWB; i += 128) {
+                    uint32_t o = i % DEC_ROWB;
+                    (&cp->rows[0][0])[i] = (o < 130) ? 0 : 0xFF;
+                }
             }
         }
         __syncthreads();
@@ -166,16 +172,25 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
         __syncthreads();
         if (s_bad) break;
         if (small) {
-            // cumulative ends over byte ranks: warp 0, lane owns ranks 2*lane, 2*lane+1
+            // cumulative ends over byte ranks (warp 0, lane owns ranks 2*lane, 2*lane+1), then the coarse table
+            uint8_t *row = cp->rows[rank[s_ctx]];
+            uint16_t *cum = reinterpret_cast<uint16_t *>(row + 128);
             if (w == 0) {
                 uint32_t r0 = 2 * lane, r1 = r0 + 1, nU = s_nU;
                 uint32_t f0 = r0 < nU ? F[cp->ualpha[r0]] : 0, f1 = r1 < nU ? F[cp->ualpha[r1]] : 0;
-                uint32_t s = f0 + f1, inc = s;
+                uint32_t inc = f0 + f1;
                 for (int dlt = 1; dlt < 32; dlt <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, dlt); if (lane >= (uint32_t)dlt) inc += t; }
-                uint16_t *row = cp->rows[rank[s_ctx]];
-                row[r0] = (uint16_t)(inc - f1);
-                row[r1] = (uint16_t)inc;
-                if ((lane & 3) == 3) row[64 + (lane >> 2)] = (uint16_t)inc;   // end of ranks 8g..8g+7
+                if (r0 < nU) { cum[r0 + 1] = (uint16_t)(inc - f1); C[r0] = (uint16_t)(inc - f1); }
+                if (r1 < nU) { cum[r1 + 1] = (uint16_t)inc; C[r1] = (uint16_t)inc; }     // C[] reused: range ends by rank
+                if (lane == 0) cum[0] = 0;
+                for (uint32_t r = nU + 1 + lane; r < 52; r += 32) cum[r] = 0xFFFF;
+            }
+            __syncthreads();
+            {
+                // coarse[b] = first rank whose range reaches beyond slot 32*b (clamped to the last rank)
+                uint32_t nU = s_nU, slot = 32 * tid, r = 0;
+                while (r + 1 < nU && C[r] <= slot) r++;
+                row[tid] = (uint8_t)r;
             }
         } else {
             uint8_t *row_lut = lut + (size_t)s_ctx * 4096 * (o1 ? 1 : 0);
@@ -198,67 +213,44 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
 }
 
 // ---- the compressed stream of a group, staged in shared memory -----------------------------------------
-// ring[word index & (DEC_RING-1)][group]; all offsets are relative to the block start (16-byte aligned).
+// Byte ring of DEC_RINGB bytes per group, addressed by the byte offset inside the block (16-byte aligned), filled
+// by 4-byte cp.async.
+#define DEC_RINGB 512
 struct Stream {
     const uint8_t *base;      // block start in global memory
     uint32_t len4;            // block length rounded up to 4
     uint32_t wfetch;          // first word not yet requested
 };
 
-__device__ __forceinline__ void stream_fetch(Stream &s, uint32_t (*ring)[8], uint32_t g, uint32_t k, uint32_t cur)
+__device__ __forceinline__ void stream_fetch(Stream &s, uint8_t *ring, uint32_t k, uint32_t cur)
 {
-    // A chunk consumes at most DEC_CHUNK * 8 bytes = 32 words and its window reads 2 words further; what is
-    // requested now is only waited for at the start of the NEXT chunk, so stay 72 words ahead of the cursor.
+    // A chunk consumes at most DEC_CHUNK * 8 bytes = 32 words; what is requested now is only waited for at the
+    // start of the NEXT chunk, so stay 72 words ahead of the cursor (ring = 128 words).
     uint32_t tgt = ((cur >> 2) + 72 + 3) & ~3u;
     uint32_t lim = s.len4 >> 2;
     for (uint32_t w = s.wfetch + k; w < tgt; w += 4)       // the 4 lanes cover [wfetch, tgt) in strides of 4
-        if (w < lim) cp_async4(&ring[w & (DEC_RING - 1)][g], s.base + 4ull * w);
+        if (w < lim) cp_async4(ring + ((4 * w) & (DEC_RINGB - 1)), s.base + 4ull * w);
     if (tgt > s.wfetch) s.wfetch = tgt;
 }
-
-// 8 bytes of the stream starting at byte offset cur
-__device__ __forceinline__ unsigned long long stream_window(uint32_t (*ring)[8], uint32_t g, uint32_t cur)
+__device__ __forceinline__ uint32_t ring_le32(const uint8_t *ring, uint32_t pos)
 {
-    uint32_t w = cur >> 2, sh = (cur & 3) * 8;
-    uint32_t a = ring[w & (DEC_RING - 1)][g], b = ring[(w + 1) & (DEC_RING - 1)][g], c = ring[(w + 2) & (DEC_RING - 1)][g];
-    uint32_t lo = __funnelshift_r(a, b, sh), hi = __funnelshift_r(b, c, sh);
-    return ((unsigned long long)hi << 32) | lo;
+    return ring[pos & (DEC_RINGB - 1)] | (ring[(pos + 1) & (DEC_RINGB - 1)] << 8) | (ring[(pos + 2) & (DEC_RINGB - 1)] << 16) |
+           ((uint32_t)ring[(pos + 3) & (DEC_RINGB - 1)] << 24);
 }
 
-// Renormalise the 4 states of every group from the group's cursor, lanes in the order 0,1,2,3.
-// win = 8 stream bytes at the cursor.  Returns the new state and advances the cursor.
-__device__ __forceinline__ uint32_t renorm_win(uint32_t x, bool act, unsigned long long win, uint32_t &cur, uint32_t lane)
+// Renormalise the 4 states of every group from the group's cursor, lanes in the order 0,1,2,3
+// [Decoding.java:84-90].  lm / gm: ballot masks of the lower lanes of the group / of the group.
+__device__ __forceinline__ uint32_t renorm_ring(uint32_t x, bool act, const uint8_t *ring, uint32_t &cur, uint32_t lm, uint32_t gm)
 {
     bool n1 = act && x < RANS_L;
     bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
     uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1), b2 = __ballot_sync(0xFFFFFFFFu, n2);
-    uint32_t g4 = lane & ~3u, k = lane & 3u;
-    uint32_t gm = 0xFu << g4;
-    uint32_t lm = ((1u << k) - 1u) << g4;  // lower lanes of the group
-    uint32_t off = __popc(b1 & lm) + __popc(b2 & lm);
-    uint32_t v = (uint32_t)(win >> (8 * off));
-    if (n2) x = (x << 16) | ((v & 0xFF) << 8) | ((v >> 8) & 0xFF);
-    else if (n1) x = (x << 8) | (v & 0xFF);
+    uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
+    uint32_t v0 = ring[at & (DEC_RINGB - 1)], v1 = ring[(at + 1) & (DEC_RINGB - 1)];
+    uint32_t x1 = (x << 8) | v0;
+    x = n2 ? ((x1 << 8) | v1) : (n1 ? x1 : x);
     cur += __popc(b1 & gm) + __popc(b2 & gm);
     return x;
-}
-
-// number of the 8 sorted u16 in v that are <= m (all values < 2^15)
-__device__ __forceinline__ uint32_t count_le8(uint4 v, uint32_t m)
-{
-    uint32_t mm = (m + 1) * 0x00010001u;
-    const uint32_t K = 0x80008000u;
-    // bit 15 of each half survives iff half >= m+1, i.e. half > m
-    uint32_t t0 = ((v.x | K) - mm) & K, t1 = ((v.y | K) - mm) & K, t2 = ((v.z | K) - mm) & K, t3 = ((v.w | K) - mm) & K;
-    uint32_t gt = __popc(t0 | (t1 >> 1) | (t2 >> 2) | (t3 >> 3));
-    return 8 - gt;
-}
-// element e (0..7) of the 8 u16 in v
-__device__ __forceinline__ uint32_t elem8(uint4 v, uint32_t e)
-{
-    unsigned long long lo = ((unsigned long long)v.y << 32) | v.x, hi = ((unsigned long long)v.w << 32) | v.z;
-    unsigned long long h = (e & 4) ? hi : lo;
-    return (uint32_t)(h >> ((e & 3) * 16)) & 0xFFFFu;
 }
 
 // k_dec0: 1 warp per CTA, 8 blocks per warp; tables in shared memory.
@@ -269,8 +261,8 @@ __global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc,
                                              int32_t *__restrict__ status)
 {
     __shared__ __align__(16) uint8_t s_lut[8][4096];
-    __shared__ uint32_t s_fc[256][8];
-    __shared__ uint32_t ring[DEC_RING][8];
+    __shared__ uint32_t s_fc[8][256];
+    __shared__ __align__(16) uint8_t s_ring[8][DEC_RINGB];
     uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
     uint32_t slot = blockIdx.x * 8 + g;
     bool have = slot < nslots;
@@ -285,31 +277,32 @@ __global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc,
         const uint4 *src = reinterpret_cast<const uint4 *>(lut0 + (size_t)b * 4096);
         uint4 *dst = reinterpret_cast<uint4 *>(s_lut[gg]);
         for (uint32_t i = lane; i < 256; i += 32) dst[i] = __ldg(src + i);
-        for (uint32_t i = lane; i < 256; i += 32) s_fc[i][gg] = __ldg(fc0 + (size_t)b * 256 + i);
+        for (uint32_t i = lane; i < 256; i += 32) s_fc[gg][i] = __ldg(fc0 + (size_t)b * 256 + i);
     }
     Stream st;
     st.base = d_in + d.in_off;
     st.len4 = have ? (d.in_len + 3) & ~3u : 0;
     uint32_t cur = have ? meta[blk].pay_off : 0;
     st.wfetch = (cur >> 2) & ~3u;
-    stream_fetch(st, ring, g, k, cur);
+    uint8_t *ring = s_ring[g];
+    stream_fetch(st, ring, k, cur);
     cp_async_commit();
     cp_async_wait_all();
     __syncwarp();
-    uint32_t x = (uint32_t)(stream_window(ring, g, cur + 4 * k) & 0xFFFFFFFFu);
+    uint32_t x = ring_le32(ring, cur + 4 * k);
     cur += 16;
     bool under = false;
+    const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
 
     uint32_t steps = n >> 2;
     uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
     const uint8_t *lut = s_lut[g];
-    unsigned long long win = stream_window(ring, g, cur);
+    const uint32_t *fc = s_fc[g];
     for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
         cp_async_wait_all();
         __syncwarp();
-        stream_fetch(st, ring, g, k, cur);
+        stream_fetch(st, ring, k, cur);
         cp_async_commit();
-        win = stream_window(ring, g, cur);
 #pragma unroll 4
         for (uint32_t u = 0; u < DEC_CHUNK; u++) {
             uint32_t t = t0 + u;
@@ -317,12 +310,11 @@ __global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc,
             if (act) {
                 uint32_t m = x & (TOTFREQ - 1);
                 uint32_t s = lut[m];
-                uint32_t e = s_fc[s][g];
+                uint32_t e = fc[s];
                 out[(uint64_t)t * 4 + k] = (uint8_t)s;
                 x = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFF);                 // [Decoding.java:35-48]
             }
-            x = renorm_win(x, act, win, cur, lane);
-            win = stream_window(ring, g, cur);
+            x = renorm_ring(x, act, ring, cur, lm, gm);
         }
         if (cur > d.in_len) under = true;
     }
@@ -331,9 +323,9 @@ __global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc,
 }
 
 // k_dec1: lane k decodes the quarter starting at k*(n>>2); lane 3 also the remainder [D14.java:62-68].
-// Shared-memory path for blocks with <= 64 distinct bytes.  Dynamic shared memory:
-//   uint16_t rows[8][DEC_MAXU][DEC_ROW] | uint32_t ring[DEC_RING][8] | uint8_t ualpha[8][DEC_MAXU]
-#define DEC1_SMEM (8 * DEC_MAXU * DEC_ROW * 2 + DEC_RING * 8 * 4 + 8 * DEC_MAXU)
+// Shared-memory path for blocks with <= DEC_MAXU distinct bytes.  Dynamic shared memory:
+//   uint8_t rows[8][DEC_MAXU][DEC_ROWB] | uint8_t ring[8][DEC_RINGB] | uint8_t ualpha[8][DEC_MAXU]
+#define DEC1_SMEM (8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + 8 * DEC_MAXU)
 __global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
                                              const DecCompact *__restrict__ compact,
@@ -341,10 +333,6 @@ __global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc,
                                              int32_t *__restrict__ status)
 {
     extern __shared__ __align__(16) uint8_t smem[];
-    uint16_t (*rows)[DEC_MAXU][DEC_ROW] = reinterpret_cast<uint16_t (*)[DEC_MAXU][DEC_ROW]>(smem);
-    uint32_t (*ring)[8] = reinterpret_cast<uint32_t (*)[8]>(smem + 8 * DEC_MAXU * DEC_ROW * 2);
-    uint8_t (*ualpha)[DEC_MAXU] = reinterpret_cast<uint8_t (*)[DEC_MAXU]>(smem + 8 * DEC_MAXU * DEC_ROW * 2 + DEC_RING * 8 * 4);
-
     uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
     uint32_t slot = blockIdx.x * 8 + g;
     bool have = slot < nslots;
@@ -363,56 +351,57 @@ __global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc,
         if (!hv) continue;
         const DecCompact *cp = compact + oi;
         const uint4 *src = reinterpret_cast<const uint4 *>(&cp->rows[0][0]);
-        uint4 *dst = reinterpret_cast<uint4 *>(&rows[gg][0][0]);
-        for (uint32_t i = lane; i < DEC_MAXU * DEC_ROW * 2 / 16; i += 32) dst[i] = __ldg(src + i);
-        for (uint32_t i = lane; i < DEC_MAXU; i += 32) ualpha[gg][i] = cp->ualpha[i];
+        uint4 *dst = reinterpret_cast<uint4 *>(smem + gg * DEC_MAXU * DEC_ROWB);
+        for (uint32_t i = lane; i < DEC_MAXU * DEC_ROWB / 16; i += 32) dst[i] = __ldg(src + i);
+        for (uint32_t i = lane; i < DEC_MAXU; i += 32) smem[8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + gg * DEC_MAXU + i] = cp->ualpha[i];
     }
+    const uint8_t *rows = smem + g * DEC_MAXU * DEC_ROWB;
+    uint8_t *ring = smem + 8 * DEC_MAXU * DEC_ROWB + g * DEC_RINGB;
+    const uint8_t *alpha = smem + 8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + g * DEC_MAXU;
     Stream st;
     st.base = d_in + d.in_off;
     st.len4 = have ? (d.in_len + 3) & ~3u : 0;
     uint32_t cur = have ? meta[blk].pay_off : 0;
     st.wfetch = (cur >> 2) & ~3u;
-    stream_fetch(st, ring, g, k, cur);
+    stream_fetch(st, ring, k, cur);
     cp_async_commit();
     cp_async_wait_all();
     __syncwarp();
-    uint32_t x = (uint32_t)(stream_window(ring, g, cur + 4 * k) & 0xFFFFFFFFu);
+    uint32_t x = ring_le32(ring, cur + 4 * k);
     cur += 16;
     bool under = false;
+    const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
 
     uint32_t steps = n - 3 * q;
     uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    const uint16_t (*myrows)[DEC_ROW] = rows[g];
-    const uint8_t *myalpha = ualpha[g];
-    // context 0 is byte 0; its rank is 0 whenever the block has a context-0 row (it always does)
-    uint32_t ctx = 0;
-    uint4 l1v = *reinterpret_cast<const uint4 *>(&myrows[ctx][64]);
-    unsigned long long win = 0;
+    // context 0 is byte 0; it has rank 0 whenever the block has a context-0 row (the encoder always writes one)
+    const uint8_t *row = rows;
     for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
         cp_async_wait_all();
         __syncwarp();
-        stream_fetch(st, ring, g, k, cur);
+        stream_fetch(st, ring, k, cur);
         cp_async_commit();
-        win = stream_window(ring, g, cur);
 #pragma unroll 4
         for (uint32_t u = 0; u < DEC_CHUNK; u++) {
             uint32_t t = t0 + u;
             bool act = t < mylen;
             if (act) {
                 uint32_t m = x & (TOTFREQ - 1);
-                uint32_t grp = min(count_le8(l1v, m), 7u);
-                uint4 gv = *reinterpret_cast<const uint4 *>(&myrows[ctx][grp * 8]);
-                uint32_t cnt = min(count_le8(gv, m), 7u);
-                uint32_t s = grp * 8 + cnt;
-                uint32_t hi = elem8(gv, cnt);
-                uint32_t lo = cnt ? elem8(gv, cnt - 1) : (grp ? elem8(l1v, grp - 1) : 0);
-                ctx = s;
-                l1v = *reinterpret_cast<const uint4 *>(&myrows[ctx][64]);       // next step's first level, early
-                out[t] = myalpha[s];
-                x = (hi - lo) * (x >> TF_SHIFT) + m - lo;
+                uint32_t s = row[m >> 5];                                           // first candidate rank
+                const uint16_t *cum = reinterpret_cast<const uint16_t *>(row + 128) + s;
+                uint32_t c0 = cum[0], c1 = cum[1], c2 = cum[2], c3 = cum[3];        // start of s, ends of s, s+1, s+2
+                bool a1 = m >= c1, a2 = m >= c2, a3 = m >= c3;
+                uint32_t C = a3 ? c3 : a2 ? c2 : a1 ? c1 : c0;
+                uint32_t E = a3 ? 0u : a2 ? c3 : a1 ? c2 : c1;
+                s += (uint32_t)a1 + (uint32_t)a2 + (uint32_t)a3;
+                if (a3) {                                                           // rare: more than three short ranges in a row
+                    while (m >= (E = cum[(uint32_t)a1 + (uint32_t)a2 + (uint32_t)a3 + 1])) { C = E; s++; cum++; if (s + 1 >= DEC_MAXU) break; }
+                }
+                out[t] = alpha[s];
+                x = (E - C) * (x >> TF_SHIFT) + m - C;                               // [Decoding.java:35-48]
+                row = rows + s * DEC_ROWB;                                           // context of the next symbol
             }
-            x = renorm_win(x, act, win, cur, lane);
-            win = stream_window(ring, g, cur);
+            x = renorm_ring(x, act, ring, cur, lm, gm);
         }
         if (cur > d.in_len) under = true;
     }
@@ -509,7 +498,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
                        uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st)
 {
     if (nblocks == 0) return CRAMGPU_OK;
-    if (!d_in || !in_off || !in_len || !in_prefix || !d_out || !d_out_off || !d_out_len || !d_status)
+    if (!in_off || !in_len || !in_prefix || !d_out || !d_out_off || !d_out_len || !d_status)   // d_in may be NULL: absolute addresses in in_off
         return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
 
     std::vector<BlockDesc> desc(nblocks);

@@ -806,7 +806,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
                        uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st)
 {
     if (nblocks == 0) return CRAMGPU_OK;
-    if (!d_in || !in_off || !in_len || !order || !d_out_off || !d_out_len || !d_status)
+    if (!in_off || !in_len || !order || !d_out_off || !d_out_len || !d_status)   // d_in may be NULL: in_off then holds absolute device addresses
         return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
 
     // ---- plan (host): effective order, work areas, length-sorted slot lists

@@ -94,3 +94,52 @@ def rans_decode_dev(ctx, d_in, in_off, in_len, prefixes, out=None):
         ctypes.c_void_p(st.data_ptr()), _stream_ptr())
     ctx.check(rc)
     return DeviceBatchResult(out, off, ln[:n], st[:n])
+
+
+# ------------------------------------------------------------------------------------------- record-feature work
+
+def dev_to_numpy(ctx, ptr, n, dtype):
+    """copy n elements of `dtype` from a raw device pointer (a cramgpu_features field) to a numpy array"""
+    out = np.empty(int(n), dtype=dtype)
+    if out.size:
+        ctx.check(ctx.lib.cramgpu_copy_to_host(ctx.handle, ctypes.c_void_p(out.ctypes.data), ctypes.c_void_p(int(ptr)),
+                                               ctypes.c_uint64(out.nbytes), _stream_ptr()))
+    return out
+
+
+class DeviceReads(object):
+    """a batch of containers resident in HBM (torch tensors) + the small host tables the C ABI wants"""
+
+    def __init__(self, rd, ref, cont_off, device, ref_off=None, ref_len=None):
+        from . import records as rec
+        self.n = len(rd['pos'])
+        self.cont_off = np.ascontiguousarray(cont_off, np.uint64)
+        self.nc = self.cont_off.size - 1
+        ref = np.ascontiguousarray(ref, np.uint8)
+        self.ref_off = np.ascontiguousarray(np.zeros(self.nc) if ref_off is None else ref_off, np.uint64)
+        self.ref_len = np.ascontiguousarray(np.full(self.nc, ref.size) if ref_len is None else ref_len, np.uint64)
+        t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dt).view(np.uint8) if np.dtype(dt).itemsize > 1 else np.ascontiguousarray(a, dt)).to(device)
+        self.t = dict(ref=t(ref, np.uint8), bases=t(rd['bases'], np.uint8), quals=t(rd['quals'], np.uint8),
+                      read_off=t(rd['read_off'], np.uint64), cigar=t(rd['cigar'], np.uint32), cigar_off=t(rd['cigar_off'], np.uint64),
+                      pos=t(rd['pos'], np.int32), flag=t(rd['flag'], np.uint16), mapq=t(rd['mapq'], np.uint8))
+        R = rec.Reads()
+        R.n_reads = self.n; R.n_containers = self.nc
+        R.cont_off = self.cont_off.ctypes.data_as(_lib.u64p); R.ref_off = self.ref_off.ctypes.data_as(_lib.u64p)
+        R.ref_len = self.ref_len.ctypes.data_as(_lib.u64p); R.ref_total = ref.size
+        for k, v in self.t.items():
+            setattr(R, k, ctypes.c_void_p(v.data_ptr()))
+        R.rflags = None
+        self.struct = R
+
+
+def features_encode_dev(ctx, dreads, policies=None, n_policies=-1):
+    """cramgpu_features_encode_dev on torch's current stream.  Returns (cramgpu_features struct with DEVICE
+    pointers owned by ctx, stream_off, stream_len) -- the two tables as (n_containers, 12) numpy arrays."""
+    from . import records as rec
+    F = rec.Features()
+    soff = np.zeros((dreads.nc, 12), np.uint64)
+    slen = np.zeros((dreads.nc, 12), np.uint64)
+    rc = ctx.lib.cramgpu_features_encode_dev(ctx.handle, ctypes.byref(dreads.struct), policies, n_policies, ctypes.byref(F),
+                                             soff.ctypes.data_as(_lib.u64p), slen.ctypes.data_as(_lib.u64p), _stream_ptr())
+    ctx.check(rc)
+    return F, soff, slen

@@ -61,6 +61,11 @@ int cramgpu_sync(cramgpu_ctx *ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches claim). */
 uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx);
 
+/* Copy `bytes` from device memory (e.g. a result of a *_dev call) to host memory and wait for it.  `stream`:
+ * the stream the producing work was enqueued on (NULL = the context's own).  Convenience for shims that own no
+ * CUDA binding of their own; no Java counterpart. */
+int cramgpu_copy_to_host(cramgpu_ctx *ctx, void *dst_host, const void *src_dev, uint64_t bytes, void *stream);
+
 /*
  * Per-kernel device timing, the CUDA-event counterpart of the reference's System.nanoTime() stage
  * counters (Cram2Bam.java:172-178,291-294; Container.buildHeaderTime/buildSlicesTime).  While enabled,
@@ -120,7 +125,9 @@ int cramgpu_rans_decode_batch(cramgpu_ctx *ctx, uint32_t nblocks,
 /*
  * Device-resident variants.  Same results, but data stay in HBM.
  *   d_in            device buffer holding all blocks; block i is d_in[in_off[i] .. +in_len[i]);
- *                   in_off[i] must be a multiple of 16
+ *                   in_off[i] must be a multiple of 16.  d_in may be NULL, in which case in_off[i] are absolute
+ *                   device addresses (blocks scattered over several buffers); every block must be followed by
+ *                   at least 3 readable bytes (the coders fetch whole 4-byte words)
  *   in_off/in_len/order   HOST arrays (the Java host knows every block length)
  *   d_out           device buffer of out_cap bytes; compressed/decoded blocks are packed into it
  *                   back to back, each starting at a multiple of 16

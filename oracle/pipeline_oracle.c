@@ -1,0 +1,170 @@
+/*
+ * oracle/pipeline_oracle.c -- TEST INFRASTRUCTURE ONLY.
+ *
+ * CPU driver that strings the restated reference functions together the way the reference's own
+ * multi-threaded converter does (one container per pool thread, paralell/BamToCram_OBA_Function.java:51-94
+ * and paralell/CramToBam_OBA_Function.java:53-84): per container
+ *   encode: feature extraction + substitution matrix + quality preservation + series packing,
+ *           then rANS of QS / BA (order 1) and of the caller's extra series (BF, CF, RL, ... as given)
+ *   decode: rANS decode of the same blocks, then base and quality restoration of every record.
+ * bench.py times this as the CPU baseline / `--impl reference` arm (there is no JVM in the image).
+ */
+#include <pthread.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct {
+    int64_t n_feat; uint8_t *f_op; int32_t *f_pos, *f_val, *f_aux; int64_t *feat_off;
+    uint8_t *payload; int64_t payload_len;
+    int64_t subst_counts[5][5];
+    uint8_t matrix[5];
+} rec_features_t;
+typedef struct { int32_t read_cat, read_param, n_base_cats, base_cat[8], treatment, treat_param; } qs_policy_t;
+
+int rec_oracle_extract(int64_t, const uint8_t *, const int64_t *, const uint32_t *, const int64_t *, const int32_t *,
+                       const uint16_t *, const uint8_t *, int64_t, rec_features_t *);
+void rec_oracle_free(rec_features_t *);
+int rec_oracle_quality(const uint8_t *, const uint8_t *, int64_t, int, const uint32_t *, int64_t, int32_t, uint16_t, uint8_t,
+                       const uint8_t *, int64_t, const qs_policy_t *, int, uint8_t *);
+void rec_oracle_write_streams(int64_t, const uint8_t *, const int64_t *, const uint16_t *, const uint8_t *, const int32_t *,
+                              const rec_features_t *, const uint8_t *, const uint8_t *, uint8_t **, int64_t *);
+int rec_oracle_restore_bases(int32_t, int64_t, int64_t, const uint8_t *, const int32_t *, const int32_t *, const int32_t *,
+                             const uint8_t *, const uint8_t *, int64_t, int64_t, const uint8_t *, uint8_t *);
+int rec_oracle_restore_quals(int, int64_t, int64_t, const uint8_t *, const int32_t *, const int32_t *, const int32_t *, uint8_t *);
+int rec_oracle_parse_policies(const char *, qs_policy_t *, int);
+uint32_t rans_oracle_bound(uint32_t);
+int rans_oracle_compress(const uint8_t *, uint32_t, int, uint8_t *, uint32_t, uint32_t *);
+int rans_oracle_uncompress(const uint8_t *, uint32_t, uint8_t *, uint32_t, uint32_t *);
+
+enum { S_FN = 0, S_FC, S_FP, S_BS, S_DL, S_BA, S_SC, S_QS, S_RS, S_HC, S_PD, S_MQ, S_COUNT };
+
+typedef struct {
+    /* one container */
+    int64_t n_reads;
+    const uint8_t *bases, *quals; const int64_t *read_off;       /* read_off relative to bases */
+    const uint32_t *cigar; const int64_t *cigar_off;
+    const int32_t *pos; const uint16_t *flag; const uint8_t *mapq;
+    const uint8_t *ref; int64_t ref_len;
+    int n_extra; const uint8_t *const *extra; const uint32_t *extra_len; const uint8_t *extra_order;
+    const qs_policy_t *pol; int n_pol;
+    /* results */
+    uint64_t checksum; int64_t comp_bytes; int rc;
+} container_job_t;
+
+static void run_container(container_job_t *j)
+{
+    const int64_t n = j->n_reads;
+    const int64_t total = j->read_off[n] - j->read_off[0];
+    rec_features_t ft;
+    j->rc = rec_oracle_extract(n, j->bases, j->read_off, j->cigar, j->cigar_off, j->pos, j->flag, j->ref, j->ref_len, &ft);
+    if (j->rc) return;
+    uint8_t *force = malloc((size_t)n + 1), *scores = malloc((size_t)total + 16);
+    memset(scores, 0xFF, (size_t)total + 16);
+    uint8_t *sc0 = scores - j->read_off[0];          /* indexable by the absolute read offsets */
+    for (int64_t r = 0; r < n; r++) {
+        int64_t lo = j->read_off[r], len = j->read_off[r + 1] - lo;
+        force[r] = (uint8_t)rec_oracle_quality(j->bases + lo, j->quals + lo, len, 1, j->cigar + j->cigar_off[r],
+                                               j->cigar_off[r + 1] - j->cigar_off[r], j->pos[r], j->flag[r], j->mapq[r],
+                                               j->ref, j->ref_len, j->pol, j->n_pol, sc0 + lo);
+    }
+    int64_t cap = 3 * total + 16 * ft.n_feat + 16 * n + 64;
+    uint8_t *streams[S_COUNT]; int64_t lens[S_COUNT];
+    for (int k = 0; k < S_COUNT; k++) streams[k] = malloc((size_t)cap);
+    rec_oracle_write_streams(n, j->bases, j->read_off, j->flag, j->mapq, j->pos, &ft, force, sc0, streams, lens);
+
+    /* block codec: QS, BA order 1, then the caller's series */
+    int nblk = 2 + j->n_extra;
+    const uint8_t **in = malloc(sizeof(*in) * (size_t)nblk); uint32_t *ilen = malloc(4 * (size_t)nblk); int *ord = malloc(sizeof(int) * (size_t)nblk);
+    in[0] = streams[S_QS]; ilen[0] = (uint32_t)lens[S_QS]; ord[0] = 1;
+    in[1] = streams[S_BA]; ilen[1] = (uint32_t)lens[S_BA]; ord[1] = 1;
+    for (int e = 0; e < j->n_extra; e++) { in[2 + e] = j->extra[e]; ilen[2 + e] = j->extra_len[e]; ord[2 + e] = j->extra_order[e]; }
+    uint64_t sum = 0;
+    uint8_t *qs_back = NULL;
+    for (int b = 0; b < nblk; b++) {
+        uint32_t capb = rans_oracle_bound(ilen[b]), clen = 0, rlen = 0;
+        uint8_t *comp = malloc(capb), *back = malloc(ilen[b] + 16);
+        j->rc |= rans_oracle_compress(in[b], ilen[b], ord[b], comp, capb, &clen);
+        j->rc |= rans_oracle_uncompress(comp, clen, back, ilen[b] + 16, &rlen);
+        if (rlen != ilen[b] || memcmp(back, in[b], ilen[b])) j->rc |= 1;
+        j->comp_bytes += clen;
+        for (uint32_t i = 0; i < clen; i += 97) sum += comp[i];
+        free(comp);
+        if (b == 0) qs_back = back; else free(back);
+    }
+    /* decode: restore every record from the reference window [min start, max end] (CramNormalizer.java:212-225) */
+    int64_t wmin = -1, wmax = 0;
+    for (int64_t r = 0; r < n; r++) {
+        if ((j->flag[r] & 4) || j->pos[r] <= 0) continue;
+        int64_t s = j->pos[r] - 1, e = s + (j->read_off[r + 1] - j->read_off[r]) + 64;
+        if (wmin < 0 || s < wmin) wmin = s;
+        if (e > wmax) wmax = e;
+    }
+    if (wmin < 0) wmin = 0;
+    if (wmax > j->ref_len) wmax = j->ref_len;
+    uint8_t *ob = malloc((size_t)total + 16), *oq = malloc((size_t)total + 16);
+    int64_t qcur = 0;     /* walk the decoded QS stream in record order */
+    for (int64_t r = 0; r < n; r++) {
+        int64_t lo = j->read_off[r] - j->read_off[0], len = j->read_off[r + 1] - j->read_off[r];
+        int64_t a = ft.feat_off[r], nf = ft.feat_off[r + 1] - a;
+        if (!(j->flag[r] & 4))
+            j->rc |= rec_oracle_restore_bases(j->pos[r], len, nf, ft.f_op + a, ft.f_pos + a, ft.f_val + a, ft.f_aux + a, ft.payload,
+                                              j->ref + wmin, wmax - wmin, wmin, ft.matrix, ob + lo) ? 2 : 0;
+        else memcpy(ob + lo, j->bases + j->read_off[r], (size_t)len);
+        if (force[r] & 1) { memcpy(oq + lo, qs_back + qcur, (size_t)len); qcur += len; }
+        rec_oracle_restore_quals(force[r] & 1, len, nf, ft.f_op + a, ft.f_pos + a, ft.f_val + a, ft.f_aux + a, oq + lo);
+    }
+    for (int64_t i = 0; i < total; i += 61) sum += ob[i] + 3 * oq[i];
+    if (j->n_pol < 0 && (memcmp(ob, j->bases + j->read_off[0], (size_t)total) || memcmp(oq, j->quals + j->read_off[0], (size_t)total))) j->rc |= 4;
+    j->checksum = sum;
+    free(ob); free(oq); free(qs_back); free(in); free(ilen); free(ord);
+    for (int k = 0; k < S_COUNT; k++) free(streams[k]);
+    free(force); free(scores);
+    rec_oracle_free(&ft);
+}
+
+typedef struct { container_job_t *jobs; int n, tid, nthreads; } worker_t;
+static void *worker(void *a)
+{
+    worker_t *w = a;
+    for (int i = w->tid; i < w->n; i += w->nthreads) run_container(&w->jobs[i]);
+    return NULL;
+}
+
+/*
+ * Containers share the flat read arrays: container c holds reads cont_off[c] .. cont_off[c+1]-1.
+ * extra[c * n_extra + e] are the caller's already packed series of container c.
+ * Returns 0 when every container round-tripped; *comp_bytes and *checksum accumulate.
+ */
+int oracle_cram_step(int nthreads, int n_cont, const int64_t *cont_off, const uint8_t *bases, const uint8_t *quals,
+                     const int64_t *read_off, const uint32_t *cigar, const int64_t *cigar_off, const int32_t *pos,
+                     const uint16_t *flag, const uint8_t *mapq, const uint8_t *ref, int64_t ref_len, int n_extra,
+                     const uint8_t *const *extra, const uint32_t *extra_len, const uint8_t *extra_order, const char *spec,
+                     int64_t *comp_bytes, uint64_t *checksum)
+{
+    qs_policy_t pol[16];
+    int n_pol = -1;
+    if (spec && spec[0] && strcmp(spec, "lossless")) { n_pol = rec_oracle_parse_policies(spec, pol, 16); if (n_pol < 0) return -100; }
+    container_job_t *jobs = calloc((size_t)n_cont, sizeof *jobs);
+    for (int c = 0; c < n_cont; c++) {
+        container_job_t *j = &jobs[c];
+        int64_t a = cont_off[c];
+        j->n_reads = cont_off[c + 1] - a;
+        j->bases = bases; j->quals = quals; j->read_off = read_off + a;
+        j->cigar = cigar; j->cigar_off = cigar_off + a; j->pos = pos + a; j->flag = flag + a; j->mapq = mapq + a;
+        j->ref = ref; j->ref_len = ref_len;
+        j->n_extra = n_extra; j->extra = extra + (size_t)c * n_extra; j->extra_len = extra_len + (size_t)c * n_extra;
+        j->extra_order = extra_order;
+        j->pol = pol; j->n_pol = n_pol;
+    }
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    pthread_t th[256]; worker_t w[256];
+    for (int t = 0; t < nthreads; t++) { w[t] = (worker_t){jobs, n_cont, t, nthreads}; pthread_create(&th[t], NULL, worker, &w[t]); }
+    for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+    int rc = 0;
+    *comp_bytes = 0; *checksum = 0;
+    for (int c = 0; c < n_cont; c++) { rc |= jobs[c].rc; *comp_bytes += jobs[c].comp_bytes; *checksum += jobs[c].checksum; }
+    free(jobs);
+    return rc;
+}

@@ -10,7 +10,7 @@ _SO = os.path.join(_HERE, '_build', 'liboracle.so')
 
 
 def build(force=False):
-    srcs = [os.path.join(_HERE, f) for f in ('rans_oracle.c', 'records_oracle.c', 'Makefile')]
+    srcs = [os.path.join(_HERE, f) for f in ('rans_oracle.c', 'records_oracle.c', 'pipeline_oracle.c', 'Makefile')]
     if force or not os.path.exists(_SO) or any(
             os.path.exists(s) and os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
         subprocess.check_call(['make', '-s', '-C', _HERE] + (['-B'] if force else []))
