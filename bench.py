@@ -251,6 +251,10 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     dev = torch.device('cuda', local)
+    # everything (torch ops and the library's kernels) runs on ONE explicit stream; the events that time the step are
+    # recorded on it.  (torch's default stream has handle 0, which the C ABI reads as "use the context's own stream".)
+    work_stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(work_stream)
     ctx = cramtools_b200.Context(local)
     peaks, peak_kind = measured_peaks()
     vp = C.c_void_p
@@ -462,13 +466,28 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
     from cramtools_b200._lib import u8p, u32p, u64p, i32p, u8pp
     import torch
     vp = C.c_void_p
+    keep_pinned = []
+
+    def pinned(x):
+        # page-locked host arrays, as the contract asks ("inputs from pinned host memory"); the library sends them to the DMA engine as they are
+        t = torch.empty(x.nbytes, dtype=torch.uint8, pin_memory=True)
+        keep_pinned.append(t)
+        out = t.numpy().view(x.dtype).reshape(x.shape)
+        out[...] = x
+        return out
+
+    def pinned_empty(n, dt):
+        t = torch.empty(int(n) * np.dtype(dt).itemsize, dtype=torch.uint8, pin_memory=True)
+        keep_pinned.append(t)
+        return t.numpy().view(dt)
     trd = tile_reads(rd, nu, n_cont)
     n_reads = n_cont * READS_PER_CONTAINER
+    ref = pinned(ref)
     cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
     ref_off = np.zeros(n_cont, np.uint64); ref_len = np.full(n_cont, ref.size, np.uint64)
-    a = dict(bases=trd['bases'], quals=trd['quals'], read_off=trd['read_off'].astype(np.uint64), cigar=trd['cigar'].astype(np.uint32),
-             cigar_off=trd['cigar_off'].astype(np.uint64), pos=trd['pos'].astype(np.int32), flag=trd['flag'].astype(np.uint16),
-             mapq=trd['mapq'].astype(np.uint8))
+    a = dict(bases=pinned(trd['bases']), quals=pinned(trd['quals']), read_off=pinned(trd['read_off'].astype(np.uint64)),
+             cigar=pinned(trd['cigar'].astype(np.uint32)), cigar_off=pinned(trd['cigar_off'].astype(np.uint64)),
+             pos=pinned(trd['pos'].astype(np.int32)), flag=pinned(trd['flag'].astype(np.uint16)), mapq=pinned(trd['mapq'].astype(np.uint8)))
     R = rec.Reads()
     R.n_reads = n_reads; R.n_containers = n_cont
     R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
@@ -488,10 +507,10 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
     cap_qs = rans_bound(READS_PER_CONTAINER * READ_LEN)
     caps = np.tile(np.array([cap_qs] + [rans_bound(60000)] * (NB - 1), np.uint32), n_cont)
     cap_off = np.concatenate([[0], np.cumsum(caps.astype(np.int64))])
-    comp = np.empty(int(cap_off[-1]), np.uint8)
+    comp = pinned_empty(cap_off[-1], np.uint8)
     out_ptr = (np.uint64(comp.ctypes.data) + cap_off[:-1].astype(np.uint64))
     out_len = np.zeros(nblk, np.uint32); status = np.zeros(nblk, np.int32)
-    back = np.empty(int(cap_off[-1]), np.uint8)                     # decoded series, same slots
+    back = pinned_empty(cap_off[-1], np.uint8)                      # decoded series, same slots
     back_ptr = (np.uint64(back.ctypes.data) + cap_off[:-1].astype(np.uint64))
     back_len = np.zeros(nblk, np.uint32)
     p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
@@ -500,7 +519,8 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
     win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
     win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
     rfl = np.ones(n_reads, np.uint8)
-    o_b = np.empty(n_reads * READ_LEN, np.uint8); o_q = np.empty_like(o_b); o_s = np.empty(n_reads, np.uint8); o_t = np.empty(n_reads, np.int32)
+    o_b = pinned_empty(n_reads * READ_LEN, np.uint8); o_q = pinned_empty(n_reads * READ_LEN, np.uint8)
+    o_s = np.empty(n_reads, np.uint8); o_t = np.empty(n_reads, np.int32)
     cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
     rba = np.full(n_reads, 0xFFFFFFFFFFFFFFFF, np.uint64)
     N = rec.NormIn()
@@ -563,7 +583,7 @@ def main():
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
-    ap.add_argument('--e2e-containers', type=int, default=512, help='containers per GPU of the end-to-end (host buffer) leg')
+    ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

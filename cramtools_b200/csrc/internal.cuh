@@ -5,6 +5,7 @@
 #include <stddef.h>
 #include <string>
 #include <vector>
+#include <algorithm>
 
 #include "../../include/cramgpu.h"
 
@@ -67,6 +68,7 @@ struct cramgpu_ctx {
     DevPool dev_in, dev_out;  // device staging of the host entry points
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
     void *pin_rec = nullptr; size_t pin_rec_cap = 0;
+    void *pin_feat = nullptr; size_t pin_feat_cap = 0;   // host copy of the last cramgpu_features_encode result
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
     size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
     cudaEvent_t ev = nullptr;
@@ -110,6 +112,10 @@ struct Carver {
         return o;
     }
 };
+
+struct CopyJob { void *dst; const void *src; size_t n; };
+void par_memcpy(std::vector<CopyJob> &jobs);      // multi-threaded staging copies (clears the list)
+bool host_is_pinned(const void *p);               // page-locked host memory known to CUDA?
 
 // rans.cu
 int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,

@@ -851,6 +851,23 @@ extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads
 struct Stager {
     std::vector<const void *> src; std::vector<size_t> bytes, off; size_t total = 0;
     size_t add(const void *p, size_t b) { off.push_back(total); src.push_back(p); bytes.push_back(b); total += rup(b ? b : 1, 256); return off.back(); }
+    // H2D of the first `count` entries: arrays in caller-pinned memory go directly, the others through `pin`
+    int to_device(cramgpu_ctx *ctx, uint8_t *pin, uint8_t *D, size_t count, cudaStream_t st)
+    {
+        std::vector<CopyJob> jobs;
+        std::vector<uint8_t> direct(count, 0);
+        for (size_t k = 0; k < count; k++) {
+            if (!bytes[k] || !src[k]) continue;
+            if (bytes[k] >= (64u << 10) && host_is_pinned(src[k])) direct[k] = 1;
+            else jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]});
+        }
+        par_memcpy(jobs);
+        for (size_t k = 0; k < count; k++) {
+            if (!bytes[k] || !src[k]) continue;
+            CUDA_TRY(ctx, cudaMemcpyAsync(D + off[k], direct[k] ? src[k] : (const void *)(pin + off[k]), bytes[k], cudaMemcpyHostToDevice, st));
+        }
+        return CRAMGPU_OK;
+    }
 };
 
 extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies,
@@ -875,8 +892,7 @@ extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R,
     if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
-    for (size_t k = 0; k < sg.src.size(); k++) if (sg.bytes[k]) memcpy(pin + sg.off[k], sg.src[k], sg.bytes[k]);
-    CUDA_TRY(ctx, cudaMemcpyAsync(D, pin, sg.total, cudaMemcpyHostToDevice, st));
+    if (int rc = sg.to_device(ctx, pin, D, sg.src.size(), st)) return rc;
     cramgpu_reads dev = *R;
     dev.ref = D + i_ref; dev.bases = D + i_bases; dev.quals = D + i_quals; dev.read_off = (const uint64_t *)(D + i_roff);
     dev.cigar = (const uint32_t *)(D + i_cig); dev.cigar_off = (const uint64_t *)(D + i_coff); dev.pos = (const int32_t *)(D + i_pos);
@@ -892,8 +908,10 @@ extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R,
     size_t r_force = so.add(df.force_qs, n), r_mtx = so.add(df.matrix, 8 * (size_t)nc), r_str = so.add(df.streams, df.streams_len);
     size_t r_soff = so.add(df.stream_off, tab), r_slen = so.add(df.stream_len, tab);
     size_t r_qso = so.add(df.read_qs_off, 8 * n), r_bao = so.add(df.read_ba_off, 8 * n);
-    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, so.total)) return rc;
-    uint8_t *po = (uint8_t *)ctx->pin_out;
+    // results get a pinned buffer of their own: they must survive the following block-codec / normaliser calls,
+    // which recycle pin_in / pin_out
+    if (int rc = pinned_reserve(ctx, &ctx->pin_feat, &ctx->pin_feat_cap, so.total)) return rc;
+    uint8_t *po = (uint8_t *)ctx->pin_feat;
     for (size_t k = 0; k < so.src.size(); k++)
         if (so.bytes[k]) CUDA_TRY(ctx, cudaMemcpyAsync(po + so.off[k], so.src[k], so.bytes[k], cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -987,8 +1005,7 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
-    for (size_t k = 0; k < sg.src.size(); k++) if (sg.bytes[k] && sg.src[k]) memcpy(pin + sg.off[k], sg.src[k], sg.bytes[k]);
-    CUDA_TRY(ctx, cudaMemcpyAsync(D, pin, o_bases, cudaMemcpyHostToDevice, st));
+    if (int rc = sg.to_device(ctx, pin, D, sg.src.size(), st)) return rc;
     // records without a stored array / BA bases still need valid offset tables
     if (!in->read_qs_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_qso, 0xFF, 8 * n, st));
     if (!in->read_ba_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_bao, 0xFF, 8 * n, st));
@@ -1001,12 +1018,18 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256))) return rc;
     uint8_t *po = (uint8_t *)ctx->pin_out;
     size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256);
-    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(po, D + o_bases, nb, cudaMemcpyDeviceToHost, st));
-    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(po + p_q, D + o_quals, nb, cudaMemcpyDeviceToHost, st));
+    const bool pb = nb && host_is_pinned(bases), pq = nb && host_is_pinned(quals);
+    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(pb ? bases : po, D + o_bases, nb, cudaMemcpyDeviceToHost, st));
+    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(pq ? quals : po + p_q, D + o_quals, nb, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, D + o_star, n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(po + p_t, D + o_stat, 4 * n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
-    if (nb) { memcpy(bases, po, nb); memcpy(quals, po + p_q, nb); }
+    {
+        std::vector<CopyJob> jobs;
+        if (nb && !pb) jobs.push_back(CopyJob{bases, po, (size_t)nb});
+        if (nb && !pq) jobs.push_back(CopyJob{quals, po + p_q, (size_t)nb});
+        par_memcpy(jobs);
+    }
     memcpy(qual_star, po + p_s, n);
     memcpy(status, po + p_t, 4 * n);
     for (uint64_t r = 0; r < n; r++)

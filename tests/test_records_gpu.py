@@ -180,3 +180,21 @@ def test_empty_batch(R, gpu_ctx):
               cigar_off=np.zeros(1, np.uint64), pos=np.zeros(0, np.int32), flag=np.zeros(0, np.uint16), mapq=np.zeros(0, np.uint8))
     enc = R.features_encode(rd, b'ACGT', None, cont_off=[0, 0], ctx=gpu_ctx)
     assert enc.n_feat == 0
+
+
+def test_host_chain_features_then_block_codec(R, gpu_ctx):
+    """the call sequence of the Java host: convert() -> compress() of the QS/BA series -> uncompress() -> normalize();
+    results of the first call must survive the later ones (they live in context-owned pinned memory)"""
+    from cramtools_b200 import ExternalCompression as EC
+    from oracle import rans as orans
+    ref, rd, cont_off = _sim(4000, 2, 31)
+    enc = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    series = [enc.series(c, nm) for c in range(2) for nm in ('QS', 'BA')]
+    blobs = EC.rans_batch(series, [1] * len(series), gpu_ctx)
+    for s_, b in zip(series, blobs):
+        assert b == orans.compress(s_, 1)
+    back = EC.unrans_batch(blobs, gpu_ctx)
+    assert back == series
+    # the first call's results are still intact after the other calls reused the staging buffers
+    enc2 = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    assert enc2.streams.tobytes() == enc.streams.tobytes()
