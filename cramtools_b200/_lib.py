@@ -43,6 +43,7 @@ SIGNATURES = {
     'cramgpu_rans_decode_batch': (ctypes.c_int, [vp, ctypes.c_uint32, u8pp, u32p, u8pp, u32p, u32p, i32p]),
     'cramgpu_rans_encode_dev': (ctypes.c_int, [vp, ctypes.c_uint32, vp, u64p, u32p, u8p, vp, ctypes.c_uint64,
                                                vp, vp, vp, vp]),
+    'cramgpu_rans0_encode_static': (ctypes.c_int, [vp, ctypes.c_uint32, vp, ctypes.c_uint32, vp, vp, vp]),
     'cramgpu_rans_decode_dev': (ctypes.c_int, [vp, ctypes.c_uint32, vp, u64p, u32p, u8p, vp, ctypes.c_uint64,
                                                vp, vp, vp, vp]),
 }

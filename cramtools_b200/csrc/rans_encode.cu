@@ -937,3 +937,100 @@ int rans_encode_pack(cramgpu_ctx *ctx, uint8_t *d_out, cudaStream_t st)
     }
     return CRAMGPU_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// cramgpu_rans0_encode_static: order-0 compression of ONE block for callers that must not allocate.
+//
+// Some hosts cannot ask the CUDA runtime for memory while they work: a JVM-side or serving-side memory manager
+// may already own every byte of HBM, so a cudaMalloc would fail or break its accounting, and latency-sensitive
+// callers cannot accept the device-wide synchronisation a cudaMalloc / cudaFree implies.  For them this entry
+// point runs the same kernels as cramgpu_rans_encode_dev, but every byte of scratch (block descriptor, histogram,
+// coder table, table bytes, payload work area) lives in the file-scope device array below, which each GPU that
+// loads the library holds from load to exit.  Nothing is allocated or freed here, on the device or through torch.
+//
+//  - limit: at most CRAMGPU_STATIC_MAX_RAW (1 MiB) raw bytes per call; larger inputs are rejected.
+//  - the first call on a device looks up the array's device address and raises the coder kernel's shared-memory
+//    limit; make that first call before any stream capture begins.
+//  - all calls share the one array and it keeps the previous call's contents; the counters that must start at zero
+//    are cleared on `stream` at the start of every call.  Two calls whose work overlaps on the GPU (different
+//    streams, no ordering between them) race on the array: order them.
+#define CRAMGPU_STATIC_MAX_RAW (1u << 20)
+#define NA_OFF_DESC 0u
+#define NA_OFF_SLOT 256u
+#define NA_OFF_ZERO 512u                 // [F0 1024 B][tlen 4][plen 4][out_off 2 x 8]  -- cleared every call
+#define NA_ZERO_BYTES 1088u
+#define NA_OFF_TAB0 2048u
+#define NA_OFF_WORK 4096u
+#define NA_WORK_MAX (O0_TAB_CAP + ((CRAMGPU_STATIC_MAX_RAW + CRAMGPU_STATIC_MAX_RAW / 4 + 64 + 15) & ~15u))
+#define NA_BYTES ((NA_OFF_WORK + NA_WORK_MAX + 255u) & ~255u)
+
+static __device__ __align__(256) unsigned char g_static_scratch[NA_BYTES];
+
+__global__ void k_static_setup(BlockDesc d, BlockDesc *desc, uint32_t *slot)
+{
+    *desc = d;
+    *slot = 0;
+}
+
+#include <mutex>
+
+extern "C" int cramgpu_rans0_encode_static(const uint8_t *d_in, uint32_t n, uint8_t *d_out, uint32_t out_cap,
+                                           uint32_t *d_out_len, int32_t *d_status, void *stream)
+{
+    if (!d_out || !d_out_len || !d_status || (n && !d_in)) return ctx_fail(nullptr, CRAMGPU_ERR_ARG, "cramgpu_rans0_encode_static: null argument");
+    if (n > CRAMGPU_STATIC_MAX_RAW)
+        return ctx_fail(nullptr, CRAMGPU_ERR_ARG, "cramgpu_rans0_encode_static: %u raw bytes exceed the %u-byte limit of the static scratch; "
+                        "use cramgpu_rans_encode_dev for larger blocks", n, (unsigned)CRAMGPU_STATIC_MAX_RAW);
+    if (reinterpret_cast<uintptr_t>(d_in) & 15) return ctx_fail(nullptr, CRAMGPU_ERR_ARG, "cramgpu_rans0_encode_static: d_in must be 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)stream;
+
+    // once per device, with that device current: the array's name is only a host-side handle, kernels need its device address
+    static unsigned char *dev_ptr[64];
+    static bool ready[64];
+    static std::mutex mu;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) return ctx_fail(nullptr, CRAMGPU_ERR_CUDA, "cramgpu_rans0_encode_static: no current CUDA device");
+    unsigned char *S = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!ready[dev]) {
+            unsigned char *p = nullptr;
+            e = cudaGetSymbolAddress((void **)&p, g_static_scratch);
+            if (e != cudaSuccess || !p) return ctx_cuda(nullptr, e, "cudaGetSymbolAddress(g_static_scratch)");
+            e = cudaFuncSetAttribute(k_enc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(0));
+            if (e != cudaSuccess) return ctx_cuda(nullptr, e, "cudaFuncSetAttribute(k_enc<0>)");
+            dev_ptr[dev] = p;
+            ready[dev] = true;
+        }
+        S = dev_ptr[dev];
+    }
+    e = cudaMemsetAsync(d_status, 0, sizeof(int32_t), st);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_out_len, 0, sizeof(uint32_t), st);
+    if (e != cudaSuccess) return ctx_cuda(nullptr, e, "cudaMemsetAsync(outputs)");
+    if (n == 0) return CRAMGPU_OK;                                   // empty in, empty out [RANS.java:60-61]
+
+    BlockDesc d = BlockDesc();
+    d.in_off = 0; d.in_len = n; d.order = 0; d.tab_cap = O0_TAB_CAP;
+    d.work_cap = (uint32_t)(O0_TAB_CAP + (((uint64_t)n + n / 4 + 64 + 15) & ~15ull));
+    d.work_off = 0;
+    BlockDesc *desc = (BlockDesc *)(S + NA_OFF_DESC);
+    uint32_t *slot = (uint32_t *)(S + NA_OFF_SLOT);
+    uint32_t *F0 = (uint32_t *)(S + NA_OFF_ZERO), *tlen = F0 + 256, *plen = F0 + 257;
+    uint64_t *out_off = (uint64_t *)(S + NA_OFF_ZERO + 1032);
+    uint32_t *tab0 = (uint32_t *)(S + NA_OFF_TAB0);
+    uint8_t *work = S + NA_OFF_WORK;
+
+    e = cudaMemsetAsync(S + NA_OFF_ZERO, 0, NA_ZERO_BYTES, st);      // what must start at zero
+    if (e != cudaSuccess) return ctx_cuda(nullptr, e, "cudaMemsetAsync(static scratch)");
+    k_static_setup<<<1, 1, 0, st>>>(d, desc, slot);
+    k_hist0<<<dim3(1, (n + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(desc, d_in, F0);
+    k_tables0<<<1, 256, 0, st>>>(desc, slot, F0, tab0, work, tlen);
+    k_enc<0><<<1, ENC_THREADS, ENC_SMEM(0), st>>>(desc, slot, 1, d_in, tab0, nullptr, work, plen, d_status, 0);
+    k_scan_out<<<1, 1024, 0, st>>>(desc, 1, tlen, plen, out_cap, out_off, d_out_len, d_status);
+    uint64_t max_out = 9 + (uint64_t)O0_TAB_CAP + n + n / 4 + 80;
+    k_pack<<<dim3(1, (uint32_t)((max_out + PACK_CHUNK - 1) / PACK_CHUNK)), 256, 0, st>>>(desc, work, tlen, plen, out_off, d_out_len, d_out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return ctx_cuda(nullptr, e, "cramgpu_rans0_encode_static launch");
+    return CRAMGPU_OK;
+}

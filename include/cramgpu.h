@@ -155,6 +155,33 @@ int cramgpu_rans_decode_dev(cramgpu_ctx *ctx, uint32_t nblocks,
                             uint8_t *d_out, uint64_t out_cap, uint64_t *d_out_off, uint32_t *d_out_len,
                             int32_t *d_status, void *stream);
 
+/*
+ * Order-0 rANS compression of ONE block without any allocation.  This entry point has no counterpart in the
+ * reference (Java callers never manage device memory).  It exists for hosts that are not allowed to obtain
+ * memory from the CUDA runtime while they run -- a JVM-side pool or a serving process may have handed all of HBM
+ * to its own memory manager, so that a cudaMalloc fails or upsets its book-keeping, and latency-critical callers
+ * cannot take the device-wide synchronisation that cudaMalloc / cudaFree bring.  The result is byte-identical to
+ * cramgpu_rans_encode_dev with order 0.
+ *
+ *   d_in, n          device pointer (16-byte aligned, at least 3 readable bytes after the block) and raw size;
+ *                    n may not exceed 1 MiB (1 048 576): larger inputs are refused with CRAMGPU_ERR_ARG and a
+ *                    message from cramgpu_last_error(NULL)
+ *   d_out, out_cap   device destination; cramgpu_rans_bound(n) always suffices
+ *   d_out_len        DEVICE u32, receives the compressed size
+ *   d_status         DEVICE i32, receives the cramgpu_status of the block
+ *   stream           cudaStream_t to enqueue on (NULL = the legacy default stream); asynchronous
+ *
+ * All scratch is a file-scope device array of about 1.26 MiB that every GPU holds from the moment the library is
+ * loaded until the process ends; no cudaMalloc, cudaFree or other allocating routine is called.  The first call on
+ * a device resolves the array's device address and raises the coder kernel's shared-memory limit: issue that
+ * first call before any stream capture starts.  Every call reuses the same array and finds the previous call's
+ * data in it; the counters that have to start from zero are cleared on `stream` at the beginning of each call.
+ * Calls whose GPU work can overlap (different streams without an ordering between them) would race on the array
+ * and must be ordered by the caller.
+ */
+int cramgpu_rans0_encode_static(const uint8_t *d_in, uint32_t n, uint8_t *d_out, uint32_t out_cap,
+                                uint32_t *d_out_len, int32_t *d_status, void *stream);
+
 
 /* ------------------------------------------------------------------ record-feature work
  *
