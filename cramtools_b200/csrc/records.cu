@@ -150,9 +150,18 @@ template <bool WRITE>
 __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
 {
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (r >= a.n_reads) return;
-    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    // grid (read groups, containers): the container comes from blockIdx.y; a flat grid (more than 65 535 containers)
+    // falls back to a binary search per warp
+    uint64_t r; uint32_t c;
+    if (gridDim.y > 1 || a.n_containers == 1) {
+        c = blockIdx.y;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.cont_off[c + 1]) return;
+    } else {
+        r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.n_reads) return;
+        c = container_of(a.cont_off, a.n_containers, r);
+    }
     const uint8_t *ref = a.ref + a.ref_off[c];
     const int64_t ref_len = (int64_t)a.ref_len[c];
     const uint64_t lo = a.read_off[r];
@@ -226,10 +235,17 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
     if (WRITE) {
         const uint64_t *B = a.base + (size_t)c * NCNT;
         auto at = [&](int k) -> uint64_t { return B[k] + a.cnt[(size_t)k * a.n_reads + r]; };
-        fbase = at(C_NFEAT); paybase = at(C_PAYLOAD);
-        sFC = a.streams + at(C_FC); sFP = a.streams + at(C_FP); sBS = a.streams + at(C_BS); sDL = a.streams + at(C_DL);
-        sBA = a.streams + at(C_BA); sSC = a.streams + at(C_SC); sQS = a.streams + at(C_QS); sRS = a.streams + at(C_RS);
-        sHC = a.streams + at(C_HC); sPD = a.streams + at(C_PD);
+        fbase = at(C_NFEAT);
+        sQS = a.streams + at(C_QS);
+        // the other series are rare: fetch their offsets only for reads that have features (or unmapped bases) at all
+        const uint32_t nf_here = a.cnt[(size_t)C_NFEAT * a.n_reads + r];
+        const uint64_t nf_next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * a.n_reads + r + 1] : ~0ull;
+        if (nf_next != nf_here || !mapped) {
+            paybase = at(C_PAYLOAD);
+            sFC = a.streams + at(C_FC); sFP = a.streams + at(C_FP); sBS = a.streams + at(C_BS); sDL = a.streams + at(C_DL);
+            sBA = a.streams + at(C_BA); sSC = a.streams + at(C_SC); sRS = a.streams + at(C_RS);
+            sHC = a.streams + at(C_HC); sPD = a.streams + at(C_PD);
+        }
         if (lane == 0) {
             a.feat_off[r] = fbase;                      // feat_off[n_reads] is filled in by the launcher
             a.read_qs_off[r] = ~0ull;
@@ -384,12 +400,19 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
 __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
 {
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (r >= a.n_reads) return;
+    uint64_t r; uint32_t c;
+    if (gridDim.y > 1 || a.n_containers == 1) {
+        c = blockIdx.y;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.cont_off[c + 1]) return;
+    } else {
+        r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.n_reads) return;
+        c = container_of(a.cont_off, a.n_containers, r);
+    }
     if (!(a.force[r] & 1)) return;
     uint64_t qoff = a.read_qs_off[r];
     if (qoff == ~0ull) return;
-    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
     const uint8_t *ref = a.ref + a.ref_off[c];
     const int64_t ref_len = (int64_t)a.ref_len[c];
     const uint64_t lo = a.read_off[r];
@@ -481,25 +504,66 @@ __global__ void __launch_bounds__(256) k_rec_scan(uint32_t *__restrict__ cnt, co
     if (tid == 0) totals[(size_t)c * NCNT + k] = carry;
 }
 
-// absolute bases: one thread walks the (container, counter) totals.  Series regions start at multiples of 16.
+// absolute bases: one CTA; thread = container; exclusive scans over the containers of (aligned series bytes, features,
+// payload bytes).  Series regions start at multiples of 16.
 // grand[0] = bytes of streams, grand[1] = features, grand[2] = payload bytes
-__global__ void k_rec_layout(const uint64_t *__restrict__ totals, uint32_t nc, uint64_t *__restrict__ base,
-                             uint64_t *__restrict__ stream_off, uint64_t *__restrict__ stream_len, uint64_t *__restrict__ grand)
+__global__ void __launch_bounds__(1024) k_rec_layout(const uint64_t *__restrict__ totals, uint32_t nc, uint64_t *__restrict__ base,
+                                                     uint64_t *__restrict__ stream_off, uint64_t *__restrict__ stream_len,
+                                                     uint64_t *__restrict__ grand)
 {
-    if (blockIdx.x || threadIdx.x) return;
-    uint64_t sbytes = 0, feats = 0, pay = 0;
-    for (uint32_t c = 0; c < nc; c++) {
-        for (int k = 0; k < CRAMGPU_S_COUNT; k++) {
-            uint64_t t = totals[(size_t)c * NCNT + k];
-            base[(size_t)c * NCNT + k] = sbytes;
-            stream_off[(size_t)c * CRAMGPU_S_COUNT + k] = sbytes;
-            stream_len[(size_t)c * CRAMGPU_S_COUNT + k] = t;
-            sbytes += (t + 15) & ~15ull;
+    __shared__ unsigned long long wsum[3][32];
+    __shared__ unsigned long long carry[3];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid < 3) carry[tid] = 0;
+    __syncthreads();
+    for (uint32_t c0 = 0; c0 < nc; c0 += 1024) {
+        uint32_t c = c0 + tid;
+        unsigned long long v[3] = {0, 0, 0};
+        if (c < nc) {
+            for (int k = 0; k < CRAMGPU_S_COUNT; k++) v[0] += (totals[(size_t)c * NCNT + k] + 15) & ~15ull;
+            v[1] = totals[(size_t)c * NCNT + C_NFEAT];
+            v[2] = totals[(size_t)c * NCNT + C_PAYLOAD];
         }
-        base[(size_t)c * NCNT + C_NFEAT] = feats; feats += totals[(size_t)c * NCNT + C_NFEAT];
-        base[(size_t)c * NCNT + C_PAYLOAD] = pay; pay += totals[(size_t)c * NCNT + C_PAYLOAD];
+        unsigned long long inc[3];
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            unsigned long long sc = v[q];
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, sc, d);
+                if (lane >= (uint32_t)d) sc += t;
+            }
+            inc[q] = sc;
+            if (lane == 31) wsum[q][w] = sc;
+        }
+        __syncthreads();
+        unsigned long long ex[3];
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            unsigned long long o = carry[q];
+            for (uint32_t j = 0; j < w; j++) o += wsum[q][j];
+            ex[q] = o + inc[q] - v[q];
+        }
+        if (c < nc) {
+            unsigned long long sb = ex[0];
+            for (int k = 0; k < CRAMGPU_S_COUNT; k++) {
+                uint64_t t = totals[(size_t)c * NCNT + k];
+                base[(size_t)c * NCNT + k] = sb;
+                stream_off[(size_t)c * CRAMGPU_S_COUNT + k] = sb;
+                stream_len[(size_t)c * CRAMGPU_S_COUNT + k] = t;
+                sb += (t + 15) & ~15ull;
+            }
+            base[(size_t)c * NCNT + C_NFEAT] = ex[1];
+            base[(size_t)c * NCNT + C_PAYLOAD] = ex[2];
+        }
+        __syncthreads();
+        if (tid == 1023) {
+#pragma unroll
+            for (int q = 0; q < 3; q++) carry[q] = ex[q] + v[q];
+        }
+        __syncthreads();
     }
-    grand[0] = sbytes; grand[1] = feats; grand[2] = pay;
+    if (tid < 3) grand[tid] = carry[tid];
 }
 
 // ------------------------------------------------------------------------------------------------ decode
@@ -534,9 +598,16 @@ __device__ __forceinline__ uint8_t matrix_base(const uint8_t *m, uint8_t refb, i
 __global__ void __launch_bounds__(128) k_norm(NormArgs a)
 {
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (r >= a.n_reads) return;
-    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    uint64_t r; uint32_t c;
+    if (gridDim.y > 1 || a.n_containers == 1) {
+        c = blockIdx.y;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.cont_off[c + 1]) return;
+    } else {
+        r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+        if (r >= a.n_reads) return;
+        c = container_of(a.cont_off, a.n_containers, r);
+    }
     const uint8_t *ref = a.ref + a.win_off[c];
     const int64_t ref_len = (int64_t)a.win_len[c], off0 = a.win_start0[c];
     const uint8_t *mtx = a.matrix + (size_t)c * 8;
@@ -791,11 +862,13 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     uint64_t *d_totals = (uint64_t *)(S + o_totals), *d_soff = (uint64_t *)(S + o_soff), *d_slen = (uint64_t *)(S + o_slen);
     uint64_t *d_grand = (uint64_t *)(S + o_grand);
 
-    const uint32_t grid = (uint32_t)((n + 3) / 4);
+    uint64_t max_reads = 0;
+    for (uint32_t c = 0; c < nc; c++) max_reads = std::max(max_reads, R->cont_off[c + 1] - R->cont_off[c]);
+    const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);
     LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<grid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
     LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
-    LAUNCH(ctx, st, "k_rec_layout", k_rec_layout<<<1, 32, 0, st>>>(d_totals, nc, (uint64_t *)(S + o_base), d_soff, d_slen, d_grand));
+    LAUNCH(ctx, st, "k_rec_layout", k_rec_layout<<<1, 1024, 0, st>>>(d_totals, nc, (uint64_t *)(S + o_base), d_soff, d_slen, d_grand));
     CUDA_TRY(ctx, cudaGetLastError());
 
     // totals (and the per-container tables the caller needs) come back to the host
@@ -958,7 +1031,10 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
     a.f_op = in->f_op; a.f_pos = in->f_pos; a.f_val = in->f_val; a.f_aux = in->f_aux; a.payload = in->payload;
     a.qs = in->qs; a.read_qs_off = in->read_qs_off; a.ba = in->ba; a.read_ba_off = in->read_ba_off;
     a.bases = d_bases; a.quals = d_quals; a.qual_star = d_star; a.status = d_status;
-    LAUNCH(ctx, st, "k_norm", k_norm<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    uint64_t max_reads = 0;
+    for (uint32_t c = 0; c < nc; c++) max_reads = std::max(max_reads, in->cont_off[c + 1] - in->cont_off[c]);
+    const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);
+    LAUNCH(ctx, st, "k_norm", k_norm<<<grid, 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     return CRAMGPU_OK;
 }
