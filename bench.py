@@ -237,12 +237,173 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------- our arm
 
 
+class Lane(object):
+    """One CUDA stream + one cramgpu context + a share of the rank's containers, resident in HBM.  The rank's step is
+    the step of all its lanes, each driven by its own host thread, so that one lane's latency-bound coder kernels
+    (a few warps per SM) overlap the other lanes' record kernels and copies."""
+
+    def __init__(self, lane_id, n_cont, ref, rd, extra, nu, dev, rank, world, group):
+        import torch
+        import cramtools_b200
+        from cramtools_b200 import device as dv, records as rec
+        from cramtools_b200._lib import u64p
+        self.torch, self.rec, self.dv = torch, rec, dv
+        self.n_cont, self.rank, self.world, self.group, self.dev = n_cont, rank, world, group, dev
+        self.stream = torch.cuda.Stream(device=dev)
+        self.ctx = cramtools_b200.Context(dev.index)
+        vp = C.c_void_p
+        with torch.cuda.stream(self.stream):
+            reps = (n_cont + nu - 1) // nu
+            first = (lane_id * 7) % nu                    # lanes start at different unique containers
+            n_reads = self.n_reads = n_cont * READS_PER_CONTAINER
+            ncg_u = int(rd['cigar_off'][-1])
+
+            def up(a, dt):
+                return torch.from_numpy(np.ascontiguousarray(a, dt).view(np.uint8)).to(dev)
+
+            def tile_u8(a, dt, n_elems):
+                return up(a, dt).repeat(reps)[:n_elems * np.dtype(dt).itemsize].contiguous()
+            self.t_bases = tile_u8(rd['bases'], np.uint8, n_reads * READ_LEN)
+            self.t_quals = tile_u8(rd['quals'], np.uint8, n_reads * READ_LEN)
+            self.t_pos = tile_u8(rd['pos'], np.int32, n_reads); self.t_flag = tile_u8(rd['flag'], np.uint16, n_reads)
+            self.t_mapq = tile_u8(rd['mapq'], np.uint8, n_reads)
+            cig_all = np.tile(rd['cigar'], reps)
+            co_all = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg_u)[:, None]).reshape(-1)
+            co_all = np.concatenate([co_all[:n_reads], [co_all[n_reads] if n_reads < co_all.size else reps * ncg_u]]).astype(np.uint64)
+            self.t_cigar = up(cig_all[:int(co_all[-1])], np.uint32)
+            self.t_coff = up(co_all, np.uint64)
+            self.t_roff = up(np.arange(n_reads + 1, dtype=np.uint64) * READ_LEN, np.uint64)
+            self.t_ref = up(ref, np.uint8)
+            self.cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
+            self.ref_off = np.zeros(n_cont, np.uint64); self.ref_len = np.full(n_cont, ref.size, np.uint64)
+            R = self.R = rec.Reads()
+            R.n_reads = n_reads; R.n_containers = n_cont
+            R.cont_off = self.cont_off.ctypes.data_as(u64p); R.ref_off = self.ref_off.ctypes.data_as(u64p)
+            R.ref_len = self.ref_len.ctypes.data_as(u64p)
+            R.ref = vp(self.t_ref.data_ptr()); R.ref_total = ref.size
+            R.bases = vp(self.t_bases.data_ptr()); R.quals = vp(self.t_quals.data_ptr()); R.read_off = vp(self.t_roff.data_ptr())
+            R.cigar = vp(self.t_cigar.data_ptr()); R.cigar_off = vp(self.t_coff.data_ptr()); R.pos = vp(self.t_pos.data_ptr())
+            R.flag = vp(self.t_flag.data_ptr()); R.mapq = vp(self.t_mapq.data_ptr()); R.rflags = None
+            # host-produced series, resident: one buffer, 16-byte aligned blocks
+            ex_blocks = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
+            self.t_extra, ex_off, ex_len = dv.pack_blocks(ex_blocks, dev)
+            ex_addr = ex_off + np.uint64(self.t_extra.data_ptr())
+            NX = len(EXTRA)
+            NB = self.NB = 2 + NX                               # rANS blocks per container: QS, BA, then EXTRA
+            nblk = self.nblk = n_cont * NB
+            self.order = np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont)
+            self.KQS, self.KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
+            self.soff = np.zeros((n_cont, 12), np.uint64); self.slen = np.zeros((n_cont, 12), np.uint64)
+            self.F = rec.Features()
+            self.in_addr = np.zeros(nblk, np.uint64); self.in_len = np.zeros(nblk, np.uint32)
+            self.in_addr.reshape(n_cont, NB)[:, 2:] = ex_addr.reshape(n_cont, NX)
+            self.in_len.reshape(n_cont, NB)[:, 2:] = ex_len.reshape(n_cont, NX)
+            self.enc_cap = int(n_reads * READ_LEN * 0.6) + nblk * 4096 + int(ex_len.sum())
+            self.enc_out = torch.empty(self.enc_cap, dtype=torch.uint8, device=dev)
+            self.e_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); self.e_len = torch.empty(nblk, dtype=torch.int32, device=dev)
+            self.e_st = torch.empty(nblk, dtype=torch.int32, device=dev)
+            # region per container = [min start, max end] of its records (CramNormalizer.java:212-225)
+            p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
+            ws = (p.min(axis=1) - 1)
+            we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
+            self.win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); self.win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
+            self.win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
+            self.o_bases = torch.empty(n_reads * READ_LEN, dtype=torch.uint8, device=dev); self.o_quals = torch.empty_like(self.o_bases)
+            self.o_star = torch.empty(n_reads, dtype=torch.uint8, device=dev); self.o_stat = torch.empty(n_reads, dtype=torch.int32, device=dev)
+            self.t_rfl = torch.ones(n_reads, dtype=torch.uint8, device=dev)          # lossless, mapped: force-preserve QS
+        self.prepared = False
+
+    def _sp(self):
+        return C.c_void_p(self.stream.cuda_stream)
+
+    def encode(self):
+        from cramtools_b200 import sharding
+        from cramtools_b200._lib import u8p, u32p, u64p
+        ctx, F, vp = self.ctx, self.F, C.c_void_p
+        ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), None, -1, C.byref(F), self.soff.ctypes.data_as(u64p),
+                                                      self.slen.ctypes.data_as(u64p), self._sp()))
+        base = np.uint64(F.streams)
+        v = self.in_addr.reshape(self.n_cont, self.NB); w = self.in_len.reshape(self.n_cont, self.NB)
+        v[:, 0] = base + self.soff[:, self.KQS]; w[:, 0] = self.slen[:, self.KQS]
+        v[:, 1] = base + self.soff[:, self.KBA]; w[:, 1] = self.slen[:, self.KBA]
+        ctx.check(ctx.lib.cramgpu_rans_encode_dev(ctx.handle, self.nblk, None, self.in_addr.ctypes.data_as(u64p),
+                                                  self.in_len.ctypes.data_as(u32p), self.order.ctypes.data_as(u8p),
+                                                  vp(self.enc_out.data_ptr()), C.c_uint64(self.enc_cap), vp(self.e_off.data_ptr()),
+                                                  vp(self.e_len.data_ptr()), vp(self.e_st.data_ptr()), self._sp()))
+        with self.torch.cuda.stream(self.stream):
+            sizes = self.e_len.view(self.n_cont, self.NB).sum(dim=1, dtype=self.torch.int64)
+            return sharding.allgather_offsets(sizes, self.rank, self.world, group=self.group)   # the path's only collective
+
+    def prepare(self):
+        """one verified pass to learn what the Java host would know on the decode side (block sizes, prefixes, offsets)"""
+        torch, rec, dv = self.torch, self.rec, self.dv
+        from cramtools_b200._lib import u64p
+        vp = C.c_void_p
+        self.encode()
+        self.stream.synchronize()
+        assert int(self.e_st.abs().sum()) == 0, 'rANS encode status'
+        nblk, n_cont, NB, n_reads = self.nblk, self.n_cont, self.NB, self.n_reads
+        with torch.cuda.stream(self.stream):
+            self.c_off = self.e_off.cpu().numpy().view(np.uint64)[:-1].copy(); self.c_len = self.e_len.cpu().numpy().view(np.uint32).copy()
+            self.comp_bytes = float(self.c_len.sum())
+            enc_host = self.enc_out[:int(self.c_off[-1]) + int(self.c_len[-1])].cpu().numpy()
+            self.prefixes = np.zeros((nblk, 9), np.uint8)
+            idx = self.c_off[:, None].astype(np.int64) + np.arange(9)[None, :]
+            ok = self.c_len >= 9
+            self.prefixes[ok] = enc_host[idx[ok]]
+            del enc_host
+            raw = self.in_len.astype(np.int64)
+            d_off = np.concatenate([[0], np.cumsum((raw + 15) & ~15)]).astype(np.uint64)
+            self.dec_out = torch.empty(int(d_off[-1]) + 64, dtype=torch.uint8, device=self.dev)
+            self.dd_off = torch.empty(nblk + 1, dtype=torch.int64, device=self.dev); self.dd_len = torch.empty(nblk, dtype=torch.int32, device=self.dev)
+            self.dd_st = torch.empty(nblk, dtype=torch.int32, device=self.dev)
+            # per-read offset of its score array inside the decoded QS block (what CramRecordReader knows while parsing)
+            rq = np.empty(n_reads, np.uint64)
+            self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(rq.ctypes.data), vp(self.F.read_qs_off),
+                                                             C.c_uint64(rq.nbytes), self._sp()))
+            cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
+            rq_new = rq - self.soff[cidx, self.KQS] + d_off[cidx * NB + 0]
+            self.t_rq = torch.from_numpy(rq_new.view(np.uint8)).to(self.dev)
+            self.t_rba = torch.full((n_reads,), -1, dtype=torch.int64, device=self.dev)
+            self.raw_bytes = float(raw.sum())
+            self.raw_o0 = float(self.in_len.reshape(n_cont, NB)[:, -1].sum())
+            self.qs_bytes = float(self.slen[:, self.KQS].sum())
+        N = self.N = rec.NormIn()
+        N.n_reads = n_reads; N.n_containers = n_cont
+        N.cont_off = self.cont_off.ctypes.data_as(u64p); N.win_off = self.win_off.ctypes.data_as(u64p); N.win_len = self.win_len.ctypes.data_as(u64p)
+        N.win_start0 = self.win_s0.ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(self.t_ref.data_ptr()); N.ref_total = self.t_ref.numel()
+        N.pos = vp(self.t_pos.data_ptr()); N.read_off = vp(self.t_roff.data_ptr()); N.rflags = vp(self.t_rfl.data_ptr())
+        N.qs = vp(self.dec_out.data_ptr()); N.read_qs_off = vp(self.t_rq.data_ptr()); N.ba = vp(self.dec_out.data_ptr())
+        N.read_ba_off = vp(self.t_rba.data_ptr())
+        # correctness of what is timed: the round trip restores every base and quality of every read
+        self.decode()
+        self.stream.synchronize()
+        assert int(self.dd_st.abs().sum()) == 0 and int(self.o_stat.abs().sum()) == 0 and int(self.o_star.sum()) == 0
+        assert torch.equal(self.o_bases, self.t_bases) and torch.equal(self.o_quals, self.t_quals), 'round trip mismatch'
+        self.prepared = True
+
+    def decode(self):
+        from cramtools_b200._lib import u8p, u32p, u64p
+        ctx, F, N, vp = self.ctx, self.F, self.N, C.c_void_p
+        ctx.check(ctx.lib.cramgpu_rans_decode_dev(ctx.handle, self.nblk, vp(self.enc_out.data_ptr()), self.c_off.ctypes.data_as(u64p),
+                                                  self.c_len.ctypes.data_as(u32p), self.prefixes.ctypes.data_as(u8p),
+                                                  vp(self.dec_out.data_ptr()), C.c_uint64(self.dec_out.numel()), vp(self.dd_off.data_ptr()),
+                                                  vp(self.dd_len.data_ptr()), vp(self.dd_st.data_ptr()), self._sp()))
+        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
+        N.payload = F.payload
+        ctx.check(ctx.lib.cramgpu_normalize_decode_dev(ctx.handle, C.byref(N), vp(self.o_bases.data_ptr()), vp(self.o_quals.data_ptr()),
+                                                       vp(self.o_star.data_ptr()), vp(self.o_stat.data_ptr()), self._sp()))
+
+    def steps(self, k):
+        for _ in range(k):
+            self.encode()
+            self.decode()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    import cramtools_b200
-    from cramtools_b200 import device as dv, sharding, records as rec, _lib
-    from cramtools_b200._lib import u8p, u32p, u64p, i32p
+    import cramtools_b200  # noqa: F401  (fails loudly here when libcramgpu.so is missing)
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -251,166 +412,69 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     dev = torch.device('cuda', local)
-    # everything (torch ops and the library's kernels) runs on ONE explicit stream; the events that time the step are
-    # recorded on it.  (torch's default stream has handle 0, which the C ABI reads as "use the context's own stream".)
-    work_stream = torch.cuda.Stream(device=dev)
-    torch.cuda.set_stream(work_stream)
-    ctx = cramtools_b200.Context(local)
     peaks, peak_kind = measured_peaks()
-    vp = C.c_void_p
 
     n_cont = args.containers
     nu = min(UNIQUE, n_cont)
     ref, rd, extra = unique_containers(nu, 1000 + 17 * rank)
-    reps = (n_cont + nu - 1) // nu
-    n_reads = n_cont * READS_PER_CONTAINER
-    nb_u, ncg_u = int(rd['read_off'][-1]), int(rd['cigar_off'][-1])
-
-    # ---- resident inputs: upload the unique containers once, tile on the device
-    def up(a, dt):
-        return torch.from_numpy(np.ascontiguousarray(a, dt).view(np.uint8)).to(dev)
-
-    def tile_u8(a, dt, n_elems):
-        t = up(a, dt)
-        return t.repeat(reps)[:n_elems * np.dtype(dt).itemsize].contiguous()
-    t_bases = tile_u8(rd['bases'], np.uint8, n_reads * READ_LEN)
-    t_quals = tile_u8(rd['quals'], np.uint8, n_reads * READ_LEN)
-    t_pos = tile_u8(rd['pos'], np.int32, n_reads); t_flag = tile_u8(rd['flag'], np.uint16, n_reads); t_mapq = tile_u8(rd['mapq'], np.uint8, n_reads)
-    cig_all = np.tile(rd['cigar'], reps)
-    co_all = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg_u)[:, None]).reshape(-1)
-    co_all = np.concatenate([co_all[:n_reads], [co_all[n_reads] if n_reads < co_all.size else reps * ncg_u]]).astype(np.uint64)
-    t_cigar = up(cig_all[:int(co_all[-1])], np.uint32)
-    t_coff = up(co_all, np.uint64)
-    t_roff = up(np.arange(n_reads + 1, dtype=np.uint64) * READ_LEN, np.uint64)
-    t_ref = up(ref, np.uint8)
-    cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
-    ref_off = np.zeros(n_cont, np.uint64); ref_len = np.full(n_cont, ref.size, np.uint64)
-    R = rec.Reads()
-    R.n_reads = n_reads; R.n_containers = n_cont
-    R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
-    R.ref = vp(t_ref.data_ptr()); R.ref_total = ref.size
-    R.bases = vp(t_bases.data_ptr()); R.quals = vp(t_quals.data_ptr()); R.read_off = vp(t_roff.data_ptr())
-    R.cigar = vp(t_cigar.data_ptr()); R.cigar_off = vp(t_coff.data_ptr()); R.pos = vp(t_pos.data_ptr()); R.flag = vp(t_flag.data_ptr())
-    R.mapq = vp(t_mapq.data_ptr()); R.rflags = None
-
-    # host-produced series, resident: one buffer, 16-byte aligned blocks
-    ex_blocks = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
-    t_extra, ex_off, ex_len = dv.pack_blocks(ex_blocks, dev)
-    ex_addr = ex_off + np.uint64(t_extra.data_ptr())
-    NX = len(EXTRA)
-    NB = 2 + NX                                         # rANS blocks per container: QS, BA, then EXTRA
-    order = np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont)
-    stream = vp(torch.cuda.current_stream().cuda_stream)
-    KQS, KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
-    soff = np.zeros((n_cont, 12), np.uint64); slen = np.zeros((n_cont, 12), np.uint64)
-    F = rec.Features()
-    in_addr = np.zeros(n_cont * NB, np.uint64); in_len = np.zeros(n_cont * NB, np.uint32)
-    in_addr.reshape(n_cont, NB)[:, 2:] = ex_addr.reshape(n_cont, NX)
-    in_len.reshape(n_cont, NB)[:, 2:] = ex_len.reshape(n_cont, NX)
-    enc_cap = int(n_reads * READ_LEN * 0.6) + n_cont * NB * 4096 + int(ex_len.sum())
-    enc_out = torch.empty(enc_cap, dtype=torch.uint8, device=dev)
-    nblk = n_cont * NB
-    e_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); e_len = torch.empty(nblk, dtype=torch.int32, device=dev)
-    e_st = torch.empty(nblk, dtype=torch.int32, device=dev)
-    # region per container = [min start, max end] of its records (CramNormalizer.java:212-225)
-    p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
-    ws = (p.min(axis=1) - 1)
-    we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
-    win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
-    win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
-    o_bases = torch.empty(n_reads * READ_LEN, dtype=torch.uint8, device=dev); o_quals = torch.empty_like(o_bases)
-    o_star = torch.empty(n_reads, dtype=torch.uint8, device=dev); o_stat = torch.empty(n_reads, dtype=torch.int32, device=dev)
-    t_rfl = torch.ones(n_reads, dtype=torch.uint8, device=dev)          # lossless, mapped: force-preserve QS
-
-    def encode_dev():
-        ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(R), None, -1, C.byref(F), soff.ctypes.data_as(u64p),
-                                                      slen.ctypes.data_as(u64p), stream))
-        base = np.uint64(F.streams)
-        v = in_addr.reshape(n_cont, NB); w = in_len.reshape(n_cont, NB)
-        v[:, 0] = base + soff[:, KQS]; w[:, 0] = slen[:, KQS]
-        v[:, 1] = base + soff[:, KBA]; w[:, 1] = slen[:, KBA]
-        ctx.check(ctx.lib.cramgpu_rans_encode_dev(ctx.handle, nblk, None, in_addr.ctypes.data_as(u64p), in_len.ctypes.data_as(u32p),
-                                                  order.ctypes.data_as(u8p), vp(enc_out.data_ptr()), C.c_uint64(enc_cap),
-                                                  vp(e_off.data_ptr()), vp(e_len.data_ptr()), vp(e_st.data_ptr()), stream))
-        sizes = e_len.view(n_cont, NB).sum(dim=1, dtype=torch.int64)
-        return sharding.allgather_offsets(sizes, rank, world)             # the path's only collective
-
-    # ---- one verified pass to learn what the Java host would know on the decode side (block sizes, prefixes, offsets)
-    offs = encode_dev()
-    torch.cuda.synchronize()
-    assert int(e_st.abs().sum()) == 0, 'rANS encode status'
-    c_off = e_off.cpu().numpy().view(np.uint64)[:-1].copy(); c_len = e_len.cpu().numpy().view(np.uint32).copy()
-    comp_bytes = float(c_len.sum())
-    enc_host = enc_out[:int(c_off[-1]) + int(c_len[-1])].cpu().numpy()
-    prefixes = np.zeros((nblk, 9), np.uint8)
-    idx = c_off[:, None].astype(np.int64) + np.arange(9)[None, :]
-    ok = c_len >= 9
-    prefixes[ok] = enc_host[idx[ok]]
-    del enc_host
-    raw = in_len.astype(np.int64)
-    d_off = np.concatenate([[0], np.cumsum((raw + 15) & ~15)]).astype(np.uint64)
-    dec_out = torch.empty(int(d_off[-1]) + 64, dtype=torch.uint8, device=dev)
-    dd_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); dd_len = torch.empty(nblk, dtype=torch.int32, device=dev)
-    dd_st = torch.empty(nblk, dtype=torch.int32, device=dev)
-    # per-read offset of its score array inside the decoded QS block (what CramRecordReader knows while parsing)
-    rq = dv.dev_to_numpy(ctx, F.read_qs_off, n_reads, np.uint64)
-    cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
-    rq_new = rq - soff[cidx, KQS] + d_off[cidx * NB + 0]
-    t_rq = up(rq_new, np.uint64)
-    t_rba = torch.full((n_reads,), -1, dtype=torch.int64, device=dev)
-    raw_bytes = float(raw.sum())
-    qs_bytes = float(slen[:, KQS].sum())
-
-    N = rec.NormIn()
-    N.n_reads = n_reads; N.n_containers = n_cont
-    N.cont_off = cont_off.ctypes.data_as(u64p); N.win_off = win_off.ctypes.data_as(u64p); N.win_len = win_len.ctypes.data_as(u64p)
-    N.win_start0 = win_s0.ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(t_ref.data_ptr()); N.ref_total = ref.size
-    N.pos = vp(t_pos.data_ptr()); N.read_off = vp(t_roff.data_ptr()); N.rflags = vp(t_rfl.data_ptr())
-    N.qs = vp(dec_out.data_ptr()); N.read_qs_off = vp(t_rq.data_ptr()); N.ba = vp(dec_out.data_ptr()); N.read_ba_off = vp(t_rba.data_ptr())
-
-    def decode_dev():
-        ctx.check(ctx.lib.cramgpu_rans_decode_dev(ctx.handle, nblk, vp(enc_out.data_ptr()), c_off.ctypes.data_as(u64p),
-                                                  c_len.ctypes.data_as(u32p), prefixes.ctypes.data_as(u8p), vp(dec_out.data_ptr()),
-                                                  C.c_uint64(dec_out.numel()), vp(dd_off.data_ptr()), vp(dd_len.data_ptr()),
-                                                  vp(dd_st.data_ptr()), stream))
-        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
-        N.payload = F.payload
-        ctx.check(ctx.lib.cramgpu_normalize_decode_dev(ctx.handle, C.byref(N), vp(o_bases.data_ptr()), vp(o_quals.data_ptr()),
-                                                       vp(o_star.data_ptr()), vp(o_stat.data_ptr()), stream))
-
-    def step_dev():
-        o = encode_dev()
-        decode_dev()
-        return o
-
-    # correctness of what is timed: the round trip restores every base and quality of every read
-    decode_dev()
-    torch.cuda.synchronize()
-    assert int(dd_st.abs().sum()) == 0 and int(o_stat.abs().sum()) == 0 and int(o_star.sum()) == 0
-    assert torch.equal(o_bases, t_bases) and torch.equal(o_quals, t_quals), 'round trip mismatch'
+    n_lanes = max(1, min(args.lanes, n_cont))
+    share = [n_cont // n_lanes + (1 if i < n_cont % n_lanes else 0) for i in range(n_lanes)]
+    groups = [dist.new_group() if world > 1 else None for _ in range(n_lanes)]
+    lanes = [Lane(i, share[i], ref, rd, extra, nu, dev, rank, world, groups[i]) for i in range(n_lanes)]
+    for ln in lanes:
+        ln.prepare()
+    n_reads = sum(ln.n_reads for ln in lanes)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step_dev()
+    def run_steps(k):
+        """every lane runs k steps on its own stream, driven by its own host thread (the C calls release the GIL)"""
+        if n_lanes == 1:
+            lanes[0].steps(k)
+            return
+        errs = []
+
+        def work(ln, i):
+            try:
+                torch.cuda.set_device(local)
+                # lanes start staggered so that one lane's latency-bound coder kernels (few warps per SM) run beside the
+                # others' record kernels instead of all lanes doing the same phase at once
+                time.sleep(i * args.stagger_ms * 1e-3)
+                ln.steps(k)
+            except Exception as e:      # noqa: BLE001
+                errs.append(e)
+        th = [threading.Thread(target=work, args=(ln, i)) for i, ln in enumerate(lanes)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        if errs:
+            raise errs[0]
+
+    run_steps(args.warmup)
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    launches0 = ctx.launch_count()
-    ctx.profile_enable(True)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        step_dev()
-    e1.record()
+    launches0 = sum(ln.ctx.launch_count() for ln in lanes)
+    for ln in lanes:
+        ln.ctx.profile_enable(True)
+    # device time of the timed region: first start .. last end over the lanes' streams
+    e0 = [torch.cuda.Event(enable_timing=True) for _ in lanes]; e1 = [torch.cuda.Event(enable_timing=True) for _ in lanes]
+    for ln, ev in zip(lanes, e0):
+        ev.record(ln.stream)
+    run_steps(args.steps)
+    for ln, ev in zip(lanes, e1):
+        ev.record(ln.stream)
     barrier()
-    ms = e0.elapsed_time(e1) / args.steps
-    spans = ctx.profile_read()
-    ctx.profile_enable(False)
-    launches = (ctx.launch_count() - launches0) // args.steps
+    ms = max(e0[0].elapsed_time(b) for b in e1) / args.steps      # all e0 are recorded back to back right after a device-wide sync
+    spans = []
+    for ln in lanes:
+        spans += ln.ctx.profile_read()
+        ln.ctx.profile_enable(False)
+    launches = (sum(ln.ctx.launch_count() for ln in lanes) - launches0) // args.steps
     clocks = sampler.summary()
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -419,38 +483,45 @@ def run_ours(args):
     kt = {}
     for name, m in spans:
         kt.setdefault(name, []).append(m)
-    kavg = {k: float(np.sum(v)) / args.steps for k, v in kt.items()}       # per step (a kernel may launch more than once per step)
+    kavg = {k: float(np.sum(v)) / args.steps for k, v in kt.items()}       # summed over lanes and launches, per step
+    kcount = {k: len(v) / args.steps for k, v in kt.items()}
     top = max(kavg, key=kavg.get)
 
     # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
     n_e2e = min(n_cont, args.e2e_containers)
-    e2e = run_e2e(ctx, args, ref, rd, extra, nu, n_e2e, world, barrier)
+    e2e = run_e2e(lanes[0].ctx, args, ref, rd, extra, nu, n_e2e, world, barrier)
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
-        o1_raw = raw_bytes - float(in_len.reshape(n_cont, NB)[:, -1].sum())
+        raw_bytes = sum(ln.raw_bytes for ln in lanes); comp_bytes = sum(ln.comp_bytes for ln in lanes)
+        o1_raw = raw_bytes - sum(ln.raw_o0 for ln in lanes)
         comp1 = comp_bytes * (o1_raw / raw_bytes)
         algo = {'k_enc1': o1_raw + comp1, 'k_dec1': o1_raw + comp1, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
                 'k_rec_walk_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_walk_write': n_reads * (3 * READ_LEN + 40.0),
                 'k_norm': n_reads * (3 * READ_LEN + 20.0), 'k_pack': 2 * comp_bytes}
         ab = algo.get(top)
-        achieved = ab / (kavg[top] * 1e-3) / 1e9 if ab else None
+        # kavg sums the lanes' launches, which overlap in time; the per-launch figure is what the roofline wants
+        per_launch_ms = kavg[top] / max(kcount[top], 1)
+        achieved = (ab / max(kcount[top], 1)) / (per_launch_ms * 1e-3) / 1e9 if ab else None
         peak = float(peaks['hbm_gbs'])
         rans_ms_enc = sum(v for k, v in kavg.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
         rans_ms_dec = sum(v for k, v in kavg.items() if k in ('k_dec_tables', 'k_dec0', 'k_dec1', 'k_dec1_big'))
+        cfg = workload_config(args, n_cont)
+        cfg['lanes'] = '%d CUDA streams per GPU, each with its own share of the containers' % n_lanes
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
-            'dtype': 'u8/i32 integer (+f64 in the order-1 frequency normalisation)', 'data': 'synthetic',
-            'config': workload_config(args, n_cont),
+            'dtype': 'u8/i32 integer (+f64 in the order-1 frequency normalisation)', 'data': 'synthetic', 'config': cfg,
             'rans': {'raw_GB_per_step_per_gpu': raw_bytes / 1e9, 'compressed_ratio': comp_bytes / raw_bytes,
-                     'encode_GBps_per_gpu': raw_bytes / (rans_ms_enc * 1e-3) / 1e9, 'decode_GBps_per_gpu': raw_bytes / (rans_ms_dec * 1e-3) / 1e9,
-                     'qs_block_bytes': qs_bytes / n_cont, 'state_lanes_in_flight': int(4 * nblk)},
-            'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'gpu_launches': int(launches),
+                     'encode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_enc / n_lanes * 1e-3) / 1e9,
+                     'decode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_dec / n_lanes * 1e-3) / 1e9,
+                     'qs_block_bytes': sum(ln.qs_bytes for ln in lanes) / n_cont, 'state_lanes_in_flight': int(4 * sum(ln.nblk for ln in lanes))},
+            'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
+            'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak if achieved else None, 'traffic': None, 'peak_kind': peak_kind,
-                         'note': 'rANS is a recurrence per state: attainable rate = resident states x clock / cycles per step '
-                                 '(DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
+                         'note': 'per launch of one lane; rANS is a recurrence per state: attainable rate = resident states x clock / '
+                                 'cycles per step (DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
             'e2e': e2e, 'clocks': clocks,
         }
         if world == 1 and not args.no_cpu:
@@ -584,6 +655,8 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
     ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
+    ap.add_argument('--lanes', type=int, default=1, help='CUDA streams per GPU, each owning a share of the containers')
+    ap.add_argument('--stagger-ms', type=float, default=0.0, help='start offset between consecutive lanes')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -21,7 +21,7 @@ def local_ordinals(n_total, rank, world):
     return list(range(rank, n_total, world))
 
 
-def allgather_offsets(local_sizes, rank, world, base=0):
+def allgather_offsets(local_sizes, rank, world, base=0, group=None):
     """local_sizes: int64 tensor, compressed bytes of this rank's containers (local order; every rank holds the
     same count, pad with zeros otherwise).  Returns the int64 tensor of global byte offsets of this rank's
     containers: container with global ordinal g = j*world + rank starts at base + sum(sizes of ordinals < g).
@@ -30,7 +30,7 @@ def allgather_offsets(local_sizes, rank, world, base=0):
         return base + torch.cumsum(local_sizes, 0) - local_sizes
     n = local_sizes.numel()
     gathered = torch.empty(world * n, dtype=local_sizes.dtype, device=local_sizes.device)
-    dist.all_gather_into_tensor(gathered, local_sizes.contiguous().view(-1))
+    dist.all_gather_into_tensor(gathered, local_sizes.contiguous().view(-1), group=group)
     flat = gathered.view(world, n).t().reshape(-1)   # ordinal order: j*world + r
     excl = torch.cumsum(flat, 0) - flat
     return base + excl.view(-1, world)[:, rank].contiguous()
