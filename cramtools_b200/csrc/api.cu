@@ -4,6 +4,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 static thread_local std::string g_init_error;
 
@@ -141,6 +142,13 @@ int cramgpu_init(int device, cramgpu_ctx **out)
     ctx->device = device;
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming);
+    if (e == cudaSuccess && !getenv("CRAMGPU_NO_HP_STREAM")) {
+        int lo = 0, hi = 0;
+        cudaDeviceGetStreamPriorityRange(&lo, &hi);
+        e = cudaStreamCreateWithPriority(&ctx->hp_stream, cudaStreamNonBlocking, hi);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->hp_in, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->hp_out, cudaEventDisableTiming);
+    }
     if (e != cudaSuccess) { delete ctx; return ctx_cuda(nullptr, e, "stream/event creation"); }
     *out = ctx;
     return CRAMGPU_OK;
@@ -163,6 +171,9 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
     if (ctx->pin_meta) cudaFreeHost(ctx->pin_meta);
     if (ctx->ev) cudaEventDestroy(ctx->ev);
+    if (ctx->hp_in) cudaEventDestroy(ctx->hp_in);
+    if (ctx->hp_out) cudaEventDestroy(ctx->hp_out);
+    if (ctx->hp_stream) cudaStreamDestroy(ctx->hp_stream);
     for (auto &s : ctx->spans) { cudaEventDestroy(s.a); cudaEventDestroy(s.b); }
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -72,6 +72,11 @@ struct cramgpu_ctx {
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
     size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
     cudaEvent_t ev = nullptr;
+    // The coder kernels are latency-bound (a few warps per SM for tens of milliseconds).  They run on a high-priority
+    // side stream so that, when several contexts share a GPU, their CTAs are placed ahead of the queued CTAs of the
+    // throughput kernels of other streams instead of waiting behind them.
+    cudaStream_t hp_stream = nullptr;
+    cudaEvent_t hp_in = nullptr, hp_out = nullptr;
     EncodePending pend;
     // optional per-kernel timing (cramgpu_profile_*): CUDA events around every launch
     bool profiling = false;
@@ -83,6 +88,16 @@ struct cramgpu_ctx {
 // LAUNCH(ctx, stream, "name", kernel<<<...>>>(...)) counts the launch and, when profiling, brackets it with events
 void prof_begin(cramgpu_ctx *ctx, cudaStream_t st, const char *name);
 void prof_end(cramgpu_ctx *ctx, cudaStream_t st);
+// run `...` (kernel launches that use the stream variable `hs`) on the context's high-priority stream, ordered after
+// everything enqueued on `st` so far and before everything enqueued on `st` afterwards
+#define ON_HP_STREAM(ctx, st, ...)                                              \
+    do {                                                                        \
+        cudaStream_t hs = (ctx)->hp_stream ? (ctx)->hp_stream : (st);           \
+        if (hs != (st)) { cudaEventRecord((ctx)->hp_in, (st)); cudaStreamWaitEvent(hs, (ctx)->hp_in, 0); } \
+        __VA_ARGS__;                                                            \
+        if (hs != (st)) { cudaEventRecord((ctx)->hp_out, hs); cudaStreamWaitEvent((st), (ctx)->hp_out, 0); } \
+    } while (0)
+
 #define LAUNCH(ctx, st, name, ...)              \
     do {                                        \
         if ((ctx)->profiling) prof_begin((ctx), (st), (name)); \

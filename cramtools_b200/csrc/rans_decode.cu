@@ -579,7 +579,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     if (n0 + n1) {
         LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, compact, meta, d_status));
         if (n1) {
-            LAUNCH(ctx, st, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, DEC1_SMEM, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, compact, meta, d_out, d_status));
+            ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, DEC1_SMEM, hs>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, compact, meta, d_out, d_status)));
             LAUNCH(ctx, st, "k_dec1_big", k_dec1_big<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
         }
         if (n0) {

@@ -902,11 +902,11 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
             LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
             LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
             LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
-            LAUNCH(ctx, st, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), st>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status, dbg));
+            ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), hs>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status, dbg)));
         }
         if (n0) {
             LAUNCH(ctx, st, "k_tables0", k_tables0<<<n0, 256, 0, st>>>(dd, d_o0, F0, syms0, work, tlen));
-            LAUNCH(ctx, st, "k_enc0", k_enc<0><<<(n0 + 7) / 8, ENC_THREADS, ENC_SMEM(0), st>>>(dd, d_s0, n0, d_in, syms0, meta, work, plen, d_status, dbg));
+            ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_enc0", k_enc<0><<<(n0 + 7) / 8, ENC_THREADS, ENC_SMEM(0), hs>>>(dd, d_s0, n0, d_in, syms0, meta, work, plen, d_status, dbg)));
         }
     }
     LAUNCH(ctx, st, "k_scan_out", k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status));

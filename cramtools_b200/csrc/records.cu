@@ -262,6 +262,47 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
             }
             n_ba += (uint32_t)rlen;
         }
+    } else if (hasfeat && c1 - c0 == 1 && !q_feats && rlen > 0 && (a.cigar[c0] & 15) != OP_I && (a.cigar[c0] & 15) != OP_S &&
+               consumes_read(a.cigar[c0] & 15) && (int64_t)(a.cigar[c0] >> 4) == rlen) {
+        // ---- fast path: "<len>M" (or = / X) over the whole read, no sparse quality features.  Same result as the general
+        //      walk below, a fraction of its instructions: only substitutions can occur.
+        const uint8_t *codes = WRITE ? a.codes + (size_t)c * 32 : nullptr;
+        const int64_t rp0 = (int64_t)pos - 1;
+        for (int64_t i0 = 0; i0 < rlen; i0 += 32) {
+            const int64_t i = i0 + lane;
+            const bool in = i < rlen;
+            const uint8_t b = in ? rb[i] : 0;
+            const int64_t rp = rp0 + i;
+            const uint8_t refb = norm_base((in && rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N');   // [:306-308]
+            const bool isX = in && b != refb;
+            const uint32_t bX = __ballot_sync(0xFFFFFFFFu, isX);
+            if (bX) {
+                const uint32_t lt = (1u << lane) - 1u;
+                const int32_t mypos = (int32_t)i + 1;
+                const uint32_t below = bX & lt;
+                const int32_t pprev = below ? (int32_t)(i0 + (31 - __clz(below))) + 1 : prev;
+                const uint32_t dF = isX ? (uint32_t)(mypos - pprev) : 0;
+                const uint32_t lF = isX ? itf8_len(dF) : 0;
+                uint32_t fp_tot, fp_off = warp_excl_scan_u32(lF, lane, fp_tot);
+                if (isX) {
+                    const int ri = base_index(refb), bi = base_index(b);
+                    if (!WRITE) {
+                        if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
+                    } else {
+                        const uint32_t k = n_feat + __popc(below);
+                        const uint64_t fi = fbase + k;
+                        const uint8_t code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;
+                        a.f_op[fi] = 'X'; a.f_pos[fi] = mypos; a.f_val[fi] = code; a.f_aux[fi] = (int32_t)b | ((int32_t)refb << 8);
+                        sFC[k] = 'X';
+                        itf8_put(sFP + n_fp + fp_off, dF);
+                        sBS[n_bs + __popc(below)] = code;
+                    }
+                }
+                const uint32_t nx = __popc(bX);
+                n_feat += nx; n_bs += nx; n_fp += fp_tot;
+                prev = (int32_t)(i0 + (31 - __clz(bX))) + 1;
+            }
+        }
     } else if (hasfeat) {
         const uint8_t *codes = WRITE ? a.codes + (size_t)c * 32 : nullptr;
         int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
@@ -380,13 +421,19 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
         n_qs += (uint32_t)rlen;
     }
     if (!WRITE && lane == 0) {
+        // the counter arrays were cleared before the pass: store only what is not zero (most reads: FN, QS, MQ)
         uint32_t *cn = a.cnt + r;
         const uint64_t N = a.n_reads;
-        cn[C_FN * N] = mapped ? itf8_len(n_feat) : 0;
-        cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_BS * N] = n_bs; cn[C_DL * N] = n_dl; cn[C_BA * N] = n_ba;
-        cn[C_SC * N] = n_sc; cn[C_QS * N] = n_qs; cn[C_RS * N] = n_rs; cn[C_HC * N] = n_hc; cn[C_PD * N] = n_pd;
-        cn[C_MQ * N] = mapped ? itf8_len(mapq) : 0;
-        cn[C_NFEAT * N] = n_feat; cn[C_PAYLOAD * N] = n_pay;
+        if (mapped) { cn[C_FN * N] = itf8_len(n_feat); cn[C_MQ * N] = itf8_len(mapq); }
+        if (n_qs) cn[C_QS * N] = n_qs;
+        if (n_feat) { cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_NFEAT * N] = n_feat; }
+        if (n_bs) cn[C_BS * N] = n_bs;
+        if (n_ba) cn[C_BA * N] = n_ba;
+        if (n_dl) cn[C_DL * N] = n_dl;
+        if (n_sc) { cn[C_SC * N] = n_sc; cn[C_PAYLOAD * N] = n_pay; }
+        if (n_rs) cn[C_RS * N] = n_rs;
+        if (n_hc) cn[C_HC * N] = n_hc;
+        if (n_pd) cn[C_PD * N] = n_pd;
     }
     if (WRITE && lane == 0 && mapped) {
         const uint64_t *B = a.base + (size_t)c * NCNT;
@@ -849,7 +896,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     CUDA_TRY(ctx, U.up(R->ref_off, 8 * (size_t)nc, S + o_roff));
     CUDA_TRY(ctx, U.up(R->ref_len, 8 * (size_t)nc, S + o_rlen));
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev, st));
-    CUDA_TRY(ctx, cudaMemsetAsync(S + o_subst, 0, o_zero_end - o_subst, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_cnt, 0, o_zero_end - o_cnt, st));      // counters, flags, histogram, status
 
     RecArgs a;
     memset(&a, 0, sizeof a);
