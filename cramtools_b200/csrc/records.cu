@@ -50,6 +50,11 @@ struct RecArgs {
     uint8_t *f_op; int32_t *f_pos, *f_val, *f_aux; uint64_t *feat_off;
     uint8_t *payload, *streams;
     uint64_t *read_qs_off, *read_ba_off;
+    // fast path (k_rec_simple): normalised copy of the reference, per-container totals, and the list of the reads
+    // it leaves to the general walk
+    const uint8_t *nref;         // normalizeBase(ref[i]) at the same offsets as ref
+    const uint64_t *totals;      // [n_containers][NCNT] (write pass)
+    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;
 };
 
 __device__ __forceinline__ uint8_t norm_base(uint8_t b)      // cram/build/Utils.normalizeBase [Utils.java:31-49]
@@ -146,22 +151,245 @@ __device__ __forceinline__ uint32_t container_of(const uint64_t *cont_off, uint3
     return lo;
 }
 
+// ---- byte copies by one thread -------------------------------------------------------------------
+// 4 source bytes at any address: two aligned words and a funnel shift.  The second word is read only when the address
+// is not aligned, so no word is touched that does not hold at least one byte of [p, p + 4).
+__device__ __forceinline__ uint32_t ld_u32_any(const uint8_t *p)
+{
+    const uint32_t sh = (uint32_t)((uintptr_t)p & 3);
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(p - sh);
+    const uint32_t lo = w[0], hi = sh ? w[1] : 0u;
+    return __funnelshift_r(lo, hi, sh * 8);
+}
+// copy n bytes src -> dst, any alignment on both sides: 16-byte stores where dst allows, 4-byte loads.  xw maps a
+// word of 4 source bytes, xb a single byte (the same function on one byte).
+template <class FW, class FB>
+__device__ __forceinline__ void copy_bytes(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint32_t n, FW xw, FB xb)
+{
+    uint32_t i = 0;
+    while (i < n && ((uintptr_t)(dst + i) & 3)) { dst[i] = xb(src[i]); i++; }
+    while (i + 4 <= n && ((uintptr_t)(dst + i) & 15)) { *reinterpret_cast<uint32_t *>(dst + i) = xw(ld_u32_any(src + i)); i += 4; }
+    if (i + 16 <= n) {
+        const uint8_t *s = src + i;
+        const uint32_t sh = (uint32_t)((uintptr_t)s & 3), sh8 = sh * 8;
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(s - sh);
+        uint32_t w0 = *w;
+        for (; i + 16 <= n; i += 16) {
+            const uint32_t w1 = w[1], w2 = w[2], w3 = w[3];
+            const uint32_t w4 = sh ? w[4] : 0u;
+            uint4 o;
+            o.x = xw(__funnelshift_r(w0, w1, sh8)); o.y = xw(__funnelshift_r(w1, w2, sh8));
+            o.z = xw(__funnelshift_r(w2, w3, sh8)); o.w = xw(__funnelshift_r(w3, w4, sh8));
+            *reinterpret_cast<uint4 *>(dst + i) = o;
+            w0 = sh ? w4 : ((i + 32 <= n) ? w[4] : 0u);
+            w += 4;
+        }
+    }
+    while (i + 4 <= n) { *reinterpret_cast<uint32_t *>(dst + i) = xw(ld_u32_any(src + i)); i += 4; }
+    while (i < n) { dst[i] = xb(src[i]); i++; }
+}
+struct IdW { __device__ __forceinline__ uint32_t operator()(uint32_t w) const { return w; } };
+struct IdB { __device__ __forceinline__ uint8_t operator()(uint8_t b) const { return b; } };
+
+// normalizeBase over the reference (windows or whole), 16 bytes per thread: grid (chunks, windows)
+__global__ void __launch_bounds__(256) k_ref_norm(const uint8_t *__restrict__ ref, uint8_t *__restrict__ nref,
+                                                  const uint64_t *__restrict__ win_off, const uint64_t *__restrict__ win_len,
+                                                  uint64_t whole_len)
+{
+    uint64_t lo, hi;
+    if (win_off) { lo = win_off[blockIdx.y]; hi = lo + win_len[blockIdx.y]; } else { lo = 0; hi = whole_len; }
+    // 16-byte granules of the absolute offsets, clipped to the window
+    const uint64_t g0 = (lo & ~15ull) + ((uint64_t)blockIdx.x * 256 + threadIdx.x) * 16;
+    if (g0 >= hi) return;
+    if (g0 >= lo && g0 + 16 <= hi && (((uintptr_t)ref | (uintptr_t)nref) & 15) == 0) {
+        uint4 v = *reinterpret_cast<const uint4 *>(ref + g0);
+        uint32_t *w = &v.x;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t x = w[k], o = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) o |= (uint32_t)norm_base((uint8_t)(x >> (8 * j))) << (8 * j);
+            w[k] = o;
+        }
+        *reinterpret_cast<uint4 *>(nref + g0) = v;
+    } else {
+        for (uint64_t i = g0 < lo ? lo : g0; i < g0 + 16 && i < hi; i++) nref[i] = norm_base(ref[i]);
+    }
+}
+
+// ---- k_rec_simple: one THREAD per read, for the reads whose walk is trivial ------------------------
+//   * unmapped reads                                  (bases into BA, score array into QS)
+//   * mapped reads without alignment start            (no features)
+//   * "<len>M" (or = / X) over the whole read, inside the reference window: substitutions only
+// and only under quality models without base categories (so that force-preserve is a per-read decision and no sparse
+// Q features can occur).  Everything else goes to the list of the general walk.  Neighbouring threads own neighbouring
+// reads: the per-read tables are read and the per-read results written coalesced, and the bases / reference bytes
+// come as aligned words (one funnel shift re-aligns the reference against the read).
+struct SimpleRead {
+    bool live, simple, mapped, forced, window;   // window: compare against the reference
+    uint8_t force, rfl, mapq;
+    uint32_t rlen;
+    int32_t pos;
+    uint64_t lo;
+};
+__device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolSet &ps, uint64_t r, uint32_t c, bool live)
+{
+    SimpleRead s;
+    s.live = live; s.simple = false; s.mapped = false; s.forced = false; s.window = false;
+    s.force = 0; s.rfl = 0; s.mapq = 0; s.rlen = 0; s.pos = 0; s.lo = 0;
+    if (!live) return s;
+    s.lo = a.read_off[r];
+    const uint64_t rlen = a.read_off[r + 1] - s.lo;
+    const uint64_t c0 = a.cigar_off[r], c1 = a.cigar_off[r + 1];
+    s.pos = a.pos[r];
+    const uint16_t flag = a.flag[r];
+    s.mapq = a.mapq[r];
+    s.rfl = a.rflags ? a.rflags[r] : 0;
+    const bool has_quals = !(s.rfl & CRAMGPU_RF_NO_QUALS);
+    s.mapped = !(flag & SAM_UNMAPPED);
+    if (ps.per_base || rlen >= (1ull << 31)) return s;
+    bool qposs = false;
+    if (ps.n < 0) s.force = has_quals ? 3 : 0;
+    else if (has_quals) {
+        bool f = false;
+        for (int k = 0; k < ps.n; k++) {
+            const cramgpu_qs_policy &p = ps.p[k];
+            if (!read_in_category(p, flag, s.mapq)) continue;
+            f = p.treatment != 2;
+            qposs = qposs || p.treatment != 2;
+        }
+        s.force = (f ? 1 : 0) | 2;
+    }
+    s.forced = s.force & 1;
+    s.rlen = (uint32_t)rlen;
+    if (!s.mapped || s.pos == 0) { s.simple = true; return s; }
+    if (!s.forced && qposs) return s;                                   // sparse Q features possible
+    if (c1 - c0 != 1 || rlen == 0) return s;
+    const uint32_t cw = a.cigar[c0], op = cw & 15;
+    if (!(op == OP_M || op == OP_EQ || op == OP_X) || (uint64_t)(cw >> 4) != rlen) return s;
+    if ((uint64_t)(s.pos - 1) + rlen > a.ref_len[c]) return s;           // overhang ('N' fill): general walk
+    s.simple = true; s.window = true;
+    return s;
+}
+
 template <bool WRITE>
-__global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
+__global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
 {
     const uint32_t lane = threadIdx.x & 31;
-    // grid (read groups, containers): the container comes from blockIdx.y; a flat grid (more than 65 535 containers)
-    // falls back to a binary search per warp
-    uint64_t r; uint32_t c;
+    uint64_t r; uint32_t c; bool live;
     if (gridDim.y > 1 || a.n_containers == 1) {
         c = blockIdx.y;
-        r = a.cont_off[c] + (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-        if (r >= a.cont_off[c + 1]) return;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.cont_off[c + 1];
     } else {
-        r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-        if (r >= a.n_reads) return;
-        c = container_of(a.cont_off, a.n_containers, r);
+        r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.n_reads;
+        c = live ? container_of(a.cont_off, a.n_containers, r) : 0;
     }
+    const SimpleRead s = classify_read(a, ps, r, c, live);
+    if (!WRITE) {
+        // the others: appended to the list, one atomic per warp
+        const bool cx = live && !s.simple;
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, cx);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(a.clist_n, (unsigned long long)__popc(m));
+            base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+            if (cx) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); a.clist_r[k] = r; a.clist_c[k] = c; }
+        }
+    }
+    if (!s.simple) return;
+
+    const uint64_t N = a.n_reads;
+    const uint32_t rlen = s.rlen;
+    uint32_t n_feat = 0, n_fp = 0;
+    // write-pass bases
+    const uint64_t *B = WRITE ? a.base + (size_t)c * NCNT : nullptr;
+    uint64_t fbase = 0;
+    uint32_t nf = 0;
+    uint8_t *sFC = nullptr, *sFP = nullptr, *sBS = nullptr;
+    const uint8_t *codes = nullptr;
+    if (WRITE) {
+        const uint32_t here = a.cnt[(size_t)C_NFEAT * N + r];
+        const uint64_t next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * N + r + 1] : a.totals[(size_t)c * NCNT + C_NFEAT];
+        nf = (uint32_t)(next - here);
+        fbase = B[C_NFEAT] + here;
+        a.feat_off[r] = fbase;
+        a.read_qs_off[r] = s.forced ? B[C_QS] + a.cnt[(size_t)C_QS * N + r] : ~0ull;
+        const bool ba = !s.mapped && !(s.rfl & CRAMGPU_RF_NO_BASES);
+        const uint64_t bao = ba ? B[C_BA] + a.cnt[(size_t)C_BA * N + r] : ~0ull;
+        a.read_ba_off[r] = bao;
+        if (ba) copy_bytes(a.streams + bao, a.bases + s.lo, rlen, IdW(), IdB());          // [Writer.java:254-256]
+        if (s.mapped) {
+            itf8_put(a.streams + B[C_FN] + a.cnt[(size_t)C_FN * N + r], nf);
+            itf8_put(a.streams + B[C_MQ] + a.cnt[(size_t)C_MQ * N + r], s.mapq);
+        }
+        if (nf) {
+            sFC = a.streams + B[C_FC] + a.cnt[(size_t)C_FC * N + r];
+            sFP = a.streams + B[C_FP] + a.cnt[(size_t)C_FP * N + r];
+            sBS = a.streams + B[C_BS] + a.cnt[(size_t)C_BS * N + r];
+            codes = a.codes + (size_t)c * 32;
+        }
+    }
+
+    if (s.window && (!WRITE || nf)) {
+        // read words (aligned) against the reference bytes at the same read offsets
+        const uint8_t *A = a.bases + s.lo;
+        const uint32_t sa = (uint32_t)((uintptr_t)A & 3);
+        const uint32_t *aw = reinterpret_cast<const uint32_t *>(A - sa);
+        const uint8_t *Bs = a.nref + a.ref_off[c] + (uint64_t)(s.pos - 1) - sa;     // nref has 16 bytes of slack on both sides
+        const uint32_t sb = (uint32_t)((uintptr_t)Bs & 3), sb8 = sb * 8;
+        const uint32_t *bw = reinterpret_cast<const uint32_t *>(Bs - sb);
+        const uint32_t nwords = (sa + rlen + 3) >> 2, tail = (sa + rlen) & 3;
+        uint32_t bprev = bw[0];
+        int32_t prev = 0;
+        for (uint32_t k = 0; k < nwords; k++) {
+            const uint32_t av = aw[k], bnext = bw[k + 1];
+            const uint32_t bv = __funnelshift_r(bprev, bnext, sb8);
+            bprev = bnext;
+            uint32_t x = av ^ bv;
+            if (k == 0) x &= 0xFFFFFFFFu << (8 * sa);
+            if (k == nwords - 1 && tail) x &= (1u << (8 * tail)) - 1u;
+            while (x) {                                                  // a substitution per differing byte [:306-330]
+                const uint32_t j = (uint32_t)(__ffs(x) - 1) >> 3;
+                x &= ~(0xFFu << (8 * j));
+                const uint8_t b = (uint8_t)(av >> (8 * j)), refb = (uint8_t)(bv >> (8 * j));
+                const int32_t mypos = (int32_t)(4 * k + j - sa) + 1;
+                const uint32_t d = (uint32_t)(mypos - prev);
+                prev = mypos;
+                const int ri = base_index(refb), bi = base_index(b);
+                if (!WRITE) {
+                    if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
+                } else {
+                    const uint64_t fi = fbase + n_feat;
+                    const uint8_t code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;
+                    a.f_op[fi] = 'X'; a.f_pos[fi] = mypos; a.f_val[fi] = code; a.f_aux[fi] = (int32_t)b | ((int32_t)refb << 8);
+                    sFC[n_feat] = 'X';
+                    itf8_put(sFP + n_fp, d);
+                    sBS[n_feat] = code;
+                }
+                n_feat++; n_fp += itf8_len(d);
+            }
+        }
+    }
+
+    if (!WRITE) {
+        a.force[r] = s.force;
+        uint32_t *cn = a.cnt + r;
+        if (s.mapped) { cn[C_FN * N] = itf8_len(n_feat); cn[C_MQ * N] = itf8_len(s.mapq); }
+        else if (!(s.rfl & CRAMGPU_RF_NO_BASES) && rlen) cn[C_BA * N] = rlen;
+        if (s.forced && rlen) cn[C_QS * N] = rlen;
+        if (n_feat) { cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_NFEAT * N] = n_feat; cn[C_BS * N] = n_feat; }
+    } else if (s.forced && ps.n < 0) {
+        // lossless: the preserved array is the record's own qualities [Writer.java:250-251,257-258]
+        copy_bytes(a.streams + B[C_QS] + a.cnt[(size_t)C_QS * N + r], a.quals + s.lo, rlen, IdW(), IdB());
+    }
+}
+
+// the general walk of one read by one warp (any CIGAR, any policy)
+template <bool WRITE>
+__device__ __forceinline__ void walk_read(const RecArgs &a, const PolSet &ps, const uint64_t r, const uint32_t c, const uint32_t lane)
+{
     const uint8_t *ref = a.ref + a.ref_off[c];
     const int64_t ref_len = (int64_t)a.ref_len[c];
     const uint64_t lo = a.read_off[r];
@@ -261,47 +489,6 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
                 if (lane == 0) a.read_ba_off[r] = (uint64_t)(sBA - a.streams);
             }
             n_ba += (uint32_t)rlen;
-        }
-    } else if (hasfeat && c1 - c0 == 1 && !q_feats && rlen > 0 && (a.cigar[c0] & 15) != OP_I && (a.cigar[c0] & 15) != OP_S &&
-               consumes_read(a.cigar[c0] & 15) && (int64_t)(a.cigar[c0] >> 4) == rlen) {
-        // ---- fast path: "<len>M" (or = / X) over the whole read, no sparse quality features.  Same result as the general
-        //      walk below, a fraction of its instructions: only substitutions can occur.
-        const uint8_t *codes = WRITE ? a.codes + (size_t)c * 32 : nullptr;
-        const int64_t rp0 = (int64_t)pos - 1;
-        for (int64_t i0 = 0; i0 < rlen; i0 += 32) {
-            const int64_t i = i0 + lane;
-            const bool in = i < rlen;
-            const uint8_t b = in ? rb[i] : 0;
-            const int64_t rp = rp0 + i;
-            const uint8_t refb = norm_base((in && rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N');   // [:306-308]
-            const bool isX = in && b != refb;
-            const uint32_t bX = __ballot_sync(0xFFFFFFFFu, isX);
-            if (bX) {
-                const uint32_t lt = (1u << lane) - 1u;
-                const int32_t mypos = (int32_t)i + 1;
-                const uint32_t below = bX & lt;
-                const int32_t pprev = below ? (int32_t)(i0 + (31 - __clz(below))) + 1 : prev;
-                const uint32_t dF = isX ? (uint32_t)(mypos - pprev) : 0;
-                const uint32_t lF = isX ? itf8_len(dF) : 0;
-                uint32_t fp_tot, fp_off = warp_excl_scan_u32(lF, lane, fp_tot);
-                if (isX) {
-                    const int ri = base_index(refb), bi = base_index(b);
-                    if (!WRITE) {
-                        if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
-                    } else {
-                        const uint32_t k = n_feat + __popc(below);
-                        const uint64_t fi = fbase + k;
-                        const uint8_t code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;
-                        a.f_op[fi] = 'X'; a.f_pos[fi] = mypos; a.f_val[fi] = code; a.f_aux[fi] = (int32_t)b | ((int32_t)refb << 8);
-                        sFC[k] = 'X';
-                        itf8_put(sFP + n_fp + fp_off, dF);
-                        sBS[n_bs + __popc(below)] = code;
-                    }
-                }
-                const uint32_t nx = __popc(bX);
-                n_feat += nx; n_bs += nx; n_fp += fp_tot;
-                prev = (int32_t)(i0 + (31 - __clz(bX))) + 1;
-            }
         }
     } else if (hasfeat) {
         const uint8_t *codes = WRITE ? a.codes + (size_t)c * 32 : nullptr;
@@ -440,6 +627,16 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
         itf8_put(a.streams + B[C_FN] + a.cnt[(size_t)C_FN * a.n_reads + r], n_feat);
         itf8_put(a.streams + B[C_MQ] + a.cnt[(size_t)C_MQ * a.n_reads + r], mapq);
     }
+}
+
+// general walk over the reads k_rec_simple left aside: warps stride over the list
+template <bool WRITE>
+__global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t n = *a.clist_n, step = (uint64_t)gridDim.x * 4;
+    for (uint64_t i = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); i < n; i += step)
+        walk_read<WRITE>(a, ps, a.clist_r[i], a.clist_c[i], lane);
 }
 
 // Forced arrays under a lossy model need the per-base scores again; done by a second small kernel so that the walk above
@@ -623,6 +820,7 @@ struct NormArgs {
     const uint8_t *f_op; const int32_t *f_pos, *f_val, *f_aux; const uint8_t *payload;
     const uint8_t *qs; const uint64_t *read_qs_off; const uint8_t *ba; const uint64_t *read_ba_off;
     uint8_t *bases, *quals, *qual_star; int32_t *status;
+    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;            // reads left to the general kernel
 };
 
 // base with rank `code` for normalised reference base r: SubstitutionMatrix(byte[]) / base() [:59-..,177]
@@ -641,20 +839,72 @@ __device__ __forceinline__ uint8_t matrix_base(const uint8_t *m, uint8_t refb, i
     return out;
 }
 
-// one warp per record
-__global__ void __launch_bounds__(128) k_norm(NormArgs a)
+// Records whose restoration is a plain copy, one THREAD per record: no read features and inside the reference region
+// (bases = the region bytes as they are, :346-362), or unmapped (bases from BA), or unknown bases; and a stored score
+// array (FORCE_QS).  The others go to the list of k_norm.
+__global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
 {
     const uint32_t lane = threadIdx.x & 31;
-    uint64_t r; uint32_t c;
+    uint64_t r; uint32_t c; bool live;
     if (gridDim.y > 1 || a.n_containers == 1) {
         c = blockIdx.y;
-        r = a.cont_off[c] + (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-        if (r >= a.cont_off[c + 1]) return;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.cont_off[c + 1];
     } else {
-        r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-        if (r >= a.n_reads) return;
-        c = container_of(a.cont_off, a.n_containers, r);
+        r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.n_reads;
+        c = live ? container_of(a.cont_off, a.n_containers, r) : 0;
     }
+    bool simple = false;
+    uint64_t lo = 0, rlen = 0, qo = ~0ull;
+    const uint8_t *src = nullptr;              // where the bases come from (nullptr: nothing to write)
+    if (live) {
+        lo = a.read_off[r];
+        rlen = a.read_off[r + 1] - lo;
+        const uint8_t rfl = a.rflags[r];
+        qo = a.read_qs_off[r];
+        simple = (rfl & CRAMGPU_NF_FORCE_QS) && rlen < (1ull << 31);
+        if (rfl & CRAMGPU_NF_UNKNOWN_BASES) {
+        } else if (rfl & CRAMGPU_NF_UNMAPPED) {
+            const uint64_t bo = a.read_ba_off[r];
+            if (bo != ~0ull) src = a.ba + bo;
+        } else if (rlen > 0) {
+            const int64_t o = (int64_t)a.pos[r] - 1 - a.win_start0[c];
+            if (a.feat_off[r] != a.feat_off[r + 1] || o < 0 || (uint64_t)o + rlen > a.win_len[c]) simple = false;
+            else src = a.ref + a.win_off[c] + o;
+        }
+    }
+    const bool cx = live && !simple;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, cx);
+    if (m) {
+        unsigned long long base = 0;
+        if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(a.clist_n, (unsigned long long)__popc(m));
+        base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+        if (cx) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); a.clist_r[k] = r; a.clist_c[k] = c; }
+    }
+    if (!simple) return;
+    if (src) copy_bytes(a.bases + lo, src, (uint32_t)rlen, IdW(), IdB());
+    // restoreQualityScores with a stored array (:306-333): 0xFF = missing -> default score
+    const uint32_t dflt = '?' - '!';
+    uint32_t present = 0;
+    if (qo != ~0ull) {
+        auto xw = [&](uint32_t w) -> uint32_t {
+            const uint32_t miss = __vcmpeq4(w, 0xFFFFFFFFu);
+            present |= ~miss;
+            return (w & ~miss) | (miss & (dflt * 0x01010101u));
+        };
+        auto xb = [&](uint8_t b) -> uint8_t { if (b == 0xFF) return (uint8_t)dflt; present = 1; return b; };
+        copy_bytes(a.quals + lo, a.qs + qo, (uint32_t)rlen, xw, xb);
+    } else {
+        copy_bytes(a.quals + lo, a.quals + lo, (uint32_t)rlen, [&](uint32_t) { return dflt * 0x01010101u; }, [&](uint8_t) { return (uint8_t)dflt; });
+    }
+    a.qual_star[r] = present == 0;             // missingScores == scores.length
+    a.status[r] = CRAMGPU_OK;
+}
+
+// the general restoration of one record by one warp
+__device__ __forceinline__ void norm_read(const NormArgs &a, const uint64_t r, const uint32_t c, const uint32_t lane)
+{
     const uint8_t *ref = a.ref + a.win_off[c];
     const int64_t ref_len = (int64_t)a.win_len[c], off0 = a.win_start0[c];
     const uint8_t *mtx = a.matrix + (size_t)c * 8;
@@ -768,6 +1018,14 @@ __global__ void __launch_bounds__(128) k_norm(NormArgs a)
     }
 }
 
+__global__ void __launch_bounds__(128) k_norm(NormArgs a)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t n = *a.clist_n, step = (uint64_t)gridDim.x * 4;
+    for (uint64_t i = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); i < n; i += step)
+        norm_read(a, a.clist_r[i], a.clist_c[i], lane);
+}
+
 
 // ------------------------------------------------------------------------------------------------ host side
 
@@ -879,8 +1137,10 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_roff = cv.take(8 * (size_t)nc), o_rlen = cv.take(8 * (size_t)nc);
     size_t o_cnt = cv.take(4 * (size_t)NCNT * n), o_force = cv.take(n);
-    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16);
+    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16), o_cln = cv.take(16);
     size_t o_zero_end = cv.off;
+    size_t o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n);
+    size_t o_nref = cv.take(R->ref_total + 512) + 256;                          // slack on both sides of the normalised copy
     size_t o_codes = cv.take(32 * (size_t)nc), o_matrix = cv.take(8 * (size_t)nc);
     size_t o_totals = cv.take(8 * (size_t)NCNT * nc), o_base = cv.take(8 * (size_t)NCNT * nc);
     size_t o_soff = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc), o_slen = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc);
@@ -908,11 +1168,26 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.codes = S + o_codes; a.base = (const uint64_t *)(S + o_base); a.status = (int32_t *)(S + o_status);
     uint64_t *d_totals = (uint64_t *)(S + o_totals), *d_soff = (uint64_t *)(S + o_soff), *d_slen = (uint64_t *)(S + o_slen);
     uint64_t *d_grand = (uint64_t *)(S + o_grand);
+    a.nref = S + o_nref; a.totals = d_totals;
+    a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
 
-    uint64_t max_reads = 0;
-    for (uint32_t c = 0; c < nc; c++) max_reads = std::max(max_reads, R->cont_off[c + 1] - R->cont_off[c]);
-    const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);
-    LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<grid, 128, 0, st>>>(a, ps));
+    uint64_t max_reads = 0, max_win = 0, sum_win = 0;
+    for (uint32_t c = 0; c < nc; c++) {
+        max_reads = std::max(max_reads, R->cont_off[c + 1] - R->cont_off[c]);
+        max_win = std::max(max_win, R->ref_len[c]); sum_win += R->ref_len[c];
+    }
+    // normalised reference: the windows, or the whole array when the windows add up to more than that
+    if (!ps.per_base) {
+        if (nc <= 65535 && sum_win < R->ref_total)
+            LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)((max_win + 31) / 4096 + 1), nc), 256, 0, st>>>(R->ref, S + o_nref, a.ref_off, a.ref_len, 0));
+        else
+            LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)(R->ref_total / 4096 + 1), 1), 256, 0, st>>>(R->ref, S + o_nref, nullptr, nullptr, R->ref_total));
+    }
+    const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);      // warp per read
+    const dim3 sgrid = nc <= 65535 ? dim3((uint32_t)((max_reads + 127) / 128), nc) : dim3((uint32_t)((n + 127) / 128), 1);   // thread per read
+    const uint32_t wgrid = (uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16);
+    LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false><<<sgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<wgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
     LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
     LAUNCH(ctx, st, "k_rec_layout", k_rec_layout<<<1, 1024, 0, st>>>(d_totals, nc, (uint64_t *)(S + o_base), d_soff, d_slen, d_grand));
@@ -943,7 +1218,8 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.f_op = O + q_op; a.f_pos = (int32_t *)(O + q_pos); a.f_val = (int32_t *)(O + q_val); a.f_aux = (int32_t *)(O + q_aux);
     a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.streams = O + q_str;
     a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
-    LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<grid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true><<<sgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<wgrid, 128, 0, st>>>(a, ps));
     if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
     CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(ctx, cudaGetLastError());
@@ -1059,6 +1335,7 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
         if (in->win_off[c] + in->win_len[c] > in->ref_total) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "reference region of container %u outside ref", c);
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_woff = cv.take(8 * (size_t)nc), o_wlen = cv.take(8 * (size_t)nc), o_ws = cv.take(8 * (size_t)nc);
+    size_t o_cln = cv.take(16), o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n);
     if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
     if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, 8 * (size_t)(4 * nc + 1) + 256)) return rc;
@@ -1080,8 +1357,11 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
     a.bases = d_bases; a.quals = d_quals; a.qual_star = d_star; a.status = d_status;
     uint64_t max_reads = 0;
     for (uint32_t c = 0; c < nc; c++) max_reads = std::max(max_reads, in->cont_off[c + 1] - in->cont_off[c]);
-    const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);
-    LAUNCH(ctx, st, "k_norm", k_norm<<<grid, 128, 0, st>>>(a));
+    a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_cln, 0, 16, st));
+    const dim3 sgrid = nc <= 65535 ? dim3((uint32_t)((max_reads + 127) / 128), nc) : dim3((uint32_t)((n + 127) / 128), 1);
+    LAUNCH(ctx, st, "k_norm_simple", k_norm_simple<<<sgrid, 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_norm", k_norm<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     return CRAMGPU_OK;
 }
