@@ -417,22 +417,28 @@ def run_ours(args):
     n_cont = args.containers
     nu = min(UNIQUE, n_cont)
     ref, rd, extra = unique_containers(nu, 1000 + 17 * rank)
-    n_lanes = max(1, min(args.lanes, n_cont))
-    share = [n_cont // n_lanes + (1 if i < n_cont % n_lanes else 0) for i in range(n_lanes)]
-    groups = [dist.new_group() if world > 1 else None for _ in range(n_lanes)]
-    lanes = [Lane(i, share[i], ref, rd, extra, nu, dev, rank, world, groups[i]) for i in range(n_lanes)]
+    # Software pipeline over consecutive steps: `depth` contexts, each with its own stream and the whole batch; step i runs
+    # on context i % depth.  The order-1 decoder is a recurrence per rANS state -- a few warps per SM for tens of
+    # milliseconds, whatever the batch size -- so the encode of step i+1 (record kernels, histograms, encoder) runs beside
+    # the decode of step i instead of after it, the way consecutive batches of a whole-genome stream would be fed.
+    # Two host locks keep at most one context in each phase.
+    n_lanes = depth = max(1, args.pipeline)
+    groups = [dist.new_group() if world > 1 else None for _ in range(depth)]
+    lanes = [Lane(i, n_cont, ref, rd, extra, nu, dev, rank, world, groups[i]) for i in range(depth)]
     for ln in lanes:
         ln.prepare()
-    n_reads = sum(ln.n_reads for ln in lanes)
+    n_reads = lanes[0].n_reads
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    enc_lock, dec_lock = threading.Lock(), threading.Lock()
+
     def run_steps(k):
-        """every lane runs k steps on its own stream, driven by its own host thread (the C calls release the GIL)"""
-        if n_lanes == 1:
+        """k steps in all; with depth > 1 each context is driven by its own host thread (the C calls release the GIL)"""
+        if depth == 1:
             lanes[0].steps(k)
             return
         errs = []
@@ -440,10 +446,11 @@ def run_ours(args):
         def work(ln, i):
             try:
                 torch.cuda.set_device(local)
-                # lanes start staggered so that one lane's latency-bound coder kernels (few warps per SM) run beside the
-                # others' record kernels instead of all lanes doing the same phase at once
-                time.sleep(i * args.stagger_ms * 1e-3)
-                ln.steps(k)
+                for _ in range(i, k, depth):
+                    with enc_lock:
+                        ln.encode()
+                    with dec_lock:
+                        ln.decode()
             except Exception as e:      # noqa: BLE001
                 errs.append(e)
         th = [threading.Thread(target=work, args=(ln, i)) for i, ln in enumerate(lanes)]
@@ -493,12 +500,12 @@ def run_ours(args):
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
-        raw_bytes = sum(ln.raw_bytes for ln in lanes); comp_bytes = sum(ln.comp_bytes for ln in lanes)
-        o1_raw = raw_bytes - sum(ln.raw_o0 for ln in lanes)
+        raw_bytes = lanes[0].raw_bytes; comp_bytes = lanes[0].comp_bytes
+        o1_raw = raw_bytes - lanes[0].raw_o0
         comp1 = comp_bytes * (o1_raw / raw_bytes)
         algo = {'k_enc1': o1_raw + comp1, 'k_dec1': o1_raw + comp1, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
-                'k_rec_walk_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_walk_write': n_reads * (3 * READ_LEN + 40.0),
-                'k_norm': n_reads * (3 * READ_LEN + 20.0), 'k_pack': 2 * comp_bytes}
+                'k_rec_simple_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_simple_write': n_reads * (2 * READ_LEN + 60.0),
+                'k_norm_simple': n_reads * (4 * READ_LEN + 40.0), 'k_pack': 2 * comp_bytes}
         ab = algo.get(top)
         # kavg sums the lanes' launches, which overlap in time; the per-launch figure is what the roofline wants
         per_launch_ms = kavg[top] / max(kcount[top], 1)
@@ -507,15 +514,15 @@ def run_ours(args):
         rans_ms_enc = sum(v for k, v in kavg.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
         rans_ms_dec = sum(v for k, v in kavg.items() if k in ('k_dec_tables', 'k_dec0', 'k_dec1', 'k_dec1_big'))
         cfg = workload_config(args, n_cont)
-        cfg['lanes'] = '%d CUDA streams per GPU, each with its own share of the containers' % n_lanes
+        cfg['pipeline'] = ('%d contexts/streams per GPU, step i on context i %% %d: encode of step i+1 overlaps decode of step i' % (depth, depth)) if depth > 1 else 'none: one stream, phases back to back'
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
             'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
             'dtype': 'u8/i32 integer (+f64 in the order-1 frequency normalisation)', 'data': 'synthetic', 'config': cfg,
             'rans': {'raw_GB_per_step_per_gpu': raw_bytes / 1e9, 'compressed_ratio': comp_bytes / raw_bytes,
-                     'encode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_enc / n_lanes * 1e-3) / 1e9,
-                     'decode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_dec / n_lanes * 1e-3) / 1e9,
-                     'qs_block_bytes': sum(ln.qs_bytes for ln in lanes) / n_cont, 'state_lanes_in_flight': int(4 * sum(ln.nblk for ln in lanes))},
+                     'encode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_enc * 1e-3) / 1e9,
+                     'decode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_dec * 1e-3) / 1e9,
+                     'qs_block_bytes': lanes[0].qs_bytes / n_cont, 'state_lanes_in_flight': int(4 * lanes[0].nblk)},
             'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
             'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
@@ -655,8 +662,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
     ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
-    ap.add_argument('--lanes', type=int, default=1, help='CUDA streams per GPU, each owning a share of the containers')
-    ap.add_argument('--stagger-ms', type=float, default=0.0, help='start offset between consecutive lanes')
+    ap.add_argument('--pipeline', type=int, default=2, help='contexts per GPU taking consecutive steps in turn (1 = no overlap of encode and decode)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -323,89 +323,228 @@ __global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc,
 }
 
 // k_dec1: lane k decodes the quarter starting at k*(n>>2); lane 3 also the remainder [D14.java:62-68].
-// Shared-memory path for blocks with <= DEC_MAXU distinct bytes.  Dynamic shared memory:
-//   uint8_t rows[8][DEC_MAXU][DEC_ROWB] | uint8_t ring[8][DEC_RINGB] | uint8_t ualpha[8][DEC_MAXU]
-#define DEC1_SMEM (8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + 8 * DEC_MAXU)
-__global__ void __launch_bounds__(32) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+// Shared-memory path for blocks with <= DEC_MAXU distinct bytes.  Two warps per CTA:
+//   warp 0  decoder: lane = state, 8 blocks; per step only the recurrence itself -- table search, state update,
+//           renormalisation from the group's byte ring -- and one byte store (the symbol RANK) into the out ring;
+//   warp 1  helper: keeps the 8 byte rings filled (cp.async), and turns the ranks of finished chunks into bytes that
+//           go to global memory as aligned 16-byte stores.
+// The warps meet once per chunk of DEC1_CH steps through two counters in shared memory (release / acquire).
+// Dynamic shared memory, see Dec1Smem.
+#define DEC1_CH 32                   // steps per chunk (<= 8 compressed bytes per step and group: 256 bytes per chunk)
+#define DEC1_SLOTS 4                 // out-ring chunks
+#define DEC1_RINGB 1024              // compressed-byte ring per group
+struct __align__(16) Dec1Smem {
+    uint8_t ring[8][DEC1_RINGB];                         // compressed bytes, per group (ring-size aligned)
+    uint8_t outr[DEC1_SLOTS][DEC1_CH][32];               // symbol ranks: [chunk slot][step][decoder lane]
+    uint8_t rows[8][(DEC_MAXU + 1) * DEC_ROWB + 8];      // +1 row: a corrupt table can point one row past the alphabet; 16-byte multiple
+    uint8_t alpha[8][DEC_MAXU + 16];
+    uint32_t cur[8];                                     // group cursors at the end of the last finished chunk
+    int32_t ready, done;                                 // last chunk decoded / last helper round finished
+};
+static_assert(((DEC_MAXU + 1) * DEC_ROWB + 8) % 16 == 0 && (DEC_MAXU * DEC_ROWB) % 16 == 0, "table rows are copied as 16-byte vectors");
+#define DEC1_SMEM (sizeof(Dec1Smem) + DEC1_RINGB)
+
+__device__ __forceinline__ void st_release_s32(int32_t *p, int32_t v)
+{
+    asm volatile("st.release.cta.shared.s32 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(v) : "memory");
+}
+__device__ __forceinline__ int32_t ld_acquire_s32(const int32_t *p)
+{
+    int32_t v;
+    asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t saddr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+
+// table reads (immutable while the kernel runs: the compiler may schedule them freely)
+__device__ __forceinline__ uint32_t lds_tab_u8(uint32_t saddr)
+{
+    uint32_t v;
+    asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_tab_u16(uint32_t saddr)
+{
+    uint32_t v;
+    asm("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+
+__global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
                                              const DecCompact *__restrict__ compact,
                                              const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
                                              int32_t *__restrict__ status)
 {
-    extern __shared__ __align__(16) uint8_t smem[];
-    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
-    uint32_t slot = blockIdx.x * 8 + g;
+    extern __shared__ uint8_t smem_raw[];
+    Dec1Smem &S = *reinterpret_cast<Dec1Smem *>(smem_raw + ((DEC1_RINGB - ((uint32_t)__cvta_generic_to_shared(smem_raw) & (DEC1_RINGB - 1))) & (DEC1_RINGB - 1)));
+    const uint32_t lane = threadIdx.x & 31, k = lane & 3u, g = lane >> 2;
+    // warp role as a value the compiler knows to be warp-uniform (votes inside the role branches then need no divergence checks)
+    const bool helper = __reduce_max_sync(0xFFFFFFFFu, threadIdx.x >> 5) != 0;
+    const uint32_t slot = blockIdx.x * 8 + g;
     bool have = slot < nslots;
-    uint32_t blk = have ? slots[slot] : 0;
-    BlockDesc d = desc[blk];
+    const uint32_t blk = have ? slots[slot] : 0;
+    const BlockDesc d = desc[blk];
     have = have && status[blk] == 0 && meta[blk].small == 1;
-    if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;
-    uint32_t n = have ? d.out_len : 0;
-    uint32_t q = n >> 2;
+    if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;            // both warps see the same flags
+    const uint32_t n = have ? d.out_len : 0;
+    const uint32_t q = n >> 2;
     uint8_t *out = d_out + d.out_off + (uint64_t)k * q;
-    uint32_t mylen = (k == 3) ? n - 3 * q : q;
+    const uint32_t mylen = (k == 3) ? n - 3 * q : q;
+    const uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, n - 3 * q);
+    const int32_t nchunks = (int32_t)((max_steps + DEC1_CH - 1) / DEC1_CH);
 
+    // tables of the 8 blocks (both warps copy), first ring fill and the 4 states (decoder)
     for (uint32_t gg = 0; gg < 8; gg++) {
-        uint32_t hv = __shfl_sync(0xFFFFFFFFu, (uint32_t)have, gg * 4);
-        uint32_t oi = __shfl_sync(0xFFFFFFFFu, d.o1_index, gg * 4);
-        if (!hv) continue;
+        const uint32_t hv = __shfl_sync(0xFFFFFFFFu, (uint32_t)have, gg * 4);
+        const uint32_t oi = __shfl_sync(0xFFFFFFFFu, d.o1_index, gg * 4);
+        if (!hv) {
+            // no block in this group: its lanes still run the loop, on empty contexts (coarse 0, cum[0] = 0, the ends 0xFFFF)
+            for (uint32_t i = threadIdx.x; i < DEC_MAXU * DEC_ROWB; i += 64) S.rows[gg][i] = (i % DEC_ROWB) < 130 ? 0 : 0xFF;
+            continue;
+        }
         const DecCompact *cp = compact + oi;
         const uint4 *src = reinterpret_cast<const uint4 *>(&cp->rows[0][0]);
-        uint4 *dst = reinterpret_cast<uint4 *>(smem + gg * DEC_MAXU * DEC_ROWB);
-        for (uint32_t i = lane; i < DEC_MAXU * DEC_ROWB / 16; i += 32) dst[i] = __ldg(src + i);
-        for (uint32_t i = lane; i < DEC_MAXU; i += 32) smem[8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + gg * DEC_MAXU + i] = cp->ualpha[i];
+        uint4 *dst = reinterpret_cast<uint4 *>(&S.rows[gg][0]);
+        for (uint32_t i = threadIdx.x; i < DEC_MAXU * DEC_ROWB / 16; i += 64) dst[i] = __ldg(src + i);
+        for (uint32_t i = threadIdx.x; i < DEC_MAXU; i += 64) S.alpha[gg][i] = cp->ualpha[i];
     }
-    const uint8_t *rows = smem + g * DEC_MAXU * DEC_ROWB;
-    uint8_t *ring = smem + 8 * DEC_MAXU * DEC_ROWB + g * DEC_RINGB;
-    const uint8_t *alpha = smem + 8 * DEC_MAXU * DEC_ROWB + 8 * DEC_RINGB + g * DEC_MAXU;
+    // the row past the alphabet: an empty context (coarse 0, cum[0] = 0, the ends 0xFFFF), like the unused rows k_dec_tables writes
+    for (uint32_t i = threadIdx.x; i < 8 * DEC_ROWB; i += 64) S.rows[i / DEC_ROWB][DEC_MAXU * DEC_ROWB + i % DEC_ROWB] = (i % DEC_ROWB) < 130 ? 0 : 0xFF;
+    if (threadIdx.x == 0) { S.ready = -1; S.done = -1; }
     Stream st;
     st.base = d_in + d.in_off;
     st.len4 = have ? (d.in_len + 3) & ~3u : 0;
-    uint32_t cur = have ? meta[blk].pay_off : 0;
-    st.wfetch = (cur >> 2) & ~3u;
-    stream_fetch(st, ring, k, cur);
-    cp_async_commit();
-    cp_async_wait_all();
-    __syncwarp();
-    uint32_t x = ring_le32(ring, cur + 4 * k);
-    cur += 16;
-    bool under = false;
-    const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
-
-    uint32_t steps = n - 3 * q;
-    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    // context 0 is byte 0; it has rank 0 whenever the block has a context-0 row (the encoder always writes one)
-    const uint8_t *row = rows;
-    for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
-        cp_async_wait_all();
-        __syncwarp();
-        stream_fetch(st, ring, k, cur);
+    const uint32_t cur0 = have ? meta[blk].pay_off : 0;
+    st.wfetch = cur0 >> 2;
+    uint8_t *ring = S.ring[g];
+    if (helper) {
+        // the ring holds the words [cur / 4, (cur + ring) / 4) of its group
+        const uint32_t tgt = (cur0 + DEC1_RINGB) >> 2, lim = st.len4 >> 2;
+        for (uint32_t w = st.wfetch + k; w < tgt; w += 4)
+            if (w < lim) cp_async4(ring + ((4 * w) & (DEC1_RINGB - 1)), st.base + 4ull * w);
+        st.wfetch = tgt;
         cp_async_commit();
-#pragma unroll 4
-        for (uint32_t u = 0; u < DEC_CHUNK; u++) {
-            uint32_t t = t0 + u;
-            bool act = t < mylen;
-            if (act) {
-                uint32_t m = x & (TOTFREQ - 1);
-                uint32_t s = row[m >> 5];                                           // first candidate rank
-                const uint16_t *cum = reinterpret_cast<const uint16_t *>(row + 128) + s;
-                uint32_t c0 = cum[0], c1 = cum[1], c2 = cum[2], c3 = cum[3];        // start of s, ends of s, s+1, s+2
-                bool a1 = m >= c1, a2 = m >= c2, a3 = m >= c3;
-                uint32_t C = a3 ? c3 : a2 ? c2 : a1 ? c1 : c0;
-                uint32_t E = a3 ? 0u : a2 ? c3 : a1 ? c2 : c1;
-                s += (uint32_t)a1 + (uint32_t)a2 + (uint32_t)a3;
-                if (a3) {                                                           // rare: more than three short ranges in a row
-                    while (m >= (E = cum[(uint32_t)a1 + (uint32_t)a2 + (uint32_t)a3 + 1])) { C = E; s++; cum++; if (s + 1 >= DEC_MAXU) break; }
-                }
-                out[t] = alpha[s];
-                x = (E - C) * (x >> TF_SHIFT) + m - C;                               // [Decoding.java:35-48]
-                row = rows + s * DEC_ROWB;                                           // context of the next symbol
-            }
-            x = renorm_ring(x, act, ring, cur, lm, gm);
-        }
-        if (cur > d.in_len) under = true;
+        cp_async_wait_all();
     }
-    if (have && (under || cur > d.in_len)) status[blk] = CRAMGPU_ERR_CORRUPT;
+    __syncthreads();
+
+    if (!helper) {
+        // ------------------------------------------------------------------------------ decoder warp
+        uint32_t x = ring[(cur0 + 4 * k) & (DEC1_RINGB - 1)] | (ring[(cur0 + 4 * k + 1) & (DEC1_RINGB - 1)] << 8) |
+                     (ring[(cur0 + 4 * k + 2) & (DEC1_RINGB - 1)] << 16) | ((uint32_t)ring[(cur0 + 4 * k + 3) & (DEC1_RINGB - 1)] << 24);
+        uint32_t cur = cur0 + 16;
+        const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
+        const uint32_t rb = (uint32_t)__cvta_generic_to_shared(ring);            // aligned to the ring size
+        const uint32_t rows = (uint32_t)__cvta_generic_to_shared(&S.rows[g][0]);
+        uint32_t row = rows;                  // context 0 is byte 0, rank 0 whenever the block has a context-0 row
+        for (int32_t c = 0; c < nchunks; c++) {
+            // the helper must be done with round c-2: stream bytes of this chunk staged (<= 256 per chunk), out slot free
+            if (c >= 2) while (ld_acquire_s32(&S.done) < c - 2) {}
+            uint8_t *orow = &S.outr[c & (DEC1_SLOTS - 1)][0][lane];
+            const uint32_t t0 = (uint32_t)c * DEC1_CH;
+            uint32_t rem = mylen > t0 ? mylen - t0 : 0;                          // steps this lane still owes
+            for (uint32_t uo = 0; uo < DEC1_CH; uo += 8, rem = rem > 8 ? rem - 8 : 0, orow += 8 * 32) {
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const bool act = u < rem;
+                    const uint32_t m = x & (TOTFREQ - 1);
+                    uint32_t r = lds_tab_u8(row + (m >> 5));                        // first candidate rank
+                    const uint32_t ca = row + 2 * r;
+                    const uint32_t c0 = lds_tab_u16(ca + 128), c1 = lds_tab_u16(ca + 130);   // start of r, end of r
+                    const uint32_t c2 = lds_tab_u16(ca + 132), c3 = lds_tab_u16(ca + 134);   // ends of r+1, r+2
+                    const bool a1 = m >= c1, a2 = m >= c2, a3 = m >= c3;
+                    uint32_t C = a2 ? (a3 ? c3 : c2) : (a1 ? c1 : c0);
+                    uint32_t E = a2 ? c3 : (a1 ? c2 : c1);
+                    r += a2 ? (a3 ? 3u : 2u) : (a1 ? 1u : 0u);
+                    if (__any_sync(0xFFFFFFFFu, a3)) {                              // rare: more than three short ranges in a row
+                        uint32_t pa = ca + 136;
+                        bool go = a3;
+                        while (__any_sync(0xFFFFFFFFu, go)) {                       // ends at the 0xFFFF padding at the latest
+                            const uint32_t e = lds_tab_u16(pa);
+                            if (go) { if (m >= e) { C = e; r++; } else { E = e; go = false; } }
+                            pa += 2;
+                        }
+                    }
+                    orow[u * 32] = (uint8_t)r;
+                    x = (E - C) * (x >> TF_SHIFT) + m - C;                          // [Decoding.java:35-48]; lanes past their end idle on garbage
+                    row = rows + r * DEC_ROWB;                                      // context of the next symbol
+                    // renormalise, lanes of a group in the order 0,1,2,3 [Decoding.java:84-90]
+                    const bool n1 = act && x < RANS_L;
+                    const bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
+                    const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1);
+                    if (__any_sync(0xFFFFFFFFu, n2)) {
+                        const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, n2);
+                        const uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
+                        const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1))), v1 = lds_u8(rb | ((at + 1) & (DEC1_RINGB - 1)));
+                        const uint32_t x1 = (x << 8) | v0;
+                        x = n2 ? ((x1 << 8) | v1) : (n1 ? x1 : x);
+                        cur += __popc(b1 & gm) + __popc(b2 & gm);
+                    } else {
+                        const uint32_t at = cur + __popc(b1 & lm);
+                        const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1)));
+                        x = __byte_perm(x, v0, n1 ? 0x2104u : 0x3210u);
+                        cur += __popc(b1 & gm);
+                    }
+                }
+            }
+            if (k == 0) S.cur[g] = cur;
+            __syncwarp();
+            if (lane == 0) st_release_s32(&S.ready, c);
+        }
+        if (have && cur > d.in_len) status[blk] = CRAMGPU_ERR_CORRUPT;       // ran past the compressed bytes
+    } else {
+        // ------------------------------------------------------------------------------ helper warp
+        const uint32_t ph = (uint32_t)((uintptr_t)out & 15);
+        const uint8_t *alpha = S.alpha[g];
+        const uint8_t *oring = &S.outr[0][0][lane];
+        const uint32_t lim = st.len4 >> 2;
+        for (int32_t c = 0; c <= nchunks; c++) {
+            // round c: chunk c is decoded (round nchunks only flushes the bytes held back for alignment)
+            if (c < nchunks) {
+                while (ld_acquire_s32(&S.ready) < c) __nanosleep(100);
+                // stream: the ring may now hold [cur, cur + ring) of its group
+                const uint32_t tgt = (S.cur[g] + DEC1_RINGB) >> 2;
+                for (uint32_t w = st.wfetch + k; w < tgt; w += 4)
+                    if (w < lim) cp_async4(ring + ((4 * w) & (DEC1_RINGB - 1)), st.base + 4ull * w);
+                if (tgt > st.wfetch) st.wfetch = tgt;
+                cp_async_commit();
+            }
+            // output: steps [32c - ph, 32c + 32 - ph) of this lane's quarter, as two aligned 16-byte granules
+            const int64_t tb = (int64_t)c * DEC1_CH - ph;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int64_t t0 = tb + 16 * j;
+                if (t0 + 16 <= 0 || t0 >= (int64_t)mylen) continue;
+                uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const int64_t t = t0 + i;
+                    const uint32_t tt = (uint32_t)t & (DEC1_SLOTS * DEC1_CH - 1);
+                    const uint32_t b = (t >= 0 && t < (int64_t)mylen) ? alpha[oring[tt * 32]] : 0;
+                    w[i >> 2] |= b << (8 * (i & 3));
+                }
+                if (t0 >= 0 && t0 + 16 <= (int64_t)mylen) *reinterpret_cast<uint4 *>(out + t0) = make_uint4(w[0], w[1], w[2], w[3]);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) {
+                        const int64_t t = t0 + i;
+                        if (t >= 0 && t < (int64_t)mylen) out[t] = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+                    }
+                }
+            }
+            if (c < nchunks) {
+                cp_async_wait_all();
+                __syncwarp();
+                if (lane == 0) st_release_s32(&S.done, c);
+            }
+        }
+    }
 }
 
 __device__ __forceinline__ uint32_t ld_byte(const uint8_t *p, uint32_t pos, uint32_t len, bool &under)
@@ -579,7 +718,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     if (n0 + n1) {
         LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, compact, meta, d_status));
         if (n1) {
-            ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_dec1", k_dec1<<<(n1 + 7) / 8, 32, DEC1_SMEM, hs>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, compact, meta, d_out, d_status)));
+            ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_dec1", k_dec1<<<(n1 + 7) / 8, 64, DEC1_SMEM, hs>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, compact, meta, d_out, d_status)));
             LAUNCH(ctx, st, "k_dec1_big", k_dec1_big<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
         }
         if (n0) {

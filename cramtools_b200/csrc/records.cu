@@ -54,7 +54,8 @@ struct RecArgs {
     // it leaves to the general walk
     const uint8_t *nref;         // normalizeBase(ref[i]) at the same offsets as ref
     const uint64_t *totals;      // [n_containers][NCNT] (write pass)
-    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;
+    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;      // reads of the general warp-per-read walk
+    uint64_t *tlist_r; uint32_t *tlist_c; unsigned long long *tlist_n;      // reads with several CIGAR operators (k_rec_multi)
 };
 
 __device__ __forceinline__ uint8_t norm_base(uint8_t b)      // cram/build/Utils.normalizeBase [Utils.java:31-49]
@@ -217,30 +218,31 @@ __global__ void __launch_bounds__(256) k_ref_norm(const uint8_t *__restrict__ re
     }
 }
 
-// ---- k_rec_simple: one THREAD per read, for the reads whose walk is trivial ------------------------
-//   * unmapped reads                                  (bases into BA, score array into QS)
-//   * mapped reads without alignment start            (no features)
-//   * "<len>M" (or = / X) over the whole read, inside the reference window: substitutions only
-// and only under quality models without base categories (so that force-preserve is a per-read decision and no sparse
-// Q features can occur).  Everything else goes to the list of the general walk.  Neighbouring threads own neighbouring
-// reads: the per-read tables are read and the per-read results written coalesced, and the bases / reference bytes
-// come as aligned words (one funnel shift re-aligns the reference against the read).
+// ---- k_rec_simple: one THREAD per read ------------------------------------------------------------
+// Every read under a quality model without base categories (lossless included): force-preserve is then a per-read
+// decision and no sparse Q features occur, so the walk over the CIGAR needs no cross-lane work at all.  Left to the list
+// of the general warp-per-read walk: models with base categories, reads that overhang their reference window, CIGARs
+// that do not add up to the read length, more than SIMPLE_MAX_OPS operators, unknown operators.
+// Neighbouring threads own neighbouring reads: the per-read tables are read and the per-read results written coalesced,
+// and M segments are compared as aligned words (one funnel shift re-aligns the reference against the read).
+#define SIMPLE_MAX_OPS 12
 struct SimpleRead {
-    bool live, simple, mapped, forced, window;   // window: compare against the reference
+    bool live, simple, mapped, forced, walk;      // walk: there is a CIGAR to walk
     uint8_t force, rfl, mapq;
-    uint32_t rlen;
+    uint32_t rlen, nops;
     int32_t pos;
-    uint64_t lo;
+    uint64_t lo, c0;
 };
 __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolSet &ps, uint64_t r, uint32_t c, bool live)
 {
     SimpleRead s;
-    s.live = live; s.simple = false; s.mapped = false; s.forced = false; s.window = false;
-    s.force = 0; s.rfl = 0; s.mapq = 0; s.rlen = 0; s.pos = 0; s.lo = 0;
+    s.live = live; s.simple = false; s.mapped = false; s.forced = false; s.walk = false;
+    s.force = 0; s.rfl = 0; s.mapq = 0; s.rlen = 0; s.nops = 0; s.pos = 0; s.lo = 0; s.c0 = 0;
     if (!live) return s;
     s.lo = a.read_off[r];
     const uint64_t rlen = a.read_off[r + 1] - s.lo;
-    const uint64_t c0 = a.cigar_off[r], c1 = a.cigar_off[r + 1];
+    s.c0 = a.cigar_off[r];
+    const uint64_t nops = a.cigar_off[r + 1] - s.c0;
     s.pos = a.pos[r];
     const uint16_t flag = a.flag[r];
     s.mapq = a.mapq[r];
@@ -264,14 +266,35 @@ __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolS
     s.rlen = (uint32_t)rlen;
     if (!s.mapped || s.pos == 0) { s.simple = true; return s; }
     if (!s.forced && qposs) return s;                                   // sparse Q features possible
-    if (c1 - c0 != 1 || rlen == 0) return s;
-    const uint32_t cw = a.cigar[c0], op = cw & 15;
-    if (!(op == OP_M || op == OP_EQ || op == OP_X) || (uint64_t)(cw >> 4) != rlen) return s;
-    if ((uint64_t)(s.pos - 1) + rlen > a.ref_len[c]) return s;           // overhang ('N' fill): general walk
-    s.simple = true; s.window = true;
+    if (nops == 0) { s.simple = true; return s; }
+    if (nops > SIMPLE_MAX_OPS || rlen == 0 || s.pos < 0) return s;
+    uint64_t nread = 0, nref = 0;
+    for (uint32_t i = 0; i < (uint32_t)nops; i++) {
+        const uint32_t cw = a.cigar[s.c0 + i], op = cw & 15, len = cw >> 4;
+        if (op > OP_X) return s;
+        if (consumes_read(op)) nread += len;
+        if (consumes_ref(op)) nref += len;
+    }
+    if (nread != rlen || (uint64_t)(s.pos - 1) + nref > a.ref_len[c]) return s;   // odd CIGAR / overhang ('N' fill): general walk
+    s.simple = true; s.walk = true; s.nops = (uint32_t)nops;
     return s;
 }
 
+__device__ __forceinline__ void rec_list_append(uint64_t *lr, uint32_t *lc, unsigned long long *ln, bool put, uint64_t r, uint32_t c, uint32_t lane)
+{
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, put);
+    if (!m) return;
+    unsigned long long base = 0;
+    if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(ln, (unsigned long long)__popc(m));      // one atomic per warp
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+    if (put) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); lr[k] = r; lc[k] = c; }
+}
+
+template <bool WRITE>
+__device__ __forceinline__ void simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c);
+
+// all reads in order; reads with several CIGAR operators are only classified here and done by k_rec_multi, so that the
+// lanes of a warp do the same kind of work
 template <bool WRITE>
 __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
 {
@@ -287,89 +310,142 @@ __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
         c = live ? container_of(a.cont_off, a.n_containers, r) : 0;
     }
     const SimpleRead s = classify_read(a, ps, r, c, live);
+    const bool multi = s.simple && s.nops > 1;
     if (!WRITE) {
-        // the others: appended to the list, one atomic per warp
-        const bool cx = live && !s.simple;
-        const uint32_t m = __ballot_sync(0xFFFFFFFFu, cx);
-        if (m) {
-            unsigned long long base = 0;
-            if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(a.clist_n, (unsigned long long)__popc(m));
-            base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
-            if (cx) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); a.clist_r[k] = r; a.clist_c[k] = c; }
-        }
+        rec_list_append(a.clist_r, a.clist_c, a.clist_n, live && !s.simple, r, c, lane);
+        rec_list_append(a.tlist_r, a.tlist_c, a.tlist_n, multi, r, c, lane);
     }
-    if (!s.simple) return;
+    if (s.simple && !multi) simple_read<WRITE>(a, ps, s, r, c);
+}
 
+template <bool WRITE>
+__global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps)
+{
+    const uint64_t n = *a.tlist_n, step = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
+        const uint64_t r = a.tlist_r[i];
+        const uint32_t c = a.tlist_c[i];
+        simple_read<WRITE>(a, ps, classify_read(a, ps, r, c, true), r, c);
+    }
+}
+
+template <bool WRITE>
+__device__ __forceinline__ void simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c)
+{
     const uint64_t N = a.n_reads;
     const uint32_t rlen = s.rlen;
-    uint32_t n_feat = 0, n_fp = 0;
+    uint32_t n_feat = 0, n_fp = 0, n_bs = 0, n_dl = 0, n_ba = 0, n_sc = 0, n_rs = 0, n_hc = 0, n_pd = 0, n_pay = 0;
     // write-pass bases
     const uint64_t *B = WRITE ? a.base + (size_t)c * NCNT : nullptr;
-    uint64_t fbase = 0;
+    uint64_t fbase = 0, paybase = 0;
     uint32_t nf = 0;
-    uint8_t *sFC = nullptr, *sFP = nullptr, *sBS = nullptr;
+    uint8_t *sFC = nullptr, *sFP = nullptr, *sBS = nullptr, *sDL = nullptr, *sBA = nullptr, *sSC = nullptr, *sRS = nullptr,
+            *sHC = nullptr, *sPD = nullptr;
     const uint8_t *codes = nullptr;
     if (WRITE) {
+        auto at = [&](int k) -> uint64_t { return B[k] + a.cnt[(size_t)k * N + r]; };
         const uint32_t here = a.cnt[(size_t)C_NFEAT * N + r];
         const uint64_t next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * N + r + 1] : a.totals[(size_t)c * NCNT + C_NFEAT];
         nf = (uint32_t)(next - here);
         fbase = B[C_NFEAT] + here;
         a.feat_off[r] = fbase;
-        a.read_qs_off[r] = s.forced ? B[C_QS] + a.cnt[(size_t)C_QS * N + r] : ~0ull;
+        a.read_qs_off[r] = s.forced ? at(C_QS) : ~0ull;
         const bool ba = !s.mapped && !(s.rfl & CRAMGPU_RF_NO_BASES);
-        const uint64_t bao = ba ? B[C_BA] + a.cnt[(size_t)C_BA * N + r] : ~0ull;
+        const uint64_t bao = ba ? at(C_BA) : ~0ull;
         a.read_ba_off[r] = bao;
         if (ba) copy_bytes(a.streams + bao, a.bases + s.lo, rlen, IdW(), IdB());          // [Writer.java:254-256]
         if (s.mapped) {
-            itf8_put(a.streams + B[C_FN] + a.cnt[(size_t)C_FN * N + r], nf);
-            itf8_put(a.streams + B[C_MQ] + a.cnt[(size_t)C_MQ * N + r], s.mapq);
+            itf8_put(a.streams + at(C_FN), nf);
+            itf8_put(a.streams + at(C_MQ), s.mapq);
         }
-        if (nf) {
-            sFC = a.streams + B[C_FC] + a.cnt[(size_t)C_FC * N + r];
-            sFP = a.streams + B[C_FP] + a.cnt[(size_t)C_FP * N + r];
-            sBS = a.streams + B[C_BS] + a.cnt[(size_t)C_BS * N + r];
+        if (nf || s.nops > 1) {
+            sFC = a.streams + at(C_FC); sFP = a.streams + at(C_FP); sBS = a.streams + at(C_BS); sDL = a.streams + at(C_DL);
+            sBA = a.streams + at(C_BA); sSC = a.streams + at(C_SC); sRS = a.streams + at(C_RS); sHC = a.streams + at(C_HC);
+            sPD = a.streams + at(C_PD); paybase = at(C_PAYLOAD);
             codes = a.codes + (size_t)c * 32;
         }
     }
 
-    if (s.window && (!WRITE || nf)) {
-        // read words (aligned) against the reference bytes at the same read offsets
-        const uint8_t *A = a.bases + s.lo;
-        const uint32_t sa = (uint32_t)((uintptr_t)A & 3);
-        const uint32_t *aw = reinterpret_cast<const uint32_t *>(A - sa);
-        const uint8_t *Bs = a.nref + a.ref_off[c] + (uint64_t)(s.pos - 1) - sa;     // nref has 16 bytes of slack on both sides
-        const uint32_t sb = (uint32_t)((uintptr_t)Bs & 3), sb8 = sb * 8;
-        const uint32_t *bw = reinterpret_cast<const uint32_t *>(Bs - sb);
-        const uint32_t nwords = (sa + rlen + 3) >> 2, tail = (sa + rlen) & 3;
-        uint32_t bprev = bw[0];
+    if (s.walk && (!WRITE || nf || s.nops > 1)) {
+        // createVariations [Sam2CramRecordFactory.java:205-296], one operator after the other
+        const uint8_t *rb = a.bases + s.lo;
+        const uint8_t *nref = a.nref + a.ref_off[c] + (uint64_t)(s.pos - 1);          // nref has slack on both sides
+        uint32_t z = 0, aoff = 0;
         int32_t prev = 0;
-        for (uint32_t k = 0; k < nwords; k++) {
-            const uint32_t av = aw[k], bnext = bw[k + 1];
-            const uint32_t bv = __funnelshift_r(bprev, bnext, sb8);
-            bprev = bnext;
-            uint32_t x = av ^ bv;
-            if (k == 0) x &= 0xFFFFFFFFu << (8 * sa);
-            if (k == nwords - 1 && tail) x &= (1u << (8 * tail)) - 1u;
-            while (x) {                                                  // a substitution per differing byte [:306-330]
-                const uint32_t j = (uint32_t)(__ffs(x) - 1) >> 3;
-                x &= ~(0xFFu << (8 * j));
-                const uint8_t b = (uint8_t)(av >> (8 * j)), refb = (uint8_t)(bv >> (8 * j));
-                const int32_t mypos = (int32_t)(4 * k + j - sa) + 1;
-                const uint32_t d = (uint32_t)(mypos - prev);
-                prev = mypos;
-                const int ri = base_index(refb), bi = base_index(b);
-                if (!WRITE) {
-                    if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
-                } else {
-                    const uint64_t fi = fbase + n_feat;
-                    const uint8_t code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;
-                    a.f_op[fi] = 'X'; a.f_pos[fi] = mypos; a.f_val[fi] = code; a.f_aux[fi] = (int32_t)b | ((int32_t)refb << 8);
-                    sFC[n_feat] = 'X';
-                    itf8_put(sFP + n_fp, d);
-                    sBS[n_feat] = code;
-                }
-                n_feat++; n_fp += itf8_len(d);
+        // a feature without series bytes of its own
+        auto feature = [&](uint8_t opc, int32_t fpos, int32_t val, int32_t aux) {
+            const uint32_t d = (uint32_t)(fpos - prev);
+            prev = fpos;
+            if (WRITE) {
+                const uint64_t fi = fbase + n_feat;
+                a.f_op[fi] = opc; a.f_pos[fi] = fpos; a.f_val[fi] = val; a.f_aux[fi] = aux;
+                sFC[n_feat] = opc;
+                itf8_put(sFP + n_fp, d);
             }
+            n_feat++; n_fp += itf8_len(d);
+        };
+        for (uint32_t ci = 0; ci < s.nops; ci++) {
+            const uint32_t cw = a.cigar[s.c0 + ci], op = cw & 15, len = cw >> 4;
+            if (!consumes_read(op)) {
+                // D, N, H, P: one feature at the next read position [:228-240]
+                const uint32_t vl = itf8_len(len);
+                if (WRITE) itf8_put(op == OP_D ? sDL + n_dl : op == OP_N ? sRS + n_rs : op == OP_H ? sHC + n_hc : sPD + n_pd, len);
+                feature(op == OP_D ? 'D' : op == OP_N ? 'N' : op == OP_H ? 'H' : 'P', (int32_t)z + 1, (int32_t)len, 0);
+                if (op == OP_D) n_dl += vl; else if (op == OP_N) n_rs += vl; else if (op == OP_H) n_hc += vl; else n_pd += vl;
+            } else if (op == OP_I) {
+                // one 'i' feature per inserted base [:262-266]
+                for (uint32_t i = 0; i < len; i++) {
+                    const uint8_t b = rb[z + i];
+                    if (WRITE) sBA[n_ba] = b;
+                    feature('i', (int32_t)(z + i) + 1, b, 0);
+                    n_ba++;
+                }
+            } else if (op == OP_S) {
+                // SoftClip(pos, bases[pos .. pos+len)) [:268-272]; bytes + TAB into SC, bytes into the payload
+                if (len) {
+                    if (WRITE) {
+                        for (uint32_t i = 0; i < len; i++) { const uint8_t b = rb[z + i]; sSC[n_sc + i] = b; a.payload[paybase + n_pay + i] = b; }
+                    }
+                    feature('S', (int32_t)z + 1, (int32_t)(paybase + n_pay), (int32_t)len);
+                }
+                if (WRITE) sSC[n_sc + len] = '\t';
+                n_sc += len + 1; n_pay += len;
+            } else if (len) {
+                // M, =, X: read words (aligned) against the reference bytes at the same read offsets
+                const uint8_t *A = rb + z;
+                const uint32_t sa = (uint32_t)((uintptr_t)A & 3);
+                const uint32_t *aw = reinterpret_cast<const uint32_t *>(A - sa);
+                const uint8_t *Bs = nref + aoff - sa;
+                const uint32_t sb = (uint32_t)((uintptr_t)Bs & 3), sb8 = sb * 8;
+                const uint32_t *bw = reinterpret_cast<const uint32_t *>(Bs - sb);
+                const uint32_t nwords = (sa + len + 3) >> 2, tail = (sa + len) & 3;
+                uint32_t bprev = bw[0];
+                for (uint32_t k = 0; k < nwords; k++) {
+                    const uint32_t av = aw[k], bnext = bw[k + 1];
+                    const uint32_t bv = __funnelshift_r(bprev, bnext, sb8);
+                    bprev = bnext;
+                    uint32_t x = av ^ bv;
+                    if (k == 0) x &= 0xFFFFFFFFu << (8 * sa);
+                    if (k == nwords - 1 && tail) x &= (1u << (8 * tail)) - 1u;
+                    while (x) {                                              // a substitution per differing byte [:306-330]
+                        const uint32_t j = (uint32_t)(__ffs(x) - 1) >> 3;
+                        x &= ~(0xFFu << (8 * j));
+                        const uint8_t b = (uint8_t)(av >> (8 * j)), refb = (uint8_t)(bv >> (8 * j));
+                        const int ri = base_index(refb), bi = base_index(b);
+                        uint8_t code = 0;
+                        if (!WRITE) {
+                            if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull);
+                        } else {
+                            code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0;           // codes[][] default 0 [:39]
+                            sBS[n_bs] = code;
+                        }
+                        feature('X', (int32_t)(z + 4 * k + j - sa) + 1, code, (int32_t)b | ((int32_t)refb << 8));
+                        n_bs++;
+                    }
+                }
+            }
+            if (consumes_read(op)) z += len;
+            if (consumes_ref(op)) aoff += len;
         }
     }
 
@@ -377,9 +453,16 @@ __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
         a.force[r] = s.force;
         uint32_t *cn = a.cnt + r;
         if (s.mapped) { cn[C_FN * N] = itf8_len(n_feat); cn[C_MQ * N] = itf8_len(s.mapq); }
-        else if (!(s.rfl & CRAMGPU_RF_NO_BASES) && rlen) cn[C_BA * N] = rlen;
+        else if (!(s.rfl & CRAMGPU_RF_NO_BASES) && rlen) n_ba = rlen;
         if (s.forced && rlen) cn[C_QS * N] = rlen;
-        if (n_feat) { cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_NFEAT * N] = n_feat; cn[C_BS * N] = n_feat; }
+        if (n_feat) { cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_NFEAT * N] = n_feat; }
+        if (n_bs) cn[C_BS * N] = n_bs;
+        if (n_ba) cn[C_BA * N] = n_ba;
+        if (n_dl) cn[C_DL * N] = n_dl;
+        if (n_sc) { cn[C_SC * N] = n_sc; cn[C_PAYLOAD * N] = n_pay; }
+        if (n_rs) cn[C_RS * N] = n_rs;
+        if (n_hc) cn[C_HC * N] = n_hc;
+        if (n_pd) cn[C_PD * N] = n_pd;
     } else if (s.forced && ps.n < 0) {
         // lossless: the preserved array is the record's own qualities [Writer.java:250-251,257-258]
         copy_bytes(a.streams + B[C_QS] + a.cnt[(size_t)C_QS * N + r], a.quals + s.lo, rlen, IdW(), IdB());
@@ -820,7 +903,8 @@ struct NormArgs {
     const uint8_t *f_op; const int32_t *f_pos, *f_val, *f_aux; const uint8_t *payload;
     const uint8_t *qs; const uint64_t *read_qs_off; const uint8_t *ba; const uint64_t *read_ba_off;
     uint8_t *bases, *quals, *qual_star; int32_t *status;
-    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;            // reads left to the general kernel
+    uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;            // records left to k_norm
+    const uint8_t *nref;                                                         // normalizeBase(ref[i]) over the regions, same offsets as ref
 };
 
 // base with rank `code` for normalised reference base r: SubstitutionMatrix(byte[]) / base() [:59-..,177]
@@ -839,9 +923,23 @@ __device__ __forceinline__ uint8_t matrix_base(const uint8_t *m, uint8_t refb, i
     return out;
 }
 
-// Records whose restoration is a plain copy, one THREAD per record: no read features and inside the reference region
-// (bases = the region bytes as they are, :346-362), or unmapped (bases from BA), or unknown bases; and a stored score
-// array (FORCE_QS).  The others go to the list of k_norm.
+// Decode runs one THREAD per record, in two kernels:
+//   k_norm_simple  every record, in order (coalesced tables and results): the qualities of records with a stored score
+//                  array, and the bases of records whose restoration is a plain copy -- no read features and inside the
+//                  reference region (the region bytes as they are, :346-362), unmapped (bases from BA), unknown bases.
+//                  The others (read features, region overhang, no stored array) go to a list;
+//   k_norm         the list, one thread per entry, so that all lanes of a warp do the same kind of work: the
+//                  feature-by-feature restoration [CramNormalizer.java:335-434] over a normalised copy of the region.
+__device__ __forceinline__ void append_list(const NormArgs &a, bool cx, uint64_t r, uint32_t c, uint32_t lane)
+{
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, cx);
+    if (!m) return;
+    unsigned long long base = 0;
+    if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(a.clist_n, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+    if (cx) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); a.clist_r[k] = r; a.clist_c[k] = c; }
+}
+
 __global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -855,35 +953,30 @@ __global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
         live = r < a.n_reads;
         c = live ? container_of(a.cont_off, a.n_containers, r) : 0;
     }
-    bool simple = false;
+    bool listed = false, stored = false;
     uint64_t lo = 0, rlen = 0, qo = ~0ull;
-    const uint8_t *src = nullptr;              // where the bases come from (nullptr: nothing to write)
+    const uint8_t *src = nullptr;              // where the bases come from (nullptr: nothing to write here)
     if (live) {
         lo = a.read_off[r];
         rlen = a.read_off[r + 1] - lo;
         const uint8_t rfl = a.rflags[r];
         qo = a.read_qs_off[r];
-        simple = (rfl & CRAMGPU_NF_FORCE_QS) && rlen < (1ull << 31);
+        stored = (rfl & CRAMGPU_NF_FORCE_QS) != 0;
+        listed = !stored || rlen >= (1ull << 31);
         if (rfl & CRAMGPU_NF_UNKNOWN_BASES) {
         } else if (rfl & CRAMGPU_NF_UNMAPPED) {
             const uint64_t bo = a.read_ba_off[r];
             if (bo != ~0ull) src = a.ba + bo;
         } else if (rlen > 0) {
             const int64_t o = (int64_t)a.pos[r] - 1 - a.win_start0[c];
-            if (a.feat_off[r] != a.feat_off[r + 1] || o < 0 || (uint64_t)o + rlen > a.win_len[c]) simple = false;
+            if (a.feat_off[r] != a.feat_off[r + 1] || o < 0 || (uint64_t)o + rlen > a.win_len[c]) listed = true;
             else src = a.ref + a.win_off[c] + o;
         }
     }
-    const bool cx = live && !simple;
-    const uint32_t m = __ballot_sync(0xFFFFFFFFu, cx);
-    if (m) {
-        unsigned long long base = 0;
-        if (lane == (uint32_t)(__ffs(m) - 1)) base = atomicAdd(a.clist_n, (unsigned long long)__popc(m));
-        base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
-        if (cx) { const uint64_t k = base + __popc(m & ((1u << lane) - 1u)); a.clist_r[k] = r; a.clist_c[k] = c; }
-    }
-    if (!simple) return;
+    append_list(a, listed, r, c, lane);
+    if (!live || rlen >= (1ull << 31)) return;
     if (src) copy_bytes(a.bases + lo, src, (uint32_t)rlen, IdW(), IdB());
+    if (!stored) return;
     // restoreQualityScores with a stored array (:306-333): 0xFF = missing -> default score
     const uint32_t dflt = '?' - '!';
     uint32_t present = 0;
@@ -899,131 +992,118 @@ __global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
         copy_bytes(a.quals + lo, a.quals + lo, (uint32_t)rlen, [&](uint32_t) { return dflt * 0x01010101u; }, [&](uint8_t) { return (uint8_t)dflt; });
     }
     a.qual_star[r] = present == 0;             // missingScores == scores.length
-    a.status[r] = CRAMGPU_OK;
-}
-
-// the general restoration of one record by one warp
-__device__ __forceinline__ void norm_read(const NormArgs &a, const uint64_t r, const uint32_t c, const uint32_t lane)
-{
-    const uint8_t *ref = a.ref + a.win_off[c];
-    const int64_t ref_len = (int64_t)a.win_len[c], off0 = a.win_start0[c];
-    const uint8_t *mtx = a.matrix + (size_t)c * 8;
-    const uint64_t lo = a.read_off[r];
-    const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
-    const uint8_t rfl = a.rflags[r];
-    const uint64_t f0 = a.feat_off[r], f1 = a.feat_off[r + 1];
-    uint8_t *bases = a.bases + lo, *quals = a.quals + lo;
-    int bad = 0;
-
-    // ---- bases: CramNormalizer.restoreBases / restoreReadBases (build/CramNormalizer.java:208-244,335-434)
-    if (rfl & CRAMGPU_NF_UNKNOWN_BASES) {
-        // NULL_SEQUENCE: nothing to write (readLength bytes stay as they are; callers treat the read as '*')
-    } else if (rfl & CRAMGPU_NF_UNMAPPED) {
-        uint64_t bo = a.read_ba_off[r];
-        if (bo != ~0ull) for (int64_t i = lane; i < rlen; i += 32) bases[i] = a.ba[bo + i];
-    } else if (rlen > 0) {
-        const int64_t al0 = (int64_t)a.pos[r] - 1;
-        if (f0 == f1) {
-            // no features: straight copy, 'N' fill when the record overhangs the region (:346-362); no normalizeBase here
-            if (ref_len + off0 < al0 + rlen) {
-                int64_t o = al0 - off0, avail = ref_len - o;
-                int64_t ncopy = (o > 0 && avail > 0) ? (rlen < avail ? rlen : avail) : 0;
-                for (int64_t i = lane; i < rlen; i += 32) bases[i] = i < ncopy ? ref[o + i] : (uint8_t)'N';
-            } else if (al0 - off0 < 0) {
-                bad = 1;
-            } else {
-                for (int64_t i = lane; i < rlen; i += 32) bases[i] = ref[al0 - off0 + i];
-            }
-        } else {
-            int64_t pir = 1, pis = 0;      // posInRead (1-based), posInSeq
-            for (uint64_t f = f0; f < f1 && !bad; f++) {
-                int64_t fpos = a.f_pos[f];
-                uint8_t op = a.f_op[f];
-                // reference bases up to the feature (:365-373)
-                int64_t n = fpos - pir;
-                if (n > 0) {
-                    if (al0 + pis - off0 < 0 || fpos - 1 > rlen) { bad = 1; break; }
-                    for (int64_t i = lane; i < n; i += 32) {
-                        int64_t rp = al0 + pis + i - off0;
-                        bases[pir - 1 + i] = norm_base(rp >= ref_len ? (uint8_t)'N' : ref[rp]);
-                    }
-                    pir += n; pis += n;
-                }
-                switch (op) {
-                case 'X': {
-                    int64_t rp = al0 + pis - off0;
-                    if (rp < 0 || pir > rlen) { bad = 1; break; }
-                    uint8_t refb = norm_base(rp >= ref_len ? (uint8_t)'N' : ref[rp]);
-                    if (lane == 0) bases[pir - 1] = norm_base(matrix_base(mtx, refb, a.f_val[f]));
-                    pir++; pis++;
-                    break;
-                }
-                case 'S': case 'I': {
-                    int64_t ln = a.f_aux[f];
-                    if (pir - 1 + ln > rlen) { bad = 1; break; }
-                    for (int64_t i = lane; i < ln; i += 32) bases[pir - 1 + i] = norm_base(a.payload[a.f_val[f] + i]);
-                    pir += ln;
-                    break;
-                }
-                case 'D': case 'N': pis += a.f_val[f]; break;
-                case 'i':
-                    if (pir > rlen) { bad = 1; break; }
-                    if (lane == 0) bases[pir - 1] = norm_base((uint8_t)a.f_val[f]);
-                    pir++;
-                    break;
-                default: break;            // H, P, Q, B consume nothing here
-                }
-            }
-            if (!bad) {
-                // tail from the reference while it lasts (:412-415); what is left stays 0 -> normalizeBase -> 'N'
-                int64_t n = rlen - pir + 1;
-                if (n > 0 && al0 + pis - off0 < 0) bad = 1;
-                for (int64_t i = lane; i < n && !bad; i += 32) {
-                    int64_t rp = al0 + pis + i - off0;
-                    bases[pir - 1 + i] = rp < ref_len ? norm_base(ref[rp]) : (uint8_t)'N';
-                }
-                __syncwarp();
-                for (uint64_t f = f0; f < f1; f++)          // ReadBase overwrites (:418-427)
-                    if (a.f_op[f] == 'B' && lane == 0) bases[a.f_pos[f] - 1] = norm_base((uint8_t)a.f_val[f]);
-            }
-        }
-    }
-
-    // ---- qualities: restoreQualityScores (:287-333)
-    const uint8_t dflt = '?' - '!';
-    uint32_t star;
-    if (!(rfl & CRAMGPU_NF_FORCE_QS)) {
-        for (int64_t i = lane; i < rlen; i += 32) quals[i] = dflt;
-        __syncwarp();
-        uint32_t any = 0;
-        for (uint64_t f = f0 + lane; f < f1; f += 32) {
-            uint8_t op = a.f_op[f];
-            if (op == 'Q') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_val[f]; any = 1; }
-            else if (op == 'B') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_aux[f]; any = 1; }
-        }
-        star = __ballot_sync(0xFFFFFFFFu, any) == 0;
-    } else {
-        uint64_t qo = a.read_qs_off[r];
-        uint32_t present = 0;
-        for (int64_t i = lane; i < rlen; i += 32) {
-            uint8_t s = qo != ~0ull ? a.qs[qo + i] : (uint8_t)0xFF;
-            if (s == 0xFF) s = dflt; else present = 1;
-            quals[i] = s;
-        }
-        star = __ballot_sync(0xFFFFFFFFu, present) == 0;     // missingScores == scores.length
-    }
-    if (lane == 0) {
-        a.qual_star[r] = (uint8_t)star;
-        a.status[r] = bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
-    }
+    if (!listed) a.status[r] = CRAMGPU_OK;
 }
 
 __global__ void __launch_bounds__(128) k_norm(NormArgs a)
 {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint64_t n = *a.clist_n, step = (uint64_t)gridDim.x * 4;
-    for (uint64_t i = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); i < n; i += step)
-        norm_read(a, a.clist_r[i], a.clist_c[i], lane);
+    const uint64_t n = *a.clist_n, step = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t li = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; li < n; li += step) {
+        const uint64_t r = a.clist_r[li];
+        const uint32_t c = a.clist_c[li];
+        const uint8_t *ref = a.ref + a.win_off[c];             // 'N' fill / region checks use the raw region ...
+        const uint8_t *nref = a.nref + a.win_off[c];           // ... feature records see normalizeBase(region)
+        const int64_t ref_len = (int64_t)a.win_len[c], off0 = a.win_start0[c];
+        const uint8_t *mtx = a.matrix + (size_t)c * 8;
+        const uint64_t lo = a.read_off[r];
+        const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
+        const uint8_t rfl = a.rflags[r];
+        const uint64_t f0 = a.feat_off[r], f1 = a.feat_off[r + 1];
+        uint8_t *bases = a.bases + lo, *quals = a.quals + lo;
+        int bad = 0;
+        // a run of n region bases (normalised) into the read at 0-based offset `at`
+        auto run = [&](int64_t at, int64_t rp, int64_t cnt) {
+            if (rp + cnt <= ref_len && cnt < (1ll << 31)) copy_bytes(bases + at, nref + rp, (uint32_t)cnt, IdW(), IdB());
+            else for (int64_t i = 0; i < cnt; i++) bases[at + i] = rp + i >= ref_len ? (uint8_t)'N' : nref[rp + i];
+        };
+
+        // ---- bases: restoreBases / restoreReadBases (build/CramNormalizer.java:208-244,335-434); the plain cases were done by k_norm_simple
+        if (!(rfl & (CRAMGPU_NF_UNKNOWN_BASES | CRAMGPU_NF_UNMAPPED)) && rlen > 0) {
+            const int64_t al0 = (int64_t)a.pos[r] - 1;
+            if (f0 == f1) {
+                // no features: straight copy, 'N' fill when the record overhangs the region (:346-362); no normalizeBase here
+                if (ref_len + off0 < al0 + rlen) {
+                    const int64_t o = al0 - off0, avail = ref_len - o;
+                    const int64_t ncopy = (o > 0 && avail > 0) ? (rlen < avail ? rlen : avail) : 0;
+                    for (int64_t i = 0; i < rlen; i++) bases[i] = i < ncopy ? ref[o + i] : (uint8_t)'N';
+                } else if (al0 - off0 < 0) {
+                    bad = 1;
+                } else if (rlen >= (1ll << 31)) {
+                    for (int64_t i = 0; i < rlen; i++) bases[i] = ref[al0 - off0 + i];
+                }
+            } else {
+                int64_t pir = 1, pis = 0;      // posInRead (1-based), posInSeq
+                for (uint64_t f = f0; f < f1 && !bad; f++) {
+                    const int64_t fpos = a.f_pos[f];
+                    const uint8_t op = a.f_op[f];
+                    const int64_t cnt = fpos - pir;            // reference bases up to the feature (:365-373)
+                    if (cnt > 0) {
+                        if (al0 + pis - off0 < 0 || fpos - 1 > rlen) { bad = 1; break; }
+                        run(pir - 1, al0 + pis - off0, cnt);
+                        pir += cnt; pis += cnt;
+                    }
+                    switch (op) {
+                    case 'X': {
+                        const int64_t rp = al0 + pis - off0;
+                        if (rp < 0 || pir > rlen) { bad = 1; break; }
+                        const uint8_t refb = rp >= ref_len ? (uint8_t)'N' : nref[rp];
+                        bases[pir - 1] = norm_base(matrix_base(mtx, refb, a.f_val[f]));
+                        pir++; pis++;
+                        break;
+                    }
+                    case 'S': case 'I': {
+                        const int64_t ln = a.f_aux[f];
+                        if (pir - 1 + ln > rlen) { bad = 1; break; }
+                        const uint8_t *pay = a.payload + a.f_val[f];
+                        for (int64_t i = 0; i < ln; i++) bases[pir - 1 + i] = norm_base(pay[i]);
+                        pir += ln;
+                        break;
+                    }
+                    case 'D': case 'N': pis += a.f_val[f]; break;
+                    case 'i':
+                        if (pir > rlen) { bad = 1; break; }
+                        bases[pir - 1] = norm_base((uint8_t)a.f_val[f]);
+                        pir++;
+                        break;
+                    default: break;            // H, P, Q, B consume nothing here
+                    }
+                }
+                if (!bad) {
+                    // tail from the reference while it lasts (:412-415); what is left stays 0 -> normalizeBase -> 'N'
+                    const int64_t cnt = rlen - pir + 1;
+                    if (cnt > 0 && al0 + pis - off0 < 0) bad = 1;
+                    else if (cnt > 0) run(pir - 1, al0 + pis - off0, cnt);
+                    if (!bad)
+                        for (uint64_t f = f0; f < f1; f++)          // ReadBase overwrites (:418-427)
+                            if (a.f_op[f] == 'B') bases[a.f_pos[f] - 1] = norm_base((uint8_t)a.f_val[f]);
+                }
+            }
+        }
+
+        // ---- qualities without a stored array: restoreQualityScores (:287-305)
+        if (!(rfl & CRAMGPU_NF_FORCE_QS)) {
+            const uint8_t dflt = '?' - '!';
+            for (int64_t i = 0; i < rlen; i++) quals[i] = dflt;
+            uint32_t any = 0;
+            for (uint64_t f = f0; f < f1; f++) {
+                const uint8_t op = a.f_op[f];
+                if (op == 'Q') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_val[f]; any = 1; }
+                else if (op == 'B') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_aux[f]; any = 1; }
+            }
+            a.qual_star[r] = any == 0;
+        } else if (rlen >= (1ll << 31)) {
+            // (k_norm_simple leaves reads of 2 GiB and more alone)
+            const uint64_t qo = a.read_qs_off[r];
+            uint32_t present = 0;
+            for (int64_t i = 0; i < rlen; i++) {
+                uint8_t sc = qo != ~0ull ? a.qs[qo + i] : (uint8_t)0xFF;
+                if (sc == 0xFF) sc = '?' - '!'; else present = 1;
+                quals[i] = sc;
+            }
+            a.qual_star[r] = present == 0;
+        }
+        a.status[r] = bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
+    }
 }
 
 
@@ -1137,9 +1217,9 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_roff = cv.take(8 * (size_t)nc), o_rlen = cv.take(8 * (size_t)nc);
     size_t o_cnt = cv.take(4 * (size_t)NCNT * n), o_force = cv.take(n);
-    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16), o_cln = cv.take(16);
+    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16), o_cln = cv.take(16), o_tln = cv.take(16);
     size_t o_zero_end = cv.off;
-    size_t o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n);
+    size_t o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n), o_tlr = cv.take(8 * (size_t)n), o_tlc = cv.take(4 * (size_t)n);
     size_t o_nref = cv.take(R->ref_total + 512) + 256;                          // slack on both sides of the normalised copy
     size_t o_codes = cv.take(32 * (size_t)nc), o_matrix = cv.take(8 * (size_t)nc);
     size_t o_totals = cv.take(8 * (size_t)NCNT * nc), o_base = cv.take(8 * (size_t)NCNT * nc);
@@ -1170,6 +1250,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     uint64_t *d_grand = (uint64_t *)(S + o_grand);
     a.nref = S + o_nref; a.totals = d_totals;
     a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
+    a.tlist_r = (uint64_t *)(S + o_tlr); a.tlist_c = (uint32_t *)(S + o_tlc); a.tlist_n = (unsigned long long *)(S + o_tln);
 
     uint64_t max_reads = 0, max_win = 0, sum_win = 0;
     for (uint32_t c = 0; c < nc; c++) {
@@ -1186,7 +1267,9 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + 3) / 4), nc) : dim3((uint32_t)((n + 3) / 4), 1);      // warp per read
     const dim3 sgrid = nc <= 65535 ? dim3((uint32_t)((max_reads + 127) / 128), nc) : dim3((uint32_t)((n + 127) / 128), 1);   // thread per read
     const uint32_t wgrid = (uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16);
+    const uint32_t mgrid = (uint32_t)std::min<uint64_t>((n + 127) / 128, 148 * 8);
     LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false><<<sgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false><<<mgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<wgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
     LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
@@ -1219,6 +1302,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.streams = O + q_str;
     a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
     LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true><<<sgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<wgrid, 128, 0, st>>>(a, ps));
     if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
     CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
@@ -1336,6 +1420,7 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_woff = cv.take(8 * (size_t)nc), o_wlen = cv.take(8 * (size_t)nc), o_ws = cv.take(8 * (size_t)nc);
     size_t o_cln = cv.take(16), o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n);
+    size_t o_nref = cv.take(in->ref_total + 512) + 256;
     if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
     if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, 8 * (size_t)(4 * nc + 1) + 256)) return rc;
@@ -1355,13 +1440,21 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
     a.f_op = in->f_op; a.f_pos = in->f_pos; a.f_val = in->f_val; a.f_aux = in->f_aux; a.payload = in->payload;
     a.qs = in->qs; a.read_qs_off = in->read_qs_off; a.ba = in->ba; a.read_ba_off = in->read_ba_off;
     a.bases = d_bases; a.quals = d_quals; a.qual_star = d_star; a.status = d_status;
-    uint64_t max_reads = 0;
-    for (uint32_t c = 0; c < nc; c++) max_reads = std::max(max_reads, in->cont_off[c + 1] - in->cont_off[c]);
+    uint64_t max_reads = 0, max_win = 0, sum_win = 0;
+    for (uint32_t c = 0; c < nc; c++) {
+        max_reads = std::max(max_reads, in->cont_off[c + 1] - in->cont_off[c]);
+        max_win = std::max(max_win, in->win_len[c]); sum_win += in->win_len[c];
+    }
     a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
+    a.nref = S + o_nref;
     CUDA_TRY(ctx, cudaMemsetAsync(S + o_cln, 0, 16, st));
+    if (nc <= 65535 && sum_win < in->ref_total)
+        LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)((max_win + 31) / 4096 + 1), nc), 256, 0, st>>>(in->ref, S + o_nref, a.win_off, a.win_len, 0));
+    else
+        LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)(in->ref_total / 4096 + 1), 1), 256, 0, st>>>(in->ref, S + o_nref, nullptr, nullptr, in->ref_total));
     const dim3 sgrid = nc <= 65535 ? dim3((uint32_t)((max_reads + 127) / 128), nc) : dim3((uint32_t)((n + 127) / 128), 1);
     LAUNCH(ctx, st, "k_norm_simple", k_norm_simple<<<sgrid, 128, 0, st>>>(a));
-    LAUNCH(ctx, st, "k_norm", k_norm<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16), 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_norm", k_norm<<<(uint32_t)std::min<uint64_t>((n + 127) / 128, 148 * 8), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     return CRAMGPU_OK;
 }
