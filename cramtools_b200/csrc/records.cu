@@ -56,6 +56,7 @@ struct RecArgs {
     const uint64_t *totals;      // [n_containers][NCNT] (write pass)
     uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;      // reads of the general warp-per-read walk
     uint64_t *tlist_r; uint32_t *tlist_c; unsigned long long *tlist_n;      // reads with several CIGAR operators (k_rec_multi)
+    uint64_t *wlist_r; uint32_t *wlist_c; unsigned long long *wlist_n;      // single-operator reads that have features (write pass: k_rec_multi)
 };
 
 __device__ __forceinline__ uint8_t norm_base(uint8_t b)      // cram/build/Utils.normalizeBase [Utils.java:31-49]
@@ -192,6 +193,77 @@ __device__ __forceinline__ void copy_bytes(uint8_t *__restrict__ dst, const uint
 struct IdW { __device__ __forceinline__ uint32_t operator()(uint32_t w) const { return w; } };
 struct IdB { __device__ __forceinline__ uint8_t operator()(uint8_t b) const { return b; } };
 
+// ---- byte copies by one warp ---------------------------------------------------------------------
+// 16 source bytes at any address as four words (aligned loads, funnel shift; the fifth word only when it holds data)
+__device__ __forceinline__ uint4 ld_u128_any(const uint8_t *p)
+{
+    const uint32_t sh = (uint32_t)((uintptr_t)p & 3), sh8 = sh * 8;
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(p - sh);
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], w3 = w[3], w4 = sh ? w[4] : 0u;
+    return make_uint4(__funnelshift_r(w0, w1, sh8), __funnelshift_r(w1, w2, sh8), __funnelshift_r(w2, w3, sh8), __funnelshift_r(w3, w4, sh8));
+}
+// [src, src + n) -> [dst, dst + n), both contiguous, lanes over consecutive 16-byte granules of dst: every load and store
+// of the warp falls into a handful of cache lines (a thread-per-read copy touches one line per lane).
+// Returns, per lane, whether it saw a byte 0xFF.
+__device__ __forceinline__ bool warp_copy(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint32_t n, uint32_t lane)
+{
+    bool ff = false;
+    uint32_t h = (16u - (uint32_t)((uintptr_t)dst & 15)) & 15u;
+    if (h > n) h = n;
+    if (lane < h) { const uint8_t b = src[lane]; dst[lane] = b; ff = b == 0xFF; }
+    const uint32_t ng = (n - h) >> 4;
+    for (uint32_t g = lane; g < ng; g += 32) {
+        const uint4 v = ld_u128_any(src + h + 16 * g);
+        ff = ff || (__vcmpeq4(v.x, 0xFFFFFFFFu) | __vcmpeq4(v.y, 0xFFFFFFFFu) | __vcmpeq4(v.z, 0xFFFFFFFFu) | __vcmpeq4(v.w, 0xFFFFFFFFu)) != 0;
+        *reinterpret_cast<uint4 *>(dst + h + 16 * g) = v;
+    }
+    const uint32_t t0 = h + 16 * ng;
+    if (t0 + lane < n) { const uint8_t b = src[t0 + lane]; dst[t0 + lane] = b; ff = ff || b == 0xFF; }
+    return ff;
+}
+// the bases of 32 consecutive reads of one length L (16 <= L <= 8192), read j = bytes [o_j, o_j + L) of `ref`, into the
+// contiguous [dst, dst + 32 L): lanes over the aligned 16-byte granules of dst; a granule takes its bytes from one read
+// or from the end of one and the start of the next.  o = this lane's o_j; `slack` / `avail` = readable bytes in front of / from ref.
+// Called by all 32 lanes.
+__device__ __forceinline__ void warp_gather_reads(uint8_t *__restrict__ dst, const uint8_t *__restrict__ ref, uint64_t slack, uint64_t avail,
+                                                  uint32_t o, uint32_t L, uint32_t lane)
+{
+    const uint32_t n = 32 * L;
+    const uint32_t h = (16u - (uint32_t)((uintptr_t)dst & 15)) & 15u;            // < 16 <= L: head bytes belong to read 0
+    const uint32_t ng = (n - h) >> 4, t0 = h + 16 * ng;                          // tail bytes (< 16) belong to read 31
+    if (lane == 0) for (uint32_t i = 0; i < h; i++) dst[i] = ref[o + i];
+    if (lane == 31) for (uint32_t i = t0; i < n; i++) dst[i] = ref[o + (i - 31 * L)];
+    const uint32_t inv = 0xFFFFFFFFu / L + 1;                                    // floor(x / L) = umulhi(x, inv) for x < 2^32 / L
+    for (uint32_t g0 = 0; g0 < ng; g0 += 32) {
+        const uint32_t g = g0 + lane;
+        const bool valid = g < ng;
+        const uint32_t off = h + 16 * (valid ? g : 0);                           // first byte of the granule inside the span
+        const uint32_t j = __umulhi(off, inv), within = off - j * L;
+        const uint32_t nA = min(16u, L - within);                                // bytes of the granule that come from read j
+        const uint32_t oA = __shfl_sync(0xFFFFFFFFu, o, j), oB = __shfl_sync(0xFFFFFFFFu, o, min(j + 1, 31u));
+        if (!valid) continue;
+        // vector loads may touch up to 19 bytes from their start: stay inside the reference array at both ends
+        const bool vec = (uint64_t)oA + within + 20 <= avail && (nA == 16 || ((uint64_t)oB + slack >= nA && (uint64_t)oB + 20 <= avail));
+        if (!vec) {
+            for (uint32_t i = 0; i < 16; i++) dst[off + i] = i < nA ? ref[oA + within + i] : ref[oB + i - nA];
+            continue;
+        }
+        uint4 v = ld_u128_any(ref + oA + within);
+        if (nA < 16) {
+            // granule byte i >= nA is byte i - nA of read j + 1: 16 bytes from nA bytes in front of it line up with the granule
+            const uint4 b = ld_u128_any(ref + oB - nA);
+            const uint32_t m0 = nA >= 4 ? 0xFFFFFFFFu : ((1u << (8 * nA)) - 1u);
+            const uint32_t m1 = nA >= 8 ? 0xFFFFFFFFu : (nA <= 4 ? 0u : ((1u << (8 * (nA - 4))) - 1u));
+            const uint32_t m2 = nA >= 12 ? 0xFFFFFFFFu : (nA <= 8 ? 0u : ((1u << (8 * (nA - 8))) - 1u));
+            const uint32_t m3 = nA <= 12 ? 0u : ((1u << (8 * (nA - 12))) - 1u);
+            v.x = (v.x & m0) | (b.x & ~m0); v.y = (v.y & m1) | (b.y & ~m1);
+            v.z = (v.z & m2) | (b.z & ~m2); v.w = (v.w & m3) | (b.w & ~m3);
+        }
+        *reinterpret_cast<uint4 *>(dst + off) = v;
+    }
+}
+
+
 // normalizeBase over the reference (windows or whole), 16 bytes per thread: grid (chunks, windows)
 __global__ void __launch_bounds__(256) k_ref_norm(const uint8_t *__restrict__ ref, uint8_t *__restrict__ nref,
                                                   const uint64_t *__restrict__ win_off, const uint64_t *__restrict__ win_len,
@@ -291,7 +363,7 @@ __device__ __forceinline__ void rec_list_append(uint64_t *lr, uint32_t *lc, unsi
 }
 
 template <bool WRITE>
-__device__ __forceinline__ void simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c);
+__device__ __forceinline__ uint32_t simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c);
 
 // all reads in order; reads with several CIGAR operators are only classified here and done by k_rec_multi, so that the
 // lanes of a warp do the same kind of work
@@ -314,23 +386,44 @@ __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
     if (!WRITE) {
         rec_list_append(a.clist_r, a.clist_c, a.clist_n, live && !s.simple, r, c, lane);
         rec_list_append(a.tlist_r, a.tlist_c, a.tlist_n, multi, r, c, lane);
+        uint32_t nf = 0;
+        if (s.simple && !multi) nf = simple_read<false>(a, ps, s, r, c);
+        // the write pass of a read with features is done from a list as well: most reads have none, and a warp of the
+        // in-order kernel would otherwise wait for its few that do
+        rec_list_append(a.wlist_r, a.wlist_c, a.wlist_n, nf != 0, r, c, lane);
+    } else if (s.simple && !multi) {
+        const uint32_t here = a.cnt[(size_t)C_NFEAT * a.n_reads + r];
+        const uint64_t next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * a.n_reads + r + 1] : a.totals[(size_t)c * NCNT + C_NFEAT];
+        if (next == here) simple_read<true>(a, ps, s, r, c);
     }
-    if (s.simple && !multi) simple_read<WRITE>(a, ps, s, r, c);
+    if (WRITE && ps.n < 0) {
+        // lossless: the preserved array is the record's own qualities [Writer.java:250-251,257-258] (multi-operator reads
+        // included).  The reads of a warp lie back to back in `quals`; when their arrays do so in QS too, one warp-wide copy
+        const bool cp = s.simple && s.forced;
+        const uint64_t qs = cp ? a.base[(size_t)c * NCNT + C_QS] + a.cnt[(size_t)C_QS * a.n_reads + r] : 0;
+        const uint64_t qs0 = __shfl_sync(0xFFFFFFFFu, qs, 0), lo0 = __shfl_sync(0xFFFFFFFFu, s.lo, 0);
+        const uint32_t L0 = __shfl_sync(0xFFFFFFFFu, s.rlen, 0);
+        const bool flat = cp && s.rlen == L0 && qs == qs0 + (uint64_t)lane * L0 && s.lo == lo0 + (uint64_t)lane * L0;
+        if (__all_sync(0xFFFFFFFFu, flat) && L0 <= (1u << 20)) warp_copy(a.streams + qs0, a.quals + lo0, 32 * L0, lane);
+        else if (cp) copy_bytes(a.streams + qs, a.quals + s.lo, s.rlen, IdW(), IdB());
+    }
 }
 
 template <bool WRITE>
-__global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps)
+__global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps, const uint64_t *__restrict__ lr, const uint32_t *__restrict__ lc,
+                                                   const unsigned long long *__restrict__ ln)
 {
-    const uint64_t n = *a.tlist_n, step = (uint64_t)gridDim.x * blockDim.x;
+    const uint64_t n = *ln, step = (uint64_t)gridDim.x * blockDim.x;
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
-        const uint64_t r = a.tlist_r[i];
-        const uint32_t c = a.tlist_c[i];
+        const uint64_t r = lr[i];
+        const uint32_t c = lc[i];
         simple_read<WRITE>(a, ps, classify_read(a, ps, r, c, true), r, c);
     }
 }
 
+// -> number of read features
 template <bool WRITE>
-__device__ __forceinline__ void simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c)
+__device__ __forceinline__ uint32_t simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c)
 {
     const uint64_t N = a.n_reads;
     const uint32_t rlen = s.rlen;
@@ -463,10 +556,8 @@ __device__ __forceinline__ void simple_read(const RecArgs &a, const PolSet &ps, 
         if (n_rs) cn[C_RS * N] = n_rs;
         if (n_hc) cn[C_HC * N] = n_hc;
         if (n_pd) cn[C_PD * N] = n_pd;
-    } else if (s.forced && ps.n < 0) {
-        // lossless: the preserved array is the record's own qualities [Writer.java:250-251,257-258]
-        copy_bytes(a.streams + B[C_QS] + a.cnt[(size_t)C_QS * N + r], a.quals + s.lo, rlen, IdW(), IdB());
     }
+    return n_feat;
 }
 
 // the general walk of one read by one warp (any CIGAR, any policy)
@@ -905,6 +996,7 @@ struct NormArgs {
     uint8_t *bases, *quals, *qual_star; int32_t *status;
     uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;            // records left to k_norm
     const uint8_t *nref;                                                         // normalizeBase(ref[i]) over the regions, same offsets as ref
+    uint64_t ref_total;
 };
 
 // base with rank `code` for normalised reference base r: SubstitutionMatrix(byte[]) / base() [:59-..,177]
@@ -953,8 +1045,9 @@ __global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
         live = r < a.n_reads;
         c = live ? container_of(a.cont_off, a.n_containers, r) : 0;
     }
-    bool listed = false, stored = false;
+    bool listed = false, stored = false, inwin = false;
     uint64_t lo = 0, rlen = 0, qo = ~0ull;
+    int64_t o = 0;                             // offset of the record inside its reference region
     const uint8_t *src = nullptr;              // where the bases come from (nullptr: nothing to write here)
     if (live) {
         lo = a.read_off[r];
@@ -968,17 +1061,35 @@ __global__ void __launch_bounds__(128) k_norm_simple(NormArgs a)
             const uint64_t bo = a.read_ba_off[r];
             if (bo != ~0ull) src = a.ba + bo;
         } else if (rlen > 0) {
-            const int64_t o = (int64_t)a.pos[r] - 1 - a.win_start0[c];
-            if (a.feat_off[r] != a.feat_off[r + 1] || o < 0 || (uint64_t)o + rlen > a.win_len[c]) listed = true;
+            o = (int64_t)a.pos[r] - 1 - a.win_start0[c];
+            inwin = o >= 0 && (uint64_t)o + rlen <= a.win_len[c];
+            if (a.feat_off[r] != a.feat_off[r + 1] || !inwin) listed = true;
             else src = a.ref + a.win_off[c] + o;
         }
     }
     append_list(a, listed, r, c, lane);
-    if (!live || rlen >= (1ull << 31)) return;
-    if (src) copy_bytes(a.bases + lo, src, (uint32_t)rlen, IdW(), IdB());
-    if (!stored) return;
-    // restoreQualityScores with a stored array (:306-333): 0xFF = missing -> default score
+    const uint64_t lo0 = __shfl_sync(0xFFFFFFFFu, lo, 0), rl0 = __shfl_sync(0xFFFFFFFFu, rlen, 0);
+    const uint32_t L0 = (uint32_t)rl0, c0 = __shfl_sync(0xFFFFFFFFu, c, 0);
+    // ---- bases.  32 mapped records of one length inside one region: the warp fills their (contiguous) bases together;
+    //      records with read features get the plain region bytes too and are redone by k_norm, which runs afterwards.
+    const bool fb = live && inwin && rlen == rl0 && c == c0 && o < (int64_t)0xFFFF0000ll;
+    if (__all_sync(0xFFFFFFFFu, fb) && rl0 >= 16 && rl0 <= 8192)
+        warp_gather_reads(a.bases + lo0, a.ref + a.win_off[c], a.win_off[c], a.ref_total - a.win_off[c], (uint32_t)o, L0, lane);
+    else if (src && rlen < (1ull << 31)) copy_bytes(a.bases + lo, src, (uint32_t)rlen, IdW(), IdB());
+    // ---- qualities: restoreQualityScores with a stored array (:306-333): 0xFF = missing -> default score
     const uint32_t dflt = '?' - '!';
+    const uint64_t qo0 = __shfl_sync(0xFFFFFFFFu, qo, 0);
+    const bool fq = live && stored && qo != ~0ull && rlen == rl0 && qo == qo0 + (uint64_t)lane * L0;
+    if (__all_sync(0xFFFFFFFFu, fq) && rl0 >= 1 && rl0 <= (1u << 20)) {
+        // the 32 arrays lie back to back in QS as the records do in `quals`: one warp-wide copy, unless a score is missing
+        const bool ff = warp_copy(a.quals + lo0, a.qs + qo0, 32 * L0, lane);
+        if (!__any_sync(0xFFFFFFFFu, ff)) {
+            a.qual_star[r] = 0;
+            if (!listed) a.status[r] = CRAMGPU_OK;
+            return;
+        }
+    }
+    if (!live || !stored || rlen >= (1ull << 31)) return;
     uint32_t present = 0;
     if (qo != ~0ull) {
         auto xw = [&](uint32_t w) -> uint32_t {
@@ -1217,9 +1328,10 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_roff = cv.take(8 * (size_t)nc), o_rlen = cv.take(8 * (size_t)nc);
     size_t o_cnt = cv.take(4 * (size_t)NCNT * n), o_force = cv.take(n);
-    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16), o_cln = cv.take(16), o_tln = cv.take(16);
+    size_t o_subst = cv.take(8 * 25 * (size_t)nc), o_status = cv.take(16), o_cln = cv.take(16), o_tln = cv.take(16), o_wln = cv.take(16);
     size_t o_zero_end = cv.off;
-    size_t o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n), o_tlr = cv.take(8 * (size_t)n), o_tlc = cv.take(4 * (size_t)n);
+    size_t o_clr = cv.take(8 * (size_t)n), o_clc = cv.take(4 * (size_t)n), o_tlr = cv.take(8 * (size_t)n), o_tlc = cv.take(4 * (size_t)n),
+           o_wlr = cv.take(8 * (size_t)n), o_wlc = cv.take(4 * (size_t)n);
     size_t o_nref = cv.take(R->ref_total + 512) + 256;                          // slack on both sides of the normalised copy
     size_t o_codes = cv.take(32 * (size_t)nc), o_matrix = cv.take(8 * (size_t)nc);
     size_t o_totals = cv.take(8 * (size_t)NCNT * nc), o_base = cv.take(8 * (size_t)NCNT * nc);
@@ -1251,6 +1363,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.nref = S + o_nref; a.totals = d_totals;
     a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
     a.tlist_r = (uint64_t *)(S + o_tlr); a.tlist_c = (uint32_t *)(S + o_tlc); a.tlist_n = (unsigned long long *)(S + o_tln);
+    a.wlist_r = (uint64_t *)(S + o_wlr); a.wlist_c = (uint32_t *)(S + o_wlc); a.wlist_n = (unsigned long long *)(S + o_wln);
 
     uint64_t max_reads = 0, max_win = 0, sum_win = 0;
     for (uint32_t c = 0; c < nc; c++) {
@@ -1269,7 +1382,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     const uint32_t wgrid = (uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16);
     const uint32_t mgrid = (uint32_t)std::min<uint64_t>((n + 127) / 128, 148 * 8);
     LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false><<<sgrid, 128, 0, st>>>(a, ps));
-    LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false><<<mgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
     LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<wgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
     LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
@@ -1302,7 +1415,8 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.streams = O + q_str;
     a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
     LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true><<<sgrid, 128, 0, st>>>(a, ps));
-    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps));
+    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.wlist_r, a.wlist_c, a.wlist_n));
     LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<wgrid, 128, 0, st>>>(a, ps));
     if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
     CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
@@ -1446,7 +1560,7 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
         max_win = std::max(max_win, in->win_len[c]); sum_win += in->win_len[c];
     }
     a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
-    a.nref = S + o_nref;
+    a.nref = S + o_nref; a.ref_total = in->ref_total;
     CUDA_TRY(ctx, cudaMemsetAsync(S + o_cln, 0, 16, st));
     if (nc <= 65535 && sum_win < in->ref_total)
         LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)((max_win + 31) / 4096 + 1), nc), 256, 0, st>>>(in->ref, S + o_nref, a.win_off, a.win_len, 0));
