@@ -375,6 +375,38 @@ __device__ __forceinline__ uint32_t lds_tab_u16(uint32_t saddr)
     return v;
 }
 
+// ---- the two rare cases of a decoder step, out of line so that the common path is straight-line code ----
+// More than three short ranges in a row: lanes with a3 know their rank is >= first + 3 (C = start of first + 3) and
+// search on, four cumulative ends per round; the rows end in 0xFFFF padding.  -> C | E << 16 | rank << 32
+__device__ __noinline__ uint64_t dec1_long_search(uint32_t ca, uint32_t m, bool a3, uint32_t C, uint32_t E, uint32_t r)
+{
+    uint32_t pa = ca + 128 + 8;               // cum[first + 4]
+    bool go = a3;
+    while (__any_sync(0xFFFFFFFFu, go)) {
+        const uint32_t e0 = lds_tab_u16(pa), e1 = lds_tab_u16(pa + 2), e2 = lds_tab_u16(pa + 4), e3 = lds_tab_u16(pa + 6);
+        if (go) {
+            const bool g0 = m >= e0, g1 = m >= e1, g2 = m >= e2, g3 = m >= e3;     // sorted: a prefix of them holds
+            r += (uint32_t)g0 + (uint32_t)g1 + (uint32_t)g2 + (uint32_t)g3;
+            C = g3 ? e3 : g2 ? e2 : g1 ? e1 : g0 ? e0 : C;
+            E = g3 ? 0u : g2 ? e3 : g1 ? e2 : g0 ? e1 : e0;
+            go = g3;
+        }
+        pa += 8;
+    }
+    return (uint64_t)(C & 0xFFFFu) | ((uint64_t)(E & 0xFFFFu) << 16) | ((uint64_t)r << 32);
+}
+// a lane needs two bytes: the general renormalisation.  -> x | cursor << 32
+__device__ __noinline__ uint64_t dec1_renorm2(uint32_t x, bool n1, bool n2, uint32_t b1, uint32_t cur, uint32_t lm, uint32_t gm, uint32_t rb)
+{
+    const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, n2);
+    const uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
+    const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1))), v1 = lds_u8(rb | ((at + 1) & (DEC1_RINGB - 1)));
+    const uint32_t x1 = (x << 8) | v0;
+    x = n2 ? ((x1 << 8) | v1) : (n1 ? x1 : x);
+    cur += __popc(b1 & gm) + __popc(b2 & gm);
+    return (uint64_t)x | ((uint64_t)cur << 32);
+}
+
 __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
                                              const DecCompact *__restrict__ compact,
@@ -462,33 +494,27 @@ __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc,
                     uint32_t C = a2 ? (a3 ? c3 : c2) : (a1 ? c1 : c0);
                     uint32_t E = a2 ? c3 : (a1 ? c2 : c1);
                     r += a2 ? (a3 ? 3u : 2u) : (a1 ? 1u : 0u);
-                    if (__any_sync(0xFFFFFFFFu, a3)) {                              // rare: more than three short ranges in a row
-                        uint32_t pa = ca + 136;
-                        bool go = a3;
-                        while (__any_sync(0xFFFFFFFFu, go)) {                       // ends at the 0xFFFF padding at the latest
-                            const uint32_t e = lds_tab_u16(pa);
-                            if (go) { if (m >= e) { C = e; r++; } else { E = e; go = false; } }
-                            pa += 2;
-                        }
+                    uint32_t xn = (E - C) * (x >> TF_SHIFT) + m - C;                // [Decoding.java:35-48]; lanes past their end idle on garbage
+                    // rare (out of line, tested after the common result is on its way): more than three short ranges in a row
+                    if (__any_sync(0xFFFFFFFFu, a3)) {
+                        const uint64_t fix = dec1_long_search(ca, m, a3, C, E, r);
+                        C = (uint32_t)fix & 0xFFFFu; E = ((uint32_t)fix >> 16) & 0xFFFFu; r = (uint32_t)(fix >> 32);
+                        xn = (E - C) * (x >> TF_SHIFT) + m - C;
                     }
                     orow[u * 32] = (uint8_t)r;
-                    x = (E - C) * (x >> TF_SHIFT) + m - C;                          // [Decoding.java:35-48]; lanes past their end idle on garbage
                     row = rows + r * DEC_ROWB;                                      // context of the next symbol
-                    // renormalise, lanes of a group in the order 0,1,2,3 [Decoding.java:84-90]
-                    const bool n1 = act && x < RANS_L;
-                    const bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
+                    // renormalise, lanes of a group in the order 0,1,2,3 [Decoding.java:84-90]; one byte is the common case
+                    const bool n1 = act && xn < RANS_L;
+                    const bool n2 = act && xn < (1u << 15);      // after one byte still below 2^23 -> a second byte
                     const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1);
+                    const uint32_t at = cur + __popc(b1 & lm);
+                    const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1)));
+                    x = xn;
+                    if (n1) x = __byte_perm(xn, v0, 0x2104u);
                     if (__any_sync(0xFFFFFFFFu, n2)) {
-                        const uint32_t b2 = __ballot_sync(0xFFFFFFFFu, n2);
-                        const uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
-                        const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1))), v1 = lds_u8(rb | ((at + 1) & (DEC1_RINGB - 1)));
-                        const uint32_t x1 = (x << 8) | v0;
-                        x = n2 ? ((x1 << 8) | v1) : (n1 ? x1 : x);
-                        cur += __popc(b1 & gm) + __popc(b2 & gm);
+                        const uint64_t two = dec1_renorm2(xn, n1, n2, b1, cur, lm, gm, rb);
+                        x = (uint32_t)two; cur = (uint32_t)(two >> 32);
                     } else {
-                        const uint32_t at = cur + __popc(b1 & lm);
-                        const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1)));
-                        x = __byte_perm(x, v0, n1 ? 0x2104u : 0x3210u);
                         cur += __popc(b1 & gm);
                     }
                 }
