@@ -354,6 +354,18 @@ __device__ __forceinline__ int32_t ld_acquire_s32(const int32_t *p)
     asm volatile("ld.acquire.cta.shared.s32 %0, [%1];" : "=r"(v) : "r"((unsigned)__cvta_generic_to_shared(p)) : "memory");
     return v;
 }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t saddr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint32_t prmt_raw(uint32_t a, uint32_t b, uint32_t sel)     // bytes of {b:a} picked by the nibbles of sel
+{
+    uint32_t v;
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(v) : "r"(a), "r"(b), "r"(sel));
+    return v;
+}
 __device__ __forceinline__ uint32_t lds_u8(uint32_t saddr)
 {
     uint32_t v;
@@ -471,6 +483,9 @@ __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc,
         uint32_t x = ring[(cur0 + 4 * k) & (DEC1_RINGB - 1)] | (ring[(cur0 + 4 * k + 1) & (DEC1_RINGB - 1)] << 8) |
                      (ring[(cur0 + 4 * k + 2) & (DEC1_RINGB - 1)] << 16) | ((uint32_t)ring[(cur0 + 4 * k + 3) & (DEC1_RINGB - 1)] << 24);
         uint32_t cur = cur0 + 16;
+        // Wc = the next 4 bytes of the group's stream (bytes cur .. cur + 3), in a register
+        uint32_t Wc = __funnelshift_r(lds_u32((uint32_t)__cvta_generic_to_shared(ring) | (cur & (DEC1_RINGB - 4))),
+                                      lds_u32((uint32_t)__cvta_generic_to_shared(ring) | ((cur + 4) & (DEC1_RINGB - 4))), cur << 3);
         const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
         const uint32_t rb = (uint32_t)__cvta_generic_to_shared(ring);            // aligned to the ring size
         const uint32_t rows = (uint32_t)__cvta_generic_to_shared(&S.rows[g][0]);
@@ -496,7 +511,7 @@ __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc,
                     r += a2 ? (a3 ? 3u : 2u) : (a1 ? 1u : 0u);
                     uint32_t xn = (E - C) * (x >> TF_SHIFT) + m - C;                // [Decoding.java:35-48]; lanes past their end idle on garbage
                     // rare (out of line, tested after the common result is on its way): more than three short ranges in a row
-                    if (__any_sync(0xFFFFFFFFu, a3)) {
+                    if (__builtin_expect(__any_sync(0xFFFFFFFFu, a3), 0)) {
                         const uint64_t fix = dec1_long_search(ca, m, a3, C, E, r);
                         C = (uint32_t)fix & 0xFFFFu; E = ((uint32_t)fix >> 16) & 0xFFFFu; r = (uint32_t)(fix >> 32);
                         xn = (E - C) * (x >> TF_SHIFT) + m - C;
@@ -507,16 +522,17 @@ __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc,
                     const bool n1 = act && xn < RANS_L;
                     const bool n2 = act && xn < (1u << 15);      // after one byte still below 2^23 -> a second byte
                     const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1);
-                    const uint32_t at = cur + __popc(b1 & lm);
-                    const uint32_t v0 = lds_u8(rb | (at & (DEC1_RINGB - 1)));
-                    x = xn;
-                    if (n1) x = __byte_perm(xn, v0, 0x2104u);
-                    if (__any_sync(0xFFFFFFFFu, n2)) {
+                    // this lane's byte is byte (bytes taken by the lower lanes of the group) of the window Wc; one byte-permute
+                    // shifts it into the state, or leaves the state alone (selector 0x3210) when the lane does not renormalise
+                    x = prmt_raw(xn, Wc, (n1 ? 0x2104u : 0x3210u) + __popc(b1 & (n1 ? lm : 0u)));
+                    if (__builtin_expect(__any_sync(0xFFFFFFFFu, n2), 0)) {
                         const uint64_t two = dec1_renorm2(xn, n1, n2, b1, cur, lm, gm, rb);
                         x = (uint32_t)two; cur = (uint32_t)(two >> 32);
                     } else {
                         cur += __popc(b1 & gm);
                     }
+                    // the window for the next step (not needed before its renormalisation, a whole table search away)
+                    Wc = __funnelshift_r(lds_u32(rb | (cur & (DEC1_RINGB - 4))), lds_u32(rb | ((cur + 4) & (DEC1_RINGB - 4))), cur << 3);
                 }
             }
             if (k == 0) S.cur[g] = cur;
