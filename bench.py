@@ -609,27 +609,39 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
     N.ba = vp(back.ctypes.data); N.read_ba_off = vp(rba.ctypes.data); N.qs = vp(back.ctypes.data)
     h2d = d2h = 0
 
+    call_ms = {'features_encode': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0, 'normalize_decode': 0.0, 'host_glue': 0.0}
+
     def step():
         nonlocal h2d, d2h
+        t_0 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_features_encode(ctx.handle, C.byref(R), None, -1, C.byref(F)))
+        t_1 = time.perf_counter()
         soff = np.ctypeslib.as_array(C.cast(F.stream_off, u64p), (n_cont, 12)); slen = np.ctypeslib.as_array(C.cast(F.stream_len, u64p), (n_cont, 12))
         v = in_ptr.reshape(n_cont, NB); w = in_len.reshape(n_cont, NB)
         v[:, 0] = np.uint64(F.streams) + soff[:, KQS]; w[:, 0] = slen[:, KQS]
         v[:, 1] = np.uint64(F.streams) + soff[:, KBA]; w[:, 1] = slen[:, KBA]
+        t_2 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_rans_encode_batch(ctx.handle, nblk, C.cast(in_ptr.ctypes.data, u8pp), in_len.ctypes.data_as(u32p),
                                                     order.ctypes.data_as(u8p), C.cast(out_ptr.ctypes.data, u8pp), caps.ctypes.data_as(u32p),
                                                     out_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+        t_3 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_rans_decode_batch(ctx.handle, nblk, C.cast(out_ptr.ctypes.data, u8pp), out_len.ctypes.data_as(u32p),
                                                     C.cast(back_ptr.ctypes.data, u8pp), caps.ctypes.data_as(u32p),
                                                     back_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+        t_4 = time.perf_counter()
         # records as CramRecordReader would hand them over: features from the encoder, score arrays inside the decoded QS series
         rq = np.ctypeslib.as_array(C.cast(F.read_qs_off, u64p), (n_reads,))
         rq_new = rq - soff[cidx, KQS] + cap_off[cidx * NB].astype(np.uint64)
         N.read_qs_off = vp(rq_new.ctypes.data)
         N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
         N.payload = F.payload
+        t_5 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(N), o_b.ctypes.data_as(u8p), o_q.ctypes.data_as(u8p),
                                                    o_s.ctypes.data_as(u8p), o_t.ctypes.data_as(i32p)))
+        t_6 = time.perf_counter()
+        for key, dt in (('features_encode', t_1 - t_0), ('rans_encode_batch', t_3 - t_2), ('rans_decode_batch', t_4 - t_3),
+                        ('normalize_decode', t_6 - t_5), ('host_glue', (t_2 - t_1) + (t_5 - t_4))):
+            call_ms[key] += dt * 1e3
         nf = int(F.n_feat)
         h2d = int(2 * n_reads * READ_LEN + ref.size + 20 * n_reads + a['cigar'].nbytes + in_len.sum() + out_len.sum()
                   + ref.size + 17 * nf + 33 * n_reads + in_len.sum())
@@ -638,6 +650,8 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
     assert np.array_equal(o_b, a['bases']) and np.array_equal(o_q, a['quals']), 'e2e round trip mismatch'
     barrier()
     k = max(1, min(args.steps, 3))
+    for key in call_ms:
+        call_ms[key] = 0.0
     t0 = time.perf_counter()
     for _ in range(k):
         step()
@@ -649,7 +663,7 @@ def run_e2e(ctx, args, ref, rd, extra, nu, n_cont, world, barrier):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
     return {'value': n_reads * world / (ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-            'ms_per_step': ms, 'containers_per_gpu': n_cont,
+            'ms_per_step': ms, 'containers_per_gpu': n_cont, 'calls_ms': {kk: round(vv / k, 2) for kk, vv in call_ms.items()},
             'path': 'cramgpu_features_encode -> cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_normalize_decode, '
                     'host buffers in and out, every copy inside the timed region'}
 

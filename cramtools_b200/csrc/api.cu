@@ -81,6 +81,51 @@ bool host_is_pinned(const void *p)
     return a.type == cudaMemoryTypeHost;
 }
 
+// cuPointerGetAttribute through the runtime's driver entry point lookup (no link-time dependency on libcuda)
+#include <cuda.h>
+typedef CUresult (*PointerAttrFn)(void *, CUpointer_attribute, CUdeviceptr);
+static PointerAttrFn pointer_attr_fn()
+{
+    static PointerAttrFn fn = []() -> PointerAttrFn {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuPointerGetAttribute", &f, cudaEnableDefault, &qr) != cudaSuccess || qr != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return (PointerAttrFn)f;
+    }();
+    return fn;
+}
+
+MemKind MemMap::kind(const void *p)
+{
+    const uintptr_t a = (uintptr_t)p;
+    if (!p) return MEM_PAGEABLE;
+    if (last < ranges.size() && a >= ranges[last].lo && a < ranges[last].hi) return ranges[last].kind;
+    for (size_t i = 0; i < ranges.size(); i++)
+        if (a >= ranges[i].lo && a < ranges[i].hi) { last = i; return ranges[i].kind; }
+    cudaPointerAttributes at;
+    MemKind k = MEM_PAGEABLE;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) cudaGetLastError();
+    else if (at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged) k = MEM_DEVICE;
+    else if (at.type == cudaMemoryTypeHost) k = MEM_PINNED;
+    Range r{a, a + 1, k};
+    if (k == MEM_PAGEABLE) {
+        // memory CUDA does not know: a 2 MB window of host address space never holds device memory
+        r.lo = a & ~(uintptr_t)((2u << 20) - 1); r.hi = r.lo + (2u << 20);
+    } else if (PointerAttrFn fn = pointer_attr_fn()) {
+        CUdeviceptr start = 0; size_t size = 0;
+        if (fn(&start, CU_POINTER_ATTRIBUTE_RANGE_START_ADDR, (CUdeviceptr)a) == CUDA_SUCCESS &&
+            fn(&size, CU_POINTER_ATTRIBUTE_RANGE_SIZE, (CUdeviceptr)a) == CUDA_SUCCESS && size) {
+            r.lo = (uintptr_t)start; r.hi = r.lo + size;
+        }
+    }
+    ranges.push_back(r);
+    last = ranges.size() - 1;
+    return k;
+}
+
 void par_memcpy(std::vector<CopyJob> &jobs)
 {
     size_t total = 0;
@@ -264,13 +309,25 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
 
-    std::vector<uint64_t> off(nblocks);
+    // Blocks in device memory are coded where they are (16-byte aligned ones; others are copied next to the staged
+    // blocks); large blocks in memory the caller pinned go to the device directly; the rest is staged, and every run of
+    // consecutive staged blocks travels as one copy.
+    const uint32_t BIG = 64u << 10;
+    MemMap mm;
+    std::vector<uint64_t> off(nblocks), addr(nblocks);
+    std::vector<uint8_t> how(nblocks, 0);                       // 0 staged, 1 direct from pinned memory, 2 in place on the device, 3 device copy
     std::vector<uint8_t> prefix(encode ? 0 : 9 * (size_t)nblocks, 0);
     uint64_t total_in = 0, total_out_cap = 0;
     for (uint32_t i = 0; i < nblocks; i++) {
         if (in_len[i] && !in[i]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in[%u] is null", i);
         off[i] = total_in;
-        total_in += rup(in_len[i], 16);
+        if (!in_len[i]) continue;
+        const MemKind k = mm.kind(in[i]);
+        if (k == MEM_DEVICE) {
+            if (!encode) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in[%u]: compressed blocks in device memory go through cramgpu_rans_decode_dev", i);
+            how[i] = ((uintptr_t)in[i] & 15) ? 3 : 2;
+        } else if (k == MEM_PINNED && in_len[i] >= BIG) how[i] = 1;
+        if (how[i] != 2) total_in += rup(in_len[i], 16);
         if (!encode) {
             memcpy(&prefix[9 * (size_t)i], in[i], in_len[i] < 9 ? in_len[i] : 9);
             uint32_t ord, raw;
@@ -288,23 +345,20 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     uint32_t *d_out_len = (uint32_t *)(d_hdr + 8 * (size_t)(nblocks + 1));
     int32_t *d_status = (int32_t *)(d_hdr + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
     {
-        // large blocks in memory the caller pinned go to the device directly; the rest is staged, and every run of
-        // consecutive staged blocks travels as one copy
-        const uint32_t BIG = 64u << 10;
         std::vector<CopyJob> jobs;
-        std::vector<uint8_t> direct(nblocks, 0);
         for (uint32_t i = 0; i < nblocks; i++) {
-            if (!in_len[i]) continue;
-            if (in_len[i] >= BIG && host_is_pinned(in[i])) direct[i] = 1;
-            else jobs.push_back(CopyJob{pin + off[i], in[i], in_len[i]});
+            addr[i] = how[i] == 2 ? (uint64_t)(uintptr_t)in[i] : (uint64_t)(uintptr_t)(d_in + off[i]);
+            if (in_len[i] && how[i] == 0) jobs.push_back(CopyJob{pin + off[i], in[i], in_len[i]});
         }
         par_memcpy(jobs);
         uint32_t i = 0;
         while (i < nblocks) {
-            if (direct[i]) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyHostToDevice, st)); i++; continue; }
+            if (how[i] == 2 || !in_len[i]) { i++; continue; }
+            if (how[i] == 1) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyHostToDevice, st)); i++; continue; }
+            if (how[i] == 3) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyDeviceToDevice, st)); i++; continue; }
             uint32_t j = i;
-            while (j < nblocks && !direct[j]) j++;
-            uint64_t a = off[i], b = (j < nblocks) ? off[j] : total_in;
+            uint64_t a = off[i], b = a;
+            while (j < nblocks && (how[j] == 0 || how[j] == 2 || !in_len[j])) { if (how[j] == 0 && in_len[j]) b = off[j] + in_len[j]; j++; }
             if (b > a) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + a, pin + a, b - a, cudaMemcpyHostToDevice, st));
             i = j;
         }
@@ -312,7 +366,7 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
 
     if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, hdr_bytes + 64)) return rc;
     if (encode) {
-        if (int rc = rans_encode_device(ctx, nblocks, d_in, off.data(), in_len, order, nullptr, ~0ull, d_out_off, d_out_len,
+        if (int rc = rans_encode_device(ctx, nblocks, nullptr, addr.data(), in_len, order, nullptr, ~0ull, d_out_off, d_out_len,
                                         d_status, st))
             return rc;
         // the packed size is only known on the device: fetch it, then size the output buffers
@@ -323,7 +377,7 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
         if (int rc = rans_encode_pack(ctx, (uint8_t *)ctx->dev_out.p, st)) return rc;
     } else {
         if (int rc = pool_reserve(ctx, ctx->dev_out, total_out_cap + 64)) return rc;
-        if (int rc = rans_decode_device(ctx, nblocks, d_in, off.data(), in_len, prefix.data(), (uint8_t *)ctx->dev_out.p,
+        if (int rc = rans_decode_device(ctx, nblocks, nullptr, addr.data(), in_len, prefix.data(), (uint8_t *)ctx->dev_out.p,
                                         total_out_cap, d_out_off, d_out_len, d_status, st))
             return rc;
     }
@@ -336,25 +390,28 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     const uint64_t *h_off = (const uint64_t *)pout;
     const uint32_t *h_len = (const uint32_t *)(pout + 8 * (size_t)(nblocks + 1));
     const int32_t *h_status = (const int32_t *)(pout + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
-    // results: large blocks straight into pinned caller memory, the rest through the staging buffer (one copy per run)
+    // results: blocks whose destination is device memory are copied there on the device; large blocks go straight into
+    // pinned caller memory; the rest through the staging buffer (one copy per run)
     std::vector<uint8_t> direct(nblocks, 0);
     const uint8_t *d_out = (const uint8_t *)ctx->dev_out.p;
     {
-        const uint32_t BIG = 64u << 10;
+        auto dest = [&](uint32_t i) -> int {                     // 0 staged, 1 pinned direct, 2 device
+            if (!(h_status[i] == CRAMGPU_OK && h_len[i] && h_len[i] <= out_cap[i]) || !out[i]) return 0;
+            const MemKind k = mm.kind(out[i]);
+            return k == MEM_DEVICE ? 2 : (k == MEM_PINNED && h_len[i] >= BIG) ? 1 : 0;
+        };
         uint32_t i = 0;
         while (i < nblocks) {
-            bool okb = h_status[i] == CRAMGPU_OK && h_len[i] && h_len[i] <= out_cap[i];
-            if (okb && h_len[i] >= BIG && host_is_pinned(out[i])) {
+            const int di = dest(i);
+            if (di) {
                 direct[i] = 1;
-                CUDA_TRY(ctx, cudaMemcpyAsync(out[i], d_out + h_off[i], h_len[i], cudaMemcpyDeviceToHost, st));
+                CUDA_TRY(ctx, cudaMemcpyAsync(out[i], d_out + h_off[i], h_len[i], di == 2 ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
                 i++;
                 continue;
             }
             uint32_t j = i;
             uint64_t a = h_off[i], b = a;
-            while (j < nblocks) {
-                bool okj = h_status[j] == CRAMGPU_OK && h_len[j] && h_len[j] <= out_cap[j];
-                if (okj && h_len[j] >= BIG && host_is_pinned(out[j])) break;
+            while (j < nblocks && !dest(j)) {
                 if (h_len[j]) b = h_off[j] + h_len[j];
                 j++;
             }

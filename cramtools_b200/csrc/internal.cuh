@@ -132,6 +132,17 @@ struct CopyJob { void *dst; const void *src; size_t n; };
 void par_memcpy(std::vector<CopyJob> &jobs);      // multi-threaded staging copies (clears the list)
 bool host_is_pinned(const void *p);               // page-locked host memory known to CUDA?
 
+// Where a caller's pointer lives.  The host entry points take host OR device pointers for their bulk arrays (unified
+// virtual addressing tells them apart): device memory is used in place, page-locked host memory goes to the DMA engine
+// as it is, pageable host memory is staged.  One MemMap per call remembers the ranges it has already asked about.
+enum MemKind { MEM_PAGEABLE = 0, MEM_PINNED = 1, MEM_DEVICE = 2 };
+struct MemMap {
+    struct Range { uintptr_t lo, hi; MemKind kind; };
+    std::vector<Range> ranges;
+    size_t last = 0;
+    MemKind kind(const void *p);
+};
+
 // rans.cu
 int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
                        const uint32_t *in_len, const uint8_t *order, uint8_t *d_out, uint64_t out_cap,

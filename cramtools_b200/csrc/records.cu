@@ -922,66 +922,81 @@ __global__ void __launch_bounds__(256) k_rec_scan(uint32_t *__restrict__ cnt, co
     if (tid == 0) totals[(size_t)c * NCNT + k] = carry;
 }
 
-// absolute bases: one CTA; thread = container; exclusive scans over the containers of (aligned series bytes, features,
-// payload bytes).  Series regions start at multiples of 16.
-// grand[0] = bytes of streams, grand[1] = features, grand[2] = payload bytes
+// absolute bases: one CTA; thread = container.  The streams buffer is SERIES-major: all containers' FN regions, then all
+// FC regions, ... so that a whole series of the call is one contiguous piece of memory (one copy takes it to the host, or
+// leaves it out).  Region starts are multiples of 16, series starts multiples of 256.
+// grand[0] = bytes of streams, grand[1] = features, grand[2] = payload bytes, grand[4 + 2k] / [5 + 2k] = start / extent of series k
+#define NSCAN (CRAMGPU_S_COUNT + 2)
 __global__ void __launch_bounds__(1024) k_rec_layout(const uint64_t *__restrict__ totals, uint32_t nc, uint64_t *__restrict__ base,
                                                      uint64_t *__restrict__ stream_off, uint64_t *__restrict__ stream_len,
                                                      uint64_t *__restrict__ grand)
 {
-    __shared__ unsigned long long wsum[3][32];
-    __shared__ unsigned long long carry[3];
+    __shared__ unsigned long long wsum[NSCAN][32];
+    __shared__ unsigned long long carry[NSCAN], start[NSCAN];
     const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-    if (tid < 3) carry[tid] = 0;
-    __syncthreads();
-    for (uint32_t c0 = 0; c0 < nc; c0 += 1024) {
-        uint32_t c = c0 + tid;
-        unsigned long long v[3] = {0, 0, 0};
-        if (c < nc) {
-            for (int k = 0; k < CRAMGPU_S_COUNT; k++) v[0] += (totals[(size_t)c * NCNT + k] + 15) & ~15ull;
-            v[1] = totals[(size_t)c * NCNT + C_NFEAT];
-            v[2] = totals[(size_t)c * NCNT + C_PAYLOAD];
-        }
-        unsigned long long inc[3];
+    auto val = [&](uint32_t c, int q) -> unsigned long long {
+        if (c >= nc) return 0;
+        if (q < CRAMGPU_S_COUNT) return (totals[(size_t)c * NCNT + q] + 15) & ~15ull;
+        return totals[(size_t)c * NCNT + (q == CRAMGPU_S_COUNT ? C_NFEAT : C_PAYLOAD)];
+    };
+    // pass 1: extent of every series over all containers -> where each series starts
+    {
+        unsigned long long acc[NSCAN];
 #pragma unroll
-        for (int q = 0; q < 3; q++) {
-            unsigned long long sc = v[q];
+        for (int q = 0; q < NSCAN; q++) acc[q] = 0;
+        for (uint32_t c = tid; c < nc; c += 1024)
+#pragma unroll
+            for (int q = 0; q < NSCAN; q++) acc[q] += val(c, q);
+#pragma unroll
+        for (int q = 0; q < NSCAN; q++) {
+            unsigned long long v = acc[q];
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+            if (lane == 0) wsum[q][w] = v;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long at = 0;
+            for (int q = 0; q < NSCAN; q++) {
+                unsigned long long t = 0;
+                for (int j = 0; j < 32; j++) t += wsum[q][j];
+                if (q < CRAMGPU_S_COUNT) { start[q] = at; grand[4 + 2 * q] = at; grand[5 + 2 * q] = t; at += (t + 255) & ~255ull; }
+                else { start[q] = 0; grand[q - CRAMGPU_S_COUNT + 1] = t; }
+                carry[q] = 0;
+            }
+            grand[0] = at;
+        }
+        __syncthreads();
+    }
+    // pass 2: exclusive scans over the containers, one quantity after the other
+    for (uint32_t c0 = 0; c0 < nc; c0 += 1024) {
+        const uint32_t c = c0 + tid;
+        for (int q = 0; q < NSCAN; q++) {
+            const unsigned long long v = val(c, q);
+            unsigned long long sc = v;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, sc, d);
                 if (lane >= (uint32_t)d) sc += t;
             }
-            inc[q] = sc;
-            if (lane == 31) wsum[q][w] = sc;
-        }
-        __syncthreads();
-        unsigned long long ex[3];
-#pragma unroll
-        for (int q = 0; q < 3; q++) {
-            unsigned long long o = carry[q];
-            for (uint32_t j = 0; j < w; j++) o += wsum[q][j];
-            ex[q] = o + inc[q] - v[q];
-        }
-        if (c < nc) {
-            unsigned long long sb = ex[0];
-            for (int k = 0; k < CRAMGPU_S_COUNT; k++) {
-                uint64_t t = totals[(size_t)c * NCNT + k];
-                base[(size_t)c * NCNT + k] = sb;
-                stream_off[(size_t)c * CRAMGPU_S_COUNT + k] = sb;
-                stream_len[(size_t)c * CRAMGPU_S_COUNT + k] = t;
-                sb += (t + 15) & ~15ull;
+            if (lane == 31) wsum[0][w] = sc;
+            __syncthreads();
+            unsigned long long ex = carry[q] + sc - v;
+            for (uint32_t j = 0; j < w; j++) ex += wsum[0][j];
+            if (c < nc) {
+                if (q < CRAMGPU_S_COUNT) {
+                    const unsigned long long sb = start[q] + ex;
+                    base[(size_t)c * NCNT + q] = sb;
+                    stream_off[(size_t)c * CRAMGPU_S_COUNT + q] = sb;
+                    stream_len[(size_t)c * CRAMGPU_S_COUNT + q] = totals[(size_t)c * NCNT + q];
+                } else {
+                    base[(size_t)c * NCNT + (q == CRAMGPU_S_COUNT ? C_NFEAT : C_PAYLOAD)] = ex;
+                }
             }
-            base[(size_t)c * NCNT + C_NFEAT] = ex[1];
-            base[(size_t)c * NCNT + C_PAYLOAD] = ex[2];
+            __syncthreads();
+            if (tid == 1023) carry[q] = ex + v;
+            __syncthreads();
         }
-        __syncthreads();
-        if (tid == 1023) {
-#pragma unroll
-            for (int q = 0; q < 3; q++) carry[q] = ex[q] + v[q];
-        }
-        __syncthreads();
     }
-    if (tid < 3) grand[tid] = carry[tid];
 }
 
 // ------------------------------------------------------------------------------------------------ decode
@@ -1307,7 +1322,8 @@ struct Uploader {
 
 // device-pointer implementation shared by both encode entry points.  R holds device pointers for the big arrays.
 static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *pol, int npol,
-                                cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len, cudaStream_t st)
+                                cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len, uint64_t *series_span,
+                                cudaStream_t st)
 {
     if (!R || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
     memset(out, 0, sizeof *out);
@@ -1336,7 +1352,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     size_t o_codes = cv.take(32 * (size_t)nc), o_matrix = cv.take(8 * (size_t)nc);
     size_t o_totals = cv.take(8 * (size_t)NCNT * nc), o_base = cv.take(8 * (size_t)NCNT * nc);
     size_t o_soff = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc), o_slen = cv.take(8 * (size_t)CRAMGPU_S_COUNT * nc);
-    size_t o_grand = cv.take(64);
+    size_t o_grand = cv.take(512);
     if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
 
@@ -1391,19 +1407,20 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
 
     // totals (and the per-container tables the caller needs) come back to the host
     size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
-    if (int rc = pinned_reserve(ctx, &ctx->pin_rec, &ctx->pin_rec_cap, 2 * tab + 128)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_rec, &ctx->pin_rec_cap, 2 * tab + 512)) return rc;
     uint8_t *pr = (uint8_t *)ctx->pin_rec;
-    CUDA_TRY(ctx, cudaMemcpyAsync(pr, d_grand, 32, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 32, S + o_status, 4, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 64, d_soff, tab, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 64 + tab, d_slen, tab, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr, d_grand, 256, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 256, S + o_status, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 320, d_soff, tab, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(pr + 320 + tab, d_slen, tab, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     const uint64_t *grand = (const uint64_t *)pr;
-    int32_t dstatus = *(const int32_t *)(pr + 32);
+    int32_t dstatus = *(const int32_t *)(pr + 256);
     if (dstatus) return ctx_fail(ctx, dstatus, "Unsupported cigar operator");
     const uint64_t sbytes = grand[0], nfeat = grand[1], paylen = grand[2];
-    if (h_stream_off) memcpy(h_stream_off, pr + 64, tab);
-    if (h_stream_len) memcpy(h_stream_len, pr + 64 + tab, tab);
+    if (h_stream_off) memcpy(h_stream_off, pr + 320, tab);
+    if (h_stream_len) memcpy(h_stream_len, pr + 320 + tab, tab);
+    if (series_span) memcpy(series_span, grand + 4, 16 * CRAMGPU_S_COUNT);      // (start, extent) of every series in streams
 
     Carver co;
     size_t q_op = co.take(nfeat + 16), q_pos = co.take(4 * nfeat + 16), q_val = co.take(4 * nfeat + 16), q_aux = co.take(4 * nfeat + 16);
@@ -1436,48 +1453,60 @@ extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads
     if (!ctx) return CRAMGPU_ERR_ARG;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
-    if (int rc = features_encode_impl(ctx, reads, policies, n_policies, out, h_stream_off, h_stream_len, st)) return rc;
+    if (int rc = features_encode_impl(ctx, reads, policies, n_policies, out, h_stream_off, h_stream_len, nullptr, st)) return rc;
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     return CRAMGPU_OK;
 }
 
-// copy helper for the host entry points: place host arrays back to back in one pinned buffer / one device buffer
+// copy helper for the host entry points: place the caller's arrays back to back in one device buffer.  Arrays that are in
+// device memory already are used where they are; arrays in memory the caller pinned go to the DMA engine directly; the
+// others are staged through `pin`.
 struct Stager {
-    std::vector<const void *> src; std::vector<size_t> bytes, off; size_t total = 0;
-    size_t add(const void *p, size_t b) { off.push_back(total); src.push_back(p); bytes.push_back(b); total += rup(b ? b : 1, 256); return off.back(); }
-    // H2D of the first `count` entries: arrays in caller-pinned memory go directly, the others through `pin`
-    int to_device(cramgpu_ctx *ctx, uint8_t *pin, uint8_t *D, size_t count, cudaStream_t st)
+    MemMap mm;
+    std::vector<const void *> src; std::vector<size_t> bytes, off; std::vector<uint8_t> kind; size_t total = 0;
+    size_t add(const void *p, size_t b)
+    {
+        const MemKind k = (p && b) ? mm.kind(p) : MEM_PAGEABLE;
+        off.push_back(total); src.push_back(p); bytes.push_back(b); kind.push_back((uint8_t)k);
+        if (k != MEM_DEVICE) total += rup(b ? b : 1, 256);
+        return off.size() - 1;
+    }
+    size_t reserve(size_t b) { off.push_back(total); src.push_back(nullptr); bytes.push_back(0); kind.push_back(MEM_PAGEABLE); total += rup(b ? b : 1, 256); return off.size() - 1; }
+    bool on_device(size_t k) const { return kind[k] == MEM_DEVICE; }
+    // where entry k is (or will be, once to_device has run) in device memory
+    uint8_t *at(uint8_t *D, size_t k) const { return kind[k] == MEM_DEVICE ? (uint8_t *)src[k] : D + off[k]; }
+    int to_device(cramgpu_ctx *ctx, uint8_t *pin, uint8_t *D, cudaStream_t st)
     {
         std::vector<CopyJob> jobs;
-        std::vector<uint8_t> direct(count, 0);
-        for (size_t k = 0; k < count; k++) {
-            if (!bytes[k] || !src[k]) continue;
-            if (bytes[k] >= (64u << 10) && host_is_pinned(src[k])) direct[k] = 1;
-            else jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]});
-        }
+        for (size_t k = 0; k < src.size(); k++)
+            if (bytes[k] && src[k] && kind[k] == MEM_PAGEABLE) jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]});
+            else if (bytes[k] && src[k] && kind[k] == MEM_PINNED && bytes[k] < (64u << 10)) { jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]}); kind[k] = MEM_PAGEABLE; }
         par_memcpy(jobs);
-        for (size_t k = 0; k < count; k++) {
-            if (!bytes[k] || !src[k]) continue;
-            CUDA_TRY(ctx, cudaMemcpyAsync(D + off[k], direct[k] ? src[k] : (const void *)(pin + off[k]), bytes[k], cudaMemcpyHostToDevice, st));
+        for (size_t k = 0; k < src.size(); k++) {
+            if (!bytes[k] || !src[k] || kind[k] == MEM_DEVICE) continue;
+            CUDA_TRY(ctx, cudaMemcpyAsync(D + off[k], kind[k] == MEM_PINNED ? src[k] : (const void *)(pin + off[k]), bytes[k], cudaMemcpyHostToDevice, st));
         }
         return CRAMGPU_OK;
     }
 };
 
-extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies,
-                                       int n_policies, cramgpu_features *out)
+// host-memory encode: copy in, run, copy out.  host_series: bit k = series k comes back to the host; dev_out (optional)
+// receives the same results as device pointers.
+static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies, int n_policies,
+                                uint32_t host_series, cramgpu_features *out, cramgpu_features *dev_out)
 {
     if (!ctx) return CRAMGPU_ERR_ARG;
     if (!R || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
     memset(out, 0, sizeof *out);
+    if (dev_out) memset(dev_out, 0, sizeof *dev_out);
     const uint64_t n = R->n_reads;
     const uint32_t nc = R->n_containers;
     if (n == 0 || nc == 0) return CRAMGPU_OK;
     if (!R->read_off || !R->cigar_off || !R->bases || !R->quals || !R->pos || !R->flag || !R->mapq || !R->ref)
         return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
-    const uint64_t nb = R->read_off[n], ncig = R->cigar_off[n];
+    const uint64_t nb = R->read_off[n], ncig = R->cigar_off[n];           // the two offset tables are read here: host memory
     Stager sg;
     size_t i_ref = sg.add(R->ref, R->ref_total), i_bases = sg.add(R->bases, nb), i_quals = sg.add(R->quals, nb);
     size_t i_roff = sg.add(R->read_off, 8 * (n + 1)), i_cig = sg.add(R->cigar, 4 * ncig), i_coff = sg.add(R->cigar_off, 8 * (n + 1));
@@ -1486,36 +1515,63 @@ extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R,
     if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
-    if (int rc = sg.to_device(ctx, pin, D, sg.src.size(), st)) return rc;
+    if (int rc = sg.to_device(ctx, pin, D, st)) return rc;
     cramgpu_reads dev = *R;
-    dev.ref = D + i_ref; dev.bases = D + i_bases; dev.quals = D + i_quals; dev.read_off = (const uint64_t *)(D + i_roff);
-    dev.cigar = (const uint32_t *)(D + i_cig); dev.cigar_off = (const uint64_t *)(D + i_coff); dev.pos = (const int32_t *)(D + i_pos);
-    dev.flag = (const uint16_t *)(D + i_flag); dev.mapq = D + i_mapq; dev.rflags = R->rflags ? D + i_rfl : nullptr;
+    dev.ref = sg.at(D, i_ref); dev.bases = sg.at(D, i_bases); dev.quals = sg.at(D, i_quals); dev.read_off = (const uint64_t *)sg.at(D, i_roff);
+    dev.cigar = (const uint32_t *)sg.at(D, i_cig); dev.cigar_off = (const uint64_t *)sg.at(D, i_coff); dev.pos = (const int32_t *)sg.at(D, i_pos);
+    dev.flag = (const uint16_t *)sg.at(D, i_flag); dev.mapq = sg.at(D, i_mapq); dev.rflags = R->rflags ? sg.at(D, i_rfl) : nullptr;
     cramgpu_features df;
-    if (int rc = features_encode_impl(ctx, &dev, policies, n_policies, &df, nullptr, nullptr, st)) return rc;
+    uint64_t span[2 * CRAMGPU_S_COUNT];
+    if (int rc = features_encode_impl(ctx, &dev, policies, n_policies, &df, nullptr, nullptr, span, st)) return rc;
+    if (dev_out) *dev_out = df;
 
-    // results to pinned host memory owned by the context
+    // results to pinned host memory owned by the context.  The streams buffer keeps its device layout; a series is one
+    // contiguous piece of it, copied only when asked for.
     const size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
     Stager so;
-    size_t r_op = so.add(df.f_op, df.n_feat), r_pos = so.add(df.f_pos, 4 * df.n_feat), r_val = so.add(df.f_val, 4 * df.n_feat);
-    size_t r_aux = so.add(df.f_aux, 4 * df.n_feat), r_foff = so.add(df.feat_off, 8 * (n + 1)), r_pay = so.add(df.payload, df.payload_len);
-    size_t r_force = so.add(df.force_qs, n), r_mtx = so.add(df.matrix, 8 * (size_t)nc), r_str = so.add(df.streams, df.streams_len);
-    size_t r_soff = so.add(df.stream_off, tab), r_slen = so.add(df.stream_len, tab);
-    size_t r_qso = so.add(df.read_qs_off, 8 * n), r_bao = so.add(df.read_ba_off, 8 * n);
+    size_t r_op = so.reserve(df.n_feat), r_pos = so.reserve(4 * df.n_feat), r_val = so.reserve(4 * df.n_feat);
+    size_t r_aux = so.reserve(4 * df.n_feat), r_foff = so.reserve(8 * (n + 1)), r_pay = so.reserve(df.payload_len);
+    size_t r_force = so.reserve(n), r_mtx = so.reserve(8 * (size_t)nc), r_str = so.reserve(df.streams_len);
+    size_t r_soff = so.reserve(tab), r_slen = so.reserve(tab);
+    size_t r_qso = so.reserve(8 * n), r_bao = so.reserve(8 * n);
     // results get a pinned buffer of their own: they must survive the following block-codec / normaliser calls,
     // which recycle pin_in / pin_out
     if (int rc = pinned_reserve(ctx, &ctx->pin_feat, &ctx->pin_feat_cap, so.total)) return rc;
     uint8_t *po = (uint8_t *)ctx->pin_feat;
-    for (size_t k = 0; k < so.src.size(); k++)
-        if (so.bytes[k]) CUDA_TRY(ctx, cudaMemcpyAsync(po + so.off[k], so.src[k], so.bytes[k], cudaMemcpyDeviceToHost, st));
+    auto down = [&](size_t slot, const void *d, size_t bytes) -> cudaError_t {
+        return bytes ? cudaMemcpyAsync(po + so.off[slot], d, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+    };
+    CUDA_TRY(ctx, down(r_op, df.f_op, df.n_feat)); CUDA_TRY(ctx, down(r_pos, df.f_pos, 4 * df.n_feat));
+    CUDA_TRY(ctx, down(r_val, df.f_val, 4 * df.n_feat)); CUDA_TRY(ctx, down(r_aux, df.f_aux, 4 * df.n_feat));
+    CUDA_TRY(ctx, down(r_foff, df.feat_off, 8 * (n + 1))); CUDA_TRY(ctx, down(r_pay, df.payload, df.payload_len));
+    CUDA_TRY(ctx, down(r_force, df.force_qs, n)); CUDA_TRY(ctx, down(r_mtx, df.matrix, 8 * (size_t)nc));
+    CUDA_TRY(ctx, down(r_soff, df.stream_off, tab)); CUDA_TRY(ctx, down(r_slen, df.stream_len, tab));
+    CUDA_TRY(ctx, down(r_qso, df.read_qs_off, 8 * n)); CUDA_TRY(ctx, down(r_bao, df.read_ba_off, 8 * n));
+    for (int k = 0; k < CRAMGPU_S_COUNT; k++)
+        if (((host_series >> k) & 1) && span[2 * k + 1])
+            CUDA_TRY(ctx, cudaMemcpyAsync(po + so.off[r_str] + span[2 * k], df.streams + span[2 * k], span[2 * k + 1], cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     *out = df;
-    out->f_op = po + r_op; out->f_pos = (const int32_t *)(po + r_pos); out->f_val = (const int32_t *)(po + r_val);
-    out->f_aux = (const int32_t *)(po + r_aux); out->feat_off = (const uint64_t *)(po + r_foff); out->payload = po + r_pay;
-    out->force_qs = po + r_force; out->matrix = po + r_mtx; out->streams = po + r_str;
-    out->stream_off = (const uint64_t *)(po + r_soff); out->stream_len = (const uint64_t *)(po + r_slen);
-    out->read_qs_off = (const uint64_t *)(po + r_qso); out->read_ba_off = (const uint64_t *)(po + r_bao);
+    out->f_op = po + so.off[r_op]; out->f_pos = (const int32_t *)(po + so.off[r_pos]); out->f_val = (const int32_t *)(po + so.off[r_val]);
+    out->f_aux = (const int32_t *)(po + so.off[r_aux]); out->feat_off = (const uint64_t *)(po + so.off[r_foff]); out->payload = po + so.off[r_pay];
+    out->force_qs = po + so.off[r_force]; out->matrix = po + so.off[r_mtx]; out->streams = po + so.off[r_str];
+    out->stream_off = (const uint64_t *)(po + so.off[r_soff]); out->stream_len = (const uint64_t *)(po + so.off[r_slen]);
+    out->read_qs_off = (const uint64_t *)(po + so.off[r_qso]); out->read_ba_off = (const uint64_t *)(po + so.off[r_bao]);
     return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies,
+                                       int n_policies, cramgpu_features *out)
+{
+    return features_encode_host(ctx, R, policies, n_policies, 0xFFFFFFFFu, out, nullptr);
+}
+
+extern "C" int cramgpu_features_encode_resident(cramgpu_ctx *ctx, const cramgpu_reads *R, const cramgpu_qs_policy *policies,
+                                                int n_policies, uint32_t host_series, cramgpu_features *out,
+                                                cramgpu_features *dev_out)
+{
+    if (!dev_out) return ctx ? ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument") : CRAMGPU_ERR_ARG;
+    return features_encode_host(ctx, R, policies, n_policies, host_series, out, dev_out);
 }
 
 static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *d_bases, uint8_t *d_quals,
@@ -1592,56 +1648,64 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     const uint32_t nc = in->n_containers;
     if (n == 0 || nc == 0) return CRAMGPU_OK;
     if (!in->read_off || !in->feat_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
-    const uint64_t nb = in->read_off[n], nf = in->feat_off[n];
-    // extents of the side buffers: the furthest byte any record refers to
-    uint64_t qs_len = 0, ba_len = 0, pay_len = 0;
-    for (uint64_t r = 0; r < n; r++) {
-        uint64_t len = in->read_off[r + 1] - in->read_off[r];
-        if (in->read_qs_off && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
-        if (in->read_ba_off && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
-    }
-    for (uint64_t f = 0; f < nf; f++)
-        if (in->f_op[f] == 'S' || in->f_op[f] == 'I') pay_len = std::max(pay_len, (uint64_t)in->f_val[f] + (uint64_t)in->f_aux[f]);
+    const uint64_t nb = in->read_off[n], nf = in->feat_off[n];           // the offset tables are read here: host memory
     Stager sg;
+    // extents of the side buffers in host memory: the furthest byte any record refers to (buffers in device memory are
+    // used where they are, whatever their extent)
+    uint64_t qs_len = 0, ba_len = 0, pay_len = 0;
+    const bool qs_dev = in->qs && sg.mm.kind(in->qs) == MEM_DEVICE, ba_dev = in->ba && sg.mm.kind(in->ba) == MEM_DEVICE;
+    const bool pay_dev = in->payload && sg.mm.kind(in->payload) == MEM_DEVICE;
+    if ((in->read_qs_off && !qs_dev) || (in->read_ba_off && !ba_dev))
+        for (uint64_t r = 0; r < n; r++) {
+            uint64_t len = in->read_off[r + 1] - in->read_off[r];
+            if (in->read_qs_off && !qs_dev && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
+            if (in->read_ba_off && !ba_dev && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
+        }
+    if (!pay_dev)
+        for (uint64_t f = 0; f < nf; f++)
+            if (in->f_op[f] == 'S' || in->f_op[f] == 'I') pay_len = std::max(pay_len, (uint64_t)in->f_val[f] + (uint64_t)in->f_aux[f]);
     size_t i_ref = sg.add(in->ref, in->ref_total), i_mtx = sg.add(in->matrix, 8 * (size_t)nc), i_pos = sg.add(in->pos, 4 * n);
     size_t i_roff = sg.add(in->read_off, 8 * (n + 1)), i_rfl = sg.add(in->rflags, n), i_foff = sg.add(in->feat_off, 8 * (n + 1));
     size_t i_op = sg.add(in->f_op, nf), i_fp = sg.add(in->f_pos, 4 * nf), i_fv = sg.add(in->f_val, 4 * nf), i_fa = sg.add(in->f_aux, 4 * nf);
-    size_t i_pay = sg.add(in->payload, pay_len), i_qs = sg.add(in->qs, qs_len), i_qso = sg.add(in->read_qs_off, 8 * n);
-    size_t i_ba = sg.add(in->ba, ba_len), i_bao = sg.add(in->read_ba_off, 8 * n);
-    size_t o_bases = sg.add(nullptr, 0); sg.total += rup(nb + 16, 256);
-    size_t o_quals = sg.add(nullptr, 0); sg.total += rup(nb + 16, 256);
-    size_t o_star = sg.add(nullptr, 0); sg.total += rup(n, 256);
-    size_t o_stat = sg.add(nullptr, 0); sg.total += rup(4 * n, 256);
+    size_t i_pay = sg.add(in->payload, pay_dev ? 1 : pay_len), i_qs = sg.add(in->qs, qs_dev ? 1 : qs_len);
+    size_t i_qso = in->read_qs_off ? sg.add(in->read_qs_off, 8 * n) : sg.reserve(8 * n);
+    size_t i_ba = sg.add(in->ba, ba_dev ? 1 : ba_len);
+    size_t i_bao = in->read_ba_off ? sg.add(in->read_ba_off, 8 * n) : sg.reserve(8 * n);
+    // results: into the caller's buffers when those are device memory, else into slots of the staging buffer
+    const bool b_dev = sg.mm.kind(bases) == MEM_DEVICE, q_dev = sg.mm.kind(quals) == MEM_DEVICE;
+    size_t o_bases = sg.reserve(b_dev ? 1 : nb + 16), o_quals = sg.reserve(q_dev ? 1 : nb + 16);
+    size_t o_star = sg.reserve(n), o_stat = sg.reserve(4 * n);
     if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
-    if (int rc = sg.to_device(ctx, pin, D, sg.src.size(), st)) return rc;
+    if (int rc = sg.to_device(ctx, pin, D, st)) return rc;
     // records without a stored array / BA bases still need valid offset tables
-    if (!in->read_qs_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_qso, 0xFF, 8 * n, st));
-    if (!in->read_ba_off) CUDA_TRY(ctx, cudaMemsetAsync(D + i_bao, 0xFF, 8 * n, st));
+    if (!in->read_qs_off) CUDA_TRY(ctx, cudaMemsetAsync(sg.at(D, i_qso), 0xFF, 8 * n, st));
+    if (!in->read_ba_off) CUDA_TRY(ctx, cudaMemsetAsync(sg.at(D, i_bao), 0xFF, 8 * n, st));
     cramgpu_norm_in dev = *in;
-    dev.ref = D + i_ref; dev.matrix = D + i_mtx; dev.pos = (const int32_t *)(D + i_pos); dev.read_off = (const uint64_t *)(D + i_roff);
-    dev.rflags = D + i_rfl; dev.feat_off = (const uint64_t *)(D + i_foff); dev.f_op = D + i_op; dev.f_pos = (const int32_t *)(D + i_fp);
-    dev.f_val = (const int32_t *)(D + i_fv); dev.f_aux = (const int32_t *)(D + i_fa); dev.payload = D + i_pay; dev.qs = D + i_qs;
-    dev.read_qs_off = (const uint64_t *)(D + i_qso); dev.ba = D + i_ba; dev.read_ba_off = (const uint64_t *)(D + i_bao);
-    if (int rc = normalize_impl(ctx, &dev, D + o_bases, D + o_quals, D + o_star, (int32_t *)(D + o_stat), st)) return rc;
+    dev.ref = sg.at(D, i_ref); dev.matrix = sg.at(D, i_mtx); dev.pos = (const int32_t *)sg.at(D, i_pos); dev.read_off = (const uint64_t *)sg.at(D, i_roff);
+    dev.rflags = sg.at(D, i_rfl); dev.feat_off = (const uint64_t *)sg.at(D, i_foff); dev.f_op = sg.at(D, i_op); dev.f_pos = (const int32_t *)sg.at(D, i_fp);
+    dev.f_val = (const int32_t *)sg.at(D, i_fv); dev.f_aux = (const int32_t *)sg.at(D, i_fa); dev.payload = sg.at(D, i_pay); dev.qs = sg.at(D, i_qs);
+    dev.read_qs_off = (const uint64_t *)sg.at(D, i_qso); dev.ba = sg.at(D, i_ba); dev.read_ba_off = (const uint64_t *)sg.at(D, i_bao);
+    uint8_t *d_b = b_dev ? bases : sg.at(D, o_bases), *d_q = q_dev ? quals : sg.at(D, o_quals);
+    if (int rc = normalize_impl(ctx, &dev, d_b, d_q, sg.at(D, o_star), (int32_t *)sg.at(D, o_stat), st)) return rc;
     if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256))) return rc;
     uint8_t *po = (uint8_t *)ctx->pin_out;
     size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256);
-    const bool pb = nb && host_is_pinned(bases), pq = nb && host_is_pinned(quals);
-    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(pb ? bases : po, D + o_bases, nb, cudaMemcpyDeviceToHost, st));
-    if (nb) CUDA_TRY(ctx, cudaMemcpyAsync(pq ? quals : po + p_q, D + o_quals, nb, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, D + o_star, n, cudaMemcpyDeviceToHost, st));
-    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_t, D + o_stat, 4 * n, cudaMemcpyDeviceToHost, st));
+    const bool pb = nb && !b_dev && host_is_pinned(bases), pq = nb && !q_dev && host_is_pinned(quals);
+    if (nb && !b_dev) CUDA_TRY(ctx, cudaMemcpyAsync(pb ? bases : po, d_b, nb, cudaMemcpyDeviceToHost, st));
+    if (nb && !q_dev) CUDA_TRY(ctx, cudaMemcpyAsync(pq ? quals : po + p_q, d_q, nb, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, sg.at(D, o_star), n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_t, sg.at(D, o_stat), 4 * n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     {
         std::vector<CopyJob> jobs;
-        if (nb && !pb) jobs.push_back(CopyJob{bases, po, (size_t)nb});
-        if (nb && !pq) jobs.push_back(CopyJob{quals, po + p_q, (size_t)nb});
+        if (nb && !b_dev && !pb) jobs.push_back(CopyJob{bases, po, (size_t)nb});
+        if (nb && !q_dev && !pq) jobs.push_back(CopyJob{quals, po + p_q, (size_t)nb});
+        jobs.push_back(CopyJob{qual_star, po + p_s, (size_t)n});
+        jobs.push_back(CopyJob{status, po + p_t, (size_t)(4 * n)});
         par_memcpy(jobs);
     }
-    memcpy(qual_star, po + p_s, n);
-    memcpy(status, po + p_t, 4 * n);
     for (uint64_t r = 0; r < n; r++)
         if (status[r]) return ctx_fail(ctx, status[r], "record %llu lies outside its reference region (ArrayIndexOutOfBoundsException in the reference)", (unsigned long long)r);
     return CRAMGPU_OK;

@@ -53,6 +53,8 @@ _lib.SIGNATURES.update({
     'cramgpu_features_encode': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features)]),
     'cramgpu_features_encode_dev': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features),
                                               u64p, u64p, C.c_void_p]),
+    'cramgpu_features_encode_resident': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.c_uint32,
+                                                   C.POINTER(Features), C.POINTER(Features)]),
     'cramgpu_normalize_decode': (C.c_int, [C.c_void_p, C.POINTER(NormIn), u8p, u8p, u8p, i32p]),
     'cramgpu_normalize_decode_dev': (C.c_int, [C.c_void_p, C.POINTER(NormIn), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                                C.c_void_p]),
@@ -170,6 +172,24 @@ def features_encode(rd, ref, spec=None, cont_off=None, ref_off=None, ref_len=Non
     rc = ctx.lib.cramgpu_features_encode(ctx.handle, C.byref(R), pol, npol, C.byref(F))
     ctx.check(rc)
     return EncodedFeatures(F, n, nc)
+
+
+def features_encode_resident(rd, ref, spec=None, host_series=None, cont_off=None, ref_off=None, ref_len=None, ctx=None):
+    """cramgpu_features_encode_resident: as features_encode, but the results also stay on the device and only the series
+    named in host_series (default: all but QS and BA) come back to the host.  -> (EncodedFeatures, Features with DEVICE
+    pointers); the device result is valid until the next record call on ctx."""
+    ctx = ctx or _lib.default_context()
+    keep = []
+    R, n, nc = _reads_struct(rd, ref, cont_off, ref_off, ref_len, keep)
+    pol, npol = _policy_args(spec)
+    if host_series is None:
+        host_series = [s for s in SERIES if s not in ('QS', 'BA')]
+    mask = 0
+    for name in host_series:
+        mask |= 1 << SERIES.index(name)
+    F, D = Features(), Features()
+    ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(R), pol, npol, mask, C.byref(F), C.byref(D)))
+    return EncodedFeatures(F, n, nc), D
 
 
 def normalize_decode(pos, read_off, rflags, enc, window, window_start0, matrix, cont_off=None, win_off=None, win_len=None,

@@ -97,6 +97,14 @@ uint32_t cramgpu_rans_bound(uint32_t n);
  *   out_len[i]         bytes written
  *   status             optional per-block status array (may be NULL)
  * Returns the first non-OK per-block status, else CRAMGPU_OK.
+ *
+ * Where the bytes live: in[i] and out[i] may each point to pageable host memory (staged), to host memory the
+ * caller page-locked (handed to the DMA engine as it is), or to DEVICE memory (unified addressing tells them
+ * apart).  A raw block in device memory is coded where it is -- e.g. a series cramgpu_features_encode_resident
+ * left on the device -- and a destination in device memory receives its bytes without crossing the bus; that is
+ * how a host keeps intermediate series on the GPU between calls.  (Compressed INPUT blocks of the decoder are
+ * host memory; blocks that already sit on the device go through cramgpu_rans_decode_dev.)  No counterpart in
+ * the reference, whose blocks are always Java arrays.
  */
 int cramgpu_rans_encode_batch(cramgpu_ctx *ctx, uint32_t nblocks,
                               const uint8_t *const *in, const uint32_t *in_len, const uint8_t *order,
@@ -280,7 +288,8 @@ typedef struct cramgpu_features {
     uint64_t payload_len;
     const uint8_t *force_qs;      /* [n_reads] bit0 = CramCompressionRecord.isForcePreserveQualityScores(), bit1 = has a score array */
     const uint8_t *matrix;        /* [n_containers][8]: 5 bytes of SubstitutionMatrix.getEncodedMatrix(), 3 pad */
-    const uint8_t *streams;       /* all series bytes; every (container, series) region starts at a multiple of 16 */
+    const uint8_t *streams;       /* all series bytes, SERIES-major: the FN regions of all containers, then FC, ...; every
+                                     (container, series) region starts at a multiple of 16 */
     uint64_t streams_len;
     const uint64_t *stream_off;   /* [n_containers][CRAMGPU_S_COUNT] */
     const uint64_t *stream_len;   /* [n_containers][CRAMGPU_S_COUNT] */
@@ -298,10 +307,22 @@ typedef struct cramgpu_features {
  * stream_off / stream_len and the scalars are also mirrored on the host (h_stream_off, h_stream_len) so that
  * the caller can hand the series straight to cramgpu_rans_encode_dev.  The call returns after the device
  * has finished (it needs the totals).
- * Reads longer than 4096 bases are rejected with CRAMGPU_ERR_UNSUPPORTED when a per-base policy (R/N/D/I) is present.
+ * In the host variants the bulk arrays of `reads` (ref, bases, quals, cigar, pos, flag, mapq, rflags) may also be
+ * device pointers -- e.g. a reference that stays resident across calls -- and are then used where they are;
+ * read_off and cigar_off are read on the host and must be host memory.
+ *
+ * cramgpu_features_encode_resident: the host variant for callers that code the big series on the GPU right away.
+ * Results stay in device memory (`dev_out`, device pointers, valid until the next record call on ctx) and come
+ * back to the host (`out`) as usual, except that of `streams` only the series whose bit is set in `host_series`
+ * (1u << CRAMGPU_S_x) are copied; `out->streams` keeps the device layout, the other series' bytes are left
+ * unwritten.  Typical use: host_series = all but QS and BA, then cramgpu_rans_encode_batch with
+ * in[i] = dev_out->streams + stream_off[c][QS].  No counterpart in the reference.
  */
 int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
                             int n_policies, cramgpu_features *out);
+int cramgpu_features_encode_resident(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
+                                     int n_policies, uint32_t host_series, cramgpu_features *out,
+                                     cramgpu_features *dev_out);
 int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
                                 int n_policies, cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len,
                                 void *stream);
@@ -339,6 +360,10 @@ typedef struct cramgpu_norm_in {
  * reference yields SAMRecord.NULL_QUALS; status[r] = CRAMGPU_ERR_CORRUPT where the reference would throw
  * ArrayIndexOutOfBoundsException (record outside its region).  Host variant takes/returns host memory; the
  * device variant takes device pointers for everything not marked HOST and enqueues on `stream`.
+ * In the host variant ref, matrix, the feature arrays, payload, qs, ba and the outputs bases / quals may also be
+ * device pointers (a QS series cramgpu_rans_decode_batch left on the device, say) and are then used in place;
+ * the per-record tables (pos, read_off, rflags, feat_off, read_qs_off, read_ba_off) and qual_star / status are
+ * host memory.
  */
 int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *bases, uint8_t *quals,
                              uint8_t *qual_star, int32_t *status);

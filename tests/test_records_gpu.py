@@ -198,3 +198,85 @@ def test_host_chain_features_then_block_codec(R, gpu_ctx):
     # the first call's results are still intact after the other calls reused the staging buffers
     enc2 = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
     assert enc2.streams.tobytes() == enc.streams.tobytes()
+
+
+def test_resident_series_and_device_pointers(R, gpu_ctx):
+    """The host entry points with intermediates left on the device: encode with QS/BA resident, code them from device
+    pointers, decode QS into device memory, restore from it -- same bytes as the all-host path at every stage."""
+    import ctypes as C
+    import torch
+    from cramtools_b200 import ExternalCompression, rans_bound
+    from cramtools_b200._lib import u8p, u32p, i32p, u8pp
+    ref, rd, cont_off = _sim(12000, 5, 41, unmapped_tail=200)
+    n, nc = len(rd['pos']), 5
+    host = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    enc, dev = R.features_encode_resident(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    KQS, KBA = R.SERIES.index('QS'), R.SERIES.index('BA')
+    assert (enc.stream_off == host.stream_off).all() and (enc.stream_len == host.stream_len).all()
+    for c in range(nc):
+        for name in R.SERIES:
+            if name not in ('QS', 'BA'):
+                assert enc.series(c, name) == host.series(c, name), (c, name)
+    for name in ('f_op', 'f_pos', 'f_val', 'f_aux', 'feat_off', 'payload', 'force_qs', 'read_qs_off', 'read_ba_off'):
+        assert (getattr(enc, name) == getattr(host, name)).all(), name
+    # rANS of QS and BA straight from the device-resident series, plus one ordinary host block, in one call
+    extra = np.frombuffer(b'host block ' * 700, np.uint8).copy()
+    blocks = [(int(dev.streams) + int(enc.stream_off[c, k]), int(enc.stream_len[c, k])) for c in range(nc) for k in (KQS, KBA)]
+    blocks.append((extra.ctypes.data, extra.size))
+    nb = len(blocks)
+    in_ptr = np.array([b[0] for b in blocks], np.uint64); in_len = np.array([b[1] for b in blocks], np.uint32)
+    order = np.ones(nb, np.uint8)
+    caps = np.array([rans_bound(int(x)) for x in in_len], np.uint32)
+    outs = [np.zeros(int(cp), np.uint8) for cp in caps]
+    out_ptr = np.array([o.ctypes.data for o in outs], np.uint64)
+    out_len = np.zeros(nb, np.uint32); status = np.zeros(nb, np.int32)
+    gpu_ctx.check(gpu_ctx.lib.cramgpu_rans_encode_batch(gpu_ctx.handle, nb, C.cast(in_ptr.ctypes.data, u8pp), in_len.ctypes.data_as(u32p),
+                                                        order.ctypes.data_as(u8p), C.cast(out_ptr.ctypes.data, u8pp),
+                                                        caps.ctypes.data_as(u32p), out_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+    want = [host.series(c, name) for c in range(nc) for name in ('QS', 'BA')] + [extra.tobytes()]
+    for i in range(nb):
+        assert outs[i][:out_len[i]].tobytes() == ExternalCompression.rans(want[i], 1, ctx=gpu_ctx), i
+    # decode: QS and BA land in device memory (one buffer laid out like `streams`), the host block in host memory
+    d_streams = torch.zeros(int(host.streams.size) + 64, dtype=torch.uint8, device='cuda')
+    back_host = np.zeros(extra.size + 16, np.uint8)
+    dst = [int(d_streams.data_ptr()) + int(enc.stream_off[c, k]) for c in range(nc) for k in (KQS, KBA)] + [back_host.ctypes.data]
+    dst_ptr = np.array(dst, np.uint64)
+    dcap = np.array([int(x) + 16 for x in in_len], np.uint32)
+    back_len = np.zeros(nb, np.uint32)
+    gpu_ctx.check(gpu_ctx.lib.cramgpu_rans_decode_batch(gpu_ctx.handle, nb, C.cast(out_ptr.ctypes.data, u8pp), out_len.ctypes.data_as(u32p),
+                                                        C.cast(dst_ptr.ctypes.data, u8pp), dcap.ctypes.data_as(u32p),
+                                                        back_len.ctypes.data_as(u32p), status.ctypes.data_as(i32p)))
+    assert (back_len == in_len).all()
+    assert back_host[:extra.size].tobytes() == extra.tobytes()
+    got = d_streams.cpu().numpy()
+    for c in range(nc):
+        for k in (KQS, KBA):
+            o, ln = int(enc.stream_off[c, k]), int(enc.stream_len[c, k])
+            assert got[o:o + ln].tobytes() == host.streams[o:o + ln].tobytes(), (c, k)
+    # restore with qs / ba as device pointers
+    rfl = (enc.force_qs & 1).astype(np.uint8)
+    rfl[(rd['flag'] & 4) != 0] |= 2
+    keep = []
+    I = R.NormIn()
+    co = np.ascontiguousarray(cont_off, np.uint64); wo = np.zeros(nc, np.uint64); wl = np.full(nc, ref.size, np.uint64); w0 = np.zeros(nc, np.int64)
+    arrs = dict(pos=np.ascontiguousarray(rd['pos'], np.int32), read_off=np.ascontiguousarray(rd['read_off'], np.uint64), rflags=rfl,
+                feat_off=enc.feat_off, f_op=enc.f_op if enc.f_op.size else np.zeros(1, np.uint8),
+                f_pos=enc.f_pos if enc.f_pos.size else np.zeros(1, np.int32), f_val=enc.f_val if enc.f_val.size else np.zeros(1, np.int32),
+                f_aux=enc.f_aux if enc.f_aux.size else np.zeros(1, np.int32), payload=enc.payload if enc.payload.size else np.zeros(1, np.uint8),
+                read_qs_off=enc.read_qs_off, read_ba_off=enc.read_ba_off, matrix=np.ascontiguousarray(enc.matrix, np.uint8))
+    refa = np.ascontiguousarray(ref, np.uint8)
+    keep.extend([co, wo, wl, w0, refa] + list(arrs.values()))
+    I.n_reads = n; I.n_containers = nc
+    from cramtools_b200._lib import u64p
+    i64p = C.POINTER(C.c_int64)
+    I.cont_off = co.ctypes.data_as(u64p); I.win_off = wo.ctypes.data_as(u64p); I.win_len = wl.ctypes.data_as(u64p)
+    I.win_start0 = w0.ctypes.data_as(i64p); I.ref = refa.ctypes.data; I.ref_total = refa.size
+    for k, v in arrs.items():
+        setattr(I, k, v.ctypes.data)
+    I.qs = d_streams.data_ptr(); I.ba = d_streams.data_ptr()
+    total = int(rd['read_off'][n])
+    bases = np.zeros(total, np.uint8); quals = np.zeros(total, np.uint8); star = np.zeros(n, np.uint8); st = np.zeros(n, np.int32)
+    gpu_ctx.check(gpu_ctx.lib.cramgpu_normalize_decode(gpu_ctx.handle, C.byref(I), bases.ctypes.data_as(u8p), quals.ctypes.data_as(u8p),
+                                                       star.ctypes.data_as(u8p), st.ctypes.data_as(i32p)))
+    assert (st == 0).all() and (star == 0).all()
+    assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
