@@ -496,12 +496,22 @@ def run_ours(args):
 
     # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
     n_e2e = min(n_cont, args.e2e_containers)
-    e2e = run_e2e(lanes[0].ctx, args, ref, rd, extra, nu, n_e2e, world, barrier, args.e2e_pipeline)
+    st0 = lanes[0]
+    stats = dict(raw_bytes=st0.raw_bytes, comp_bytes=st0.comp_bytes, raw_o0=st0.raw_o0, qs_bytes=st0.qs_bytes, nblk=st0.nblk)
+    comp_hint = st0.c_len[:n_e2e * st0.NB].copy()
+    # the device-resident leg is over: its buffers and contexts go before the end-to-end leg allocates its own
+    for ln in lanes:
+        ln.ctx.close()
+    del lanes, st0, ln
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
+    e2e = run_e2e(args, ref, rd, extra, nu, n_e2e, world, barrier, args.e2e_pipeline, comp_hint, local)
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
-        raw_bytes = lanes[0].raw_bytes; comp_bytes = lanes[0].comp_bytes
-        o1_raw = raw_bytes - lanes[0].raw_o0
+        raw_bytes = stats['raw_bytes']; comp_bytes = stats['comp_bytes']
+        o1_raw = raw_bytes - stats['raw_o0']
         comp1 = comp_bytes * (o1_raw / raw_bytes)
         algo = {'k_enc1': o1_raw + comp1, 'k_dec1': o1_raw + comp1, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
                 'k_rec_simple_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_simple_write': n_reads * (2 * READ_LEN + 60.0),
@@ -522,7 +532,7 @@ def run_ours(args):
             'rans': {'raw_GB_per_step_per_gpu': raw_bytes / 1e9, 'compressed_ratio': comp_bytes / raw_bytes,
                      'encode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_enc * 1e-3) / 1e9,
                      'decode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_dec * 1e-3) / 1e9,
-                     'qs_block_bytes': lanes[0].qs_bytes / n_cont, 'state_lanes_in_flight': int(4 * lanes[0].nblk)},
+                     'qs_block_bytes': stats['qs_bytes'] / n_cont, 'state_lanes_in_flight': int(4 * stats['nblk'])},
             'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
             'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
@@ -553,22 +563,27 @@ class E2EContext(object):
         self.F, self.D = rec.Features(), rec.Features()
         self.in_ptr = np.zeros(nblk, np.uint64); self.in_len = np.zeros(nblk, np.uint32)
         self.in_ptr.reshape(n_cont, NB)[:, 2:] = inp['ex_ptr']; self.in_len.reshape(n_cont, NB)[:, 2:] = inp['ex_len']
-        # output buffers: generous fixed slots (the reference allocates rans_bound(n) per block)
-        cap_qs = rans_bound(READS_PER_CONTAINER * READ_LEN)
-        self.caps = np.tile(np.array([cap_qs] + [rans_bound(60000)] * (NB - 1), np.uint32), n_cont)
+        # compressed blocks, the product of the encode side: one pinned buffer, a slot per block.  (The reference allocates
+        # rans_bound(n) per block and trims; here the slots are the sizes the device-resident leg saw plus a margin, so that
+        # the page-locked memory stays in proportion to the data.)
+        self.caps = ((inp['comp_hint'].astype(np.int64) * 9 // 8 + 4096 + 15) & ~15).astype(np.uint32)
         self.cap_off = np.concatenate([[0], np.cumsum(self.caps.astype(np.int64))])
-        self.comp = pinned_empty(self.cap_off[-1], np.uint8)                    # compressed blocks: the product of the encode side
+        self.comp = pinned_empty(self.cap_off[-1], np.uint8)
         self.out_ptr = (np.uint64(self.comp.ctypes.data) + self.cap_off[:-1].astype(np.uint64))
         self.out_len = np.zeros(nblk, np.uint32); self.status = np.zeros(nblk, np.int32)
-        # decoded series: QS and BA stay in device memory (same slots), the host-parsed series come back to the host
-        self.d_back = torch.empty(int(self.cap_off[-1]), dtype=torch.uint8, device='cuda')
-        self.back = pinned_empty(self.cap_off[-1], np.uint8)
-        bp = (np.uint64(self.back.ctypes.data) + self.cap_off[:-1].astype(np.uint64)).reshape(n_cont, NB)
-        dp = (np.uint64(self.d_back.data_ptr()) + self.cap_off[:-1].astype(np.uint64)).reshape(n_cont, NB)
-        bp[:, :2] = dp[:, :2]
+        # decoded series: QS and BA stay in device memory, the host-parsed series come back to the host
+        raw_qs = READS_PER_CONTAINER * READ_LEN + 64
+        self.dcap = np.tile(np.array([raw_qs, raw_qs] + [60000 + 64] * (NB - 2), np.uint32), n_cont)
+        dslot = np.concatenate([[0], np.cumsum(self.dcap.astype(np.int64))])
+        self.d_back = torch.empty(int(dslot[-1]), dtype=torch.uint8, device='cuda')
+        self.back = pinned_empty(int((60000 + 64) * (NB - 2) * n_cont), np.uint8)
+        hslot = (np.arange(n_cont * (NB - 2), dtype=np.int64) * (60000 + 64)).reshape(n_cont, NB - 2)
+        bp = np.zeros((n_cont, NB), np.uint64)
+        bp[:, :2] = (np.uint64(self.d_back.data_ptr()) + dslot[:-1].astype(np.uint64)).reshape(n_cont, NB)[:, :2]
+        bp[:, 2:] = np.uint64(self.back.ctypes.data) + hslot.astype(np.uint64)
         self.back_ptr = np.ascontiguousarray(bp.reshape(-1))
         self.back_len = np.zeros(nblk, np.uint32)
-        self.qs_slot = self.cap_off[np.arange(n_cont) * NB].astype(np.int64)      # where container c's QS lands in d_back
+        self.qs_slot = dslot[np.arange(n_cont) * NB].astype(np.int64)             # where container c's QS lands in d_back
         self.rfl = np.ones(n_reads, np.uint8)
         self.rba = np.full(n_reads, 0xFFFFFFFFFFFFFFFF, np.uint64)
         self.rq_new = np.zeros(n_reads, np.uint64)
@@ -582,14 +597,28 @@ class E2EContext(object):
         N.ba = vp(self.d_back.data_ptr()); N.read_ba_off = vp(self.rba.ctypes.data); N.qs = vp(self.d_back.data_ptr())
         self.ms = {'features_encode_resident': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0, 'normalize_decode': 0.0, 'host_glue': 0.0}
         self.h2d = self.d2h = 0
+        self.stages = (self.stage_features, self.stage_rans_encode, self.stage_rans_decode, self.stage_normalize)
 
-    def encode(self):
-        """reads (host) -> compressed blocks (host) + the small series and the feature arrays (host)"""
+    def step(self, locks=None):
+        for k, stage in enumerate(self.stages):
+            if locks is None:
+                stage()
+            else:
+                with locks[k]:
+                    stage()
+
+    def stage_features(self):
+        """reads (host) -> the small series and the feature arrays (host); QS / BA stay on the device"""
+        ctx, inp, F, D = self.ctx, self.inp, self.F, self.D
+        t0 = time.perf_counter()
+        ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(inp['R']), None, -1, inp['host_series'], C.byref(F), C.byref(D)))
+        self.ms['features_encode_resident'] += (time.perf_counter() - t0) * 1e3
+
+    def stage_rans_encode(self):
+        """series -> compressed blocks (host)"""
         from cramtools_b200._lib import u8p, u32p, u64p, i32p, u8pp
         ctx, inp, rec, F, D = self.ctx, self.inp, self.rec, self.F, self.D
         n_cont, NB = inp['n_cont'], inp['NB']
-        t0 = time.perf_counter()
-        ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(inp['R']), None, -1, inp['host_series'], C.byref(F), C.byref(D)))
         t1 = time.perf_counter()
         self.soff = np.ctypeslib.as_array(C.cast(F.stream_off, u64p), (n_cont, 12)); self.slen = np.ctypeslib.as_array(C.cast(F.stream_len, u64p), (n_cont, 12))
         v = self.in_ptr.reshape(n_cont, NB); w = self.in_len.reshape(n_cont, NB)
@@ -601,18 +630,24 @@ class E2EContext(object):
                                                     inp['order'].ctypes.data_as(u8p), C.cast(self.out_ptr.ctypes.data, u8pp), self.caps.ctypes.data_as(u32p),
                                                     self.out_len.ctypes.data_as(u32p), self.status.ctypes.data_as(i32p)))
         t3 = time.perf_counter()
-        self.ms['features_encode_resident'] += (t1 - t0) * 1e3; self.ms['rans_encode_batch'] += (t3 - t2) * 1e3; self.ms['host_glue'] += (t2 - t1) * 1e3
+        self.ms['rans_encode_batch'] += (t3 - t2) * 1e3; self.ms['host_glue'] += (t2 - t1) * 1e3
 
-    def decode(self):
-        """compressed blocks (host) + records as CramRecordReader would hand them over -> bases and qualities (host)"""
-        from cramtools_b200._lib import u8p, u32p, u64p, i32p, u8pp
+    def stage_rans_decode(self):
+        """compressed blocks (host) -> series: QS / BA into device memory, the host-parsed ones into host memory"""
+        from cramtools_b200._lib import u32p, i32p, u8pp
+        ctx = self.ctx
+        t3 = time.perf_counter()
+        ctx.check(ctx.lib.cramgpu_rans_decode_batch(ctx.handle, self.nblk, C.cast(self.out_ptr.ctypes.data, u8pp), self.out_len.ctypes.data_as(u32p),
+                                                    C.cast(self.back_ptr.ctypes.data, u8pp), self.dcap.ctypes.data_as(u32p),
+                                                    self.back_len.ctypes.data_as(u32p), self.status.ctypes.data_as(i32p)))
+        self.ms['rans_decode_batch'] += (time.perf_counter() - t3) * 1e3
+
+    def stage_normalize(self):
+        """records as CramRecordReader would hand them over + the decoded QS / BA on the device -> bases and qualities (host)"""
+        from cramtools_b200._lib import u8p, u64p, i32p
         ctx, inp, F, N = self.ctx, self.inp, self.F, self.N
         n_reads = inp['n_reads']
         vp = C.c_void_p
-        t3 = time.perf_counter()
-        ctx.check(ctx.lib.cramgpu_rans_decode_batch(ctx.handle, self.nblk, C.cast(self.out_ptr.ctypes.data, u8pp), self.out_len.ctypes.data_as(u32p),
-                                                    C.cast(self.back_ptr.ctypes.data, u8pp), self.caps.ctypes.data_as(u32p),
-                                                    self.back_len.ctypes.data_as(u32p), self.status.ctypes.data_as(i32p)))
         t4 = time.perf_counter()
         # score arrays sit inside the decoded QS series: per read, its offset there (the encoder's offset, moved to the QS slot)
         rq = np.ctypeslib.as_array(C.cast(F.read_qs_off, u64p), (n_reads,))
@@ -626,7 +661,7 @@ class E2EContext(object):
         ctx.check(ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(N), self.o_b.ctypes.data_as(u8p), self.o_q.ctypes.data_as(u8p),
                                                    self.o_s.ctypes.data_as(u8p), self.o_t.ctypes.data_as(i32p)))
         t6 = time.perf_counter()
-        self.ms['rans_decode_batch'] += (t4 - t3) * 1e3; self.ms['normalize_decode'] += (t6 - t5) * 1e3; self.ms['host_glue'] += (t5 - t4) * 1e3
+        self.ms['normalize_decode'] += (t6 - t5) * 1e3; self.ms['host_glue'] += (t5 - t4) * 1e3
         # bytes that crossed the bus in this step
         a, nf, nb = inp['a'], int(F.n_feat), n_reads * READ_LEN
         KQS, KBA = inp['KQS'], inp['KBA']
@@ -641,11 +676,12 @@ class E2EContext(object):
                        + comp_bytes + ex_bytes + 2 * nb + 5 * n_reads)
 
 
-def run_e2e(ctx0, args, ref, rd, extra, nu, n_cont, world, barrier, depth):
+def run_e2e(args, ref, rd, extra, nu, n_cont, world, barrier, depth, comp_hint, device):
     """the same step through the host-memory entry points: inputs start in (pinned) host memory, the compressed blocks and
     the restored bases / qualities end in host memory, every copy inside the timed region.  Intermediate series the host
-    does not parse (QS, BA) stay on the device between the calls.  `depth` contexts take consecutive steps in turn, so the
-    host-to-device traffic of one step's encode overlaps the device-to-host traffic of the previous step's decode."""
+    does not parse (QS, BA) stay on the device between the calls.  `depth` contexts take consecutive steps in turn, each call
+    guarded by its own lock, so the host-to-device traffic of one step's encode overlaps the device-to-host traffic and the
+    coder kernels of the steps before it."""
     import cramtools_b200
     from cramtools_b200 import records as rec
     from cramtools_b200._lib import u64p
@@ -690,42 +726,37 @@ def run_e2e(ctx0, args, ref, rd, extra, nu, n_cont, world, barrier, depth):
                ex_ptr=np.array([e.ctypes.data for e in ex], np.uint64).reshape(n_cont, NX),
                ex_len=np.array([e.size for e in ex], np.uint32).reshape(n_cont, NX),
                order=np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont), KQS=KQS, KBA=KBA,
-               host_series=sum(1 << k for k in range(len(rec.SERIES)) if k not in (KQS, KBA)),
+               host_series=sum(1 << k for k in range(len(rec.SERIES)) if k not in (KQS, KBA)), comp_hint=comp_hint,
                win_off=np.tile(ws, reps)[:n_cont].astype(np.uint64), win_len=np.tile(we - ws, reps)[:n_cont].astype(np.uint64),
                win_s0=np.tile(ws, reps)[:n_cont].astype(np.int64))
     depth = max(1, depth)
-    ctxs = [ctx0] + [cramtools_b200.Context(torch.cuda.current_device()) for _ in range(depth - 1)]
+    ctxs = [cramtools_b200.Context(device) for _ in range(depth)]
     lanes = [E2EContext(c, inp, pinned_empty) for c in ctxs]
     for ln in lanes:
-        ln.encode(); ln.decode()
+        ln.step()
         assert np.array_equal(ln.o_b, a['bases']) and np.array_equal(ln.o_q, a['quals']), 'e2e round trip mismatch'
+        ln.o_b[:] = 0; ln.o_q[:] = 0
     barrier()
-    k = max(1, min(args.steps, 4))
+    k = max(depth, min(args.steps, 6))
     for ln in lanes:
         for key in ln.ms:
             ln.ms[key] = 0.0
-    enc_lock, dec_lock = threading.Lock(), threading.Lock()
+    # one lock per call: at most one context inside each of the four calls, different calls of different steps overlap
+    locks = [threading.Lock() for _ in range(4)]
     errs = []
-
-    def work(ln, i):
-        try:
-            torch.cuda.set_device(torch.cuda.current_device())
-            for _ in range(i, k, depth):
-                with enc_lock:
-                    ln.encode()
-                with dec_lock:
-                    ln.decode()
-        except Exception as e:      # noqa: BLE001
-            errs.append(e)
     dev_index = torch.cuda.current_device()
 
     def runner(ln, i):
-        torch.cuda.set_device(dev_index)
-        work(ln, i)
+        try:
+            torch.cuda.set_device(dev_index)
+            for _ in range(i, k, depth):
+                ln.step(None if os.environ.get('CRAMGPU_E2E_NOLOCK') else locks)
+        except Exception as e:      # noqa: BLE001
+            errs.append(e)
     t0 = time.perf_counter()
     if depth == 1:
         for _ in range(k):
-            lanes[0].encode(); lanes[0].decode()
+            lanes[0].step()
     else:
         th = [threading.Thread(target=runner, args=(ln, i)) for i, ln in enumerate(lanes)]
         for t in th:
@@ -758,7 +789,7 @@ def main():
     ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
     ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
     ap.add_argument('--pipeline', type=int, default=2, help='contexts per GPU taking consecutive steps in turn (1 = no overlap of encode and decode)')
-    ap.add_argument('--e2e-pipeline', type=int, default=2, help='contexts of the end-to-end leg taking consecutive steps in turn')
+    ap.add_argument('--e2e-pipeline', type=int, default=4, help='contexts of the end-to-end leg taking consecutive steps in turn')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

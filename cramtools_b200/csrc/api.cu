@@ -73,6 +73,16 @@ void prof_end(cramgpu_ctx *ctx, cudaStream_t st) { cudaEventRecord(ctx->spans.ba
 // handed to the DMA engine directly, without staging.
 #include <thread>
 
+cudaError_t memcpy_pieces(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st)
+{
+    const size_t P = 16u << 20;
+    for (size_t o = 0; o < bytes; o += P) {
+        cudaError_t e = cudaMemcpyAsync((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(P, bytes - o), kind, st);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
 bool host_is_pinned(const void *p)
 {
     if (!p) return false;
@@ -297,8 +307,10 @@ static const char *status_text(int rc)
     }
 }
 
-// Shared by the two host entry points: stage inputs in pinned memory, one H2D copy, run the device
-// pipeline, one D2H copy of the packed results, scatter into the caller's buffers.
+// Shared by the two host entry points.  Inputs: blocks in device memory are coded where they are (16-byte aligned ones;
+// others are copied next to the staged blocks); large blocks in memory the caller pinned go to the device directly; the
+// rest is staged in pinned memory, every run of consecutive staged blocks travelling as one copy.  Results the other way
+// round; the decoder writes blocks whose destination is device memory straight to that address.
 static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uint8_t *const *in, const uint32_t *in_len,
                       const uint8_t *order, uint8_t *const *out, const uint32_t *out_cap, uint32_t *out_len,
                       int32_t *status)
@@ -309,34 +321,37 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     cudaStream_t st = ctx->stream;
 
-    // Blocks in device memory are coded where they are (16-byte aligned ones; others are copied next to the staged
-    // blocks); large blocks in memory the caller pinned go to the device directly; the rest is staged, and every run of
-    // consecutive staged blocks travels as one copy.
     const uint32_t BIG = 64u << 10;
+    enum { STAGED = 0, PINNED = 1, IN_PLACE = 2, DEV_COPY = 3 };
     MemMap mm;
-    std::vector<uint64_t> off(nblocks), addr(nblocks);
-    std::vector<uint8_t> how(nblocks, 0);                       // 0 staged, 1 direct from pinned memory, 2 in place on the device, 3 device copy
+    std::vector<uint64_t> off(nblocks), poff(nblocks), addr(nblocks);      // place in the device input buffer / in pinned staging / final device address
+    std::vector<uint8_t> how(nblocks, STAGED);
     std::vector<uint8_t> prefix(encode ? 0 : 9 * (size_t)nblocks, 0);
-    uint64_t total_in = 0, total_out_cap = 0;
+    std::vector<uint64_t> dst_addr(encode ? 0 : nblocks, 0);               // decoder: device destinations
+    uint64_t total_in = 0, total_pin = 0, total_out_cap = 0;
     for (uint32_t i = 0; i < nblocks; i++) {
         if (in_len[i] && !in[i]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in[%u] is null", i);
-        off[i] = total_in;
+        off[i] = total_in; poff[i] = total_pin;
         if (!in_len[i]) continue;
         const MemKind k = mm.kind(in[i]);
         if (k == MEM_DEVICE) {
             if (!encode) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "in[%u]: compressed blocks in device memory go through cramgpu_rans_decode_dev", i);
-            how[i] = ((uintptr_t)in[i] & 15) ? 3 : 2;
-        } else if (k == MEM_PINNED && in_len[i] >= BIG) how[i] = 1;
-        if (how[i] != 2) total_in += rup(in_len[i], 16);
+            how[i] = ((uintptr_t)in[i] & 15) ? DEV_COPY : IN_PLACE;
+        } else if (k == MEM_PINNED && in_len[i] >= BIG) how[i] = PINNED;
+        if (how[i] != IN_PLACE) total_in += rup(in_len[i], 16);
+        if (how[i] == STAGED) total_pin += rup(in_len[i], 16);
         if (!encode) {
             memcpy(&prefix[9 * (size_t)i], in[i], in_len[i] < 9 ? in_len[i] : 9);
             uint32_t ord, raw;
-            if (rans_parse_prefix(in[i], in_len[i], &ord, &raw) == CRAMGPU_OK) total_out_cap += rup(raw, 16);
+            if (rans_parse_prefix(in[i], in_len[i], &ord, &raw) == CRAMGPU_OK) {
+                if (out[i] && mm.kind(out[i]) == MEM_DEVICE) dst_addr[i] = (uint64_t)(uintptr_t)out[i];
+                else total_out_cap += rup(raw, 16);
+            }
         }
     }
     // results header: out_off (nblocks+1 u64) | out_len (u32) | status (i32)
     size_t hdr_bytes = 8 * (size_t)(nblocks + 1) + 8 * (size_t)nblocks;
-    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, total_in + 16)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, total_pin + 16)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, total_in + hdr_bytes + 64)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in;
     uint8_t *d_in = (uint8_t *)ctx->dev_in.p;
@@ -347,19 +362,20 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     {
         std::vector<CopyJob> jobs;
         for (uint32_t i = 0; i < nblocks; i++) {
-            addr[i] = how[i] == 2 ? (uint64_t)(uintptr_t)in[i] : (uint64_t)(uintptr_t)(d_in + off[i]);
-            if (in_len[i] && how[i] == 0) jobs.push_back(CopyJob{pin + off[i], in[i], in_len[i]});
+            addr[i] = how[i] == IN_PLACE ? (uint64_t)(uintptr_t)in[i] : (uint64_t)(uintptr_t)(d_in + off[i]);
+            if (in_len[i] && how[i] == STAGED) jobs.push_back(CopyJob{pin + poff[i], in[i], in_len[i]});
         }
         par_memcpy(jobs);
         uint32_t i = 0;
         while (i < nblocks) {
-            if (how[i] == 2 || !in_len[i]) { i++; continue; }
-            if (how[i] == 1) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyHostToDevice, st)); i++; continue; }
-            if (how[i] == 3) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyDeviceToDevice, st)); i++; continue; }
+            if (how[i] == IN_PLACE || !in_len[i]) { i++; continue; }
+            if (how[i] == PINNED) { CUDA_TRY(ctx, memcpy_pieces(d_in + off[i], in[i], in_len[i], cudaMemcpyHostToDevice, st)); i++; continue; }
+            if (how[i] == DEV_COPY) { CUDA_TRY(ctx, cudaMemcpyAsync(d_in + off[i], in[i], in_len[i], cudaMemcpyDeviceToDevice, st)); i++; continue; }
+            // a run of staged blocks (blocks coded in place and empty ones take no room): contiguous in both buffers
             uint32_t j = i;
-            uint64_t a = off[i], b = a;
-            while (j < nblocks && (how[j] == 0 || how[j] == 2 || !in_len[j])) { if (how[j] == 0 && in_len[j]) b = off[j] + in_len[j]; j++; }
-            if (b > a) CUDA_TRY(ctx, cudaMemcpyAsync(d_in + a, pin + a, b - a, cudaMemcpyHostToDevice, st));
+            uint64_t end = 0;
+            while (j < nblocks && (how[j] == STAGED || how[j] == IN_PLACE || !in_len[j])) { if (how[j] == STAGED && in_len[j]) end = off[j] + in_len[j]; j++; }
+            if (end > off[i]) CUDA_TRY(ctx, memcpy_pieces(d_in + off[i], pin + poff[i], end - off[i], cudaMemcpyHostToDevice, st));
             i = j;
         }
     }
@@ -378,44 +394,50 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
     } else {
         if (int rc = pool_reserve(ctx, ctx->dev_out, total_out_cap + 64)) return rc;
         if (int rc = rans_decode_device(ctx, nblocks, nullptr, addr.data(), in_len, prefix.data(), (uint8_t *)ctx->dev_out.p,
-                                        total_out_cap, d_out_off, d_out_len, d_status, st))
+                                        total_out_cap, d_out_off, d_out_len, d_status, st, dst_addr.data(), out_cap))
             return rc;
     }
-    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, hdr_bytes + 64 + total_out_cap)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, hdr_bytes + 64)) return rc;
     uint8_t *pout = (uint8_t *)ctx->pin_out;
-    uint8_t *pdata = pout + rup(hdr_bytes, 64);
     CUDA_TRY(ctx, cudaMemcpyAsync(pout, d_hdr, hdr_bytes, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    // the header moves aside: pin_out may be re-allocated for the staged results
+    std::vector<uint8_t> hdr(pout, pout + hdr_bytes);
+    const uint64_t *h_off = (const uint64_t *)hdr.data();
+    const uint32_t *h_len = (const uint32_t *)(hdr.data() + 8 * (size_t)(nblocks + 1));
+    const int32_t *h_status = (const int32_t *)(hdr.data() + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
 
-    const uint64_t *h_off = (const uint64_t *)pout;
-    const uint32_t *h_len = (const uint32_t *)(pout + 8 * (size_t)(nblocks + 1));
-    const int32_t *h_status = (const int32_t *)(pout + 8 * (size_t)(nblocks + 1) + 4 * (size_t)nblocks);
-    // results: blocks whose destination is device memory are copied there on the device; large blocks go straight into
-    // pinned caller memory; the rest through the staging buffer (one copy per run)
-    std::vector<uint8_t> direct(nblocks, 0);
+    // results: 0 = through the staging buffer, 1 = straight into pinned caller memory, 2 = device copy, 3 = already in place
     const uint8_t *d_out = (const uint8_t *)ctx->dev_out.p;
+    std::vector<uint8_t> dest(nblocks, 0);
+    std::vector<uint64_t> pso(nblocks, 0);
+    uint64_t total_ps = 0;
+    for (uint32_t i = 0; i < nblocks; i++) {
+        const bool okb = h_status[i] == CRAMGPU_OK && h_len[i] && h_len[i] <= out_cap[i] && out[i];
+        if (!okb) { dest[i] = 0; continue; }
+        if (!encode && dst_addr[i]) { dest[i] = 3; continue; }
+        const MemKind k = mm.kind(out[i]);
+        dest[i] = k == MEM_DEVICE ? 2 : (k == MEM_PINNED && h_len[i] >= BIG) ? 1 : 0;
+        if (dest[i] == 0) { pso[i] = total_ps; total_ps += rup(h_len[i], 16); }
+    }
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, total_ps + 64)) return rc;
+    uint8_t *pdata = (uint8_t *)ctx->pin_out;
     {
-        auto dest = [&](uint32_t i) -> int {                     // 0 staged, 1 pinned direct, 2 device
-            if (!(h_status[i] == CRAMGPU_OK && h_len[i] && h_len[i] <= out_cap[i]) || !out[i]) return 0;
-            const MemKind k = mm.kind(out[i]);
-            return k == MEM_DEVICE ? 2 : (k == MEM_PINNED && h_len[i] >= BIG) ? 1 : 0;
-        };
         uint32_t i = 0;
         while (i < nblocks) {
-            const int di = dest(i);
-            if (di) {
-                direct[i] = 1;
-                CUDA_TRY(ctx, cudaMemcpyAsync(out[i], d_out + h_off[i], h_len[i], di == 2 ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
+            const bool okb = h_status[i] == CRAMGPU_OK && h_len[i] && h_len[i] <= out_cap[i] && out[i];
+            if (!okb || dest[i] == 3) { i++; continue; }
+            if (dest[i]) {
+                CUDA_TRY(ctx, cudaMemcpyAsync(out[i], d_out + h_off[i], h_len[i], dest[i] == 2 ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, st));
                 i++;
                 continue;
             }
-            uint32_t j = i;
-            uint64_t a = h_off[i], b = a;
-            while (j < nblocks && !dest(j)) {
-                if (h_len[j]) b = h_off[j] + h_len[j];
-                j++;
-            }
-            if (b > a) CUDA_TRY(ctx, cudaMemcpyAsync(pdata + a, d_out + a, b - a, cudaMemcpyDeviceToHost, st));
+            // a run of staged results that are neighbours on the device (16-byte aligned back to back there and in staging)
+            uint32_t j = i + 1;
+            uint64_t end = h_off[i] + h_len[i];
+            while (j < nblocks && dest[j] == 0 && h_status[j] == CRAMGPU_OK && h_len[j] && h_len[j] <= out_cap[j] && out[j] &&
+                   h_off[j] == rup(end, 16) && pso[j] == pso[i] + (h_off[j] - h_off[i])) { end = h_off[j] + h_len[j]; j++; }
+            CUDA_TRY(ctx, memcpy_pieces(pdata + pso[i], d_out + h_off[i], end - h_off[i], cudaMemcpyDeviceToHost, st));
             i = j;
         }
         CUDA_TRY(ctx, cudaStreamSynchronize(st));
@@ -428,7 +450,7 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
         if (rc == CRAMGPU_OK) {
             if (h_len[i] > out_cap[i]) rc = CRAMGPU_ERR_OUT_TOO_SMALL;
             else {
-                if (h_len[i] && !direct[i]) jobs.push_back(CopyJob{out[i], pdata + h_off[i], h_len[i]});
+                if (h_len[i] && dest[i] == 0 && out[i]) jobs.push_back(CopyJob{out[i], pdata + pso[i], h_len[i]});
                 out_len[i] = h_len[i];
             }
         }

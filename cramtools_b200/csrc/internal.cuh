@@ -128,6 +128,10 @@ struct Carver {
     }
 };
 
+// Host <-> device copies are issued in pieces: a copy engine serves the streams' copies one whole operation after the
+// other, and a multi-gigabyte copy of one context would hold up the small copies of every other context for its duration.
+cudaError_t memcpy_pieces(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st);
+
 struct CopyJob { void *dst; const void *src; size_t n; };
 void par_memcpy(std::vector<CopyJob> &jobs);      // multi-threaded staging copies (clears the list)
 bool host_is_pinned(const void *p);               // page-locked host memory known to CUDA?
@@ -150,5 +154,6 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
 int rans_encode_pack(cramgpu_ctx *ctx, uint8_t *d_out, cudaStream_t st);
 int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
                        const uint32_t *in_len, const uint8_t *in_prefix, uint8_t *d_out, uint64_t out_cap,
-                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st);
+                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st,
+                       const uint64_t *dst_addr = nullptr, const uint32_t *dst_cap = nullptr);
 int rans_parse_prefix(const uint8_t *p, uint32_t len, uint32_t *order, uint32_t *raw);

@@ -676,7 +676,8 @@ int rans_parse_prefix(const uint8_t *p, uint32_t len, uint32_t *order, uint32_t 
 
 int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, const uint64_t *in_off,
                        const uint32_t *in_len, const uint8_t *in_prefix, uint8_t *d_out, uint64_t out_cap,
-                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st)
+                       uint64_t *d_out_off, uint32_t *d_out_len, int32_t *d_status, cudaStream_t st,
+                       const uint64_t *dst_addr, const uint32_t *dst_cap)
 {
     if (nblocks == 0) return CRAMGPU_OK;
     if (!in_off || !in_len || !in_prefix || !d_out || !d_out_off || !d_out_len || !d_status)   // d_in may be NULL: absolute addresses in in_off
@@ -701,14 +702,15 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         d.order = 0xFF;
         if (rc != CRAMGPU_OK || in_len[i] == 0) { hlen[i] = 0; continue; }
         hlen[i] = raw;
-        if (out_total + rup(raw, 16) > out_cap) {
+        const bool placed = dst_addr && dst_addr[i];            // decoded straight to a device address of the caller's
+        if (placed ? (dst_cap && raw > dst_cap[i]) : (out_total + rup(raw, 16) > out_cap)) {
             hstatus[i] = CRAMGPU_ERR_OUT_TOO_SMALL; hlen[i] = 0;
             continue;
         }
         d.order = ord;
         d.out_len = raw;
-        d.out_off = out_total;
-        out_total += rup(raw, 16);
+        if (placed) { d.out_off = dst_addr[i] - (uint64_t)(uintptr_t)d_out; hoff[i] = d.out_off; }       // d_out + out_off = the address
+        else { d.out_off = out_total; out_total += rup(raw, 16); }
         if (ord) { d.o1_index = n1++; s1.push_back(i); } else s0.push_back(i);
     }
     hoff[nblocks] = out_total;

@@ -1233,6 +1233,14 @@ __global__ void __launch_bounds__(128) k_norm(NormArgs a)
 }
 
 
+// flag[0] = 1 when any record failed (the host then looks for the first one)
+__global__ void __launch_bounds__(256) k_any_status(const int32_t *__restrict__ status, uint64_t n, int32_t *__restrict__ flag)
+{
+    bool bad = false;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) bad = bad || status[i] != 0;
+    if (__any_sync(0xFFFFFFFFu, bad) && (threadIdx.x & 31) == 0) flag[0] = 1;
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 
 #include <string.h>
@@ -1463,15 +1471,18 @@ extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads
 // others are staged through `pin`.
 struct Stager {
     MemMap mm;
-    std::vector<const void *> src; std::vector<size_t> bytes, off; std::vector<uint8_t> kind; size_t total = 0;
+    std::vector<const void *> src; std::vector<size_t> bytes, off, poff; std::vector<uint8_t> kind;
+    size_t total = 0, ptotal = 0;          // bytes of the device buffer / of the pinned staging buffer
     size_t add(const void *p, size_t b)
     {
-        const MemKind k = (p && b) ? mm.kind(p) : MEM_PAGEABLE;
-        off.push_back(total); src.push_back(p); bytes.push_back(b); kind.push_back((uint8_t)k);
+        MemKind k = (p && b) ? mm.kind(p) : MEM_PAGEABLE;
+        if (k == MEM_PINNED && b < (64u << 10)) k = MEM_PAGEABLE;          // small: cheaper to stage than to copy on its own
+        off.push_back(total); poff.push_back(ptotal); src.push_back(p); bytes.push_back(b); kind.push_back((uint8_t)k);
         if (k != MEM_DEVICE) total += rup(b ? b : 1, 256);
+        if (k == MEM_PAGEABLE && p) ptotal += rup(b ? b : 1, 256);
         return off.size() - 1;
     }
-    size_t reserve(size_t b) { off.push_back(total); src.push_back(nullptr); bytes.push_back(0); kind.push_back(MEM_PAGEABLE); total += rup(b ? b : 1, 256); return off.size() - 1; }
+    size_t reserve(size_t b) { off.push_back(total); poff.push_back(ptotal); src.push_back(nullptr); bytes.push_back(0); kind.push_back(MEM_PAGEABLE); total += rup(b ? b : 1, 256); return off.size() - 1; }
     bool on_device(size_t k) const { return kind[k] == MEM_DEVICE; }
     // where entry k is (or will be, once to_device has run) in device memory
     uint8_t *at(uint8_t *D, size_t k) const { return kind[k] == MEM_DEVICE ? (uint8_t *)src[k] : D + off[k]; }
@@ -1479,12 +1490,11 @@ struct Stager {
     {
         std::vector<CopyJob> jobs;
         for (size_t k = 0; k < src.size(); k++)
-            if (bytes[k] && src[k] && kind[k] == MEM_PAGEABLE) jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]});
-            else if (bytes[k] && src[k] && kind[k] == MEM_PINNED && bytes[k] < (64u << 10)) { jobs.push_back(CopyJob{pin + off[k], src[k], bytes[k]}); kind[k] = MEM_PAGEABLE; }
+            if (bytes[k] && src[k] && kind[k] == MEM_PAGEABLE) jobs.push_back(CopyJob{pin + poff[k], src[k], bytes[k]});
         par_memcpy(jobs);
         for (size_t k = 0; k < src.size(); k++) {
             if (!bytes[k] || !src[k] || kind[k] == MEM_DEVICE) continue;
-            CUDA_TRY(ctx, cudaMemcpyAsync(D + off[k], kind[k] == MEM_PINNED ? src[k] : (const void *)(pin + off[k]), bytes[k], cudaMemcpyHostToDevice, st));
+            CUDA_TRY(ctx, memcpy_pieces(D + off[k], kind[k] == MEM_PINNED ? src[k] : (const void *)(pin + poff[k]), bytes[k], cudaMemcpyHostToDevice, st));
         }
         return CRAMGPU_OK;
     }
@@ -1512,7 +1522,7 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     size_t i_roff = sg.add(R->read_off, 8 * (n + 1)), i_cig = sg.add(R->cigar, 4 * ncig), i_coff = sg.add(R->cigar_off, 8 * (n + 1));
     size_t i_pos = sg.add(R->pos, 4 * n), i_flag = sg.add(R->flag, 2 * n), i_mapq = sg.add(R->mapq, n);
     size_t i_rfl = R->rflags ? sg.add(R->rflags, n) : 0;
-    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.ptotal + 16)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
     if (int rc = sg.to_device(ctx, pin, D, st)) return rc;
@@ -1539,7 +1549,7 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     if (int rc = pinned_reserve(ctx, &ctx->pin_feat, &ctx->pin_feat_cap, so.total)) return rc;
     uint8_t *po = (uint8_t *)ctx->pin_feat;
     auto down = [&](size_t slot, const void *d, size_t bytes) -> cudaError_t {
-        return bytes ? cudaMemcpyAsync(po + so.off[slot], d, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+        return bytes ? memcpy_pieces(po + so.off[slot], d, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
     };
     CUDA_TRY(ctx, down(r_op, df.f_op, df.n_feat)); CUDA_TRY(ctx, down(r_pos, df.f_pos, 4 * df.n_feat));
     CUDA_TRY(ctx, down(r_val, df.f_val, 4 * df.n_feat)); CUDA_TRY(ctx, down(r_aux, df.f_aux, 4 * df.n_feat));
@@ -1549,7 +1559,7 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     CUDA_TRY(ctx, down(r_qso, df.read_qs_off, 8 * n)); CUDA_TRY(ctx, down(r_bao, df.read_ba_off, 8 * n));
     for (int k = 0; k < CRAMGPU_S_COUNT; k++)
         if (((host_series >> k) & 1) && span[2 * k + 1])
-            CUDA_TRY(ctx, cudaMemcpyAsync(po + so.off[r_str] + span[2 * k], df.streams + span[2 * k], span[2 * k + 1], cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(ctx, memcpy_pieces(po + so.off[r_str] + span[2 * k], df.streams + span[2 * k], span[2 * k + 1], cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     *out = df;
     out->f_op = po + so.off[r_op]; out->f_pos = (const int32_t *)(po + so.off[r_pos]); out->f_val = (const int32_t *)(po + so.off[r_val]);
@@ -1674,8 +1684,8 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     // results: into the caller's buffers when those are device memory, else into slots of the staging buffer
     const bool b_dev = sg.mm.kind(bases) == MEM_DEVICE, q_dev = sg.mm.kind(quals) == MEM_DEVICE;
     size_t o_bases = sg.reserve(b_dev ? 1 : nb + 16), o_quals = sg.reserve(q_dev ? 1 : nb + 16);
-    size_t o_star = sg.reserve(n), o_stat = sg.reserve(4 * n);
-    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.total)) return rc;
+    size_t o_star = sg.reserve(n), o_stat = sg.reserve(4 * n), o_flag = sg.reserve(16);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.ptotal + 16)) return rc;
     if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
     uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
     if (int rc = sg.to_device(ctx, pin, D, st)) return rc;
@@ -1689,14 +1699,18 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     dev.read_qs_off = (const uint64_t *)sg.at(D, i_qso); dev.ba = sg.at(D, i_ba); dev.read_ba_off = (const uint64_t *)sg.at(D, i_bao);
     uint8_t *d_b = b_dev ? bases : sg.at(D, o_bases), *d_q = q_dev ? quals : sg.at(D, o_quals);
     if (int rc = normalize_impl(ctx, &dev, d_b, d_q, sg.at(D, o_star), (int32_t *)sg.at(D, o_stat), st)) return rc;
-    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256))) return rc;
+    int32_t *d_flag = (int32_t *)sg.at(D, o_flag);
+    CUDA_TRY(ctx, cudaMemsetAsync(d_flag, 0, 4, st));
+    LAUNCH(ctx, st, "k_any_status", k_any_status<<<(uint32_t)std::min<uint64_t>((n + 255) / 256, 148 * 8), 256, 0, st>>>((const int32_t *)sg.at(D, o_stat), n, d_flag));
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256) + 256)) return rc;
     uint8_t *po = (uint8_t *)ctx->pin_out;
-    size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256);
+    size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256), p_f = p_t + rup(4 * n, 256);
     const bool pb = nb && !b_dev && host_is_pinned(bases), pq = nb && !q_dev && host_is_pinned(quals);
-    if (nb && !b_dev) CUDA_TRY(ctx, cudaMemcpyAsync(pb ? bases : po, d_b, nb, cudaMemcpyDeviceToHost, st));
-    if (nb && !q_dev) CUDA_TRY(ctx, cudaMemcpyAsync(pq ? quals : po + p_q, d_q, nb, cudaMemcpyDeviceToHost, st));
+    if (nb && !b_dev) CUDA_TRY(ctx, memcpy_pieces(pb ? bases : po, d_b, nb, cudaMemcpyDeviceToHost, st));
+    if (nb && !q_dev) CUDA_TRY(ctx, memcpy_pieces(pq ? quals : po + p_q, d_q, nb, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, sg.at(D, o_star), n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(po + p_t, sg.at(D, o_stat), 4 * n, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(po + p_f, d_flag, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     {
         std::vector<CopyJob> jobs;
@@ -1706,7 +1720,8 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
         jobs.push_back(CopyJob{status, po + p_t, (size_t)(4 * n)});
         par_memcpy(jobs);
     }
-    for (uint64_t r = 0; r < n; r++)
-        if (status[r]) return ctx_fail(ctx, status[r], "record %llu lies outside its reference region (ArrayIndexOutOfBoundsException in the reference)", (unsigned long long)r);
+    if (*(const int32_t *)(po + p_f))
+        for (uint64_t r = 0; r < n; r++)
+            if (status[r]) return ctx_fail(ctx, status[r], "record %llu lies outside its reference region (ArrayIndexOutOfBoundsException in the reference)", (unsigned long long)r);
     return CRAMGPU_OK;
 }
