@@ -46,6 +46,18 @@ def measured_peaks():
     return {'hbm_gbs': 6650.0, 'sm_max_mhz': 1965.0}, 'fallback'
 
 
+def ncu_traffic(kernel, n_cont):
+    """DRAM bytes of one launch of `kernel` from the committed ncu capture (profiles/r1_traffic.json), if it was taken at this size"""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'r1_traffic.json')) as f:
+            t = json.load(f).get(kernel)
+        if t and int(t['containers_per_gpu']) == int(n_cont):
+            return int(t['dram_bytes_read']) + int(t['dram_bytes_write'])
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 # ------------------------------------------------------------------------------------------- workload
 
 
@@ -495,7 +507,7 @@ def run_ours(args):
     top = max(kavg, key=kavg.get)
 
     # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
-    n_e2e = min(n_cont, args.e2e_containers)
+    n_e2e = min(n_cont, args.e2e_containers, max(128, 2 * args.e2e_containers // max(world, 2)) if world > 1 else args.e2e_containers)   # page-locked host memory is per rank
     st0 = lanes[0]
     stats = dict(raw_bytes=st0.raw_bytes, comp_bytes=st0.comp_bytes, raw_o0=st0.raw_o0, qs_bytes=st0.qs_bytes, nblk=st0.nblk)
     comp_hint = st0.c_len[:n_e2e * st0.NB].copy()
@@ -536,9 +548,11 @@ def run_ours(args):
             'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
             'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
-                         'frac': achieved / peak if achieved else None, 'traffic': None, 'peak_kind': peak_kind,
-                         'note': 'per launch of one lane; rANS is a recurrence per state: attainable rate = resident states x clock / '
-                                 'cycles per step (DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
+                         'frac': achieved / peak if achieved else None, 'traffic': ncu_traffic(top, n_cont), 'peak_kind': peak_kind,
+                         'algorithmic_bytes_per_launch': (ab / max(kcount[top], 1)) if ab else None,
+                         'note': 'per launch; traffic = dram bytes read + written by one launch in the ncu --set full capture of '
+                                 'profiles/ (null at other sizes); rANS is a recurrence per state: attainable rate = resident states x '
+                                 'clock / cycles per step (DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
             'e2e': e2e, 'clocks': clocks,
         }
         if world == 1 and not args.no_cpu:

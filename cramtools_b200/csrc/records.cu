@@ -1702,10 +1702,12 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     int32_t *d_flag = (int32_t *)sg.at(D, o_flag);
     CUDA_TRY(ctx, cudaMemsetAsync(d_flag, 0, 4, st));
     LAUNCH(ctx, st, "k_any_status", k_any_status<<<(uint32_t)std::min<uint64_t>((n + 255) / 256, 148 * 8), 256, 0, st>>>((const int32_t *)sg.at(D, o_stat), n, d_flag));
-    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, 2 * rup(nb + 16, 256) + rup(n, 256) + rup(4 * n, 256) + 256)) return rc;
-    uint8_t *po = (uint8_t *)ctx->pin_out;
-    size_t p_q = rup(nb + 16, 256), p_s = 2 * p_q, p_t = p_s + rup(n, 256), p_f = p_t + rup(4 * n, 256);
+    // staging for what does not go straight into the caller's memory
     const bool pb = nb && !b_dev && host_is_pinned(bases), pq = nb && !q_dev && host_is_pinned(quals);
+    const size_t s_b = (nb && !b_dev && !pb) ? rup(nb + 16, 256) : 0, s_q = (nb && !q_dev && !pq) ? rup(nb + 16, 256) : 0;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_out, &ctx->pin_out_cap, s_b + s_q + rup(n, 256) + rup(4 * n, 256) + 256)) return rc;
+    uint8_t *po = (uint8_t *)ctx->pin_out;
+    size_t p_q = s_b, p_s = s_b + s_q, p_t = p_s + rup(n, 256), p_f = p_t + rup(4 * n, 256);
     if (nb && !b_dev) CUDA_TRY(ctx, memcpy_pieces(pb ? bases : po, d_b, nb, cudaMemcpyDeviceToHost, st));
     if (nb && !q_dev) CUDA_TRY(ctx, memcpy_pieces(pq ? quals : po + p_q, d_q, nb, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(po + p_s, sg.at(D, o_star), n, cudaMemcpyDeviceToHost, st));
