@@ -1727,3 +1727,228 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
             if (status[r]) return ctx_fail(ctx, status[r], "record %llu lies outside its reference region (ArrayIndexOutOfBoundsException in the reference)", (unsigned long long)r);
     return CRAMGPU_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ series -> features
+// Row P, the mirror of the stream packing above: the feature part of CramRecordReader.read
+// [encoding/reader/CramRecordReader.java:59-...] for the series cramgpu_features_encode writes.  Per mapped record:
+// FN, then per feature FC (operator), FP (position delta) and the operator's value -- X: BS code, D: DL, N: RS, H: HC,
+// P: PD, i: BA byte, Q: QS byte, S: SC bytes up to the TAB (ByteArrayStopEncoding) --, then MQ, then the score array
+// (readLength bytes of QS) when the record carries one.  Unmapped: readLength bytes of BA unless the bases are
+// unknown, then the score array.  Every integer is ITF8 [ITF8.java:21-51].
+// The walk is sequential by nature (every field's position depends on the ones before it): one thread per container,
+// all containers of the call side by side.
+struct UnpackArgs {
+    uint32_t n_containers;
+    const uint64_t *cont_off, *soff, *slen, *fbase, *pbase;     // device copies of the per-container tables
+    const uint8_t *streams;
+    const uint64_t *read_off; const uint8_t *rflags;
+    uint8_t *f_op; int32_t *f_pos, *f_val, *f_aux; uint64_t *feat_off; uint8_t *payload;
+    uint64_t *read_qs_off, *read_ba_off; uint8_t *mapq; int32_t *status;
+};
+
+__global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= a.n_containers) return;
+    uint64_t p[CRAMGPU_S_COUNT], e[CRAMGPU_S_COUNT];
+#pragma unroll
+    for (int k = 0; k < CRAMGPU_S_COUNT; k++) { p[k] = a.soff[(size_t)c * CRAMGPU_S_COUNT + k]; e[k] = p[k] + a.slen[(size_t)c * CRAMGPU_S_COUNT + k]; }
+    const uint8_t *S = a.streams;
+    int bad = 0;
+    auto byte = [&](int k) -> uint32_t { if (p[k] >= e[k]) { bad = 1; return 0; } return S[p[k]++]; };
+    auto itf8 = [&](int k) -> int32_t {                               // ITF8.readUnsignedITF8 [ITF8.java:21-51]
+        const uint32_t b1 = byte(k);
+        if (b1 < 0x80) return (int32_t)b1;
+        if (b1 < 0xC0) return (int32_t)(((b1 & 0x7F) << 8) | byte(k));
+        if (b1 < 0xE0) { const uint32_t b2 = byte(k); return (int32_t)(((b1 & 0x3F) << 16) | (b2 << 8) | byte(k)); }
+        if (b1 < 0xF0) { const uint32_t b2 = byte(k), b3 = byte(k); return (int32_t)(((b1 & 0x1F) << 24) | (b2 << 16) | (b3 << 8) | byte(k)); }
+        const uint32_t b2 = byte(k), b3 = byte(k), b4 = byte(k);
+        return (int32_t)(((b1 & 0x0F) << 28) | (b2 << 20) | (b3 << 12) | (b4 << 4) | (byte(k) & 0x0F));
+    };
+    uint64_t nf_total = 0, pay = a.pbase[c];
+    const uint64_t fb = a.fbase[c], f_cap = a.slen[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_FC];
+    for (uint64_t r = a.cont_off[c]; r < a.cont_off[c + 1]; r++) {
+        const uint64_t rlen = a.read_off[r + 1] - a.read_off[r];
+        const uint8_t fl = a.rflags[r];
+        a.feat_off[r] = fb + nf_total;
+        uint64_t qo = ~0ull, bo = ~0ull;
+        uint32_t mq = 0;
+        if (!(fl & CRAMGPU_NF_UNMAPPED)) {
+            const uint32_t nf = (uint32_t)itf8(CRAMGPU_S_FN);
+            int32_t prev = 0;
+            for (uint32_t i = 0; i < nf && !bad; i++) {
+                if (nf_total >= f_cap) { bad = 1; break; }            // more features than operator bytes
+                const uint8_t op = (uint8_t)byte(CRAMGPU_S_FC);
+                prev += itf8(CRAMGPU_S_FP);
+                int32_t val = 0, aux = 0;
+                switch (op) {
+                case 'X': val = (int32_t)byte(CRAMGPU_S_BS); break;
+                case 'D': val = itf8(CRAMGPU_S_DL); break;
+                case 'N': val = itf8(CRAMGPU_S_RS); break;
+                case 'H': val = itf8(CRAMGPU_S_HC); break;
+                case 'P': val = itf8(CRAMGPU_S_PD); break;
+                case 'i': val = (int32_t)byte(CRAMGPU_S_BA); break;
+                case 'Q': val = (int32_t)byte(CRAMGPU_S_QS); break;
+                case 'S': {
+                    val = (int32_t)pay;
+                    for (;;) {
+                        if (p[CRAMGPU_S_SC] >= e[CRAMGPU_S_SC]) { bad = 1; break; }
+                        const uint8_t b = S[p[CRAMGPU_S_SC]++];
+                        if (b == '\t') break;
+                        a.payload[pay++] = b; aux++;
+                    }
+                    break;
+                }
+                default: bad = 2; break;                              // an operator this library does not write (B, I, b, q)
+                }
+                const uint64_t fi = fb + nf_total;
+                a.f_op[fi] = op; a.f_pos[fi] = prev; a.f_val[fi] = val; a.f_aux[fi] = aux;
+                nf_total++;
+            }
+            mq = (uint32_t)itf8(CRAMGPU_S_MQ);
+        } else if (!(fl & CRAMGPU_NF_UNKNOWN_BASES)) {
+            bo = p[CRAMGPU_S_BA]; p[CRAMGPU_S_BA] += rlen;
+            if (p[CRAMGPU_S_BA] > e[CRAMGPU_S_BA]) bad = 1;
+        }
+        if (fl & CRAMGPU_NF_FORCE_QS) {
+            qo = p[CRAMGPU_S_QS]; p[CRAMGPU_S_QS] += rlen;
+            if (p[CRAMGPU_S_QS] > e[CRAMGPU_S_QS]) bad = 1;
+        }
+        a.read_qs_off[r] = qo; a.read_ba_off[r] = bo; a.mapq[r] = (uint8_t)mq;
+        if (bad) break;
+    }
+    // the operator bytes a corrupt container does not account for still get defined feature slots
+    for (uint64_t i = nf_total; i < f_cap; i++) { a.f_op[fb + i] = 0; a.f_pos[fb + i] = 0; a.f_val[fb + i] = 0; a.f_aux[fb + i] = 0; }
+    if (bad) for (uint64_t r = a.cont_off[c]; r < a.cont_off[c + 1]; r++) if (a.feat_off[r] > fb + nf_total || a.feat_off[r] < fb) a.feat_off[r] = fb + nf_total;
+    a.status[c] = bad == 2 ? CRAMGPU_ERR_UNSUPPORTED : bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
+}
+
+static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t **d_mapq,
+                                int32_t *h_status, cudaStream_t st)
+{
+    if (!in || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    memset(out, 0, sizeof *out);
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!in->cont_off || !in->stream_off || !in->stream_len || !in->streams || !in->read_off || !in->rflags)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (in->cont_off[0] != 0 || in->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
+    // one operator byte per feature: the FC lengths give every container's place in the feature arrays up front
+    std::vector<uint64_t> fbase(nc), pbase(nc);
+    uint64_t nfeat = 0, paylen = 0;
+    for (uint32_t c = 0; c < nc; c++) {
+        fbase[c] = nfeat; nfeat += in->stream_len[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_FC];
+        pbase[c] = paylen; paylen += in->stream_len[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_SC];   // soft-clip bytes incl. their TABs: an upper bound
+        for (int k = 0; k < CRAMGPU_S_COUNT; k++)
+            if (in->stream_off[(size_t)c * CRAMGPU_S_COUNT + k] + in->stream_len[(size_t)c * CRAMGPU_S_COUNT + k] > in->streams_len)
+                return ctx_fail(ctx, CRAMGPU_ERR_ARG, "series %d of container %u lies outside streams", k, c);
+    }
+    const size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
+    Carver cv;
+    size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_soff = cv.take(tab), o_slen = cv.take(tab), o_fb = cv.take(8 * (size_t)nc), o_pb = cv.take(8 * (size_t)nc);
+    size_t o_stat = cv.take(4 * (size_t)nc);
+    if (int rc = pool_reserve(ctx, ctx->rec_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->rec_scratch.p;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, 2 * tab + 8 * (size_t)(3 * nc + 1) + 512)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev));
+    Uploader U{ctx, st};
+    CUDA_TRY(ctx, U.up(in->cont_off, 8 * (size_t)(nc + 1), S + o_cont));
+    CUDA_TRY(ctx, U.up(in->stream_off, tab, S + o_soff));
+    CUDA_TRY(ctx, U.up(in->stream_len, tab, S + o_slen));
+    CUDA_TRY(ctx, U.up(fbase.data(), 8 * (size_t)nc, S + o_fb));
+    CUDA_TRY(ctx, U.up(pbase.data(), 8 * (size_t)nc, S + o_pb));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev, st));
+    Carver co;
+    size_t q_op = co.take(nfeat + 16), q_pos = co.take(4 * nfeat + 16), q_val = co.take(4 * nfeat + 16), q_aux = co.take(4 * nfeat + 16);
+    size_t q_foff = co.take(8 * (size_t)(n + 1)), q_pay = co.take(paylen + 16);
+    size_t q_qso = co.take(8 * (size_t)n), q_bao = co.take(8 * (size_t)n), q_mq = co.take(n);
+    if (int rc = pool_reserve(ctx, ctx->rec_out, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->rec_out.p;
+    UnpackArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_containers = nc;
+    a.cont_off = (const uint64_t *)(S + o_cont); a.soff = (const uint64_t *)(S + o_soff); a.slen = (const uint64_t *)(S + o_slen);
+    a.fbase = (const uint64_t *)(S + o_fb); a.pbase = (const uint64_t *)(S + o_pb);
+    a.streams = in->streams; a.read_off = in->read_off; a.rflags = in->rflags;
+    a.f_op = O + q_op; a.f_pos = (int32_t *)(O + q_pos); a.f_val = (int32_t *)(O + q_val); a.f_aux = (int32_t *)(O + q_aux);
+    a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
+    a.mapq = O + q_mq; a.status = (int32_t *)(S + o_stat);
+    LAUNCH(ctx, st, "k_unpack", k_unpack<<<(nc + 31) / 32, 32, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    // feat_off[n] = all features; per-container status back to the host
+    if (int rc = pinned_reserve(ctx, &ctx->pin_rec, &ctx->pin_rec_cap, 4 * (size_t)nc + 64)) return rc;
+    uint64_t *pr = (uint64_t *)ctx->pin_rec;
+    pr[0] = nfeat;
+    CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, pr, 8, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync((uint8_t *)pr + 16, a.status, 4 * (size_t)nc, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const int32_t *hs = (const int32_t *)((uint8_t *)pr + 16);
+    int first = CRAMGPU_OK;
+    for (uint32_t c = 0; c < nc; c++) {
+        if (h_status) h_status[c] = hs[c];
+        if (hs[c] && !first) {
+            first = hs[c];
+            ctx_fail(ctx, first, first == CRAMGPU_ERR_UNSUPPORTED ? "container %u: read feature operator outside {X,D,N,H,P,i,Q,S}" : "container %u: series end before the records do", c);
+        }
+    }
+    out->n_feat = nfeat; out->f_op = a.f_op; out->f_pos = a.f_pos; out->f_val = a.f_val; out->f_aux = a.f_aux;
+    out->feat_off = a.feat_off; out->payload = a.payload; out->payload_len = paylen;
+    out->streams = in->streams; out->streams_len = in->streams_len;
+    out->read_qs_off = a.read_qs_off; out->read_ba_off = a.read_ba_off;
+    if (d_mapq) *d_mapq = a.mapq;
+    return first;
+}
+
+extern "C" int cramgpu_features_unpack_dev(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t **d_mapq,
+                                           int32_t *status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return features_unpack_impl(ctx, in, out, d_mapq, status, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+extern "C" int cramgpu_features_unpack(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t *mapq,
+                                       int32_t *status)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    memset(out, 0, sizeof *out);
+    const uint64_t n = in->n_reads;
+    if (n == 0 || in->n_containers == 0) return CRAMGPU_OK;
+    if (!in->read_off || !in->rflags || !in->streams) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    Stager sg;
+    size_t i_str = sg.add(in->streams, in->streams_len), i_roff = sg.add(in->read_off, 8 * (n + 1)), i_rfl = sg.add(in->rflags, n);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_in, &ctx->pin_in_cap, sg.ptotal + 16)) return rc;
+    if (int rc = pool_reserve(ctx, ctx->dev_in, sg.total)) return rc;
+    uint8_t *pin = (uint8_t *)ctx->pin_in, *D = (uint8_t *)ctx->dev_in.p;
+    if (int rc = sg.to_device(ctx, pin, D, st)) return rc;
+    cramgpu_series dev = *in;
+    dev.streams = sg.at(D, i_str); dev.read_off = (const uint64_t *)sg.at(D, i_roff); dev.rflags = sg.at(D, i_rfl);
+    cramgpu_features df;
+    uint8_t *d_mq = nullptr;
+    const int rc0 = features_unpack_impl(ctx, &dev, &df, &d_mq, status, st);
+    if (rc0 != CRAMGPU_OK && rc0 != CRAMGPU_ERR_CORRUPT && rc0 != CRAMGPU_ERR_UNSUPPORTED) return rc0;
+    Stager so;
+    size_t r_op = so.reserve(df.n_feat), r_pos = so.reserve(4 * df.n_feat), r_val = so.reserve(4 * df.n_feat), r_aux = so.reserve(4 * df.n_feat);
+    size_t r_foff = so.reserve(8 * (n + 1)), r_pay = so.reserve(df.payload_len), r_qso = so.reserve(8 * n), r_bao = so.reserve(8 * n), r_mq = so.reserve(n);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_feat, &ctx->pin_feat_cap, so.total)) return rc;
+    uint8_t *po = (uint8_t *)ctx->pin_feat;
+    auto down = [&](size_t slot, const void *d, size_t bytes) -> cudaError_t {
+        return bytes ? memcpy_pieces(po + so.off[slot], d, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
+    };
+    CUDA_TRY(ctx, down(r_op, df.f_op, df.n_feat)); CUDA_TRY(ctx, down(r_pos, df.f_pos, 4 * df.n_feat));
+    CUDA_TRY(ctx, down(r_val, df.f_val, 4 * df.n_feat)); CUDA_TRY(ctx, down(r_aux, df.f_aux, 4 * df.n_feat));
+    CUDA_TRY(ctx, down(r_foff, df.feat_off, 8 * (n + 1))); CUDA_TRY(ctx, down(r_pay, df.payload, df.payload_len));
+    CUDA_TRY(ctx, down(r_qso, df.read_qs_off, 8 * n)); CUDA_TRY(ctx, down(r_bao, df.read_ba_off, 8 * n)); CUDA_TRY(ctx, down(r_mq, d_mq, n));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    *out = df;
+    out->f_op = po + so.off[r_op]; out->f_pos = (const int32_t *)(po + so.off[r_pos]); out->f_val = (const int32_t *)(po + so.off[r_val]);
+    out->f_aux = (const int32_t *)(po + so.off[r_aux]); out->feat_off = (const uint64_t *)(po + so.off[r_foff]); out->payload = po + so.off[r_pay];
+    out->read_qs_off = (const uint64_t *)(po + so.off[r_qso]); out->read_ba_off = (const uint64_t *)(po + so.off[r_bao]);
+    out->streams = in->streams;
+    if (mapq) memcpy(mapq, po + so.off[r_mq], n);
+    return rc0;
+}

@@ -48,7 +48,16 @@ class NormIn(C.Structure):
                 ('ba', C.c_void_p), ('read_ba_off', C.c_void_p)]
 
 
+class Series(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('streams', C.c_void_p),
+                ('streams_len', C.c_uint64), ('stream_off', u64p), ('stream_len', u64p), ('read_off', C.c_void_p),
+                ('rflags', C.c_void_p)]
+
+
 _lib.SIGNATURES.update({
+    'cramgpu_features_unpack': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), u8p, i32p]),
+    'cramgpu_features_unpack_dev': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), C.POINTER(C.c_void_p), i32p,
+                                              C.c_void_p]),
     'cramgpu_parse_lossy_spec': (C.c_int, [C.c_char_p, C.POINTER(QsPolicy), C.c_int]),
     'cramgpu_features_encode': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features)]),
     'cramgpu_features_encode_dev': (C.c_int, [C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, C.POINTER(Features),
@@ -190,6 +199,43 @@ def features_encode_resident(rd, ref, spec=None, host_series=None, cont_off=None
     F, D = Features(), Features()
     ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(R), pol, npol, mask, C.byref(F), C.byref(D)))
     return EncodedFeatures(F, n, nc), D
+
+
+class UnpackedFeatures(object):
+    """host copy of a cramgpu_features_unpack result"""
+
+    def __init__(self, f, n_reads, streams, mapq, status):
+        nf = int(f.n_feat)
+        self.n_feat = nf
+        self.f_op = _view(f.f_op, nf, np.uint8); self.f_pos = _view(f.f_pos, nf, np.int32)
+        self.f_val = _view(f.f_val, nf, np.int32); self.f_aux = _view(f.f_aux, nf, np.int32)
+        self.feat_off = _view(f.feat_off, n_reads + 1, np.uint64)
+        self.payload = _view(f.payload, f.payload_len, np.uint8)
+        self.read_qs_off = _view(f.read_qs_off, n_reads, np.uint64)
+        self.read_ba_off = _view(f.read_ba_off, n_reads, np.uint64)
+        self.streams, self.mapq, self.status = streams, mapq, status
+
+
+def features_unpack(streams, stream_off, stream_len, read_off, rflags, cont_off=None, ctx=None, check=True):
+    """CramRecordReader.read's feature part through cramgpu_features_unpack (host buffers): decoded series -> feature arrays.
+    stream_off / stream_len: [n_containers][12]; rflags: CRAMGPU_NF_* per read.  -> UnpackedFeatures"""
+    ctx = ctx or _lib.default_context()
+    n = len(rflags)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    streams = _arr(streams, np.uint8)
+    so = _arr(np.asarray(stream_off, np.uint64).reshape(nc, 12), np.uint64); sl = _arr(np.asarray(stream_len, np.uint64).reshape(nc, 12), np.uint64)
+    ro = _arr(read_off, np.uint64); rf = _arr(rflags, np.uint8)
+    I = Series()
+    I.n_reads = n; I.n_containers = nc
+    I.cont_off = cont_off.ctypes.data_as(u64p); I.streams = _vp(streams); I.streams_len = streams.size
+    I.stream_off = so.ctypes.data_as(u64p); I.stream_len = sl.ctypes.data_as(u64p); I.read_off = _vp(ro); I.rflags = _vp(rf)
+    F = Features()
+    mapq = np.zeros(max(n, 1), np.uint8); status = np.zeros(max(nc, 1), np.int32)
+    rc = ctx.lib.cramgpu_features_unpack(ctx.handle, C.byref(I), C.byref(F), mapq.ctypes.data_as(u8p), status.ctypes.data_as(i32p))
+    if rc != _lib.OK and (check or rc not in (_lib.ERR_CORRUPT, _lib.ERR_UNSUPPORTED)):
+        ctx.check(rc)
+    return UnpackedFeatures(F, n, streams, mapq[:n], status[:nc])
 
 
 def normalize_decode(pos, read_off, rflags, enc, window, window_start0, matrix, cont_off=None, win_off=None, win_len=None,

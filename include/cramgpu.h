@@ -327,6 +327,42 @@ int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads *reads, co
                                 int n_policies, cramgpu_features *out, uint64_t *h_stream_off, uint64_t *h_stream_len,
                                 void *stream);
 
+/*
+ * Series -> read features: the feature part of CramRecordReader.read
+ * (htsjdk/samtools/cram/encoding/reader/CramRecordReader.java:59-..., mirror of Writer.write [Writer.java:180-258])
+ * for the series listed above, so that decoded series can go to cramgpu_normalize_decode without a trip through
+ * CramCompressionRecord objects.  Per mapped record: FN; per feature FC, FP (delta) and the
+ * operator's value (X: BS, D: DL, N: RS, H: HC, P: PD, i: BA, Q: QS, S: SC bytes up to the TAB); MQ; then the score
+ * array in QS when the record carries one.  Unmapped: readLength bytes of BA unless the bases are unknown, then the
+ * score array.  What the host still parses (BF/CF/RL/AP...) arrives as read_off (read lengths) and rflags.
+ */
+typedef struct cramgpu_series {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    const uint8_t *streams;       /* decoded series bytes of all containers */
+    uint64_t streams_len;
+    const uint64_t *stream_off;   /* HOST [n_containers][CRAMGPU_S_COUNT] */
+    const uint64_t *stream_len;   /* HOST [n_containers][CRAMGPU_S_COUNT] */
+    const uint64_t *read_off;     /* [n_reads+1] cumulative readLength */
+    const uint8_t *rflags;        /* [n_reads] CRAMGPU_NF_* */
+} cramgpu_series;
+
+/*
+ * Result: feature arrays as cramgpu_features_encode returns them (f_aux of an X feature is 0: the bases are not in the
+ * series), payload = soft-clip bytes, read_qs_off / read_ba_off = offsets into `streams`, plus the mapping qualities.
+ * Not set: force_qs, matrix, stream_off / stream_len.  status[c] (HOST, optional) = CRAMGPU_ERR_CORRUPT when a series
+ * of container c ends before its records do, CRAMGPU_ERR_UNSUPPORTED for an operator outside the list; the call
+ * returns the first such status.  Host variant: streams / read_off / rflags may be host or device memory, results are
+ * host memory owned by the context (mapq: caller's array, optional).  Device variant: those three are device
+ * pointers, results are device memory owned by the context (*d_mapq receives the mapq array), valid until the next
+ * record call on ctx.
+ */
+int cramgpu_features_unpack(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t *mapq,
+                            int32_t *status);
+int cramgpu_features_unpack_dev(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t **d_mapq,
+                                int32_t *status, void *stream);
+
 /* input of the decode-side normaliser: records as CramRecordReader leaves them, structure of arrays */
 typedef struct cramgpu_norm_in {
     uint64_t n_reads;

@@ -207,3 +207,80 @@ def write_streams(rd, ex, force, scores):
                                    _p(np.ascontiguousarray(rd['pos'], np.int32), i32p), _c.byref(rf),
                                    _p(np.ascontiguousarray(force, np.uint8), u8p), _p(sc, u8p), ptrs, _p(lens, i64p))
     return {nm: bufs[i][:int(lens[i])].tobytes() for i, nm in enumerate(STREAMS)}
+
+
+def read_streams(st, read_len, rflags):
+    """row P: the feature part of CramRecordReader.read [encoding/reader/CramRecordReader.java:59-...], the mirror of
+    Writer.write [Writer.java:180-258], restated for the series of write_streams (pure Python: small cases only).
+    st: dict series name -> bytes; read_len[r]; rflags[r]: bit0 force-preserved score array, bit1 unmapped, bit2 unknown
+    bases.  -> (rows, mapq, qs_off, ba_off): rows[r] = [[op, pos, value], ...] with value = int, or bytes for 'S';
+    qs_off / ba_off = offset of the record's score array in QS / of an unmapped record's bases in BA (None = none).
+    Parity: unpinned by the jar itself (its reader needs the whole codec factory); pinned indirectly -- reading back the
+    series write_streams makes from the jar's feature lists must give those lists (tests/test_oracle_records.py)."""
+    cur = {k: 0 for k in st}
+
+    def byte(name):
+        v = st[name][cur[name]]
+        cur[name] += 1
+        return v
+
+    def itf8(name):                                  # ITF8.readUnsignedITF8 [ITF8.java:21-51]
+        b1 = byte(name)
+        if b1 < 0x80:
+            v = b1
+        elif b1 < 0xC0:
+            v = ((b1 & 0x7F) << 8) | byte(name)
+        elif b1 < 0xE0:
+            v = ((b1 & 0x3F) << 16) | (byte(name) << 8)
+            v |= byte(name)
+        elif b1 < 0xF0:
+            v = ((b1 & 0x1F) << 24) | (byte(name) << 16)
+            v |= byte(name) << 8
+            v |= byte(name)
+        else:
+            v = ((b1 & 0x0F) << 28) | (byte(name) << 20)
+            v |= byte(name) << 12
+            v |= byte(name) << 4
+            v |= byte(name) & 0x0F
+        return v - (1 << 32) if v >= (1 << 31) else v
+    rows, mapq, qs_off, ba_off = [], [], [], []
+    for r in range(len(rflags)):
+        fl, rl = int(rflags[r]), int(read_len[r])
+        row, mq, qo, bo = [], 0, None, None
+        if not fl & 2:
+            nf = itf8('FN')
+            prev = 0
+            for _ in range(nf):
+                op = chr(byte('FC'))
+                prev += itf8('FP')
+                if op == 'X':
+                    row.append([op, prev, byte('BS')])
+                elif op == 'D':
+                    row.append([op, prev, itf8('DL')])
+                elif op == 'N':
+                    row.append([op, prev, itf8('RS')])
+                elif op == 'H':
+                    row.append([op, prev, itf8('HC')])
+                elif op == 'P':
+                    row.append([op, prev, itf8('PD')])
+                elif op == 'i':
+                    row.append([op, prev, byte('BA')])
+                elif op == 'Q':
+                    row.append([op, prev, byte('QS')])
+                elif op == 'S':
+                    e = st['SC'].index(b'\t', cur['SC'])              # ByteArrayStopEncoding: bytes up to the stop byte
+                    row.append([op, prev, bytes(st['SC'][cur['SC']:e])])
+                    cur['SC'] = e + 1
+                else:
+                    raise ValueError('read feature operator %r' % op)
+            mq = itf8('MQ')
+        elif not fl & 4:
+            bo = cur['BA']
+            cur['BA'] += rl
+        if fl & 1:
+            qo = cur['QS']
+            cur['QS'] += rl
+        rows.append(row); mapq.append(mq); qs_off.append(qo); ba_off.append(bo)
+    for k in st:
+        assert cur[k] == len(st[k]), (k, cur[k], len(st[k]))      # every byte of every series accounted for
+    return rows, mapq, qs_off, ba_off

@@ -124,68 +124,30 @@ def test_restore_quals_matches_jar(G):
 
 
 def test_streams_consistent_with_features(G):
-    """row W is restated from the disassembly only: check its structure -- FN counts, FP deltas and payloads must
-    reproduce the jar's feature lists when read back the way CramRecordReader would."""
+    """rows W and P are restated from the disassembly only: check them against each other and against the jar -- the
+    series write_streams makes from the jar's feature lists, read back by read_streams the way CramRecordReader would,
+    must reproduce those lists (FN counts, FP deltas, operator values), every mapping quality, and use up every byte."""
     g, ref, rd = G
     n = len(rd['pos'])
     ex = orec.extract(rd, ref)
+    rl = np.diff(np.asarray(rd['read_off'], np.int64))
     for spec in ('lossless', 'N40-D8', '*8'):
         force, scores = orec.quality(rd, ref, spec)
         st = orec.write_streams(rd, ex, force, scores)
+        rfl = (np.asarray(force) & 1).astype(np.uint8)
+        rfl[(np.asarray(rd['flag']) & 4) != 0] |= 2
+        rows, mapq, qs_off, ba_off = orec.read_streams(st, rl, rfl)
         want = g['features_coded'] if spec == 'lossless' else None
-        # walk the streams
-        cur = {k: 0 for k in st}
-
-        def itf8(name):
-            b = st[name]; p = cur[name]; v = b[p]
-            if v < 0x80:
-                cur[name] = p + 1; return v
-            if v < 0xC0:
-                cur[name] = p + 2; return ((v & 0x7F) << 8) | b[p + 1]
-            if v < 0xE0:
-                cur[name] = p + 3; return ((v & 0x3F) << 16) | (b[p + 1] << 8) | b[p + 2]
-            raise AssertionError('long ITF8 not expected here')
-
-        def byte(name):
-            v = st[name][cur[name]]; cur[name] += 1; return v
         for i in range(n):
             if rd['flag'][i] & 4:
-                rl = int(rd['read_off'][i + 1] - rd['read_off'][i])
-                cur['BA'] += rl                      # unmapped: bases go to BA one by one [Writer.java:254-258]
-                if force[i] & 1:
-                    cur['QS'] += rl
+                assert rows[i] == [] and ba_off[i] is not None
                 continue
-            nf = itf8('FN')
-            prev = 0
-            row = []
-            for _ in range(nf):
-                op = chr(byte('FC')); prev += itf8('FP')
-                if op == 'X':
-                    row.append(['X', prev, byte('BS')])
-                elif op == 'D':
-                    row.append(['D', prev, itf8('DL')])
-                elif op == 'N':
-                    row.append(['N', prev, itf8('RS')])
-                elif op == 'H':
-                    row.append(['H', prev, itf8('HC')])
-                elif op == 'P':
-                    row.append(['P', prev, itf8('PD')])
-                elif op == 'i':
-                    row.append(['i', prev, byte('BA')])
-                elif op == 'Q':
-                    row.append(['Q', prev, byte('QS')])
-                elif op == 'S':
-                    e = st['SC'].index(b'\t', cur['SC'])
-                    row.append(['S', prev, base64.b64encode(st['SC'][cur['SC']:e]).decode()]); cur['SC'] = e + 1
-            assert itf8('MQ') == rd['mapq'][i]
-            if force[i] & 1:
-                rl = int(rd['read_off'][i + 1] - rd['read_off'][i])
-                cur['QS'] += rl
+            assert mapq[i] == rd['mapq'][i]
+            row = [[f[0], f[1], base64.b64encode(f[2]).decode()] if f[0] == 'S' else f for f in rows[i]]
             if want is not None:
                 exp = [[f[0], f[1], f[4]] if f[0] == 'X' else f for f in (want[i] or [])]
                 assert row == exp, (i, rd['names'][i])
             elif spec in g['lossy']:
                 exp = [[f[0], f[1]] for f in (g['lossy'][spec][i].get('features') or [])]
                 assert [[f[0], f[1]] for f in row] == exp, (spec, i)
-        for k in st:
-            assert cur[k] == len(st[k]), (spec, k)      # every byte of every stream accounted for
+            assert (qs_off[i] is not None) == bool(force[i] & 1)

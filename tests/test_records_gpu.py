@@ -280,3 +280,79 @@ def test_resident_series_and_device_pointers(R, gpu_ctx):
                                                        star.ctypes.data_as(u8p), st.ctypes.data_as(i32p)))
     assert (st == 0).all() and (star == 0).all()
     assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
+
+
+def _nf_flags(enc, rd):
+    rfl = (enc.force_qs & 1).astype(np.uint8)
+    rfl[(rd['flag'] & 4) != 0] |= 2
+    if rd.get('rflags') is not None:
+        rfl[(np.asarray(rd['rflags']) & 2) != 0] |= 4          # NO_BASES -> unknown bases
+    return rfl
+
+
+@pytest.mark.parametrize('spec', [None, '*8', 'N40-D8', 'D8-I40-m30'])
+def test_unpack_parity_with_oracle(R, gpu_ctx, spec):
+    """row P: series -> features on the GPU against the Python restatement of CramRecordReader.read, per container"""
+    from oracle import records as orec
+    ref, rd, cont_off = _sim(5000, 4, 19, unmapped_tail=120)
+    n, nc = len(rd['pos']), 4
+    enc = R.features_encode(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+    rfl = _nf_flags(enc, rd)
+    up = R.features_unpack(enc.streams, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx)
+    assert (up.status == 0).all()
+    rl = np.diff(np.asarray(rd['read_off'], np.int64))
+    for c in range(nc):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        st = {name: enc.series(c, name) for name in R.SERIES}
+        rows, mapq, qs_off, ba_off = orec.read_streams(st, rl[a:b], rfl[a:b])
+        for i in range(a, b):
+            f0, f1 = int(up.feat_off[i]), int(up.feat_off[i + 1])
+            got = []
+            for f in range(f0, f1):
+                op = chr(up.f_op[f])
+                if op == 'S':
+                    o, ln = int(up.f_val[f]), int(up.f_aux[f])
+                    got.append([op, int(up.f_pos[f]), up.payload[o:o + ln].tobytes()])
+                else:
+                    got.append([op, int(up.f_pos[f]), int(up.f_val[f])])
+            assert got == rows[i - a], (spec, i)
+            assert up.mapq[i] == mapq[i - a]
+            qo, bo = qs_off[i - a], ba_off[i - a]
+            assert int(up.read_qs_off[i]) == (0xFFFFFFFFFFFFFFFF if qo is None else int(enc.stream_off[c, R.SERIES.index('QS')]) + qo)
+            assert int(up.read_ba_off[i]) == (0xFFFFFFFFFFFFFFFF if bo is None else int(enc.stream_off[c, R.SERIES.index('BA')]) + bo)
+    assert int(up.feat_off[n]) == up.n_feat == enc.n_feat
+
+
+def test_unpack_then_normalize_round_trip(R, gpu_ctx):
+    """decode side without the encoder's feature arrays: series -> features (row P) -> bases and qualities (rows N1, N2)"""
+    ref, rd, cont_off = _sim(20000, 6, 29, unmapped_tail=250)
+    n = len(rd['pos'])
+    enc = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    rfl = _nf_flags(enc, rd)
+    up = R.features_unpack(enc.streams, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx)
+    assert (up.mapq[(rd['flag'] & 4) == 0] == rd['mapq'][(rd['flag'] & 4) == 0]).all()
+    nc = 6
+    ws0 = np.zeros(nc, np.int64)
+    bases, quals, star, status = R.normalize_decode(rd['pos'], rd['read_off'], rfl, up, ref, ws0, enc.matrix, cont_off=cont_off,
+                                                    qs=enc.streams, read_qs_off=up.read_qs_off, ba=enc.streams,
+                                                    read_ba_off=up.read_ba_off, ctx=gpu_ctx)
+    assert (status == 0).all() and (star == 0).all()
+    assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
+
+
+def test_unpack_corrupt_and_foreign_series(R, gpu_ctx):
+    """a series that ends early -> CRAMGPU_ERR_CORRUPT for that container only; an operator the library does not write ->
+    CRAMGPU_ERR_UNSUPPORTED"""
+    ref, rd, cont_off = _sim(3000, 3, 31)
+    enc = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    rfl = _nf_flags(enc, rd)
+    sl = enc.stream_len.copy()
+    sl[1, R.SERIES.index('FP')] -= 1                     # container 1 loses the last byte of its FP series
+    up = R.features_unpack(enc.streams, enc.stream_off, sl, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx, check=False)
+    assert list(up.status) == [0, _lib.ERR_CORRUPT, 0]
+    st = enc.streams.copy()
+    o = int(enc.stream_off[2, R.SERIES.index('FC')])
+    assert enc.stream_len[2, R.SERIES.index('FC')] > 0
+    st[o] = ord('B')                                     # ReadBase: needs the BA+QS pair this library never writes
+    up = R.features_unpack(st, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx, check=False)
+    assert list(up.status) == [0, 0, _lib.ERR_UNSUPPORTED]
