@@ -254,13 +254,14 @@ class Lane(object):
     the step of all its lanes, each driven by its own host thread, so that one lane's latency-bound coder kernels
     (a few warps per SM) overlap the other lanes' record kernels and copies."""
 
-    def __init__(self, lane_id, n_cont, ref, rd, extra, nu, dev, rank, world, group):
+    def __init__(self, lane_id, n_cont, ref, rd, extra, nu, dev, rank, world, group, use_unpack=True):
         import torch
         import cramtools_b200
         from cramtools_b200 import device as dv, records as rec
         from cramtools_b200._lib import u64p
         self.torch, self.rec, self.dv = torch, rec, dv
         self.n_cont, self.rank, self.world, self.group, self.dev = n_cont, rank, world, group, dev
+        self.use_unpack = use_unpack
         self.stream = torch.cuda.Stream(device=dev)
         self.ctx = cramtools_b200.Context(dev.index)
         vp = C.c_void_p
@@ -387,22 +388,50 @@ class Lane(object):
         N.pos = vp(self.t_pos.data_ptr()); N.read_off = vp(self.t_roff.data_ptr()); N.rflags = vp(self.t_rfl.data_ptr())
         N.qs = vp(self.dec_out.data_ptr()); N.read_qs_off = vp(self.t_rq.data_ptr()); N.ba = vp(self.dec_out.data_ptr())
         N.read_ba_off = vp(self.t_rba.data_ptr())
+        if self.use_unpack:
+            # series table of the decode side: absolute device addresses (QS / BA inside dec_out, the others inside F.streams)
+            sa = (np.uint64(self.F.streams) + self.soff).astype(np.uint64)
+            sa[:, self.KQS] = np.uint64(self.dec_out.data_ptr()) + d_off[np.arange(n_cont) * NB + 0]
+            sa[:, self.KBA] = np.uint64(self.dec_out.data_ptr()) + d_off[np.arange(n_cont) * NB + 1]
+            self.s_addr = np.ascontiguousarray(sa); self.s_len = np.ascontiguousarray(self.slen.astype(np.uint64))
+            SR = self.SR = rec.Series()
+            SR.n_reads = n_reads; SR.n_containers = n_cont
+            SR.cont_off = self.cont_off.ctypes.data_as(u64p); SR.streams = None; SR.streams_len = 0
+            SR.stream_off = self.s_addr.ctypes.data_as(u64p); SR.stream_len = self.s_len.ctypes.data_as(u64p)
+            SR.read_off = vp(self.t_roff.data_ptr()); SR.rflags = vp(self.t_rfl.data_ptr())
+            self.U = rec.Features(); self.d_mapq = C.c_void_p(); self.u_status = np.zeros(n_cont, np.int32)
         # correctness of what is timed: the round trip restores every base and quality of every read
         self.decode()
         self.stream.synchronize()
         assert int(self.dd_st.abs().sum()) == 0 and int(self.o_stat.abs().sum()) == 0 and int(self.o_star.sum()) == 0
         assert torch.equal(self.o_bases, self.t_bases) and torch.equal(self.o_quals, self.t_quals), 'round trip mismatch'
+        if self.use_unpack:
+            got = np.empty(n_reads, np.uint8)
+            self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(got.ctypes.data), self.d_mapq, C.c_uint64(n_reads), self._sp()))
+            assert np.array_equal(got, self.t_mapq.cpu().numpy()) and int(np.abs(self.u_status).sum()) == 0, 'series -> features mismatch'
         self.prepared = True
 
     def decode(self):
-        from cramtools_b200._lib import u8p, u32p, u64p
+        from cramtools_b200._lib import u8p, u32p, u64p, i32p
         ctx, F, N, vp = self.ctx, self.F, self.N, C.c_void_p
         ctx.check(ctx.lib.cramgpu_rans_decode_dev(ctx.handle, self.nblk, vp(self.enc_out.data_ptr()), self.c_off.ctypes.data_as(u64p),
                                                   self.c_len.ctypes.data_as(u32p), self.prefixes.ctypes.data_as(u8p),
                                                   vp(self.dec_out.data_ptr()), C.c_uint64(self.dec_out.numel()), vp(self.dd_off.data_ptr()),
                                                   vp(self.dd_len.data_ptr()), vp(self.dd_st.data_ptr()), self._sp()))
-        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
-        N.payload = F.payload
+        if self.use_unpack:
+            # row P on the device: the read features come from the series themselves (QS / BA as just decoded, the series the
+            # Java host inflates -- FN FC FP BS DL SC RS HC PD MQ -- as the encoder left them), not from the encoder's arrays
+            U = self.U
+            sa = self.s_addr; keepq, keepb = sa[:, self.KQS].copy(), sa[:, self.KBA].copy()
+            sa[:] = np.uint64(F.streams) + self.soff; sa[:, self.KQS] = keepq; sa[:, self.KBA] = keepb
+            ctx.check(ctx.lib.cramgpu_features_unpack_dev(ctx.handle, C.byref(self.SR), C.byref(U), C.byref(self.d_mapq),
+                                                          self.u_status.ctypes.data_as(i32p), self._sp()))
+            N.feat_off = U.feat_off; N.f_op = U.f_op; N.f_pos = U.f_pos; N.f_val = U.f_val; N.f_aux = U.f_aux; N.payload = U.payload
+            N.qs = None; N.read_qs_off = U.read_qs_off; N.ba = None; N.read_ba_off = U.read_ba_off      # absolute addresses
+            N.matrix = F.matrix
+        else:
+            N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
+            N.payload = F.payload
         ctx.check(ctx.lib.cramgpu_normalize_decode_dev(ctx.handle, C.byref(N), vp(self.o_bases.data_ptr()), vp(self.o_quals.data_ptr()),
                                                        vp(self.o_star.data_ptr()), vp(self.o_stat.data_ptr()), self._sp()))
 
@@ -436,7 +465,7 @@ def run_ours(args):
     # Two host locks keep at most one context in each phase.
     n_lanes = depth = max(1, args.pipeline)
     groups = [dist.new_group() if world > 1 else None for _ in range(depth)]
-    lanes = [Lane(i, n_cont, ref, rd, extra, nu, dev, rank, world, groups[i]) for i in range(depth)]
+    lanes = [Lane(i, n_cont, ref, rd, extra, nu, dev, rank, world, groups[i], not args.no_unpack) for i in range(depth)]
     for ln in lanes:
         ln.prepare()
     n_reads = lanes[0].n_reads
@@ -536,6 +565,7 @@ def run_ours(args):
         rans_ms_enc = sum(v for k, v in kavg.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
         rans_ms_dec = sum(v for k, v in kavg.items() if k in ('k_dec_tables', 'k_dec0', 'k_dec1', 'k_dec1_big'))
         cfg = workload_config(args, n_cont)
+        cfg['decode_features'] = 'taken from the encoder' if args.no_unpack else 'unpacked from the decoded series on the device (k_unpack, row P)'
         cfg['pipeline'] = ('%d contexts/streams per GPU, step i on context i %% %d: encode of step i+1 overlaps decode of step i' % (depth, depth)) if depth > 1 else 'none: one stream, phases back to back'
         line = {
             'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
@@ -804,6 +834,7 @@ def main():
     ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
     ap.add_argument('--pipeline', type=int, default=2, help='contexts per GPU taking consecutive steps in turn (1 = no overlap of encode and decode)')
     ap.add_argument('--e2e-pipeline', type=int, default=4, help='contexts of the end-to-end leg taking consecutive steps in turn')
+    ap.add_argument('--no-unpack', action='store_true', help='decode side: take the read features from the encoder instead of unpacking the series (row P)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':

@@ -220,6 +220,7 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->dev_out.p) cudaFree(ctx->dev_out.p);
     if (ctx->rec_scratch.p) cudaFree(ctx->rec_scratch.p);
     if (ctx->rec_out.p) cudaFree(ctx->rec_out.p);
+    if (ctx->rec_unp.p) cudaFree(ctx->rec_unp.p);
     if (ctx->pin_rec) cudaFreeHost(ctx->pin_rec);
     if (ctx->pin_feat) cudaFreeHost(ctx->pin_feat);
     if (ctx->pin_in) cudaFreeHost(ctx->pin_in);

@@ -67,6 +67,7 @@ struct cramgpu_ctx {
     DevPool scratch;          // carved anew by every call
     DevPool dev_in, dev_out;  // device staging of the host entry points
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
+    DevPool rec_unp;                // results of cramgpu_features_unpack (its input series may be an encode result in rec_out)
     void *pin_rec = nullptr; size_t pin_rec_cap = 0;
     void *pin_feat = nullptr; size_t pin_feat_cap = 0;   // host copy of the last cramgpu_features_encode result
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;

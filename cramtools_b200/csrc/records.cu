@@ -1735,8 +1735,9 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
 // P: PD, i: BA byte, Q: QS byte, S: SC bytes up to the TAB (ByteArrayStopEncoding) --, then MQ, then the score array
 // (readLength bytes of QS) when the record carries one.  Unmapped: readLength bytes of BA unless the bases are
 // unknown, then the score array.  Every integer is ITF8 [ITF8.java:21-51].
-// The walk is sequential by nature (every field's position depends on the ones before it): one thread per container,
-// all containers of the call side by side.
+// The walk is sequential by nature (every field's position depends on the ones before it): one warp per container with
+// one working lane (containers in the lanes of one warp would wait for each other's cache misses at every load), all
+// containers of the call side by side.
 struct UnpackArgs {
     uint32_t n_containers;
     const uint64_t *cont_off, *soff, *slen, *fbase, *pbase;     // device copies of the per-container tables
@@ -1746,17 +1747,14 @@ struct UnpackArgs {
     uint64_t *read_qs_off, *read_ba_off; uint8_t *mapq; int32_t *status;
 };
 
-__global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
-{
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= a.n_containers) return;
+// cursors of one container's walk (lane 0 owns them; the other lanes see the values lane 0 publishes per batch)
+struct UnpackCur {
     uint64_t p[CRAMGPU_S_COUNT], e[CRAMGPU_S_COUNT];
-#pragma unroll
-    for (int k = 0; k < CRAMGPU_S_COUNT; k++) { p[k] = a.soff[(size_t)c * CRAMGPU_S_COUNT + k]; e[k] = p[k] + a.slen[(size_t)c * CRAMGPU_S_COUNT + k]; }
-    const uint8_t *S = a.streams;
-    int bad = 0;
-    auto byte = [&](int k) -> uint32_t { if (p[k] >= e[k]) { bad = 1; return 0; } return S[p[k]++]; };
-    auto itf8 = [&](int k) -> int32_t {                               // ITF8.readUnsignedITF8 [ITF8.java:21-51]
+    const uint8_t *S;
+    int bad;
+    __device__ __forceinline__ uint32_t byte(int k) { if (p[k] >= e[k]) { bad |= 1; return 0; } return S[p[k]++]; }
+    __device__ __forceinline__ int32_t itf8(int k)                                   // ITF8.readUnsignedITF8 [ITF8.java:21-51]
+    {
         const uint32_t b1 = byte(k);
         if (b1 < 0x80) return (int32_t)b1;
         if (b1 < 0xC0) return (int32_t)(((b1 & 0x7F) << 8) | byte(k));
@@ -1764,63 +1762,153 @@ __global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
         if (b1 < 0xF0) { const uint32_t b2 = byte(k), b3 = byte(k); return (int32_t)(((b1 & 0x1F) << 24) | (b2 << 16) | (b3 << 8) | byte(k)); }
         const uint32_t b2 = byte(k), b3 = byte(k), b4 = byte(k);
         return (int32_t)(((b1 & 0x0F) << 28) | (b2 << 20) | (b3 << 12) | (b4 << 4) | (byte(k) & 0x0F));
-    };
-    uint64_t nf_total = 0, pay = a.pbase[c];
-    const uint64_t fb = a.fbase[c], f_cap = a.slen[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_FC];
-    for (uint64_t r = a.cont_off[c]; r < a.cont_off[c + 1]; r++) {
-        const uint64_t rlen = a.read_off[r + 1] - a.read_off[r];
-        const uint8_t fl = a.rflags[r];
-        a.feat_off[r] = fb + nf_total;
-        uint64_t qo = ~0ull, bo = ~0ull;
-        uint32_t mq = 0;
-        if (!(fl & CRAMGPU_NF_UNMAPPED)) {
-            const uint32_t nf = (uint32_t)itf8(CRAMGPU_S_FN);
-            int32_t prev = 0;
-            for (uint32_t i = 0; i < nf && !bad; i++) {
-                if (nf_total >= f_cap) { bad = 1; break; }            // more features than operator bytes
-                const uint8_t op = (uint8_t)byte(CRAMGPU_S_FC);
-                prev += itf8(CRAMGPU_S_FP);
-                int32_t val = 0, aux = 0;
-                switch (op) {
-                case 'X': val = (int32_t)byte(CRAMGPU_S_BS); break;
-                case 'D': val = itf8(CRAMGPU_S_DL); break;
-                case 'N': val = itf8(CRAMGPU_S_RS); break;
-                case 'H': val = itf8(CRAMGPU_S_HC); break;
-                case 'P': val = itf8(CRAMGPU_S_PD); break;
-                case 'i': val = (int32_t)byte(CRAMGPU_S_BA); break;
-                case 'Q': val = (int32_t)byte(CRAMGPU_S_QS); break;
-                case 'S': {
-                    val = (int32_t)pay;
-                    for (;;) {
-                        if (p[CRAMGPU_S_SC] >= e[CRAMGPU_S_SC]) { bad = 1; break; }
-                        const uint8_t b = S[p[CRAMGPU_S_SC]++];
-                        if (b == '\t') break;
-                        a.payload[pay++] = b; aux++;
-                    }
-                    break;
-                }
-                default: bad = 2; break;                              // an operator this library does not write (B, I, b, q)
-                }
-                const uint64_t fi = fb + nf_total;
-                a.f_op[fi] = op; a.f_pos[fi] = prev; a.f_val[fi] = val; a.f_aux[fi] = aux;
-                nf_total++;
-            }
-            mq = (uint32_t)itf8(CRAMGPU_S_MQ);
-        } else if (!(fl & CRAMGPU_NF_UNKNOWN_BASES)) {
-            bo = p[CRAMGPU_S_BA]; p[CRAMGPU_S_BA] += rlen;
-            if (p[CRAMGPU_S_BA] > e[CRAMGPU_S_BA]) bad = 1;
-        }
-        if (fl & CRAMGPU_NF_FORCE_QS) {
-            qo = p[CRAMGPU_S_QS]; p[CRAMGPU_S_QS] += rlen;
-            if (p[CRAMGPU_S_QS] > e[CRAMGPU_S_QS]) bad = 1;
-        }
-        a.read_qs_off[r] = qo; a.read_ba_off[r] = bo; a.mapq[r] = (uint8_t)mq;
-        if (bad) break;
     }
-    // the operator bytes a corrupt container does not account for still get defined feature slots
-    for (uint64_t i = nf_total; i < f_cap; i++) { a.f_op[fb + i] = 0; a.f_pos[fb + i] = 0; a.f_val[fb + i] = 0; a.f_aux[fb + i] = 0; }
-    if (bad) for (uint64_t r = a.cont_off[c]; r < a.cont_off[c + 1]; r++) if (a.feat_off[r] > fb + nf_total || a.feat_off[r] < fb) a.feat_off[r] = fb + nf_total;
-    a.status[c] = bad == 2 ? CRAMGPU_ERR_UNSUPPORTED : bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
+};
+// the nf features of one record, in the order the writer put them; fi = first free feature slot; -> features written
+__device__ __forceinline__ uint32_t unpack_features(const UnpackArgs &a, UnpackCur &cu, uint32_t nf, uint64_t fi, uint64_t f_end, uint64_t &pay)
+{
+    int32_t prev = 0;
+    uint32_t done = 0;
+    for (; done < nf && !cu.bad; done++, fi++) {
+        if (fi >= f_end) { cu.bad |= 1; break; }                       // more features than operator bytes
+        const uint8_t op = (uint8_t)cu.byte(CRAMGPU_S_FC);
+        prev += cu.itf8(CRAMGPU_S_FP);
+        int32_t val = 0, aux = 0;
+        switch (op) {
+        case 'X': val = (int32_t)cu.byte(CRAMGPU_S_BS); break;
+        case 'D': val = cu.itf8(CRAMGPU_S_DL); break;
+        case 'N': val = cu.itf8(CRAMGPU_S_RS); break;
+        case 'H': val = cu.itf8(CRAMGPU_S_HC); break;
+        case 'P': val = cu.itf8(CRAMGPU_S_PD); break;
+        case 'i': val = (int32_t)cu.byte(CRAMGPU_S_BA); break;
+        case 'Q': val = (int32_t)cu.byte(CRAMGPU_S_QS); break;
+        case 'S': {
+            val = (int32_t)pay;
+            for (;;) {
+                if (cu.p[CRAMGPU_S_SC] >= cu.e[CRAMGPU_S_SC]) { cu.bad |= 1; break; }
+                const uint8_t b = cu.S[cu.p[CRAMGPU_S_SC]++];
+                if (b == '\t') break;
+                a.payload[pay++] = b; aux++;
+            }
+            break;
+        }
+        default: cu.bad |= 2; break;                                  // an operator this library does not write (B, I, b, q)
+        }
+        a.f_op[fi] = op; a.f_pos[fi] = prev; a.f_val[fi] = val; a.f_aux[fi] = aux;
+    }
+    return done;
+}
+
+// One warp per container.  32 records per round: their per-record fields (FN, MQ -- one byte each in all but rare
+// records --, flags, lengths, the offsets of the score arrays) are handled by the 32 lanes at once; lane 0 walks the few
+// features of the round one after the other (every field's position depends on the fields before it).  A round with a
+// multi-byte FN or MQ is walked by lane 0 alone.
+__global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
+{
+    const uint32_t c = blockIdx.x, lane = threadIdx.x, lt = (1u << lane) - 1u;
+    if (c >= a.n_containers) return;
+    __shared__ uint32_t s_nf[32], s_arrq[32], s_arrb[32], s_bad;
+    __shared__ uint64_t s_p[CRAMGPU_S_COUNT], s_pay;
+    UnpackCur cu;
+#pragma unroll
+    for (int k = 0; k < CRAMGPU_S_COUNT; k++) { cu.p[k] = a.soff[(size_t)c * CRAMGPU_S_COUNT + k]; cu.e[k] = cu.p[k] + a.slen[(size_t)c * CRAMGPU_S_COUNT + k]; }
+    cu.S = a.streams; cu.bad = 0;
+    const uint64_t fb = a.fbase[c], f_cap = a.slen[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_FC];
+    uint64_t nf_total = 0, pay = a.pbase[c];                           // kept identical in all lanes
+    const uint64_t r_end = a.cont_off[c + 1];
+    for (uint64_t r0 = a.cont_off[c]; r0 < r_end; r0 += 32) {
+        const uint64_t r = r0 + lane;
+        const bool live = r < r_end;
+        const uint64_t rlen = live ? a.read_off[r + 1] - a.read_off[r] : 0;
+        const uint8_t fl = live ? a.rflags[r] : (uint8_t)(CRAMGPU_NF_UNMAPPED | CRAMGPU_NF_UNKNOWN_BASES);
+        const bool mapped = live && !(fl & CRAMGPU_NF_UNMAPPED);
+        const uint32_t mb = __ballot_sync(0xFFFFFFFFu, mapped), rank = __popc(mb & lt), nm = __popc(mb);
+        // lane 0's cursors, as of the start of the round
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < CRAMGPU_S_COUNT; k++) s_p[k] = cu.p[k];
+        }
+        __syncwarp();
+        const uint64_t pFN = s_p[CRAMGPU_S_FN], pMQ = s_p[CRAMGPU_S_MQ], pQS = s_p[CRAMGPU_S_QS], pBA = s_p[CRAMGPU_S_BA];
+        // FN and MQ of record `rank` among the mapped ones, if every such field of the round is a single byte
+        uint32_t bFN = 0, bMQ = 0;
+        bool ok = true;
+        if (mapped) {
+            ok = pFN + rank < cu.e[CRAMGPU_S_FN] && pMQ + rank < cu.e[CRAMGPU_S_MQ];
+            if (ok) { bFN = cu.S[pFN + rank]; bMQ = cu.S[pMQ + rank]; ok = bFN < 0x80 && bMQ < 0x80; }
+        }
+        const bool fast = __all_sync(0xFFFFFFFFu, ok);
+        const uint32_t arrq = (live && (fl & CRAMGPU_NF_FORCE_QS)) ? (uint32_t)rlen : 0u;                              // score array
+        const uint32_t arrb = (live && !mapped && !(fl & CRAMGPU_NF_UNKNOWN_BASES)) ? (uint32_t)rlen : 0u;             // unmapped bases
+        if (fast) {
+            const uint32_t nf = bFN;
+            uint32_t tot, ex = warp_excl_scan_u32(nf, lane, tot);
+            if (live) { a.feat_off[r] = fb + nf_total + ex; a.mapq[r] = (uint8_t)bMQ; }
+            s_nf[lane] = nf; s_arrq[lane] = arrq; s_arrb[lane] = arrb;
+            __syncwarp();
+            if (lane == 0) {
+                cu.p[CRAMGPU_S_FN] += nm; cu.p[CRAMGPU_S_MQ] += nm;
+                // records in turn: features (they may take bytes of QS / BA), then the record's arrays
+                uint64_t fi = fb + nf_total;
+                for (uint32_t l = 0; l < 32; l++) {
+                    const uint32_t n = s_nf[l];
+                    if (n) fi += unpack_features(a, cu, n, fi, fb + f_cap, pay);
+                    const uint32_t aq = s_arrq[l], ab = s_arrb[l];
+                    s_arrq[l] = (uint32_t)(cu.p[CRAMGPU_S_QS] - pQS); s_arrb[l] = (uint32_t)(cu.p[CRAMGPU_S_BA] - pBA);   // where its arrays start
+                    cu.p[CRAMGPU_S_QS] += aq; cu.p[CRAMGPU_S_BA] += ab;
+                }
+                if (cu.p[CRAMGPU_S_QS] > cu.e[CRAMGPU_S_QS] || cu.p[CRAMGPU_S_BA] > cu.e[CRAMGPU_S_BA]) cu.bad |= 1;
+                s_pay = pay; s_bad = (uint32_t)cu.bad;
+            }
+            __syncwarp();
+            if (live) {
+                a.read_qs_off[r] = (fl & CRAMGPU_NF_FORCE_QS) ? pQS + s_arrq[lane] : ~0ull;
+                a.read_ba_off[r] = (!mapped && !(fl & CRAMGPU_NF_UNKNOWN_BASES)) ? pBA + s_arrb[lane] : ~0ull;
+            }
+            nf_total += tot; pay = s_pay;
+            if (s_bad) break;
+            __syncwarp();
+        } else {
+            // a multi-byte FN or MQ somewhere in the round: lane 0 walks its records one by one
+            if (lane == 0) {
+                uint64_t nft = nf_total;
+                for (uint64_t rr = r0; rr < r0 + 32 && rr < r_end && !cu.bad; rr++) {
+                    const uint64_t len = a.read_off[rr + 1] - a.read_off[rr];
+                    const uint8_t f2 = a.rflags[rr];
+                    a.feat_off[rr] = fb + nft;
+                    uint64_t qo = ~0ull, bo = ~0ull;
+                    uint32_t mq = 0;
+                    if (!(f2 & CRAMGPU_NF_UNMAPPED)) {
+                        const uint32_t n = (uint32_t)cu.itf8(CRAMGPU_S_FN);
+                        nft += unpack_features(a, cu, n, fb + nft, fb + f_cap, pay);
+                        mq = (uint32_t)cu.itf8(CRAMGPU_S_MQ);
+                    } else if (!(f2 & CRAMGPU_NF_UNKNOWN_BASES)) {
+                        bo = cu.p[CRAMGPU_S_BA]; cu.p[CRAMGPU_S_BA] += len;
+                        if (cu.p[CRAMGPU_S_BA] > cu.e[CRAMGPU_S_BA]) cu.bad |= 1;
+                    }
+                    if (f2 & CRAMGPU_NF_FORCE_QS) {
+                        qo = cu.p[CRAMGPU_S_QS]; cu.p[CRAMGPU_S_QS] += len;
+                        if (cu.p[CRAMGPU_S_QS] > cu.e[CRAMGPU_S_QS]) cu.bad |= 1;
+                    }
+                    a.read_qs_off[rr] = qo; a.read_ba_off[rr] = bo; a.mapq[rr] = (uint8_t)mq;
+                }
+                s_p[0] = nft; s_pay = pay; s_bad = (uint32_t)cu.bad;
+            }
+            __syncwarp();
+            nf_total = s_p[0]; pay = s_pay;
+            if (s_bad) break;
+            __syncwarp();
+        }
+    }
+    __syncwarp();
+    const int bad = (int)__shfl_sync(0xFFFFFFFFu, (uint32_t)cu.bad, 0);
+    // the operator bytes a corrupt container does not account for still get defined feature slots, and its records defined offsets
+    for (uint64_t i = (bad ? 0 : nf_total) + lane; i < f_cap; i += 32) { a.f_op[fb + i] = 0; a.f_pos[fb + i] = 0; a.f_val[fb + i] = 0; a.f_aux[fb + i] = 0; }
+    if (bad) {
+        // nothing of a corrupt container is handed on: its records get no features and no arrays
+        for (uint64_t r = a.cont_off[c] + lane; r < r_end; r += 32) { a.feat_off[r] = fb; a.read_qs_off[r] = ~0ull; a.read_ba_off[r] = ~0ull; a.mapq[r] = 0; }
+    }
+    if (lane == 0) a.status[c] = (bad & 2) ? CRAMGPU_ERR_UNSUPPORTED : bad ? CRAMGPU_ERR_CORRUPT : CRAMGPU_OK;
 }
 
 static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t **d_mapq,
@@ -1831,7 +1919,7 @@ static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cram
     const uint64_t n = in->n_reads;
     const uint32_t nc = in->n_containers;
     if (n == 0 || nc == 0) return CRAMGPU_OK;
-    if (!in->cont_off || !in->stream_off || !in->stream_len || !in->streams || !in->read_off || !in->rflags)
+    if (!in->cont_off || !in->stream_off || !in->stream_len || !in->read_off || !in->rflags)
         return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
     if (in->cont_off[0] != 0 || in->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
     // one operator byte per feature: the FC lengths give every container's place in the feature arrays up front
@@ -1841,7 +1929,7 @@ static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cram
         fbase[c] = nfeat; nfeat += in->stream_len[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_FC];
         pbase[c] = paylen; paylen += in->stream_len[(size_t)c * CRAMGPU_S_COUNT + CRAMGPU_S_SC];   // soft-clip bytes incl. their TABs: an upper bound
         for (int k = 0; k < CRAMGPU_S_COUNT; k++)
-            if (in->stream_off[(size_t)c * CRAMGPU_S_COUNT + k] + in->stream_len[(size_t)c * CRAMGPU_S_COUNT + k] > in->streams_len)
+            if (in->streams && in->stream_off[(size_t)c * CRAMGPU_S_COUNT + k] + in->stream_len[(size_t)c * CRAMGPU_S_COUNT + k] > in->streams_len)
                 return ctx_fail(ctx, CRAMGPU_ERR_ARG, "series %d of container %u lies outside streams", k, c);
     }
     const size_t tab = 8 * (size_t)CRAMGPU_S_COUNT * nc;
@@ -1863,8 +1951,8 @@ static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cram
     size_t q_op = co.take(nfeat + 16), q_pos = co.take(4 * nfeat + 16), q_val = co.take(4 * nfeat + 16), q_aux = co.take(4 * nfeat + 16);
     size_t q_foff = co.take(8 * (size_t)(n + 1)), q_pay = co.take(paylen + 16);
     size_t q_qso = co.take(8 * (size_t)n), q_bao = co.take(8 * (size_t)n), q_mq = co.take(n);
-    if (int rc = pool_reserve(ctx, ctx->rec_out, co.off)) return rc;
-    uint8_t *O = (uint8_t *)ctx->rec_out.p;
+    if (int rc = pool_reserve(ctx, ctx->rec_unp, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->rec_unp.p;
     UnpackArgs a;
     memset(&a, 0, sizeof a);
     a.n_containers = nc;
@@ -1874,7 +1962,7 @@ static int features_unpack_impl(cramgpu_ctx *ctx, const cramgpu_series *in, cram
     a.f_op = O + q_op; a.f_pos = (int32_t *)(O + q_pos); a.f_val = (int32_t *)(O + q_val); a.f_aux = (int32_t *)(O + q_aux);
     a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
     a.mapq = O + q_mq; a.status = (int32_t *)(S + o_stat);
-    LAUNCH(ctx, st, "k_unpack", k_unpack<<<(nc + 31) / 32, 32, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_unpack", k_unpack<<<nc, 32, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     // feat_off[n] = all features; per-container status back to the host
     if (int rc = pinned_reserve(ctx, &ctx->pin_rec, &ctx->pin_rec_cap, 4 * (size_t)nc + 64)) return rc;

@@ -340,7 +340,8 @@ typedef struct cramgpu_series {
     uint64_t n_reads;
     uint32_t n_containers;
     const uint64_t *cont_off;     /* HOST [n_containers+1] */
-    const uint8_t *streams;       /* decoded series bytes of all containers */
+    const uint8_t *streams;       /* decoded series bytes of all containers; device variant: NULL = stream_off holds absolute
+                                     device addresses (series decoded into different buffers), results' offsets then too */
     uint64_t streams_len;
     const uint64_t *stream_off;   /* HOST [n_containers][CRAMGPU_S_COUNT] */
     const uint64_t *stream_len;   /* HOST [n_containers][CRAMGPU_S_COUNT] */
@@ -356,7 +357,7 @@ typedef struct cramgpu_series {
  * returns the first such status.  Host variant: streams / read_off / rflags may be host or device memory, results are
  * host memory owned by the context (mapq: caller's array, optional).  Device variant: those three are device
  * pointers, results are device memory owned by the context (*d_mapq receives the mapq array), valid until the next
- * record call on ctx.
+ * unpack call on ctx (an encode result of the same context stays valid: it may be the input).
  */
 int cramgpu_features_unpack(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t *mapq,
                             int32_t *status);
