@@ -205,21 +205,27 @@ __device__ __forceinline__ uint4 ld_u128_any(const uint8_t *p)
 // [src, src + n) -> [dst, dst + n), both contiguous, lanes over consecutive 16-byte granules of dst: every load and store
 // of the warp falls into a handful of cache lines (a thread-per-read copy touches one line per lane).
 // Returns, per lane, whether it saw a byte 0xFF.
-__device__ __forceinline__ bool warp_copy(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint32_t n, uint32_t lane)
+template <class FW, class FB>
+__device__ __forceinline__ bool warp_copy_x(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint32_t n, uint32_t lane, FW xw, FB xb)
 {
     bool ff = false;
     uint32_t h = (16u - (uint32_t)((uintptr_t)dst & 15)) & 15u;
     if (h > n) h = n;
-    if (lane < h) { const uint8_t b = src[lane]; dst[lane] = b; ff = b == 0xFF; }
+    if (lane < h) { const uint8_t b = src[lane]; dst[lane] = xb(b); ff = b == 0xFF; }
     const uint32_t ng = (n - h) >> 4;
     for (uint32_t g = lane; g < ng; g += 32) {
-        const uint4 v = ld_u128_any(src + h + 16 * g);
+        uint4 v = ld_u128_any(src + h + 16 * g);
         ff = ff || (__vcmpeq4(v.x, 0xFFFFFFFFu) | __vcmpeq4(v.y, 0xFFFFFFFFu) | __vcmpeq4(v.z, 0xFFFFFFFFu) | __vcmpeq4(v.w, 0xFFFFFFFFu)) != 0;
+        v.x = xw(v.x); v.y = xw(v.y); v.z = xw(v.z); v.w = xw(v.w);
         *reinterpret_cast<uint4 *>(dst + h + 16 * g) = v;
     }
     const uint32_t t0 = h + 16 * ng;
-    if (t0 + lane < n) { const uint8_t b = src[t0 + lane]; dst[t0 + lane] = b; ff = ff || b == 0xFF; }
+    if (t0 + lane < n) { const uint8_t b = src[t0 + lane]; dst[t0 + lane] = xb(b); ff = ff || b == 0xFF; }
     return ff;
+}
+__device__ __forceinline__ bool warp_copy(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, uint32_t n, uint32_t lane)
+{
+    return warp_copy_x(dst, src, n, lane, IdW(), IdB());
 }
 // the bases of 32 consecutive reads of one length L (16 <= L <= 8192), read j = bytes [o_j, o_j + L) of `ref`, into the
 // contiguous [dst, dst + 32 L): lanes over the aligned 16-byte granules of dst; a granule takes its bytes from one read
@@ -811,6 +817,60 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
     const uint64_t n = *a.clist_n, step = (uint64_t)gridDim.x * 4;
     for (uint64_t i = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); i < n; i += step)
         walk_read<WRITE>(a, ps, a.clist_r[i], a.clist_c[i], lane);
+}
+
+// Score arrays under a quality model WITHOUT base categories: every score of a force-preserved record gets the treatment
+// of the last policy that applies to the record (QualityScorePreservation.addQualityScores [:276-301] with only read
+// categories in play) -- preserved as it is, or binned [Binning.java:63-71].  One thread per read, in order; 32 records of
+// one length and one treatment whose arrays lie back to back are done as one warp-wide copy.
+struct BinW {
+    __device__ __forceinline__ uint32_t operator()(uint32_t w) const
+    {
+        return (uint32_t)illumina_bin((uint8_t)w) | ((uint32_t)illumina_bin((uint8_t)(w >> 8)) << 8) |
+               ((uint32_t)illumina_bin((uint8_t)(w >> 16)) << 16) | ((uint32_t)illumina_bin((uint8_t)(w >> 24)) << 24);
+    }
+};
+struct BinB { __device__ __forceinline__ uint8_t operator()(uint8_t b) const { return illumina_bin(b); } };
+struct FillW { __device__ __forceinline__ uint32_t operator()(uint32_t) const { return 0xFFFFFFFFu; } };
+struct FillB { __device__ __forceinline__ uint8_t operator()(uint8_t) const { return 0xFF; } };
+
+__global__ void __launch_bounds__(128) k_rec_forced_flat(RecArgs a, PolSet ps)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    uint64_t r; uint32_t c; bool live;
+    if (gridDim.y > 1 || a.n_containers == 1) {
+        c = blockIdx.y;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.cont_off[c + 1];
+    } else {
+        r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+        live = r < a.n_reads;
+    }
+    uint64_t qoff = ~0ull, lo = 0, rlen = 0;
+    int treatment = 2;                                   // 2: no policy sets a score (bytes stay "none")
+    if (live && (a.force[r] & 1)) {
+        qoff = a.read_qs_off[r];
+        lo = a.read_off[r];
+        rlen = a.read_off[r + 1] - lo;
+        const uint16_t flag = a.flag[r];
+        const uint8_t mapq = a.mapq[r];
+        for (int k = 0; k < ps.n; k++)
+            if (read_in_category(ps.p[k], flag, mapq) && ps.p[k].treatment != 2) treatment = ps.p[k].treatment;
+    }
+    const bool has = qoff != ~0ull && rlen < (1ull << 31);
+    const uint64_t q0 = __shfl_sync(0xFFFFFFFFu, qoff, 0), lo0 = __shfl_sync(0xFFFFFFFFu, lo, 0), rl0 = __shfl_sync(0xFFFFFFFFu, rlen, 0);
+    const int t0 = __shfl_sync(0xFFFFFFFFu, treatment, 0);
+    const uint32_t L0 = (uint32_t)rl0;
+    const bool flat = has && rlen == rl0 && treatment == t0 && qoff == q0 + (uint64_t)lane * L0 && lo == lo0 + (uint64_t)lane * L0;
+    if (__all_sync(0xFFFFFFFFu, flat) && rl0 <= (1u << 20)) {
+        if (t0 == 0) warp_copy(a.streams + q0, a.quals + lo0, 32 * L0, lane);
+        else if (t0 == 1) warp_copy_x(a.streams + q0, a.quals + lo0, 32 * L0, lane, BinW(), BinB());
+        else warp_copy_x(a.streams + q0, a.quals + lo0, 32 * L0, lane, FillW(), FillB());
+    } else if (has) {
+        if (treatment == 0) copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, IdW(), IdB());
+        else if (treatment == 1) copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, BinW(), BinB());
+        else copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, FillW(), FillB());
+    }
 }
 
 // Forced arrays under a lossy model need the per-base scores again; done by a second small kernel so that the walk above
@@ -1443,7 +1503,8 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
     LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.wlist_r, a.wlist_c, a.wlist_n));
     LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<wgrid, 128, 0, st>>>(a, ps));
-    if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
+    if (ps.n >= 0 && !ps.per_base) LAUNCH(ctx, st, "k_rec_forced_flat", k_rec_forced_flat<<<sgrid, 128, 0, st>>>(a, ps));
+    else if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
     CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(ctx, cudaGetLastError());
 
