@@ -356,3 +356,64 @@ def test_unpack_corrupt_and_foreign_series(R, gpu_ctx):
     st[o] = ord('B')                                     # ReadBase: needs the BA+QS pair this library never writes
     up = R.features_unpack(st, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx, check=False)
     assert list(up.status) == [0, 0, _lib.ERR_UNSUPPORTED]
+
+
+def _concat_reads(parts):
+    """several synth.reads results over one reference -> one SoA batch"""
+    out = {}
+    for k in ('bases', 'quals', 'cigar', 'pos', 'flag', 'mapq'):
+        out[k] = np.concatenate([p[k] for p in parts])
+    ro, co = [np.zeros(1, np.int64)], [np.zeros(1, np.int64)]
+    for p in parts:
+        ro.append(p['read_off'][1:] + ro[-1][-1]); co.append(p['cigar_off'][1:] + co[-1][-1])
+    out['read_off'] = np.concatenate(ro); out['cigar_off'] = np.concatenate(co)
+    out['names'] = sum([list(p.get('names', [b''] * len(p['pos']))) for p in parts], [])
+    return out
+
+
+def test_mixed_read_lengths_and_region_edges(R, gpu_ctx):
+    """the warp-wide copies only apply to 32 records of one length well inside the reference: records of other lengths, runs
+    that change length inside a warp, records at the very start / end of the reference and short (< 16 bases) records take
+    the per-record paths -- same results (oracle parity on encode, bit-exact round trip on decode)"""
+    from oracle import records as orec
+    ref = synth.reference(30000, 77)
+    parts = [synth.reads(ref, 700, 78, read_len=150, sub_rate=0.01), synth.reads(ref, 333, 79, read_len=100, sub_rate=0.01),
+             synth.reads(ref, 150, 80, read_len=40, indel_frac=0.2, clip_frac=0.1), synth.reads(ref, 97, 81, read_len=33),
+             synth.reads(ref, 64, 82, read_len=150, indel_frac=0.0, clip_frac=0.0, contig_start=0, contig_end=260),           # at the start
+             synth.reads(ref, 64, 83, read_len=150, indel_frac=0.0, clip_frac=0.0, contig_start=ref.size - 400, contig_end=ref.size)]
+    rd = _concat_reads(parts)
+    n = len(rd['pos'])
+    cont_off = np.array([0, 500, 1100, n], np.uint64)
+    enc = R.features_encode(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    for c in range(3):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        sub = dict(bases=rd['bases'][rd['read_off'][a]:rd['read_off'][b]], quals=rd['quals'][rd['read_off'][a]:rd['read_off'][b]],
+                   read_off=rd['read_off'][a:b + 1] - rd['read_off'][a], cigar=rd['cigar'][rd['cigar_off'][a]:rd['cigar_off'][b]],
+                   cigar_off=rd['cigar_off'][a:b + 1] - rd['cigar_off'][a], pos=rd['pos'][a:b], flag=rd['flag'][a:b], mapq=rd['mapq'][a:b])
+        ex = orec.extract(sub, ref)
+        force, scores = orec.quality(sub, ref, None)
+        want = orec.write_streams(sub, ex, force, scores)
+        for name in R.SERIES:
+            assert enc.series(c, name) == want[name], (c, name)
+    rfl = (enc.force_qs & 1).astype(np.uint8)
+    # decode with the tightest regions: [min start, max end] of each container
+    win_off = np.zeros(3, np.uint64); win_len = np.zeros(3, np.uint64); ws0 = np.zeros(3, np.int64)
+    rl = np.diff(rd['read_off'])
+    for c in range(3):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        s = int(rd['pos'][a:b].min()) - 1
+        e = min(int((rd['pos'][a:b] + rl[a:b] + 8).max()), ref.size)
+        win_off[c] = s; win_len[c] = e - s; ws0[c] = s
+    up = R.features_unpack(enc.streams, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx)
+    bases, quals, star, status = R.normalize_decode(rd['pos'], rd['read_off'], rfl, up, ref, ws0, enc.matrix, cont_off=cont_off,
+                                                    win_off=win_off, win_len=win_len, qs=enc.streams, read_qs_off=up.read_qs_off,
+                                                    ba=enc.streams, read_ba_off=up.read_ba_off, ctx=gpu_ctx)
+    assert (status == 0).all() and (star == 0).all()
+    assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
+    # and under a read-level lossy model: binned arrays of mixed lengths
+    encb = R.features_encode(rd, ref, '*8', cont_off=cont_off, ctx=gpu_ctx)
+    sub = dict(rd); forceb, scoresb = orec.quality(rd, ref, '*8')
+    assert ((encb.force_qs & 1) == (np.asarray(forceb) & 1)).all()
+    for i in range(n):
+        o, ln = int(encb.read_qs_off[i]), int(rl[i])
+        assert encb.streams[o:o + ln].tobytes() == np.asarray(scoresb[rd['read_off'][i]:rd['read_off'][i + 1]], np.uint8).tobytes(), i
