@@ -190,11 +190,12 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
     const O1Meta *m = meta + blockIdx.x;
     uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
 
-    __shared__ uint8_t cmap[256], smap[256];
+    // cs[b] = (context row of byte b: cmap[b] * nsym) | (symbol rank of b: smap[b]) << 16 -- one lookup per byte gives the
+    // column of this byte and the row of the next one
+    __shared__ uint32_t cs[256];
     __shared__ uint32_t cells[O1_SMEM_ENTRIES];
-    cmap[threadIdx.x] = m->cmap[threadIdx.x];
-    smap[threadIdx.x] = m->smap[threadIdx.x];
     const uint32_t ns = m->nsym, ncell = m->nsym * m->nctx;
+    cs[threadIdx.x] = (uint32_t)m->cmap[threadIdx.x] * ns | ((uint32_t)m->smap[threadIdx.x] << 16);
     const bool in_smem = ncell <= O1_SMEM_ENTRIES;
     if (in_smem) for (uint32_t i = threadIdx.x; i < ncell; i += 256) cells[i] = 0;
     __syncthreads();
@@ -207,26 +208,26 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
         uint32_t w[4] = {q.x, q.y, q.z, q.w};
         uint64_t gpos = start + ((uint64_t)i << 4);
         uint32_t prev = gpos ? in[((int64_t)i << 4) - 1] : 0;   // last = 0 before the first byte [:152]
-        uint32_t row = cmap[prev] * ns;
+        uint32_t row = cs[prev] & 0xFFFFu;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
 #pragma unroll
             for (int b = 0; b < 4; b++) {
-                uint32_t c = (w[k] >> (8 * b)) & 0xFF;
-                atomicAdd(&t[row + smap[c]], 1u);
-                row = cmap[c] * ns;
+                const uint32_t e = cs[(w[k] >> (8 * b)) & 0xFF];
+                atomicAdd(&t[row + (e >> 16)], 1u);
+                row = e & 0xFFFFu;
             }
         }
     }
     for (uint32_t i = (nvec << 4) + threadIdx.x; i < len; i += 256) {
         uint64_t gpos = start + i;
         uint32_t prev = gpos ? base[gpos - 1] : 0;
-        atomicAdd(&t[cmap[prev] * ns + smap[in[i]]], 1u);
+        atomicAdd(&t[(cs[prev] & 0xFFFFu) + (cs[in[i]] >> 16)], 1u);
     }
     if (blockIdx.y == 0 && threadIdx.x < 3) {
         // start symbols of lanes 1..3 are coded in context 0 [:163-166]
         uint32_t q = d.in_len >> 2;
-        atomicAdd(&t[cmap[0] * ns + smap[base[(uint64_t)(threadIdx.x + 1) * q]]], 1u);
+        atomicAdd(&t[(cs[0] & 0xFFFFu) + (cs[base[(uint64_t)(threadIdx.x + 1) * q]] >> 16)], 1u);
     }
     if (in_smem) {
         __syncthreads();
