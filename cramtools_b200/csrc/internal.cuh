@@ -14,6 +14,7 @@
 #define RANS_L (1u << 23)
 
 #define HIST_CHUNK (128u * 1024u)   // bytes of one block handled by one histogram CTA
+#define HIST1_CHUNK (512u * 1024u)  // the same for the order-1 pair counts (their shared-memory tables cost more to clear and add up)
 #define PACK_CHUNK (64u * 1024u)    // bytes of one block copied by one pack CTA
 #define O0_TAB_CAP 1040u            // >= 256*(1+1+2)+1
 #define O1_TAB_CAP 263936u          // >= 256*(2+1025)+1, multiple of 256

@@ -182,9 +182,9 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
                                                uint32_t *__restrict__ F1)
 {
     const BlockDesc d = desc[o1_blocks[blockIdx.x]];
-    uint64_t start = (uint64_t)blockIdx.y * HIST_CHUNK;
+    uint64_t start = (uint64_t)blockIdx.y * HIST1_CHUNK;
     if (start >= d.in_len) return;
-    uint32_t len = min((uint64_t)HIST_CHUNK, d.in_len - start);
+    uint32_t len = min((uint64_t)HIST1_CHUNK, d.in_len - start);
     const uint8_t *base = d_in + d.in_off;
     const uint8_t *in = base + start;
     const O1Meta *m = meta + blockIdx.x;
@@ -197,9 +197,12 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
     const uint32_t ns = m->nsym, ncell = m->nsym * m->nctx;
     cs[threadIdx.x] = (uint32_t)m->cmap[threadIdx.x] * ns | ((uint32_t)m->smap[threadIdx.x] << 16);
     const bool in_smem = ncell <= O1_SMEM_ENTRIES;
-    if (in_smem) for (uint32_t i = threadIdx.x; i < ncell; i += 256) cells[i] = 0;
+    // Quality streams put a third of all pairs into one cell: lanes of a warp hitting the same word are served one after
+    // the other.  As many copies of the table as fit (up to 8): lane l counts into copy l % copies, added up at the end.
+    const uint32_t ncopy = in_smem ? min(8u, O1_SMEM_ENTRIES / max(ncell, 1u)) : 1u;
+    if (in_smem) for (uint32_t i = threadIdx.x; i < ncell * ncopy; i += 256) cells[i] = 0;
     __syncthreads();
-    uint32_t *t = in_smem ? cells : g;
+    uint32_t *t = in_smem ? cells + (threadIdx.x % ncopy) * ncell : g;
 
     uint32_t nvec = len >> 4;
     const uint4 *v = reinterpret_cast<const uint4 *>(in);
@@ -233,6 +236,7 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < ncell; i += 256) {
             uint32_t c = cells[i];
+            for (uint32_t k = 1; k < ncopy; k++) c += cells[k * ncell + i];
             if (c) atomicAdd(&g[i], c);
         }
     }
@@ -901,7 +905,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         if (n1) {
             uint32_t max1 = desc[s1[0]].in_len;
             LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
-            LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST_CHUNK - 1) / HIST_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
+            LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST1_CHUNK - 1) / HIST1_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
             LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
             ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), hs>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status, dbg)));
         }
