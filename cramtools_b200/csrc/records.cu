@@ -1868,7 +1868,7 @@ __global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
 {
     const uint32_t c = blockIdx.x, lane = threadIdx.x, lt = (1u << lane) - 1u;
     if (c >= a.n_containers) return;
-    __shared__ uint32_t s_nf[32], s_arrq[32], s_arrb[32], s_bad;
+    __shared__ uint32_t s_nf[32], s_cnt[32], s_arrq[32], s_arrb[32], s_q[32], s_i[32], s_bad;
     __shared__ uint64_t s_p[CRAMGPU_S_COUNT], s_pay;
     UnpackCur cu;
 #pragma unroll
@@ -1905,26 +1905,39 @@ __global__ void __launch_bounds__(32) k_unpack(UnpackArgs a)
             const uint32_t nf = bFN;
             uint32_t tot, ex = warp_excl_scan_u32(nf, lane, tot);
             if (live) { a.feat_off[r] = fb + nf_total + ex; a.mapq[r] = (uint8_t)bMQ; }
-            s_nf[lane] = nf; s_arrq[lane] = arrq; s_arrb[lane] = arrb;
+            // where the arrays of the records before this one end (arrays only; the Q / i bytes of features come on top)
+            uint32_t totq, totb;
+            const uint32_t exq = warp_excl_scan_u32(arrq, lane, totq), exb = warp_excl_scan_u32(arrb, lane, totb);
+            s_nf[lane] = ex; s_cnt[lane] = nf; s_arrq[lane] = exq; s_arrb[lane] = exb; s_q[lane] = 0; s_i[lane] = 0;
+            const uint32_t fm = __ballot_sync(0xFFFFFFFFu, nf != 0);
             __syncwarp();
             if (lane == 0) {
                 cu.p[CRAMGPU_S_FN] += nm; cu.p[CRAMGPU_S_MQ] += nm;
-                // records in turn: features (they may take bytes of QS / BA), then the record's arrays
-                uint64_t fi = fb + nf_total;
-                for (uint32_t l = 0; l < 32; l++) {
-                    const uint32_t n = s_nf[l];
-                    if (n) fi += unpack_features(a, cu, n, fi, fb + f_cap, pay);
-                    const uint32_t aq = s_arrq[l], ab = s_arrb[l];
-                    s_arrq[l] = (uint32_t)(cu.p[CRAMGPU_S_QS] - pQS); s_arrb[l] = (uint32_t)(cu.p[CRAMGPU_S_BA] - pBA);   // where its arrays start
-                    cu.p[CRAMGPU_S_QS] += aq; cu.p[CRAMGPU_S_BA] += ab;
+                // only the records that have features are walked, in turn (their features may take bytes of QS / BA)
+                uint32_t qrun = 0, irun = 0;
+                for (uint32_t mk = fm; mk && !cu.bad; mk &= mk - 1) {
+                    const uint32_t l = (uint32_t)__ffs(mk) - 1;
+                    const uint32_t n = s_cnt[l];
+                    const uint64_t q0 = pQS + s_arrq[l] + qrun, b0 = pBA + s_arrb[l] + irun;
+                    cu.p[CRAMGPU_S_QS] = q0; cu.p[CRAMGPU_S_BA] = b0;
+                    unpack_features(a, cu, n, fb + nf_total + s_nf[l], fb + f_cap, pay);
+                    const uint32_t q = (uint32_t)(cu.p[CRAMGPU_S_QS] - q0), i = (uint32_t)(cu.p[CRAMGPU_S_BA] - b0);
+                    s_q[l] = q; s_i[l] = i; qrun += q; irun += i;
                 }
+                cu.p[CRAMGPU_S_QS] = pQS + totq + qrun; cu.p[CRAMGPU_S_BA] = pBA + totb + irun;
                 if (cu.p[CRAMGPU_S_QS] > cu.e[CRAMGPU_S_QS] || cu.p[CRAMGPU_S_BA] > cu.e[CRAMGPU_S_BA]) cu.bad |= 1;
                 s_pay = pay; s_bad = (uint32_t)cu.bad;
             }
             __syncwarp();
-            if (live) {
-                a.read_qs_off[r] = (fl & CRAMGPU_NF_FORCE_QS) ? pQS + s_arrq[lane] : ~0ull;
-                a.read_ba_off[r] = (!mapped && !(fl & CRAMGPU_NF_UNKNOWN_BASES)) ? pBA + s_arrb[lane] : ~0ull;
+            {
+                // a record's arrays start after the arrays of the records before it and after every feature byte up to its own
+                uint32_t tq, ti;
+                const uint32_t q = s_q[lane], i = s_i[lane];
+                const uint32_t qi = warp_excl_scan_u32(q, lane, tq) + q, ii = warp_excl_scan_u32(i, lane, ti) + i;
+                if (live) {
+                    a.read_qs_off[r] = (fl & CRAMGPU_NF_FORCE_QS) ? pQS + exq + qi : ~0ull;
+                    a.read_ba_off[r] = (!mapped && !(fl & CRAMGPU_NF_UNKNOWN_BASES)) ? pBA + exb + ii : ~0ull;
+                }
             }
             nf_total += tot; pay = s_pay;
             if (s_bad) break;
