@@ -18,9 +18,10 @@
 // so it uses a compact form instead (232 B per context, blocks with <= 48 distinct bytes): a 128-entry table
 // slot >> 5 -> first candidate symbol rank, plus the cumulative frequencies of the ranks; the symbol is the
 // candidate advanced by the number of range ends <= slot among the next three (a loop finishes the rare longer
-// runs).  One profile-driven rule shaped the kernel: a warp alone on its SM issues one dependent instruction every
-// ~4 cycles, so the step was cut from 135 to ~65 instructions (profiles/r1_k_dec1_v2_mix.txt).  The compressed
-// stream is staged through a per-group byte ring in shared memory by cp.async.
+// runs, out of line).  Profiles shaped the kernel (profiles/r1_k_dec1_v*.txt): a warp alone on its SM sub-partition
+// issues one dependent instruction every ~4-5 cycles, so the decoder warp keeps only the recurrence (48 instructions per
+// step, a chain of 13 ALU operations and 2 shared-memory loads) and a helper warp per CTA stages the compressed stream
+// (cp.async into a byte ring per group) and writes the output (aligned 16-byte stores); see k_dec1.
 #include "internal.cuh"
 
 #define DEC_MAXU 48          // alphabet limit of the shared-memory order-1 path

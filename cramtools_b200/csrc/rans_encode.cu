@@ -419,14 +419,14 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
 //                     words themselves arrive two chunks ahead by cp.async.  rcp_freq comes from a 4096-entry table
 //                     built in shared memory when the CTA starts.
 //   1 CODER warp      lane = state: 32 dependent steps of chunk I-1; nothing but the recurrence of
-//                     RansEncPutSymbol [Encoding.java:46-71], ~20 instructions per step, no global memory.  It sits
-//                     shares its SM sub-partition with one producer only.
-//   2 EMITTER warps (4 blocks each)  chunk I-2: positions of the renormalisation bytes (lanes emit in the order 3,2,1,0
+//                     RansEncPutSymbol [Encoding.java:46-71], ~25 instructions per step, no global memory.  It shares
+//                     its SM sub-partition with one producer and one emitter.
+//   3 EMITTER warps (3, 3 and 2 blocks)  chunk I-2: positions of the renormalisation bytes (lanes emit in the order 3,2,1,0
 //                     within a step, [E04.java:41-44]) by a prefix sum over the steps; bytes stored downwards from the
 //                     end of the block's work area == the reversed buffer of [rans/Utils.java:7-33]
 //
 // Why: a warp alone on an SM issues one dependent instruction every ~4 cycles and a sub-partition sustains ~0.6 IPC on
-// this code (ncu: profiles/r1_k_enc1_v2_hotloop.txt, profiles/r1_k_enc_v3_roles.txt), so the states' recurrence is kept
+// this code (ncu: profiles/r1_k_enc1_v2_hotloop.txt, profiles/r1_k_enc_v6_roles.txt), so the states' recurrence is kept
 // as short as possible and everything that does not depend on the state runs beside it on other warps.
 // A step in which a state has no symbol (tails, shorter blocks of the CTA) gets freq = 4096: x_max = 2^31 (never
 // renormalises), cmpl_freq = 0, bias = 0 -- the recurrence maps x to x without any special case.
