@@ -80,6 +80,7 @@ struct cramgpu_ctx {
     cudaStream_t hp_stream = nullptr;
     cudaEvent_t hp_in = nullptr, hp_out = nullptr;
     EncodePending pend;
+    bool enc_attr_done = false, dec_attr_done = false;   // per context (= per device): dynamic shared-memory limits of the coder kernels set
     // optional per-kernel timing (cramgpu_profile_*): CUDA events around every launch
     bool profiling = false;
     struct Span { const char *name; cudaEvent_t a, b; };

@@ -755,10 +755,9 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     uint8_t *lut0 = S + o_lut0, *lut1 = S + o_lut1;
     uint32_t *fc0 = (uint32_t *)(S + o_fc0), *fc1 = (uint32_t *)(S + o_fc1);
     DecCompact *compact = (DecCompact *)(S + o_compact);
-    static bool attr_done = false;
-    if (!attr_done) {
+    if (!ctx->dec_attr_done) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_dec1, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC1_SMEM));
-        attr_done = true;
+        ctx->dec_attr_done = true;
     }
     if (n0 + n1) {
         LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, lut1, fc1, compact, meta, d_status));

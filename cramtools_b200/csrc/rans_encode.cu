@@ -887,11 +887,10 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
     uint32_t *syms0 = (uint32_t *)(S + o_syms0), *syms1 = (uint32_t *)(S + o_syms1);
     const int dbg = getenv("CRAMGPU_DBG") ? atoi(getenv("CRAMGPU_DBG")) : 0;   // timing experiments only (wrong output)
-    static bool attr_done = false;
-    if (!attr_done) {
+    if (!ctx->enc_attr_done) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(1)));
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(0)));
-        attr_done = true;
+        ctx->enc_attr_done = true;
     }
     O1Meta *meta = (O1Meta *)(S + o_meta);
     uint32_t *F1 = (uint32_t *)(S + o_F1);
