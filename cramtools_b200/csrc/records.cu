@@ -306,7 +306,9 @@ __global__ void __launch_bounds__(256) k_ref_norm(const uint8_t *__restrict__ re
 #define SIMPLE_MAX_OPS 12
 struct SimpleRead {
     bool live, simple, mapped, forced, walk;      // walk: there is a CIGAR to walk
+    bool pb;                                      // model with base categories and a record they apply to: perbase_read
     uint8_t force, rfl, mapq;
+    uint16_t flag;
     uint32_t rlen, nops;
     int32_t pos;
     uint64_t lo, c0;
@@ -314,7 +316,7 @@ struct SimpleRead {
 __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolSet &ps, uint64_t r, uint32_t c, bool live)
 {
     SimpleRead s;
-    s.live = live; s.simple = false; s.mapped = false; s.forced = false; s.walk = false;
+    s.live = live; s.simple = false; s.mapped = false; s.forced = false; s.walk = false; s.pb = false; s.flag = 0;
     s.force = 0; s.rfl = 0; s.mapq = 0; s.rlen = 0; s.nops = 0; s.pos = 0; s.lo = 0; s.c0 = 0;
     if (!live) return s;
     s.lo = a.read_off[r];
@@ -323,18 +325,21 @@ __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolS
     const uint64_t nops = a.cigar_off[r + 1] - s.c0;
     s.pos = a.pos[r];
     const uint16_t flag = a.flag[r];
+    s.flag = flag;
     s.mapq = a.mapq[r];
     s.rfl = a.rflags ? a.rflags[r] : 0;
     const bool has_quals = !(s.rfl & CRAMGPU_RF_NO_QUALS);
     s.mapped = !(flag & SAM_UNMAPPED);
-    if (ps.per_base || rlen >= (1ull << 31)) return s;
+    if (rlen >= (1ull << 31)) return s;
+    // base categories only matter for records with scores, an alignment start and a CIGAR (QualityScorePreservation :332-340)
+    const bool pb = ps.per_base && has_quals && s.pos != 0 && nops > 0;
     bool qposs = false;
     if (ps.n < 0) s.force = has_quals ? 3 : 0;
     else if (has_quals) {
         bool f = false;
         for (int k = 0; k < ps.n; k++) {
             const cramgpu_qs_policy &p = ps.p[k];
-            if (!read_in_category(p, flag, s.mapq)) continue;
+            if (!read_in_category(p, flag, s.mapq) || p.n_base_cats) continue;        // (with pb the final word is perbase_read's)
             f = p.treatment != 2;
             qposs = qposs || p.treatment != 2;
         }
@@ -342,8 +347,8 @@ __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolS
     }
     s.forced = s.force & 1;
     s.rlen = (uint32_t)rlen;
-    if (!s.mapped || s.pos == 0) { s.simple = true; return s; }
-    if (!s.forced && qposs) return s;                                   // sparse Q features possible
+    if (!s.mapped || s.pos == 0) { s.simple = !pb; return s; }
+    if (!pb && !s.forced && qposs) return s;                            // sparse Q features from read-level policies alone: general walk
     if (nops == 0) { s.simple = true; return s; }
     if (nops > SIMPLE_MAX_OPS || rlen == 0 || s.pos < 0) return s;
     uint64_t nread = 0, nref = 0;
@@ -354,7 +359,7 @@ __device__ __forceinline__ SimpleRead classify_read(const RecArgs &a, const PolS
         if (consumes_ref(op)) nref += len;
     }
     if (nread != rlen || (uint64_t)(s.pos - 1) + nref > a.ref_len[c]) return s;   // odd CIGAR / overhang ('N' fill): general walk
-    s.simple = true; s.walk = true; s.nops = (uint32_t)nops;
+    s.simple = true; s.walk = true; s.nops = (uint32_t)nops; s.pb = pb;
     return s;
 }
 
@@ -370,10 +375,19 @@ __device__ __forceinline__ void rec_list_append(uint64_t *lr, uint32_t *lc, unsi
 
 template <bool WRITE>
 __device__ __forceinline__ uint32_t simple_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c);
+template <bool WRITE>
+__device__ __forceinline__ uint32_t perbase_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c);
+// PB: the model has base categories (a separate instantiation of the kernels, so that the others do not carry its registers)
+template <bool WRITE, bool PB>
+__device__ __forceinline__ uint32_t thread_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c)
+{
+    if (PB && s.pb) return perbase_read<WRITE>(a, ps, s, r, c);
+    return simple_read<WRITE>(a, ps, s, r, c);
+}
 
 // all reads in order; reads with several CIGAR operators are only classified here and done by k_rec_multi, so that the
 // lanes of a warp do the same kind of work
-template <bool WRITE>
+template <bool WRITE, bool PB>
 __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -393,14 +407,14 @@ __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
         rec_list_append(a.clist_r, a.clist_c, a.clist_n, live && !s.simple, r, c, lane);
         rec_list_append(a.tlist_r, a.tlist_c, a.tlist_n, multi, r, c, lane);
         uint32_t nf = 0;
-        if (s.simple && !multi) nf = simple_read<false>(a, ps, s, r, c);
+        if (s.simple && !multi) nf = thread_read<false, PB>(a, ps, s, r, c);
         // the write pass of a read with features is done from a list as well: most reads have none, and a warp of the
         // in-order kernel would otherwise wait for its few that do
         rec_list_append(a.wlist_r, a.wlist_c, a.wlist_n, nf != 0, r, c, lane);
     } else if (s.simple && !multi) {
         const uint32_t here = a.cnt[(size_t)C_NFEAT * a.n_reads + r];
         const uint64_t next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * a.n_reads + r + 1] : a.totals[(size_t)c * NCNT + C_NFEAT];
-        if (next == here) simple_read<true>(a, ps, s, r, c);
+        if (next == here) thread_read<true, PB>(a, ps, s, r, c);
     }
     if (WRITE && ps.n < 0) {
         // lossless: the preserved array is the record's own qualities [Writer.java:250-251,257-258] (multi-operator reads
@@ -415,7 +429,7 @@ __global__ void __launch_bounds__(128) k_rec_simple(RecArgs a, PolSet ps)
     }
 }
 
-template <bool WRITE>
+template <bool WRITE, bool PB>
 __global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps, const uint64_t *__restrict__ lr, const uint32_t *__restrict__ lc,
                                                    const unsigned long long *__restrict__ ln)
 {
@@ -423,8 +437,275 @@ __global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps, const u
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += step) {
         const uint64_t r = lr[i];
         const uint32_t c = lc[i];
-        simple_read<WRITE>(a, ps, classify_read(a, ps, r, c, true), r, c);
+        thread_read<WRITE, PB>(a, ps, classify_read(a, ps, r, c, true), r, c);
     }
+}
+
+// ---- quality models with base categories, one thread per read --------------------------------------
+// The per-base part of QualityScorePreservation.addQualityScores / addQS [:332-489] works on masks over the bases of a
+// record; here a mask is a machine word, one bit per base of a group of up to four bases (the four bytes of an aligned
+// word of the record's bases), and the policies are evaluated with bitwise operations on all bases of the group at once.
+//   match / ins / dm: base equals the RAW reference base at its position / lies in an insertion / is at or right after
+//   the start of one of the last two deletions.
+// mask of one per-base policy over a group (base_mask above, bit-parallel)
+__device__ __forceinline__ uint32_t pb_mask(const cramgpu_qs_policy &p, uint32_t match, uint32_t ins, uint32_t dm)
+{
+    uint32_t m = 0;
+    for (int b = 0; b < p.n_base_cats; b++) {
+        switch (p.base_cat[b]) {
+        case 1: m = match; break;            // MATCH: assignment
+        case 2: m = ~match; break;           // MISMATCH
+        case 3: m |= dm; break;              // FLANKING_DELETION: only sets
+        case 4: m |= ins; break;             // INSERTION: only sets
+        }
+    }
+    return m;
+}
+// score_at above, bit-parallel: `has` = bases that end up with a score, `bin` = those whose score is binned.
+// appl: bit k = policy k applies to the record (its read category)
+__device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint32_t match, uint32_t ins, uint32_t dm, uint32_t &has, uint32_t &bin)
+{
+    has = 0; bin = 0;
+    for (int k = 0; k < ps.n; k++) {
+        if (!((appl >> k) & 1)) continue;
+        const cramgpu_qs_policy &p = ps.p[k];
+        uint32_t hit;
+        if (p.n_base_cats == 0) { if (p.treatment == 2) continue; hit = ~0u; }
+        else hit = pb_mask(p, match, ins, dm);
+        has = (has & ~hit) | (p.treatment != 2 ? hit : 0u);
+        bin = (bin & ~hit) | (p.treatment == 1 ? hit : 0u);
+    }
+}
+// one bit per byte of a word: bit j = byte j of v is non-zero in its low bit (v holds 0x00 / 0xFF per byte)
+__device__ __forceinline__ uint32_t nibble_of(uint32_t v) { return (((v & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
+// bits of the deletion-flank positions d_a, d_a + 1, d_b, d_b + 1 inside the group that starts at read offset z0
+__device__ __forceinline__ uint32_t pb_dm(int32_t z0, int32_t d_a, int32_t d_b)
+{
+    uint32_t m = 0;
+    if (d_a < 0) return 0;
+    int32_t o = d_a - z0; if (o >= 0 && o < 4) m |= 1u << o;
+    o++; if (o >= 0 && o < 4) m |= 1u << o;
+    o = d_b - z0; if (o >= 0 && o < 4 && d_b >= 0) m |= 1u << o;
+    o++; if (o >= 0 && o < 4 && d_b >= 0) m |= 1u << o;
+    return m;
+}
+
+// a group of up to four bases of one read-consuming operator
+struct PbGroup {
+    int32_t z0;          // read offset of bit 0 (negative by up to 3 for the first word of an M segment)
+    int32_t r0;          // reference offset (from the alignment start) that goes with bit 0
+    uint32_t valid;      // bits that are bases of this operator
+    uint32_t match, ins, dm;
+    uint32_t op, len;    // the operator and its length
+    uint32_t rel;        // offset of bit 0 inside the operator (I and S: the base's index)
+    uint32_t av;         // the bases: aligned word (M / = / X) or one byte (I, S)
+};
+// Walks the operators of a record: visit(PbGroup) for the read-consuming ones in groups of up to four bases, other(op, len, z)
+// for the rest (and for an empty soft clip).  M / = / X segments go by aligned words of the bases, I and S base by base
+// (their "reference position" is where the walk stands, [:398-476], and may lie beyond the window).
+template <class V, class O>
+__device__ __forceinline__ void pb_walk(const RecArgs &a, uint64_t lo, uint64_t c0, uint32_t nops, int32_t pos, uint32_t c, V visit, O other)
+{
+    const uint8_t *rb = a.bases + lo;
+    const uint8_t *ref = a.ref + a.ref_off[c];
+    const int64_t ref_len = (int64_t)a.ref_len[c];
+    uint32_t z = 0, aoff = 0;
+    int32_t d_a = -9, d_b = -9;
+    for (uint32_t ci = 0; ci < nops; ci++) {
+        const uint32_t cw = a.cigar[c0 + ci], op = cw & 15, len = cw >> 4;
+        if (op == OP_D) { if (d_a != (int32_t)z) { d_b = d_a; d_a = (int32_t)z; } }
+        PbGroup g;
+        g.op = op; g.len = len;
+        if (!consumes_read(op) || (op == OP_S && len == 0)) other(op, len, z);
+        else if (op == OP_I || op == OP_S) {
+            for (uint32_t i = 0; i < len; i++) {
+                const int64_t rp = (int64_t)pos - 1 + aoff + i;
+                const uint8_t b = rb[z + i], tb = (rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)0;
+                g.z0 = (int32_t)(z + i); g.r0 = (int32_t)(aoff + i); g.valid = 1u; g.match = b == tb ? 1u : 0u; g.ins = op == OP_I ? 1u : 0u;
+                g.dm = pb_dm(g.z0, d_a, d_b) & 1u; g.rel = i; g.av = b;
+                visit(g);
+            }
+        } else if (len) {
+            const uint8_t *A = rb + z;
+            const uint32_t sa = (uint32_t)((uintptr_t)A & 3);
+            const uint32_t *aw = reinterpret_cast<const uint32_t *>(A - sa);
+            const uint8_t *Rs = ref + (int64_t)pos - 1 + aoff;                 // raw reference at the segment's first base (inside the window)
+            const uint32_t nwords = (sa + len + 3) >> 2, tail = (sa + len) & 3;
+            for (uint32_t k = 0; k < nwords; k++) {
+                g.av = aw[k];
+                g.valid = 0xFu;
+                if (k == 0) g.valid &= 0xFu << sa;
+                if (k == nwords - 1 && tail) g.valid &= (1u << tail) - 1u;
+                // the raw reference bytes of the word's valid bases (bytes in front of / behind the segment are not touched)
+                uint32_t rv = 0;
+#pragma unroll
+                for (int j = 0; j < 4; j++)
+                    if ((g.valid >> j) & 1) rv |= (uint32_t)Rs[(int64_t)4 * k + j - sa] << (8 * j);
+                g.z0 = (int32_t)(z + 4 * k) - (int32_t)sa; g.r0 = (int32_t)(aoff + 4 * k) - (int32_t)sa;
+                g.match = nibble_of(__vcmpeq4(g.av, rv)) & g.valid; g.ins = 0; g.dm = pb_dm(g.z0, d_a, d_b); g.rel = 4 * k - sa;
+                visit(g);
+            }
+        }
+        if (consumes_read(op)) z += len;
+        if (consumes_ref(op)) aoff += len;
+    }
+}
+
+// force-preserve decision of a record under a model with base categories: the safety latch [:487-488] needs the number of
+// bases every per-base policy masks
+__device__ __forceinline__ uint8_t pb_force(const RecArgs &a, const PolSet &ps, uint64_t lo, uint64_t c0, uint32_t nops, int32_t pos, uint32_t rlen,
+                                            uint32_t c, uint32_t appl)
+{
+    uint32_t masked[MAX_POL];
+#pragma unroll
+    for (int k = 0; k < MAX_POL; k++) masked[k] = 0;
+    pb_walk(a, lo, c0, nops, pos, c,
+            [&](const PbGroup &g) {
+#pragma unroll
+                for (int k = 0; k < MAX_POL; k++)
+                    if (k < ps.n && ps.p[k].n_base_cats) masked[k] += __popc(pb_mask(ps.p[k], g.match, g.ins, g.dm) & g.valid);
+            },
+            [&](uint32_t, uint32_t, uint32_t) {});
+    bool f = false;
+#pragma unroll
+    for (int k = 0; k < MAX_POL; k++) {
+        if (k >= ps.n || !((appl >> k) & 1)) continue;
+        if (ps.p[k].n_base_cats == 0) f = ps.p[k].treatment != 2;                  // BIN / PRESERVE force, DROP clears
+        else if (masked[k] > rlen / 2) f = true;
+    }
+    return (uint8_t)((f ? 1 : 0) | 2);
+}
+
+// A record with quality scores, an alignment start and a regular CIGAR under a model with base categories, by one thread:
+// force decision, features merged with the sparse Q features in position order (a base's own feature first), series
+// bytes.  Same results as walk_read.  -> number of read features
+template <bool WRITE>
+__device__ __forceinline__ uint32_t perbase_read(const RecArgs &a, const PolSet &ps, const SimpleRead &s, const uint64_t r, const uint32_t c)
+{
+    const uint64_t N = a.n_reads;
+    const uint32_t rlen = s.rlen;
+    uint32_t appl = 0;
+    for (int k = 0; k < ps.n; k++) if (read_in_category(ps.p[k], s.flag, s.mapq)) appl |= 1u << k;
+    const uint8_t force = WRITE ? a.force[r] : pb_force(a, ps, s.lo, s.c0, s.nops, s.pos, rlen, c, appl);
+    const bool forced = force & 1, qf = !forced;
+    uint32_t n_feat = 0, n_fp = 0, n_bs = 0, n_dl = 0, n_ba = 0, n_sc = 0, n_qs = 0, n_rs = 0, n_hc = 0, n_pd = 0, n_pay = 0;
+    const uint64_t *B = WRITE ? a.base + (size_t)c * NCNT : nullptr;
+    uint64_t fbase = 0, paybase = 0;
+    uint8_t *sFC = nullptr, *sFP = nullptr, *sBS = nullptr, *sDL = nullptr, *sBA = nullptr, *sSC = nullptr, *sQS = nullptr, *sRS = nullptr,
+            *sHC = nullptr, *sPD = nullptr;
+    const uint8_t *codes = nullptr;
+    uint32_t nf = 0;
+    if (WRITE) {
+        auto at = [&](int k) -> uint64_t { return B[k] + a.cnt[(size_t)k * N + r]; };
+        const uint32_t here = a.cnt[(size_t)C_NFEAT * N + r];
+        const uint64_t next = (r + 1 < a.cont_off[c + 1]) ? (uint64_t)a.cnt[(size_t)C_NFEAT * N + r + 1] : a.totals[(size_t)c * NCNT + C_NFEAT];
+        nf = (uint32_t)(next - here);
+        fbase = B[C_NFEAT] + here;
+        a.feat_off[r] = fbase;
+        a.read_ba_off[r] = ~0ull;
+        itf8_put(a.streams + at(C_FN), nf);
+        itf8_put(a.streams + at(C_MQ), s.mapq);
+        sFC = a.streams + at(C_FC); sFP = a.streams + at(C_FP); sBS = a.streams + at(C_BS); sDL = a.streams + at(C_DL);
+        sBA = a.streams + at(C_BA); sSC = a.streams + at(C_SC); sQS = a.streams + at(C_QS); sRS = a.streams + at(C_RS);
+        sHC = a.streams + at(C_HC); sPD = a.streams + at(C_PD); paybase = at(C_PAYLOAD);
+        codes = a.codes + (size_t)c * 32;
+    }
+    if (!WRITE || nf || s.nops > 1) {
+        const uint8_t *rb = a.bases + s.lo, *rq = a.quals + s.lo;
+        const uint8_t *nref = a.nref + a.ref_off[c] + (uint64_t)(s.pos - 1);
+        int32_t prev = 0;
+        auto feature = [&](uint8_t opc, int32_t fpos, int32_t val, int32_t aux) {
+            const uint32_t d = (uint32_t)(fpos - prev);
+            prev = fpos;
+            if (WRITE) {
+                const uint64_t fi = fbase + n_feat;
+                a.f_op[fi] = opc; a.f_pos[fi] = fpos; a.f_val[fi] = val; a.f_aux[fi] = aux;
+                sFC[n_feat] = opc;
+                itf8_put(sFP + n_fp, d);
+            }
+            n_feat++; n_fp += itf8_len(d);
+        };
+        pb_walk(a, s.lo, s.c0, s.nops, s.pos, c,
+                [&](const PbGroup &g) {
+                    const uint32_t op = g.op, av = g.av, valid = g.valid;
+                    const int32_t z0 = g.z0;
+                    const bool isM = op != OP_I && op != OP_S;
+                    uint32_t fbits = 0, rv = 0;
+                    if (isM) {
+                        // normalised reference bytes of the valid bases: substitutions [:306-330]
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            if ((valid >> j) & 1) rv |= (uint32_t)nref[g.r0 + j] << (8 * j);
+                        fbits = ~nibble_of(__vcmpeq4(av, rv)) & valid;
+                    } else if (op == OP_I) fbits = 1;
+                    else fbits = g.rel == 0 ? 1u : 0u;                            // S: the clip's feature sits at its first base
+                    uint32_t has = 0, bin = 0;
+                    if (qf) { pb_planes(ps, appl, g.match, g.ins, g.dm, has, bin); has &= valid; }
+                    for (uint32_t todo = fbits | has; todo; todo &= todo - 1) {
+                        const uint32_t j = (uint32_t)__ffs(todo) - 1;
+                        const int32_t zi = z0 + (int32_t)j;
+                        if ((fbits >> j) & 1) {
+                            if (isM) {
+                                const uint8_t b = (uint8_t)(av >> (8 * j)), refb = (uint8_t)(rv >> (8 * j));
+                                const int ri = base_index(refb), bi = base_index(b);
+                                uint8_t code = 0;
+                                if (!WRITE) { if (ri >= 0 && bi >= 0) atomicAdd(&a.subst[(size_t)c * 25 + ri * 5 + bi], 1ull); }
+                                else { code = (ri >= 0 && bi >= 0) ? codes[ri * 5 + bi] : 0; sBS[n_bs] = code; }
+                                feature('X', zi + 1, code, (int32_t)b | ((int32_t)refb << 8));
+                                n_bs++;
+                            } else if (op == OP_I) {
+                                const uint8_t b = (uint8_t)av;
+                                if (WRITE) sBA[n_ba] = b;
+                                feature('i', zi + 1, b, 0);
+                                n_ba++;
+                            } else {
+                                // SoftClip(pos, bases[pos .. pos+len)) [:268-272]
+                                const uint32_t len = g.len;
+                                if (WRITE) {
+                                    for (uint32_t i = 0; i < len; i++) { const uint8_t b = rb[zi + i]; sSC[n_sc + i] = b; a.payload[paybase + n_pay + i] = b; }
+                                    sSC[n_sc + len] = '\t';
+                                }
+                                feature('S', zi + 1, (int32_t)(paybase + n_pay), (int32_t)len);
+                                n_sc += len + 1; n_pay += len;
+                            }
+                        }
+                        if ((has >> j) & 1) {
+                            const uint8_t q = rq[zi], sc = ((bin >> j) & 1) ? illumina_bin(q) : q;
+                            if (sc < 128) {                                          // scores[i] > -1 [:290]
+                                if (WRITE) sQS[n_qs] = sc;
+                                feature('Q', zi + 1, sc, 0);
+                                n_qs++;
+                            }
+                        }
+                    }
+                },
+                [&](uint32_t op, uint32_t len, uint32_t z) {
+                    if (op == OP_S) { if (WRITE) sSC[n_sc] = '\t'; n_sc++; return; }       // empty clip: only its terminator
+                    // D, N, H, P: one feature at the next read position [:228-240]
+                    const uint32_t vl = itf8_len(len);
+                    if (WRITE) itf8_put(op == OP_D ? sDL + n_dl : op == OP_N ? sRS + n_rs : op == OP_H ? sHC + n_hc : sPD + n_pd, len);
+                    feature(op == OP_D ? 'D' : op == OP_N ? 'N' : op == OP_H ? 'H' : 'P', (int32_t)z + 1, (int32_t)len, 0);
+                    if (op == OP_D) n_dl += vl; else if (op == OP_N) n_rs += vl; else if (op == OP_H) n_hc += vl; else n_pd += vl;
+                });
+    }
+    if (WRITE) {
+        a.read_qs_off[r] = forced ? (uint64_t)(sQS + n_qs - a.streams) : ~0ull;     // the array itself: k_rec_forced_scores
+    } else {
+        a.force[r] = force;
+        uint32_t *cn = a.cnt + r;
+        cn[C_FN * N] = itf8_len(n_feat); cn[C_MQ * N] = itf8_len(s.mapq);
+        if (forced) n_qs += rlen;
+        if (n_qs) cn[C_QS * N] = n_qs;
+        if (n_feat) { cn[C_FC * N] = n_feat; cn[C_FP * N] = n_fp; cn[C_NFEAT * N] = n_feat; }
+        if (n_bs) cn[C_BS * N] = n_bs;
+        if (n_ba) cn[C_BA * N] = n_ba;
+        if (n_dl) cn[C_DL * N] = n_dl;
+        if (n_sc) { cn[C_SC * N] = n_sc; cn[C_PAYLOAD * N] = n_pay; }
+        if (n_rs) cn[C_RS * N] = n_rs;
+        if (n_hc) cn[C_HC * N] = n_hc;
+        if (n_pd) cn[C_PD * N] = n_pd;
+    }
+    return n_feat;
 }
 
 // -> number of read features
@@ -1455,7 +1736,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
         max_win = std::max(max_win, R->ref_len[c]); sum_win += R->ref_len[c];
     }
     // normalised reference: the windows, or the whole array when the windows add up to more than that
-    if (!ps.per_base) {
+    {
         if (nc <= 65535 && sum_win < R->ref_total)
             LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)((max_win + 31) / 4096 + 1), nc), 256, 0, st>>>(R->ref, S + o_nref, a.ref_off, a.ref_len, 0));
         else
@@ -1465,8 +1746,13 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     const dim3 sgrid = nc <= 65535 ? dim3((uint32_t)((max_reads + 127) / 128), nc) : dim3((uint32_t)((n + 127) / 128), 1);   // thread per read
     const uint32_t wgrid = (uint32_t)std::min<uint64_t>((n + 3) / 4, 148 * 16);
     const uint32_t mgrid = (uint32_t)std::min<uint64_t>((n + 127) / 128, 148 * 8);
-    LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false><<<sgrid, 128, 0, st>>>(a, ps));
-    LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+    if (ps.per_base) {
+        LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false, true><<<sgrid, 128, 0, st>>>(a, ps));
+        LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false, true><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+    } else {
+        LAUNCH(ctx, st, "k_rec_simple_count", k_rec_simple<false, false><<<sgrid, 128, 0, st>>>(a, ps));
+        LAUNCH(ctx, st, "k_rec_multi_count", k_rec_multi<false, false><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+    }
     LAUNCH(ctx, st, "k_rec_walk_count", k_rec_walk<false><<<wgrid, 128, 0, st>>>(a, ps));
     LAUNCH(ctx, st, "k_rec_matrix", k_rec_matrix<<<(nc + 127) / 128, 128, 0, st>>>(a.subst, nc, S + o_codes, S + o_matrix));
     LAUNCH(ctx, st, "k_rec_scan", k_rec_scan<<<dim3(nc, NCNT), 256, 0, st>>>(a.cnt, a.cont_off, n, d_totals));
@@ -1499,9 +1785,15 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     a.f_op = O + q_op; a.f_pos = (int32_t *)(O + q_pos); a.f_val = (int32_t *)(O + q_val); a.f_aux = (int32_t *)(O + q_aux);
     a.feat_off = (uint64_t *)(O + q_foff); a.payload = O + q_pay; a.streams = O + q_str;
     a.read_qs_off = (uint64_t *)(O + q_qso); a.read_ba_off = (uint64_t *)(O + q_bao);
-    LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true><<<sgrid, 128, 0, st>>>(a, ps));
-    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
-    LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true><<<mgrid, 128, 0, st>>>(a, ps, a.wlist_r, a.wlist_c, a.wlist_n));
+    if (ps.per_base) {
+        LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true, true><<<sgrid, 128, 0, st>>>(a, ps));
+        LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true, true><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+        LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true, true><<<mgrid, 128, 0, st>>>(a, ps, a.wlist_r, a.wlist_c, a.wlist_n));
+    } else {
+        LAUNCH(ctx, st, "k_rec_simple_write", k_rec_simple<true, false><<<sgrid, 128, 0, st>>>(a, ps));
+        LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true, false><<<mgrid, 128, 0, st>>>(a, ps, a.tlist_r, a.tlist_c, a.tlist_n));
+        LAUNCH(ctx, st, "k_rec_multi_write", k_rec_multi<true, false><<<mgrid, 128, 0, st>>>(a, ps, a.wlist_r, a.wlist_c, a.wlist_n));
+    }
     LAUNCH(ctx, st, "k_rec_walk_write", k_rec_walk<true><<<wgrid, 128, 0, st>>>(a, ps));
     if (ps.n >= 0 && !ps.per_base) LAUNCH(ctx, st, "k_rec_forced_flat", k_rec_forced_flat<<<sgrid, 128, 0, st>>>(a, ps));
     else if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
