@@ -536,7 +536,19 @@ def run_ours(args):
     top = max(kavg, key=kavg.get)
 
     # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
-    n_e2e = min(n_cont, args.e2e_containers, max(128, 2 * args.e2e_containers // max(world, 2)) if world > 1 else args.e2e_containers)   # page-locked host memory is per rank
+    # every rank page-locks its own buffers (~21 MB per container with four contexts): keep all ranks of the node together
+    # under 40 % of the free host memory
+    n_e2e = min(n_cont, args.e2e_containers)
+    try:
+        import psutil
+        per_rank = 0.4 * psutil.virtual_memory().available / max(world, 1)
+        n_e2e = int(max(128, min(n_e2e, per_rank // (21 << 20))))
+    except Exception:      # noqa: BLE001
+        n_e2e = min(n_e2e, max(128, 2 * args.e2e_containers // max(world, 2))) if world > 1 else n_e2e
+    if world > 1:
+        t_n = torch.tensor([n_e2e], dtype=torch.int64, device=dev)
+        dist.all_reduce(t_n, op=dist.ReduceOp.MIN)
+        n_e2e = int(t_n.item())
     st0 = lanes[0]
     stats = dict(raw_bytes=st0.raw_bytes, comp_bytes=st0.comp_bytes, raw_o0=st0.raw_o0, qs_bytes=st0.qs_bytes, nblk=st0.nblk)
     comp_hint = st0.c_len[:n_e2e * st0.NB].copy()
