@@ -417,3 +417,52 @@ def test_mixed_read_lengths_and_region_edges(R, gpu_ctx):
     for i in range(n):
         o, ln = int(encb.read_qs_off[i]), int(rl[i])
         assert encb.streams[o:o + ln].tobytes() == np.asarray(scoresb[rd['read_off'][i]:rd['read_off'][i + 1]], np.uint8).tobytes(), i
+
+
+@pytest.mark.parametrize('spec', ['*8', 'N40-D8'])
+def test_full_size_containers_lossy_pipeline(R, gpu_ctx, spec):
+    """BASELINE config 4 at the reference's container size (10 000 reads, 1.5 MB of scores per slice): features under a lossy
+    model -> rANS order 1 of the QS series (byte-identical to the oracle) -> decode -> series unpack -> restoration.  Size-
+    independent properties: bases come back bit for bit; under *8 every score comes back as its Illumina bin; under N40-D8
+    a record either keeps all scores that the model keeps (array) or exactly its Q features, and every kept score is
+    the original one or its bin."""
+    from oracle import rans as orans
+    from cramtools_b200 import ExternalCompression as EC
+    ref = synth.reference(140000, 91)
+    rd = synth.reads(ref, 40000, 92, with_names=False)
+    n, nc = len(rd['pos']), 4
+    cont_off = np.arange(nc + 1, dtype=np.uint64) * 10000
+    enc = R.features_encode(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+    KQS = R.SERIES.index('QS')
+    qs_blocks = [enc.series(c, 'QS') for c in range(nc)]
+    comp = EC.rans_batch(qs_blocks, [1] * nc, gpu_ctx)
+    for c in range(nc):
+        assert comp[c] == orans.compress(np.frombuffer(qs_blocks[c], np.uint8), 1), c
+    back = EC.unrans_batch(comp, gpu_ctx)
+    assert back == qs_blocks
+    rfl = (enc.force_qs & 1).astype(np.uint8)
+    up = R.features_unpack(enc.streams, enc.stream_off, enc.stream_len, rd['read_off'], rfl, cont_off=cont_off, ctx=gpu_ctx)
+    assert (up.status == 0).all() and up.n_feat == enc.n_feat
+    bases, quals, star, status = R.normalize_decode(rd['pos'], rd['read_off'], rfl, up, ref, np.zeros(nc, np.int64), enc.matrix,
+                                                    cont_off=cont_off, qs=enc.streams, read_qs_off=up.read_qs_off, ba=enc.streams,
+                                                    read_ba_off=up.read_ba_off, ctx=gpu_ctx)
+    assert (status == 0).all()
+    assert (bases == rd['bases']).all()
+    binned = np.array([q if q < 2 else 6 if q < 10 else 15 if q < 20 else 22 if q < 25 else 27 if q < 30 else 33 if q < 35 else 37 if q < 40 else 40
+                       for q in range(256)], np.uint8)            # Binning.Illumina_binning_matrix [Binning.java:63-71]
+    q_in = np.asarray(rd['quals'], np.uint8)
+    if spec == '*8':
+        assert (rfl == 1).all() and (star == 0).all()
+        assert (quals == binned[q_in]).all()
+    else:
+        dflt = ord('?') - ord('!')
+        ok = (quals == q_in) | (quals == binned[q_in]) | (quals == dflt)
+        assert ok.all()
+        # a record without a stored array has exactly its Q features' positions set, everything else the default score
+        fo = up.feat_off.astype(np.int64)
+        isq = up.f_op == ord('Q')
+        nq = np.add.reduceat(np.concatenate([isq, [False]]).astype(np.int64), np.minimum(fo[:-1], isq.size)) * (fo[1:] > fo[:-1])
+        ro = np.asarray(rd['read_off'], np.int64)
+        notd = np.add.reduceat((quals != dflt).astype(np.int64), ro[:-1])
+        unforced = rfl == 0
+        assert (notd[unforced] <= nq[unforced]).all()
