@@ -198,3 +198,15 @@ def test_fuzz_skewed_alphabets_against_oracle(gpu_ctx):
         back = EC.unrans_batch(got, gpu_ctx)
         for i, (b, g) in enumerate(zip(blocks, back)):
             assert g == b.tobytes(), (order, i)
+
+
+def test_eight_megabyte_blocks(gpu_ctx):
+    """the top of BASELINE config[1]'s sweep: 8 MB blocks of the three stream kinds, both orders, byte-identical to the oracle"""
+    from cramtools_b200 import ExternalCompression as EC, synth
+    from oracle import rans as orans
+    blocks = [synth.qs_stream(8 << 20, 301), synth.ba_stream(8 << 20, 302), synth.rn_stream((8 << 20) - 3, 303)]
+    for order in (0, 1):
+        got = EC.rans_batch(blocks, [order] * 3, gpu_ctx)
+        for b, g in zip(blocks, got):
+            assert g == orans.compress(b, order)
+        assert EC.unrans_batch(got, gpu_ctx) == [b.tobytes() for b in blocks]
