@@ -214,114 +214,12 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
 }
 
 // ---- the compressed stream of a group, staged in shared memory -----------------------------------------
-// Byte ring of DEC_RINGB bytes per group, addressed by the byte offset inside the block (16-byte aligned), filled
-// by 4-byte cp.async.
-#define DEC_RINGB 512
+// Byte ring per group (DEC1_RINGB bytes), addressed by the byte offset inside the block, filled by 4-byte cp.async.
 struct Stream {
     const uint8_t *base;      // block start in global memory
     uint32_t len4;            // block length rounded up to 4
     uint32_t wfetch;          // first word not yet requested
 };
-
-__device__ __forceinline__ void stream_fetch(Stream &s, uint8_t *ring, uint32_t k, uint32_t cur)
-{
-    // A chunk consumes at most DEC_CHUNK * 8 bytes = 32 words; what is requested now is only waited for at the
-    // start of the NEXT chunk, so stay 72 words ahead of the cursor (ring = 128 words).
-    uint32_t tgt = ((cur >> 2) + 72 + 3) & ~3u;
-    uint32_t lim = s.len4 >> 2;
-    for (uint32_t w = s.wfetch + k; w < tgt; w += 4)       // the 4 lanes cover [wfetch, tgt) in strides of 4
-        if (w < lim) cp_async4(ring + ((4 * w) & (DEC_RINGB - 1)), s.base + 4ull * w);
-    if (tgt > s.wfetch) s.wfetch = tgt;
-}
-__device__ __forceinline__ uint32_t ring_le32(const uint8_t *ring, uint32_t pos)
-{
-    return ring[pos & (DEC_RINGB - 1)] | (ring[(pos + 1) & (DEC_RINGB - 1)] << 8) | (ring[(pos + 2) & (DEC_RINGB - 1)] << 16) |
-           ((uint32_t)ring[(pos + 3) & (DEC_RINGB - 1)] << 24);
-}
-
-// Renormalise the 4 states of every group from the group's cursor, lanes in the order 0,1,2,3
-// [Decoding.java:84-90].  lm / gm: ballot masks of the lower lanes of the group / of the group.
-__device__ __forceinline__ uint32_t renorm_ring(uint32_t x, bool act, const uint8_t *ring, uint32_t &cur, uint32_t lm, uint32_t gm)
-{
-    bool n1 = act && x < RANS_L;
-    bool n2 = act && x < (1u << 15);       // after one byte still below 2^23 -> a second byte
-    uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1), b2 = __ballot_sync(0xFFFFFFFFu, n2);
-    uint32_t at = cur + __popc(b1 & lm) + __popc(b2 & lm);
-    uint32_t v0 = ring[at & (DEC_RINGB - 1)], v1 = ring[(at + 1) & (DEC_RINGB - 1)];
-    uint32_t x1 = (x << 8) | v0;
-    x = n2 ? ((x1 << 8) | v1) : (n1 ? x1 : x);
-    cur += __popc(b1 & gm) + __popc(b2 & gm);
-    return x;
-}
-
-// k_dec0: 1 warp per CTA, 8 blocks per warp; tables in shared memory.
-__global__ void __launch_bounds__(32) k_dec0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
-                                             uint32_t nslots, const uint8_t *__restrict__ d_in,
-                                             const uint8_t *__restrict__ lut0, const uint32_t *__restrict__ fc0,
-                                             const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
-                                             int32_t *__restrict__ status)
-{
-    __shared__ __align__(16) uint8_t s_lut[8][4096];
-    __shared__ uint32_t s_fc[8][256];
-    __shared__ __align__(16) uint8_t s_ring[8][DEC_RINGB];
-    uint32_t lane = threadIdx.x, k = lane & 3u, g = lane >> 2;
-    uint32_t slot = blockIdx.x * 8 + g;
-    bool have = slot < nslots;
-    uint32_t blk = have ? slots[slot] : 0;
-    BlockDesc d = desc[blk];
-    have = have && status[blk] == 0;
-    uint32_t n = have ? d.out_len : 0;
-    uint8_t *out = d_out + d.out_off;
-
-    for (uint32_t gg = 0; gg < 8; gg++) {
-        uint32_t b = __shfl_sync(0xFFFFFFFFu, blk, gg * 4);
-        const uint4 *src = reinterpret_cast<const uint4 *>(lut0 + (size_t)b * 4096);
-        uint4 *dst = reinterpret_cast<uint4 *>(s_lut[gg]);
-        for (uint32_t i = lane; i < 256; i += 32) dst[i] = __ldg(src + i);
-        for (uint32_t i = lane; i < 256; i += 32) s_fc[gg][i] = __ldg(fc0 + (size_t)b * 256 + i);
-    }
-    Stream st;
-    st.base = d_in + d.in_off;
-    st.len4 = have ? (d.in_len + 3) & ~3u : 0;
-    uint32_t cur = have ? meta[blk].pay_off : 0;
-    st.wfetch = (cur >> 2) & ~3u;
-    uint8_t *ring = s_ring[g];
-    stream_fetch(st, ring, k, cur);
-    cp_async_commit();
-    cp_async_wait_all();
-    __syncwarp();
-    uint32_t x = ring_le32(ring, cur + 4 * k);
-    cur += 16;
-    bool under = false;
-    const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
-
-    uint32_t steps = n >> 2;
-    uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
-    const uint8_t *lut = s_lut[g];
-    const uint32_t *fc = s_fc[g];
-    for (uint32_t t0 = 0; t0 < max_steps; t0 += DEC_CHUNK) {
-        cp_async_wait_all();
-        __syncwarp();
-        stream_fetch(st, ring, k, cur);
-        cp_async_commit();
-#pragma unroll 4
-        for (uint32_t u = 0; u < DEC_CHUNK; u++) {
-            uint32_t t = t0 + u;
-            bool act = t < steps;
-            if (act) {
-                uint32_t m = x & (TOTFREQ - 1);
-                uint32_t s = lut[m];
-                uint32_t e = fc[s];
-                out[(uint64_t)t * 4 + k] = (uint8_t)s;
-                x = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFF);                 // [Decoding.java:35-48]
-            }
-            x = renorm_ring(x, act, ring, cur, lm, gm);
-        }
-        if (cur > d.in_len) under = true;
-    }
-    if (have && k < (n & 3u)) out[(uint64_t)steps * 4 + k] = lut[x & (TOTFREQ - 1)];   // tail [D04.java:60-83]
-    if (have && (under || cur > d.in_len)) status[blk] = CRAMGPU_ERR_CORRUPT;
-}
 
 // k_dec1: lane k decodes the quarter starting at k*(n>>2); lane 3 also the remainder [D14.java:62-68].
 // Shared-memory path for blocks with <= DEC_MAXU distinct bytes.  Two warps per CTA:
@@ -379,6 +277,12 @@ __device__ __forceinline__ uint32_t lds_tab_u8(uint32_t saddr)
 {
     uint32_t v;
     asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(saddr));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_tab_u32(uint32_t saddr)
+{
+    uint32_t v;
+    asm("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(saddr));
     return v;
 }
 __device__ __forceinline__ uint32_t lds_tab_u16(uint32_t saddr)
@@ -590,6 +494,166 @@ __global__ void __launch_bounds__(64) k_dec1(const BlockDesc *__restrict__ desc,
     }
 }
 
+// k_dec0: the order-0 decoder in the two-warp form of k_dec1 (decoder warp + helper warp, 8 blocks per CTA).
+// The four states of a block take the bytes 4t + k of the output in turn [D04.java:36-58], so a group's ranks of one
+// step are four consecutive output bytes and the helper writes one contiguous stream per group.
+struct __align__(16) Dec0Smem {
+    uint8_t ring[8][DEC1_RINGB];                         // compressed bytes, per group (ring-size aligned)
+    uint8_t outr[DEC1_SLOTS][DEC1_CH][32];               // decoded bytes: [chunk slot][step][decoder lane]
+    uint8_t lut[8][4096];                                // slot -> symbol
+    uint32_t fc[8][256];                                 // symbol -> freq << 16 | start
+    uint32_t cur[8];
+    int32_t ready, done;
+};
+#define DEC0_SMEM (sizeof(Dec0Smem) + DEC1_RINGB)
+
+__global__ void __launch_bounds__(64) k_dec0(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
+                                              uint32_t nslots, const uint8_t *__restrict__ d_in,
+                                              const uint8_t *__restrict__ lut0, const uint32_t *__restrict__ fc0,
+                                              const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out,
+                                              int32_t *__restrict__ status)
+{
+    extern __shared__ uint8_t smem_raw[];
+    Dec0Smem &S = *reinterpret_cast<Dec0Smem *>(smem_raw + ((DEC1_RINGB - ((uint32_t)__cvta_generic_to_shared(smem_raw) & (DEC1_RINGB - 1))) & (DEC1_RINGB - 1)));
+    const uint32_t lane = threadIdx.x & 31, k = lane & 3u, g = lane >> 2;
+    const bool helper = __reduce_max_sync(0xFFFFFFFFu, threadIdx.x >> 5) != 0;       // warp-uniform role (see k_dec1)
+    const uint32_t slot = blockIdx.x * 8 + g;
+    bool have = slot < nslots;
+    const uint32_t blk = have ? slots[slot] : 0;
+    const BlockDesc d = desc[blk];
+    have = have && status[blk] == 0;
+    if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;
+    const uint32_t n = have ? d.out_len : 0;
+    const uint32_t steps = n >> 2;                                     // whole steps; the last n & 3 bytes come from the final states
+    uint8_t *out = d_out + d.out_off;
+    const uint32_t max_steps = __reduce_max_sync(0xFFFFFFFFu, steps);
+    const int32_t nchunks = (int32_t)((max_steps + DEC1_CH - 1) / DEC1_CH);
+
+    for (uint32_t gg = 0; gg < 8; gg++) {
+        const uint32_t hv = __shfl_sync(0xFFFFFFFFu, (uint32_t)have, gg * 4);
+        const uint32_t b = __shfl_sync(0xFFFFFFFFu, blk, gg * 4);
+        if (!hv) {
+            // no block in this group: its lanes idle on a table that maps every slot to symbol 0 with frequency 4096
+            for (uint32_t i = threadIdx.x; i < 1024; i += 64) reinterpret_cast<uint32_t *>(S.lut[gg])[i] = 0;
+            for (uint32_t i = threadIdx.x; i < 256; i += 64) S.fc[gg][i] = 4096u << 16;
+            continue;
+        }
+        const uint4 *src = reinterpret_cast<const uint4 *>(lut0 + (size_t)b * 4096);
+        uint4 *dst = reinterpret_cast<uint4 *>(S.lut[gg]);
+        for (uint32_t i = threadIdx.x; i < 256; i += 64) dst[i] = __ldg(src + i);
+        for (uint32_t i = threadIdx.x; i < 256; i += 64) S.fc[gg][i] = __ldg(fc0 + (size_t)b * 256 + i);
+    }
+    if (threadIdx.x == 0) { S.ready = -1; S.done = -1; }
+    Stream st;
+    st.base = d_in + d.in_off;
+    st.len4 = have ? (d.in_len + 3) & ~3u : 0;
+    const uint32_t cur0 = have ? meta[blk].pay_off : 0;
+    st.wfetch = cur0 >> 2;
+    uint8_t *ring = S.ring[g];
+    if (helper) {
+        const uint32_t tgt = (cur0 + DEC1_RINGB) >> 2, lim = st.len4 >> 2;
+        for (uint32_t w = st.wfetch + k; w < tgt; w += 4)
+            if (w < lim) cp_async4(ring + ((4 * w) & (DEC1_RINGB - 1)), st.base + 4ull * w);
+        st.wfetch = tgt;
+        cp_async_commit();
+        cp_async_wait_all();
+    }
+    __syncthreads();
+
+    if (!helper) {
+        // ------------------------------------------------------------------------------ decoder warp
+        uint32_t x = ring[(cur0 + 4 * k) & (DEC1_RINGB - 1)] | (ring[(cur0 + 4 * k + 1) & (DEC1_RINGB - 1)] << 8) |
+                     (ring[(cur0 + 4 * k + 2) & (DEC1_RINGB - 1)] << 16) | ((uint32_t)ring[(cur0 + 4 * k + 3) & (DEC1_RINGB - 1)] << 24);
+        uint32_t cur = cur0 + 16;
+        const uint32_t rb = (uint32_t)__cvta_generic_to_shared(ring);
+        uint32_t Wc = __funnelshift_r(lds_u32(rb | (cur & (DEC1_RINGB - 4))), lds_u32(rb | ((cur + 4) & (DEC1_RINGB - 4))), cur << 3);
+        const uint32_t gm = 0xFu << (lane & ~3u), lm = ((1u << k) - 1u) << (lane & ~3u);
+        const uint32_t lutb = (uint32_t)__cvta_generic_to_shared(&S.lut[g][0]), fcb = (uint32_t)__cvta_generic_to_shared(&S.fc[g][0]);
+        for (int32_t c = 0; c < nchunks; c++) {
+            if (c >= 2) while (ld_acquire_s32(&S.done) < c - 2) {}
+            uint8_t *orow = &S.outr[c & (DEC1_SLOTS - 1)][0][lane];
+            const uint32_t t0 = (uint32_t)c * DEC1_CH;
+            uint32_t rem = steps > t0 ? steps - t0 : 0;
+            for (uint32_t uo = 0; uo < DEC1_CH; uo += 8, rem = rem > 8 ? rem - 8 : 0, orow += 8 * 32) {
+#pragma unroll
+                for (uint32_t u = 0; u < 8; u++) {
+                    const bool act = u < rem;
+                    const uint32_t xold = x;
+                    const uint32_t m = x & (TOTFREQ - 1);
+                    const uint32_t s = lds_tab_u8(lutb + m);
+                    const uint32_t e = lds_tab_u32(fcb + 4 * s);
+                    orow[u * 32] = (uint8_t)s;
+                    const uint32_t xn = (e >> 16) * (x >> TF_SHIFT) + m - (e & 0xFFFFu);      // [Decoding.java:35-48]
+                    const bool n1 = act && xn < RANS_L;
+                    const bool n2 = act && xn < (1u << 15);
+                    const uint32_t b1 = __ballot_sync(0xFFFFFFFFu, n1);
+                    x = prmt_raw(xn, Wc, (n1 ? 0x2104u : 0x3210u) + __popc(b1 & (n1 ? lm : 0u)));
+                    if (__builtin_expect(__any_sync(0xFFFFFFFFu, n2), 0)) {
+                        const uint64_t two = dec1_renorm2(xn, n1, n2, b1, cur, lm, gm, rb);
+                        x = (uint32_t)two; cur = (uint32_t)(two >> 32);
+                    } else {
+                        cur += __popc(b1 & gm);
+                    }
+                    x = act ? x : xold;                                     // a finished block keeps its final states: they give the tail bytes
+                    Wc = __funnelshift_r(lds_u32(rb | (cur & (DEC1_RINGB - 4))), lds_u32(rb | ((cur + 4) & (DEC1_RINGB - 4))), cur << 3);
+                }
+            }
+            if (k == 0) S.cur[g] = cur;
+            __syncwarp();
+            if (lane == 0) st_release_s32(&S.ready, c);
+        }
+        if (have && k < (n & 3u)) out[(uint64_t)steps * 4 + k] = S.lut[g][x & (TOTFREQ - 1)];   // tail [D04.java:60-83]
+        if (have && cur > d.in_len) status[blk] = CRAMGPU_ERR_CORRUPT;
+    } else {
+        // ------------------------------------------------------------------------------ helper warp
+        // output: the group's bytes [0, 4 * steps) are one stream; lane k of the group writes the k-th quarter of every
+        // chunk's 128 bytes, shifted so that its stores are aligned 16-byte granules
+        const uint32_t nbytes = steps * 4;
+        const uint32_t ph = (uint32_t)((uintptr_t)out & 15);
+        const uint8_t *oring = &S.outr[0][0][4 * g];
+        const uint32_t lim = st.len4 >> 2;
+        for (int32_t c = 0; c <= nchunks; c++) {
+            if (c < nchunks) {
+                while (ld_acquire_s32(&S.ready) < c) __nanosleep(100);
+                const uint32_t tgt = (S.cur[g] + DEC1_RINGB) >> 2;
+                for (uint32_t w = st.wfetch + k; w < tgt; w += 4)
+                    if (w < lim) cp_async4(ring + ((4 * w) & (DEC1_RINGB - 1)), st.base + 4ull * w);
+                if (tgt > st.wfetch) st.wfetch = tgt;
+                cp_async_commit();
+            }
+            // stream bytes [128 c - ph, 128 c + 128 - ph): 8 granules, two per lane of the group
+            const int64_t tb = (int64_t)c * (4 * DEC1_CH) - ph + 32 * (int64_t)k;
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int64_t p0 = tb + 16 * j;
+                if (p0 + 16 <= 0 || p0 >= (int64_t)nbytes) continue;
+                uint32_t w[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int i = 0; i < 16; i++) {
+                    const int64_t p = p0 + i;
+                    // byte p of the stream = state p & 3 of step p >> 2
+                    const uint32_t stp = (uint32_t)(p >> 2) & (DEC1_SLOTS * DEC1_CH - 1);
+                    const uint32_t b = (p >= 0 && p < (int64_t)nbytes) ? oring[stp * 32 + ((uint32_t)p & 3u)] : 0;
+                    w[i >> 2] |= b << (8 * (i & 3));
+                }
+                if (p0 >= 0 && p0 + 16 <= (int64_t)nbytes) *reinterpret_cast<uint4 *>(out + p0) = make_uint4(w[0], w[1], w[2], w[3]);
+                else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) {
+                        const int64_t p = p0 + i;
+                        if (p >= 0 && p < (int64_t)nbytes) out[p] = (uint8_t)(w[i >> 2] >> (8 * (i & 3)));
+                    }
+                }
+            }
+            if (c < nchunks) {
+                cp_async_wait_all();
+                __syncwarp();
+                if (lane == 0) st_release_s32(&S.done, c);
+            }
+        }
+    }
+}
+
 __device__ __forceinline__ uint32_t ld_byte(const uint8_t *p, uint32_t pos, uint32_t len, bool &under)
 {
     if (pos >= len) { under = true; return 0; }
@@ -757,6 +821,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     DecCompact *compact = (DecCompact *)(S + o_compact);
     if (!ctx->dec_attr_done) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_dec1, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC1_SMEM));
+        CUDA_TRY(ctx, cudaFuncSetAttribute(k_dec0, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC0_SMEM));
         ctx->dec_attr_done = true;
     }
     if (n0 + n1) {
@@ -766,7 +831,7 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
             LAUNCH(ctx, st, "k_dec1_big", k_dec1_big<<<(n1 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s1), n1, d_in, lut1, fc1, meta, d_out, d_status));
         }
         if (n0) {
-            LAUNCH(ctx, st, "k_dec0", k_dec0<<<(n0 + 7) / 8, 32, 0, st>>>(dd, (const uint32_t *)(S + o_s0), n0, d_in, lut0, fc0, meta, d_out, d_status));
+            LAUNCH(ctx, st, "k_dec0", k_dec0<<<(n0 + 7) / 8, 64, DEC0_SMEM, st>>>(dd, (const uint32_t *)(S + o_s0), n0, d_in, lut0, fc0, meta, d_out, d_status));
         }
     }
     CUDA_TRY(ctx, cudaGetLastError());
