@@ -426,12 +426,12 @@ class Lane(object):
             sa[:] = np.uint64(F.streams) + self.soff; sa[:, self.KQS] = keepq; sa[:, self.KBA] = keepb
             ctx.check(ctx.lib.cramgpu_features_unpack_dev(ctx.handle, C.byref(self.SR), C.byref(U), C.byref(self.d_mapq),
                                                           self.u_status.ctypes.data_as(i32p), self._sp()))
-            N.feat_off = U.feat_off; N.f_op = U.f_op; N.f_pos = U.f_pos; N.f_val = U.f_val; N.f_aux = U.f_aux; N.payload = U.payload
+            N.feat_off = U.feat_off; N.f_op = U.f_op; N.f_pos = U.f_pos; N.f_val = U.f_val; N.f_aux = U.f_aux; N.payload = U.payload; N.payload_len = U.payload_len
             N.qs = None; N.read_qs_off = U.read_qs_off; N.ba = None; N.read_ba_off = U.read_ba_off      # absolute addresses
             N.matrix = F.matrix
         else:
             N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
-            N.payload = F.payload
+            N.payload = F.payload; N.payload_len = F.payload_len
         ctx.check(ctx.lib.cramgpu_normalize_decode_dev(ctx.handle, C.byref(N), vp(self.o_bases.data_ptr()), vp(self.o_quals.data_ptr()),
                                                        vp(self.o_star.data_ptr()), vp(self.o_stat.data_ptr()), self._sp()))
 
@@ -712,7 +712,7 @@ class E2EContext(object):
                out=self.rq_new.view(np.int64).reshape(inp['n_cont'], READS_PER_CONTAINER))
         N.read_qs_off = vp(self.rq_new.ctypes.data)
         N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
-        N.payload = F.payload
+        N.payload = F.payload; N.payload_len = F.payload_len
         t5 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(N), self.o_b.ctypes.data_as(u8p), self.o_q.ctypes.data_as(u8p),
                                                    self.o_s.ctypes.data_as(u8p), self.o_t.ctypes.data_as(i32p)))

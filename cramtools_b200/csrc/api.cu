@@ -221,6 +221,11 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->rec_scratch.p) cudaFree(ctx->rec_scratch.p);
     if (ctx->rec_out.p) cudaFree(ctx->rec_out.p);
     if (ctx->rec_unp.p) cudaFree(ctx->rec_unp.p);
+    if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
+    if (ctx->hs_out.p) cudaFree(ctx->hs_out.p);
+    if (ctx->hs_in.p) cudaFree(ctx->hs_in.p);
+    if (ctx->pin_hs) cudaFreeHost(ctx->pin_hs);
+    if (ctx->pin_hs2) cudaFreeHost(ctx->pin_hs2);
     if (ctx->pin_rec) cudaFreeHost(ctx->pin_rec);
     if (ctx->pin_feat) cudaFreeHost(ctx->pin_feat);
     if (ctx->pin_in) cudaFreeHost(ctx->pin_in);

@@ -69,6 +69,8 @@ struct cramgpu_ctx {
     DevPool dev_in, dev_out;  // device staging of the host entry points
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
     DevPool rec_unp;                // results of cramgpu_features_unpack (its input series may be an encode result in rec_out)
+    DevPool hs_scratch, hs_out, hs_in;   // cramgpu_host_series_pack: tables, result, staged inputs of the host variant
+    void *pin_hs = nullptr, *pin_hs2 = nullptr; size_t pin_hs_cap = 0, pin_hs2_cap = 0;
     void *pin_rec = nullptr; size_t pin_rec_cap = 0;
     void *pin_feat = nullptr; size_t pin_feat_cap = 0;   // host copy of the last cramgpu_features_encode result
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
@@ -107,7 +109,21 @@ void prof_end(cramgpu_ctx *ctx, cudaStream_t st);
         __VA_ARGS__;                            \
         (ctx)->launches++;                      \
         if ((ctx)->profiling) prof_end((ctx), (st)); \
+        LAUNCH_CHECK((st), (name));             \
     } while (0)
+
+// Debug builds (-DCRAMGPU_SYNC_LAUNCHES): wait for every kernel and name the one that faulted.  compute-sanitizer is not
+// available on every pool; this at least says where to look.
+#ifdef CRAMGPU_SYNC_LAUNCHES
+#include <stdio.h>
+#define LAUNCH_CHECK(st, name)                                                                    \
+    do {                                                                                          \
+        cudaError_t le__ = cudaStreamSynchronize(st);                                             \
+        if (le__ != cudaSuccess) fprintf(stderr, "[cramgpu] kernel %s: %s\n", (name), cudaGetErrorString(le__)); \
+    } while (0)
+#else
+#define LAUNCH_CHECK(st, name) do { } while (0)
+#endif
 
 int ctx_fail(cramgpu_ctx *ctx, int code, const char *fmt, ...);
 int ctx_cuda(cramgpu_ctx *ctx, cudaError_t e, const char *what);

@@ -432,7 +432,7 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
 // renormalises), cmpl_freq = 0, bias = 0 -- the recurrence maps x to x without any special case.
 #define EC 32
 #define ENC_TAB_ENTRIES 1792u     // order-1 {freq,start} cells per block kept in shared memory (ctx x sym <= 1792, e.g. 42 x 42)
-#define ENC_THREADS 384
+#define ENC_THREADS 480               // 15 warps: 1 coder, 8 producers, 3 emitters and 3 that only help with the set-up
 #define DR_STRIDE 33              // descriptor ring: uint2 per (state row, step), padded: conflict-free for both sides
 #define OR_STRIDE 36              // byte ring: u32 per (step row, state), padded so the emitter's 16-byte reads spread over the banks
 
@@ -454,7 +454,12 @@ struct EncStream {                // one per state lane of the CTA, in shared me
 };
 
 #define NULL_DESC make_uint2(0u, 4096u << 13)
+#ifdef CRAMGPU_TIMING_EXPERIMENTS
 __device__ unsigned long long g_enc_dbg[16];   // CRAMGPU_DBG bit 4: busy cycles per warp of CTA 0
+#define ENC_DBG(x) x
+#else
+#define ENC_DBG(x)
+#endif
 
 template <int ORDER>
 __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots,
@@ -487,12 +492,16 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
     __shared__ uint32_t s_max_steps;
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    // roles, balanced over the 4 SM sub-partitions (warp w runs on sub-partition w % 4; each sustains ~0.5 IPC here):
-    //   0: coder(0) + producer(4) + emitter(8)   1: emitter(1) + producers(5, 9)
-    //   2: emitter(2) + producers(6, 10)         3: producers(3, 7, 11)
-    const bool is_coder = wid == 0, is_emit = wid == 1 || wid == 2 || wid == 8, is_prod = wid >= 3 && wid != 8;
-    const uint32_t prod_id = wid < 8 ? wid - 3 : wid - 4;                        // 3,4,5,6,7,9,10,11 -> 0..7
-    const uint32_t emit_first = wid == 1 ? 0 : wid == 2 ? 3 : 6, emit_last = wid == 1 ? 3 : wid == 2 ? 6 : 8;
+    // Roles by SM sub-partition (warp w runs on sub-partition w % 4).  The coder's recurrence is the critical path of the
+    // whole kernel and a sub-partition issues in order, one instruction per cycle at best: every instruction another warp
+    // issues there is a cycle the coder may have to wait (ncu, profiles/r1_k_enc_v6_roles.txt: 52 cycles per step alone,
+    // 97 when it shared its sub-partition with a producer and an emitter).  So sub-partition 0 runs the coder and nothing
+    // else -- warps 4, 8 and 12 help with the set-up and leave -- and the 11 helpers share the other three:
+    //   1: emitter(1) + producers(5, 9, 13)    2: emitter(2) + producers(6, 10, 14)    3: emitter(3) + producers(7, 11)
+    const bool is_coder = wid == 0, is_emit = wid >= 1 && wid <= 3, is_prod = wid > 4 && (wid & 3) != 0;
+    const bool is_idle = wid != 0 && (wid & 3) == 0;
+    const uint32_t prod_id = wid - 5 - (wid >> 2) + 1;                            // 5,6,7,9,10,11,13,14 -> 0..7
+    const uint32_t emit_first = wid == 1 ? 0 : wid == 2 ? 3 : 5, emit_last = wid == 1 ? 3 : wid == 2 ? 5 : 8;
 
     // ---- set-up: every warp helps
     if (tid < 32) {
@@ -556,6 +565,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
         }
     }
     __syncthreads();
+    if (is_idle) return;                       // (a warp that has exited no longer takes part in the CTA's barriers)
 
     const uint32_t max_steps = s_max_steps;
     const uint32_t nchunks = (max_steps + EC - 1) / EC;
@@ -611,9 +621,9 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
         cp_async_commit();
     }
 
-    unsigned long long busy = 0, t_start = clock64();
+    ENC_DBG(unsigned long long busy = 0; unsigned long long t_start = clock64();)
     for (uint32_t I = 0; I < nchunks + 2; I++) {
-        unsigned long long t_in = clock64();
+        ENC_DBG(unsigned long long t_in = clock64();)
         if (is_prod) {
             // ================= PRODUCERS: descriptors of chunk I; input words of chunk I+2 on their way
             // one cp.async group per chunk; chunk I was requested two iterations ago, so only it has to have landed
@@ -701,10 +711,10 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
                 }
             }
         }
-        busy += clock64() - t_in;
+        ENC_DBG(busy += clock64() - t_in;)
         __syncthreads();
     }
-    if ((dbg & 16) && blockIdx.x == 0 && lane == 0) { g_enc_dbg[wid] = busy; if (wid == 0) g_enc_dbg[12] = clock64() - t_start; }
+    ENC_DBG(if ((dbg & 16) && blockIdx.x == 0 && lane == 0) { g_enc_dbg[wid] = busy; if (wid == 0) g_enc_dbg[12] = clock64() - t_start; })
     if (is_coder) xfin[lane] = x;
     __syncthreads();
     if (wid == 2) {
@@ -757,7 +767,7 @@ __global__ void __launch_bounds__(1024) k_scan_out(const BlockDesc *__restrict__
         for (uint32_t k = 0; k < w; k++) off += wsum[k];
         off += s - a;
         if (i < nblocks) {
-            if (off + a > out_cap && len) { status[i] = CRAMGPU_ERR_OUT_TOO_SMALL; len = 0; }
+            if (off + len > out_cap && len) { status[i] = CRAMGPU_ERR_OUT_TOO_SMALL; len = 0; }      // the bytes themselves must fit; the rounding only places the next block
             out_off[i] = off;
             out_len[i] = len;
         }
@@ -801,7 +811,9 @@ __global__ void __launch_bounds__(256) k_pack(const BlockDesc *__restrict__ desc
 
 uint32_t cramgpu_rans_bound(uint32_t n)
 {
-    return (uint32_t)(int)(1.05 * (double)n + 257 * 257 * 3 + 4);
+    // (int)(1.05 * n + 257*257*3 + 4) with Java's saturating double -> int conversion
+    const double b = 1.05 * (double)n + 257 * 257 * 3 + 4;
+    return b >= 2147483647.0 ? 0x7FFFFFFFu : (uint32_t)(int64_t)b;
 }
 
 #include <algorithm>
@@ -886,7 +898,11 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     const BlockDesc *dd = (const BlockDesc *)(S + o_desc);
     uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
     uint32_t *syms0 = (uint32_t *)(S + o_syms0), *syms1 = (uint32_t *)(S + o_syms1);
-    const int dbg = getenv("CRAMGPU_DBG") ? atoi(getenv("CRAMGPU_DBG")) : 0;   // timing experiments only (wrong output)
+#ifdef CRAMGPU_TIMING_EXPERIMENTS
+    const int dbg = getenv("CRAMGPU_DBG") ? atoi(getenv("CRAMGPU_DBG")) : 0;   // role-by-role timing (scripts/time_enc.py): wrong output, never in a shipped build
+#else
+    const int dbg = 0;
+#endif
     if (!ctx->enc_attr_done) {
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(1)));
         CUDA_TRY(ctx, cudaFuncSetAttribute(k_enc<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, ENC_SMEM(0)));
@@ -914,6 +930,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         }
     }
     LAUNCH(ctx, st, "k_scan_out", k_scan_out<<<1, 1024, 0, st>>>(dd, nblocks, tlen, plen, out_cap, d_out_off, d_out_len, d_status));
+#ifdef CRAMGPU_TIMING_EXPERIMENTS
     if (dbg & 16) {
         unsigned long long h[16];
         cudaStreamSynchronize(st);
@@ -922,6 +939,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         for (int w = 0; w < 12; w++) fprintf(stderr, " %llu", h[w]);
         fprintf(stderr, "\n");
     }
+#endif
     CUDA_TRY(ctx, cudaGetLastError());
     ctx->pend = EncodePending{dd, work, tlen, plen, d_out_off, d_out_len, nblocks,
                               (n0 + n1) ? 9 + (uint64_t)(n1 ? O1_TAB_CAP : O0_TAB_CAP) + max_len + max_len / 4 + 80 : 0};

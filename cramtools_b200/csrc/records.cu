@@ -1353,6 +1353,7 @@ struct NormArgs {
     uint64_t *clist_r; uint32_t *clist_c; unsigned long long *clist_n;            // records left to k_norm
     const uint8_t *nref;                                                         // normalizeBase(ref[i]) over the regions, same offsets as ref
     uint64_t ref_total;
+    uint64_t payload_len;                                                        // bytes in payload (soft-clip / insertion offsets are checked against it)
 };
 
 // base with rank `code` for normalised reference base r: SubstitutionMatrix(byte[]) / base() [:59-..,177]
@@ -1505,30 +1506,31 @@ __global__ void __launch_bounds__(128) k_norm(NormArgs a)
                     const uint8_t op = a.f_op[f];
                     const int64_t cnt = fpos - pir;            // reference bases up to the feature (:365-373)
                     if (cnt > 0) {
-                        if (al0 + pis - off0 < 0 || fpos - 1 > rlen) { bad = 1; break; }
+                        if (al0 + pis - off0 < 0 || fpos - 1 > rlen || pir < 1) { bad = 1; break; }
                         run(pir - 1, al0 + pis - off0, cnt);
                         pir += cnt; pis += cnt;
                     }
                     switch (op) {
                     case 'X': {
                         const int64_t rp = al0 + pis - off0;
-                        if (rp < 0 || pir > rlen) { bad = 1; break; }
+                        if (rp < 0 || pir > rlen || pir < 1) { bad = 1; break; }
                         const uint8_t refb = rp >= ref_len ? (uint8_t)'N' : nref[rp];
                         bases[pir - 1] = norm_base(matrix_base(mtx, refb, a.f_val[f]));
                         pir++; pis++;
                         break;
                     }
                     case 'S': case 'I': {
-                        const int64_t ln = a.f_aux[f];
-                        if (pir - 1 + ln > rlen) { bad = 1; break; }
-                        const uint8_t *pay = a.payload + a.f_val[f];
+                        const int64_t ln = a.f_aux[f], po = a.f_val[f];
+                        // Java: ArrayIndexOutOfBoundsException / NegativeArraySizeException on a read or payload overrun
+                        if (ln < 0 || pir < 1 || pir - 1 + ln > rlen || po < 0 || (uint64_t)(po + ln) > a.payload_len) { bad = 1; break; }
+                        const uint8_t *pay = a.payload + po;
                         for (int64_t i = 0; i < ln; i++) bases[pir - 1 + i] = norm_base(pay[i]);
                         pir += ln;
                         break;
                     }
                     case 'D': case 'N': pis += a.f_val[f]; break;
                     case 'i':
-                        if (pir > rlen) { bad = 1; break; }
+                        if (pir > rlen || pir < 1) { bad = 1; break; }
                         bases[pir - 1] = norm_base((uint8_t)a.f_val[f]);
                         pir++;
                         break;
@@ -1542,7 +1544,11 @@ __global__ void __launch_bounds__(128) k_norm(NormArgs a)
                     else if (cnt > 0) run(pir - 1, al0 + pis - off0, cnt);
                     if (!bad)
                         for (uint64_t f = f0; f < f1; f++)          // ReadBase overwrites (:418-427)
-                            if (a.f_op[f] == 'B') bases[a.f_pos[f] - 1] = norm_base((uint8_t)a.f_val[f]);
+                            if (a.f_op[f] == 'B') {
+                                const int64_t fp = a.f_pos[f];
+                                if (fp < 1 || fp > rlen) { bad = 1; break; }       // Java: ArrayIndexOutOfBoundsException
+                                bases[fp - 1] = norm_base((uint8_t)a.f_val[f]);
+                            }
                 }
             }
         }
@@ -1554,8 +1560,11 @@ __global__ void __launch_bounds__(128) k_norm(NormArgs a)
             uint32_t any = 0;
             for (uint64_t f = f0; f < f1; f++) {
                 const uint8_t op = a.f_op[f];
-                if (op == 'Q') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_val[f]; any = 1; }
-                else if (op == 'B') { quals[a.f_pos[f] - 1] = (uint8_t)a.f_aux[f]; any = 1; }
+                if (op != 'Q' && op != 'B') continue;
+                const int64_t fp = a.f_pos[f];
+                if (fp < 1 || fp > rlen) { bad = 1; break; }                       // Java: ArrayIndexOutOfBoundsException (:296-302)
+                quals[fp - 1] = (uint8_t)(op == 'Q' ? a.f_val[f] : a.f_aux[f]);
+                any = 1;
             }
             a.qual_star[r] = any == 0;
         } else if (rlen >= (1ll << 31)) {
@@ -1979,7 +1988,7 @@ static int normalize_impl(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *
         max_win = std::max(max_win, in->win_len[c]); sum_win += in->win_len[c];
     }
     a.clist_r = (uint64_t *)(S + o_clr); a.clist_c = (uint32_t *)(S + o_clc); a.clist_n = (unsigned long long *)(S + o_cln);
-    a.nref = S + o_nref; a.ref_total = in->ref_total;
+    a.nref = S + o_nref; a.ref_total = in->ref_total; a.payload_len = in->payload ? in->payload_len : 0;
     CUDA_TRY(ctx, cudaMemsetAsync(S + o_cln, 0, 16, st));
     if (nc <= 65535 && sum_win < in->ref_total)
         LAUNCH(ctx, st, "k_ref_norm", k_ref_norm<<<dim3((uint32_t)((max_win + 31) / 4096 + 1), nc), 256, 0, st>>>(in->ref, S + o_nref, a.win_off, a.win_len, 0));
@@ -2024,9 +2033,7 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
             if (in->read_qs_off && !qs_dev && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
             if (in->read_ba_off && !ba_dev && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
         }
-    if (!pay_dev)
-        for (uint64_t f = 0; f < nf; f++)
-            if (in->f_op[f] == 'S' || in->f_op[f] == 'I') pay_len = std::max(pay_len, (uint64_t)in->f_val[f] + (uint64_t)in->f_aux[f]);
+    if (!pay_dev) pay_len = in->payload ? in->payload_len : 0;
     size_t i_ref = sg.add(in->ref, in->ref_total), i_mtx = sg.add(in->matrix, 8 * (size_t)nc), i_pos = sg.add(in->pos, 4 * n);
     size_t i_roff = sg.add(in->read_off, 8 * (n + 1)), i_rfl = sg.add(in->rflags, n), i_foff = sg.add(in->feat_off, 8 * (n + 1));
     size_t i_op = sg.add(in->f_op, nf), i_fp = sg.add(in->f_pos, 4 * nf), i_fv = sg.add(in->f_val, 4 * nf), i_fa = sg.add(in->f_aux, 4 * nf);

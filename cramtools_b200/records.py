@@ -45,7 +45,7 @@ class NormIn(C.Structure):
                 ('win_start0', i64p), ('ref', C.c_void_p), ('ref_total', C.c_uint64), ('matrix', C.c_void_p), ('pos', C.c_void_p),
                 ('read_off', C.c_void_p), ('rflags', C.c_void_p), ('feat_off', C.c_void_p), ('f_op', C.c_void_p), ('f_pos', C.c_void_p),
                 ('f_val', C.c_void_p), ('f_aux', C.c_void_p), ('payload', C.c_void_p), ('qs', C.c_void_p), ('read_qs_off', C.c_void_p),
-                ('ba', C.c_void_p), ('read_ba_off', C.c_void_p)]
+                ('ba', C.c_void_p), ('read_ba_off', C.c_void_p), ('payload_len', C.c_uint64)]
 
 
 class Series(C.Structure):
@@ -54,7 +54,26 @@ class Series(C.Structure):
                 ('rflags', C.c_void_p)]
 
 
+HOST_SERIES = ['BF', 'CF', 'RI', 'RL', 'AP', 'RG', 'RN', 'MF', 'NS', 'NP', 'TS', 'NF', 'TL']
+HOST_SERIES_CONTENT_ID = {'BF': 0, 'CF': 21, 'RI': 25, 'RL': 9, 'AP': 1, 'RG': 10, 'RN': 12, 'MF': 19, 'NS': 20, 'NP': 13, 'TS': 14,
+                          'NF': 8, 'TL': 24}
+
+
+class HostFields(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('slice_start', i32p), ('multi_ref', u8p),
+                ('ap_delta', C.c_uint32), ('names_included', C.c_uint32), ('flag', C.c_void_p), ('cf', C.c_void_p),
+                ('mate_cf', C.c_void_p), ('force_qs', C.c_void_p), ('rflags', C.c_void_p), ('ref_id', C.c_void_p), ('pos', C.c_void_p),
+                ('read_off', C.c_void_p), ('read_group', C.c_void_p), ('names', C.c_void_p), ('name_off', C.c_void_p),
+                ('mate_ref_id', C.c_void_p), ('mate_pos', C.c_void_p), ('tlen', C.c_void_p), ('nf', C.c_void_p), ('tl', C.c_void_p)]
+
+
+class HostSeries(C.Structure):
+    _fields_ = [('streams', C.c_void_p), ('streams_len', C.c_uint64), ('stream_off', C.c_void_p), ('stream_len', C.c_void_p)]
+
+
 _lib.SIGNATURES.update({
+    'cramgpu_host_series_pack': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.POINTER(HostSeries)]),
+    'cramgpu_host_series_pack_dev': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.POINTER(HostSeries), u64p, u64p, C.c_void_p]),
     'cramgpu_features_unpack': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), u8p, i32p]),
     'cramgpu_features_unpack_dev': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), C.POINTER(C.c_void_p), i32p,
                                               C.c_void_p]),
@@ -265,6 +284,7 @@ def normalize_decode(pos, read_off, rflags, enc, window, window_start0, matrix, 
     I.win_start0 = ws0.ctypes.data_as(i64p); I.ref = _vp(window); I.ref_total = window.size; I.matrix = _vp(matrix)
     for k, v in a.items():
         setattr(I, k, _vp(v))
+    I.payload_len = a['payload'].size
     total = int(a['read_off'][n])
     bases = np.zeros(max(total, 1), np.uint8); quals = np.zeros(max(total, 1), np.uint8)
     star = np.zeros(max(n, 1), np.uint8); status = np.zeros(max(n, 1), np.int32)
@@ -273,3 +293,52 @@ def normalize_decode(pos, read_off, rflags, enc, window, window_start0, matrix, 
     if rc != _lib.OK and (check or rc != _lib.ERR_CORRUPT):
         ctx.check(rc)
     return bases[:total], quals[:total], star[:n], status[:n]
+
+
+class PackedHostSeries(object):
+    """result of host_series_pack: series(c, name) -> bytes"""
+
+    def __init__(self, hs, nc):
+        self.streams = _view(hs.streams, hs.streams_len, np.uint8)
+        self.stream_off = _view(hs.stream_off, nc * len(HOST_SERIES), np.uint64).reshape(nc, len(HOST_SERIES))
+        self.stream_len = _view(hs.stream_len, nc * len(HOST_SERIES), np.uint64).reshape(nc, len(HOST_SERIES))
+
+    def series(self, c, name):
+        k = HOST_SERIES.index(name)
+        o, ln = int(self.stream_off[c, k]), int(self.stream_len[c, k])
+        return self.streams[o:o + ln].tobytes()
+
+
+def host_series_pack(flag, pos, read_off, cont_off=None, slice_start=None, multi_ref=None, ap_delta=True, names_included=False,
+                     cf=None, mate_cf=None, force_qs=None, rflags=None, ref_id=None, read_group=None, names=None,
+                     mate_ref_id=None, mate_pos=None, tlen=None, nf=None, tl=None, ctx=None):
+    """The fields Writer.write emits in front of the read features [Writer.java:139-172], through cramgpu_host_series_pack
+    (host buffers).  names: list of bytes / str.  -> PackedHostSeries"""
+    ctx = ctx or _lib.default_context()
+    n = len(flag)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    keep = dict(flag=_arr(flag, np.uint16), pos=_arr(pos, np.int32), read_off=_arr(read_off, np.uint64))
+    opt = dict(cf=(cf, np.uint8), mate_cf=(mate_cf, np.uint8), force_qs=(force_qs, np.uint8), rflags=(rflags, np.uint8),
+               ref_id=(ref_id, np.int32), read_group=(read_group, np.int32), mate_ref_id=(mate_ref_id, np.int32),
+               mate_pos=(mate_pos, np.int32), tlen=(tlen, np.int32), nf=(nf, np.int32), tl=(tl, np.int32))
+    for k, (v, dt) in opt.items():
+        keep[k] = None if v is None else _arr(v, dt)
+    if names is not None:
+        nb = [x.encode('latin-1') if isinstance(x, str) else bytes(x) for x in names]
+        keep['names'] = _arr(b''.join(nb), np.uint8)
+        keep['name_off'] = np.concatenate([[0], np.cumsum([len(x) for x in nb])]).astype(np.uint64)
+    else:
+        keep['names'] = keep['name_off'] = None
+    ss = _arr(np.zeros(nc) if slice_start is None else slice_start, np.int32)
+    mr = None if multi_ref is None else _arr(multi_ref, np.uint8)
+    I = HostFields()
+    I.n_reads = n; I.n_containers = nc
+    I.cont_off = cont_off.ctypes.data_as(u64p); I.slice_start = ss.ctypes.data_as(i32p)
+    I.multi_ref = mr.ctypes.data_as(u8p) if mr is not None else None
+    I.ap_delta = 1 if ap_delta else 0; I.names_included = 1 if names_included else 0
+    for k, v in keep.items():
+        setattr(I, k, _vp(v))
+    H = HostSeries()
+    ctx.check(ctx.lib.cramgpu_host_series_pack(ctx.handle, C.byref(I), C.byref(H)))
+    return PackedHostSeries(H, nc)

@@ -386,6 +386,7 @@ typedef struct cramgpu_norm_in {
     const uint64_t *read_qs_off;  /* [n_reads] offset of the read's preserved array in qs; ~0 = none */
     const uint8_t *ba;            /* decoded BA series */
     const uint64_t *read_ba_off;  /* [n_reads] offset of an unmapped read's bases in ba; ~0 = none */
+    uint64_t payload_len;         /* bytes in payload; an S / I feature that points outside it makes its record CRAMGPU_ERR_CORRUPT */
 } cramgpu_norm_in;
 
 #define CRAMGPU_NF_FORCE_QS 1u
@@ -395,7 +396,9 @@ typedef struct cramgpu_norm_in {
 /*
  * Base and quality restoration.  bases / quals receive read_off[n_reads] bytes; qual_star[r] = 1 where the
  * reference yields SAMRecord.NULL_QUALS; status[r] = CRAMGPU_ERR_CORRUPT where the reference would throw
- * ArrayIndexOutOfBoundsException (record outside its region).  Host variant takes/returns host memory; the
+ * ArrayIndexOutOfBoundsException (record outside its region, a feature position outside [1, readLength], a
+ * soft clip or insertion that overruns the read or the payload); such a record's own bases / scores are then
+ * undefined, every other record is unaffected.  Host variant takes/returns host memory; the
  * device variant takes device pointers for everything not marked HOST and enqueues on `stream`.
  * In the host variant ref, matrix, the feature arrays, payload, qs, ba and the outputs bases / quals may also be
  * device pointers (a QS series cramgpu_rans_decode_batch left on the device, say) and are then used in place;
@@ -406,6 +409,78 @@ int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_
                              uint8_t *qual_star, int32_t *status);
 int cramgpu_normalize_decode_dev(cramgpu_ctx *ctx, const cramgpu_norm_in *in, uint8_t *d_bases, uint8_t *d_quals,
                                  uint8_t *d_qual_star, int32_t *d_status, void *stream);
+
+
+/* ------------------------------------------------------------------ the record fields in front of the read features
+ *
+ * Replaces the first half of Writer.write [Writer.java:139-172], driven per record from ContainerFactory.buildSlice
+ * [ContainerFactory.java:179-184], and the flag part of Sam2CramRecordFactory.createCramRecord [:114-131,143-152]:
+ * the series BF CF RI RL AP RG RN MF NS NP TS NF TL of every container of the batch, byte-identical to what the
+ * reference's Writer produces (tests/golden/streams_jvm.json).  What stays on the Java host is what needs the whole
+ * container at once: mate linking (CramSerilization.setMateInfo, :274-373 -- it decides `detached`, `mate downstream`
+ * and recordsToNextFragment) and the tag dictionary.
+ */
+enum {
+    CRAMGPU_HS_BF = 0, /* CRAM bit flags, ITF8                                   content id 0  */
+    CRAMGPU_HS_CF,     /* compression bit flags, one byte                        content id 21 */
+    CRAMGPU_HS_RI,     /* reference id, ITF8 (multi-reference slices only)       content id 25 */
+    CRAMGPU_HS_RL,     /* read length, ITF8                                      content id 9  */
+    CRAMGPU_HS_AP,     /* alignment start or its delta, ITF8                     content id 1  */
+    CRAMGPU_HS_RG,     /* read group index, ITF8                                 content id 10 */
+    CRAMGPU_HS_RN,     /* read name + TAB                                        content id 12 */
+    CRAMGPU_HS_MF,     /* mate flags, one byte                                   content id 19 */
+    CRAMGPU_HS_NS,     /* mate reference id, ITF8                                content id 20 */
+    CRAMGPU_HS_NP,     /* mate alignment start, ITF8                             content id 13 */
+    CRAMGPU_HS_TS,     /* template size, ITF8                                    content id 14 */
+    CRAMGPU_HS_NF,     /* records to the next fragment, ITF8                     content id 8  */
+    CRAMGPU_HS_TL,     /* tag id list index, ITF8                                content id 24 */
+    CRAMGPU_HS_COUNT
+};
+
+typedef struct cramgpu_host_fields {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    const int32_t *slice_start;   /* HOST [n_containers] Slice.alignmentStart: AP of the first record is its start minus this (ap_delta only) */
+    const uint8_t *multi_ref;     /* HOST [n_containers] 1 = Slice.MULTI_REFERENCE: RI is written; NULL = none */
+    uint32_t ap_delta;            /* CompressionHeader.APDelta (coordinate-sorted input) */
+    uint32_t names_included;      /* CompressionHeader.readNamesIncluded: names of all records, else of detached ones only */
+    const uint16_t *flag;         /* [n_reads] SAM flags: BF and MF are derived from them */
+    const uint8_t *cf;            /* [n_reads] CF as CramCompressionRecord.getCompressionFlags() returns it, or NULL: then composed from */
+    const uint8_t *mate_cf;       /*   the mate-linking bits (2 detached, 4 mate downstream; NULL = every record detached), */
+    const uint8_t *force_qs;      /*   bit 0 of cramgpu_features.force_qs (NULL = 0) and */
+    const uint8_t *rflags;        /*   CRAMGPU_RF_NO_BASES of the reads' rflags (NULL = 0) */
+    const int32_t *ref_id;        /* [n_reads] sequenceId (needed for multi-reference slices) */
+    const int32_t *pos;           /* [n_reads] alignmentStart */
+    const uint64_t *read_off;     /* [n_reads+1] cumulative read length */
+    const int32_t *read_group;    /* [n_reads] readGroupID; NULL = -1 everywhere */
+    const uint8_t *names;         /* read names, concatenated (no terminators); NULL = RN stays empty */
+    const uint64_t *name_off;     /* [n_reads+1] */
+    const int32_t *mate_ref_id;   /* [n_reads] mateSequenceID      ) read for detached records only (NULL: -1, 0, 0) */
+    const int32_t *mate_pos;      /* [n_reads] mateAlignmentStart  )                                                 */
+    const int32_t *tlen;          /* [n_reads] templateSize        )                                                 */
+    const int32_t *nf;            /* [n_reads] recordsToNextFragment (records with their mate downstream) */
+    const int32_t *tl;            /* [n_reads] tagIdsIndex; NULL = 0 */
+} cramgpu_host_fields;
+
+/* Result: all series bytes SERIES-major like cramgpu_features.streams (the BF regions of all containers, then CF, ...),
+ * every (container, series) region at a multiple of 16.  Memory belongs to the context and stays valid until the next
+ * call of the same kind on it. */
+typedef struct cramgpu_host_series {
+    const uint8_t *streams;
+    uint64_t streams_len;
+    const uint64_t *stream_off;   /* [n_containers][CRAMGPU_HS_COUNT] */
+    const uint64_t *stream_len;   /* [n_containers][CRAMGPU_HS_COUNT] */
+} cramgpu_host_series;
+
+/* Device variant: the per-record arrays of `in` are device pointers, results are device pointers; the layout tables are
+ * mirrored into h_stream_off / h_stream_len ([n_containers][CRAMGPU_HS_COUNT], optional) so that the caller can hand the
+ * series to cramgpu_rans_encode_dev.  The call returns after the counting pass (it sizes the result buffer from the
+ * totals); the packing kernel is still running on `stream` then.
+ * Host variant: everything in host memory; results are host memory owned by the context. */
+int cramgpu_host_series_pack_dev(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out,
+                                 uint64_t *h_stream_off, uint64_t *h_stream_len, void *stream);
+int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out);
 
 #ifdef __cplusplus
 }

@@ -266,6 +266,7 @@ class MiniJVM:
         self.initialized = set()
         self.nbytecodes = 0
         self.strings = {}
+        self.hooks = {}      # (class, method, descriptor) or ('*', method, descriptor) -> python function(vm, method, args): replaces a jar method
 
     # ---- loading
     def load(self, name):
@@ -300,6 +301,58 @@ class MiniJVM:
     def is_jdk(self, name):
         return name.startswith('java/')
 
+    def jdk_base(self, cname):
+        """first JDK class among the superclasses of a jar class (ExposedByteArrayOutputStream -> ByteArrayOutputStream)"""
+        c = cname
+        while c and not self.is_jdk(c):
+            c = self.load(c).super_name
+        return c
+
+    # ---- just enough java.lang.reflect for DataWriterFactory.buildWriter / DataReaderFactory.buildReader
+    def public_fields(self, cname):
+        """Class.getFields(): public fields of the class and its superclasses, as java.lang.reflect.Field stand-ins that
+        carry the RuntimeVisibleAnnotations of the class file (enum-valued and string-valued elements)"""
+        out = []
+        c = cname
+        while c and not self.is_jdk(c):
+            cf = self.load(c)
+            for acc, nm, ds, attrs in cf.fields:
+                if not acc & 0x0001:
+                    continue
+                f = JObject('java/lang/reflect/Field')
+                f.fields.update(owner=c, name=nm, desc=ds, static=bool(acc & 0x0008), annotations=self._annotations(cf, attrs))
+                out.append(f)
+            c = cf.super_name
+        return out
+
+    def _annotations(self, cf, attrs):
+        raw = attrs.get('RuntimeVisibleAnnotations')
+        res = {}
+        if not raw:
+            return res
+        p = 2
+        for _ in range(struct.unpack_from('>H', raw, 0)[0]):
+            tname = cf.utf(struct.unpack_from('>H', raw, p)[0])[1:-1]
+            npairs = struct.unpack_from('>H', raw, p + 2)[0]
+            p += 4
+            proxy = JObject('java/lang/annotation/$Proxy')
+            for _ in range(npairs):
+                ename = cf.utf(struct.unpack_from('>H', raw, p)[0])
+                tag = chr(raw[p + 2])
+                if tag == 'e':
+                    ecls = cf.utf(struct.unpack_from('>H', raw, p + 3)[0])[1:-1]
+                    econst = cf.utf(struct.unpack_from('>H', raw, p + 5)[0])
+                    self.load(ecls)
+                    proxy.fields[ename] = self.statics[(ecls, econst)]
+                    p += 7
+                elif tag == 's':
+                    proxy.fields[ename] = cf.utf(struct.unpack_from('>H', raw, p + 3)[0])
+                    p += 5
+                else:
+                    raise NotImplementedError('annotation element tag ' + tag)
+            res[tname] = proxy
+        return res
+
     def find_method(self, cname, name, desc):
         c = cname
         while c and not self.is_jdk(c):
@@ -324,6 +377,8 @@ class MiniJVM:
     def instance_of(self, obj, cname):
         if obj is None:
             return False
+        if isinstance(obj, str):
+            return cname in ('java/lang/String', 'java/lang/Object', 'java/lang/CharSequence', 'java/lang/Comparable')
         c = obj.cls if isinstance(obj, JObject) else None
         if isinstance(obj, ByteBuffer):
             return cname in ('java/nio/ByteBuffer', 'java/nio/Buffer', 'java/lang/Object')
@@ -387,6 +442,10 @@ class MiniJVM:
         return self.invoke(m, args)
 
     def invoke(self, m, args):
+        if self.hooks:
+            h = self.hooks.get((m.cf.name, m.name, m.desc)) or self.hooks.get(('*', m.name, m.desc))
+            if h is not None:
+                return h(self, m, args)
         if m.code is None:
             raise NotImplementedError('native/abstract %s.%s%s' % (m.cf.name, m.name, m.desc))
         loc = [None] * m.max_locals
@@ -396,7 +455,11 @@ class MiniJVM:
             args = args[1:]
         for w, a in zip(m.nargs, args):
             loc[i] = a; i += w
-        return self.run(m, loc)
+        try:
+            return self.run(m, loc)
+        except NotImplementedError as e:       # missing JDK emulation: say where the jar needed it
+            e.args = (str(e.args[0]) + '\n    at %s.%s%s' % (m.cf.name, m.name, m.desc),) + e.args[1:]
+            raise
 
     def run(self, m, loc):
         code = m.code
@@ -822,7 +885,19 @@ class MiniJVM:
     def jdk_special(self, cn, mn, ds, args):
         o = args[0]
         if mn == '<init>':
-            if cn in ('java/lang/Object',):
+            if cn in ('java/lang/Object', 'java/io/OutputStream', 'java/io/InputStream'):
+                return None
+            if cn in ('java/io/DataInputStream', 'java/io/FilterInputStream'):
+                o.fields['in'] = args[1]
+                return None
+            if cn == 'java/io/ByteArrayOutputStream':
+                o.fields['buf'] = JArray('B', bytearray()); o.fields['count'] = 0
+                return None
+            if cn == 'java/io/ByteArrayInputStream':
+                o.fields['buf'] = args[1]; o.fields['pos'] = 0; o.fields['count'] = len(args[1].a)
+                return None
+            if cn == 'java/util/zip/CRC32':
+                o.fields['crc'] = 0
                 return None
             if cn == 'java/lang/Enum':
                 o.fields['name'] = args[1]; o.fields['ordinal'] = args[2]; return None
@@ -846,6 +921,8 @@ class MiniJVM:
                 return None
             if cn in JDK_MAPS:
                 o.fields['map'] = {}
+                if cn == 'java/util/TreeMap' and ds == '(Ljava/util/Comparator;)V':
+                    o.fields['cmp'] = args[1]
                 return None
             if cn in JDK_SETS:
                 o.fields['map'] = {}
@@ -956,6 +1033,29 @@ class MiniJVM:
             o = JObject('java/lang/Integer'); o.fields['value'] = args[0]; return o
         if cn == 'java/lang/String' and mn == 'valueOf':
             return self.to_jstring(args[0], ds)
+        if cn == 'java/util/regex/Pattern' and mn == 'compile':
+            import re as _re
+            o = JObject('java/util/regex/Pattern'); o.fields['re'] = _re.compile(args[0]); o.fields['pattern'] = args[0]; return o
+        if cn == 'java/nio/charset/Charset' and mn == 'forName':
+            o = JObject('java/nio/charset/Charset'); o.fields['name'] = args[0]; return o
+        if cn == 'java/util/EnumSet' and mn in ('allOf', 'noneOf', 'of', 'copyOf'):
+            o = JObject('java/util/EnumSet'); o.fields['map'] = {}
+            if mn == 'allOf':
+                self.load(args[0][1])
+                vals = self.statics[(args[0][1], '$VALUES')].a
+            elif mn == 'noneOf':
+                vals = []
+            elif mn == 'copyOf':
+                vals = list(args[0].fields['map'].values()) if 'map' in args[0].fields else list(args[0].fields['list'])
+            else:
+                vals = [a for a in args if isinstance(a, JObject)] + [x for a in args if isinstance(a, JArray) for x in a.a]
+            for v in sorted(vals, key=lambda e: e.fields['ordinal']):
+                o.fields['map'][_key(v)] = v
+            return o
+        if cn == 'java/security/MessageDigest' and mn == 'getInstance':
+            import hashlib
+            alg = {'SHA-1': 'sha1', 'SHA-512': 'sha512', 'MD5': 'md5', 'SHA-256': 'sha256'}[args[0]]
+            o = JObject('java/security/MessageDigest'); o.fields['alg'] = alg; o.fields['h'] = hashlib.new(alg); return o
         if cn == 'java/lang/Enum' and mn == 'valueOf':
             _, cname = args[0]
             for v in self.statics[(cname, '$VALUES')].a:
@@ -987,13 +1087,121 @@ class MiniJVM:
         if isinstance(o, tuple) and o[0] == 'class':
             if mn == 'desiredAssertionStatus':
                 return 0       # plain `java` without -ea
+            if mn == 'isArray':
+                return 1 if o[1].startswith('[') else 0
             if mn == 'getName':
                 return o[1].replace('/', '.')
             if mn == 'getSimpleName':
                 return o[1].split('/')[-1].split('$')[-1]
+        if isinstance(o, tuple) and o[0] == 'class' and mn == 'getFields':
+            return JArray('L', self.public_fields(o[1]))
         if isinstance(o, JArray) and mn == 'clone':
             return JArray(o.kind, o.a[:])
+        if isinstance(o, JObject):
+            base = o.cls if self.is_jdk(o.cls) else self.jdk_base(o.cls)
+            if base == 'java/io/ByteArrayOutputStream':
+                buf = o.fields['buf'].a
+                if mn == 'write':
+                    if ds == '(I)V':
+                        buf.append(args[1] & 0xFF)
+                    elif ds == '([B)V':
+                        buf.extend(args[1].a)
+                    else:
+                        src, sp, n = args[1:]
+                        if sp < 0 or n < 0 or sp + n > len(src.a):
+                            self.throw('java/lang/IndexOutOfBoundsException', None)
+                        buf.extend(src.a[sp:sp + n])
+                    o.fields['count'] = len(buf)
+                    return None
+                if mn == 'toByteArray':
+                    return JArray('B', bytearray(buf))
+                if mn == 'size':
+                    return len(buf)
+                if mn == 'reset':
+                    del buf[:]; o.fields['count'] = 0; return None
+                if mn in ('flush', 'close'):
+                    return None
+            if base == 'java/io/ByteArrayInputStream':
+                buf = o.fields['buf'].a
+                if mn == 'read' and ds == '()I':
+                    if o.fields['pos'] >= o.fields['count']:
+                        return -1
+                    v = buf[o.fields['pos']]; o.fields['pos'] += 1; return v
+                if mn == 'read':
+                    dst, dp, n = (args[1], 0, len(args[1].a)) if ds == '([B)I' else args[1:]
+                    left = o.fields['count'] - o.fields['pos']
+                    if left <= 0:
+                        return -1 if n > 0 else 0
+                    n = min(n, left)
+                    dst.a[dp:dp + n] = buf[o.fields['pos']:o.fields['pos'] + n]
+                    o.fields['pos'] += n
+                    return n
+                if mn == 'available':
+                    return o.fields['count'] - o.fields['pos']
+                if mn == 'close':
+                    return None
+            if base in ('java/io/OutputStream', 'java/io/InputStream') and mn in ('flush', 'close'):
+                return None
+            if base == 'java/io/OutputStream' and mn == 'write' and ds == '([B)V':
+                # OutputStream.write(byte[]) = write(b, 0, b.length), which loops over the subclass's write(int)
+                m1 = self.find_method(o.cls, 'write', '([BII)V')
+                if m1 is not None:
+                    return self.invoke(m1, [o, args[1], 0, len(args[1].a)])
+                m1 = self.find_method(o.cls, 'write', '(I)V')
+                for b in args[1].a:
+                    self.invoke(m1, [o, b])
+                return None
+            if base == 'java/io/OutputStream' and mn == 'write' and ds == '([BII)V':
+                m1 = self.find_method(o.cls, 'write', '(I)V')
+                for b in args[1].a[args[2]:args[2] + args[3]]:
+                    self.invoke(m1, [o, b])
+                return None
+            if o.cls == 'java/util/regex/Pattern' and mn == 'matcher':
+                r = JObject('java/util/regex/Matcher'); r.fields['re'] = o.fields['re']; r.fields['s'] = args[1]; return r
+            if o.cls == 'java/util/regex/Matcher':
+                if mn == 'matches':
+                    return 1 if o.fields['re'].fullmatch(o.fields['s']) else 0
+                if mn == 'find':
+                    return 1 if o.fields['re'].search(o.fields['s']) else 0
+            if o.cls == 'java/lang/reflect/Field':
+                if mn == 'isAnnotationPresent':
+                    return 1 if args[1][1] in o.fields['annotations'] else 0
+                if mn == 'getAnnotation':
+                    return o.fields['annotations'].get(args[1][1])
+                if mn == 'set':
+                    args[1].fields[o.fields['name']] = args[2]; return None
+                if mn == 'get':
+                    return args[1].fields.get(o.fields['name'])
+                if mn == 'getName':
+                    return o.fields['name']
+            if o.cls == 'java/lang/annotation/$Proxy':
+                return o.fields[mn]
+            if o.cls == 'java/util/zip/CRC32':
+                import zlib
+                if mn == 'update':
+                    data = bytes(args[1].a) if ds == '([B)V' else (bytes([args[1] & 0xFF]) if ds == '(I)V' else bytes(args[1].a[args[2]:args[2] + args[3]]))
+                    o.fields['crc'] = zlib.crc32(data, o.fields['crc'])
+                    return None
+                if mn == 'getValue':
+                    return o.fields['crc']
+                if mn == 'reset':
+                    o.fields['crc'] = 0; return None
+            if o.cls == 'java/security/MessageDigest':
+                import hashlib
+                if mn == 'digest':
+                    if ds == '([B)[B':
+                        o.fields['h'].update(bytes(args[1].a))
+                    d = o.fields['h'].digest()
+                    o.fields['h'] = hashlib.new(o.fields['alg'])
+                    return JArray('B', bytearray(d))
+                if mn == 'update':
+                    o.fields['h'].update(bytes(args[1].a) if ds == '([B)V' else bytes(args[1].a[args[2]:args[2] + args[3]]))
+                    return None
+                if mn == 'reset':
+                    o.fields['h'] = hashlib.new(o.fields['alg']); return None
         if isinstance(o, str):
+            if mn == 'getClass':
+                return ('class', 'java/lang/String')
             if mn == 'length':
                 return len(o)
             if mn == 'charAt':
@@ -1073,12 +1281,39 @@ class MiniJVM:
                     v = o.fields['it'][o.fields['i']]; o.fields['i'] += 1; return v
             if 'map' in o.fields and o.cls in JDK_MAPS:
                 mp = o.fields['map']
+                cmpo = o.fields.get('cmp')
+
+                def find(key):
+                    """dictionary key of the entry equal to `key`: by the TreeMap's comparator when it has one"""
+                    if cmpo is None:
+                        return _key(key)
+                    mc = self.find_method(cmpo.cls, 'compare', '(Ljava/lang/Object;Ljava/lang/Object;)I')
+                    for dk, (k0, _) in mp.items():
+                        if self.invoke(mc, [cmpo, key, k0]) == 0:
+                            return dk
+                    return _key(key)
+
+                def ordered():
+                    items = list(mp.values())
+                    if o.cls == 'java/util/TreeMap':
+                        import functools
+                        if cmpo is not None:
+                            mc = self.find_method(cmpo.cls, 'compare', '(Ljava/lang/Object;Ljava/lang/Object;)I')
+                            items.sort(key=functools.cmp_to_key(lambda a, b: self.invoke(mc, [cmpo, a[0], b[0]])))
+                        else:
+                            items.sort(key=lambda kv: kv[0].fields['value'] if isinstance(kv[0], JObject) else kv[0])
+                    return items
                 if mn == 'put':
-                    k = _key(args[1]); old = mp.get(k, (None, None))[1]; mp[k] = (args[1], args[2]); return old
+                    k = find(args[1]); old = mp.get(k, (None, None))
+                    mp[k] = (old[0] if old[0] is not None and cmpo is not None else args[1], args[2]); return old[1]
                 if mn == 'get':
-                    return mp.get(_key(args[1]), (None, None))[1]
+                    return mp.get(find(args[1]), (None, None))[1]
                 if mn == 'containsKey':
-                    return 1 if _key(args[1]) in mp else 0
+                    return 1 if find(args[1]) in mp else 0
+                if mn == 'values' and o.cls == 'java/util/TreeMap':
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [v for _, v in ordered()]; return r
+                if mn == 'keySet' and o.cls == 'java/util/TreeMap':
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [k for k, _ in ordered()]; return r
                 if mn == 'size':
                     return len(mp)
                 if mn == 'isEmpty':
@@ -1226,7 +1461,7 @@ class MiniJVM:
 
 JDK_LISTS = ('java/util/ArrayList', 'java/util/LinkedList')
 JDK_MAPS = ('java/util/HashMap', 'java/util/TreeMap', 'java/util/LinkedHashMap')
-JDK_SETS = ('java/util/HashSet', 'java/util/TreeSet', 'java/util/LinkedHashSet')
+JDK_SETS = ('java/util/HashSet', 'java/util/TreeSet', 'java/util/LinkedHashSet', 'java/util/EnumSet')
 
 
 def _key(v):

@@ -284,3 +284,68 @@ def read_streams(st, read_len, rflags):
     for k in st:
         assert cur[k] == len(st[k]), (k, cur[k], len(st[k]))      # every byte of every series accounted for
     return rows, mapq, qs_off, ba_off
+
+
+# ---------------------------------------------------------------------------------------------- host-side series (row W, first half)
+# EncodingKey.ordinal() = content id of the series' external block (htsjdk/samtools/cram/structure/EncodingKey)
+CONTENT_ID = {'BF': 0, 'AP': 1, 'FP': 2, 'FC': 3, 'QS': 4, 'DL': 5, 'BA': 6, 'TN': 7, 'NF': 8, 'RL': 9, 'RG': 10, 'MQ': 11,
+              'RN': 12, 'NP': 13, 'TS': 14, 'FN': 15, 'BS': 16, 'IN': 17, 'TC': 18, 'MF': 19, 'NS': 20, 'CF': 21, 'TL': 24,
+              'RI': 25, 'RS': 26, 'SC': 27, 'HC': 28, 'PD': 29}
+HOST_STREAMS = ['BF', 'CF', 'RI', 'RL', 'AP', 'RG', 'RN', 'MF', 'NS', 'NP', 'TS', 'NF', 'TL']
+
+# CramCompressionRecord flag bits (htsjdk/samtools/cram/structure/CramCompressionRecord)
+CF_FORCE_QS, CF_DETACHED, CF_MATE_DOWNSTREAM, CF_UNKNOWN_BASES = 1, 2, 4, 8
+MF_NEG_STRAND, MF_UNMAPPED = 1, 2
+
+
+def cram_bit_flags(sam_flag):
+    """BF of Sam2CramRecordFactory.createCramRecord [:122-131,143-152]: the SAM flag without the two mate bits (they go to
+    MF); for an unpaired read the proper-pair and first / last segment bits are dropped too."""
+    f = int(sam_flag)
+    if f & 0x1:
+        return f & (0x1 | 0x2 | 0x4 | 0x10 | 0x40 | 0x80 | 0x100 | 0x200 | 0x400 | 0x800)
+    return f & (0x4 | 0x10 | 0x100 | 0x200 | 0x400 | 0x800)
+
+
+def mate_bit_flags(sam_flag):
+    """MF [:114-115]: bit 0 mate on the reverse strand (SAM 0x20), bit 1 mate unmapped (SAM 0x8); 0 for an unpaired read"""
+    f = int(sam_flag)
+    if not f & 0x1:
+        return 0
+    return (MF_NEG_STRAND if f & 0x20 else 0) | (MF_UNMAPPED if f & 0x8 else 0)
+
+
+def write_host_streams(sc, ap_delta, multi_ref, slice_start, capture_names=True):
+    """The fields Writer.write emits before the read features [Writer.java:139-172], per record in this order:
+    BF (ITF8), CF (byte), RI (ITF8, multi-reference slices only), RL, AP (delta to the previous record's start when the
+    header says so -- ContainerFactory.buildSlice [:179-182], the first record against the slice start -- else the start
+    itself), RG, RN (name + TAB), then MF (byte), NS, NP, TS for a detached record or NF for one whose mate follows, TL.
+    sc: list of dicts with flags, cf, seq_id, read_length, start, read_group, name, mate_flags, mate_seq_id, mate_start,
+    tlen, nf, tl.  -> dict series -> bytes"""
+    out = {k: bytearray() for k in HOST_STREAMS}
+    prev = slice_start
+    for r in sc:
+        out['BF'] += itf8(r['flags'])
+        out['CF'].append(r['cf'] & 0xFF)
+        if multi_ref:
+            out['RI'] += itf8(r['seq_id'])
+        out['RL'] += itf8(r['read_length'])
+        if ap_delta:
+            out['AP'] += itf8(r['start'] - prev)
+            prev = r['start']
+        else:
+            out['AP'] += itf8(r['start'])
+        out['RG'] += itf8(r['read_group'])
+        if capture_names:
+            out['RN'] += r['name'].encode('latin-1') + b'\t'
+        if r['cf'] & CF_DETACHED:
+            out['MF'].append(r['mate_flags'] & 0xFF)
+            if not capture_names:
+                out['RN'] += r['name'].encode('latin-1') + b'\t'
+            out['NS'] += itf8(r['mate_seq_id'])
+            out['NP'] += itf8(r['mate_start'])
+            out['TS'] += itf8(r['tlen'])
+        elif r['cf'] & CF_MATE_DOWNSTREAM:
+            out['NF'] += itf8(r['nf'])
+        out['TL'] += itf8(r.get('tl', 0))
+    return {k: bytes(v) for k, v in out.items()}

@@ -1,0 +1,46 @@
+"""helpers: load tests/golden/streams_jvm.json (per-series bytes of three slices written by the reference jar's own
+Writer / ContainerFactory.buildSlice in the mini-JVM, and the records its CramRecordReader read back) into the SoA layout"""
+import base64
+import json
+import os
+
+import numpy as np
+
+from cramtools_b200 import synth
+from tests.golden_records import _parse_cigar
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def load():
+    with open(os.path.join(ROOT, 'tests', 'golden', 'streams_jvm.json')) as f:
+        g = json.load(f)
+    ref = np.frombuffer(base64.b64decode(g['ref']), np.uint8)
+    out = []
+    for c in g['containers']:
+        reads = c['reads']
+        n = len(reads)
+        bases, quals, cig = [], [], []
+        read_off = np.zeros(n + 1, np.int64)
+        cigar_off = np.zeros(n + 1, np.int64)
+        rflags = np.zeros(n, np.uint8)
+        for i, r in enumerate(reads):
+            b = base64.b64decode(r['bases']) if r['bases'] is not None else b''
+            q = base64.b64decode(r['quals']) if r['quals'] is not None else b'\xff' * len(b)
+            if r['quals'] is None:
+                rflags[i] |= 1
+            if r['bases'] is None:
+                rflags[i] |= 2
+            bases.append(b); quals.append(q)
+            read_off[i + 1] = read_off[i] + len(b)
+            cg = synth.pack_cigar(_parse_cigar(r['cigar']))
+            cig.append(cg)
+            cigar_off[i + 1] = cigar_off[i] + len(cg)
+        rd = dict(bases=np.frombuffer(b''.join(bases), np.uint8).copy(), quals=np.frombuffer(b''.join(quals), np.uint8).copy(),
+                  read_off=read_off, cigar=np.concatenate(cig) if cig else np.zeros(0, np.uint32), cigar_off=cigar_off,
+                  pos=np.array([r['pos'] for r in reads], np.int32), flag=np.array([r['flag'] for r in reads], np.uint16),
+                  mapq=np.array([r['mapq'] for r in reads], np.uint8), ref_id=np.array([r['ref_id'] for r in reads], np.int32),
+                  rflags=rflags, names=[r['name'] for r in reads])
+        series = {int(k): base64.b64decode(v) for k, v in c['series'].items()}
+        out.append((c, rd, series))
+    return g, ref, out

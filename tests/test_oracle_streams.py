@@ -1,0 +1,98 @@
+"""CPU: rows W and P of the oracle against what the reference jar itself wrote and read (tests/golden/streams_jvm.json:
+ContainerFactory.buildSlice -> Writer.write, DataReaderFactory.buildReader -> CramRecordReader.read, run in the mini-JVM
+by oracle/make_golden_streams.py; only ExternalCompressor.compress was stubbed to keep the raw series)."""
+import base64
+
+import numpy as np
+import pytest
+
+from oracle import records as orec
+from tests import golden_streams as gs
+
+CID = orec.CONTENT_ID
+
+
+@pytest.fixture(scope='module')
+def G():
+    return gs.load()
+
+
+def test_series_to_compressor_map_matches_survey(G):
+    """row R0: which external compressor CompressionHeaderFactory.build gives each series [:84-113]"""
+    g, _, conts = G
+    want = {'rans1': ['BA', 'QS', 'BF', 'CF', 'NS', 'RG', 'RL', 'TS'], 'rans0': ['AP', 'RI'],
+            'gzip': ['BS', 'DL', 'FC', 'FN', 'FP', 'HC', 'IN', 'MF', 'MQ', 'NF', 'NP', 'PD', 'RN', 'RS', 'SC', 'TC', 'TL', 'TN']}
+    for c, _, _ in conts:
+        comp = c['compressors']
+        for nm in want['rans1']:
+            assert (comp[str(CID[nm])]['method'], comp[str(CID[nm])]['order']) == ('RANS', 'ONE'), nm
+        for nm in want['rans0']:
+            assert (comp[str(CID[nm])]['method'], comp[str(CID[nm])]['order']) == ('RANS', 'ZERO'), nm
+        for nm in want['gzip']:
+            assert comp[str(CID[nm])]['method'] == 'GZIP', nm
+        assert base64.b64decode(c['core']) == b''            # every series is external: nothing in the core block
+
+
+def _scalars(c, rd):
+    """the record fields Writer.write reads, as the jar left them after createCramRecord + setMateInfo"""
+    out = []
+    for s, pos in zip(c['scalars'], rd['pos']):
+        out.append(dict(flags=s['flags'], cf=s['cf'], seq_id=s['seq_id'], read_length=s['read_length'], start=int(pos),
+                        read_group=s['read_group'], name=s['name'], mate_flags=s['mate_flags'], mate_seq_id=s['mate_seq_id'],
+                        mate_start=s['mate_start'], tlen=s['tlen'], nf=s['nf'], tl=0))
+    return out
+
+
+def test_host_series_match_jar(G):
+    """BF CF RI RL AP RG RN MF NS NP TS NF TL byte for byte"""
+    g, _, conts = G
+    for c, rd, series in conts:
+        multi = c['slice']['sequence_id'] == -2
+        got = orec.write_host_streams(_scalars(c, rd), c['ap_delta'], multi, c['slice']['alignment_start'],
+                                      capture_names=bool(c['read_names_included']))
+        for nm in orec.HOST_STREAMS:
+            assert got[nm] == series.get(CID[nm], b''), (c['tag'], nm)
+
+
+def test_bit_flags_match_jar(G):
+    """row F2, scalar half: BF and MF from the SAM flag"""
+    g, _, conts = G
+    for c, rd, _ in conts:
+        for s, fl in zip(c['scalars'], rd['flag']):
+            assert orec.cram_bit_flags(fl) == s['flags'], (c['tag'], s['name'], int(fl))
+            assert orec.mate_bit_flags(fl) == s['mate_flags'], (c['tag'], s['name'], int(fl))
+
+
+def test_feature_series_match_jar(G):
+    """FN FC FP BS DL BA SC QS RS HC PD MQ of the C oracle's Writer restatement, byte for byte"""
+    g, ref, conts = G
+    for c, rd, series in conts:
+        ex = orec.extract(rd, ref)
+        force, scores = orec.quality(rd, ref, None)
+        st = orec.write_streams(rd, ex, force, scores)
+        assert ex.matrix == base64.b64decode(c['subst_matrix']), c['tag']
+        for nm in orec.STREAMS:
+            assert st[nm] == series.get(CID[nm], b''), (c['tag'], nm)
+
+
+def test_reader_matches_jar(G):
+    """row P: read_streams over the jar's own series gives what the jar's CramRecordReader read"""
+    g, ref, conts = G
+    for c, rd, series in conts:
+        st = {nm: series.get(CID[nm], b'') for nm in orec.STREAMS}
+        back = c['read_back']
+        rl = [b['read_length'] for b in back]
+        # the flags the host part of the reader hands over: CF bit 0 (stored score array), BF 0x4 (unmapped), CF bit 3 (unknown bases)
+        rfl = np.array([(b['cf'] & 1) | (2 if b['flags'] & 4 else 0) | (4 if b['cf'] & 8 else 0) for b in back], np.uint8)
+        rows, mapq, qs_off, ba_off = orec.read_streams(st, rl, rfl)
+        for i, b in enumerate(back):
+            want = [[f[0], f[1], f[4]] if f[0] == 'X' else f for f in (b['features'] or [])]
+            got = [[f[0], f[1], base64.b64encode(f[2]).decode()] if f[0] == 'S' else f for f in rows[i]]
+            assert got == want, (c['tag'], i, b['name'])
+            if not b['flags'] & 4:
+                assert mapq[i] == b['mapq'], (c['tag'], i)
+            if b['quals'] is not None and b['cf'] & 1:
+                assert st['QS'][qs_off[i]:qs_off[i] + rl[i]] == base64.b64decode(b['quals']), (c['tag'], i)
+            if b['flags'] & 4 and b['bases'] is not None:
+                assert st['BA'][ba_off[i]:ba_off[i] + rl[i]] == base64.b64decode(b['bases']), (c['tag'], i)
+        assert set(c['bytes_left'].values()) == {0}            # and the jar's reader used up every byte of every series

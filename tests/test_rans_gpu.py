@@ -210,3 +210,21 @@ def test_eight_megabyte_blocks(gpu_ctx):
         for b, g in zip(blocks, got):
             assert g == orans.compress(b, order)
         assert EC.unrans_batch(got, gpu_ctx) == [b.tobytes() for b in blocks]
+
+
+def test_decode_dev_rejects_misaligned_blocks(EC, gpu_ctx):
+    """the decoders fetch a block as aligned words: an offset that is not a multiple of 16 must be refused with
+    CRAMGPU_ERR_ARG (the header's contract) instead of faulting the device"""
+    import torch
+    from cramtools_b200 import device as dv, _lib
+    blocks = [synth.qs_stream(5000, 7)]
+    comp = EC.rans_batch(blocks, [1], gpu_ctx)
+    pad = b'\0' * 4 + comp[0]                               # the block starts 4 bytes into the buffer
+    d_in, off, ln = dv.pack_blocks([pad], 'cuda:0')
+    pref = np.frombuffer(comp[0][:9], np.uint8).reshape(1, 9)
+    with pytest.raises(_lib.CramGpuError) as e:
+        dv.rans_decode_dev(gpu_ctx, d_in, np.array([4], np.uint64), np.array([len(comp[0])], np.uint32), pref)
+    assert e.value.status == _lib.ERR_ARG
+    # and the context stays usable
+    back = EC.unrans_batch(comp, gpu_ctx)
+    assert back[0] == blocks[0].tobytes()

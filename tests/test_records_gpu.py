@@ -273,6 +273,7 @@ def test_resident_series_and_device_pointers(R, gpu_ctx):
     I.win_start0 = w0.ctypes.data_as(i64p); I.ref = refa.ctypes.data; I.ref_total = refa.size
     for k, v in arrs.items():
         setattr(I, k, v.ctypes.data)
+    I.payload_len = int(enc.payload.size)
     I.qs = d_streams.data_ptr(); I.ba = d_streams.data_ptr()
     total = int(rd['read_off'][n])
     bases = np.zeros(total, np.uint8); quals = np.zeros(total, np.uint8); star = np.zeros(n, np.uint8); st = np.zeros(n, np.int32)
@@ -466,3 +467,46 @@ def test_full_size_containers_lossy_pipeline(R, gpu_ctx, spec):
         notd = np.add.reduceat((quals != dflt).astype(np.int64), ro[:-1])
         unforced = rfl == 0
         assert (notd[unforced] <= nq[unforced]).all()
+
+
+def test_normalize_rejects_out_of_range_features(R, gpu_ctx):
+    """A corrupt series can hand the normaliser any position, length or payload offset (the reference throws
+    ArrayIndexOutOfBoundsException there): the record must come back CRAMGPU_ERR_CORRUPT and every other record's bases and
+    scores must be what they are without the corruption -- nothing may be written outside the record."""
+    import types
+    ref, rd, cont_off = _sim(3000, 2, 41)
+    n = len(rd['pos'])
+    enc = R.features_encode(rd, ref, 'N40-I40', cont_off=cont_off, ctx=gpu_ctx)          # sparse Q features, no stored arrays
+    rfl = _nf_flags(enc, rd)
+    win = dict(window=ref, window_start0=0, matrix=enc.matrix, cont_off=cont_off, win_off=np.zeros(2), win_len=np.full(2, ref.size))
+    args = (rd['pos'], rd['read_off'], rfl)
+    kw = dict(qs=enc.streams, read_qs_off=enc.read_qs_off, ba=enc.streams, read_ba_off=enc.read_ba_off, ctx=gpu_ctx, check=False, **win)
+    base_b, base_q, _, base_st = R.normalize_decode(*args, enc, **kw)
+    assert (base_st == 0).all()
+    fo = np.asarray(enc.feat_off, np.int64)
+    op = np.asarray(enc.f_op)
+
+    def first_with(ch, skip=0):
+        idx = np.nonzero(op == ord(ch))[0]
+        return int(idx[skip])
+    bad = types.SimpleNamespace(f_op=op.copy(), f_pos=np.asarray(enc.f_pos).copy(), f_val=np.asarray(enc.f_val).copy(),
+                                f_aux=np.asarray(enc.f_aux).copy(), feat_off=enc.feat_off, payload=enc.payload)
+    hit = []
+    f = first_with('Q'); bad.f_pos[f] = 0; hit.append(f)                       # score written in front of the record
+    f = first_with('Q', 40); bad.f_pos[f] = 1 << 30; hit.append(f)            # ... a gigabyte behind it
+    f = first_with('Q', 90); bad.f_pos[f] = -7; hit.append(f)
+    f = first_with('X', 5); bad.f_pos[f] = 100000; hit.append(f)
+    f = first_with('S'); bad.f_aux[f] = -5; hit.append(f)                      # negative soft-clip length
+    f = first_with('S', 3); bad.f_val[f] = int(enc.payload.size) + 1000; hit.append(f)   # payload offset outside the payload
+    f = first_with('S', 6); bad.f_aux[f] = 1 << 20; hit.append(f)
+    f = first_with('i', 2); bad.f_op[f] = ord('B'); bad.f_pos[f] = 5000; hit.append(f)   # ReadBase far outside
+    recs = sorted({int(np.searchsorted(fo, f, side='right') - 1) for f in hit})
+    assert len(recs) == len(hit)
+    b, q, _, st = R.normalize_decode(*args, bad, **kw)
+    ro = np.asarray(rd['read_off'], np.int64)
+    for r in range(n):
+        if r in recs:
+            assert st[r] == _lib.ERR_CORRUPT, r
+        else:
+            assert st[r] == 0, r
+            assert (b[ro[r]:ro[r + 1]] == base_b[ro[r]:ro[r + 1]]).all() and (q[ro[r]:ro[r + 1]] == base_q[ro[r]:ro[r + 1]]).all(), r

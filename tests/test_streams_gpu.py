@@ -1,0 +1,156 @@
+"""GPU parity for rows W and P against what the reference jar itself wrote and read (tests/golden/streams_jvm.json):
+the series cramgpu_features_encode packs must equal, byte for byte, the external blocks' raw content that
+ContainerFactory.buildSlice / Writer.write produced in the mini-JVM; cramgpu_features_unpack over the jar's own series
+must return the records the jar's CramRecordReader read back."""
+import base64
+
+import numpy as np
+import pytest
+
+from tests import golden_streams as gs
+
+pytestmark = pytest.mark.gpu
+
+CID = {'BF': 0, 'AP': 1, 'FP': 2, 'FC': 3, 'QS': 4, 'DL': 5, 'BA': 6, 'TN': 7, 'NF': 8, 'RL': 9, 'RG': 10, 'MQ': 11, 'RN': 12,
+       'NP': 13, 'TS': 14, 'FN': 15, 'BS': 16, 'IN': 17, 'TC': 18, 'MF': 19, 'NS': 20, 'CF': 21, 'TL': 24, 'RI': 25, 'RS': 26,
+       'SC': 27, 'HC': 28, 'PD': 29}
+
+
+@pytest.fixture(scope='module')
+def R():
+    from cramtools_b200 import records
+    return records
+
+
+@pytest.fixture(scope='module')
+def G():
+    return gs.load()
+
+
+def test_feature_series_match_jar(R, G, gpu_ctx):
+    g, ref, conts = G
+    for c, rd, series in conts:
+        enc = R.features_encode(rd, ref, None, ctx=gpu_ctx)
+        assert enc.matrix[0, :5].tobytes() == base64.b64decode(c['subst_matrix']), c['tag']
+        for nm in R.SERIES:
+            assert enc.series(0, nm) == series.get(CID[nm], b''), (c['tag'], nm)
+
+
+def test_all_containers_in_one_call_match_jar(R, G, gpu_ctx):
+    """the three slices as one batch of three containers"""
+    g, ref, conts = G
+    cat = {}
+    for k in ('bases', 'quals', 'cigar'):
+        cat[k] = np.concatenate([rd[k] for _, rd, _ in conts])
+    for k in ('pos', 'flag', 'mapq', 'rflags'):
+        cat[k] = np.concatenate([rd[k] for _, rd, _ in conts])
+    ro, co, cont_off = [np.zeros(1, np.int64)], [np.zeros(1, np.int64)], [0]
+    for _, rd, _ in conts:
+        ro.append(rd['read_off'][1:] + ro[-1][-1]); co.append(rd['cigar_off'][1:] + co[-1][-1]); cont_off.append(cont_off[-1] + len(rd['pos']))
+    cat['read_off'] = np.concatenate(ro); cat['cigar_off'] = np.concatenate(co)
+    enc = R.features_encode(cat, ref, None, cont_off=np.array(cont_off, np.uint64), ctx=gpu_ctx)
+    for ci, (c, rd, series) in enumerate(conts):
+        assert enc.matrix[ci, :5].tobytes() == base64.b64decode(c['subst_matrix']), c['tag']
+        for nm in R.SERIES:
+            assert enc.series(ci, nm) == series.get(CID[nm], b''), (c['tag'], nm)
+
+
+def test_unpack_matches_jar_reader(R, G, gpu_ctx):
+    g, ref, conts = G
+    for c, rd, series in conts:
+        back = c['read_back']
+        n = len(back)
+        # the jar's series laid out the way the decoder leaves them: every series at a multiple of 16
+        buf, off, ln = bytearray(), np.zeros((1, len(R.SERIES)), np.uint64), np.zeros((1, len(R.SERIES)), np.uint64)
+        for i, nm in enumerate(R.SERIES):
+            b = series.get(CID[nm], b'')
+            off[0, i] = len(buf); ln[0, i] = len(b)
+            buf += b + b'\0' * (-len(b) % 16)
+        streams = np.frombuffer(bytes(buf) + b'\0' * 16, np.uint8)
+        read_off = np.concatenate([[0], np.cumsum([b['read_length'] for b in back])]).astype(np.uint64)
+        rfl = np.array([(b['cf'] & 1) | (2 if b['flags'] & 4 else 0) | (4 if b['cf'] & 8 else 0) for b in back], np.uint8)
+        up = R.features_unpack(streams, off, ln, read_off, rfl, ctx=gpu_ctx)
+        assert (up.status == 0).all()
+        qs0, ba0 = int(off[0, R.SERIES.index('QS')]), int(off[0, R.SERIES.index('BA')])
+        for i, b in enumerate(back):
+            f0, f1 = int(up.feat_off[i]), int(up.feat_off[i + 1])
+            got = []
+            for f in range(f0, f1):
+                op = chr(up.f_op[f])
+                if op == 'S':
+                    o, l = int(up.f_val[f]), int(up.f_aux[f])
+                    got.append([op, int(up.f_pos[f]), base64.b64encode(up.payload[o:o + l].tobytes()).decode()])
+                else:
+                    got.append([op, int(up.f_pos[f]), int(up.f_val[f])])
+            want = [[f[0], f[1], f[4]] if f[0] == 'X' else f for f in (b['features'] or [])]
+            assert got == want, (c['tag'], i, b['name'])
+            if not b['flags'] & 4:
+                assert int(up.mapq[i]) == b['mapq'], (c['tag'], i)
+            rl = b['read_length']
+            if b['cf'] & 1 and b['quals'] is not None:
+                o = int(up.read_qs_off[i])
+                assert streams[o:o + rl].tobytes() == base64.b64decode(b['quals']), (c['tag'], i)
+            if b['flags'] & 4 and b['bases'] is not None:
+                o = int(up.read_ba_off[i])
+                assert streams[o:o + rl].tobytes() == base64.b64decode(b['bases']), (c['tag'], i)
+
+
+def _host_fields(c, rd):
+    sc = c['scalars']
+    return dict(flag=rd['flag'], pos=rd['pos'], read_off=rd['read_off'], slice_start=[c['slice']['alignment_start']],
+                multi_ref=[1 if c['slice']['sequence_id'] == -2 else 0], ap_delta=bool(c['ap_delta']),
+                names_included=bool(c['read_names_included']), ref_id=[s['seq_id'] for s in sc],
+                read_group=[s['read_group'] for s in sc], names=[s['name'] for s in sc], mate_ref_id=[s['mate_seq_id'] for s in sc],
+                mate_pos=[s['mate_start'] for s in sc], tlen=[s['tlen'] for s in sc], nf=[s['nf'] for s in sc])
+
+
+def test_host_series_match_jar(R, G, gpu_ctx):
+    """BF CF RI RL AP RG RN MF NS NP TS NF TL from the records' scalars (mate linking done by the jar's setMateInfo): BF / MF
+    derived from the SAM flags on the device, CF once handed over whole and once composed from its parts"""
+    g, ref, conts = G
+    for c, rd, series in conts:
+        sc = c['scalars']
+        kw = _host_fields(c, rd)
+        full = R.host_series_pack(cf=[s['cf'] for s in sc], ctx=gpu_ctx, **kw)
+        enc = R.features_encode(rd, ref, None, ctx=gpu_ctx)
+        parts = R.host_series_pack(mate_cf=[s['cf'] & 6 for s in sc], force_qs=enc.force_qs, rflags=rd['rflags'], ctx=gpu_ctx, **kw)
+        for nm in R.HOST_SERIES:
+            want = series.get(CID[nm], b'')
+            assert full.series(0, nm) == want, (c['tag'], nm)
+            assert parts.series(0, nm) == want, (c['tag'], nm, 'cf composed')
+
+
+def test_host_series_multi_container_and_options(R, G, gpu_ctx):
+    """the three slices as one batch (per-container slice start / multi-reference flag), against the oracle's restatement too"""
+    from oracle import records as orec
+    g, ref, conts = G
+    same = [x for x in conts if x[0]['ap_delta'] == conts[0][0]['ap_delta'] and x[0]['read_names_included'] == conts[0][0]['read_names_included']]
+    assert len(same) >= 2
+    cat = {k: [] for k in ('flag', 'pos', 'ref_id', 'read_group', 'names', 'mate_ref_id', 'mate_pos', 'tlen', 'nf', 'cf')}
+    ro, cont_off, ss, mr = [np.zeros(1, np.int64)], [0], [], []
+    for c, rd, _ in same:
+        kw = _host_fields(c, rd)
+        for k in ('flag', 'pos', 'ref_id', 'read_group', 'names', 'mate_ref_id', 'mate_pos', 'tlen', 'nf'):
+            cat[k] += list(kw[k])
+        cat['cf'] += [s['cf'] for s in c['scalars']]
+        ro.append(rd['read_off'][1:] + ro[-1][-1]); cont_off.append(cont_off[-1] + len(rd['pos']))
+        ss.append(c['slice']['alignment_start']); mr.append(1 if c['slice']['sequence_id'] == -2 else 0)
+    got = R.host_series_pack(cat['flag'], cat['pos'], np.concatenate(ro), cont_off=cont_off, slice_start=ss, multi_ref=mr,
+                             ap_delta=bool(same[0][0]['ap_delta']), names_included=bool(same[0][0]['read_names_included']),
+                             cf=cat['cf'], ref_id=cat['ref_id'], read_group=cat['read_group'], names=cat['names'],
+                             mate_ref_id=cat['mate_ref_id'], mate_pos=cat['mate_pos'], tlen=cat['tlen'], nf=cat['nf'], ctx=gpu_ctx)
+    for ci, (c, rd, series) in enumerate(same):
+        for nm in R.HOST_SERIES:
+            assert got.series(ci, nm) == series.get(CID[nm], b''), (c['tag'], nm)
+    # names for every record (CompressionHeader.readNamesIncluded) and absolute AP: against the oracle's restatement of the Writer
+    c, rd, _ = conts[0]
+    sc = [dict(flags=s['flags'], cf=s['cf'], seq_id=s['seq_id'], read_length=s['read_length'], start=int(p), read_group=s['read_group'],
+               name=s['name'], mate_flags=s['mate_flags'], mate_seq_id=s['mate_seq_id'], mate_start=s['mate_start'], tlen=s['tlen'],
+               nf=s['nf'], tl=0) for s, p in zip(c['scalars'], rd['pos'])]
+    for apd, named in ((False, True), (True, True), (False, False)):
+        want = orec.write_host_streams(sc, apd, c['slice']['sequence_id'] == -2, c['slice']['alignment_start'], capture_names=named)
+        kw = _host_fields(c, rd)
+        kw.update(ap_delta=apd, names_included=named)
+        got = R.host_series_pack(cf=[s['cf'] for s in c['scalars']], ctx=gpu_ctx, **kw)
+        for nm in R.HOST_SERIES:
+            assert got.series(0, nm) == want[nm], (apd, named, nm)
