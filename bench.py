@@ -6,8 +6,9 @@
 Workload (BASELINE.json configs[2], "chr20-scale"): C containers PER GPU of 10 000 simulated 150 bp reads each at
 ~45x over a random reference, lossless quality scores.  A "step" is one pass of the whole hot path over this GPU's
 containers:
-    encode  feature extraction + substitution matrix + series packing  ->  rANS of the slice's rANS-coded series
-            (QS, BA from the device; BF, CF, RL, RG, NS, TS order 1 and AP order 0 as the Java host hands them over)
+    encode  feature extraction + substitution matrix + series packing (read features and the record fields in front of
+            them: flags, lengths, positions, read groups, names, mate fields)  ->  rANS of the slice's rANS-coded series
+            (QS, BA, BF, CF, RL, RG, NS, TS order 1 and AP order 0)
     decode  rANS decode of the same blocks  ->  base and quality restoration of every record
 Containers are independent and dealt round-robin to the ranks (weak scaling); the only collective is an all-gather
 of per-container compressed sizes, from which every rank derives its containers' output offsets.
@@ -35,7 +36,9 @@ COVERAGE = 45
 UNIQUE = 32                     # distinct synthetic containers; tiled to --containers (every copy lives in HBM)
 METRIC = 'cram_encode_decode_reads_per_s'
 UNIT = 'reads/s'
-EXTRA = [('BF', 1), ('CF', 1), ('RL', 1), ('RG', 1), ('NS', 1), ('TS', 1), ('AP', 0)]   # host-produced rANS series (R0)
+# the record-field series the reference codes with rANS (CompressionHeaderFactory.build [:84-113]); the others
+# (RN MF NP NF TL, RI of single-reference slices is empty) go to gzip on the Java host
+EXTRA = [('BF', 1), ('CF', 1), ('RL', 1), ('RG', 1), ('NS', 1), ('TS', 1), ('AP', 0)]
 
 
 def measured_peaks():
@@ -80,26 +83,26 @@ def itf8_pack_np(v):
 
 
 def unique_containers(n_unique, seed):
-    """n_unique coordinate-sorted containers over one synthetic contig; returns (ref, rd, extra) where extra[c] is the list of
-    host-produced series of container c in EXTRA order (what htsjdk's Writer would hand to the rANS block codec)."""
+    """n_unique coordinate-sorted containers over one synthetic contig: (ref, rd).  rd also carries what the record fields
+    in front of the read features are made of (Writer.write [Writer.java:139-172]): read names (`names` u8 concatenated,
+    `name_off`) and a read-group index per read.  The reads are single-end, so every record is detached
+    (CramSerilization.setMateInfo, :278-285): MF 0, NS -1, NP 0, TS 0."""
     from cramtools_b200 import synth
     n = n_unique * READS_PER_CONTAINER
     ref_len = n * READ_LEN // COVERAGE + 4096
     ref = synth.reference(ref_len, seed)
     rd = synth.reads(ref, n, seed + 1, read_len=READ_LEN, with_names=False)
-    extra = []
-    for c in range(n_unique):
-        a, b = c * READS_PER_CONTAINER, (c + 1) * READS_PER_CONTAINER
-        flag, pos = rd['flag'][a:b].astype(np.int64), rd['pos'][a:b].astype(np.int64)
-        bf = np.where(flag & 16, 0x10, 0)                                   # CRAM BF: negative strand bit
-        cf = np.full(b - a, 3, np.uint8)                                    # force-preserve QS | detached
-        rl = np.full(b - a, READ_LEN)
-        rg = np.full(b - a, -1)                                             # no read group -> 5-byte ITF8
-        ns = np.full(b - a, -1)
-        ts = np.zeros(b - a, np.int64)
-        ap = np.diff(np.concatenate([[pos[0]], pos]))                       # AP delta vs previous record
-        extra.append([itf8_pack_np(bf), cf, itf8_pack_np(rl), itf8_pack_np(rg), itf8_pack_np(ns), itf8_pack_np(ts), itf8_pack_np(ap)])
-    return ref, rd, extra
+    rng = np.random.default_rng(seed + 2)
+    # SIM:1:FC01:<lane>:<tile>:<x>:<y>, built vectorised (synth.read_names makes the same kind of name one by one)
+    lane = rng.integers(1, 9, size=n); tile = rng.integers(1101, 2229, size=n); x = rng.integers(1000, 30000, size=n); y = rng.integers(1000, 200000, size=n)
+    names = np.char.add(np.char.add(np.char.add(np.char.add('SIM:1:FC01:', lane.astype('U1')), np.char.add(':', tile.astype('U4'))),
+                                    np.char.add(':', x.astype('U5'))), np.char.add(':', y.astype('U6')))
+    nb = np.char.encode(names, 'ascii')
+    lens = np.char.str_len(names).astype(np.int64)
+    rd['names'] = np.frombuffer(b''.join(nb.tolist()), np.uint8).copy()
+    rd['name_off'] = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    rd['read_group'] = rng.integers(0, 4, size=n).astype(np.int32)
+    return ref, rd
 
 
 def tile_reads(rd, n_unique, n_cont):
@@ -108,18 +111,23 @@ def tile_reads(rd, n_unique, n_cont):
     nr = n_cont * READS_PER_CONTAINER
     nb = int(rd['read_off'][-1])
     ncg = int(rd['cigar_off'][-1])
+    nnm = int(rd['name_off'][-1])
     out = {}
-    for k in ('bases', 'quals', 'cigar', 'pos', 'flag', 'mapq'):
+    for k in ('bases', 'quals', 'cigar', 'pos', 'flag', 'mapq', 'names', 'read_group'):
         out[k] = np.tile(rd[k], reps)
-    ro = (rd['read_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * nb)[:, None]).reshape(-1)
-    co = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg)[:, None]).reshape(-1)
-    out['read_off'] = np.concatenate([ro[:nr], [ro[nr] if nr < ro.size else reps * nb]])
-    out['cigar_off'] = np.concatenate([co[:nr], [co[nr] if nr < co.size else reps * ncg]])
-    for k in ('pos', 'flag', 'mapq'):
+
+    def tile_off(off, total):
+        o = (off[:-1][None, :] + (np.arange(reps, dtype=np.int64) * total)[:, None]).reshape(-1)
+        return np.concatenate([o[:nr], [o[nr] if nr < o.size else reps * total]])
+    out['read_off'] = tile_off(rd['read_off'], nb)
+    out['cigar_off'] = tile_off(rd['cigar_off'], ncg)
+    out['name_off'] = tile_off(rd['name_off'], nnm)
+    for k in ('pos', 'flag', 'mapq', 'read_group'):
         out[k] = out[k][:nr]
     out['bases'] = out['bases'][:int(out['read_off'][-1])]
     out['quals'] = out['quals'][:int(out['read_off'][-1])]
     out['cigar'] = out['cigar'][:int(out['cigar_off'][-1])]
+    out['names'] = out['names'][:int(out['name_off'][-1])]
     return out
 
 
@@ -161,7 +169,7 @@ class ClockSampler(threading.Thread):
 
 def workload_config(args, n_cont, note=''):
     return {'workload': 'chr20-scale slices (BASELINE configs[2]): %d containers/GPU x 10000 simulated 150 bp reads at %dx, '
-                        'lossless QS; encode = features + series packing + rANS (QS, BA, BF, CF, RL, RG, NS, TS o1; AP o0), '
+                        'lossless QS; encode = features + packing of all series (read features and record fields) + rANS (QS, BA, BF, CF, RL, RG, NS, TS o1; AP o0), '
                         'decode = rANS + base/quality restoration' % (n_cont, COVERAGE),
             'containers_per_gpu': n_cont, 'reads_per_container': READS_PER_CONTAINER, 'read_len': READ_LEN,
             'unique_containers': min(UNIQUE, n_cont), 'quality_model': 'lossless',
@@ -172,21 +180,18 @@ def workload_config(args, n_cont, note=''):
 # ------------------------------------------------------------------------------------------- CPU arm
 
 
-def cpu_step_setup(n_cont, seed):
+def cpu_step_setup(n_cont, seed, spec=b'lossless'):
     from oracle import rans as orans
     lib = orans.lib()
     nu = min(UNIQUE, n_cont)
-    ref, rd, extra = unique_containers(nu, seed)
+    ref, rd = unique_containers(nu, seed)
     trd = tile_reads(rd, nu, n_cont)
     i64 = C.POINTER(C.c_int64)
     keep = dict(cont=np.arange(n_cont + 1, dtype=np.int64) * READS_PER_CONTAINER, bases=trd['bases'], quals=trd['quals'],
                 ro=trd['read_off'].astype(np.int64), cg=trd['cigar'], co=trd['cigar_off'].astype(np.int64), pos=trd['pos'].astype(np.int32),
-                flag=trd['flag'].astype(np.uint16), mapq=trd['mapq'].astype(np.uint8), ref=ref)
-    ex = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
-    ex_ptr = np.array([e.ctypes.data for e in ex], np.uint64)
-    ex_len = np.array([e.size for e in ex], np.uint32)
-    ex_ord = np.array([o for _, o in EXTRA], np.uint8)
-    keep.update(ex=ex, ex_ptr=ex_ptr, ex_len=ex_len, ex_ord=ex_ord)
+                flag=trd['flag'].astype(np.uint16), mapq=trd['mapq'].astype(np.uint8), ref=ref,
+                rg=np.ascontiguousarray(trd['read_group'], np.int32), names=np.ascontiguousarray(trd['names'], np.uint8),
+                no=trd['name_off'].astype(np.int64))
     lib.oracle_cram_step.restype = C.c_int
     comp = C.c_int64(0); chk = C.c_uint64(0)
 
@@ -195,9 +200,9 @@ def cpu_step_setup(n_cont, seed):
             C.c_int(threads), C.c_int(n_cont), keep['cont'].ctypes.data_as(i64), C.c_void_p(keep['bases'].ctypes.data),
             C.c_void_p(keep['quals'].ctypes.data), keep['ro'].ctypes.data_as(i64), C.c_void_p(keep['cg'].ctypes.data),
             keep['co'].ctypes.data_as(i64), C.c_void_p(keep['pos'].ctypes.data), C.c_void_p(keep['flag'].ctypes.data),
-            C.c_void_p(keep['mapq'].ctypes.data), C.c_void_p(keep['ref'].ctypes.data), C.c_int64(keep['ref'].size), C.c_int(len(EXTRA)),
-            C.c_void_p(keep['ex_ptr'].ctypes.data), C.c_void_p(keep['ex_len'].ctypes.data), C.c_void_p(keep['ex_ord'].ctypes.data),
-            C.c_char_p(b'lossless'), C.byref(comp), C.byref(chk))
+            C.c_void_p(keep['mapq'].ctypes.data), C.c_void_p(keep['ref'].ctypes.data), C.c_int64(keep['ref'].size),
+            C.c_void_p(keep['rg'].ctypes.data), C.c_void_p(keep['names'].ctypes.data), keep['no'].ctypes.data_as(i64),
+            C.c_char_p(spec), C.byref(comp), C.byref(chk))
         assert rc == 0, 'CPU oracle round trip failed (%d)' % rc
         return comp.value
     return step, keep
@@ -254,37 +259,44 @@ class Lane(object):
     the step of all its lanes, each driven by its own host thread, so that one lane's latency-bound coder kernels
     (a few warps per SM) overlap the other lanes' record kernels and copies."""
 
-    def __init__(self, lane_id, n_cont, ref, rd, extra, nu, dev, rank, world, group, use_unpack=True):
+    def __init__(self, lane_id, n_cont, ref, rd, nu, dev, rank, world, group, use_unpack=True, spec=None):
         import torch
         import cramtools_b200
         from cramtools_b200 import device as dv, records as rec
-        from cramtools_b200._lib import u64p
+        from cramtools_b200._lib import u64p, u8p
         self.torch, self.rec, self.dv = torch, rec, dv
         self.n_cont, self.rank, self.world, self.group, self.dev = n_cont, rank, world, group, dev
         self.use_unpack = use_unpack
+        self.spec = spec
+        self.pol, self.npol = rec._policy_args(spec)
         self.stream = torch.cuda.Stream(device=dev)
         self.ctx = cramtools_b200.Context(dev.index)
         vp = C.c_void_p
         with torch.cuda.stream(self.stream):
             reps = (n_cont + nu - 1) // nu
-            first = (lane_id * 7) % nu                    # lanes start at different unique containers
             n_reads = self.n_reads = n_cont * READS_PER_CONTAINER
-            ncg_u = int(rd['cigar_off'][-1])
+            ncg_u = int(rd['cigar_off'][-1]); nnm_u = int(rd['name_off'][-1])
 
             def up(a, dt):
                 return torch.from_numpy(np.ascontiguousarray(a, dt).view(np.uint8)).to(dev)
 
             def tile_u8(a, dt, n_elems):
                 return up(a, dt).repeat(reps)[:n_elems * np.dtype(dt).itemsize].contiguous()
+
+            def tile_off(off, total):
+                o = (off[:-1][None, :] + (np.arange(reps, dtype=np.int64) * total)[:, None]).reshape(-1)
+                return np.concatenate([o[:n_reads], [o[n_reads] if n_reads < o.size else reps * total]]).astype(np.uint64)
             self.t_bases = tile_u8(rd['bases'], np.uint8, n_reads * READ_LEN)
             self.t_quals = tile_u8(rd['quals'], np.uint8, n_reads * READ_LEN)
             self.t_pos = tile_u8(rd['pos'], np.int32, n_reads); self.t_flag = tile_u8(rd['flag'], np.uint16, n_reads)
             self.t_mapq = tile_u8(rd['mapq'], np.uint8, n_reads)
-            cig_all = np.tile(rd['cigar'], reps)
-            co_all = (rd['cigar_off'][:-1][None, :] + (np.arange(reps, dtype=np.int64) * ncg_u)[:, None]).reshape(-1)
-            co_all = np.concatenate([co_all[:n_reads], [co_all[n_reads] if n_reads < co_all.size else reps * ncg_u]]).astype(np.uint64)
-            self.t_cigar = up(cig_all[:int(co_all[-1])], np.uint32)
+            self.t_rg = tile_u8(rd['read_group'], np.int32, n_reads)
+            co_all = tile_off(rd['cigar_off'], ncg_u)
+            self.t_cigar = up(np.tile(rd['cigar'], reps)[:int(co_all[-1])], np.uint32)
             self.t_coff = up(co_all, np.uint64)
+            no_all = tile_off(rd['name_off'], nnm_u)
+            self.t_names = tile_u8(rd['names'], np.uint8, int(no_all[-1]))
+            self.t_noff = up(no_all, np.uint64)
             self.t_roff = up(np.arange(n_reads + 1, dtype=np.uint64) * READ_LEN, np.uint64)
             self.t_ref = up(ref, np.uint8)
             self.cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
@@ -297,10 +309,26 @@ class Lane(object):
             R.bases = vp(self.t_bases.data_ptr()); R.quals = vp(self.t_quals.data_ptr()); R.read_off = vp(self.t_roff.data_ptr())
             R.cigar = vp(self.t_cigar.data_ptr()); R.cigar_off = vp(self.t_coff.data_ptr()); R.pos = vp(self.t_pos.data_ptr())
             R.flag = vp(self.t_flag.data_ptr()); R.mapq = vp(self.t_mapq.data_ptr()); R.rflags = None
-            # host-produced series, resident: one buffer, 16-byte aligned blocks
-            ex_blocks = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
-            self.t_extra, ex_off, ex_len = dv.pack_blocks(ex_blocks, dev)
-            ex_addr = ex_off + np.uint64(self.t_extra.data_ptr())
+            # region per container = [min start, max end] of its records (CramNormalizer.java:212-225); Slice.alignmentStart = min start
+            p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
+            ws = (p.min(axis=1) - 1)
+            we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
+            self.win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); self.win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
+            self.win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
+            self.slice_start = np.tile(p.min(axis=1), reps)[:n_cont].astype(np.int32)
+            # the record fields in front of the read features, packed on the device (cramgpu_host_series_pack_dev)
+            H = self.H = rec.HostFields()
+            H.n_reads = n_reads; H.n_containers = n_cont
+            H.cont_off = self.cont_off.ctypes.data_as(u64p); H.slice_start = self.slice_start.ctypes.data_as(C.POINTER(C.c_int32))
+            H.multi_ref = None; H.ap_delta = 1; H.names_included = 0
+            H.flag = vp(self.t_flag.data_ptr()); H.cf = None; H.mate_cf = None; H.force_qs = None; H.rflags = None
+            H.ref_id = None; H.pos = vp(self.t_pos.data_ptr()); H.read_off = vp(self.t_roff.data_ptr()); H.read_group = vp(self.t_rg.data_ptr())
+            H.names = vp(self.t_names.data_ptr()); H.name_off = vp(self.t_noff.data_ptr())
+            H.mate_ref_id = None; H.mate_pos = None; H.tlen = None; H.nf = None; H.tl = None
+            self.HS = rec.HostSeries()
+            NHS = len(rec.HOST_SERIES)
+            self.hoff = np.zeros((n_cont, NHS), np.uint64); self.hlen = np.zeros((n_cont, NHS), np.uint64)
+            self.KX = [rec.HOST_SERIES.index(nm) for nm, _ in EXTRA]
             NX = len(EXTRA)
             NB = self.NB = 2 + NX                               # rANS blocks per container: QS, BA, then EXTRA
             nblk = self.nblk = n_cont * NB
@@ -309,18 +337,10 @@ class Lane(object):
             self.soff = np.zeros((n_cont, 12), np.uint64); self.slen = np.zeros((n_cont, 12), np.uint64)
             self.F = rec.Features()
             self.in_addr = np.zeros(nblk, np.uint64); self.in_len = np.zeros(nblk, np.uint32)
-            self.in_addr.reshape(n_cont, NB)[:, 2:] = ex_addr.reshape(n_cont, NX)
-            self.in_len.reshape(n_cont, NB)[:, 2:] = ex_len.reshape(n_cont, NX)
-            self.enc_cap = int(n_reads * READ_LEN * 0.6) + nblk * 4096 + int(ex_len.sum())
+            self.enc_cap = int(n_reads * READ_LEN * 0.6) + nblk * 4096 + n_reads * 16
             self.enc_out = torch.empty(self.enc_cap, dtype=torch.uint8, device=dev)
             self.e_off = torch.empty(nblk + 1, dtype=torch.int64, device=dev); self.e_len = torch.empty(nblk, dtype=torch.int32, device=dev)
             self.e_st = torch.empty(nblk, dtype=torch.int32, device=dev)
-            # region per container = [min start, max end] of its records (CramNormalizer.java:212-225)
-            p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
-            ws = (p.min(axis=1) - 1)
-            we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
-            self.win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); self.win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
-            self.win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
             self.o_bases = torch.empty(n_reads * READ_LEN, dtype=torch.uint8, device=dev); self.o_quals = torch.empty_like(self.o_bases)
             self.o_star = torch.empty(n_reads, dtype=torch.uint8, device=dev); self.o_stat = torch.empty(n_reads, dtype=torch.int32, device=dev)
             self.t_rfl = torch.ones(n_reads, dtype=torch.uint8, device=dev)          # lossless, mapped: force-preserve QS
@@ -333,12 +353,16 @@ class Lane(object):
         from cramtools_b200 import sharding
         from cramtools_b200._lib import u8p, u32p, u64p
         ctx, F, vp = self.ctx, self.F, C.c_void_p
-        ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), None, -1, C.byref(F), self.soff.ctypes.data_as(u64p),
+        ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), self.pol, self.npol, C.byref(F), self.soff.ctypes.data_as(u64p),
                                                       self.slen.ctypes.data_as(u64p), self._sp()))
-        base = np.uint64(F.streams)
+        self.H.force_qs = F.force_qs                     # CF bit 0 comes from the quality model's decision
+        ctx.check(ctx.lib.cramgpu_host_series_pack_dev(ctx.handle, C.byref(self.H), C.byref(self.HS), self.hoff.ctypes.data_as(u64p),
+                                                       self.hlen.ctypes.data_as(u64p), self._sp()))
+        base = np.uint64(F.streams); hbase = np.uint64(self.HS.streams)
         v = self.in_addr.reshape(self.n_cont, self.NB); w = self.in_len.reshape(self.n_cont, self.NB)
         v[:, 0] = base + self.soff[:, self.KQS]; w[:, 0] = self.slen[:, self.KQS]
         v[:, 1] = base + self.soff[:, self.KBA]; w[:, 1] = self.slen[:, self.KBA]
+        v[:, 2:] = hbase + self.hoff[:, self.KX]; w[:, 2:] = self.hlen[:, self.KX]
         ctx.check(ctx.lib.cramgpu_rans_encode_dev(ctx.handle, self.nblk, None, self.in_addr.ctypes.data_as(u64p),
                                                   self.in_len.ctypes.data_as(u32p), self.order.ctypes.data_as(u8p),
                                                   vp(self.enc_out.data_ptr()), C.c_uint64(self.enc_cap), vp(self.e_off.data_ptr()),
@@ -356,6 +380,7 @@ class Lane(object):
         self.stream.synchronize()
         assert int(self.e_st.abs().sum()) == 0, 'rANS encode status'
         nblk, n_cont, NB, n_reads = self.nblk, self.n_cont, self.NB, self.n_reads
+        lossless = self.npol < 0
         with torch.cuda.stream(self.stream):
             self.c_off = self.e_off.cpu().numpy().view(np.uint64)[:-1].copy(); self.c_len = self.e_len.cpu().numpy().view(np.uint32).copy()
             self.comp_bytes = float(self.c_len.sum())
@@ -375,9 +400,15 @@ class Lane(object):
             self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(rq.ctypes.data), vp(self.F.read_qs_off),
                                                              C.c_uint64(rq.nbytes), self._sp()))
             cidx = np.repeat(np.arange(n_cont), READS_PER_CONTAINER)
-            rq_new = rq - self.soff[cidx, self.KQS] + d_off[cidx * NB + 0]
+            rq_new = np.where(rq == np.uint64(0xFFFFFFFFFFFFFFFF), rq, rq - self.soff[cidx, self.KQS] + d_off[cidx * NB + 0])
             self.t_rq = torch.from_numpy(rq_new.view(np.uint8)).to(self.dev)
             self.t_rba = torch.full((n_reads,), -1, dtype=torch.int64, device=self.dev)
+            if not lossless:
+                # CF bit 0 of every record, as the host reads it from the CF series
+                fq = np.empty(n_reads, np.uint8)
+                self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(fq.ctypes.data), vp(self.F.force_qs),
+                                                                 C.c_uint64(n_reads), self._sp()))
+                self.t_rfl = torch.from_numpy((fq & 1).astype(np.uint8)).to(self.dev)
             self.raw_bytes = float(raw.sum())
             self.raw_o0 = float(self.in_len.reshape(n_cont, NB)[:, -1].sum())
             self.qs_bytes = float(self.slen[:, self.KQS].sum())
@@ -400,11 +431,19 @@ class Lane(object):
             SR.stream_off = self.s_addr.ctypes.data_as(u64p); SR.stream_len = self.s_len.ctypes.data_as(u64p)
             SR.read_off = vp(self.t_roff.data_ptr()); SR.rflags = vp(self.t_rfl.data_ptr())
             self.U = rec.Features(); self.d_mapq = C.c_void_p(); self.u_status = np.zeros(n_cont, np.int32)
-        # correctness of what is timed: the round trip restores every base and quality of every read
+        # correctness of what is timed: the round trip restores every base and (lossless) every quality of every read
         self.decode()
         self.stream.synchronize()
-        assert int(self.dd_st.abs().sum()) == 0 and int(self.o_stat.abs().sum()) == 0 and int(self.o_star.sum()) == 0
-        assert torch.equal(self.o_bases, self.t_bases) and torch.equal(self.o_quals, self.t_quals), 'round trip mismatch'
+        assert int(self.dd_st.abs().sum()) == 0 and int(self.o_stat.abs().sum()) == 0
+        assert torch.equal(self.o_bases, self.t_bases), 'round trip mismatch (bases)'
+        if lossless:
+            assert int(self.o_star.sum()) == 0 and torch.equal(self.o_quals, self.t_quals), 'round trip mismatch (qualities)'
+        # the decoded record-field series are the packed ones
+        for k in range(2, NB):
+            a = int(self.in_addr[k]) - int(self.HS.streams); ln = int(self.in_len[k])
+            want = self.dv.dev_to_numpy(self.ctx, int(self.HS.streams) + a, ln, np.uint8)
+            got = self.dec_out[int(d_off[k]):int(d_off[k]) + ln].cpu().numpy()
+            assert np.array_equal(got, want), 'record-field series round trip mismatch'
         if self.use_unpack:
             got = np.empty(n_reads, np.uint8)
             self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(got.ctypes.data), self.d_mapq, C.c_uint64(n_reads), self._sp()))
@@ -440,6 +479,29 @@ class Lane(object):
             self.encode()
             self.decode()
 
+    def timed(self, steps, warmup):
+        """`steps` unpipelined steps on this lane's stream, device-timed: (ms per step, isolated kernel times of one step)"""
+        torch = self.torch
+        self.steps(warmup)
+        self.stream.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(self.stream)
+        self.steps(steps)
+        e1.record(self.stream)
+        self.stream.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        self.ctx.profile_enable(True)
+        self.steps(1)
+        self.stream.synchronize()
+        kt = {}
+        for name, m in self.ctx.profile_read():
+            kt[name] = kt.get(name, 0.0) + m
+        self.ctx.profile_enable(False)
+        return ms, kt
+
+    def close(self):
+        self.ctx.close()
+
 
 def run_ours(args):
     import torch
@@ -457,7 +519,7 @@ def run_ours(args):
 
     n_cont = args.containers
     nu = min(UNIQUE, n_cont)
-    ref, rd, extra = unique_containers(nu, 1000 + 17 * rank)
+    ref, rd = unique_containers(nu, 1000 + 17 * rank)
     # Software pipeline over consecutive steps: `depth` contexts, each with its own stream and the whole batch; step i runs
     # on context i % depth.  The order-1 decoder is a recurrence per rANS state -- a few warps per SM for tens of
     # milliseconds, whatever the batch size -- so the encode of step i+1 (record kernels, histograms, encoder) runs beside
@@ -465,7 +527,7 @@ def run_ours(args):
     # Two host locks keep at most one context in each phase.
     n_lanes = depth = max(1, args.pipeline)
     groups = [dist.new_group() if world > 1 else None for _ in range(depth)]
-    lanes = [Lane(i, n_cont, ref, rd, extra, nu, dev, rank, world, groups[i], not args.no_unpack) for i in range(depth)]
+    lanes = [Lane(i, n_cont, ref, rd, nu, dev, rank, world, groups[i], not args.no_unpack) for i in range(depth)]
     for ln in lanes:
         ln.prepare()
     n_reads = lanes[0].n_reads
@@ -535,6 +597,49 @@ def run_ours(args):
     kcount = {k: len(v) / args.steps for k, v in kt.items()}
     top = max(kavg, key=kavg.get)
 
+    def max_over_ranks(x):
+        t_ = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+        return float(t_.item())
+
+    # ---- what the pipelined spans cannot say: one context alone, phases back to back -> true kernel durations
+    for ln in lanes[1:]:
+        ln.close()
+    ms_unpip, kiso = lanes[0].timed(2, 1)
+    ms_unpip = max_over_ranks(ms_unpip)
+
+    # ---- the other configurations north_star names, each a short unpipelined run of the same step
+    def leg(nc, spec, steps=2, warmup=1):
+        ln_ = Lane(0, nc, ref, rd, nu, dev, rank, world, groups[0], not args.no_unpack, spec=spec)
+        ln_.prepare()
+        m_, k_ = ln_.timed(steps, warmup)
+        ln_.close()
+        del ln_
+        torch.cuda.empty_cache()
+        m_ = max_over_ranks(m_)
+        return {'containers_per_gpu': nc, 'ms_per_step': m_, 'reads_per_s': nc * READS_PER_CONTAINER * world / (m_ * 1e-3),
+                'kernels_ms': {k: round(v, 3) for k, v in k_.items() if v >= 0.05}}
+    extra_legs = {}
+    if not args.no_configs:
+        # configs[3]: the lossy quality models on the same workload
+        extra_legs['config4_quality_models'] = {sp: leg(n_cont, sp) for sp in ('*8', 'm5', 'N40-D8')}
+        extra_legs['config4_quality_models']['lossless'] = {'containers_per_gpu': n_cont, 'ms_per_step': ms_unpip,
+                                                            'reads_per_s': n_reads * world / (ms_unpip * 1e-3)}
+        # configs[0]: 200 000 reads = 20 containers in all: one coder block's latency whatever the GPU count
+        nc1 = max(1, -(-20 // world))
+        extra_legs['config1_20_containers'] = leg(nc1, None, steps=3, warmup=2)
+        # configs[2] at its stated FIXED size: 2 048 containers in all, 2048 / N per GPU (strong scaling); at N = 1 that is the main run
+        if world > 1 and n_cont == 2048:
+            st_ = leg(max(1, 2048 // world), None, steps=3, warmup=2)
+            st_['speedup_vs_one_gpu_unpipelined'] = ms_unpip / st_['ms_per_step']
+            st_['limiter'] = 'single-block coder latency: a call takes one quality block\'s chain (375 000 dependent steps per rANS state) however few blocks a GPU holds'
+            extra_legs['config3_fixed_total_2048_containers'] = st_
+        else:
+            extra_legs['config3_fixed_total_2048_containers'] = {'containers_per_gpu': n_cont, 'ms_per_step': ms_unpip,
+                                                                 'reads_per_s': n_reads * world / (ms_unpip * 1e-3),
+                                                                 'note': 'N = 1: the fixed-size configuration is the main run (unpipelined figure)'}
+
     # ---- end-to-end through the host-buffer C ABI (bounded to keep pinned host memory modest at 8 ranks)
     # every rank page-locks its own buffers (~21 MB per container with four contexts): keep all ranks of the node together
     # under 40 % of the free host memory
@@ -542,7 +647,7 @@ def run_ours(args):
     try:
         import psutil
         per_rank = 0.4 * psutil.virtual_memory().available / max(world, 1)
-        n_e2e = int(max(128, min(n_e2e, per_rank // (21 << 20))))
+        n_e2e = min(n_cont, int(max(128, min(n_e2e, per_rank // (21 << 20)))))
     except Exception:      # noqa: BLE001
         n_e2e = min(n_e2e, max(128, 2 * args.e2e_containers // max(world, 2))) if world > 1 else n_e2e
     if world > 1:
@@ -551,22 +656,24 @@ def run_ours(args):
         n_e2e = int(t_n.item())
     st0 = lanes[0]
     stats = dict(raw_bytes=st0.raw_bytes, comp_bytes=st0.comp_bytes, raw_o0=st0.raw_o0, qs_bytes=st0.qs_bytes, nblk=st0.nblk)
+    stats['comp_qs'] = float(st0.c_len.reshape(st0.n_cont, st0.NB)[:, 0].sum())
     comp_hint = st0.c_len[:n_e2e * st0.NB].copy()
     # the device-resident leg is over: its buffers and contexts go before the end-to-end leg allocates its own
-    for ln in lanes:
-        ln.ctx.close()
+    lanes[0].close()
     del lanes, st0, ln
     import gc
     gc.collect()
     torch.cuda.empty_cache()
-    e2e = run_e2e(args, ref, rd, extra, nu, n_e2e, world, barrier, args.e2e_pipeline, comp_hint, local)
+    e2e = run_e2e(args, ref, rd, nu, n_e2e, world, barrier, args.e2e_pipeline, comp_hint, local)
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
         raw_bytes = stats['raw_bytes']; comp_bytes = stats['comp_bytes']
         o1_raw = raw_bytes - stats['raw_o0']
         comp1 = comp_bytes * (o1_raw / raw_bytes)
-        algo = {'k_enc1': o1_raw + comp1, 'k_dec1': o1_raw + comp1, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
+        # k_dec1 decodes the long blocks (the quality series) when the short ones ride beside it in k_dec1s
+        dec1_bytes = (stats['qs_bytes'] + stats['comp_qs']) if 'k_dec1s' in kavg else (o1_raw + comp1)
+        algo = {'k_enc1': o1_raw + comp1, 'k_dec1': dec1_bytes, 'k_hist1': o1_raw, 'k_hist0': raw_bytes,
                 'k_rec_simple_count': n_reads * (2 * READ_LEN + 40.0), 'k_rec_simple_write': n_reads * (2 * READ_LEN + 60.0),
                 'k_norm_simple': n_reads * (4 * READ_LEN + 40.0), 'k_pack': 2 * comp_bytes}
         ab = algo.get(top)
@@ -574,8 +681,10 @@ def run_ours(args):
         per_launch_ms = kavg[top] / max(kcount[top], 1)
         achieved = (ab / max(kcount[top], 1)) / (per_launch_ms * 1e-3) / 1e9 if ab else None
         peak = float(peaks['hbm_gbs'])
-        rans_ms_enc = sum(v for k, v in kavg.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
-        rans_ms_dec = sum(v for k, v in kavg.items() if k in ('k_dec_tables', 'k_dec0', 'k_dec1', 'k_dec1_big'))
+        # rANS GB/s from the ISOLATED kernel durations (one context, phases back to back); k_dec1s / k_dec0 / k_dec1_big run
+        # beside k_dec1, their spans lie inside its
+        rans_ms_enc = sum(v for k, v in kiso.items() if k in ('k_hist0', 'k_prep_o1', 'k_hist1', 'k_tables0', 'k_tables1', 'k_enc0', 'k_enc1', 'k_scan_out', 'k_pack'))
+        rans_ms_dec = sum(v for k, v in kiso.items() if k in ('k_dec_tables', 'k_dec_plan', 'k_dec1'))
         cfg = workload_config(args, n_cont)
         cfg['decode_features'] = 'taken from the encoder' if args.no_unpack else 'unpacked from the decoded series on the device (k_unpack, row P)'
         cfg['pipeline'] = ('%d contexts/streams per GPU, step i on context i %% %d: encode of step i+1 overlaps decode of step i' % (depth, depth)) if depth > 1 else 'none: one stream, phases back to back'
@@ -587,7 +696,11 @@ def run_ours(args):
                      'encode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_enc * 1e-3) / 1e9,
                      'decode_GBps_per_gpu_kernel_time': raw_bytes / (rans_ms_dec * 1e-3) / 1e9,
                      'qs_block_bytes': stats['qs_bytes'] / n_cont, 'state_lanes_in_flight': int(4 * stats['nblk'])},
-            'kernels_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
+            'kernels_ms': {k: round(v, 4) for k, v in kiso.items()},
+            'kernels_ms_note': 'durations of one unpipelined step on one context (CUDA events around every launch); kernels that '
+                               'run beside k_dec1 on another stream (k_dec1s, k_dec1_big, k_dec0) include their wait for SM resources',
+            'ms_per_step_unpipelined': ms_unpip,
+            'pipelined_spans_ms': {k: round(v, 4) for k, v in kavg.items()}, 'kernel_launches_per_step': {k: v for k, v in kcount.items()},
             'gpu_launches': int(launches),
             'roofline': {'bound': 'hbm', 'kernel': top, 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                          'frac': achieved / peak if achieved else None, 'traffic': ncu_traffic(top, n_cont), 'peak_kind': peak_kind,
@@ -597,6 +710,7 @@ def run_ours(args):
                                  'clock / cycles per step (DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
             'e2e': e2e, 'clocks': clocks,
         }
+        line.update(extra_legs)
         if world == 1 and not args.no_cpu:
             line['cpu_baseline'] = cpu_baseline(args)
         print(json.dumps(line))
@@ -618,7 +732,9 @@ class E2EContext(object):
         nblk = self.nblk = n_cont * NB
         self.F, self.D = rec.Features(), rec.Features()
         self.in_ptr = np.zeros(nblk, np.uint64); self.in_len = np.zeros(nblk, np.uint32)
-        self.in_ptr.reshape(n_cont, NB)[:, 2:] = inp['ex_ptr']; self.in_len.reshape(n_cont, NB)[:, 2:] = inp['ex_len']
+        self.HS, self.HD = rec.HostSeries(), rec.HostSeries()
+        self.H = rec.HostFields()
+        C.memmove(C.byref(self.H), C.byref(inp['H']), C.sizeof(rec.HostFields))       # force_qs is set per step
         # compressed blocks, the product of the encode side: one pinned buffer, a slot per block.  (The reference allocates
         # rans_bound(n) per block and trims; here the slots are the sizes the device-resident leg saw plus a margin, so that
         # the page-locked memory stays in proportion to the data.)
@@ -651,7 +767,8 @@ class E2EContext(object):
         N.win_start0 = inp['win_s0'].ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(inp['ref'].ctypes.data); N.ref_total = inp['ref'].size
         N.pos = vp(inp['a']['pos'].ctypes.data); N.read_off = vp(inp['a']['read_off'].ctypes.data); N.rflags = vp(self.rfl.ctypes.data)
         N.ba = vp(self.d_back.data_ptr()); N.read_ba_off = vp(self.rba.ctypes.data); N.qs = vp(self.d_back.data_ptr())
-        self.ms = {'features_encode_resident': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0, 'normalize_decode': 0.0, 'host_glue': 0.0}
+        self.ms = {'features_encode_resident': 0.0, 'host_series_pack_resident': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0,
+                   'normalize_decode': 0.0, 'host_glue': 0.0}
         self.h2d = self.d2h = 0
         self.stages = (self.stage_features, self.stage_rans_encode, self.stage_rans_decode, self.stage_normalize)
 
@@ -668,7 +785,13 @@ class E2EContext(object):
         ctx, inp, F, D = self.ctx, self.inp, self.F, self.D
         t0 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(inp['R']), None, -1, inp['host_series'], C.byref(F), C.byref(D)))
-        self.ms['features_encode_resident'] += (time.perf_counter() - t0) * 1e3
+        t1 = time.perf_counter()
+        # the record fields in front of the features: the rANS-coded series stay on the device, the gzip ones come back
+        # (RN is not sent at all: packing names is a plain copy the Java host does itself)
+        self.H.force_qs = D.force_qs
+        ctx.check(ctx.lib.cramgpu_host_series_pack_resident(ctx.handle, C.byref(self.H), inp['hs_mask'], C.byref(self.HS), C.byref(self.HD)))
+        t2 = time.perf_counter()
+        self.ms['features_encode_resident'] += (t1 - t0) * 1e3; self.ms['host_series_pack_resident'] += (t2 - t1) * 1e3
 
     def stage_rans_encode(self):
         """series -> compressed blocks (host)"""
@@ -681,6 +804,11 @@ class E2EContext(object):
         KQS, KBA = inp['KQS'], inp['KBA']
         v[:, 0] = np.uint64(D.streams) + self.soff[:, KQS]; w[:, 0] = self.slen[:, KQS]      # QS and BA: coded where they are, on the device
         v[:, 1] = np.uint64(D.streams) + self.soff[:, KBA]; w[:, 1] = self.slen[:, KBA]
+        NHS = len(rec.HOST_SERIES)
+        hoff = np.ctypeslib.as_array(C.cast(self.HS.stream_off, u64p), (n_cont, NHS)); hlen = np.ctypeslib.as_array(C.cast(self.HS.stream_len, u64p), (n_cont, NHS))
+        v[:, 2:] = np.uint64(self.HD.streams) + hoff[:, inp['KX']]; w[:, 2:] = hlen[:, inp['KX']]
+        self.hs_down = int(sum(int(hlen[:, k].sum()) for k in range(NHS) if inp['hs_mask'] & (1 << k)))
+        self.ex_bytes = int(w[:, 2:].sum())
         t2 = time.perf_counter()
         ctx.check(ctx.lib.cramgpu_rans_encode_batch(ctx.handle, self.nblk, C.cast(self.in_ptr.ctypes.data, u8pp), self.in_len.ctypes.data_as(u32p),
                                                     inp['order'].ctypes.data_as(u8p), C.cast(self.out_ptr.ctypes.data, u8pp), self.caps.ctypes.data_as(u32p),
@@ -722,17 +850,18 @@ class E2EContext(object):
         a, nf, nb = inp['a'], int(F.n_feat), n_reads * READ_LEN
         KQS, KBA = inp['KQS'], inp['KBA']
         small = int(self.slen.sum() - self.slen[:, KQS].sum() - self.slen[:, KBA].sum())
-        ex_bytes = int(inp['ex_len'].sum())
+        ex_bytes = self.ex_bytes
         comp_bytes = int(self.out_len.sum())
         self.h2d = int(2 * nb + inp['ref'].size + a['read_off'].nbytes + a['cigar_off'].nbytes + a['cigar'].nbytes + 7 * n_reads      # reads
-                       + ex_bytes                                                                                         # host-produced series
+                       + (2 + 4 + 8 + 4) * n_reads                                                                        # record fields: flag, pos, read_off, read group
                        + comp_bytes                                                                                       # compressed blocks, decode side
                        + inp['ref'].size + 37 * n_reads + 17 * nf + int(F.payload_len))                                   # records + features, decode side
         self.d2h = int(17 * nf + 25 * n_reads + int(F.payload_len) + small                                                # features, tables, small series
+                       + self.hs_down                                                                                     # record-field series the host gzips
                        + comp_bytes + ex_bytes + 2 * nb + 5 * n_reads)
 
 
-def run_e2e(args, ref, rd, extra, nu, n_cont, world, barrier, depth, comp_hint, device):
+def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device):
     """the same step through the host-memory entry points: inputs start in (pinned) host memory, the compressed blocks and
     the restored bases / qualities end in host memory, every copy inside the timed region.  Intermediate series the host
     does not parse (QS, BA) stay on the device between the calls.  `depth` contexts take consecutive steps in turn, each call
@@ -773,14 +902,21 @@ def run_e2e(args, ref, rd, extra, nu, n_cont, world, barrier, depth, comp_hint, 
         setattr(R, k, vp(v.ctypes.data))
     R.rflags = None
     NX = len(EXTRA); NB = 2 + NX
-    ex = [np.ascontiguousarray(e, np.uint8) for c in range(n_cont) for e in extra[c % nu]]
+    rg = pinned(trd['read_group'].astype(np.int32))
     p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
     reps = (n_cont + nu - 1) // nu
     ws = (p.min(axis=1) - 1); we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
     KQS, KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
-    inp = dict(n_cont=n_cont, n_reads=n_reads, NB=NB, R=R, a=a, ref=ref, cont_off=cont_off, keep=[ref_off, ref_len, ex],
-               ex_ptr=np.array([e.ctypes.data for e in ex], np.uint64).reshape(n_cont, NX),
-               ex_len=np.array([e.size for e in ex], np.uint32).reshape(n_cont, NX),
+    slice_start = np.tile(p.min(axis=1), reps)[:n_cont].astype(np.int32)
+    H = rec.HostFields()
+    H.n_reads = n_reads; H.n_containers = n_cont
+    H.cont_off = cont_off.ctypes.data_as(u64p); H.slice_start = slice_start.ctypes.data_as(C.POINTER(C.c_int32)); H.multi_ref = None
+    H.ap_delta = 1; H.names_included = 0
+    H.flag = vp(a['flag'].ctypes.data); H.pos = vp(a['pos'].ctypes.data); H.read_off = vp(a['read_off'].ctypes.data); H.read_group = vp(rg.ctypes.data)
+    KX = [rec.HOST_SERIES.index(nm) for nm, _ in EXTRA]
+    hs_mask = sum(1 << k for k in range(len(rec.HOST_SERIES)) if k not in KX and rec.HOST_SERIES[k] != 'RN')
+    inp = dict(n_cont=n_cont, n_reads=n_reads, NB=NB, R=R, a=a, ref=ref, cont_off=cont_off, keep=[ref_off, ref_len, rg, slice_start],
+               H=H, KX=KX, hs_mask=hs_mask,
                order=np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont), KQS=KQS, KBA=KBA,
                host_series=sum(1 << k for k in range(len(rec.SERIES)) if k not in (KQS, KBA)), comp_hint=comp_hint,
                win_off=np.tile(ws, reps)[:n_cont].astype(np.uint64), win_len=np.tile(we - ws, reps)[:n_cont].astype(np.uint64),
@@ -831,9 +967,81 @@ def run_e2e(args, ref, rd, extra, nu, n_cont, world, barrier, depth, comp_hint, 
     calls = {kk: round(sum(ln.ms[kk] for ln in lanes) / k, 2) for kk in lanes[0].ms}
     return {'value': n_reads * world / (ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': lanes[0].h2d, 'd2h_bytes_per_step': lanes[0].d2h,
             'ms_per_step': ms, 'containers_per_gpu': n_cont, 'steps': k, 'contexts': depth, 'calls_ms': calls,
-            'path': 'cramgpu_features_encode_resident -> cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_normalize_decode: '
+            'path': 'cramgpu_features_encode_resident -> cramgpu_host_series_pack_resident -> cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_normalize_decode: '
                     'reads in and compressed blocks + restored bases/qualities out through host buffers, every copy inside the timed '
-                    'region; the QS and BA series stay on the device between the calls'}
+                    'region; the rANS-coded series stay on the device between the calls'}
+
+
+# ------------------------------------------------------------------------------------------- configs[1]: block sweep
+
+
+def run_sweep(args):
+    """BASELINE configs[1]: rANS order-0 / order-1 over blocks of 64 KB - 8 MB of QS-, BA-, RN- and ITF8-like bytes, device
+    resident, byte-identical to the oracle (first block of every cell), CUDA-event timed (best of 3 calls).  Blocks per cell:
+    as many as fill ~1.5 GB, at most 2048.  The ITF8-like stream has > 100 distinct bytes: it takes the large-alphabet
+    decoder.  Prints one JSON line; profiles/r2_rans_block_sweep.txt holds a run."""
+    import torch
+    import cramtools_b200
+    from cramtools_b200 import synth, device as dv
+    from oracle import rans as orans
+    ctx = cramtools_b200.Context(0)
+    rng = np.random.default_rng(5)
+
+    def itf8_wide(n, seed):
+        # template-size-like values: ITF8 of ints around +-400 and mate positions -> all 256 byte values occur
+        r = np.random.default_rng(seed)
+        v = np.concatenate([r.normal(400, 60, n // 6).astype(np.int64), -r.normal(400, 60, n // 6).astype(np.int64), r.integers(1, 1 << 27, n // 6)])
+        r.shuffle(v)
+        return itf8_pack_np(v)[:n]
+    gens = {'QS': synth.qs_stream, 'BA': synth.ba_stream, 'RN': synth.rn_stream, 'ITF8': itf8_wide}
+    sizes = [64 << 10, 128 << 10, 256 << 10, 512 << 10, 1 << 20, 2 << 20, 4 << 20, 8 << 20]
+    rows = []
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    # a stream of our own: the legacy default stream (handle 0) would mean "the context's stream" to the library and the events
+    # would then bracket nothing
+    side = torch.cuda.Stream(device='cuda:0')
+
+    def timed(fn):
+        best = 1e9
+        for _ in range(3):
+            torch.cuda.synchronize()
+            with torch.cuda.stream(side):
+                ev[0].record(side)
+                r_ = fn()
+                ev[1].record(side)
+            torch.cuda.synchronize()
+            best = min(best, ev[0].elapsed_time(ev[1]))
+        return best, r_
+    for kind, gen in gens.items():
+        for size in sizes:
+            nb = int(max(8, min(2048, (1500 << 20) // size)))
+            uniq = [np.ascontiguousarray(gen(size, 100 + i)) for i in range(8)]
+            blocks = [uniq[i % 8] for i in range(nb)]
+            d_in, off, ln = dv.pack_blocks(blocks, 'cuda:0')
+            for order in (0, 1):
+                orders = np.full(nb, order, np.uint8)
+                t_enc, r = timed(lambda: dv.rans_encode_dev(ctx, d_in, off, ln, orders))
+                comp, st = r.to_host()
+                assert (st == 0).all()
+                t0 = time.perf_counter(); want = orans.compress(uniq[0], order); t_ce = time.perf_counter() - t0
+                assert comp[0] == want, (kind, size, order)
+                c_in, c_off, c_len = dv.pack_blocks(comp, 'cuda:0')
+                pref = np.stack([np.frombuffer(c[:9], np.uint8) for c in comp])
+                t_dec, d = timed(lambda: dv.rans_decode_dev(ctx, c_in, c_off, c_len, pref))
+                back, st = d.to_host()
+                assert (st == 0).all() and back[0] == blocks[0].tobytes() and back[-1] == blocks[-1].tobytes()
+                t0 = time.perf_counter(); orans.uncompress(want); t_cd = time.perf_counter() - t0
+                raw = float(nb) * size
+                rows.append({'kind': kind, 'block_bytes': size, 'order': order, 'blocks': nb, 'state_lanes': 4 * nb,
+                             'distinct_bytes': int(np.unique(uniq[0]).size),
+                             'encode_GBps': raw / (t_enc * 1e-3) / 1e9, 'decode_GBps': raw / (t_dec * 1e-3) / 1e9,
+                             'ratio': sum(len(c_) for c_ in comp) / raw, 'cpu_encode_GBps_1core': size / t_ce / 1e9,
+                             'cpu_decode_GBps_1core': size / t_cd / 1e9})
+                del c_in
+            del d_in
+            torch.cuda.empty_cache()
+    print(json.dumps({'sweep': 'rANS block codec, BASELINE configs[1]', 'timing': 'CUDA events around the call, best of 3; GB/s = raw bytes / time',
+                      'rows': rows}))
 
 
 def main():
@@ -848,7 +1056,12 @@ def main():
     ap.add_argument('--e2e-pipeline', type=int, default=4, help='contexts of the end-to-end leg taking consecutive steps in turn')
     ap.add_argument('--no-unpack', action='store_true', help='decode side: take the read features from the encoder instead of unpacking the series (row P)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--no-configs', action='store_true', help='skip the short runs of the other north_star configurations (quality models, 20 containers, fixed total)')
+    ap.add_argument('--sweep', action='store_true', help='BASELINE configs[1]: the rANS block sweep instead of the step benchmark')
     args = ap.parse_args()
+    if args.sweep:
+        run_sweep(args)
+        return
     if args.impl == 'reference':
         run_reference(args)
     else:

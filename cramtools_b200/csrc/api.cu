@@ -485,4 +485,44 @@ int cramgpu_rans_decode_batch(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t 
     return host_batch(ctx, false, nblocks, in, in_len, nullptr, out, out_cap, out_len, status);
 }
 
+// ---- multi-GPU: output offsets and record counters of this rank's containers -----------------------------------------
+// Containers are independent and dealt round-robin (container with global ordinal g goes to rank g % world).  What the
+// writer keeps as running sums -- container.offset (CRAMContainerStreamWriter.java:229-230) and globalRecordCounter
+// (ContainerFactory [ContainerFactory.java:77,105]) -- becomes an exclusive scan over the all-gathered per-container
+// {compressed bytes, records, bases}.  The exchange itself is the caller's: NCCL / gloo through torch.distributed in
+// cramtools_b200/sharding.py, MPI or sockets from a JVM.  Host-only.
+int cramgpu_allgather_sizes(cramgpu_ctx *ctx, uint32_t n_local, const cramgpu_container_size *local, uint32_t rank, uint32_t world,
+                            cramgpu_allgather_fn gather, void *user, uint64_t base_offset, uint64_t base_record,
+                            uint64_t *offset, uint64_t *record_counter, cramgpu_container_size *total)
+{
+    if (world == 0 || rank >= world || (n_local && (!local || !offset || !record_counter)) || (world > 1 && !gather))
+        return ctx ? ctx_fail(ctx, CRAMGPU_ERR_ARG, "bad argument") : CRAMGPU_ERR_ARG;
+    // every rank contributes the same number of slots: the largest local count (ranks may differ by one container)
+    uint64_t nmax = n_local;
+    std::vector<uint64_t> counts(world, n_local);
+    if (world > 1) {
+        uint64_t mine = n_local;
+        if (int rc = gather(user, &mine, counts.data(), sizeof mine)) return ctx ? ctx_fail(ctx, CRAMGPU_ERR_ARG, "all-gather callback failed (%d)", rc) : CRAMGPU_ERR_ARG;
+        for (uint64_t c : counts) nmax = std::max(nmax, c);
+    }
+    std::vector<cramgpu_container_size> send(nmax), all((size_t)nmax * world);
+    for (uint64_t i = 0; i < nmax; i++) send[i] = i < n_local ? local[i] : cramgpu_container_size{0, 0, 0, 0};
+    if (world > 1) {
+        if (nmax)
+            if (int rc = gather(user, send.data(), all.data(), nmax * sizeof(cramgpu_container_size)))
+                return ctx ? ctx_fail(ctx, CRAMGPU_ERR_ARG, "all-gather callback failed (%d)", rc) : CRAMGPU_ERR_ARG;
+    } else all = send;
+    uint64_t off = base_offset, rec = base_record, bases = 0, bytes = 0, recs = 0;
+    for (uint64_t j = 0; j < nmax; j++)              // global ordinal g = j * world + r
+        for (uint32_t r = 0; r < world; r++) {
+            if (j >= counts[r]) continue;
+            const cramgpu_container_size &c = all[(size_t)r * nmax + j];
+            if (r == rank) { offset[j] = off; record_counter[j] = rec; }
+            off += c.compressed_bytes; rec += c.n_records;
+            bytes += c.compressed_bytes; recs += c.n_records; bases += c.n_bases;
+        }
+    if (total) { total->compressed_bytes = bytes; total->n_bases = bases; total->n_records = (uint32_t)std::min<uint64_t>(recs, 0xFFFFFFFFu); total->reserved = 0; }
+    return CRAMGPU_OK;
+}
+
 }  // extern "C"

@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(256) k_hs_write(HsArgs a)
     for (uint64_t t0 = r0; t0 < r1; t0 += 256) {
         const uint64_t r = t0 + threadIdx.x;
         const bool live = r < r1;
-        HsRec v;
+        HsRec v = {};
         HsSizes s = {0, 0, 0, 0};
         if (live) { v = hs_load(a, r, c, r0); s = hs_sizes(v, multi); }
         unsigned long long totA, totB; uint32_t totC, totN;
@@ -224,11 +224,21 @@ __global__ void __launch_bounds__(256) k_hs_write(HsArgs a)
                 hs_itf8_put(S + base[CRAMGPU_HS_NF] + (pc & 0xFFF), v.nf);
             }
             hs_itf8_put(S + base[CRAMGPU_HS_TL] + ((pc >> 12) & 0xFFF), v.tl);
-            if (v.named) {
-                uint8_t *d = S + base[CRAMGPU_HS_RN] + pn;
-                const uint8_t *src = a.names + v.name_at;
-                for (uint32_t i = 0; i < v.name_len; i++) d[i] = src[i];
-                d[v.name_len] = (uint8_t)'\t';
+        }
+        // names: the warp copies one record's name after the other, lanes over consecutive bytes (a thread copying its own
+        // name byte by byte touches one cache line per lane and instruction)
+        {
+            const uint32_t lane = threadIdx.x & 31;
+            const bool named = live && v.named;
+            const uint64_t my_dst = base[CRAMGPU_HS_RN] + pn, my_src = named ? v.name_at : 0;
+            const uint32_t my_len = named ? v.name_len : 0xFFFFFFFFu;
+            uint32_t todo = __ballot_sync(0xFFFFFFFFu, named);
+            while (todo) {
+                const int i = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const uint64_t dst = __shfl_sync(0xFFFFFFFFu, my_dst, i), src = __shfl_sync(0xFFFFFFFFu, my_src, i);
+                const uint32_t len = __shfl_sync(0xFFFFFFFFu, my_len, i);
+                for (uint32_t b = lane; b <= len; b += 32) S[dst + b] = b < len ? a.names[src + b] : (uint8_t)'\t';
             }
         }
         __syncthreads();
@@ -319,8 +329,10 @@ extern "C" int cramgpu_host_series_pack_dev(cramgpu_ctx *ctx, const cramgpu_host
     return hs_pack_impl(ctx, in, out, h_stream_off, h_stream_len, stream ? (cudaStream_t)stream : ctx->stream);
 }
 
-// host variant: every per-record array in host memory; results come back in host memory owned by the context
-extern "C" int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out)
+// host variants: every per-record array in host memory.  host_series = bit mask (1u << CRAMGPU_HS_x) of the series that come
+// back to the host; with dev_out the result also stays on the device for cramgpu_rans_encode_batch to code in place.
+static int hs_pack_host(cramgpu_ctx *ctx, const cramgpu_host_fields *in, uint32_t host_series, cramgpu_host_series *out,
+                        cramgpu_host_series *dev_out)
 {
     if (!ctx) return CRAMGPU_ERR_ARG;
     if (!in || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
@@ -329,38 +341,66 @@ extern "C" int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fie
     const uint64_t n = in->n_reads;
     const uint32_t nc = in->n_containers;
     memset(out, 0, sizeof *out);
+    if (dev_out) memset(dev_out, 0, sizeof *dev_out);
     if (n == 0 || nc == 0) return CRAMGPU_OK;
     if (!in->flag || !in->pos || !in->read_off || (in->names && !in->name_off)) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
-    // stage the per-record arrays
+    // stage the per-record arrays (arrays that already live on the device are used where they are)
+    MemMap mm;
     struct Item { const void *src; size_t bytes; size_t off; };
     std::vector<Item> items;
     Carver cv;
-    auto add = [&](const void *p, size_t bytes) -> size_t { if (!p) return (size_t)-1; size_t o = cv.take(bytes + 16); items.push_back({p, bytes, o}); return o; };
+    auto add = [&](const void *p, size_t bytes) -> size_t {
+        if (!p || mm.kind(p) == MEM_DEVICE) return (size_t)-1;
+        size_t o = cv.take(bytes + 16); items.push_back({p, bytes, o}); return o;
+    };
+    MemKind nok = in->name_off ? mm.kind(in->name_off) : MEM_PAGEABLE;
+    if (in->names && nok == MEM_DEVICE) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "name_off must be host memory in the host variant");
     const uint64_t name_bytes = in->names ? in->name_off[n] : 0;
     size_t i_flag = add(in->flag, 2 * n), i_cf = add(in->cf, n), i_mcf = add(in->mate_cf, n), i_fq = add(in->force_qs, n), i_rfl = add(in->rflags, n);
     size_t i_ref = add(in->ref_id, 4 * n), i_pos = add(in->pos, 4 * n), i_ro = add(in->read_off, 8 * (n + 1)), i_rg = add(in->read_group, 4 * n);
     size_t i_nm = add(in->names, name_bytes), i_no = add(in->name_off, in->names ? 8 * (n + 1) : 0);
     size_t i_mr = add(in->mate_ref_id, 4 * n), i_mp = add(in->mate_pos, 4 * n), i_ts = add(in->tlen, 4 * n), i_nf = add(in->nf, 4 * n), i_tl = add(in->tl, 4 * n);
-    if (int rc = pool_reserve(ctx, ctx->hs_in, cv.off)) return rc;
+    if (int rc = pool_reserve(ctx, ctx->hs_in, cv.off + 16)) return rc;
     uint8_t *D = (uint8_t *)ctx->hs_in.p;
     for (const Item &it : items)
-        if (it.bytes) CUDA_TRY(ctx, cudaMemcpyAsync(D + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+        if (it.bytes) CUDA_TRY(ctx, memcpy_pieces(D + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st));
     cramgpu_host_fields d = *in;
-    auto at = [&](size_t o) -> const void * { return o == (size_t)-1 ? nullptr : (const void *)(D + o); };
-    d.flag = (const uint16_t *)at(i_flag); d.cf = (const uint8_t *)at(i_cf); d.mate_cf = (const uint8_t *)at(i_mcf);
-    d.force_qs = (const uint8_t *)at(i_fq); d.rflags = (const uint8_t *)at(i_rfl); d.ref_id = (const int32_t *)at(i_ref);
-    d.pos = (const int32_t *)at(i_pos); d.read_off = (const uint64_t *)at(i_ro); d.read_group = (const int32_t *)at(i_rg);
-    d.names = (const uint8_t *)at(i_nm); d.name_off = (const uint64_t *)at(i_no); d.mate_ref_id = (const int32_t *)at(i_mr);
-    d.mate_pos = (const int32_t *)at(i_mp); d.tlen = (const int32_t *)at(i_ts); d.nf = (const int32_t *)at(i_nf); d.tl = (const int32_t *)at(i_tl);
+    auto at = [&](size_t o, const void *orig) -> const void * { return o == (size_t)-1 ? orig : (const void *)(D + o); };
+    d.flag = (const uint16_t *)at(i_flag, in->flag); d.cf = (const uint8_t *)at(i_cf, in->cf); d.mate_cf = (const uint8_t *)at(i_mcf, in->mate_cf);
+    d.force_qs = (const uint8_t *)at(i_fq, in->force_qs); d.rflags = (const uint8_t *)at(i_rfl, in->rflags);
+    d.ref_id = (const int32_t *)at(i_ref, in->ref_id); d.pos = (const int32_t *)at(i_pos, in->pos);
+    d.read_off = (const uint64_t *)at(i_ro, in->read_off); d.read_group = (const int32_t *)at(i_rg, in->read_group);
+    d.names = (const uint8_t *)at(i_nm, in->names); d.name_off = (const uint64_t *)at(i_no, in->name_off);
+    d.mate_ref_id = (const int32_t *)at(i_mr, in->mate_ref_id); d.mate_pos = (const int32_t *)at(i_mp, in->mate_pos);
+    d.tlen = (const int32_t *)at(i_ts, in->tlen); d.nf = (const int32_t *)at(i_nf, in->nf); d.tl = (const int32_t *)at(i_tl, in->tl);
     cramgpu_host_series dev;
     const size_t tab = 8 * (size_t)nc * HS_N;
     if (int rc = pinned_reserve(ctx, &ctx->pin_hs, &ctx->pin_hs_cap, 2 * tab + 64)) return rc;
     uint64_t *h_off = (uint64_t *)ctx->pin_hs, *h_len = h_off + (size_t)nc * HS_N;
     if (int rc = hs_pack_impl(ctx, &d, &dev, h_off, h_len, st)) return rc;
     if (int rc = pinned_reserve(ctx, &ctx->pin_hs2, &ctx->pin_hs2_cap, dev.streams_len + 64)) return rc;
-    CUDA_TRY(ctx, memcpy_pieces(ctx->pin_hs2, dev.streams, dev.streams_len, cudaMemcpyDeviceToHost, st));
+    // the layout is series-major: a series of all containers is one contiguous piece
+    uint8_t *hstreams = (uint8_t *)ctx->pin_hs2;
+    for (uint32_t k = 0; k < HS_N; k++) {
+        if (!(host_series & (1u << k))) continue;
+        const uint64_t lo = h_off[k], hi = k + 1 < HS_N ? h_off[k + 1] : dev.streams_len;      // container 0's region of series k .. of series k + 1
+        if (hi > lo) CUDA_TRY(ctx, memcpy_pieces(hstreams + lo, dev.streams + lo, hi - lo, cudaMemcpyDeviceToHost, st));
+    }
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
-    out->streams = (const uint8_t *)ctx->pin_hs2; out->streams_len = dev.streams_len;
+    out->streams = hstreams; out->streams_len = dev.streams_len;
     out->stream_off = h_off; out->stream_len = h_len;
+    if (dev_out) *dev_out = dev;
     return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out)
+{
+    return hs_pack_host(ctx, in, 0xFFFFFFFFu, out, nullptr);
+}
+
+extern "C" int cramgpu_host_series_pack_resident(cramgpu_ctx *ctx, const cramgpu_host_fields *in, uint32_t host_series,
+                                                 cramgpu_host_series *out, cramgpu_host_series *dev_out)
+{
+    if (!dev_out) return ctx ? ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument") : CRAMGPU_ERR_ARG;
+    return hs_pack_host(ctx, in, host_series, out, dev_out);
 }

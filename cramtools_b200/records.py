@@ -73,6 +73,8 @@ class HostSeries(C.Structure):
 
 _lib.SIGNATURES.update({
     'cramgpu_host_series_pack': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.POINTER(HostSeries)]),
+    'cramgpu_host_series_pack_resident': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.c_uint32, C.POINTER(HostSeries),
+                                                    C.POINTER(HostSeries)]),
     'cramgpu_host_series_pack_dev': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.POINTER(HostSeries), u64p, u64p, C.c_void_p]),
     'cramgpu_features_unpack': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), u8p, i32p]),
     'cramgpu_features_unpack_dev': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), C.POINTER(C.c_void_p), i32p,

@@ -481,6 +481,37 @@ typedef struct cramgpu_host_series {
 int cramgpu_host_series_pack_dev(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out,
                                  uint64_t *h_stream_off, uint64_t *h_stream_len, void *stream);
 int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cramgpu_host_series *out);
+/* The host variant for callers that code the rANS series on the GPU right away (the counterpart of
+ * cramgpu_features_encode_resident): the result stays in device memory (`dev_out`: device pointers, valid until the next
+ * call of this kind on ctx) and only the series whose bit is set in `host_series` (1u << CRAMGPU_HS_x) are copied to the
+ * host; `out->streams` keeps the device layout.  Per-record arrays that already are device pointers are used in place. */
+int cramgpu_host_series_pack_resident(cramgpu_ctx *ctx, const cramgpu_host_fields *in, uint32_t host_series,
+                                      cramgpu_host_series *out, cramgpu_host_series *dev_out);
+
+/* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
+ *
+ * Containers are independent and are dealt round-robin: the container with global ordinal g is converted by
+ * rank g % world.  The writer's two running sums -- container.offset (CRAMContainerStreamWriter.java:229-230) and
+ * ContainerFactory.globalRecordCounter [ContainerFactory.java:77,105] -- become an exclusive scan over the per-container
+ * sizes of all ranks.  The library does the bookkeeping; the exchange is a callback, so that the same entry point works
+ * over NCCL / gloo (cramtools_b200/sharding.py), MPI, or the sockets of a JVM cluster.
+ *
+ *   local[i]          sizes of this rank's i-th container (global ordinal i * world + rank)
+ *   gather            all-gather of `bytes` bytes: recv receives world * bytes, rank r's contribution at r * bytes;
+ *                     returns 0 on success.  Called twice (counts, then sizes); not called when world == 1.
+ *   base_offset       file offset of the first container (after the CRAM header); base_record: its global record counter
+ *   offset[i], record_counter[i]   results for this rank's containers;  total (optional): sums over all ranks
+ */
+typedef struct cramgpu_container_size {
+    uint64_t compressed_bytes;    /* bytes ContainerIO.writeContainer produced for the container */
+    uint64_t n_bases;             /* Container.bases */
+    uint32_t n_records;           /* Container.nofRecords */
+    uint32_t reserved;
+} cramgpu_container_size;
+typedef int (*cramgpu_allgather_fn)(void *user, const void *send, void *recv, uint64_t bytes);
+int cramgpu_allgather_sizes(cramgpu_ctx *ctx, uint32_t n_local, const cramgpu_container_size *local, uint32_t rank, uint32_t world,
+                            cramgpu_allgather_fn gather, void *user, uint64_t base_offset, uint64_t base_record,
+                            uint64_t *offset, uint64_t *record_counter, cramgpu_container_size *total);
 
 #ifdef __cplusplus
 }

@@ -4,8 +4,9 @@
  * CPU driver that strings the restated reference functions together the way the reference's own
  * multi-threaded converter does (one container per pool thread, paralell/BamToCram_OBA_Function.java:51-94
  * and paralell/CramToBam_OBA_Function.java:53-84): per container
- *   encode: feature extraction + substitution matrix + quality preservation + series packing,
- *           then rANS of QS / BA (order 1) and of the caller's extra series (BF, CF, RL, ... as given)
+ *   encode: feature extraction + substitution matrix + quality preservation + series packing (the read-feature series
+ *           and the record fields in front of them), then rANS of the series the reference codes with rANS:
+ *           QS, BA, BF, CF, RL, RG, NS, TS order 1 and AP order 0 (CompressionHeaderFactory.build [:84-113])
  *   decode: rANS decode of the same blocks, then base and quality restoration of every record.
  * bench.py times this as the CPU baseline / `--impl reference` arm (there is no JVM in the image).
  */
@@ -36,6 +37,10 @@ int rec_oracle_parse_policies(const char *, qs_policy_t *, int);
 uint32_t rans_oracle_bound(uint32_t);
 int rans_oracle_compress(const uint8_t *, uint32_t, int, uint8_t *, uint32_t, uint32_t *);
 int rans_oracle_uncompress(const uint8_t *, uint32_t, uint8_t *, uint32_t, uint32_t *);
+void rec_oracle_write_host_streams(int64_t, const uint16_t *, const uint8_t *, const int32_t *, const int64_t *, const int32_t *,
+                                   const int32_t *, const uint8_t *, const int64_t *, const int32_t *, const int32_t *, const int32_t *,
+                                   const int32_t *, const int32_t *, int, int, int32_t, int, uint8_t **, int64_t *);
+enum { H_BF = 0, H_CF, H_RI, H_RL, H_AP, H_RG, H_RN, H_MF, H_NS, H_NP, H_TS, H_NF, H_TL, H_COUNT };
 
 enum { S_FN = 0, S_FC, S_FP, S_BS, S_DL, S_BA, S_SC, S_QS, S_RS, S_HC, S_PD, S_MQ, S_COUNT };
 
@@ -46,7 +51,7 @@ typedef struct {
     const uint32_t *cigar; const int64_t *cigar_off;
     const int32_t *pos; const uint16_t *flag; const uint8_t *mapq;
     const uint8_t *ref; int64_t ref_len;
-    int n_extra; const uint8_t *const *extra; const uint32_t *extra_len; const uint8_t *extra_order;
+    const int32_t *read_group; const uint8_t *names; const int64_t *name_off;     /* name_off absolute into names */
     const qs_policy_t *pol; int n_pol;
     /* results */
     uint64_t checksum; int64_t comp_bytes; int rc;
@@ -73,12 +78,23 @@ static void run_container(container_job_t *j)
     for (int k = 0; k < S_COUNT; k++) streams[k] = malloc((size_t)cap);
     rec_oracle_write_streams(n, j->bases, j->read_off, j->flag, j->mapq, j->pos, &ft, force, sc0, streams, lens);
 
-    /* block codec: QS, BA order 1, then the caller's series */
-    int nblk = 2 + j->n_extra;
+    /* the record fields in front of the features: unpaired reads, every record detached (CramSerilization.setMateInfo :278-285) */
+    uint8_t *cf = malloc((size_t)n + 1);
+    for (int64_t r = 0; r < n; r++) cf[r] = (uint8_t)((force[r] & 1) | 2);
+    int64_t name_bytes = j->names ? j->name_off[n] - j->name_off[0] : 0;
+    uint8_t *hs[H_COUNT]; int64_t hlen[H_COUNT];
+    for (int k = 0; k < H_COUNT; k++) hs[k] = malloc((size_t)(k == H_RN ? name_bytes + n + 16 : 5 * n + 16));
+    int32_t smin = 0x7FFFFFFF;
+    for (int64_t r = 0; r < n; r++) if (j->pos[r] > 0 && j->pos[r] < smin) smin = j->pos[r];       /* Slice.alignmentStart [ContainerFactory.java:160-161] */
+    rec_oracle_write_host_streams(n, j->flag, cf, NULL, j->read_off, j->pos, j->read_group, j->names, j->name_off, NULL, NULL, NULL,
+                                  NULL, NULL, 1, 0, smin, 0, hs, hlen);
+    /* block codec: QS, BA, BF, CF, RL, RG, NS, TS order 1, AP order 0 */
+    static const int coded[7] = {H_BF, H_CF, H_RL, H_RG, H_NS, H_TS, H_AP};
+    int nblk = 2 + 7;
     const uint8_t **in = malloc(sizeof(*in) * (size_t)nblk); uint32_t *ilen = malloc(4 * (size_t)nblk); int *ord = malloc(sizeof(int) * (size_t)nblk);
     in[0] = streams[S_QS]; ilen[0] = (uint32_t)lens[S_QS]; ord[0] = 1;
     in[1] = streams[S_BA]; ilen[1] = (uint32_t)lens[S_BA]; ord[1] = 1;
-    for (int e = 0; e < j->n_extra; e++) { in[2 + e] = j->extra[e]; ilen[2 + e] = j->extra_len[e]; ord[2 + e] = j->extra_order[e]; }
+    for (int e = 0; e < 7; e++) { in[2 + e] = hs[coded[e]]; ilen[2 + e] = (uint32_t)hlen[coded[e]]; ord[2 + e] = coded[e] == H_AP ? 0 : 1; }
     uint64_t sum = 0;
     uint8_t *qs_back = NULL;
     for (int b = 0; b < nblk; b++) {
@@ -119,6 +135,8 @@ static void run_container(container_job_t *j)
     j->checksum = sum;
     free(ob); free(oq); free(qs_back); free(in); free(ilen); free(ord);
     for (int k = 0; k < S_COUNT; k++) free(streams[k]);
+    for (int k = 0; k < H_COUNT; k++) free(hs[k]);
+    free(cf);
     free(force); free(scores);
     rec_oracle_free(&ft);
 }
@@ -133,13 +151,13 @@ static void *worker(void *a)
 
 /*
  * Containers share the flat read arrays: container c holds reads cont_off[c] .. cont_off[c+1]-1.
- * extra[c * n_extra + e] are the caller's already packed series of container c.
+ * read_group / names / name_off (optional) feed the RG and RN series.
  * Returns 0 when every container round-tripped; *comp_bytes and *checksum accumulate.
  */
 int oracle_cram_step(int nthreads, int n_cont, const int64_t *cont_off, const uint8_t *bases, const uint8_t *quals,
                      const int64_t *read_off, const uint32_t *cigar, const int64_t *cigar_off, const int32_t *pos,
-                     const uint16_t *flag, const uint8_t *mapq, const uint8_t *ref, int64_t ref_len, int n_extra,
-                     const uint8_t *const *extra, const uint32_t *extra_len, const uint8_t *extra_order, const char *spec,
+                     const uint16_t *flag, const uint8_t *mapq, const uint8_t *ref, int64_t ref_len,
+                     const int32_t *read_group, const uint8_t *names, const int64_t *name_off, const char *spec,
                      int64_t *comp_bytes, uint64_t *checksum)
 {
     qs_policy_t pol[16];
@@ -153,8 +171,7 @@ int oracle_cram_step(int nthreads, int n_cont, const int64_t *cont_off, const ui
         j->bases = bases; j->quals = quals; j->read_off = read_off + a;
         j->cigar = cigar; j->cigar_off = cigar_off + a; j->pos = pos + a; j->flag = flag + a; j->mapq = mapq + a;
         j->ref = ref; j->ref_len = ref_len;
-        j->n_extra = n_extra; j->extra = extra + (size_t)c * n_extra; j->extra_len = extra_len + (size_t)c * n_extra;
-        j->extra_order = extra_order;
+        j->read_group = read_group ? read_group + a : NULL; j->names = names; j->name_off = name_off ? name_off + a : NULL;
         j->pol = pol; j->n_pol = n_pol;
     }
     if (nthreads < 1) nthreads = 1;

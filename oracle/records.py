@@ -53,6 +53,9 @@ def lib():
         L.rec_oracle_restore_quals.argtypes = [_c.c_int, _c.c_int64, _c.c_int64, u8p, i32p, i32p, i32p, u8p]
         L.rec_oracle_write_streams.argtypes = [_c.c_int64, u8p, i64p, u16p, u8p, i32p, _c.POINTER(RecFeatures), u8p, u8p,
                                                _c.POINTER(u8p), i64p]
+        L.rec_oracle_write_host_streams.restype = None
+        L.rec_oracle_write_host_streams.argtypes = [_c.c_int64, u16p, u8p, i32p, i64p, i32p, i32p, u8p, i64p, i32p, i32p, i32p, i32p,
+                                                    i32p, _c.c_int, _c.c_int, _c.c_int32, _c.c_int, _c.POINTER(u8p), i64p]
         _done = True
     return L
 
@@ -349,3 +352,32 @@ def write_host_streams(sc, ap_delta, multi_ref, slice_start, capture_names=True)
             out['NF'] += itf8(r['nf'])
         out['TL'] += itf8(r.get('tl', 0))
     return {k: bytes(v) for k, v in out.items()}
+
+
+def write_host_streams_c(flag, cf, ref_id, read_off, pos, read_group, names, mate_ref, mate_pos, tlen, nf, tl, ap_delta, multi_ref,
+                         slice_start, capture_names):
+    """the same through the C restatement (oracle/records_oracle.c: rec_oracle_write_host_streams), which is what the CPU
+    baseline of bench.py runs; BF and MF come from the SAM flags there"""
+    n = len(flag)
+
+    def arr(x, dt):
+        return None if x is None else np.ascontiguousarray(x, dt)
+
+    def ptr(a, t):
+        return None if a is None else a.ctypes.data_as(t)
+    nb = None if names is None else [x.encode('latin-1') if isinstance(x, str) else bytes(x) for x in names]
+    nm = None if nb is None else np.frombuffer(b''.join(nb) + b'\0', np.uint8).copy()
+    no = None if nb is None else np.concatenate([[0], np.cumsum([len(x) for x in nb])]).astype(np.int64)
+    a = dict(flag=arr(flag, np.uint16), cf=arr(cf, np.uint8), ref_id=arr(ref_id, np.int32), read_off=arr(read_off, np.int64),
+             pos=arr(pos, np.int32), rg=arr(read_group, np.int32), mr=arr(mate_ref, np.int32), mp=arr(mate_pos, np.int32),
+             ts=arr(tlen, np.int32), nf=arr(nf, np.int32), tl=arr(tl, np.int32))
+    cap = 5 * n + 16
+    bufs = [np.zeros((int(no[-1]) + n + 16) if (k == 6 and no is not None) else cap, np.uint8) for k in range(len(HOST_STREAMS))]
+    ptrs = (u8p * len(HOST_STREAMS))(*[_p(b, u8p) for b in bufs])
+    lens = np.zeros(len(HOST_STREAMS), np.int64)
+    lib().rec_oracle_write_host_streams(n, ptr(a['flag'], u16p), ptr(a['cf'], u8p), ptr(a['ref_id'], i32p), ptr(a['read_off'], i64p),
+                                        ptr(a['pos'], i32p), ptr(a['rg'], i32p), ptr(nm, u8p), ptr(no, i64p), ptr(a['mr'], i32p),
+                                        ptr(a['mp'], i32p), ptr(a['ts'], i32p), ptr(a['nf'], i32p), ptr(a['tl'], i32p),
+                                        1 if ap_delta else 0, 1 if multi_ref else 0, int(slice_start), 1 if capture_names else 0,
+                                        ptrs, _p(lens, i64p))
+    return {nmk: bufs[i][:int(lens[i])].tobytes() for i, nmk in enumerate(HOST_STREAMS)}

@@ -15,8 +15,9 @@
  *
  * Parity pin: tests/golden/records_jvm.json was produced by executing those very methods out of
  * /root/reference/cramtools-3.0.jar with oracle/minijvm.py (oracle/make_golden_records.py);
- * tests/test_oracle_records.py checks this file against it.  Not pinned by the jar: the Writer stream
- * assembly (row W) beyond ITF8 -- restated from the disassembly only.
+ * tests/test_oracle_records.py checks this file against it.  The Writer stream assembly (row W) is pinned by
+ * tests/golden/streams_jvm.json: the raw series ContainerFactory.buildSlice / Writer.write produced in the mini-JVM
+ * (oracle/make_golden_streams.py), compared byte for byte by tests/test_oracle_streams.py.
  *
  * Per-base lossy selectors that need ReferenceTracks coverage/pile-up counters (X, P) are not restated
  * (outside BASELINE configs); R/N/D/I use "tracks present" semantics: baseAt(p) = ref[p-1].
@@ -540,4 +541,53 @@ void rec_oracle_write_streams(int64_t n_reads, const uint8_t *bases, const int64
         }
     }
     (void)pos;
+}
+
+
+/* ------------------------------------------------------------------ the record fields in front of the read features (row W, first half)
+ * Writer.write [Writer.java:139-172] driven from ContainerFactory.buildSlice [:179-184]; BF / MF from the SAM flag as
+ * Sam2CramRecordFactory.createCramRecord sets them [:114-131,143-152].  Series order of out / lens:
+ * BF CF RI RL AP RG RN MF NS NP TS NF TL.  cf = CramCompressionRecord.getCompressionFlags() (bit 1 detached, bit 2 mate
+ * downstream).  Optional arrays may be NULL (read_group: -1, mate_ref: -1, mate_pos / tlen / nf / tl: 0, names: RN empty). */
+enum { H_BF = 0, H_CF, H_RI, H_RL, H_AP, H_RG, H_RN, H_MF, H_NS, H_NP, H_TS, H_NF, H_TL, H_COUNT };
+void rec_oracle_write_host_streams(int64_t n, const uint16_t *flag, const uint8_t *cf, const int32_t *ref_id, const int64_t *read_off,
+                                   const int32_t *pos, const int32_t *read_group, const uint8_t *names, const int64_t *name_off,
+                                   const int32_t *mate_ref, const int32_t *mate_pos, const int32_t *tlen, const int32_t *nf,
+                                   const int32_t *tl, int ap_delta, int multi_ref, int32_t slice_start, int names_included,
+                                   uint8_t **out, int64_t *lens)
+{
+    for (int k = 0; k < H_COUNT; k++) lens[k] = 0;
+#define HPUT(k, b) (out[k][lens[k]++] = (uint8_t)(b))
+#define HPUT_ITF8(k, v) (lens[k] += rec_oracle_itf8((int32_t)(v), out[k] + lens[k]))
+    int32_t prev = slice_start;
+    for (int64_t r = 0; r < n; r++) {
+        const uint32_t f = flag[r];
+        const uint32_t bf = (f & 1u) ? (f & (0x1u | 0x2u | 0x4u | 0x10u | 0x40u | 0x80u | 0x100u | 0x200u | 0x400u | 0x800u))
+                                     : (f & (0x4u | 0x10u | 0x100u | 0x200u | 0x400u | 0x800u));
+        const uint32_t mf = (f & 1u) ? (((f & 0x20u) ? 1u : 0u) | ((f & 0x8u) ? 2u : 0u)) : 0u;
+        HPUT_ITF8(H_BF, bf);                                             /* :139 */
+        HPUT(H_CF, cf[r]);                                               /* :140 */
+        if (multi_ref) HPUT_ITF8(H_RI, ref_id[r]);                       /* :141-142 */
+        HPUT_ITF8(H_RL, read_off[r + 1] - read_off[r]);                  /* :144 */
+        if (ap_delta) { HPUT_ITF8(H_AP, pos[r] - prev); prev = pos[r]; } /* :146-147, ContainerFactory [:181-182] */
+        else HPUT_ITF8(H_AP, pos[r]);                                    /* :149 */
+        HPUT_ITF8(H_RG, read_group ? read_group[r] : -1);                /* :151 */
+        const int detached = (cf[r] & 2) != 0;
+        const int named = names && (names_included || detached);         /* :153-154 / :160-161 */
+        if (detached) HPUT(H_MF, mf);                                    /* :159 */
+        if (named) {
+            for (int64_t i = name_off[r]; i < name_off[r + 1]; i++) HPUT(H_RN, names[i]);
+            HPUT(H_RN, '\t');
+        }
+        if (detached) {
+            HPUT_ITF8(H_NS, mate_ref ? mate_ref[r] : -1);                /* :163 */
+            HPUT_ITF8(H_NP, mate_pos ? mate_pos[r] : 0);                 /* :164 */
+            HPUT_ITF8(H_TS, tlen ? tlen[r] : 0);                         /* :165 */
+        } else if (cf[r] & 4) {
+            HPUT_ITF8(H_NF, nf ? nf[r] : 0);                             /* :168-169 */
+        }
+        HPUT_ITF8(H_TL, tl ? tl[r] : 0);                                 /* :172 */
+    }
+#undef HPUT
+#undef HPUT_ITF8
 }

@@ -54,6 +54,20 @@ def test_host_series_match_jar(G):
             assert got[nm] == series.get(CID[nm], b''), (c['tag'], nm)
 
 
+def test_host_series_c_restatement_matches_jar(G):
+    """the C version (what bench.py's CPU baseline runs): BF / MF derived from the SAM flags inside"""
+    g, _, conts = G
+    for c, rd, series in conts:
+        sc = c['scalars']
+        got = orec.write_host_streams_c(rd['flag'], [s['cf'] for s in sc], [s['seq_id'] for s in sc], rd['read_off'], rd['pos'],
+                                        [s['read_group'] for s in sc], [s['name'] for s in sc], [s['mate_seq_id'] for s in sc],
+                                        [s['mate_start'] for s in sc], [s['tlen'] for s in sc], [s['nf'] for s in sc], None,
+                                        c['ap_delta'], c['slice']['sequence_id'] == -2, c['slice']['alignment_start'],
+                                        bool(c['read_names_included']))
+        for nm in orec.HOST_STREAMS:
+            assert got[nm] == series.get(CID[nm], b''), (c['tag'], nm)
+
+
 def test_bit_flags_match_jar(G):
     """row F2, scalar half: BF and MF from the SAM flag"""
     g, _, conts = G
