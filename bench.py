@@ -326,6 +326,14 @@ class Lane(object):
             H.names = vp(self.t_names.data_ptr()); H.name_off = vp(self.t_noff.data_ptr())
             H.mate_ref_id = None; H.mate_pos = None; H.tlen = None; H.nf = None; H.tl = None
             self.HS = rec.HostSeries()
+            # slice header fields + BD / SD digests (ContainerFactory.buildSlice :138-176), also inside the step
+            SI = self.SI = rec.SliceIn()
+            SI.n_reads = n_reads; SI.n_containers = n_cont; SI.cont_off = self.cont_off.ctypes.data_as(u64p)
+            SI.bases = vp(self.t_bases.data_ptr()); SI.read_off = vp(self.t_roff.data_ptr()); SI.rflags = None; SI.ref_id = None
+            SI.pos = vp(self.t_pos.data_ptr()); SI.flag = vp(self.t_flag.data_ptr())
+            SI.scores = vp(self.t_quals.data_ptr()) if self.npol < 0 else None      # lossless: record.qualityScores = the qualities
+            self.slice_hdr = torch.zeros(n_cont * C.sizeof(rec.SliceHeader), dtype=torch.uint8, device=dev)
+            self.uniq_reads = (rd, nu)
             NHS = len(rec.HOST_SERIES)
             self.hoff = np.zeros((n_cont, NHS), np.uint64); self.hlen = np.zeros((n_cont, NHS), np.uint64)
             self.KX = [rec.HOST_SERIES.index(nm) for nm, _ in EXTRA]
@@ -356,6 +364,10 @@ class Lane(object):
         ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), self.pol, self.npol, C.byref(F), self.soff.ctypes.data_as(u64p),
                                                       self.slen.ctypes.data_as(u64p), self._sp()))
         self.H.force_qs = F.force_qs                     # CF bit 0 comes from the quality model's decision
+        SI = self.SI
+        SI.f_op = F.f_op; SI.f_pos = F.f_pos; SI.f_val = F.f_val; SI.f_aux = F.f_aux; SI.feat_off = F.feat_off
+        SI.force_qs = F.force_qs; SI.read_qs_off = F.read_qs_off; SI.streams = F.streams
+        ctx.check(ctx.lib.cramgpu_slice_headers_dev(ctx.handle, C.byref(SI), vp(self.slice_hdr.data_ptr()), self._sp()))
         ctx.check(ctx.lib.cramgpu_host_series_pack_dev(ctx.handle, C.byref(self.H), C.byref(self.HS), self.hoff.ctypes.data_as(u64p),
                                                        self.hlen.ctypes.data_as(u64p), self._sp()))
         base = np.uint64(F.streams); hbase = np.uint64(self.HS.streams)
@@ -444,6 +456,21 @@ class Lane(object):
             want = self.dv.dev_to_numpy(self.ctx, int(self.HS.streams) + a, ln, np.uint8)
             got = self.dec_out[int(d_off[k]):int(d_off[k]) + ln].cpu().numpy()
             assert np.array_equal(got, want), 'record-field series round trip mismatch'
+        # slice headers: record / base counts of every slice, and the digests of the first distinct containers against zlib
+        hdr = np.frombuffer(self.slice_hdr.cpu().numpy().tobytes(), dtype=np.dtype([('seq', '<i4'), ('start', '<i4'), ('span', '<i4'), ('nrec', '<u4'),
+                                                                                   ('bases', '<u8'), ('bd', '<u4'), ('sd', '<u4')]))
+        assert (hdr['nrec'] == READS_PER_CONTAINER).all() and (hdr['bases'] == READS_PER_CONTAINER * READ_LEN).all() and (hdr['seq'] == 0).all()
+        assert (hdr['start'] == self.slice_start).all(), 'slice alignment start'
+        import zlib
+        urd, nu_ = self.uniq_reads
+        for c in range(min(2, n_cont)):
+            u = c % nu_
+            lo = u * READS_PER_CONTAINER * READ_LEN
+            b = urd['bases'][lo:lo + READS_PER_CONTAINER * READ_LEN].reshape(READS_PER_CONTAINER, READ_LEN)
+            assert int(hdr['bd'][c]) == sum(zlib.crc32(x.tobytes()) for x in b) & 0xFFFFFFFF, 'BD digest'
+            if lossless:
+                q = urd['quals'][lo:lo + READS_PER_CONTAINER * READ_LEN].reshape(READS_PER_CONTAINER, READ_LEN)
+                assert int(hdr['sd'][c]) == sum(zlib.crc32(x.tobytes()) for x in q) & 0xFFFFFFFF, 'SD digest'
         if self.use_unpack:
             got = np.empty(n_reads, np.uint8)
             self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(got.ctypes.data), self.d_mapq, C.c_uint64(n_reads), self._sp()))
@@ -1013,6 +1040,8 @@ def run_sweep(args):
             best = min(best, ev[0].elapsed_time(ev[1]))
         return best, r_
     for kind, gen in gens.items():
+        if args.sweep_kinds and kind not in args.sweep_kinds.split(','):
+            continue
         for size in sizes:
             nb = int(max(8, min(2048, (1500 << 20) // size)))
             uniq = [np.ascontiguousarray(gen(size, 100 + i)) for i in range(8)]
@@ -1057,6 +1086,7 @@ def main():
     ap.add_argument('--no-unpack', action='store_true', help='decode side: take the read features from the encoder instead of unpacking the series (row P)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--no-configs', action='store_true', help='skip the short runs of the other north_star configurations (quality models, 20 containers, fixed total)')
+    ap.add_argument('--sweep-kinds', default='', help='--sweep: only these kinds (comma separated: QS,BA,RN,ITF8)')
     ap.add_argument('--sweep', action='store_true', help='BASELINE configs[1]: the rANS block sweep instead of the step benchmark')
     args = ap.parse_args()
     if args.sweep:

@@ -33,6 +33,7 @@ SIGNATURES = {
     'cramgpu_last_error': (ctypes.c_char_p, [vp]),
     'cramgpu_sync': (ctypes.c_int, [vp]),
     'cramgpu_launch_count': (ctypes.c_uint64, [vp]),
+    'cramgpu_set_option': (ctypes.c_int, [vp, ctypes.c_char_p, ctypes.c_uint64]),
     'cramgpu_copy_to_host': (ctypes.c_int, [vp, vp, vp, ctypes.c_uint64, vp]),
     'cramgpu_profile_enable': (ctypes.c_int, [vp, ctypes.c_int]),
     'cramgpu_profile_read': (ctypes.c_int, [vp, ctypes.c_uint32, ctypes.POINTER(ctypes.c_char_p),
@@ -96,6 +97,9 @@ class Context:
 
     def sync(self):
         self.check(self.lib.cramgpu_sync(self.handle))
+
+    def set_option(self, name, value):
+        self.check(self.lib.cramgpu_set_option(self.handle, name.encode(), int(value)))
 
     def launch_count(self):
         return int(self.lib.cramgpu_launch_count(self.handle))

@@ -197,6 +197,7 @@ int cramgpu_init(int device, cramgpu_ctx **out)
     ctx->device = device;
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_slice, cudaEventDisableTiming);
     if (e == cudaSuccess && !getenv("CRAMGPU_NO_HP_STREAM")) {
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
@@ -222,11 +223,16 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->rec_out.p) cudaFree(ctx->rec_out.p);
     if (ctx->rec_unp.p) cudaFree(ctx->rec_unp.p);
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
+    if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
+    if (ctx->slice_in.p) cudaFree(ctx->slice_in.p);
+    if (ctx->pin_slice) cudaFreeHost(ctx->pin_slice);
+    if (ctx->ev_slice) cudaEventDestroy(ctx->ev_slice);
     if (ctx->hs_out.p) cudaFree(ctx->hs_out.p);
     if (ctx->hs_in.p) cudaFree(ctx->hs_in.p);
     if (ctx->pin_hs) cudaFreeHost(ctx->pin_hs);
     if (ctx->pin_hs2) cudaFreeHost(ctx->pin_hs2);
     if (ctx->pin_rec) cudaFreeHost(ctx->pin_rec);
+    free(ctx->rec_fault);
     if (ctx->pin_feat) cudaFreeHost(ctx->pin_feat);
     if (ctx->pin_in) cudaFreeHost(ctx->pin_in);
     if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
@@ -254,6 +260,13 @@ int cramgpu_sync(cramgpu_ctx *ctx)
 }
 
 uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int cramgpu_set_option(cramgpu_ctx *ctx, const char *name, uint64_t value)
+{
+    if (!ctx || !name) return CRAMGPU_ERR_ARG;
+    if (!strcmp(name, "dec_wide_pool_blocks")) { ctx->dec_wide_pool_blocks = (uint32_t)std::min<uint64_t>(value, 1u << 20); return CRAMGPU_OK; }
+    return ctx_fail(ctx, CRAMGPU_ERR_ARG, "unknown option %s", name);
+}
 
 int cramgpu_copy_to_host(cramgpu_ctx *ctx, void *dst_host, const void *src_dev, uint64_t bytes, void *stream)
 {
@@ -463,7 +476,9 @@ static int host_batch(cramgpu_ctx *ctx, bool encode, uint32_t nblocks, const uin
         if (status) status[i] = rc;
         if (rc != CRAMGPU_OK && first == CRAMGPU_OK) {
             first = rc;
-            if (rc == CRAMGPU_ERR_OUT_TOO_SMALL) ctx_fail(ctx, rc, "Output buffer too small to fit %u bytes. (block %u)", h_len[i], i);
+            // the compressor's wording is RANS.allocateIfNeeded's [RANS.java:79-85], the decompressor's RANS.uncompress's [:44]
+            if (rc == CRAMGPU_ERR_OUT_TOO_SMALL && encode) ctx_fail(ctx, rc, "Insufficient buffer size. (block %u needs %u bytes)", i, h_len[i]);
+            else if (rc == CRAMGPU_ERR_OUT_TOO_SMALL) ctx_fail(ctx, rc, "Output buffer too small to fit %u bytes. (block %u)", h_len[i], i);
             else if (rc == CRAMGPU_ERR_UNKNOWN_ORDER) ctx_fail(ctx, rc, "Unknown rANS order: %d (block %u)", encode ? (int)order[i] : (int)in[i][0], i);
             else ctx_fail(ctx, rc, "%s (block %u)", status_text(rc), i);
         }

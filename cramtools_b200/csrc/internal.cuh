@@ -70,8 +70,11 @@ struct cramgpu_ctx {
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
     DevPool rec_unp;                // results of cramgpu_features_unpack (its input series may be an encode result in rec_out)
     DevPool hs_scratch, hs_out, hs_in;   // cramgpu_host_series_pack: tables, result, staged inputs of the host variant
+    DevPool slice_scratch, slice_in;     // cramgpu_slice_headers: accumulators, staged inputs of the host variant
+    void *pin_slice = nullptr; size_t pin_slice_cap = 0; cudaEvent_t ev_slice = nullptr;
     void *pin_hs = nullptr, *pin_hs2 = nullptr; size_t pin_hs_cap = 0, pin_hs2_cap = 0;
     void *pin_rec = nullptr; size_t pin_rec_cap = 0;
+    void *rec_fault = nullptr;      // records.cu: arguments of the last feature call with a BIN treatment (malloc)
     void *pin_feat = nullptr; size_t pin_feat_cap = 0;   // host copy of the last cramgpu_features_encode result
     void *pin_in = nullptr, *pin_out = nullptr, *pin_meta = nullptr;
     size_t pin_in_cap = 0, pin_out_cap = 0, pin_meta_cap = 0;
@@ -82,6 +85,7 @@ struct cramgpu_ctx {
     cudaStream_t hp_stream = nullptr;
     cudaEvent_t hp_in = nullptr, hp_out = nullptr;
     EncodePending pend;
+    uint32_t dec_wide_pool_blocks = 2048;   // rans_decode.cu: pool of wide-alphabet table images (cramgpu_set_option)
     bool enc_attr_done = false, dec_attr_done = false;   // per context (= per device): dynamic shared-memory limits of the coder kernels set
     // optional per-kernel timing (cramgpu_profile_*): CUDA events around every launch
     bool profiling = false;

@@ -47,8 +47,19 @@
 //   entries 0xFFFF, is searched from r1 + 1 on.
 struct DecMeta {
     uint32_t pay_off;   // offset of the 16 state bytes inside the compressed block
-    uint32_t nU;        // order 1: number of distinct bytes when the shared-memory tables were built, else 0
+    uint32_t nU;        // order 1: number of distinct bytes (contexts and symbols together), 0 = no tables (corrupt)
+    uint32_t img;       // order 1: where the block's table image starts, in 256-byte units from `images`; DEC_NO_IMG = none
+    uint32_t pad;
 };
+#define DEC_NO_IMG 0xFFFFFFFFu
+// Table images of the blocks with more than DEC_MAXU distinct bytes ("wide": ITF8 series such as TS and NP of paired reads,
+// names, tags) have nU rows of 256 FINE buckets (16 slots each, one byte = the rank whose range holds the bucket's first
+// slot) | cumulative rows | alphabet, up to 201 KB, and live in a pool behind the fixed slots, handed out by an atomic
+// cursor while k_dec_tables runs.  They are decoded from global memory by k_dec1s<true>.  A call with more wide blocks than
+// the pool holds leaves the rest to k_dec1_big.
+__host__ __device__ __forceinline__ uint32_t dec_wide_img_bytes(uint32_t nU) { return (nU * (DEC_ROWE + ((2u * (nU + 5u) + 7u) & ~7u)) + 256u + 255u) & ~255u; }
+#define DEC_WIDE_IMG_MAX 200960u     // dec_wide_img_bytes(256)
+// the pool holds ctx->dec_wide_pool_blocks (2048) images of the largest size (410 MB), or as many as the call has order-1 blocks
 
 __host__ __device__ __forceinline__ uint32_t dec_cumb(uint32_t nU) { return (2u * (nU + 5u) + 7u) & ~7u; }          // bytes of one cumulative row
 __host__ __device__ __forceinline__ uint32_t dec_tab_bytes(uint32_t nU) { return (nU * (DEC_ROWE + dec_cumb(nU)) + 255u) & ~255u; }
@@ -113,7 +124,8 @@ struct TabParser {
 //   order 1 with more: only the alphabet size and the payload offset (k_dec1_big builds its tables itself)
 __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict__ desc, const uint8_t *__restrict__ d_in,
                                                     uint8_t *__restrict__ lut0, uint32_t *__restrict__ fc0,
-                                                    uint8_t *__restrict__ images,
+                                                    uint8_t *__restrict__ images, uint32_t pool_first, uint32_t pool_units,
+                                                    uint32_t *__restrict__ pool_cursor,
                                                     DecMeta *__restrict__ meta, int32_t *__restrict__ status)
 {
     uint32_t blk = blockIdx.x;
@@ -125,15 +137,16 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
     uint8_t *lut = lut0 + (size_t)d.o1_index * 4096;          // order 0: o1_index = rank among the order-0 blocks
     uint32_t *fc = fc0 + (size_t)d.o1_index * 256;
     uint8_t *img = images + (size_t)d.o1_index * DEC_IMG;
+    uint32_t img_units = d.o1_index * (DEC_IMG / 256u), cum_off = DEC_IMG_CUM, alpha_off = DEC_IMG_ALPHA;
 
     __shared__ uint16_t F[256];
     __shared__ uint16_t C[257];
     __shared__ uint8_t symlist[256];
     __shared__ uint8_t present[256];
     __shared__ uint8_t rank[256];
-    __shared__ uint8_t ualpha[DEC_MAXU];
+    __shared__ uint8_t ualpha[256];
     __shared__ uint32_t wcnt[4];
-    __shared__ uint32_t s_nsym, s_pos, s_ctx, s_more, s_bad, s_nU;
+    __shared__ uint32_t s_nsym, s_pos, s_ctx, s_more, s_bad, s_nU, s_img;
     uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     TabParser P = {in, len, 9u, 0u, 0, false, o1};      // thread 0 only
     // ---- order 1, pass A: which bytes occur (as context or symbol)?  -> ranks
@@ -168,16 +181,29 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
             rank[2 * tid] = (uint8_t)b0; rank[2 * tid + 1] = (uint8_t)(b0 + p0);
             if (tid == 127) s_nU = b0 + c;
             __syncthreads();
-            small = s_nU <= DEC_MAXU;
+            small = true;
+            const uint32_t nU = s_nU;
+            cumb = dec_cumb(nU);
+            if (nU > DEC_MAXU) {
+                // a wide alphabet: its image comes out of the pool (or the block is left to k_dec1_big)
+                if (tid == 0) {
+                    const uint32_t units = dec_wide_img_bytes(nU) / 256u;
+                    const uint32_t at = atomicAdd(pool_cursor, units);
+                    s_img = at + units <= pool_units ? pool_first + at : DEC_NO_IMG;
+                }
+                __syncthreads();
+                img_units = s_img;
+                small = img_units != DEC_NO_IMG;
+                img = images + (size_t)img_units * 256u;
+                cum_off = nU * DEC_ROWE; alpha_off = cum_off + nU * cumb;
+            }
             if (small) {
-                const uint32_t nU = s_nU;
-                cumb = dec_cumb(nU);
-                if (p0) { ualpha[b0] = (uint8_t)(2 * tid); img[DEC_IMG_ALPHA + b0] = (uint8_t)(2 * tid); }
-                if (p1) { ualpha[b0 + p0] = (uint8_t)(2 * tid + 1); img[DEC_IMG_ALPHA + b0 + p0] = (uint8_t)(2 * tid + 1); }
+                if (p0) { ualpha[b0] = (uint8_t)(2 * tid); img[alpha_off + b0] = (uint8_t)(2 * tid); }
+                if (p1) { ualpha[b0 + p0] = (uint8_t)(2 * tid + 1); img[alpha_off + b0 + p0] = (uint8_t)(2 * tid + 1); }
                 // contexts that never get a row (only corrupt streams reach them): empty buckets, cum[0] = 0, the ends 0xFFFF
                 uint32_t *e32 = reinterpret_cast<uint32_t *>(img);
                 for (uint32_t i = tid; i < nU * (DEC_ROWE / 4); i += 128) e32[i] = 0;
-                uint16_t *c16 = reinterpret_cast<uint16_t *>(img + DEC_IMG_CUM);
+                uint16_t *c16 = reinterpret_cast<uint16_t *>(img + cum_off);
                 const uint32_t cw = cumb / 2;
                 for (uint32_t i = tid; i < nU * cw; i += 128) c16[i] = (i % cw) ? 0xFFFF : 0;
             }
@@ -194,11 +220,12 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
         for (uint32_t i = tid; i < 256; i += 128) fc[i] = 0;
         __syncthreads();
     }
-    // ---- pass B: parse each row, expand it (a large-alphabet order-1 block stops here: pass A found its payload)
+    // ---- pass B: parse each row, expand it (a wide block that found no room in the pool stops here: pass A found its payload)
     if (o1 && !small) {
         if (tid == 0) {
             meta[blk].pay_off = s_pos;
             meta[blk].nU = s_bad ? 0u : s_nU;
+            meta[blk].img = DEC_NO_IMG;
             if (s_bad) status[blk] = CRAMGPU_ERR_CORRUPT;
         }
         return;
@@ -219,18 +246,33 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
         if (small) {
             // cumulative ends over byte ranks (warp 0, lane owns ranks 2*lane, 2*lane+1), then the bucket entries
             const uint32_t rc = rank[s_ctx], nU = s_nU;
-            uint16_t *cum = reinterpret_cast<uint16_t *>(img + DEC_IMG_CUM + (size_t)rc * cumb);
+            uint16_t *cum = reinterpret_cast<uint16_t *>(img + cum_off + (size_t)rc * cumb);
             if (w == 0) {
-                uint32_t r0 = 2 * lane, r1 = r0 + 1;
-                uint32_t f0 = r0 < nU ? F[ualpha[r0]] : 0, f1 = r1 < nU ? F[ualpha[r1]] : 0;
-                uint32_t inc = f0 + f1;
-                for (int dlt = 1; dlt < 32; dlt <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, dlt); if (lane >= (uint32_t)dlt) inc += t; }
-                if (r0 < nU) { cum[r0 + 1] = (uint16_t)(inc - f1); C[r0] = (uint16_t)(inc - f1); }
-                if (r1 < nU) { cum[r1 + 1] = (uint16_t)inc; C[r1] = (uint16_t)inc; }     // C[] reused: range ends by rank
+                uint32_t carry = 0;
+                for (uint32_t rb = 0; rb < nU; rb += 64) {                   // 64 ranks per round, lane owns two
+                    uint32_t r0 = rb + 2 * lane, r1 = r0 + 1;
+                    uint32_t f0 = r0 < nU ? F[ualpha[r0]] : 0, f1 = r1 < nU ? F[ualpha[r1]] : 0;
+                    uint32_t inc = f0 + f1;
+                    for (int dlt = 1; dlt < 32; dlt <<= 1) { uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, dlt); if (lane >= (uint32_t)dlt) inc += t; }
+                    inc += carry;
+                    if (r0 < nU) { cum[r0 + 1] = (uint16_t)(inc - f1); C[r0] = (uint16_t)(inc - f1); }
+                    if (r1 < nU) { cum[r1 + 1] = (uint16_t)inc; C[r1] = (uint16_t)inc; }     // C[] reused: range ends by rank
+                    carry = __shfl_sync(0xFFFFFFFFu, inc, 31);
+                }
                 if (lane == 0) cum[0] = 0;
             }
             __syncthreads();
-            if (tid < DEC_NB) {
+            if (nU > DEC_MAXU) {
+                // wide image: 256 fine buckets of 16 slots, one byte each = the rank whose range holds the bucket's first slot
+                // (first r with C[r] > slot, at most nU - 1); the decoder walks the cumulative row from there
+                uint8_t *fine = img + (size_t)rc * DEC_ROWE;
+                for (uint32_t b = tid; b < 256; b += 128) {
+                    const uint32_t slot = 16 * b;
+                    uint32_t lo = 0, hi = nU - 1;
+                    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (C[mid] <= slot) lo = mid + 1; else hi = mid; }
+                    fine[b] = (uint8_t)lo;
+                }
+            } else if (tid < DEC_NB) {
                 // bucket tid: r = first rank whose range reaches beyond slot 128 * tid (clamped to the last rank), q = the next rank that occurs
                 uint32_t slot = 128 * tid, r = 0;
                 while (r + 1 < nU && C[r] <= slot) r++;
@@ -260,6 +302,7 @@ __global__ void __launch_bounds__(128) k_dec_tables(const BlockDesc *__restrict_
     if (tid == 0) {
         meta[blk].pay_off = s_pos;
         meta[blk].nU = (small && !s_bad) ? s_nU : 0u;
+        meta[blk].img = img_units;
         if (s_bad) status[blk] = CRAMGPU_ERR_CORRUPT;
     }
 }
@@ -763,20 +806,31 @@ __device__ __forceinline__ uint32_t ld_byte(const uint8_t *p, uint32_t pos, uint
 // global memory (L2), the stream and the output byte by byte -- so its one-warp CTAs fit beside k_dec1's and the short
 // blocks are decoded in its shadow: a step costs ~3 L2 round trips instead of ~170 cycles, which nobody waits for.
 // One warp = 8 blocks, lane = state, every step in the general form of dec1_general_step.
+//
+// WIDE = true: the decoder of the blocks with more than DEC_MAXU distinct bytes, whose tables (up to 201 KB) fit no CTA's
+// shared memory: `slots` is the list k_dec_wide_plan made of them, wide[0] their number, wide[1] the blocks per warp (1, 2,
+// 4 or 8: as few as keep the machine's warp slots filled).  A step is a chain of three global-memory round trips (fine
+// bucket -> five cumulative entries -> renormalisation byte); every wide block of the call is in flight at once.
+template <bool WIDE>
 __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ slots, uint32_t nslots,
+                                              const uint32_t *__restrict__ wide,
                                               const uint8_t *__restrict__ d_in, const uint8_t *__restrict__ images,
                                               const DecMeta *__restrict__ meta, uint8_t *__restrict__ d_out, int32_t *__restrict__ status)
 {
     const uint32_t lane = threadIdx.x, k = lane & 3u;
-    const uint32_t slot = blockIdx.x * 8 + (lane >> 2);
-    bool have = slot < nslots;
+    uint32_t gpw = 8;
+    if (WIDE) { nslots = wide[0]; gpw = wide[1]; }
+    const uint32_t slot = blockIdx.x * gpw + (lane >> 2);
+    bool have = slot < nslots && (lane >> 2) < gpw;
     const uint32_t blk = have ? slots[slot] : 0;
     const BlockDesc d = desc[blk];
-    const uint32_t nU = have && status[blk] == 0 ? meta[blk].nU : 0u;
-    have = have && nU != 0 && nU <= DEC_MAXU;
+    const DecMeta mt = meta[blk];
+    const uint32_t nU = have && status[blk] == 0 ? mt.nU : 0u;
+    have = have && nU != 0 && mt.img != DEC_NO_IMG && (WIDE ? nU > DEC_MAXU : nU <= DEC_MAXU);
     if (__ballot_sync(0xFFFFFFFFu, have) == 0) return;
-    const uint8_t *img = images + (size_t)d.o1_index * DEC_IMG;
+    const uint8_t *img = images + (size_t)(have ? mt.img : 0u) * 256u;
     const uint32_t cumb = dec_cumb(nU);
+    const uint32_t cum_off = WIDE ? nU * DEC_ROWE : DEC_IMG_CUM, alpha_off = WIDE ? cum_off + nU * cumb : DEC_IMG_ALPHA;
     const uint32_t n = have ? d.out_len : 0, q = n >> 2;
     uint8_t *out = d_out + d.out_off + (uint64_t)k * q;
     const uint32_t mylen = (k == 3) ? n - 3 * q : q;
@@ -784,7 +838,7 @@ __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc
     const uint32_t len = d.in_len;
     bool under = false;
     uint32_t bad = 0;
-    uint32_t cur = have ? meta[blk].pay_off : 0, x = 0;
+    uint32_t cur = have ? mt.pay_off : 0, x = 0;
     if (have) {
         x = ld_byte(in, cur + 4 * k, len, under) | (ld_byte(in, cur + 4 * k + 1, len, under) << 8) |
             (ld_byte(in, cur + 4 * k + 2, len, under) << 16) | (ld_byte(in, cur + 4 * k + 3, len, under) << 24);
@@ -796,7 +850,29 @@ __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc
     for (uint32_t t = 0; t < max_steps; t++) {
         const bool act = have && t < mylen;
         uint32_t xn = x, rn = r;
-        if (act) {
+        if (act && WIDE) {
+            // fine bucket -> first candidate rank, then one round of five cumulative entries: the start of the candidate and the
+            // next four ends (sorted; the ones <= m form a prefix; the row ends in 0xFFFF padding)
+            const uint32_t m = x & (TOTFREQ - 1);
+            const uint16_t *cum = reinterpret_cast<const uint16_t *>(img + cum_off + (size_t)r * cumb);
+            uint32_t j = __ldg(img + (size_t)r * DEC_ROWE + (m >> 4));
+            uint32_t C, Fq;
+            for (;;) {
+                const uint32_t e0 = __ldg(cum + j), e1 = __ldg(cum + j + 1), e2 = __ldg(cum + j + 2), e3 = __ldg(cum + j + 3), e4 = __ldg(cum + j + 4);
+                const uint32_t c = (uint32_t)(m >= e1) + (uint32_t)(m >= e2) + (uint32_t)(m >= e3) + (uint32_t)(m >= e4);
+                j += c;
+                if (c < 4) {
+                    C = c == 0 ? e0 : c == 1 ? e1 : c == 2 ? e2 : e3;
+                    Fq = (c == 0 ? e1 : c == 1 ? e2 : c == 2 ? e3 : e4) - C;
+                    break;
+                }
+                if (j >= nU) { C = e4; Fq = 0; break; }                      // ran off the row: corrupt
+            }
+            if (j >= nU || Fq == 0 || Fq > TOTFREQ) { bad = 1; j = min(j, nU - 1); Fq &= 0x1FFF; }         // only a corrupt stream gets here
+            rn = j;
+            xn = Fq * (x >> TF_SHIFT) + m - C;                                   // [Decoding.java:35-48]
+            out[t] = __ldg(img + alpha_off + rn);
+        } else if (act) {
             const uint32_t m = x & (TOTFREQ - 1);
             const uint2 e = __ldg(reinterpret_cast<const uint2 *>(img + (size_t)r * DEC_ROWE + ((m >> 7) << 3)));
             const uint32_t c0 = e.x & 0xFFFFu, f0 = e.x >> 16, f1 = e.y & 0xFFFFu, r0 = (e.y >> 16) & 0xFFu, r1 = e.y >> 24;
@@ -805,7 +881,7 @@ __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc
             if (m - c0 >= f0) {
                 C = c0 + f0; Fq = f1; rn = r1;
                 if (m - C >= f1) {
-                    const uint16_t *cum = reinterpret_cast<const uint16_t *>(img + DEC_IMG_CUM + (size_t)r * cumb);
+                    const uint16_t *cum = reinterpret_cast<const uint16_t *>(img + cum_off + (size_t)r * cumb);
                     uint32_t j = r1 + 1;
                     while (m >= __ldg(cum + j + 1)) j++;
                     C = __ldg(cum + j);
@@ -815,7 +891,7 @@ __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc
                 }
             }
             xn = Fq * (x >> TF_SHIFT) + m - C;                                   // [Decoding.java:35-48]
-            out[t] = __ldg(img + DEC_IMG_ALPHA + rn);
+            out[t] = __ldg(img + alpha_off + rn);
         }
         __syncwarp();
         const bool n1 = act && xn < RANS_L;
@@ -830,6 +906,40 @@ __global__ void __launch_bounds__(32) k_dec1s(const BlockDesc *__restrict__ desc
         x = xn; r = rn;
     }
     if (have && (under || bad)) status[blk] = CRAMGPU_ERR_CORRUPT;
+}
+
+// k_dec_wide_plan: one CTA.  The order-1 blocks with a pooled table image, in the order of `slots` (longest first) -> wide_slots;
+// wide[0] = their number, wide[1] = blocks per warp of k_dec1s<true>: the smallest of 1, 2, 4, 8 that needs at most
+// `warp_budget` warps.
+__global__ void __launch_bounds__(256) k_dec_wide_plan(const uint32_t *__restrict__ slots, uint32_t n, const DecMeta *__restrict__ meta,
+                                                       const int32_t *__restrict__ status, uint32_t warp_budget,
+                                                       uint32_t *__restrict__ wide_slots, uint32_t *__restrict__ wide)
+{
+    __shared__ uint32_t s_w[8], s_base;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    if (tid == 0) s_base = 0;
+    __syncthreads();
+    for (uint32_t i0 = 0; i0 < n; i0 += 256) {
+        const uint32_t i = i0 + tid;
+        bool is = false;
+        uint32_t blk = 0;
+        if (i < n) { blk = slots[i]; const DecMeta m = meta[blk]; is = status[blk] == 0 && m.nU > DEC_MAXU && m.img != DEC_NO_IMG; }
+        const uint32_t b = __ballot_sync(0xFFFFFFFFu, is);
+        if (lane == 0) s_w[w] = __popc(b);
+        __syncthreads();
+        uint32_t at = s_base + __popc(b & ((1u << lane) - 1u));
+        for (uint32_t k = 0; k < w; k++) at += s_w[k];
+        if (is) wide_slots[at] = blk;
+        __syncthreads();
+        if (tid == 0) { uint32_t t = 0; for (int k = 0; k < 8; k++) t += s_w[k]; s_base += t; }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const uint32_t nw = s_base;
+        uint32_t g = 1;
+        while (g < 8 && (nw + g - 1) / g > warp_budget) g *= 2;
+        wide[0] = nw; wide[1] = g;
+    }
 }
 
 // k_dec0: the order-0 decoder in the two-warp form of k_dec1 (decoder warp + helper warp, 8 blocks per CTA).
@@ -1033,7 +1143,7 @@ __global__ void __launch_bounds__(128) k_dec1_big(const BlockDesc *__restrict__ 
     const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5, k = lane & 3u;
     for (uint32_t slot = blockIdx.x; slot < nslots; slot += gridDim.x) {
         const uint32_t blk = slots[slot];
-        if (status[blk] != 0 || meta[blk].nU <= DEC_MAXU) continue;             // same answer for the whole CTA
+        if (status[blk] != 0 || meta[blk].nU <= DEC_MAXU || meta[blk].img != DEC_NO_IMG) continue;       // same answer for the whole CTA
         const BlockDesc d = desc[blk];
         const uint8_t *in = d_in + d.in_off;
         const uint32_t len = d.in_len;
@@ -1197,7 +1307,8 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     // k_dec1s instead of queueing behind them.  s1 is sorted by length: the long blocks are its first n_long entries.
     const bool ride = ctx->hp_stream && n_long >= (uint32_t)sms && max1 >= (256u << 10) && n1 > n_long;
     const uint32_t n1_main = ride ? n_long : n1, n1_ride = n1 - n1_main;
-    const uint32_t nslab = std::min(n1, 256u);                 // CTAs (= table slabs) of the large-alphabet path
+    const uint32_t nslab = std::min(n1, 16u);                  // CTAs (= 1.25 MB table slabs) of the overflow path for wide alphabets
+    const uint64_t pool_bytes = (uint64_t)std::min(n1, ctx->dec_wide_pool_blocks) * DEC_WIDE_IMG_MAX;
     const uint32_t ncta_max = (n1_main + 3) / 4 + 1;           // a CTA of k_dec1 takes at least 4 blocks (or all that are left)
 
     Carver c;
@@ -1205,8 +1316,9 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     size_t o_s0 = c.take(4 * (size_t)std::max(n0, 1u)), o_s1 = c.take(4 * (size_t)std::max(n1, 1u));
     size_t o_meta = c.take(sizeof(DecMeta) * (size_t)nblocks);
     size_t o_lut0 = c.take(4096 * (size_t)n0 + 16), o_fc0 = c.take(1024 * (size_t)n0 + 16);
-    size_t o_img = c.take((size_t)n1 * DEC_IMG + 16);
+    size_t o_img = c.take((size_t)n1 * DEC_IMG + pool_bytes + 16);          // fixed slots, then the pool of wide images
     size_t o_slab = c.take((size_t)nslab * BIG_SLAB + 16);
+    size_t o_wslots = c.take(4 * (size_t)std::max(n1, 1u)), o_wide = c.take(16);
     size_t o_first = c.take(4 * (size_t)ncta_max), o_cfg = c.take(4 * (size_t)ncta_max), o_ncta = c.take(16);
     if (int rc = pool_reserve(ctx, ctx->scratch, c.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->scratch.p;
@@ -1244,7 +1356,10 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         ctx->dec_attr_done = true;
     }
     if (n0 + n1) {
-        LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, images, meta, d_status));
+        uint32_t *wide_slots = (uint32_t *)(S + o_wslots), *wide = (uint32_t *)(S + o_wide);
+        CUDA_TRY(ctx, cudaMemsetAsync(wide, 0, 16, st));                    // [2] = pool cursor
+        LAUNCH(ctx, st, "k_dec_tables", k_dec_tables<<<nblocks, 128, 0, st>>>(dd, d_in, lut0, fc0, images, n1 * (DEC_IMG / 256u),
+                                                                              (uint32_t)(pool_bytes / 256u), wide + 2, meta, d_status));
         // k_dec1 goes to the context's high-priority stream; the kernels that may run beside it (short blocks, large
         // alphabets, order 0) are enqueued on `st` before `st` waits for it
         cudaStream_t hs = ctx->hp_stream ? ctx->hp_stream : st;
@@ -1253,7 +1368,11 @@ int rans_decode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
             if (hs != st) { cudaEventRecord(ctx->hp_in, st); cudaStreamWaitEvent(hs, ctx->hp_in, 0); }
             LAUNCH(ctx, hs, "k_dec1", k_dec1<DEC1_NS><<<ncta_max, 32 * DEC1_WARPS, DEC1_SMEM, hs>>>(dd, slots1, cta_first, cta_cfg, ncta, d_in, images, meta, d_out, d_status));
             if (hs != st) cudaEventRecord(ctx->hp_out, hs);
-            if (n1_ride) LAUNCH(ctx, st, "k_dec1s", k_dec1s<<<(n1_ride + 7) / 8, 32, 0, st>>>(dd, slots1 + n1_main, n1_ride, d_in, images, meta, d_out, d_status));
+            if (n1_ride) LAUNCH(ctx, st, "k_dec1s", k_dec1s<false><<<(n1_ride + 7) / 8, 32, 0, st>>>(dd, slots1 + n1_main, n1_ride, nullptr, d_in, images, meta, d_out, d_status));
+            // wide alphabets: from their pooled images in global memory, every block of the call at once; what found no room in
+            // the pool goes through k_dec1_big's slabs
+            LAUNCH(ctx, st, "k_dec_wide_plan", k_dec_wide_plan<<<1, 256, 0, st>>>(slots1, n1, meta, d_status, (uint32_t)sms * 16u, wide_slots, wide));
+            LAUNCH(ctx, st, "k_dec1w", k_dec1s<true><<<n1, 32, 0, st>>>(dd, wide_slots, 0, wide, d_in, images, meta, d_out, d_status));
             LAUNCH(ctx, st, "k_dec1_big", k_dec1_big<<<nslab, 128, 0, st>>>(dd, slots1, n1, d_in, slabs, meta, d_out, d_status));
         }
         if (n0) {

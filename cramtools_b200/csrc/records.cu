@@ -25,6 +25,7 @@ enum { OP_M = 0, OP_I, OP_D, OP_N, OP_S, OP_H, OP_P, OP_EQ, OP_X };
 struct PolSet {
     int n;                       // < 0: lossless
     int per_base;                // any policy with base categories
+    int any_bin;                 // any policy with the BIN treatment (the only one that can fault, see bin_fault)
     cramgpu_qs_policy p[MAX_POL];
 };
 
@@ -89,8 +90,14 @@ __device__ __forceinline__ uint8_t illumina_bin(uint8_t q)
 {
     return q < 2 ? q : q < 10 ? 6 : q < 20 ? 15 : q < 25 ? 22 : q < 30 ? 27 : q < 35 ? 33 : q < 40 ? 37 : 40;
 }
-__device__ __forceinline__ uint8_t treat(uint8_t q, int treatment)
+// The table has 110 entries and is indexed with a signed byte: a score of 110..255 makes the reference throw
+// ArrayIndexOutOfBoundsException out of addQualityScores [QualityScorePreservation.java:258-266].  The kernels note that in
+// the call's status word; k_rec_bin_fault then marks the records (bit 7 of force_qs).
+#define BIN_FAULT_Q 110
+__device__ __forceinline__ void bin_fault(int32_t *status) { atomicCAS(status, 0, CRAMGPU_ERR_UNSUPPORTED); }
+__device__ __forceinline__ uint8_t treat(uint8_t q, int treatment, int32_t *status)
 {
+    if (treatment == 1 && q >= BIN_FAULT_Q) bin_fault(status);
     return treatment == 1 ? illumina_bin(q) : treatment == 2 ? (uint8_t)0xFF : q;
 }
 __device__ __forceinline__ bool read_in_category(const cramgpu_qs_policy &p, uint16_t flag, uint8_t mapq)
@@ -118,14 +125,14 @@ __device__ __forceinline__ bool base_mask(const cramgpu_qs_policy &p, bool match
 }
 // the score addQualityScores leaves at one base (0xFF = -1 = none), policies in their sorted order
 __device__ __forceinline__ uint8_t score_at(const PolSet &ps, uint8_t q, uint16_t flag, uint8_t mapq, int32_t pos,
-                                            bool match, bool is_ins, bool dmark)
+                                            bool match, bool is_ins, bool dmark, int32_t *status)
 {
     uint8_t s = 0xFF;
     for (int k = 0; k < ps.n; k++) {
         const cramgpu_qs_policy &p = ps.p[k];
         if (!read_in_category(p, flag, mapq)) continue;
-        if (p.n_base_cats == 0) { if (p.treatment != 2) s = treat(q, p.treatment); }
-        else if (pos != 0 && base_mask(p, match, is_ins, dmark)) s = treat(q, p.treatment);
+        if (p.n_base_cats == 0) { if (p.treatment != 2) s = treat(q, p.treatment, status); }
+        else if (pos != 0 && base_mask(p, match, is_ins, dmark)) s = treat(q, p.treatment, status);
     }
     return s;
 }
@@ -463,9 +470,12 @@ __device__ __forceinline__ uint32_t pb_mask(const cramgpu_qs_policy &p, uint32_t
 }
 // score_at above, bit-parallel: `has` = bases that end up with a score, `bin` = those whose score is binned.
 // appl: bit k = policy k applies to the record (its read category)
-__device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint32_t match, uint32_t ins, uint32_t dm, uint32_t &has, uint32_t &bin)
+// binany = bases that any applicable policy bins, overridden later or not (those are the ones the reference indexes the
+// binning table with)
+__device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint32_t match, uint32_t ins, uint32_t dm, uint32_t &has, uint32_t &bin,
+                                          uint32_t &binany)
 {
-    has = 0; bin = 0;
+    has = 0; bin = 0; binany = 0;
     for (int k = 0; k < ps.n; k++) {
         if (!((appl >> k) & 1)) continue;
         const cramgpu_qs_policy &p = ps.p[k];
@@ -474,6 +484,7 @@ __device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint3
         else hit = pb_mask(p, match, ins, dm);
         has = (has & ~hit) | (p.treatment != 2 ? hit : 0u);
         bin = (bin & ~hit) | (p.treatment == 1 ? hit : 0u);
+        binany |= p.treatment == 1 ? hit : 0u;
     }
 }
 // one bit per byte of a word: bit j = byte j of v is non-zero in its low bit (v holds 0x00 / 0xFF per byte)
@@ -640,7 +651,14 @@ __device__ __forceinline__ uint32_t perbase_read(const RecArgs &a, const PolSet 
                     } else if (op == OP_I) fbits = 1;
                     else fbits = g.rel == 0 ? 1u : 0u;                            // S: the clip's feature sits at its first base
                     uint32_t has = 0, bin = 0;
-                    if (qf) { pb_planes(ps, appl, g.match, g.ins, g.dm, has, bin); has &= valid; }
+                    if (qf) {
+                        uint32_t binany;
+                        pb_planes(ps, appl, g.match, g.ins, g.dm, has, bin, binany);
+                        has &= valid;
+                        if (ps.any_bin)
+                            for (uint32_t m = binany & valid; m; m &= m - 1)
+                                if (rq[z0 + __ffs(m) - 1] >= BIN_FAULT_Q) bin_fault(a.status);
+                    }
                     for (uint32_t todo = fbits | has; todo; todo &= todo - 1) {
                         const uint32_t j = (uint32_t)__ffs(todo) - 1;
                         const int32_t zi = z0 + (int32_t)j;
@@ -956,7 +974,7 @@ __device__ __forceinline__ void walk_read(const RecArgs &a, const PolSet &ps, co
         int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
         for (uint64_t ci = c0; ci < c1; ci++) {
             uint32_t cw = a.cigar[ci]; int op = cw & 15; int64_t len = cw >> 4;
-            if (op > OP_X) { if (lane == 0) atomicCAS(a.status, 0, CRAMGPU_ERR_ARG); break; }   // "Unsupported cigar operator"
+            if (op > OP_X) { if (lane == 0) atomicExch(a.status, CRAMGPU_ERR_ARG); break; }   // "Unsupported cigar operator"
             if (op == OP_D) { if (d_a != z) { d_b = d_a; d_a = z; } }
             if (!consumes_read(op)) {
                 // D, N, H, P: one feature at the next read position [:228-240]
@@ -998,7 +1016,7 @@ __device__ __forceinline__ void walk_read(const RecArgs &a, const PolSet &ps, co
                     uint8_t sc = 0xFF;
                     if (q_feats && in && zi < rlen) {
                         bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
-                        sc = score_at(ps, rq[zi], flag, mapq, pos, b == rraw, op == OP_I, dm);
+                        sc = score_at(ps, rq[zi], flag, mapq, pos, b == rraw, op == OP_I, dm, a.status);
                     }
                     bool hasQ = sc < 128;                                                     // scores[i] > -1 [:290]
                     uint32_t bF = __ballot_sync(0xFFFFFFFFu, hasF), bQ = __ballot_sync(0xFFFFFFFFu, hasQ);
@@ -1105,13 +1123,19 @@ __global__ void __launch_bounds__(128) k_rec_walk(RecArgs a, PolSet ps)
 // categories in play) -- preserved as it is, or binned [Binning.java:63-71].  One thread per read, in order; 32 records of
 // one length and one treatment whose arrays lie back to back are done as one warp-wide copy.
 struct BinW {
+    int32_t *status;
     __device__ __forceinline__ uint32_t operator()(uint32_t w) const
     {
+        // any byte of w >= 110: bit 7 set, or the low seven bits + 18 carry into bit 7
+        if (((w | ((w & 0x7F7F7F7Fu) + 0x12121212u)) & 0x80808080u)) bin_fault(status);
         return (uint32_t)illumina_bin((uint8_t)w) | ((uint32_t)illumina_bin((uint8_t)(w >> 8)) << 8) |
                ((uint32_t)illumina_bin((uint8_t)(w >> 16)) << 16) | ((uint32_t)illumina_bin((uint8_t)(w >> 24)) << 24);
     }
 };
-struct BinB { __device__ __forceinline__ uint8_t operator()(uint8_t b) const { return illumina_bin(b); } };
+struct BinB {
+    int32_t *status;
+    __device__ __forceinline__ uint8_t operator()(uint8_t b) const { if (b >= BIN_FAULT_Q) bin_fault(status); return illumina_bin(b); }
+};
 struct FillW { __device__ __forceinline__ uint32_t operator()(uint32_t) const { return 0xFFFFFFFFu; } };
 struct FillB { __device__ __forceinline__ uint8_t operator()(uint8_t) const { return 0xFF; } };
 
@@ -1135,8 +1159,11 @@ __global__ void __launch_bounds__(128) k_rec_forced_flat(RecArgs a, PolSet ps)
         rlen = a.read_off[r + 1] - lo;
         const uint16_t flag = a.flag[r];
         const uint8_t mapq = a.mapq[r];
+        bool binned = false;
         for (int k = 0; k < ps.n; k++)
-            if (read_in_category(ps.p[k], flag, mapq) && ps.p[k].treatment != 2) treatment = ps.p[k].treatment;
+            if (read_in_category(ps.p[k], flag, mapq) && ps.p[k].treatment != 2) { treatment = ps.p[k].treatment; binned |= treatment == 1; }
+        if (binned && treatment != 1)                    // binned by an earlier policy, then overwritten: the lookup still happened
+            for (uint64_t i = 0; i < rlen; i++) if (a.quals[lo + i] >= BIN_FAULT_Q) bin_fault(a.status);
     }
     const bool has = qoff != ~0ull && rlen < (1ull << 31);
     const uint64_t q0 = __shfl_sync(0xFFFFFFFFu, qoff, 0), lo0 = __shfl_sync(0xFFFFFFFFu, lo, 0), rl0 = __shfl_sync(0xFFFFFFFFu, rlen, 0);
@@ -1145,11 +1172,11 @@ __global__ void __launch_bounds__(128) k_rec_forced_flat(RecArgs a, PolSet ps)
     const bool flat = has && rlen == rl0 && treatment == t0 && qoff == q0 + (uint64_t)lane * L0 && lo == lo0 + (uint64_t)lane * L0;
     if (__all_sync(0xFFFFFFFFu, flat) && rl0 <= (1u << 20)) {
         if (t0 == 0) warp_copy(a.streams + q0, a.quals + lo0, 32 * L0, lane);
-        else if (t0 == 1) warp_copy_x(a.streams + q0, a.quals + lo0, 32 * L0, lane, BinW(), BinB());
+        else if (t0 == 1) warp_copy_x(a.streams + q0, a.quals + lo0, 32 * L0, lane, BinW{a.status}, BinB{a.status});
         else warp_copy_x(a.streams + q0, a.quals + lo0, 32 * L0, lane, FillW(), FillB());
     } else if (has) {
         if (treatment == 0) copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, IdW(), IdB());
-        else if (treatment == 1) copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, BinW(), BinB());
+        else if (treatment == 1) copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, BinW{a.status}, BinB{a.status});
         else copy_bytes(a.streams + qoff, a.quals + lo, (uint32_t)rlen, FillW(), FillB());
     }
 }
@@ -1182,7 +1209,7 @@ __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
     const uint8_t mapq = a.mapq[r];
     uint8_t *dst = a.streams + qoff;
     // read-level part of every base (bases not covered by a read-consuming CIGAR op see only these policies)
-    for (int64_t i = lane; i < rlen; i += 32) dst[i] = score_at(ps, rq[i], flag, mapq, 0, false, false, false);
+    for (int64_t i = lane; i < rlen; i += 32) dst[i] = score_at(ps, rq[i], flag, mapq, 0, false, false, false, a.status);
     if (!ps.per_base || pos == 0) return;
     __syncwarp();
     int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
@@ -1196,12 +1223,64 @@ __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
                 int64_t rp = (int64_t)pos - 1 + aoff + i;
                 uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : 0;
                 bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
-                dst[zi] = score_at(ps, rq[zi], flag, mapq, pos, rb[zi] == tb, op == OP_I, dm);
+                dst[zi] = score_at(ps, rq[zi], flag, mapq, pos, rb[zi] == tb, op == OP_I, dm, a.status);
             }
             z += len;
         }
         if (consumes_ref(op)) aoff += len;
     }
+}
+
+// After a call whose status word says that a binned score was outside the binning table: which records?  One warp per
+// record, every base against every BIN policy that applies to it (the places where score_at calls treat with BIN), bit 7
+// of force_qs set for the records the reference throws on.  Runs only then.
+__device__ __forceinline__ bool bin_hits(const PolSet &ps, uint16_t flag, uint8_t mapq, int32_t pos, bool match, bool is_ins, bool dmark)
+{
+    for (int k = 0; k < ps.n; k++) {
+        const cramgpu_qs_policy &p = ps.p[k];
+        if (p.treatment != 1 || !read_in_category(p, flag, mapq)) continue;
+        if (p.n_base_cats == 0 || (pos != 0 && base_mask(p, match, is_ins, dmark))) return true;
+    }
+    return false;
+}
+__global__ void __launch_bounds__(128) k_rec_bin_fault(RecArgs a, PolSet ps)
+{
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.n_reads) return;
+    if (a.rflags && (a.rflags[r] & CRAMGPU_RF_NO_QUALS)) return;                  // addQualityScores returns first [:276-280]
+    const uint32_t c = container_of(a.cont_off, a.n_containers, r);
+    const uint8_t *ref = a.ref + a.ref_off[c];
+    const int64_t ref_len = (int64_t)a.ref_len[c];
+    const uint64_t lo = a.read_off[r];
+    const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
+    const uint8_t *rb = a.bases + lo, *rq = a.quals + lo;
+    const int32_t pos = a.pos[r];
+    const uint16_t flag = a.flag[r];
+    const uint8_t mapq = a.mapq[r];
+    bool fault = false;
+    for (int64_t i = lane; i < rlen; i += 32) fault |= rq[i] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, 0, false, false, false);
+    if (ps.per_base && pos != 0) {
+        int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
+        for (uint64_t ci = a.cigar_off[r]; ci < a.cigar_off[r + 1]; ci++) {
+            uint32_t cw = a.cigar[ci]; int op = cw & 15; int64_t len = cw >> 4;
+            if (op == OP_D) { if (d_a != z) { d_b = d_a; d_a = z; } }
+            if (consumes_read(op)) {
+                for (int64_t i = lane; i < len; i += 32) {
+                    int64_t zi = z + i;
+                    if (zi >= rlen) break;
+                    int64_t rp = (int64_t)pos - 1 + aoff + i;
+                    uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                    bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
+                    fault |= rq[zi] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, pos, rb[zi] == tb, op == OP_I, dm);
+                }
+                z += len;
+            }
+            if (consumes_ref(op)) aoff += len;
+        }
+    }
+    fault = __any_sync(0xFFFFFFFFu, fault);
+    if (lane == 0 && fault) a.force[r] |= 0x80;
 }
 
 // SubstitutionMatrix.<init>(long[][]) / rank [SubstitutionMatrix.java:42-57,129-169]: one thread per container
@@ -1651,6 +1730,8 @@ extern "C" int cramgpu_parse_lossy_spec(const char *spec, cramgpu_qs_policy *out
     return n;
 }
 
+struct RecFault { RecArgs a; PolSet ps; };       // what k_rec_bin_fault needs, kept from the call (ctx->rec_fault)
+
 static int make_polset(cramgpu_ctx *ctx, const cramgpu_qs_policy *pol, int n, PolSet &ps)
 {
     memset(&ps, 0, sizeof ps);
@@ -1661,6 +1742,7 @@ static int make_polset(cramgpu_ctx *ctx, const cramgpu_qs_policy *pol, int n, Po
         ps.p[k] = pol[k];
         if (pol[k].n_base_cats < 0 || pol[k].n_base_cats > 8) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "bad policy");
         if (pol[k].n_base_cats) ps.per_base = 1;
+        if (pol[k].treatment == 1) ps.any_bin = 1;
     }
     return CRAMGPU_OK;
 }
@@ -1779,7 +1861,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     const uint64_t *grand = (const uint64_t *)pr;
     int32_t dstatus = *(const int32_t *)(pr + 256);
-    if (dstatus) return ctx_fail(ctx, dstatus, "Unsupported cigar operator");
+    if (dstatus == CRAMGPU_ERR_ARG) return ctx_fail(ctx, dstatus, "Unsupported cigar operator");    // else: a binning fault, reported at the end
     const uint64_t sbytes = grand[0], nfeat = grand[1], paylen = grand[2];
     if (h_stream_off) memcpy(h_stream_off, pr + 320, tab);
     if (h_stream_len) memcpy(h_stream_len, pr + 320 + tab, tab);
@@ -1808,6 +1890,15 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     else if (ps.n >= 0) LAUNCH(ctx, st, "k_rec_forced_scores", k_rec_forced_scores<<<grid, 128, 0, st>>>(a, ps));
     CUDA_TRY(ctx, cudaMemcpyAsync(a.feat_off + n, d_grand + 1, 8, cudaMemcpyDeviceToDevice, st));
     CUDA_TRY(ctx, cudaGetLastError());
+    *(volatile int32_t *)(pr + 264) = 0;
+    if (ps.any_bin) {
+        // a score outside the binning table: the status word says so once the stream has drained (the callers synchronise and
+        // then run features_encode_fault)
+        CUDA_TRY(ctx, cudaMemcpyAsync(pr + 264, S + o_status, 4, cudaMemcpyDeviceToHost, st));
+        if (!ctx->rec_fault) ctx->rec_fault = malloc(sizeof(RecFault));
+        if (!ctx->rec_fault) return ctx_fail(ctx, CRAMGPU_ERR_CUDA, "out of host memory");
+        ((RecFault *)ctx->rec_fault)->a = a; ((RecFault *)ctx->rec_fault)->ps = ps;
+    }
 
     out->n_feat = nfeat; out->f_op = a.f_op; out->f_pos = a.f_pos; out->f_val = a.f_val; out->f_aux = a.f_aux;
     out->feat_off = a.feat_off; out->payload = a.payload; out->payload_len = paylen; out->force_qs = a.force;
@@ -1815,6 +1906,19 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     out->stream_len = d_slen; out->read_qs_off = a.read_qs_off; out->read_ba_off = a.read_ba_off;
     return CRAMGPU_OK;
 }
+
+// after the stream has drained: did a BIN treatment meet a score of 110 or more?  Then mark the records and fail the call the
+// way the reference does (ArrayIndexOutOfBoundsException out of Binning.Illumina_binning_matrix).  The results stay valid
+// for the other records.
+static int features_encode_fault(cramgpu_ctx *ctx, cudaStream_t st)
+{
+    if (*(volatile int32_t *)((uint8_t *)ctx->pin_rec + 264) == 0) return CRAMGPU_OK;
+    const RecFault *f = (const RecFault *)ctx->rec_fault;
+    LAUNCH(ctx, st, "k_rec_bin_fault", k_rec_bin_fault<<<(uint32_t)((f->a.n_reads + 3) / 4), 128, 0, st>>>(f->a, f->ps));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CRAMGPU_ERR_UNSUPPORTED;
+}
+#define BIN_FAULT_MSG "ArrayIndexOutOfBoundsException: quality score >= 110 under a binning treatment (bit 7 of force_qs marks the records)"
 
 extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
                                            int n_policies, cramgpu_features *out, uint64_t *h_stream_off,
@@ -1825,6 +1929,10 @@ extern "C" int cramgpu_features_encode_dev(cramgpu_ctx *ctx, const cramgpu_reads
     cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
     if (int rc = features_encode_impl(ctx, reads, policies, n_policies, out, h_stream_off, h_stream_len, nullptr, st)) return rc;
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (features_encode_fault(ctx, st)) {
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        return ctx_fail(ctx, CRAMGPU_ERR_UNSUPPORTED, BIN_FAULT_MSG);
+    }
     return CRAMGPU_OK;
 }
 
@@ -1923,12 +2031,18 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
         if (((host_series >> k) & 1) && span[2 * k + 1])
             CUDA_TRY(ctx, memcpy_pieces(po + so.off[r_str] + span[2 * k], df.streams + span[2 * k], span[2 * k + 1], cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const bool fault = features_encode_fault(ctx, st) != CRAMGPU_OK;
+    if (fault) {
+        CUDA_TRY(ctx, down(r_force, df.force_qs, n));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
     *out = df;
     out->f_op = po + so.off[r_op]; out->f_pos = (const int32_t *)(po + so.off[r_pos]); out->f_val = (const int32_t *)(po + so.off[r_val]);
     out->f_aux = (const int32_t *)(po + so.off[r_aux]); out->feat_off = (const uint64_t *)(po + so.off[r_foff]); out->payload = po + so.off[r_pay];
     out->force_qs = po + so.off[r_force]; out->matrix = po + so.off[r_mtx]; out->streams = po + so.off[r_str];
     out->stream_off = (const uint64_t *)(po + so.off[r_soff]); out->stream_len = (const uint64_t *)(po + so.off[r_slen]);
     out->read_qs_off = (const uint64_t *)(po + so.off[r_qso]); out->read_ba_off = (const uint64_t *)(po + so.off[r_bao]);
+    if (fault) return ctx_fail(ctx, CRAMGPU_ERR_UNSUPPORTED, BIN_FAULT_MSG);
     return CRAMGPU_OK;
 }
 

@@ -1,0 +1,321 @@
+// slice.cu -- slice header fields and content digests of a batch of slices.
+//
+// What ContainerFactory.buildSlice [htsjdk ContainerFactory.java:138-176] derives from the records of a slice: record count,
+// base count, reference id (or MULTI_REFERENCE), alignment start / span, and the BD / SD digests: CRC32 of every record's
+// base array / score array, summed as ints (cram/digest/Crc32Hasher, IntegerSumCombine).  The four SHA tags of
+// ContentDigests.ALL are constants in htsjdk 2.4.1 (include/cramgpu.h says why).
+//
+// One thread per record.  CRC32 one byte per table lookup, the table replicated per lane in shared memory (32 KB: no bank
+// conflicts); a record's bytes are read as aligned 16-byte loads, so records may start at any byte.  The per-slice sums go
+// through a warp reduction and one atomic per warp and field.  2 bytes in per base, nothing out; bound by the shared-memory
+// lookups (one per byte and lane), not by HBM.
+#include "internal.cuh"
+#include <string.h>
+
+namespace {
+
+struct SliceAcc {                      // zero-initialised
+    unsigned long long bases;
+    uint32_t bd, sd;
+    int32_t inv_min_start;             // max of (INT32_MAX - start) over the placed records: 0 = none
+    int32_t max_end;
+    uint32_t multi;                    // a record's reference differs from the first record's
+    uint32_t pad;
+};
+
+struct SliceArgs {
+    uint64_t n_reads; uint32_t n_containers;
+    const uint64_t *cont_off;          // device copy
+    const uint8_t *bases, *scores, *rflags, *f_op, *force_qs, *streams;
+    const uint64_t *read_off, *feat_off, *read_qs_off;
+    const int32_t *ref_id, *pos, *f_pos, *f_val, *f_aux;
+    const uint16_t *flag;
+    SliceAcc *acc;
+    cramgpu_slice_header *out;
+};
+
+// CRC32 one byte at a time, T = the 256-entry table replicated 32 times: entry i of lane l at T[32 * i + l], so that the 32
+// lanes of a warp, each looking up its own index, always hit 32 different banks (a table shared by the lanes would serialise
+// 3-4 ways on random indices, and the lookups are the whole cost of this kernel).
+__device__ __forceinline__ uint32_t crc_step(uint32_t crc, const uint32_t *Tl) { return Tl[(crc & 0xFFu) << 5] ^ (crc >> 8); }
+__device__ __forceinline__ uint32_t crc_byte(uint32_t crc, uint32_t b, const uint32_t *Tl) { return crc_step(crc ^ b, Tl); }
+
+// java.util.zip.CRC32 of len bytes at p (any alignment).  The bytes come in as aligned 16-byte loads; only the aligned chunks
+// that hold bytes of the span are read, and of the first and the last chunk only the words / bytes inside it count.
+__device__ __forceinline__ uint32_t crc32_span(const uint8_t *p, uint32_t len, const uint32_t *Tl)
+{
+    if (!len) return 0;
+    const uint32_t mis = (uint32_t)((uintptr_t)p & 15);
+    const uint4 *q = (const uint4 *)((uintptr_t)p - mis);
+    const uint32_t end = mis + len;                       // span = [mis, end) in bytes from q
+    uint32_t crc = ~0u;
+    for (uint32_t base = 0; base < end; base += 16, q++) {
+        const uint4 v = __ldg(q);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (uint32_t k = 0; k < 4; k++) {
+            const uint32_t wb = base + 4 * k;             // first byte of this word
+            if (wb >= mis && wb + 4 <= end) {             // the common case: the whole word
+                crc ^= w[k];
+                crc = crc_step(crc, Tl); crc = crc_step(crc, Tl); crc = crc_step(crc, Tl); crc = crc_step(crc, Tl);
+            } else if (wb + 4 > mis && wb < end) {        // first / last word of the span: bytes [lo, hi) of it
+                const uint32_t lo = wb < mis ? mis - wb : 0u, hi = min(4u, end - wb);
+                uint32_t x = w[k] >> (8 * lo);
+                for (uint32_t b = lo; b < hi; b++) { crc = crc_byte(crc, x & 0xFFu, Tl); x >>= 8; }
+            }
+        }
+    }
+    return ~crc;
+}
+
+__device__ __forceinline__ uint32_t container_of(const uint64_t *cont_off, uint32_t nc, uint64_t r)
+{
+    uint32_t lo = 0, hi = nc;                       // largest c with cont_off[c] <= r
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (cont_off[mid] <= r) lo = mid; else hi = mid; }
+    return lo;
+}
+
+#define SLICE_THREADS 512
+__global__ void __launch_bounds__(SLICE_THREADS) k_slice_digest(SliceArgs a)
+{
+    __shared__ uint32_t Trep[256 * 32];
+    for (uint32_t i = threadIdx.x; i < 256 * 32; i += SLICE_THREADS) {
+        uint32_t c = i >> 5;
+#pragma unroll
+        for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+        Trep[i] = c;
+    }
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t *T = Trep + lane;                      // this lane's copy of the table
+    uint64_t r; uint32_t c; bool live;
+    if (gridDim.y > 1 || a.n_containers == 1) {
+        c = blockIdx.y;
+        r = a.cont_off[c] + (uint64_t)blockIdx.x * SLICE_THREADS + threadIdx.x;
+        live = r < a.cont_off[c + 1];
+    } else {
+        r = (uint64_t)blockIdx.x * SLICE_THREADS + threadIdx.x;
+        live = r < a.n_reads;
+        c = live ? container_of(a.cont_off, a.n_containers, r) : 0xFFFFFFFFu;
+    }
+    uint32_t bd = 0, sd = 0, rlen = 0, multi = 0;
+    int32_t inv_start = 0, end = 0;
+    if (live) {
+        const uint64_t lo = a.read_off[r];
+        rlen = (uint32_t)(a.read_off[r + 1] - lo);
+        bd = crc32_span(a.bases + lo, rlen, T);
+        const bool no_quals = a.rflags && (a.rflags[r] & CRAMGPU_RF_NO_QUALS);
+        const uint64_t f0 = a.feat_off[r], f1 = a.feat_off[r + 1];
+        if (no_quals) sd = 0;
+        else if (a.scores) sd = crc32_span(a.scores + lo, rlen, T);
+        else {
+            const uint8_t fq = a.force_qs[r];
+            if (!(fq & 2)) sd = 0;                                            // no score array at all
+            else if ((fq & 1) && a.read_qs_off[r] != ~0ull) sd = crc32_span(a.streams + a.read_qs_off[r], rlen, T);
+            else {
+                // -1 everywhere except at the record's Q features (they are in position order)
+                uint32_t crc = ~0u;
+                uint64_t f = f0;
+                int32_t next_q = -1, q_val = 0;
+                auto advance = [&]() {
+                    next_q = -1;
+                    while (f < f1) { const uint64_t g = f++; if (a.f_op[g] == 'Q') { next_q = a.f_pos[g] - 1; q_val = a.f_val[g]; break; } }
+                };
+                advance();
+                for (uint32_t i = 0; i < rlen; i++) {
+                    uint32_t b = 0xFF;
+                    if ((int32_t)i == next_q) { b = (uint32_t)q_val & 0xFF; advance(); }
+                    crc = crc_byte(crc, b, T);
+                }
+                sd = rlen ? ~crc : 0;
+            }
+        }
+        // placement [ContainerFactory.java:156-162]; getAlignmentEnd [CramCompressionRecord.java:160-194]
+        const int32_t first = a.ref_id ? a.ref_id[a.cont_off[c]] : 0, mine = a.ref_id ? a.ref_id[r] : 0;
+        multi = mine != first;
+        const int32_t pos = a.pos[r];
+        if (pos != 0) {
+            if (!(a.flag[r] & 4)) {
+                int32_t span = (int32_t)rlen;
+                for (uint64_t f = f0; f < f1; f++) {
+                    const uint8_t op = a.f_op[f];
+                    if (op == 'i') span -= 1;
+                    else if (op == 'S') span -= a.f_aux[f];
+                    else if (op == 'D') span += a.f_val[f];
+                }
+                end = pos + span - 1;
+            }
+            inv_start = pos > 0 ? INT32_MAX - pos : INT32_MAX;          // a negative start cannot come out of a SAMRecord
+        }
+    }
+    // per-slice sums: one atomic per warp when the warp is inside one slice
+    const uint32_t c0 = __shfl_sync(0xFFFFFFFFu, c, 0);
+    const bool same = __all_sync(0xFFFFFFFFu, !live || c == c0);
+    if (same) {
+        uint32_t len_sum = rlen;
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            bd += __shfl_xor_sync(0xFFFFFFFFu, bd, d); sd += __shfl_xor_sync(0xFFFFFFFFu, sd, d);
+            len_sum += __shfl_xor_sync(0xFFFFFFFFu, len_sum, d);
+            inv_start = max(inv_start, __shfl_xor_sync(0xFFFFFFFFu, inv_start, d));
+            end = max(end, __shfl_xor_sync(0xFFFFFFFFu, end, d));
+            multi |= __shfl_xor_sync(0xFFFFFFFFu, multi, d);
+        }
+        if (lane == 0 && c0 != 0xFFFFFFFFu) {
+            SliceAcc *s = a.acc + c0;
+            atomicAdd(&s->bd, bd); atomicAdd(&s->sd, sd); atomicAdd(&s->bases, (unsigned long long)len_sum);
+            if (inv_start) atomicMax(&s->inv_min_start, inv_start);
+            if (end > 0) atomicMax(&s->max_end, end);
+            if (multi) atomicOr(&s->multi, 1u);
+        }
+    } else if (live) {
+        SliceAcc *s = a.acc + c;
+        atomicAdd(&s->bd, bd); atomicAdd(&s->sd, sd); atomicAdd(&s->bases, (unsigned long long)rlen);
+        if (inv_start) atomicMax(&s->inv_min_start, inv_start);
+        if (end > 0) atomicMax(&s->max_end, end);
+        if (multi) atomicOr(&s->multi, 1u);
+    }
+}
+
+__global__ void k_slice_finish(SliceArgs a)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= a.n_containers) return;
+    const SliceAcc s = a.acc[c];
+    const uint64_t n = a.cont_off[c + 1] - a.cont_off[c];
+    cramgpu_slice_header h;
+    h.n_records = (uint32_t)n; h.bases = s.bases; h.bd = s.bd; h.sd = s.sd;
+    h.sequence_id = n == 0 ? -1 : s.multi ? -2 : (a.ref_id ? a.ref_id[a.cont_off[c]] : 0);
+    if (s.multi || s.inv_min_start == 0) { h.alignment_start = -1; h.alignment_span = 0; }        // [:169-172]
+    else {
+        h.alignment_start = INT32_MAX - s.inv_min_start;
+        h.alignment_span = s.max_end - h.alignment_start + 1;                                       // [:174-175]
+        if (h.alignment_span < 0) h.alignment_span = 0;                                             // CramSerilization.java:184-186
+    }
+    a.out[c] = h;
+}
+
+}  // namespace
+
+static int slice_impl(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *d_out, cudaStream_t st)
+{
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (nc == 0) return CRAMGPU_OK;
+    if (!in->cont_off || !d_out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (in->cont_off[0] != 0 || in->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
+    uint64_t max_reads = 0;
+    for (uint32_t c = 0; c < nc; c++) {
+        if (in->cont_off[c] > in->cont_off[c + 1]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off not monotonic");
+        max_reads = std::max(max_reads, in->cont_off[c + 1] - in->cont_off[c]);
+    }
+    if (n && (!in->bases || !in->read_off || !in->pos || !in->flag || !in->feat_off))
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (n && !in->scores && (!in->force_qs || !in->read_qs_off || !in->streams))
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "scores == NULL needs force_qs, read_qs_off and streams");
+    Carver cv;
+    const size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_acc = cv.take(sizeof(SliceAcc) * (size_t)nc);
+    if (int rc = pool_reserve(ctx, ctx->slice_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->slice_scratch.p;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_slice, &ctx->pin_slice_cap, 8 * (size_t)(nc + 1) + sizeof(cramgpu_slice_header) * (size_t)nc + 64)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_slice));              // the previous call's upload has left the pinned buffer
+    memcpy(ctx->pin_slice, in->cont_off, 8 * (size_t)(nc + 1));
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_cont, ctx->pin_slice, 8 * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_slice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_acc, 0, sizeof(SliceAcc) * (size_t)nc, st));
+    SliceArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_reads = n; a.n_containers = nc; a.cont_off = (const uint64_t *)(S + o_cont);
+    a.bases = in->bases; a.scores = in->scores; a.rflags = in->rflags; a.f_op = in->f_op; a.force_qs = in->force_qs; a.streams = in->streams;
+    a.read_off = in->read_off; a.feat_off = in->feat_off; a.read_qs_off = in->read_qs_off;
+    a.ref_id = in->ref_id; a.pos = in->pos; a.f_pos = in->f_pos; a.f_val = in->f_val; a.f_aux = in->f_aux; a.flag = in->flag;
+    a.acc = (SliceAcc *)(S + o_acc); a.out = d_out;
+    if (n) {
+        const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + SLICE_THREADS - 1) / SLICE_THREADS), nc)
+                                      : dim3((uint32_t)((n + SLICE_THREADS - 1) / SLICE_THREADS), 1);
+        LAUNCH(ctx, st, "k_slice_digest", k_slice_digest<<<grid, SLICE_THREADS, 0, st>>>(a));
+    }
+    LAUNCH(ctx, st, "k_slice_finish", k_slice_finish<<<(nc + 127) / 128, 128, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_slice_headers_dev(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *d_out, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return slice_impl(ctx, in, d_out, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+extern "C" int cramgpu_slice_headers(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *out)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (nc == 0) return CRAMGPU_OK;
+    if (n && (!in->read_off || !in->feat_off)) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    MemMap mm;
+    // sizes of the variable-length arrays: the last entries of the offset tables (host memory, or fetched from the device)
+    auto last_u64 = [&](const uint64_t *p, uint64_t idx, uint64_t *v) -> int {
+        if (mm.kind(p) == MEM_DEVICE) {
+            CUDA_TRY(ctx, cudaMemcpyAsync(v, p + idx, 8, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(ctx, cudaStreamSynchronize(st));
+        } else *v = p[idx];
+        return CRAMGPU_OK;
+    };
+    uint64_t nb = 0, nf = 0;
+    if (n) {
+        if (int rc = last_u64(in->read_off, n, &nb)) return rc;
+        if (int rc = last_u64(in->feat_off, n, &nf)) return rc;
+    }
+    struct Item { const void *src; size_t bytes; size_t off; };
+    std::vector<Item> items;
+    Carver cv;
+    auto add = [&](const void *p, size_t bytes) -> size_t {
+        if (!p || mm.kind(p) == MEM_DEVICE) return (size_t)-1;
+        size_t o = cv.take(bytes + 16); items.push_back({p, bytes, o}); return o;
+    };
+    if (!in->scores && in->streams && mm.kind(in->streams) != MEM_DEVICE)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "scores == NULL: streams must be the device result of a feature call");
+    const size_t i_b = add(in->bases, nb), i_s = add(in->scores, nb), i_ro = add(in->read_off, 8 * (n + 1)), i_rf = add(in->rflags, n);
+    const size_t i_id = add(in->ref_id, 4 * n), i_pos = add(in->pos, 4 * n), i_fl = add(in->flag, 2 * n);
+    const size_t i_op = add(in->f_op, nf), i_fp = add(in->f_pos, 4 * nf), i_fv = add(in->f_val, 4 * nf), i_fa = add(in->f_aux, 4 * nf);
+    const size_t i_fo = add(in->feat_off, 8 * (n + 1)), i_fq = add(in->force_qs, n), i_qo = add(in->read_qs_off, 8 * n);
+    const size_t o_out = cv.take(sizeof(cramgpu_slice_header) * (size_t)nc);
+    if (int rc = pool_reserve(ctx, ctx->slice_in, cv.off + 16)) return rc;
+    uint8_t *D = (uint8_t *)ctx->slice_in.p;
+    for (const Item &it : items)
+        if (it.bytes) CUDA_TRY(ctx, memcpy_pieces(D + it.off, it.src, it.bytes, cudaMemcpyHostToDevice, st));
+    auto at = [&](size_t o, const void *orig) -> const void * { return o == (size_t)-1 ? orig : (const void *)(D + o); };
+    cramgpu_slice_in d = *in;
+    d.bases = (const uint8_t *)at(i_b, in->bases); d.scores = (const uint8_t *)at(i_s, in->scores);
+    d.read_off = (const uint64_t *)at(i_ro, in->read_off); d.rflags = (const uint8_t *)at(i_rf, in->rflags);
+    d.ref_id = (const int32_t *)at(i_id, in->ref_id); d.pos = (const int32_t *)at(i_pos, in->pos); d.flag = (const uint16_t *)at(i_fl, in->flag);
+    d.f_op = (const uint8_t *)at(i_op, in->f_op); d.f_pos = (const int32_t *)at(i_fp, in->f_pos); d.f_val = (const int32_t *)at(i_fv, in->f_val);
+    d.f_aux = (const int32_t *)at(i_fa, in->f_aux); d.feat_off = (const uint64_t *)at(i_fo, in->feat_off);
+    d.force_qs = (const uint8_t *)at(i_fq, in->force_qs); d.read_qs_off = (const uint64_t *)at(i_qo, in->read_qs_off);
+    cramgpu_slice_header *d_out = (cramgpu_slice_header *)(D + o_out);
+    if (int rc = slice_impl(ctx, &d, d_out, st)) return rc;
+    uint8_t *ph = (uint8_t *)ctx->pin_slice + rup(8 * (size_t)(nc + 1), 64);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ph, d_out, sizeof(cramgpu_slice_header) * (size_t)nc, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    memcpy(out, ph, sizeof(cramgpu_slice_header) * (size_t)nc);
+    return CRAMGPU_OK;
+}
+
+extern "C" void cramgpu_slice_sha_tags(uint8_t sha1[20], uint8_t sha512[64])
+{
+    // SHA-1 and SHA-512 of the empty message
+    static const uint8_t S1[20] = {0xda, 0x39, 0xa3, 0xee, 0x5e, 0x6b, 0x4b, 0x0d, 0x32, 0x55, 0xbf, 0xef, 0x95, 0x60, 0x18, 0x90, 0xaf, 0xd8, 0x07, 0x09};
+    static const uint8_t S5[64] = {0xcf, 0x83, 0xe1, 0x35, 0x7e, 0xef, 0xb8, 0xbd, 0xf1, 0x54, 0x28, 0x50, 0xd6, 0x6d, 0x80, 0x07,
+                                   0xd6, 0x20, 0xe4, 0x05, 0x0b, 0x57, 0x15, 0xdc, 0x83, 0xf4, 0xa9, 0x21, 0xd3, 0x6c, 0xe9, 0xce,
+                                   0x47, 0xd0, 0xd1, 0x3c, 0x5d, 0x85, 0xf2, 0xb0, 0xff, 0x83, 0x18, 0xd2, 0x87, 0x7e, 0xec, 0x2f,
+                                   0x63, 0xb9, 0x31, 0xbd, 0x47, 0x41, 0x7a, 0x81, 0xa5, 0x38, 0x32, 0x7a, 0xf9, 0x27, 0xda, 0x3e};
+    if (sha1) memcpy(sha1, S1, 20);
+    if (sha512) memcpy(sha512, S5, 64);
+}

@@ -191,16 +191,20 @@ def _reads_struct(rd, ref, cont_off, ref_off, ref_len, keep):
     return R, n, nc
 
 
-def features_encode(rd, ref, spec=None, cont_off=None, ref_off=None, ref_len=None, ctx=None):
+def features_encode(rd, ref, spec=None, cont_off=None, ref_off=None, ref_len=None, ctx=None, allow_bin_fault=False):
     """Feature extraction + quality preservation + series packing through cramgpu_features_encode (host buffers).
-    rd: SoA dict; ref: reference bytes; spec: None/'lossless' or a lossy model string such as '*8', 'm5', 'N40-D8'."""
+    rd: SoA dict; ref: reference bytes; spec: None/'lossless' or a lossy model string such as '*8', 'm5', 'N40-D8'.
+    A BIN treatment that meets a score of 110..255 fails the call with CRAMGPU_ERR_UNSUPPORTED (the reference throws
+    ArrayIndexOutOfBoundsException, Binning.java:63-71); allow_bin_fault=True returns the results anyway, bit 7 of
+    force_qs marking the records."""
     ctx = ctx or _lib.default_context()
     keep = []
     R, n, nc = _reads_struct(rd, ref, cont_off, ref_off, ref_len, keep)
     pol, npol = _policy_args(spec)
     F = Features()
     rc = ctx.lib.cramgpu_features_encode(ctx.handle, C.byref(R), pol, npol, C.byref(F))
-    ctx.check(rc)
+    if not (allow_bin_fault and rc == _lib.ERR_UNSUPPORTED):
+        ctx.check(rc)
     return EncodedFeatures(F, n, nc)
 
 
@@ -344,3 +348,60 @@ def host_series_pack(flag, pos, read_off, cont_off=None, slice_start=None, multi
     H = HostSeries()
     ctx.check(ctx.lib.cramgpu_host_series_pack(ctx.handle, C.byref(I), C.byref(H)))
     return PackedHostSeries(H, nc)
+
+
+# ---------------------------------------------------------------------------------------------- slice headers and digests
+class SliceIn(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('bases', C.c_void_p), ('scores', C.c_void_p),
+                ('read_off', C.c_void_p), ('rflags', C.c_void_p), ('ref_id', C.c_void_p), ('pos', C.c_void_p), ('flag', C.c_void_p),
+                ('f_op', C.c_void_p), ('f_pos', C.c_void_p), ('f_val', C.c_void_p), ('f_aux', C.c_void_p), ('feat_off', C.c_void_p),
+                ('force_qs', C.c_void_p), ('read_qs_off', C.c_void_p), ('streams', C.c_void_p)]
+
+
+class SliceHeader(C.Structure):
+    _fields_ = [('sequence_id', C.c_int32), ('alignment_start', C.c_int32), ('alignment_span', C.c_int32), ('n_records', C.c_uint32),
+                ('bases', C.c_uint64), ('bd', C.c_uint32), ('sd', C.c_uint32)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_slice_headers': (C.c_int, [C.c_void_p, C.POINTER(SliceIn), C.POINTER(SliceHeader)]),
+    'cramgpu_slice_headers_dev': (C.c_int, [C.c_void_p, C.POINTER(SliceIn), C.c_void_p, C.c_void_p]),
+    'cramgpu_slice_sha_tags': (None, [u8p, u8p]),
+})
+
+
+def slice_sha_tags():
+    """(B1 = S1, B5 = S5): the constant SHA tags htsjdk 2.4.1 writes (include/cramgpu.h)"""
+    lib = _lib.load()
+    a, b = np.zeros(20, np.uint8), np.zeros(64, np.uint8)
+    lib.cramgpu_slice_sha_tags(a.ctypes.data_as(u8p), b.ctypes.data_as(u8p))
+    return a.tobytes(), b.tobytes()
+
+
+def slice_headers(bases, read_off, pos, flag, f_op, f_val, f_aux, feat_off, scores=None, rflags=None, ref_id=None, cont_off=None,
+                  f_pos=None, force_qs=None, read_qs_off=None, streams=None, ctx=None):
+    """ContainerFactory.buildSlice's header fields and BD / SD digests [ContainerFactory.java:138-176] for every slice of a
+    batch, through cramgpu_slice_headers (host buffers; `streams` / force_qs / read_qs_off: device pointers of a feature
+    call when scores is None).  -> list of dicts with sequence_id, alignment_start, alignment_span, n_records, bases, tags"""
+    import struct
+    ctx = ctx or _lib.default_context()
+    n = len(pos)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    keep = dict(bases=_arr(bases, np.uint8), read_off=_arr(read_off, np.uint64), pos=_arr(pos, np.int32), flag=_arr(flag, np.uint16),
+                f_op=_arr(f_op, np.uint8), f_val=_arr(f_val, np.int32), f_aux=_arr(f_aux, np.int32), feat_off=_arr(feat_off, np.uint64),
+                scores=None if scores is None else _arr(scores, np.uint8), rflags=None if rflags is None else _arr(rflags, np.uint8),
+                ref_id=None if ref_id is None else _arr(ref_id, np.int32), f_pos=None if f_pos is None else _arr(f_pos, np.int32))
+    I = SliceIn()
+    I.n_reads = n; I.n_containers = nc; I.cont_off = cont_off.ctypes.data_as(u64p)
+    for k, v in keep.items():
+        setattr(I, k, _vp(v))
+    for k, v in (('force_qs', force_qs), ('read_qs_off', read_qs_off), ('streams', streams)):
+        setattr(I, k, v if (v is None or isinstance(v, int)) else _vp(v))
+    out = (SliceHeader * max(nc, 1))()
+    ctx.check(ctx.lib.cramgpu_slice_headers(ctx.handle, C.byref(I), out))
+    s1, s5 = slice_sha_tags()
+    return [dict(sequence_id=h.sequence_id, alignment_start=h.alignment_start, alignment_span=h.alignment_span, n_records=h.n_records,
+                 bases=h.bases, bd=h.bd, sd=h.sd,
+                 tags={'BD': struct.pack('<I', h.bd), 'SD': struct.pack('<I', h.sd), 'B5': s5, 'S5': s5, 'B1': s1, 'S1': s1})
+            for h in out[:nc]]

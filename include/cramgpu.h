@@ -41,7 +41,8 @@ typedef struct cramgpu_ctx cramgpu_ctx;
 typedef enum cramgpu_status {
     CRAMGPU_OK = 0,
     CRAMGPU_ERR_INPUT_LENGTH = -1,  /* "Incorrect input length."                 [RANS.java:37] */
-    CRAMGPU_ERR_OUT_TOO_SMALL = -2, /* "Output buffer too small to fit N bytes." [RANS.java:44] */
+    CRAMGPU_ERR_OUT_TOO_SMALL = -2, /* decoder: "Output buffer too small to fit N bytes." [RANS.java:44];
+                                       coder: "Insufficient buffer size." [RANS.allocateIfNeeded, RANS.java:83] */
     CRAMGPU_ERR_UNKNOWN_ORDER = -3, /* "Unknown rANS order: X"                   [RANS.java:55] */
     CRAMGPU_ERR_CORRUPT = -4,       /* malformed table/payload; Java: ArrayIndexOutOfBounds / BufferUnderflow */
     CRAMGPU_ERR_CUDA = -5,          /* CUDA runtime failure or no device */
@@ -60,6 +61,10 @@ const char *cramgpu_last_error(const cramgpu_ctx *ctx);
 int cramgpu_sync(cramgpu_ctx *ctx);
 /* Number of kernels this context has launched so far (bench.py's gpu_launches claim). */
 uint64_t cramgpu_launch_count(const cramgpu_ctx *ctx);
+/* Tuning knobs (no counterpart in the reference).  Returns CRAMGPU_ERR_ARG for an unknown name.
+ *   "dec_wide_pool_blocks"  how many largest-size (201 KB) table images of order-1 blocks with more than 64 distinct bytes the
+ *                           decoder's scratch holds per call (default 2048); blocks beyond it take a slower path */
+int cramgpu_set_option(cramgpu_ctx *ctx, const char *name, uint64_t value);
 
 /* Copy `bytes` from device memory (e.g. a result of a *_dev call) to host memory and wait for it.  `stream`:
  * the stream the producing work was enqueued on (NULL = the context's own).  Convenience for shims that own no
@@ -93,7 +98,10 @@ uint32_t cramgpu_rans_bound(uint32_t n);
  *
  *   in[i], in_len[i]   caller-owned raw bytes of block i
  *   order[i]           0 or 1 (anything else: CRAMGPU_ERR_UNKNOWN_ORDER for that block)
- *   out[i], out_cap[i] caller-owned destination; cramgpu_rans_bound(in_len[i]) always suffices
+ *   out[i], out_cap[i] caller-owned destination; cramgpu_rans_bound(in_len[i]) always suffices.  The reference refuses a
+ *                      caller's buffer below that bound outright ("Insufficient buffer size."); here a smaller buffer is
+ *                      accepted when the compressed block fits and fails with that message (CRAMGPU_ERR_OUT_TOO_SMALL,
+ *                      nothing written) when it does not
  *   out_len[i]         bytes written
  *   status             optional per-block status array (may be NULL)
  * Returns the first non-OK per-block status, else CRAMGPU_OK.
@@ -286,7 +294,8 @@ typedef struct cramgpu_features {
     const uint64_t *feat_off;     /* [n_reads+1] */
     const uint8_t *payload;
     uint64_t payload_len;
-    const uint8_t *force_qs;      /* [n_reads] bit0 = CramCompressionRecord.isForcePreserveQualityScores(), bit1 = has a score array */
+    const uint8_t *force_qs;      /* [n_reads] bit0 = CramCompressionRecord.isForcePreserveQualityScores(), bit1 = has a score array,
+                                     bit7 = the reference throws for this record (see CRAMGPU_ERR_UNSUPPORTED below) */
     const uint8_t *matrix;        /* [n_containers][8]: 5 bytes of SubstitutionMatrix.getEncodedMatrix(), 3 pad */
     const uint8_t *streams;       /* all series bytes, SERIES-major: the FN regions of all containers, then FC, ...; every
                                      (container, series) region starts at a multiple of 16 */
@@ -310,6 +319,11 @@ typedef struct cramgpu_features {
  * In the host variants the bulk arrays of `reads` (ref, bases, quals, cigar, pos, flag, mapq, rflags) may also be
  * device pointers -- e.g. a reference that stays resident across calls -- and are then used where they are;
  * read_off and cigar_off are read on the host and must be host memory.
+ *
+ * A BIN treatment ('*8', 'R8', ...) whose lookup meets a score of 110..255: the reference throws ArrayIndexOutOfBoundsException
+ * out of Binning.Illumina_binning_matrix (110 entries, signed byte index; lossy/Binning.java:63-71,
+ * QualityScorePreservation.java:258-266).  The call then returns CRAMGPU_ERR_UNSUPPORTED after filling `out` as usual:
+ * bit 7 of force_qs marks the records concerned (their scores are binned as 40), the other records are unaffected.
  *
  * cramgpu_features_encode_resident: the host variant for callers that code the big series on the GPU right away.
  * Results stay in device memory (`dev_out`, device pointers, valid until the next record call on ctx) and come
@@ -487,6 +501,66 @@ int cramgpu_host_series_pack(cramgpu_ctx *ctx, const cramgpu_host_fields *in, cr
  * host; `out->streams` keeps the device layout.  Per-record arrays that already are device pointers are used in place. */
 int cramgpu_host_series_pack_resident(cramgpu_ctx *ctx, const cramgpu_host_fields *in, uint32_t host_series,
                                       cramgpu_host_series *out, cramgpu_host_series *dev_out);
+
+/* ------------------------------------------------------------------ slice header fields and content digests
+ *
+ * What ContainerFactory.buildSlice derives from a slice's records before it writes a byte
+ * [htsjdk/samtools/cram/build/ContainerFactory.java:138-176]: nofRecords, bases (sum of readLength), sequenceId (the first
+ * record's; Slice.MULTI_REFERENCE = -2 once a record differs), alignmentStart / alignmentSpan (min start over the placed
+ * records, max CramCompressionRecord.getAlignmentEnd() [CramCompressionRecord.java:160-194] -- span = readLength - #'i' -
+ * len('S') + len('D'), reference skips NOT counted, 0 for a record with the unmapped flag; -1 / 0 for a multi-reference
+ * slice or one without a placed record; a negative span becomes 0, CramSerilization.java:184-186) and the content digests
+ * ContentDigests.ALL [cram/digest/ContentDigests.java:26-83]:
+ *   BD / SD   CRC32 (java.util.zip.CRC32) of every record's readBases / qualityScores array, summed as Java ints
+ *             (Crc32Hasher + IntegerSumCombine); the tag value is the sum, 4 bytes little endian
+ *   B5 / S5 / B1 / S1   SHA-512 / SHA-1 "byte-wise sums": MessageDigestHasher.asByteArray() returns messageDigest.digest() of
+ *             a digest that getValue() has just finished (and so reset), not the combined value: in htsjdk 2.4.1 these
+ *             four tags are the digest of the EMPTY message whatever the records hold.  cramgpu_slice_sha_tags hands
+ *             out those constants; there is nothing to compute.
+ * One slice per container, as the writer builds them (CRAMContainerStreamWriter: one slice per container by default).
+ *
+ * Every per-record pointer may be host or device memory in the host variant (device memory is used where it is);
+ * cont_off is always a HOST array.
+ *   scores != NULL   record.qualityScores, laid out like bases (0xFF = -1): the qualities themselves when lossless
+ *   scores == NULL   take them from a cramgpu_features_encode[_dev] result: the score array in `streams` at read_qs_off[r]
+ *                    when force_qs[r] bit 0 is set, else 0xFF everywhere except at the record's 'Q' features
+ *                    (f_pos, f_val); needs force_qs, read_qs_off, streams, f_pos
+ *   rflags bit CRAMGPU_RF_NO_QUALS: qualityScores = SAMRecord.NULL_QUALS, an empty array (CRC32 = 0)
+ */
+typedef struct cramgpu_slice_in {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    const uint8_t *bases;         /* CramCompressionRecord.readBases, concatenated */
+    const uint8_t *scores;        /* see above; may be NULL */
+    const uint64_t *read_off;     /* [n_reads+1] */
+    const uint8_t *rflags;        /* CRAMGPU_RF_* per record; NULL = all 0 */
+    const int32_t *ref_id;        /* CramCompressionRecord.sequenceId (-1 = unmapped); NULL = all 0 */
+    const int32_t *pos;           /* alignmentStart, 0 = none */
+    const uint16_t *flag;         /* SAM flags */
+    const uint8_t *f_op;          /* read features, as cramgpu_features */
+    const int32_t *f_pos, *f_val, *f_aux;
+    const uint64_t *feat_off;     /* [n_reads+1] */
+    const uint8_t *force_qs;      /* scores == NULL only */
+    const uint64_t *read_qs_off;  /* scores == NULL only */
+    const uint8_t *streams;       /* scores == NULL only */
+} cramgpu_slice_in;
+
+typedef struct cramgpu_slice_header {
+    int32_t sequence_id;          /* Slice.sequenceId */
+    int32_t alignment_start;      /* Slice.alignmentStart */
+    int32_t alignment_span;       /* Slice.alignmentSpan */
+    uint32_t n_records;           /* Slice.nofRecords */
+    uint64_t bases;               /* Slice.bases */
+    uint32_t bd, sd;              /* tags BD and SD */
+} cramgpu_slice_header;
+
+/* out: HOST array of n_containers headers.  _dev: every pointer but cont_off is device memory, d_out is a DEVICE array,
+ * the call is asynchronous on `stream` (NULL = the context's stream). */
+int cramgpu_slice_headers(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *out);
+int cramgpu_slice_headers_dev(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *d_out, void *stream);
+/* the four constant tags: sha1 = B1 = S1 (20 bytes), sha512 = B5 = S5 (64 bytes) */
+void cramgpu_slice_sha_tags(uint8_t sha1[20], uint8_t sha512[64]);
 
 /* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
  *

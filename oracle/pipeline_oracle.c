@@ -26,6 +26,9 @@ typedef struct { int32_t read_cat, read_param, n_base_cats, base_cat[8], treatme
 int rec_oracle_extract(int64_t, const uint8_t *, const int64_t *, const uint32_t *, const int64_t *, const int32_t *,
                        const uint16_t *, const uint8_t *, int64_t, rec_features_t *);
 void rec_oracle_free(rec_features_t *);
+typedef struct { int32_t sequence_id, alignment_start, alignment_span; uint32_t n_records; uint64_t bases; uint32_t bd, sd; } slice_header_t;
+void rec_oracle_slice_header(int64_t, const uint8_t *, const uint8_t *, const int64_t *, const uint8_t *, const int32_t *, const int32_t *,
+                             const uint16_t *, const uint8_t *, const int32_t *, const int32_t *, const int64_t *, slice_header_t *);
 int rec_oracle_quality(const uint8_t *, const uint8_t *, int64_t, int, const uint32_t *, int64_t, int32_t, uint16_t, uint8_t,
                        const uint8_t *, int64_t, const qs_policy_t *, int, uint8_t *);
 void rec_oracle_write_streams(int64_t, const uint8_t *, const int64_t *, const uint16_t *, const uint8_t *, const int32_t *,
@@ -88,6 +91,10 @@ static void run_container(container_job_t *j)
     for (int64_t r = 0; r < n; r++) if (j->pos[r] > 0 && j->pos[r] < smin) smin = j->pos[r];       /* Slice.alignmentStart [ContainerFactory.java:160-161] */
     rec_oracle_write_host_streams(n, j->flag, cf, NULL, j->read_off, j->pos, j->read_group, j->names, j->name_off, NULL, NULL, NULL,
                                   NULL, NULL, 1, 0, smin, 0, hs, hlen);
+    /* slice header fields and the BD / SD content digests [ContainerFactory.java:138-176] */
+    slice_header_t sh;
+    rec_oracle_slice_header(n, j->bases, sc0, j->read_off, NULL, NULL, j->pos, j->flag, ft.f_op, ft.f_val, ft.f_aux, ft.feat_off, &sh);
+    if (sh.n_records != (uint32_t)n || (int64_t)sh.bases != total) j->rc |= 8;
     /* block codec: QS, BA, BF, CF, RL, RG, NS, TS order 1, AP order 0 */
     static const int coded[7] = {H_BF, H_CF, H_RL, H_RG, H_NS, H_TS, H_AP};
     int nblk = 2 + 7;
@@ -95,7 +102,7 @@ static void run_container(container_job_t *j)
     in[0] = streams[S_QS]; ilen[0] = (uint32_t)lens[S_QS]; ord[0] = 1;
     in[1] = streams[S_BA]; ilen[1] = (uint32_t)lens[S_BA]; ord[1] = 1;
     for (int e = 0; e < 7; e++) { in[2 + e] = hs[coded[e]]; ilen[2 + e] = (uint32_t)hlen[coded[e]]; ord[2 + e] = coded[e] == H_AP ? 0 : 1; }
-    uint64_t sum = 0;
+    uint64_t sum = (uint64_t)sh.bd + sh.sd;
     uint8_t *qs_back = NULL;
     for (int b = 0; b < nblk; b++) {
         uint32_t capb = rans_oracle_bound(ilen[b]), clen = 0, rlen = 0;

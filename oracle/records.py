@@ -56,8 +56,51 @@ def lib():
         L.rec_oracle_write_host_streams.restype = None
         L.rec_oracle_write_host_streams.argtypes = [_c.c_int64, u16p, u8p, i32p, i64p, i32p, i32p, u8p, i64p, i32p, i32p, i32p, i32p,
                                                     i32p, _c.c_int, _c.c_int, _c.c_int32, _c.c_int, _c.POINTER(u8p), i64p]
+        L.rec_oracle_crc32.restype = _c.c_uint32
+        L.rec_oracle_crc32.argtypes = [u8p, _c.c_int64]
+        L.rec_oracle_slice_header.restype = None
+        L.rec_oracle_slice_header.argtypes = [_c.c_int64, u8p, u8p, i64p, u8p, i32p, i32p, u16p, u8p, i32p, i32p, i64p,
+                                              _c.POINTER(SliceHeader)]
         _done = True
     return L
+
+
+class SliceHeader(_c.Structure):
+    """slice_header_t of records_oracle.c"""
+    _fields_ = [('sequence_id', _c.c_int32), ('alignment_start', _c.c_int32), ('alignment_span', _c.c_int32),
+                ('n_records', _c.c_uint32), ('bases', _c.c_uint64), ('bd', _c.c_uint32), ('sd', _c.c_uint32)]
+
+
+# what MessageDigestHasher.asByteArray() yields in htsjdk 2.4.1 whatever the records hold: the digest of the empty message
+SHA1_EMPTY = bytes.fromhex('da39a3ee5e6b4b0d3255bfef95601890afd80709')
+SHA512_EMPTY = bytes.fromhex('cf83e1357eefb8bdf1542850d66d8007d620e4050b5715dc83f4a921d36ce9ce'
+                             '47d0d13c5d85f2b0ff8318d2877eec2f63b931bd47417a81a538327af927da3e')
+
+
+def slice_header(rd, ex, scores):
+    """ContainerFactory.buildSlice's header fields and BD / SD digests for one slice.
+    rd needs ref_id besides the usual arrays; ex = extract(rd, ref); scores = quality(rd, ref, spec)[1].
+    -> dict(sequence_id, alignment_start, alignment_span, n_records, bases, tags={BD, SD, B5, S5, B1, S1})"""
+    import struct
+    n = len(rd['pos'])
+    one = np.zeros(1, np.uint8)
+    bases = np.ascontiguousarray(rd['bases'], np.uint8) if len(rd['bases']) else one
+    sc = np.ascontiguousarray(scores, np.uint8) if len(scores) else one
+    rfl = np.ascontiguousarray(rd.get('rflags', np.zeros(n, np.uint8)), np.uint8)
+    nf = ex.n_feat
+    f_op = ex.f_op if nf else one
+    f_val = ex.f_val if nf else np.zeros(1, np.int32)
+    f_aux = ex.f_aux if nf else np.zeros(1, np.int32)
+    H = SliceHeader()
+    lib().rec_oracle_slice_header(n, _p(bases, u8p), _p(sc, u8p), _p(np.ascontiguousarray(rd['read_off'], np.int64), i64p), _p(rfl, u8p),
+                                  _p(np.ascontiguousarray(rd['ref_id'], np.int32), i32p), _p(np.ascontiguousarray(rd['pos'], np.int32), i32p),
+                                  _p(np.ascontiguousarray(rd['flag'], np.uint16), u16p), _p(np.ascontiguousarray(f_op), u8p),
+                                  _p(np.ascontiguousarray(f_val), i32p), _p(np.ascontiguousarray(f_aux), i32p),
+                                  _p(np.ascontiguousarray(ex.feat_off, np.int64), i64p), _c.byref(H))
+    return dict(sequence_id=H.sequence_id, alignment_start=H.alignment_start, alignment_span=H.alignment_span, n_records=H.n_records,
+                bases=H.bases, bd=H.bd, sd=H.sd,
+                tags={'BD': struct.pack('<I', H.bd), 'SD': struct.pack('<I', H.sd), 'B5': SHA512_EMPTY, 'S5': SHA512_EMPTY,
+                      'B1': SHA1_EMPTY, 'S1': SHA1_EMPTY})
 
 
 def _p(a, t):
@@ -101,10 +144,12 @@ class Extracted(object):
     def __init__(self, rf, n_reads):
         n = rf.n_feat
         self.n_feat = n
-        self.f_op = np.ctypeslib.as_array(rf.f_op, (max(n, 1),))[:n].copy()
-        self.f_pos = np.ctypeslib.as_array(rf.f_pos, (max(n, 1),))[:n].copy()
-        self.f_val = np.ctypeslib.as_array(rf.f_val, (max(n, 1),))[:n].copy()
-        self.f_aux = np.ctypeslib.as_array(rf.f_aux, (max(n, 1),))[:n].copy()
+        def arr(p, dt):
+            return np.ctypeslib.as_array(p, (n,)).copy() if n and p else np.zeros(0, dt)          # no feature at all: NULL
+        self.f_op = arr(rf.f_op, np.uint8)
+        self.f_pos = arr(rf.f_pos, np.int32)
+        self.f_val = arr(rf.f_val, np.int32)
+        self.f_aux = arr(rf.f_aux, np.int32)
         self.feat_off = np.ctypeslib.as_array(rf.feat_off, (n_reads + 1,)).copy()
         pl = rf.payload_len
         self.payload = np.ctypeslib.as_array(rf.payload, (max(pl, 1),))[:pl].copy() if pl else np.zeros(0, np.uint8)

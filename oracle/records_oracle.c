@@ -307,7 +307,10 @@ int rec_oracle_parse_policies(const char *spec, qs_policy_t *out, int cap)
 /*
  * addQualityScores for one read [QualityScorePreservation.java:276-301, 332-489].
  * scores[rlen] receives the array the reference leaves in record.qualityScores (0xFF = -1 = absent).
- * Returns: bit0 = forcePreserveQualityScores, bit1 = "record has a score array" (quals were present).
+ * Returns: bit0 = forcePreserveQualityScores, bit1 = "record has a score array" (quals were present),
+ * bit7 = the reference throws ArrayIndexOutOfBoundsException for this record: a BIN treatment indexed
+ * Binning.Illumina_binning_matrix (110 entries, signed byte index) with a score of 110..255 [:258-266; Binning.java:63-71];
+ * the restatement goes on with entry 109 so that the other records of the batch can still be compared.
  * lossless (n_pol < 0): CramSerilization.java:160-161.
  */
 int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int has_quals, const uint32_t *cigar, int64_t ncig,
@@ -319,7 +322,7 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
         return has_quals ? 3 : 0;
     }
     if (!has_quals) return 0;
-    int force = 0;
+    int force = 0, fault = 0;
     memset(scores, 0xFF, (size_t)rlen);
     uint8_t *mask = malloc((size_t)rlen + 1);
     for (int k = 0; k < n_pol; k++) {
@@ -337,7 +340,7 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
         if (p->n_base_cats == 0) {
             switch (p->treatment) {
             case T_BIN:
-                for (int64_t i = 0; i < rlen; i++) scores[i] = (uint8_t)ILLUMINA_BIN[qs[i] < 110 ? qs[i] : 109];
+                for (int64_t i = 0; i < rlen; i++) { if (qs[i] >= 110) fault = 0x80; scores[i] = (uint8_t)ILLUMINA_BIN[qs[i] < 110 ? qs[i] : 109]; }
                 force = 1; break;
             case T_PRESERVE: memcpy(scores, qs, (size_t)rlen); force = 1; break;
             case T_DROP: force = 0; break;
@@ -385,7 +388,7 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
         for (int64_t i = 0; i < rlen; i++) {
             if (!mask[i]) continue;
             switch (p->treatment) {
-            case T_BIN: scores[i] = (uint8_t)ILLUMINA_BIN[qs[i] < 110 ? qs[i] : 109]; break;
+            case T_BIN: if (qs[i] >= 110) fault = 0x80; scores[i] = (uint8_t)ILLUMINA_BIN[qs[i] < 110 ? qs[i] : 109]; break;
             case T_DROP: scores[i] = 0xFF; break;
             default: scores[i] = qs[i]; break;
             }
@@ -394,7 +397,7 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
         if (masked > rlen / 2) force = 1;                             /* safety latch [:487-488] */
     }
     free(mask);
-    return force | 2;
+    return force | 2 | fault;
 }
 
 /* ------------------------------------------------------------------ normaliser (N1, N2) */
@@ -590,4 +593,83 @@ void rec_oracle_write_host_streams(int64_t n, const uint16_t *flag, const uint8_
     }
 #undef HPUT
 #undef HPUT_ITF8
+}
+
+/* ------------------------------------------------------------------ slice header fields and content digests
+ *
+ * ContainerFactory.buildSlice [ContainerFactory.java:138-176], what it derives from the records before any byte is written:
+ *   nofRecords, bases = sum of readLength, sequenceId (first record's, -2 = MULTI_REFERENCE as soon as one differs),
+ *   alignmentStart = min over the records with alignmentStart != 0, alignmentSpan = max(getAlignmentEnd()) - start + 1
+ *   (-1 / 0 for a multi-reference slice or when no record is placed), and the slice tags of ContentDigests.ALL
+ *   [cram/digest/ContentDigests.java:26-83]: for BD (bases) and SD (scores) the CRC32 of every record's array, summed as
+ *   Java ints (Crc32Hasher + IntegerSumCombine), 4 bytes little endian.
+ * The other four tags (B5, S5: SHA-512; B1, S1: SHA-1; ByteSumCombine) come out of MessageDigestHasher.asByteArray(), which
+ * returns messageDigest.digest() -- of a digest that getValue() has just finished and thereby reset -- instead of the combined
+ * value: in htsjdk 2.4.1 they are the hash of the EMPTY message whatever the records hold (tests/golden/streams_jvm.json
+ * shows it: B1 = S1 = da39a3ee..., B5 = S5 = cf83e135...).  Constants, therefore, and no work.
+ * CramCompressionRecord.getAlignmentEnd / calculateAlignmentBoundaries [CramCompressionRecord.java:160-194]: 0 for a record
+ * with the unmapped flag; else start + span - 1 with span = readLength - (#'i') - len('I') - len('S') + len('D').  Reference
+ * skips ('N') are NOT counted: that is the reference's arithmetic.
+ * CramSerilization.convert then clamps a negative span to 0 [CramSerilization.java:184-186].
+ * Pinned by tests/golden/streams_jvm.json ('slice', 'slice_tags').
+ */
+typedef struct {
+    int32_t sequence_id, alignment_start, alignment_span;
+    uint32_t n_records;
+    uint64_t bases;
+    uint32_t bd, sd;
+} slice_header_t;
+
+static uint32_t crc32_table[256];
+static void crc32_init(void)
+{
+    if (crc32_table[1]) return;
+    for (uint32_t i = 0; i < 256; i++) {
+        uint32_t c = i;
+        for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+        crc32_table[i] = c;
+    }
+}
+uint32_t rec_oracle_crc32(const uint8_t *p, int64_t n)      /* java.util.zip.CRC32 */
+{
+    crc32_init();
+    uint32_t c = 0xFFFFFFFFu;
+    for (int64_t i = 0; i < n; i++) c = crc32_table[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+    return ~c;
+}
+
+/* scores: record.qualityScores as addQualityScores / createCramRecord leave it, laid out like bases (0xFF = -1);
+ * rflags bit0 = NULL_QUALS (empty array).  Features as rec_oracle_extract gives them (Q features, if merged in, are ignored). */
+void rec_oracle_slice_header(int64_t n, const uint8_t *bases, const uint8_t *scores, const int64_t *read_off, const uint8_t *rflags,
+                             const int32_t *ref_id, const int32_t *pos, const uint16_t *flag, const uint8_t *f_op,
+                             const int32_t *f_val, const int32_t *f_aux, const int64_t *feat_off, slice_header_t *out)
+{
+    memset(out, 0, sizeof *out);
+    out->n_records = (uint32_t)n;
+    out->sequence_id = n ? (ref_id ? ref_id[0] : 0) : -1;            /* ref_id == NULL: every record on reference 0 */
+    int32_t min_start = INT32_MAX, max_end = 0;
+    for (int64_t r = 0; r < n; r++) {
+        const int64_t lo = read_off[r], rlen = read_off[r + 1] - lo;
+        out->bases += (uint64_t)rlen;
+        out->bd += rec_oracle_crc32(bases + lo, rlen);
+        out->sd += rec_oracle_crc32(scores + lo, (rflags && (rflags[r] & RF_NO_QUALS)) ? 0 : rlen);
+        if (out->sequence_id == -2) continue;
+        if (out->sequence_id != (ref_id ? ref_id[r] : 0)) { out->sequence_id = -2; continue; }
+        if (pos[r] == 0) continue;
+        int32_t end = 0;
+        if (!(flag[r] & SAM_UNMAPPED)) {
+            int32_t span = (int32_t)rlen;
+            for (int64_t f = feat_off[r]; f < feat_off[r + 1]; f++) {
+                if (f_op[f] == 'i') span -= 1;
+                else if (f_op[f] == 'S') span -= f_aux[f];
+                else if (f_op[f] == 'D') span += f_val[f];
+            }
+            end = pos[r] + span - 1;
+        }
+        if (pos[r] < min_start) min_start = pos[r];
+        if (end > max_end) max_end = end;
+    }
+    if (out->sequence_id == -2 || min_start == INT32_MAX) { out->alignment_start = -1; out->alignment_span = 0; }
+    else { out->alignment_start = min_start; out->alignment_span = max_end - min_start + 1; }
+    if (out->alignment_span < 0) out->alignment_span = 0;
 }

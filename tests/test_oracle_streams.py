@@ -110,3 +110,24 @@ def test_reader_matches_jar(G):
             if b['flags'] & 4 and b['bases'] is not None:
                 assert st['BA'][ba_off[i]:ba_off[i] + rl[i]] == base64.b64decode(b['bases']), (c['tag'], i)
         assert set(c['bytes_left'].values()) == {0}            # and the jar's reader used up every byte of every series
+
+
+def test_slice_header_and_digests_match_jar(G):
+    """what ContainerFactory.buildSlice derives from the records -- nofRecords, bases, sequenceId, alignment
+    start / span, and the six content-digest tags -- against the slices the jar built"""
+    import hashlib
+    import zlib
+    g, ref, conts = G
+    assert orec.SHA1_EMPTY == hashlib.sha1(b'').digest() and orec.SHA512_EMPTY == hashlib.sha512(b'').digest()
+    assert orec.lib().rec_oracle_crc32(orec._p(np.frombuffer(b'123456789', np.uint8).copy(), orec.u8p), 9) == zlib.crc32(b'123456789') == 0xCBF43926
+    seen = set()
+    for c, rd, series in conts:
+        ex = orec.extract(rd, ref)
+        force, scores = orec.quality(rd, ref, None)
+        h = orec.slice_header(rd, ex, scores)
+        for k in ('sequence_id', 'alignment_start', 'alignment_span', 'n_records', 'bases'):
+            assert h[k] == c['slice'][k], (c['tag'], k, h[k], c['slice'][k])
+        want = {t: base64.b64decode(v) for t, v in c['slice_tags']}
+        assert h['tags'] == want, c['tag']
+        seen.add(h['sequence_id'])
+    assert -2 in seen and 0 in seen          # a multi-reference slice and a single-reference one

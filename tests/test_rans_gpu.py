@@ -43,6 +43,16 @@ def test_error_behaviour_matches_reference(EC, rans_golden, gpu_ctx):
         assert msg in str(e.value), (name, str(e.value))
     with pytest.raises(_lib.CramGpuError):
         EC.rans(b'abcdef', 2, gpu_ctx)
+    # a caller's output buffer that cannot hold the block: the wording of RANS.allocateIfNeeded [RANS.java:83]
+    import ctypes
+    data = np.frombuffer(bytes(range(256)) * 8, np.uint8)
+    out = np.zeros(64, np.uint8)
+    pin = (_lib.u8p * 1)(data.ctypes.data_as(_lib.u8p)); pout = (_lib.u8p * 1)(out.ctypes.data_as(_lib.u8p))
+    ln = (ctypes.c_uint32 * 1)(data.size); cap = (ctypes.c_uint32 * 1)(out.size); got = (ctypes.c_uint32 * 1)(7)
+    order = (ctypes.c_uint8 * 1)(0); st = (ctypes.c_int32 * 1)(0)
+    rc = gpu_ctx.lib.cramgpu_rans_encode_batch(gpu_ctx.handle, 1, pin, ln, order, pout, cap, got, st)
+    assert rc == _lib.ERR_OUT_TOO_SMALL and st[0] == rc and got[0] == 0 and not out.any()
+    assert 'Insufficient buffer size.' in gpu_ctx.last_error()
 
 
 def _oracle():
@@ -228,3 +238,50 @@ def test_decode_dev_rejects_misaligned_blocks(EC, gpu_ctx):
     # and the context stays usable
     back = EC.unrans_batch(comp, gpu_ctx)
     assert back[0] == blocks[0].tobytes()
+
+
+def test_wide_alphabets_pool_and_overflow(EC, gpu_ctx):
+    """order-1 blocks with more than 64 distinct bytes: decoded from pooled table images (k_dec1w), and -- when a call has more
+    of them than the pool holds -- the rest through the slab path (k_dec1_big).  Same bytes either way; corrupt wide blocks
+    are reported."""
+    import cramtools_b200
+    orans = _oracle()
+    rng = np.random.default_rng(11)
+    blocks = []
+    for i in range(40):
+        kind = i % 4
+        n = int(rng.integers(2000, 90000))
+        if kind == 0: b = rng.integers(0, 65 + i, size=n, dtype=np.uint8)                       # 65 .. 104 distinct
+        elif kind == 1: b = np.minimum(rng.geometric(0.03, size=n), 255).astype(np.uint8)       # skewed, ~150 distinct
+        elif kind == 2: b = rng.integers(0, 256, size=n, dtype=np.uint8)                        # all 256
+        else: b = synth.qs_stream(n, i)                                                          # a narrow one in between
+        blocks.append(b)
+    comp = [orans.compress(b, 1) for b in blocks]
+    ctx = cramtools_b200.Context(0)
+    try:
+        for pool in (2048, 3, 0):
+            ctx.set_option('dec_wide_pool_blocks', pool)
+            back = EC.unrans_batch(comp, ctx)
+            for b, r in zip(blocks, back):
+                assert r == b.tobytes(), (pool, len(b))
+        ctx.set_option('dec_wide_pool_blocks', 2048)
+        # a wide block cut short inside its payload, and one whose table is cut: reported, neighbours unharmed
+        bad = list(comp)
+        c2 = bytearray(comp[2]); del c2[-len(c2) // 3:]; c2[1:5] = (len(c2) - 9).to_bytes(4, 'little'); bad[2] = bytes(c2)
+        ins = [np.frombuffer(x, np.uint8) for x in bad]
+        import ctypes
+        n = len(ins)
+        in_len = np.array([a.size for a in ins], np.uint32); raw = np.array([len(b) for b in blocks], np.uint32)
+        outs = [np.zeros(int(r) + 16, np.uint8) for r in raw]
+        pin = (_lib.u8p * n)(*[a.ctypes.data_as(_lib.u8p) for a in ins]); pout = (_lib.u8p * n)(*[a.ctypes.data_as(_lib.u8p) for a in outs])
+        out_len = np.zeros(n, np.uint32); st = np.zeros(n, np.int32)
+        rc = ctx.lib.cramgpu_rans_decode_batch(ctx.handle, n, pin, in_len.ctypes.data_as(_lib.u32p), pout, raw.ctypes.data_as(_lib.u32p),
+                                               out_len.ctypes.data_as(_lib.u32p), st.ctypes.data_as(_lib.i32p))
+        assert rc == _lib.ERR_CORRUPT and st[2] == _lib.ERR_CORRUPT and (np.delete(st, 2) == 0).all()
+        for i in range(n):
+            if i != 2:
+                assert outs[i][:raw[i]].tobytes() == blocks[i].tobytes()
+        with pytest.raises(_lib.CramGpuError):
+            ctx.set_option('no_such_option', 1)
+    finally:
+        ctx.close()

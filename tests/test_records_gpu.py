@@ -510,3 +510,40 @@ def test_normalize_rejects_out_of_range_features(R, gpu_ctx):
         else:
             assert st[r] == 0, r
             assert (b[ro[r]:ro[r + 1]] == base_b[ro[r]:ro[r + 1]]).all() and (q[ro[r]:ro[r + 1]] == base_q[ro[r]:ro[r + 1]]).all(), r
+
+
+@pytest.mark.parametrize('spec', ['*8', 'N40-D8', 'R8-N40', 'm20_8-N40', '*8-*40', 'm5'])
+def test_binning_table_overrun_is_reported_per_read(R, gpu_ctx, spec):
+    """Binning.Illumina_binning_matrix has 110 entries and a signed byte index: a BIN treatment that meets a score of 110..255
+    makes the reference throw ArrayIndexOutOfBoundsException (lossy/Binning.java:63-71, QualityScorePreservation.java:258-266).
+    The call fails with CRAMGPU_ERR_UNSUPPORTED, bit 7 of force_qs marks exactly the records the oracle marks, and the
+    other records' series are what they are without the fault."""
+    from oracle import records as orec
+    ref, rd, cont_off = _sim(3000, 3, 23, unmapped_tail=60)
+    rng = np.random.default_rng(4)
+    quals = rd['quals'].copy()
+    for r, q in zip(rng.choice(len(rd['pos']), 40, replace=False), rng.choice([110, 111, 127, 128, 200, 255], 40)):
+        lo, hi = int(rd['read_off'][r]), int(rd['read_off'][r + 1])
+        quals[lo + rng.integers(0, hi - lo)] = q
+    rd = dict(rd, quals=quals)
+    want_force = []
+    for c in range(3):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        sub = dict(bases=rd['bases'][rd['read_off'][a]:rd['read_off'][b]], quals=rd['quals'][rd['read_off'][a]:rd['read_off'][b]],
+                   read_off=rd['read_off'][a:b + 1] - rd['read_off'][a], cigar=rd['cigar'][rd['cigar_off'][a]:rd['cigar_off'][b]],
+                   cigar_off=rd['cigar_off'][a:b + 1] - rd['cigar_off'][a], pos=rd['pos'][a:b], flag=rd['flag'][a:b], mapq=rd['mapq'][a:b])
+        want_force.append(orec.quality(sub, ref, spec)[0])
+    want_force = np.concatenate(want_force)
+    faults = int((want_force & 0x80 != 0).sum())
+    if faults == 0:                                   # a model without BIN ('m5'), or none of the scores was binned
+        enc = R.features_encode(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+        assert spec == 'm5'
+    else:
+        with pytest.raises(_lib.CramGpuError) as e:
+            R.features_encode(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+        assert e.value.status == _lib.ERR_UNSUPPORTED and 'ArrayIndexOutOfBounds' in str(e.value)
+        enc = R.features_encode(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx, allow_bin_fault=True)
+    assert (enc.force_qs == want_force).all(), (spec, faults, int((enc.force_qs & 0x80 != 0).sum()))
+    # the context is usable afterwards and a clean call succeeds
+    ok = R.features_encode(dict(rd, quals=np.minimum(rd['quals'], 60)), ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+    assert not (ok.force_qs & 0x80).any()

@@ -154,3 +154,85 @@ def test_host_series_multi_container_and_options(R, G, gpu_ctx):
         got = R.host_series_pack(cf=[s['cf'] for s in c['scalars']], ctx=gpu_ctx, **kw)
         for nm in R.HOST_SERIES:
             assert got.series(0, nm) == want[nm], (apd, named, nm)
+
+
+def _cat(conts):
+    cat = {}
+    for k in ('bases', 'quals', 'cigar', 'pos', 'flag', 'mapq', 'rflags', 'ref_id'):
+        cat[k] = np.concatenate([rd[k] for _, rd, _ in conts])
+    ro, co, cont_off = [np.zeros(1, np.int64)], [np.zeros(1, np.int64)], [0]
+    for _, rd, _ in conts:
+        ro.append(rd['read_off'][1:] + ro[-1][-1]); co.append(rd['cigar_off'][1:] + co[-1][-1]); cont_off.append(cont_off[-1] + len(rd['pos']))
+    cat['read_off'] = np.concatenate(ro); cat['cigar_off'] = np.concatenate(co)
+    return cat, np.array(cont_off, np.uint64)
+
+
+def test_slice_headers_and_digests_match_jar(R, G, gpu_ctx):
+    """nofRecords, bases, sequenceId, alignment start / span and the six content-digest tags of the three slices the
+    jar's ContainerFactory.buildSlice built -- as one batch, and one by one"""
+    g, ref, conts = G
+    cat, cont_off = _cat(conts)
+    enc = R.features_encode(cat, ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    got = R.slice_headers(cat['bases'], cat['read_off'], cat['pos'], cat['flag'], enc.f_op, enc.f_val, enc.f_aux, enc.feat_off,
+                          scores=cat['quals'], rflags=cat['rflags'], ref_id=cat['ref_id'], cont_off=cont_off, ctx=gpu_ctx)
+    for h, (c, rd, _) in zip(got, conts):
+        for k in ('sequence_id', 'alignment_start', 'alignment_span', 'n_records', 'bases'):
+            assert h[k] == c['slice'][k], (c['tag'], k, h[k], c['slice'][k])
+        assert h['tags'] == {t: base64.b64decode(v) for t, v in c['slice_tags']}, c['tag']
+    for c, rd, _ in conts:
+        e1 = R.features_encode(rd, ref, None, ctx=gpu_ctx)
+        h = R.slice_headers(rd['bases'], rd['read_off'], rd['pos'], rd['flag'], e1.f_op, e1.f_val, e1.f_aux, e1.feat_off,
+                            scores=rd['quals'], rflags=rd['rflags'], ref_id=rd['ref_id'], ctx=gpu_ctx)[0]
+        assert h['tags'] == {t: base64.b64decode(v) for t, v in c['slice_tags']} and h['alignment_span'] == c['slice']['alignment_span']
+
+
+@pytest.mark.parametrize('spec', [None, '*8', 'm5', 'N40-D8', 'R8-N40'])
+def test_slice_headers_parity_with_oracle(R, gpu_ctx, spec):
+    """bigger slices, ragged read lengths (every byte alignment), quality models: explicit score arrays, and score arrays taken
+    from the device result of the feature call (forced arrays in QS, sparse Q features otherwise)"""
+    import ctypes
+    from oracle import records as orec
+    from cramtools_b200 import synth
+    from tests.test_records_gpu import _concat_reads
+    nc = 4
+    ref = synth.reference(40000, 3)
+    parts = [synth.reads(ref, 2500, 9, read_len=150, sub_rate=0.01, indel_frac=0.15, clip_frac=0.08), synth.reads(ref, 1500, 10, read_len=101, sub_rate=0.01),
+             synth.reads(ref, 700, 11, read_len=37, indel_frac=0.2, clip_frac=0.1), synth.reads(ref, 1300, 12, read_len=75, indel_frac=0.1)]
+    rd = _concat_reads(parts)
+    n = len(rd['pos'])
+    cont_off = np.linspace(0, n, nc + 1).astype(np.uint64)
+    ref_id = np.zeros(n, np.int32)
+    ref_id[int(cont_off[1]):int(cont_off[2])] = 2                      # slice 1: another single reference
+    ref_id[int(cont_off[2]) + 7] = 1                                    # slice 2: multi-reference
+    a3, b3 = int(cont_off[3]), int(cont_off[4])
+    pos = rd['pos'].copy(); flag = rd['flag'].copy()
+    pos[a3:b3] = 0; flag[a3:b3] |= 4; ref_id[a3:b3] = -1               # slice 3: nothing placed
+    flag[5] |= 4                                                         # unmapped flag but placed: end counts as 0
+    rd = dict(rd, pos=pos, flag=flag, ref_id=ref_id)
+    rfl = np.zeros(n, np.uint8); rfl[::97] = 1                           # some records without quality scores
+    rd['rflags'] = rfl
+    enc, D = R.features_encode_resident(rd, ref, spec, cont_off=cont_off, ctx=gpu_ctx)
+    want, all_scores = [], []
+    for c in range(nc):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        sub = dict(bases=rd['bases'][rd['read_off'][a]:rd['read_off'][b]], quals=rd['quals'][rd['read_off'][a]:rd['read_off'][b]],
+                   read_off=rd['read_off'][a:b + 1] - rd['read_off'][a], cigar=rd['cigar'][rd['cigar_off'][a]:rd['cigar_off'][b]],
+                   cigar_off=rd['cigar_off'][a:b + 1] - rd['cigar_off'][a], pos=rd['pos'][a:b], flag=rd['flag'][a:b], mapq=rd['mapq'][a:b],
+                   rflags=rfl[a:b], ref_id=ref_id[a:b])
+        ex = orec.extract(sub, ref)
+        force, scores = orec.quality(sub, ref, spec)
+        all_scores.append(scores)
+        want.append(orec.slice_header(sub, ex, scores))
+    scores = np.concatenate(all_scores)
+    keys = ('sequence_id', 'alignment_start', 'alignment_span', 'n_records', 'bases', 'bd', 'sd')
+    got = R.slice_headers(rd['bases'], rd['read_off'], pos, flag, enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, scores=scores, rflags=rfl,
+                          ref_id=ref_id, cont_off=cont_off, ctx=gpu_ctx)
+    for c in range(nc):
+        assert {k: got[c][k] for k in keys} == {k: want[c][k] for k in keys}, (spec, c)
+    assert [h['sequence_id'] for h in got] == [0, 2, -2, -1]
+    # the same from the device-resident result of the feature call, everything else staged from the host
+    got2 = R.slice_headers(rd['bases'], rd['read_off'], pos, flag, enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, scores=None, rflags=rfl,
+                           ref_id=ref_id, cont_off=cont_off, f_pos=enc.f_pos, force_qs=int(D.force_qs), read_qs_off=int(D.read_qs_off),
+                           streams=int(D.streams), ctx=gpu_ctx)
+    for c in range(nc):
+        assert {k: got2[c][k] for k in keys} == {k: want[c][k] for k in keys}, (spec, c, 'resident')

@@ -60,6 +60,26 @@ def test_static_scratch_entry_point_matches_pooled_entry_point(gpu_ctx):
     assert st3 == 0 and got3 == want[0]
 
 
+def test_static_scratch_entry_point_against_the_jar_and_the_oracle(rans_golden):
+    """the bytes themselves, not another GPU path: every order-0 vector the reference jar's bytecode produced
+    (tests/golden/rans_jvm.json, RANS.compress -> E04.compress) and the oracle on synthetic series"""
+    import torch
+    from oracle import rans as orans
+    lib = _lib.load()
+    vec, _ = rans_golden
+    seen = 0
+    for name, order, data, want in vec:
+        if int(order) != 0:
+            continue
+        got, st = _static_encode(lib, torch, np.frombuffer(data, np.uint8))
+        assert st == 0 and got == want, name
+        seen += 1
+    assert seen >= 20
+    for data in (synth.qs_stream(300001, 7), synth.ba_stream(65536, 8), synth.itf8_stream(12345, 9)):
+        got, st = _static_encode(lib, torch, data)
+        assert st == 0 and got == orans.compress(data, 0)
+
+
 def test_static_scratch_entry_point_edges(gpu_ctx):
     import torch
     from cramtools_b200 import ExternalCompression as EC
