@@ -270,6 +270,8 @@ class Lane(object):
         self.spec = spec
         self.pol, self.npol = rec._policy_args(spec)
         self.stream = torch.cuda.Stream(device=dev)
+        self.side = torch.cuda.Stream(device=dev)          # the slice digests run beside the record-field and histogram kernels
+        self.ev_fork, self.ev_join = torch.cuda.Event(), torch.cuda.Event()
         self.ctx = cramtools_b200.Context(dev.index)
         vp = C.c_void_p
         with torch.cuda.stream(self.stream):
@@ -367,7 +369,11 @@ class Lane(object):
         SI = self.SI
         SI.f_op = F.f_op; SI.f_pos = F.f_pos; SI.f_val = F.f_val; SI.f_aux = F.f_aux; SI.feat_off = F.feat_off
         SI.force_qs = F.force_qs; SI.read_qs_off = F.read_qs_off; SI.streams = F.streams
-        ctx.check(ctx.lib.cramgpu_slice_headers_dev(ctx.handle, C.byref(SI), vp(self.slice_hdr.data_ptr()), self._sp()))
+        # on a side stream: CRC32 is bound by shared-memory lookups, what follows on the main stream by HBM and by latency
+        self.ev_fork.record(self.stream)
+        self.side.wait_event(self.ev_fork)
+        ctx.check(ctx.lib.cramgpu_slice_headers_dev(ctx.handle, C.byref(SI), vp(self.slice_hdr.data_ptr()), C.c_void_p(self.side.cuda_stream)))
+        self.ev_join.record(self.side)
         ctx.check(ctx.lib.cramgpu_host_series_pack_dev(ctx.handle, C.byref(self.H), C.byref(self.HS), self.hoff.ctypes.data_as(u64p),
                                                        self.hlen.ctypes.data_as(u64p), self._sp()))
         base = np.uint64(F.streams); hbase = np.uint64(self.HS.streams)
@@ -379,6 +385,7 @@ class Lane(object):
                                                   self.in_len.ctypes.data_as(u32p), self.order.ctypes.data_as(u8p),
                                                   vp(self.enc_out.data_ptr()), C.c_uint64(self.enc_cap), vp(self.e_off.data_ptr()),
                                                   vp(self.e_len.data_ptr()), vp(self.e_st.data_ptr()), self._sp()))
+        self.stream.wait_event(self.ev_join)             # the step's results include the slice headers
         with self.torch.cuda.stream(self.stream):
             sizes = self.e_len.view(self.n_cont, self.NB).sum(dim=1, dtype=self.torch.int64)
             return sharding.allgather_offsets(sizes, self.rank, self.world, group=self.group)   # the path's only collective

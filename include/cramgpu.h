@@ -524,7 +524,9 @@ int cramgpu_host_series_pack_resident(cramgpu_ctx *ctx, const cramgpu_host_field
  *   scores != NULL   record.qualityScores, laid out like bases (0xFF = -1): the qualities themselves when lossless
  *   scores == NULL   take them from a cramgpu_features_encode[_dev] result: the score array in `streams` at read_qs_off[r]
  *                    when force_qs[r] bit 0 is set, else 0xFF everywhere except at the record's 'Q' features
- *                    (f_pos, f_val); needs force_qs, read_qs_off, streams, f_pos
+ *                    (f_pos, f_val); needs force_qs, read_qs_off, streams, f_pos.  (One case the features cannot express: a
+ *                    record with the unmapped flag AND an alignment start under a per-base quality model keeps sparse
+ *                    scores in memory that Writer.write never emits; pass `scores` when such records can occur.)
  *   rflags bit CRAMGPU_RF_NO_QUALS: qualityScores = SAMRecord.NULL_QUALS, an empty array (CRC32 = 0)
  */
 typedef struct cramgpu_slice_in {
