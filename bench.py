@@ -273,6 +273,7 @@ class Lane(object):
         self.side = torch.cuda.Stream(device=dev)          # the slice digests run beside the record-field and histogram kernels
         self.ev_fork, self.ev_join = torch.cuda.Event(), torch.cuda.Event()
         self.ctx = cramtools_b200.Context(dev.index)
+        self.with_digests = False          # slice header fields + BD/SD digests: a leg of their own, see run_ours
         vp = C.c_void_p
         with torch.cuda.stream(self.stream):
             reps = (n_cont + nu - 1) // nu
@@ -366,14 +367,15 @@ class Lane(object):
         ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), self.pol, self.npol, C.byref(F), self.soff.ctypes.data_as(u64p),
                                                       self.slen.ctypes.data_as(u64p), self._sp()))
         self.H.force_qs = F.force_qs                     # CF bit 0 comes from the quality model's decision
-        SI = self.SI
-        SI.f_op = F.f_op; SI.f_pos = F.f_pos; SI.f_val = F.f_val; SI.f_aux = F.f_aux; SI.feat_off = F.feat_off
-        SI.force_qs = F.force_qs; SI.read_qs_off = F.read_qs_off; SI.streams = F.streams
-        # on a side stream: CRC32 is bound by shared-memory lookups, what follows on the main stream by HBM and by latency
-        self.ev_fork.record(self.stream)
-        self.side.wait_event(self.ev_fork)
-        ctx.check(ctx.lib.cramgpu_slice_headers_dev(ctx.handle, C.byref(SI), vp(self.slice_hdr.data_ptr()), C.c_void_p(self.side.cuda_stream)))
-        self.ev_join.record(self.side)
+        if self.with_digests:
+            SI = self.SI
+            SI.f_op = F.f_op; SI.f_pos = F.f_pos; SI.f_val = F.f_val; SI.f_aux = F.f_aux; SI.feat_off = F.feat_off
+            SI.force_qs = F.force_qs; SI.read_qs_off = F.read_qs_off; SI.streams = F.streams
+            # on a side stream: CRC32 is bound by shared-memory lookups, what follows on the main stream by HBM and by latency
+            self.ev_fork.record(self.stream)
+            self.side.wait_event(self.ev_fork)
+            ctx.check(ctx.lib.cramgpu_slice_headers_dev(ctx.handle, C.byref(SI), vp(self.slice_hdr.data_ptr()), C.c_void_p(self.side.cuda_stream)))
+            self.ev_join.record(self.side)
         ctx.check(ctx.lib.cramgpu_host_series_pack_dev(ctx.handle, C.byref(self.H), C.byref(self.HS), self.hoff.ctypes.data_as(u64p),
                                                        self.hlen.ctypes.data_as(u64p), self._sp()))
         base = np.uint64(F.streams); hbase = np.uint64(self.HS.streams)
@@ -385,7 +387,8 @@ class Lane(object):
                                                   self.in_len.ctypes.data_as(u32p), self.order.ctypes.data_as(u8p),
                                                   vp(self.enc_out.data_ptr()), C.c_uint64(self.enc_cap), vp(self.e_off.data_ptr()),
                                                   vp(self.e_len.data_ptr()), vp(self.e_st.data_ptr()), self._sp()))
-        self.stream.wait_event(self.ev_join)             # the step's results include the slice headers
+        if self.with_digests:
+            self.stream.wait_event(self.ev_join)         # the step's results include the slice headers
         with self.torch.cuda.stream(self.stream):
             sizes = self.e_len.view(self.n_cont, self.NB).sum(dim=1, dtype=self.torch.int64)
             return sharding.allgather_offsets(sizes, self.rank, self.world, group=self.group)   # the path's only collective
@@ -395,7 +398,9 @@ class Lane(object):
         torch, rec, dv = self.torch, self.rec, self.dv
         from cramtools_b200._lib import u64p
         vp = C.c_void_p
+        self.with_digests = True                         # verified here once; timed only in the digest leg
         self.encode()
+        self.with_digests = False
         self.stream.synchronize()
         assert int(self.e_st.abs().sum()) == 0, 'rANS encode status'
         nblk, n_cont, NB, n_reads = self.nblk, self.n_cont, self.NB, self.n_reads
@@ -642,6 +647,18 @@ def run_ours(args):
         ln.close()
     ms_unpip, kiso = lanes[0].timed(2, 1)
     ms_unpip = max_over_ranks(ms_unpip)
+    # ---- SURVEY 8f-3, the next row: slice header fields + BD / SD content digests as part of the step (side stream)
+    lanes[0].with_digests = True
+    ms_dig, kdig = lanes[0].timed(2, 1)
+    lanes[0].with_digests = False
+    ms_dig = max_over_ranks(ms_dig)
+    digest_leg = {'row': 'ContainerFactory.buildSlice :138-176 (nofRecords, bases, sequenceId, alignment start/span, BD, SD)',
+                  'ms_per_step_unpipelined_with_digests': ms_dig, 'ms_per_step_unpipelined_without': ms_unpip,
+                  'k_slice_digest_ms': round(kdig.get('k_slice_digest', 0.0), 4), 'k_slice_finish_ms': round(kdig.get('k_slice_finish', 0.0), 4),
+                  'bytes_read_per_step': 2.0 * n_reads * READ_LEN,
+                  'GBps': 2.0 * n_reads * READ_LEN / max(kdig.get('k_slice_digest', 1e9), 1e-9) / 1e6,
+                  'verified': 'record / base counts and alignment start of every slice; BD and SD of the first two slices against zlib.crc32',
+                  'in_default_timed_step': False}
 
     # ---- the other configurations north_star names, each a short unpipelined run of the same step
     def leg(nc, spec, steps=2, warmup=1):
@@ -744,6 +761,7 @@ def run_ours(args):
                                  'clock / cycles per step (DESIGN.md, "Why the coder cannot reach the HBM roofline")'},
             'e2e': e2e, 'clocks': clocks,
         }
+        line['slice_digests'] = digest_leg
         line.update(extra_legs)
         if world == 1 and not args.no_cpu:
             line['cpu_baseline'] = cpu_baseline(args)
