@@ -224,6 +224,7 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->rec_unp.p) cudaFree(ctx->rec_unp.p);
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
+    if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
     if (ctx->slice_in.p) cudaFree(ctx->slice_in.p);
     if (ctx->pin_slice) cudaFreeHost(ctx->pin_slice);
     if (ctx->ev_slice) cudaEventDestroy(ctx->ev_slice);

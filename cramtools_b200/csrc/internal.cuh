@@ -70,6 +70,7 @@ struct cramgpu_ctx {
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
     DevPool rec_unp;                // results of cramgpu_features_unpack (its input series may be an encode result in rec_out)
     DevPool hs_scratch, hs_out, hs_in;   // cramgpu_host_series_pack: tables, result, staged inputs of the host variant
+    DevPool mate_scratch;                // cramgpu_mate_link: name tables
     DevPool slice_scratch, slice_in;     // cramgpu_slice_headers: accumulators, staged inputs of the host variant
     void *pin_slice = nullptr; size_t pin_slice_cap = 0; cudaEvent_t ev_slice = nullptr;
     void *pin_hs = nullptr, *pin_hs2 = nullptr; size_t pin_hs_cap = 0, pin_hs2_cap = 0;

@@ -405,3 +405,40 @@ def slice_headers(bases, read_off, pos, flag, f_op, f_val, f_aux, feat_off, scor
                  bases=h.bases, bd=h.bd, sd=h.sd,
                  tags={'BD': struct.pack('<I', h.bd), 'SD': struct.pack('<I', h.sd), 'B5': s5, 'S5': s5, 'B1': s1, 'S1': s1})
             for h in out[:nc]]
+
+
+# ---------------------------------------------------------------------------------------------- mate linking
+class MateIn(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('coordinate_sorted', C.c_uint32),
+                ('reserved', C.c_uint32), ('flag', C.c_void_p), ('names', C.c_void_p), ('name_off', C.c_void_p), ('ref_id', C.c_void_p),
+                ('pos', C.c_void_p), ('mate_ref_id', C.c_void_p), ('mate_pos', C.c_void_p), ('tlen', C.c_void_p), ('read_off', C.c_void_p),
+                ('f_op', C.c_void_p), ('f_val', C.c_void_p), ('f_aux', C.c_void_p), ('feat_off', C.c_void_p)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_mate_link': (C.c_int, [C.c_void_p, C.POINTER(MateIn), C.c_void_p, C.c_void_p]),
+    'cramgpu_mate_link_dev': (C.c_int, [C.c_void_p, C.POINTER(MateIn), C.c_void_p, C.c_void_p, C.c_void_p]),
+})
+
+
+def mate_link(flag, names, pos, mate_ref_id, mate_pos, tlen, read_off, f_op, f_val, f_aux, feat_off, ref_id=None, cont_off=None,
+              coordinate_sorted=True, ctx=None):
+    """CramSerilization.setMateInfo (CramSerilization.java:258-373) through cramgpu_mate_link (host buffers).
+    names: list of bytes / str.  -> (mate_cf u8[n]: 2 = detached, 4 = mate downstream, 0 = linked second; nf i32[n])"""
+    ctx = ctx or _lib.default_context()
+    n = len(flag)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nb = [x.encode('latin-1') if isinstance(x, str) else bytes(x) for x in names]
+    keep = dict(flag=_arr(flag, np.uint16), names=_arr(b''.join(nb), np.uint8),
+                name_off=np.concatenate([[0], np.cumsum([len(x) for x in nb])]).astype(np.uint64),
+                ref_id=None if ref_id is None else _arr(ref_id, np.int32), pos=_arr(pos, np.int32), mate_ref_id=_arr(mate_ref_id, np.int32),
+                mate_pos=_arr(mate_pos, np.int32), tlen=_arr(tlen, np.int32), read_off=_arr(read_off, np.uint64), f_op=_arr(f_op, np.uint8),
+                f_val=_arr(f_val, np.int32), f_aux=_arr(f_aux, np.int32), feat_off=_arr(feat_off, np.uint64))
+    I = MateIn()
+    I.n_reads = n; I.n_containers = cont_off.size - 1; I.cont_off = cont_off.ctypes.data_as(u64p)
+    I.coordinate_sorted = 1 if coordinate_sorted else 0
+    for k, v in keep.items():
+        setattr(I, k, _vp(v))
+    cf = np.zeros(max(n, 1), np.uint8); nf = np.zeros(max(n, 1), np.int32)
+    ctx.check(ctx.lib.cramgpu_mate_link(ctx.handle, C.byref(I), _vp(cf), _vp(nf)))
+    return cf[:n], nf[:n]

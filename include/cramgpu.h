@@ -564,6 +564,40 @@ int cramgpu_slice_headers_dev(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cram
 /* the four constant tags: sha1 = B1 = S1 (20 bytes), sha512 = B5 = S5 (64 bytes) */
 void cramgpu_slice_sha_tags(uint8_t sha1[20], uint8_t sha512[64]);
 
+/* ------------------------------------------------------------------ mate linking
+ *
+ * CramSerilization.setMateInfo / detach (src/main/java/htsjdk/samtools/cram/CramSerilization.java:258-373): which records of a
+ * coordinate-sorted container are written as linked mates -- CF bit "mate downstream" (value 4) on the first, the NF series =
+ * recordsToNextFragment -- and which are detached (CF value 2: MF, NS, NP, TS written in full).  A multi-fragment record is
+ * linked to the next record of the same name and class (primary / secondary) when exactly two such records are in the
+ * container, their first/last-of-pair flags fit, both template sizes equal +-CramNormalizer.computeInsertSize
+ * [CramNormalizer.java:455-470] and each record's mate fields describe the other [:318-349]; three or more records of one
+ * name are all detached, as the reference's map walk leaves them; so is everything when the header is not coordinate sorted
+ * [:175-179].  The results are the mate_cf / nf inputs of cramgpu_host_series_pack.
+ * Record fields as Sam2CramRecordFactory.createCramRecord sets them: flag = SAM flags; mate_ref_id / mate_pos / tlen =
+ * SAMRecord.getMateReferenceIndex / getMateAlignmentStart / getInferredInsertSize; the read features give
+ * CramCompressionRecord.getAlignmentEnd [CramCompressionRecord.java:160-194] for reverse-strand records.
+ * cont_off: HOST.  Host variant: every other pointer may be host or device memory; mate_cf / nf are HOST arrays [n_reads].
+ */
+typedef struct cramgpu_mate_in {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    uint32_t coordinate_sorted;   /* SAMFileHeader.getSortOrder() == coordinate */
+    uint32_t reserved;
+    const uint16_t *flag;
+    const uint8_t *names;         /* read names, concatenated */
+    const uint64_t *name_off;     /* [n_reads+1] */
+    const int32_t *ref_id;        /* NULL = all 0 */
+    const int32_t *pos, *mate_ref_id, *mate_pos, *tlen;
+    const uint64_t *read_off;     /* [n_reads+1] */
+    const uint8_t *f_op;          /* read features, as cramgpu_features */
+    const int32_t *f_val, *f_aux;
+    const uint64_t *feat_off;     /* [n_reads+1] */
+} cramgpu_mate_in;
+int cramgpu_mate_link(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *mate_cf, int32_t *nf);
+int cramgpu_mate_link_dev(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *d_mate_cf, int32_t *d_nf, void *stream);
+
 /* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
  *
  * Containers are independent and are dealt round-robin: the container with global ordinal g is converted by

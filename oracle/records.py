@@ -426,3 +426,105 @@ def write_host_streams_c(flag, cf, ref_id, read_off, pos, read_group, names, mat
                                         1 if ap_delta else 0, 1 if multi_ref else 0, int(slice_start), 1 if capture_names else 0,
                                         ptrs, _p(lens, i64p))
     return {nmk: bufs[i][:int(lens[i])].tobytes() for i, nmk in enumerate(HOST_STREAMS)}
+
+
+# ---------------------------------------------------------------------------------------------- mate linking
+def alignment_ends(rd, ex):
+    """CramCompressionRecord.getAlignmentEnd() [CramCompressionRecord.java:160-194] per record: 0 with the unmapped flag, else
+    start + readLength - #'i' - len('S') + len('D') - 1 (reference skips not counted)"""
+    n = len(rd['pos'])
+    out = np.zeros(n, np.int64)
+    rl = np.diff(np.asarray(rd['read_off'], np.int64))
+    for r in range(n):
+        if int(rd['flag'][r]) & 4:
+            continue
+        span = int(rl[r])
+        for f in range(int(ex.feat_off[r]), int(ex.feat_off[r + 1])):
+            op = chr(ex.f_op[f])
+            if op == 'i':
+                span -= 1
+            elif op == 'S':
+                span -= int(ex.f_aux[f])
+            elif op == 'D':
+                span += int(ex.f_val[f])
+        out[r] = int(rd['pos'][r]) + span - 1
+    return out
+
+
+def set_mate_info(flag, names, ref_id, pos, mate_ref_id, mate_pos, tlen, aln_end, coordinate_sorted=True):
+    """CramSerilization.setMateInfo / detach (src/main/java/htsjdk/samtools/cram/CramSerilization.java:258-373) for the records
+    of one container, in order, with the record fields as Sam2CramRecordFactory.createCramRecord sets them
+    [Sam2CramRecordFactory.java:112-146].  When the header is not coordinate sorted every record is detached [:175-179].
+    -> (mate_cf u8: bit 1 (value 2) detached, bit 2 (value 4) mate downstream; nf i32: recordsToNextFragment, -1 = none)"""
+    n = len(flag)
+    flag = [int(x) for x in flag]
+    det = [False] * n; down = [False] * n; nf = [-1] * n; nxt = [-1] * n; prv = [-1] * n
+    if not coordinate_sorted:
+        return np.full(n, 2, np.uint8), np.full(n, -1, np.int32)
+    paired = [bool(f & 1) for f in flag]
+    first = [paired[i] and bool(flag[i] & 0x40) for i in range(n)]
+    last_seg = [paired[i] and not (flag[i] & 0x40) and bool(flag[i] & 0x80) for i in range(n)]
+    neg = [bool(f & 0x10) for f in flag]
+    mate_neg = [paired[i] and bool(flag[i] & 0x20) for i in range(n)]
+    mseq = [int(mate_ref_id[i]) if paired[i] else -1 for i in range(n)]
+    mstart = [int(mate_pos[i]) if paired[i] else 0 for i in range(n)]
+    unm = [bool(f & 4) for f in flag]
+
+    def detach(i):
+        while i != -1:
+            det[i] = True; down[i] = False; nf[i] = -1
+            i = nxt[i]
+
+    def insert_size(a, b):                                       # CramNormalizer.computeInsertSize [CramNormalizer.java:455-470]
+        if unm[a] or unm[b] or int(ref_id[a]) != int(ref_id[b]):
+            return 0
+        pa = int(aln_end[a]) if neg[a] else int(pos[a])
+        pb = int(aln_end[b]) if neg[b] else int(pos[b])
+        return pb - pa + (1 if pb >= pa else -1)
+    maps = ({}, {})
+    for i in range(n):
+        if not paired[i]:
+            det[i] = True; down[i] = False; nf[i] = -1
+            continue
+        m = maps[1 if flag[i] & 0x100 else 0]
+        key = bytes(names[i]) if not isinstance(names[i], str) else names[i].encode('latin-1')
+        j = m.get(key)
+        if j is None:
+            m[key] = i
+            continue
+        if nxt[j] != -1 or prv[j] != -1:
+            detach(i); detach(j)
+            continue
+        nf[j] = i - j - 1
+        nxt[j] = i; prv[i] = j
+        down[j] = True; down[i] = False; det[i] = False; det[j] = False
+    for r in range(n):
+        if nxt[r] == -1 or prv[r] != -1:
+            continue
+        last = r
+        while nxt[last] != -1:
+            last = nxt[last]
+        if (first[r] and last_seg[last]) or (first[last] and last_seg[r]):
+            tl = insert_size(r, last)
+            if int(tlen[r]) == tl:
+                l2 = nxt[r]
+                while nxt[l2] != -1:
+                    if int(tlen[l2]) != -tl:
+                        break
+                    l2 = nxt[l2]
+                if int(tlen[l2]) != -tl:
+                    detach(r)
+            else:
+                detach(r)
+        else:
+            detach(r)
+        if (mseq[r] != int(ref_id[last]) or int(ref_id[r]) != mseq[last] or mate_neg[r] != neg[last] or mate_neg[last] != neg[r]
+                or mstart[r] != int(pos[last]) or mstart[last] != int(pos[r])):
+            detach(r)
+    for m in maps:
+        for i in m.values():
+            if nxt[i] != -1:
+                continue
+            det[i] = True; down[i] = False; nf[i] = -1
+    cf = np.array([(2 if det[i] else 0) | (4 if down[i] else 0) for i in range(n)], np.uint8)
+    return cf, np.array(nf, np.int32)

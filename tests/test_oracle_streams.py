@@ -131,3 +131,21 @@ def test_slice_header_and_digests_match_jar(G):
         assert h['tags'] == want, c['tag']
         seen.add(h['sequence_id'])
     assert -2 in seen and 0 in seen          # a multi-reference slice and a single-reference one
+
+
+def test_mate_linking_matches_jar(G):
+    """CramSerilization.setMateInfo -- detached / mate-downstream bits of CF and recordsToNextFragment of every
+    record, against what the jar's own setMateInfo left in the records (proper pairs, a pair with a wrong TLEN, a mate outside
+    the container, a secondary pair, a triplet, unsorted header)"""
+    g, ref, conts = G
+    linked = 0
+    for c, rd, series in conts:
+        sc = c['scalars']
+        ex = orec.extract(rd, ref)
+        ends = orec.alignment_ends(rd, ex)
+        cf, nf = orec.set_mate_info(rd['flag'], rd['names'], rd['ref_id'], rd['pos'], [s['mate_seq_id'] for s in sc],
+                                    [s['mate_start'] for s in sc], [s['tlen'] for s in sc], ends, coordinate_sorted=c['coordinate_sorted'])
+        assert [int(x) for x in cf] == [s['cf'] & 6 for s in sc], c['tag']
+        assert [int(x) for x in nf] == [s['nf'] for s in sc], c['tag']
+        linked += int((cf == 4).sum())
+    assert linked == 10

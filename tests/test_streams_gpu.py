@@ -240,3 +240,82 @@ def test_slice_headers_parity_with_oracle(R, gpu_ctx, spec):
         # emits as features [Writer.java:180-186]: the feature arrays cannot give its SD term -- slice 0 holds that record)
         ks = [k for k in keys if not (per_base and c == 0 and k == 'sd')]
         assert {k: got2[c][k] for k in ks} == {k: want[c][k] for k in ks}, (spec, c, 'resident')
+
+
+def test_mate_linking_matches_jar_and_feeds_the_writer(R, G, gpu_ctx):
+    """cramgpu_mate_link against what the jar's CramSerilization.setMateInfo left in the records, then straight into
+    cramgpu_host_series_pack: CF MF NS NP TS NF come out byte for byte as the jar's Writer wrote them -- with no mate decision
+    taken on the host"""
+    g, ref, conts = G
+    for c, rd, series in conts:
+        sc = c['scalars']
+        enc = R.features_encode(rd, ref, None, ctx=gpu_ctx)
+        cf, nf = R.mate_link(rd['flag'], rd['names'], rd['pos'], [s['mate_seq_id'] for s in sc], [s['mate_start'] for s in sc],
+                             [s['tlen'] for s in sc], rd['read_off'], enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, ref_id=rd['ref_id'],
+                             coordinate_sorted=c['coordinate_sorted'], ctx=gpu_ctx)
+        assert [int(x) for x in cf] == [s['cf'] & 6 for s in sc], c['tag']
+        assert [int(x) for x in nf] == [s['nf'] for s in sc], c['tag']
+        kw = _host_fields(c, rd)
+        kw['nf'] = nf
+        got = R.host_series_pack(mate_cf=cf, force_qs=enc.force_qs, rflags=rd['rflags'], ctx=gpu_ctx, **kw)
+        for nm in R.HOST_SERIES:
+            assert got.series(0, nm) == series.get(CID[nm], b''), (c['tag'], nm)
+
+
+def test_mate_linking_parity_with_oracle_random_pairs(R, gpu_ctx):
+    """thousands of templates over several containers: proper pairs, pairs split across containers, wrong TLEN / mate position /
+    strand, three and four records of one name, secondary pairs sharing a primary's name, unpaired records, names that differ
+    only in the last byte or in length"""
+    from oracle import records as orec
+    from cramtools_b200 import synth
+    rng = np.random.default_rng(33)
+    ref = synth.reference(60000, 5)
+    rd = synth.reads(ref, 9000, 6, read_len=100, indel_frac=0.2, clip_frac=0.1)
+    n = len(rd['pos'])
+    ex = orec.extract(rd, ref)
+    ends = orec.alignment_ends(rd, ex)
+    flag = rd['flag'].astype(np.int64) & 0x10
+    names = [b''] * n
+    mate_ref = np.full(n, -1, np.int64); mate_pos = np.zeros(n, np.int64); tlen = np.zeros(n, np.int64)
+    order = rng.permutation(n)
+    i = 0
+    t = 0
+    while i + 4 <= n:
+        kind = rng.integers(0, 10)
+        nm = ('t%d' % t).encode() if kind != 9 else ('t%d' % (t // 2 * 2)).encode() + b'x' * int(rng.integers(0, 2))
+        t += 1
+        if kind == 0:                                   # unpaired
+            names[order[i]] = nm; i += 1
+            continue
+        k = 3 if kind == 1 else 4 if kind == 2 else 2
+        members = sorted(order[i:i + k]); i += k
+        sec = 0x100 if kind == 3 else 0
+        for j, m in enumerate(members):
+            names[m] = nm
+            flag[m] |= 1 | sec | (0x40 if j == 0 else 0x80)
+        a, b = members[0], members[1]
+        for x, y in ((a, b), (b, a)):
+            mate_ref[x] = 0; mate_pos[x] = rd['pos'][y]
+            if flag[y] & 0x10:
+                flag[x] |= 0x20
+        pa = ends[a] if flag[a] & 0x10 else rd['pos'][a]; pb = ends[b] if flag[b] & 0x10 else rd['pos'][b]
+        tl = pb - pa + (1 if pb >= pa else -1)
+        tlen[a], tlen[b] = tl, -tl
+        if kind == 4: tlen[b] += 1                      # second TLEN off
+        if kind == 5: mate_pos[a] += 1                  # mate position off
+        if kind == 6: flag[a] ^= 0x20                   # mate strand off
+        if kind == 7: flag[b] = (flag[b] & ~0x80) | 0x40      # two firsts
+    cont_off = np.array([0, 2500, 2501, 6000, n], np.uint64)
+    enc = R.features_encode(dict(rd, flag=(flag & 0xFFFF).astype(np.uint16)), ref, None, cont_off=cont_off, ctx=gpu_ctx)
+    cf, nf = R.mate_link(flag, names, rd['pos'], mate_ref, mate_pos, tlen, rd['read_off'], enc.f_op, enc.f_val, enc.f_aux, enc.feat_off,
+                         cont_off=cont_off, ctx=gpu_ctx)
+    linked = 0
+    for c in range(4):
+        a, b = int(cont_off[c]), int(cont_off[c + 1])
+        wcf, wnf = orec.set_mate_info(flag[a:b], names[a:b], np.zeros(b - a), rd['pos'][a:b], mate_ref[a:b], mate_pos[a:b], tlen[a:b], ends[a:b])
+        assert (cf[a:b] == wcf).all() and (nf[a:b] == wnf).all(), c
+        linked += int((wcf == 4).sum())
+    assert linked > 500
+    cf0, nf0 = R.mate_link(flag, names, rd['pos'], mate_ref, mate_pos, tlen, rd['read_off'], enc.f_op, enc.f_val, enc.f_aux, enc.feat_off,
+                           cont_off=cont_off, coordinate_sorted=False, ctx=gpu_ctx)
+    assert (cf0 == 2).all() and (nf0 == -1).all()
