@@ -715,7 +715,10 @@ def run_ours(args):
     import gc
     gc.collect()
     torch.cuda.empty_cache()
-    e2e = run_e2e(args, ref, rd, nu, n_e2e, world, barrier, args.e2e_pipeline, comp_hint, local)
+    # contexts of the end-to-end leg: 8 on one GPU (five calls per step, each holding the host for 100+ ms: more contexts than
+    # calls keep every stage busy); fewer per GPU when several ranks share the host's cores and page-locked memory
+    e2e_depth = args.e2e_pipeline if args.e2e_pipeline > 0 else (8 if world == 1 else 6 if world == 2 else 4)
+    e2e = run_e2e(args, ref, rd, nu, n_e2e, world, barrier, e2e_depth, comp_hint, local)
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
@@ -1112,7 +1115,7 @@ def main():
     ap.add_argument('--containers', type=int, default=2048, help='containers PER GPU (10 000 reads each)')
     ap.add_argument('--e2e-containers', type=int, default=1024, help='containers per GPU of the end-to-end (host buffer) leg')
     ap.add_argument('--pipeline', type=int, default=2, help='contexts per GPU taking consecutive steps in turn (1 = no overlap of encode and decode)')
-    ap.add_argument('--e2e-pipeline', type=int, default=4, help='contexts of the end-to-end leg taking consecutive steps in turn')
+    ap.add_argument('--e2e-pipeline', type=int, default=0, help='contexts of the end-to-end leg taking consecutive steps in turn (0 = 8 on one GPU, 6 on two, 4 beyond)')
     ap.add_argument('--no-unpack', action='store_true', help='decode side: take the read features from the encoder instead of unpacking the series (row P)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     ap.add_argument('--no-configs', action='store_true', help='skip the short runs of the other north_star configurations (quality models, 20 containers, fixed total)')
