@@ -110,6 +110,10 @@ def jstr(v):
     return v.fields['s'] if isinstance(v, JObject) and v.cls == 'java/lang/String' else v
 
 
+def list_items(o):
+    return o.fields['list']
+
+
 def enum_name(o):
     return None if o is None else o.fields['name']
 
@@ -194,14 +198,53 @@ def build(reads, ref, coordinate_sorted, tag):
         vm.call(RDR, 'read', '(L%s;)V' % CCR, [reader, cr])
         qs = cr.fields.get('qualityScores')
         rb = cr.fields.get('readBases')
-        back.append(dict(flags=cr.fields.get('flags', 0), cf=i8(cr.fields.get('compressionFlags', 0)) & 0xFF, seq_id=cr.fields.get('sequenceId', 0),
+        # the CIGAR Cram2SamRecordFactory rebuilds from the read features [Cram2SamRecordFactory.java:119-225]
+        cg = vm.call('htsjdk/samtools/cram/build/Cram2SamRecordFactory', 'getCigar2', '(Ljava/util/Collection;I)Lhtsjdk/samtools/Cigar;',
+                     [cr.fields.get('readFeatures'), cr.fields.get('readLength', 0)])
+        cigar2 = ''.join('%d%s' % (e.fields['length'], 'MIDNSHP=X'[['M', 'I', 'D', 'N', 'S', 'H', 'P', 'EQ', 'X'].index(enum_name(e.fields['operator']))])
+                         for e in list_items(cg.fields['cigarElements']))
+        # ... and the BAM record cramtools' flat-buffer writer lays out from these values (BAMRecordView.java:70-241, in the order
+        # ReaderToBAM.read drives it [ReaderToBAM.java:64-176]); index bin as SAMRecord.computeIndexingBin [SAMRecord.java:1524-1531]
+        rd0 = reads[i]; sc0 = scalars[i]
+        BV = 'htsjdk/samtools/cram/encoding/reader/BAMRecordView'
+        view = new(BV, '([B)V', jbytes(bytes(4096)))
+        vm.call(BV, 'setRefID', '(I)V', [view, rd0['ref_id']])
+        vm.call(BV, 'setAlignmentStart', '(I)V', [view, rd0['pos']])
+        vm.call(BV, 'setReadName', '([B)V', [view, jbytes(rd0['name'].encode('latin-1'))])
+        vm.call(BV, 'setMappingScore', '(I)V', [view, rd0['mapq']])
+        unm = bool(rd0['flag'] & 4)
+        if unm:
+            cg_rec = new('htsjdk/samtools/Cigar')
+        else:
+            cg_rec = cg
+        beg = rd0['pos'] - 1
+        end = 0 if unm else rd0['pos'] + vm.call('htsjdk/samtools/Cigar', 'getReferenceLength', '()I', [cg_rec]) - 1
+        if end <= 0:
+            end = beg + 1
+        bam_bin = vm.call('htsjdk/samtools/GenomicIndexUtil', 'regionToBin', '(II)I', [beg, end])
+        vm.call(BV, 'setIndexBin', '(I)V', [view, bam_bin])
+        vm.call(BV, 'setCigar', '(Lhtsjdk/samtools/Cigar;)V', [view, cg_rec])
+        vm.call(BV, 'setFlags', '(I)V', [view, rd0['flag']])
+        paired = bool(rd0['flag'] & 1)
+        vm.call(BV, 'setMateRefID', '(I)V', [view, sc0['mate_seq_id'] if paired else -1])
+        vm.call(BV, 'setMateAlStart', '(I)V', [view, sc0['mate_start'] if paired else 0])
+        vm.call(BV, 'setInsertSize', '(I)V', [view, sc0['tlen']])
+        bb = b'' if rd0['bases'] is None else bytes(rd0['bases'])
+        vm.call(BV, 'setBases', '([BII)V', [view, jbytes(bb), 0, len(bb)])
+        qq = b'' if rd0['quals'] is None else bytes(rd0['quals'])
+        vm.call(BV, 'setQualityScores', '([BII)V', [view, jbytes(qq), 0, len(qq)])
+        tagb = (b'RGZ' + rd0['rg'].encode() + b'\0') if rd0.get('rg') else b''
+        vm.call(BV, 'setTagData', '([BII)V', [view, jbytes(tagb), 0, len(tagb)])
+        bsz = vm.call(BV, 'finish', '()I', [view])
+        bam_rec = bytes(view.fields['buf'].a[:bsz])
+        back.append(dict(bam=b64(bam_rec), bam_bin=bam_bin, bam_tags=b64(tagb), flags=cr.fields.get('flags', 0), cf=i8(cr.fields.get('compressionFlags', 0)) & 0xFF, seq_id=cr.fields.get('sequenceId', 0),
                          read_length=cr.fields.get('readLength', 0), alignment_delta=cr.fields.get('alignmentDelta', 0),
                          alignment_start=cr.fields.get('alignmentStart', 0),
                          read_group=cr.fields.get('readGroupID', 0), name=jstr(cr.fields.get('readName')),
                          mate_flags=i8(cr.fields.get('mateFlags', 0)) & 0xFF, mate_seq_id=cr.fields.get('mateSequenceID', 0),
                          mate_start=cr.fields.get('mateAlignmentStart', 0), tlen=cr.fields.get('templateSize', 0),
                          nf=cr.fields.get('recordsToNextFragment', 0), mapq=cr.fields.get('mappingQuality', 0),
-                         features=features_of(cr), quals=None if qs is None else b64(qs.a), bases=None if rb is None else b64(rb.a)))
+                         features=features_of(cr), cigar2=cigar2, quals=None if qs is None else b64(qs.a), bases=None if rb is None else b64(rb.a)))
     out['read_back'] = back
     left = {}
     for k, (key, bis) in imap.fields['map'].items():

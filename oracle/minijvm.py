@@ -991,6 +991,8 @@ class MiniJVM:
         if cn == 'java/util/Collections':
             if mn == 'emptyList':
                 return self.empty_list()
+            if mn == 'singletonList':
+                o = JObject('java/util/ArrayList'); o.fields['list'] = [args[0]]; return o
             if mn == 'sort':
                 lst = args[0].fields['list']
                 if len(args) == 2 and args[1] is not None:
