@@ -225,6 +225,13 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
     if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
+    if (ctx->bam_scratch.p) cudaFree(ctx->bam_scratch.p);
+    if (ctx->bam_cigar.p) cudaFree(ctx->bam_cigar.p);
+    if (ctx->bam_out.p) cudaFree(ctx->bam_out.p);
+    if (ctx->bam_unp.p) cudaFree(ctx->bam_unp.p);
+    if (ctx->bam_pk_scratch.p) cudaFree(ctx->bam_pk_scratch.p);
+    if (ctx->bam_unp_scratch.p) cudaFree(ctx->bam_unp_scratch.p);
+    if (ctx->pin_bam) cudaFreeHost(ctx->pin_bam);
     if (ctx->slice_in.p) cudaFree(ctx->slice_in.p);
     if (ctx->pin_slice) cudaFreeHost(ctx->pin_slice);
     if (ctx->ev_slice) cudaEventDestroy(ctx->ev_slice);

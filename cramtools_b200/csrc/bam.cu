@@ -1,0 +1,484 @@
+// bam.cu -- CIGAR rebuild and BAM record (de)serialisation on the device.
+//
+//   cramgpu_cigar_rebuild_dev   Cram2SamRecordFactory.getCigar2 [htsjdk Cram2SamRecordFactory.java:119-225]: read features -> CIGAR
+//   cramgpu_bam_pack_dev        the record layout of cramtools' flat-buffer BAM writer
+//                               (src/main/java/htsjdk/samtools/cram/encoding/reader/BAMRecordView.java:70-241), index bin as
+//                               SAMRecord.computeIndexingBin [SAMRecord.java:1524-1531] / GenomicIndexUtil.regionToBin [:63-70]
+//   cramgpu_bam_unpack_dev      the inverse: a stripe of raw BAM records as Bam_OBA_Supplier cuts them
+//                               (src/main/java/htsjdk/samtools/cram/paralell/Bam_OBA_Supplier.java:45-82) -> the structure of
+//                               arrays the other entry points take (4-bit bases -> ASCII, pos + 1, ...)
+//
+// All three are "sizes, scan, write": a record's output position depends on the sizes of the records before it.  Sizes are one
+// thread per record; the scan is three small kernels over 4096-item tiles; the writers are one warp per record with the lanes
+// over the bytes, so that loads and stores of a record are contiguous.  HBM-bound byte shuffling, no shared memory to speak of.
+#include "internal.cuh"
+#include <string.h>
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------- exclusive scan u32 -> u64
+#define SCAN_TILE 4096u
+__global__ void __launch_bounds__(256) k_scan_tile_sums(const uint32_t *__restrict__ in, uint64_t n, uint64_t *__restrict__ tile_sum)
+{
+    __shared__ unsigned long long s[8];
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE;
+    unsigned long long v = 0;
+    for (uint32_t k = threadIdx.x; k < SCAN_TILE; k += 256) if (base + k < n) v += in[base + k];
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+    if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) { unsigned long long t = 0; for (int k = 0; k < 8; k++) t += s[k]; tile_sum[blockIdx.x] = t; }
+}
+// one CTA: tile sums -> exclusive tile offsets (in place); total -> out[n]
+__global__ void __launch_bounds__(256) k_scan_tiles(uint64_t *__restrict__ tile_sum, uint64_t ntiles, uint64_t *__restrict__ total_at)
+{
+    __shared__ unsigned long long s[256], carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint64_t t0 = 0; t0 < ntiles; t0 += 256) {
+        const uint64_t i = t0 + threadIdx.x;
+        const unsigned long long v = i < ntiles ? tile_sum[i] : 0;
+        s[threadIdx.x] = v;
+        __syncthreads();
+        for (uint32_t d = 1; d < 256; d <<= 1) {
+            const unsigned long long a = threadIdx.x >= d ? s[threadIdx.x - d] : 0;
+            __syncthreads();
+            s[threadIdx.x] += a;
+            __syncthreads();
+        }
+        if (i < ntiles) tile_sum[i] = carry + s[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == 255) carry += s[255];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *total_at = carry;
+}
+__global__ void __launch_bounds__(256) k_scan_apply(const uint32_t *__restrict__ in, uint64_t n, const uint64_t *__restrict__ tile_off,
+                                                    uint64_t *__restrict__ out)
+{
+    // thread t owns the 16 consecutive items 16 t .. 16 t + 15 of the tile
+    __shared__ unsigned long long s[256];
+    const uint64_t base = (uint64_t)blockIdx.x * SCAN_TILE + 16ull * threadIdx.x;
+    uint32_t v[16];
+    unsigned long long sum = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) { v[k] = base + k < n ? in[base + k] : 0u; sum += v[k]; }
+    s[threadIdx.x] = sum;
+    __syncthreads();
+    for (uint32_t d = 1; d < 256; d <<= 1) {
+        const unsigned long long a = threadIdx.x >= d ? s[threadIdx.x - d] : 0;
+        __syncthreads();
+        s[threadIdx.x] += a;
+        __syncthreads();
+    }
+    unsigned long long at = tile_off[blockIdx.x] + s[threadIdx.x] - sum;
+#pragma unroll
+    for (int k = 0; k < 16; k++) { if (base + k < n) out[base + k] = at; at += v[k]; }
+}
+
+}  // namespace
+
+// sizes[n] (u32) -> off[n + 1] (u64), off[n] = total.  `tiles` = scratch of at least (n / 4096 + 1) u64.
+static int scan_sizes(cramgpu_ctx *ctx, const uint32_t *d_sizes, uint64_t n, uint64_t *d_off, uint64_t *d_tiles, cudaStream_t st)
+{
+    const uint64_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (ntiles == 0) { CUDA_TRY(ctx, cudaMemsetAsync(d_off, 0, 8, st)); return CRAMGPU_OK; }
+    LAUNCH(ctx, st, "k_scan_tile_sums", k_scan_tile_sums<<<(uint32_t)ntiles, 256, 0, st>>>(d_sizes, n, d_tiles));
+    LAUNCH(ctx, st, "k_scan_tiles", k_scan_tiles<<<1, 256, 0, st>>>(d_tiles, ntiles, d_off + n));
+    LAUNCH(ctx, st, "k_scan_apply", k_scan_apply<<<(uint32_t)ntiles, 256, 0, st>>>(d_sizes, n, d_tiles, d_off));
+    CUDA_TRY(ctx, cudaGetLastError());
+    return CRAMGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- CIGAR from read features
+namespace {
+
+enum { CG_M = 0, CG_I, CG_D, CG_N, CG_S, CG_H, CG_P };
+__device__ __forceinline__ bool cg_consumes_read(int op) { return op == CG_M || op == CG_I || op == CG_S; }
+
+struct CigarArgs {
+    uint64_t n;
+    const uint16_t *flag;
+    const uint64_t *read_off, *feat_off;
+    const uint8_t *f_op;
+    const int32_t *f_pos, *f_val, *f_aux;
+    uint32_t *count;              // elements per record
+    const uint64_t *cigar_off;    // write pass
+    uint32_t *cigar;
+};
+
+// getCigar2 [Cram2SamRecordFactory.java:119-225], one thread per record; emit(length, op) in element order.
+// A record with the unmapped flag has no CIGAR (create() sets "*" [:68-69]).
+template <typename E>
+__device__ __forceinline__ void cigar_walk(const CigarArgs &a, uint64_t r, E emit)
+{
+    if (a.flag[r] & 4) return;
+    const int32_t read_length = (int32_t)(a.read_off[r + 1] - a.read_off[r]);
+    const uint64_t f0 = a.feat_off[r], f1 = a.feat_off[r + 1];
+    int last_op = CG_M;
+    int32_t last_len = 0, last_pos = 1;
+    bool any = false, emitted = false;
+    for (uint64_t f = f0; f < f1; f++) {
+        const uint8_t op = a.f_op[f];
+        int co; int32_t rl;
+        switch (op) {                                        // [:148-183]; everything else (quality scores) is skipped before
+        case 'I': co = CG_I; rl = a.f_aux[f]; break;         // the position is even looked at? no: the gap comes first [:134-146]
+        case 'S': co = CG_S; rl = a.f_aux[f]; break;
+        case 'H': co = CG_H; rl = a.f_val[f]; break;
+        case 'i': co = CG_I; rl = 1; break;
+        case 'D': co = CG_D; rl = a.f_val[f]; break;
+        case 'N': co = CG_N; rl = a.f_val[f]; break;
+        case 'P': co = CG_P; rl = a.f_val[f]; break;
+        case 'X': case 'B': co = CG_M; rl = 1; break;
+        default: co = -1; rl = 0; break;
+        }
+        any = true;
+        const int32_t pos = a.f_pos[f];
+        const int32_t gap = pos - (last_pos + last_len);
+        if (gap > 0) {
+            if (last_op != CG_M) { emit(last_len, last_op); emitted = true; last_pos += last_len; last_len = gap; }
+            else last_len += gap;
+            last_op = CG_M;
+        }
+        if (co < 0) continue;
+        if (last_op != co) {
+            if (last_len > 0) { emit(last_len, last_op); emitted = true; }
+            last_op = co; last_len = rl; last_pos = pos;
+        } else last_len += rl;
+        if (!cg_consumes_read(co)) last_pos -= rl;
+    }
+    if (!any) { emit(read_length, CG_M); return; }           // no features at all [:119-121]
+    if (last_op != CG_M) {
+        emit(last_len, last_op); emitted = true;
+        if (read_length >= last_pos + last_len) emit(read_length - (last_len + last_pos) + 1, CG_M);
+    } else if (read_length == 0 || read_length > last_pos - 1) {
+        emit(read_length == 0 ? last_len : read_length - last_pos + 1, CG_M); emitted = true;
+    }
+    if (!emitted) emit(read_length, CG_M);                   // empty list [:220-222]
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(128) k_cigar(CigarArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (r >= a.n) return;
+    uint32_t k = 0;
+    uint32_t *dst = WRITE ? a.cigar + a.cigar_off[r] : nullptr;
+    cigar_walk(a, r, [&](int32_t len, int op) { if (WRITE) dst[k] = ((uint32_t)len << 4) | (uint32_t)op; k++; });
+    if (!WRITE) a.count[r] = k;
+}
+
+}  // namespace
+
+extern "C" int cramgpu_cigar_rebuild_dev(cramgpu_ctx *ctx, uint64_t n_reads, const uint16_t *d_flag, const uint64_t *d_read_off,
+                                         const uint64_t *d_feat_off, const uint8_t *d_f_op, const int32_t *d_f_pos, const int32_t *d_f_val,
+                                         const int32_t *d_f_aux, uint32_t **d_cigar, uint64_t **d_cigar_off, uint64_t *cigar_len, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!d_cigar || !d_cigar_off || !cigar_len) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    *d_cigar = nullptr; *d_cigar_off = nullptr; *cigar_len = 0;
+    if (n_reads == 0) return CRAMGPU_OK;
+    if (!d_flag || !d_read_off || !d_feat_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const uint64_t n = n_reads;
+    Carver cv;
+    const size_t o_cnt = cv.take(4 * n), o_off = cv.take(8 * (n + 1)), o_tiles = cv.take(8 * (n / SCAN_TILE + 2));
+    if (int rc = pool_reserve(ctx, ctx->bam_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->bam_scratch.p;
+    CigarArgs a;
+    memset(&a, 0, sizeof a);
+    a.n = n; a.flag = d_flag; a.read_off = d_read_off; a.feat_off = d_feat_off; a.f_op = d_f_op; a.f_pos = d_f_pos; a.f_val = d_f_val; a.f_aux = d_f_aux;
+    a.count = (uint32_t *)(S + o_cnt); a.cigar_off = (const uint64_t *)(S + o_off);
+    const uint32_t grid = (uint32_t)((n + 127) / 128);
+    LAUNCH(ctx, st, "k_cigar_count", k_cigar<false><<<grid, 128, 0, st>>>(a));
+    if (int rc = scan_sizes(ctx, a.count, n, (uint64_t *)(S + o_off), (uint64_t *)(S + o_tiles), st)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_bam, &ctx->pin_bam_cap, 64)) return rc;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pin_bam, S + o_off + 8 * n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));                 // the total sizes the result buffer
+    const uint64_t total = *(const uint64_t *)ctx->pin_bam;
+    if (int rc = pool_reserve(ctx, ctx->bam_cigar, 4 * total + 16)) return rc;
+    a.cigar = (uint32_t *)ctx->bam_cigar.p;
+    LAUNCH(ctx, st, "k_cigar_write", k_cigar<true><<<grid, 128, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    *d_cigar = a.cigar; *d_cigar_off = (uint64_t *)(S + o_off); *cigar_len = total;
+    return CRAMGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- BAM records: pack
+namespace {
+
+// GenomicIndexUtil.regionToBin [GenomicIndexUtil.java:63-70]
+__device__ __forceinline__ uint32_t reg2bin(int32_t beg, int32_t end)
+{
+    --end;
+    if (beg >> 14 == end >> 14) return 4681 + (beg >> 14);
+    if (beg >> 17 == end >> 17) return 585 + (beg >> 17);
+    if (beg >> 20 == end >> 20) return 73 + (beg >> 20);
+    if (beg >> 23 == end >> 23) return 9 + (beg >> 23);
+    if (beg >> 26 == end >> 26) return 1 + (beg >> 26);
+    return 0;
+}
+
+// BAMRecordView.charToCompressedBaseLow / High [BAMRecordView.java:360-530]: 16 = IllegalArgumentException
+__device__ __forceinline__ uint32_t base_nybble(uint8_t b)
+{
+    switch (b) {
+    case '=': return 0;
+    case 'A': case 'a': return 1;
+    case 'C': case 'c': return 2;
+    case 'M': case 'm': return 3;
+    case 'G': case 'g': return 4;
+    case 'R': case 'r': return 5;
+    case 'S': case 's': return 6;
+    case 'V': case 'v': return 7;
+    case 'T': case 't': return 8;
+    case 'W': case 'w': return 9;
+    case 'Y': case 'y': return 10;
+    case 'H': case 'h': return 11;
+    case 'K': case 'k': return 12;
+    case 'D': case 'd': return 13;
+    case 'B': case 'b': return 14;
+    case 'N': case 'n': case '.': return 15;
+    default: return 16;
+    }
+}
+
+struct PackArgs {
+    cramgpu_bam_records in;
+    uint32_t *size;               // bytes of every record, with the block_size field
+    const uint64_t *rec_off;      // write pass
+    uint8_t *out;
+    int32_t *status;
+};
+
+__global__ void __launch_bounds__(128) k_bam_size(PackArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (r >= a.in.n_reads) return;
+    const uint64_t lname = a.in.name_off[r + 1] - a.in.name_off[r] + 1, ncig = a.in.cigar_off[r + 1] - a.in.cigar_off[r];
+    const uint64_t lseq = a.in.read_off[r + 1] - a.in.read_off[r], ltag = a.in.tags ? a.in.tag_off[r + 1] - a.in.tag_off[r] : 0;
+    a.size[r] = (uint32_t)(36 + lname + 4 * ncig + (lseq + 1) / 2 + lseq + ltag);
+}
+
+__device__ __forceinline__ void put_le32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
+__device__ __forceinline__ void put_le16(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); }
+
+// one warp per record, lanes over the bytes
+__global__ void __launch_bounds__(128) k_bam_write(PackArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.in.n_reads) return;
+    const uint32_t lane = threadIdx.x & 31;
+    const cramgpu_bam_records &R = a.in;
+    const uint64_t n0 = R.name_off[r], c0 = R.cigar_off[r], b0 = R.read_off[r];
+    const uint32_t lname = (uint32_t)(R.name_off[r + 1] - n0), ncig = (uint32_t)(R.cigar_off[r + 1] - c0), lseq = (uint32_t)(R.read_off[r + 1] - b0);
+    const uint64_t t0 = R.tags ? R.tag_off[r] : 0;
+    const uint32_t ltag = R.tags ? (uint32_t)(R.tag_off[r + 1] - t0) : 0u;
+    uint8_t *o = a.out + a.rec_off[r];
+    const uint32_t total = (uint32_t)(a.rec_off[r + 1] - a.rec_off[r]);
+    // reference length of the CIGAR -> alignment end -> bin [SAMRecord.java:591-598,1524-1531]
+    int32_t reflen = 0;
+    for (uint32_t k = lane; k < ncig; k += 32) {
+        const uint32_t w = R.cigar[c0 + k], op = w & 15u;
+        if (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) reflen += (int32_t)(w >> 4);
+        o[36 + lname + 1 + 4 * k] = (uint8_t)w; o[36 + lname + 1 + 4 * k + 1] = (uint8_t)(w >> 8);
+        o[36 + lname + 1 + 4 * k + 2] = (uint8_t)(w >> 16); o[36 + lname + 1 + 4 * k + 3] = (uint8_t)(w >> 24);
+    }
+    for (int d = 16; d; d >>= 1) reflen += __shfl_xor_sync(0xFFFFFFFFu, reflen, d);
+    if (lane == 0) {
+        const int32_t pos = R.pos[r];
+        const uint16_t flag = R.flag[r];
+        const int32_t beg = pos - 1;
+        int32_t end = (flag & 4) ? 0 : pos + reflen - 1;
+        if (end <= 0) end = beg + 1;
+        put_le32(o, total - 4);
+        put_le32(o + 4, (uint32_t)(R.ref_id ? R.ref_id[r] : 0));
+        put_le32(o + 8, (uint32_t)beg);
+        o[12] = (uint8_t)(lname + 1);
+        o[13] = R.mapq[r];
+        put_le16(o + 14, reg2bin(beg, end));
+        put_le16(o + 16, ncig);
+        put_le16(o + 18, flag);
+        put_le32(o + 20, lseq);
+        put_le32(o + 24, (uint32_t)(R.mate_ref_id ? R.mate_ref_id[r] : -1));
+        put_le32(o + 28, (uint32_t)((R.mate_pos ? R.mate_pos[r] : 0) - 1));
+        put_le32(o + 32, (uint32_t)(R.tlen ? R.tlen[r] : 0));
+        o[36 + lname] = 0;
+    }
+    for (uint32_t k = lane; k < lname; k += 32) o[36 + k] = R.names[n0 + k];
+    uint8_t *sq = o + 36 + lname + 1 + 4 * ncig;
+    bool bad = false;
+    for (uint32_t k = lane; k < (lseq + 1) / 2; k += 32) {
+        uint32_t hi = base_nybble(R.bases[b0 + 2 * k]), lo = 2 * k + 1 < lseq ? base_nybble(R.bases[b0 + 2 * k + 1]) : 0u;
+        if (hi > 15 || lo > 15) { bad = true; hi = min(hi, 15u); lo = min(lo, 15u); }
+        sq[k] = (uint8_t)((hi << 4) | lo);
+    }
+    uint8_t *ql = sq + (lseq + 1) / 2;
+    const bool noq = R.rflags && (R.rflags[r] & CRAMGPU_RF_NO_QUALS);
+    for (uint32_t k = lane; k < lseq; k += 32) ql[k] = noq ? (uint8_t)0xFF : R.quals[b0 + k];
+    for (uint32_t k = lane; k < ltag; k += 32) ql[lseq + k] = R.tags[t0 + k];
+    bad = __any_sync(0xFFFFFFFFu, bad);
+    if (lane == 0) a.status[r] = bad ? CRAMGPU_ERR_ARG : CRAMGPU_OK;
+}
+
+}  // namespace
+
+extern "C" int cramgpu_bam_pack_dev(cramgpu_ctx *ctx, const cramgpu_bam_records *in, uint8_t **d_bam, uint64_t *bam_len, uint64_t **d_rec_off,
+                                    int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !d_bam || !bam_len || !d_rec_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    *d_bam = nullptr; *bam_len = 0; *d_rec_off = nullptr;
+    const uint64_t n = in->n_reads;
+    if (n == 0) return CRAMGPU_OK;
+    if (!in->pos || !in->flag || !in->mapq || !in->name_off || !in->cigar_off || !in->read_off || !in->bases || !in->quals || !d_status ||
+        (in->tags && !in->tag_off))
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    Carver cv;
+    const size_t o_size = cv.take(4 * n), o_off = cv.take(8 * (n + 1)), o_tiles = cv.take(8 * (n / SCAN_TILE + 2));
+    if (int rc = pool_reserve(ctx, ctx->bam_pk_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->bam_pk_scratch.p;
+    PackArgs a;
+    memset(&a, 0, sizeof a);
+    a.in = *in; a.size = (uint32_t *)(S + o_size); a.rec_off = (const uint64_t *)(S + o_off); a.status = d_status;
+    LAUNCH(ctx, st, "k_bam_size", k_bam_size<<<(uint32_t)((n + 127) / 128), 128, 0, st>>>(a));
+    if (int rc = scan_sizes(ctx, a.size, n, (uint64_t *)(S + o_off), (uint64_t *)(S + o_tiles), st)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_bam, &ctx->pin_bam_cap, 64)) return rc;
+    CUDA_TRY(ctx, cudaMemcpyAsync(ctx->pin_bam, S + o_off + 8 * n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t total = *(const uint64_t *)ctx->pin_bam;
+    if (int rc = pool_reserve(ctx, ctx->bam_out, total + 16)) return rc;
+    a.out = (uint8_t *)ctx->bam_out.p;
+    LAUNCH(ctx, st, "k_bam_write", k_bam_write<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    *d_bam = a.out; *bam_len = total; *d_rec_off = (uint64_t *)(S + o_off);
+    return CRAMGPU_OK;
+}
+
+// ---------------------------------------------------------------------------------------------- BAM records: unpack
+namespace {
+
+struct UnpackArgs {
+    const uint8_t *bam;
+    const uint64_t *rec_off;
+    uint64_t n;
+    uint32_t *sz;                  // [4][n]: name bytes, cigar elements, bases, tag bytes
+    const uint64_t *name_off, *cigar_off, *read_off, *tag_off;      // write pass
+    int32_t *ref_id, *pos, *mate_ref_id, *mate_pos, *tlen;
+    uint16_t *flag, *bin;
+    uint8_t *mapq, *rflags, *names, *bases, *quals, *tags;
+    uint32_t *cigar;
+    int32_t *status;
+};
+
+__device__ __forceinline__ uint32_t get_le32(const uint8_t *p) { return p[0] | (p[1] << 8) | (p[2] << 16) | ((uint32_t)p[3] << 24); }
+__device__ __forceinline__ uint32_t get_le16(const uint8_t *p) { return p[0] | (p[1] << 8); }
+
+__global__ void __launch_bounds__(128) k_bam_scan(UnpackArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 128 + threadIdx.x;
+    if (r >= a.n) return;
+    const uint64_t o = a.rec_off[r], len = a.rec_off[r + 1] - o;
+    uint32_t lname = 0, ncig = 0, lseq = 0, ltag = 0;
+    int32_t st = CRAMGPU_ERR_CORRUPT;
+    if (len >= 36) {
+        const uint8_t *p = a.bam + o;
+        const uint64_t bs = get_le32(p);
+        lname = p[12]; ncig = get_le16(p + 16); lseq = get_le32(p + 20);
+        const uint64_t fixed = 32ull + lname + 4ull * ncig + ((uint64_t)lseq + 1) / 2 + lseq;
+        if (bs + 4 == len && lname >= 1 && fixed <= bs) { ltag = (uint32_t)(bs - fixed); lname -= 1; st = CRAMGPU_OK; }
+        else { lname = ncig = lseq = 0; }
+    }
+    a.sz[r] = lname; a.sz[a.n + r] = ncig; a.sz[2 * a.n + r] = lseq; a.sz[3 * a.n + r] = ltag;
+    a.status[r] = st;
+}
+
+__global__ void __launch_bounds__(128) k_bam_unpack(UnpackArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (r >= a.n) return;
+    const uint32_t lane = threadIdx.x & 31;
+    const uint8_t *p = a.bam + a.rec_off[r];
+    const bool ok = a.status[r] == CRAMGPU_OK;
+    const uint32_t lname = (uint32_t)(a.name_off[r + 1] - a.name_off[r]), ncig = (uint32_t)(a.cigar_off[r + 1] - a.cigar_off[r]);
+    const uint32_t lseq = (uint32_t)(a.read_off[r + 1] - a.read_off[r]), ltag = (uint32_t)(a.tag_off[r + 1] - a.tag_off[r]);
+    const uint8_t *nm = p + 36, *cg = nm + lname + 1, *sq = cg + 4 * ncig, *ql = sq + (lseq + 1) / 2, *tg = ql + lseq;
+    if (lane == 0) {
+        if (ok) {
+            a.ref_id[r] = (int32_t)get_le32(p + 4); a.pos[r] = (int32_t)get_le32(p + 8) + 1; a.mapq[r] = p[13]; a.bin[r] = (uint16_t)get_le16(p + 14);
+            a.flag[r] = (uint16_t)get_le16(p + 18); a.mate_ref_id[r] = (int32_t)get_le32(p + 24); a.mate_pos[r] = (int32_t)get_le32(p + 28) + 1;
+            a.tlen[r] = (int32_t)get_le32(p + 32);
+            a.rflags[r] = (uint8_t)((lseq == 0 ? CRAMGPU_RF_NO_BASES : 0u) | ((lseq == 0 || ql[0] == 0xFF) ? CRAMGPU_RF_NO_QUALS : 0u));
+        } else {
+            a.ref_id[r] = -1; a.pos[r] = 0; a.mapq[r] = 0; a.bin[r] = 0; a.flag[r] = 4; a.mate_ref_id[r] = -1; a.mate_pos[r] = 0; a.tlen[r] = 0;
+            a.rflags[r] = CRAMGPU_RF_NO_BASES | CRAMGPU_RF_NO_QUALS;
+        }
+    }
+    if (!ok) return;
+    uint8_t *on = a.names + a.name_off[r];
+    for (uint32_t k = lane; k < lname; k += 32) on[k] = nm[k];
+    uint32_t *oc = a.cigar + a.cigar_off[r];
+    for (uint32_t k = lane; k < ncig; k += 32) oc[k] = get_le32(cg + 4 * k);
+    uint8_t *ob = a.bases + a.read_off[r], *oq = a.quals + a.read_off[r];
+    for (uint32_t k = lane; k < lseq; k += 32) {
+        const uint32_t ny = (sq[k >> 1] >> ((k & 1) ? 0 : 4)) & 15u;
+        ob[k] = (uint8_t)"=ACMGRSVTWYHKDBN"[ny];
+        oq[k] = ql[k];
+    }
+    uint8_t *ot = a.tags + a.tag_off[r];
+    for (uint32_t k = lane; k < ltag; k += 32) ot[k] = tg[k];
+}
+
+}  // namespace
+
+extern "C" int cramgpu_bam_unpack_dev(cramgpu_ctx *ctx, const uint8_t *d_bam, const uint64_t *d_rec_off, uint64_t n_reads,
+                                      cramgpu_bam_records *out, int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    memset(out, 0, sizeof *out);
+    const uint64_t n = n_reads;
+    if (n == 0) return CRAMGPU_OK;
+    if (!d_bam || !d_rec_off || !d_status) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    Carver cv;
+    const size_t o_sz = cv.take(16 * n), o_tiles = cv.take(8 * (n / SCAN_TILE + 2));
+    size_t o_off[4];
+    for (int k = 0; k < 4; k++) o_off[k] = cv.take(8 * (n + 1));
+    const size_t o_i32 = cv.take(20 * n), o_u16 = cv.take(4 * n), o_u8 = cv.take(2 * n);
+    if (int rc = pool_reserve(ctx, ctx->bam_unp_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->bam_unp_scratch.p;
+    UnpackArgs a;
+    memset(&a, 0, sizeof a);
+    a.bam = d_bam; a.rec_off = d_rec_off; a.n = n; a.sz = (uint32_t *)(S + o_sz); a.status = d_status;
+    LAUNCH(ctx, st, "k_bam_scan", k_bam_scan<<<(uint32_t)((n + 127) / 128), 128, 0, st>>>(a));
+    for (int k = 0; k < 4; k++)
+        if (int rc = scan_sizes(ctx, a.sz + (size_t)k * n, n, (uint64_t *)(S + o_off[k]), (uint64_t *)(S + o_tiles), st)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_bam, &ctx->pin_bam_cap, 64)) return rc;
+    uint64_t *tot = (uint64_t *)ctx->pin_bam;
+    for (int k = 0; k < 4; k++) CUDA_TRY(ctx, cudaMemcpyAsync(tot + k, S + o_off[k] + 8 * n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t t_name = tot[0], t_cig = tot[1], t_seq = tot[2], t_tag = tot[3];
+    Carver co;
+    const size_t q_names = co.take(t_name + 16), q_cig = co.take(4 * t_cig + 16), q_bases = co.take(t_seq + 16), q_quals = co.take(t_seq + 16),
+                 q_tags = co.take(t_tag + 16);
+    if (int rc = pool_reserve(ctx, ctx->bam_unp, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->bam_unp.p;
+    a.name_off = (const uint64_t *)(S + o_off[0]); a.cigar_off = (const uint64_t *)(S + o_off[1]);
+    a.read_off = (const uint64_t *)(S + o_off[2]); a.tag_off = (const uint64_t *)(S + o_off[3]);
+    int32_t *i32 = (int32_t *)(S + o_i32);
+    a.ref_id = i32; a.pos = i32 + n; a.mate_ref_id = i32 + 2 * n; a.mate_pos = i32 + 3 * n; a.tlen = i32 + 4 * n;
+    a.flag = (uint16_t *)(S + o_u16); a.bin = a.flag + n; a.mapq = S + o_u8; a.rflags = S + o_u8 + n;
+    a.names = O + q_names; a.cigar = (uint32_t *)(O + q_cig); a.bases = O + q_bases; a.quals = O + q_quals; a.tags = O + q_tags;
+    LAUNCH(ctx, st, "k_bam_unpack", k_bam_unpack<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
+    out->n_reads = n; out->ref_id = a.ref_id; out->pos = a.pos; out->mate_ref_id = a.mate_ref_id; out->mate_pos = a.mate_pos; out->tlen = a.tlen;
+    out->flag = a.flag; out->bin = a.bin; out->mapq = a.mapq; out->rflags = a.rflags; out->names = a.names; out->name_off = a.name_off;
+    out->cigar = a.cigar; out->cigar_off = a.cigar_off; out->bases = a.bases; out->quals = a.quals; out->read_off = a.read_off;
+    out->tags = a.tags; out->tag_off = a.tag_off; out->names_len = t_name; out->cigar_len = t_cig; out->bases_len = t_seq; out->tags_len = t_tag;
+    return CRAMGPU_OK;
+}

@@ -442,3 +442,21 @@ def mate_link(flag, names, pos, mate_ref_id, mate_pos, tlen, read_off, f_op, f_v
     cf = np.zeros(max(n, 1), np.uint8); nf = np.zeros(max(n, 1), np.int32)
     ctx.check(ctx.lib.cramgpu_mate_link(ctx.handle, C.byref(I), _vp(cf), _vp(nf)))
     return cf[:n], nf[:n]
+
+
+# ---------------------------------------------------------------------------------------------- CIGAR rebuild + BAM records (device resident)
+class BamRecords(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('ref_id', C.c_void_p), ('pos', C.c_void_p), ('mate_ref_id', C.c_void_p), ('mate_pos', C.c_void_p),
+                ('tlen', C.c_void_p), ('flag', C.c_void_p), ('bin', C.c_void_p), ('mapq', C.c_void_p), ('rflags', C.c_void_p),
+                ('names', C.c_void_p), ('name_off', C.c_void_p), ('cigar', C.c_void_p), ('cigar_off', C.c_void_p), ('bases', C.c_void_p),
+                ('quals', C.c_void_p), ('read_off', C.c_void_p), ('tags', C.c_void_p), ('tag_off', C.c_void_p),
+                ('names_len', C.c_uint64), ('cigar_len', C.c_uint64), ('bases_len', C.c_uint64), ('tags_len', C.c_uint64)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_cigar_rebuild_dev': (C.c_int, [C.c_void_p, C.c_uint64] + [C.c_void_p] * 7 + [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                                                                         C.POINTER(C.c_uint64), C.c_void_p]),
+    'cramgpu_bam_unpack_dev': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(BamRecords), C.c_void_p, C.c_void_p]),
+    'cramgpu_bam_pack_dev': (C.c_int, [C.c_void_p, C.POINTER(BamRecords), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p),
+                                       C.c_void_p, C.c_void_p]),
+})

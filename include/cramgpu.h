@@ -598,6 +598,50 @@ typedef struct cramgpu_mate_in {
 int cramgpu_mate_link(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *mate_cf, int32_t *nf);
 int cramgpu_mate_link_dev(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *d_mate_cf, int32_t *d_nf, void *stream);
 
+/* ------------------------------------------------------------------ CIGAR rebuild and BAM records
+ *
+ * Device-resident entry points: every pointer is DEVICE memory; results are device memory owned by the context, valid until
+ * the next call of the same name on it.  Each call synchronises `stream` once (the result buffers are sized from totals).
+ *
+ * cramgpu_cigar_rebuild_dev   Cram2SamRecordFactory.getCigar2 [Cram2SamRecordFactory.java:119-225]: the CIGAR of every record
+ *     from its read features ('X' 'B' -> M 1, 'i' -> I 1, 'I' 'S' -> their f_aux bases, 'D' 'N' 'H' 'P' -> f_val; gaps are M;
+ *     quality-score features are passed over), BAM-packed (length << 4 | op of MIDNSHP).  A record with the unmapped flag
+ *     gets no elements (Cram2SamRecordFactory.create sets "*", [:68-69]).  Note that '=' / 'X' of the original come back as M.
+ *
+ * cramgpu_bam_unpack_dev      a stripe of raw BAM records (each with its block_size prefix, back to back, as
+ *     paralell/Bam_OBA_Supplier.java:45-82 cuts them; rec_off[i] = byte offset of record i, rec_off[n] = stripe length)
+ *     -> structure of arrays: pos / mate_pos 1-based, bases as upper-case ASCII of "=ACMGRSVTWYHKDBN", names without the NUL,
+ *     rflags = CRAMGPU_RF_NO_QUALS when the first quality byte is 0xFF (BAMRecord: missing qualities), CRAMGPU_RF_NO_BASES when
+ *     l_seq = 0.  The arrays feed cramgpu_features_encode_dev (cramgpu_reads), cramgpu_mate_link_dev, cramgpu_host_series_pack_dev
+ *     and cramgpu_slice_headers_dev as they are.  status[i] = CRAMGPU_ERR_CORRUPT for a record whose lengths do not add up to
+ *     its block_size (Bam_OBA_Supplier: "Invalid record length" below 32); such a record comes out empty.
+ *
+ * cramgpu_bam_pack_dev        the inverse, laid out as cramtools' flat-buffer BAM writer does
+ *     (encoding/reader/BAMRecordView.java:70-241): block_size refID pos-1 l_read_name mapq bin n_cigar flag l_seq next_refID
+ *     next_pos-1 tlen name NUL cigar seq (4 bit, high nybble first) qual tags; bin = SAMRecord.computeIndexingBin
+ *     [SAMRecord.java:1524-1531] (`in->bin` is ignored); CRAMGPU_RF_NO_QUALS -> l_seq bytes 0xFF [BAMRecordView.java:176-180].
+ *     A base outside "=ACMGRSVTWYHKDBN" (either case) and '.': status[i] = CRAMGPU_ERR_ARG (IllegalArgumentException,
+ *     [:405-407]), the nybble is written as N.
+ */
+typedef struct cramgpu_bam_records {
+    uint64_t n_reads;
+    const int32_t *ref_id, *pos, *mate_ref_id, *mate_pos, *tlen;
+    const uint16_t *flag, *bin;
+    const uint8_t *mapq, *rflags;
+    const uint8_t *names;   const uint64_t *name_off;    /* [n_reads+1] */
+    const uint32_t *cigar;  const uint64_t *cigar_off;   /* [n_reads+1] */
+    const uint8_t *bases, *quals; const uint64_t *read_off;   /* [n_reads+1] */
+    const uint8_t *tags;    const uint64_t *tag_off;     /* [n_reads+1]; tags may be NULL on input: no tags */
+    uint64_t names_len, cigar_len, bases_len, tags_len;
+} cramgpu_bam_records;
+int cramgpu_cigar_rebuild_dev(cramgpu_ctx *ctx, uint64_t n_reads, const uint16_t *d_flag, const uint64_t *d_read_off,
+                              const uint64_t *d_feat_off, const uint8_t *d_f_op, const int32_t *d_f_pos, const int32_t *d_f_val,
+                              const int32_t *d_f_aux, uint32_t **d_cigar, uint64_t **d_cigar_off, uint64_t *cigar_len, void *stream);
+int cramgpu_bam_unpack_dev(cramgpu_ctx *ctx, const uint8_t *d_bam, const uint64_t *d_rec_off, uint64_t n_reads,
+                           cramgpu_bam_records *out, int32_t *d_status, void *stream);
+int cramgpu_bam_pack_dev(cramgpu_ctx *ctx, const cramgpu_bam_records *in, uint8_t **d_bam, uint64_t *bam_len, uint64_t **d_rec_off,
+                         int32_t *d_status, void *stream);
+
 /* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
  *
  * Containers are independent and are dealt round-robin: the container with global ordinal g is converted by

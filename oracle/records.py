@@ -528,3 +528,115 @@ def set_mate_info(flag, names, ref_id, pos, mate_ref_id, mate_pos, tlen, aln_end
             det[i] = True; down[i] = False; nf[i] = -1
     cf = np.array([(2 if det[i] else 0) | (4 if down[i] else 0) for i in range(n)], np.uint8)
     return cf, np.array(nf, np.int32)
+
+
+# ---------------------------------------------------------------------------------------------- CIGAR rebuild + BAM records
+_CONSUMES_READ = {'M': True, 'I': True, 'S': True, '=': True, 'X': True, 'D': False, 'N': False, 'H': False, 'P': False}
+
+
+def cigar_from_features(features, read_length):
+    """Cram2SamRecordFactory.getCigar2 [Cram2SamRecordFactory.java:119-225].  features: [(op char, 1-based position, length)] in
+    record order, length = bases of an 'I' / 'S', the value of 'D' 'N' 'H' 'P' (ignored for 'i' 'X' 'B'); any other operator
+    (quality scores) is skipped.  -> [(length, op char)]"""
+    if not features:
+        return [(read_length, 'M')]
+    out = []
+    last_op, last_len, last_pos = 'M', 0, 1
+    for op, pos, ln in features:
+        gap = pos - (last_pos + last_len)
+        if gap > 0:
+            if last_op != 'M':
+                out.append((last_len, last_op)); last_pos += last_len; last_len = gap
+            else:
+                last_len += gap
+            last_op = 'M'
+        if op in ('I', 'S'):
+            co, rl = ('I' if op == 'I' else 'S'), ln
+        elif op == 'H':
+            co, rl = 'H', ln
+        elif op == 'i':
+            co, rl = 'I', 1
+        elif op == 'D':
+            co, rl = 'D', ln
+        elif op == 'N':
+            co, rl = 'N', ln
+        elif op == 'P':
+            co, rl = 'P', ln
+        elif op in ('X', 'B'):
+            co, rl = 'M', 1
+        else:
+            continue
+        if last_op != co:
+            if last_len > 0:
+                out.append((last_len, last_op))
+            last_op, last_len, last_pos = co, rl, pos
+        else:
+            last_len += rl
+        if not _CONSUMES_READ[co]:
+            last_pos -= rl
+    if last_op != 'M':
+        out.append((last_len, last_op))
+        if read_length >= last_pos + last_len:
+            out.append((read_length - (last_len + last_pos) + 1, 'M'))
+    elif read_length == 0 or read_length > last_pos - 1:
+        out.append((last_len, 'M') if read_length == 0 else (read_length - last_pos + 1, 'M'))
+    return out if out else [(read_length, 'M')]
+
+
+def reg2bin(beg, end):
+    """GenomicIndexUtil.regionToBin [GenomicIndexUtil.java:63-70]"""
+    end -= 1
+    for shift, base in ((14, 4681), (17, 585), (20, 73), (23, 9), (26, 1)):
+        if beg >> shift == end >> shift:
+            return base + (beg >> shift)
+    return 0
+
+
+def indexing_bin(pos, flag, cigar):
+    """SAMRecord.computeIndexingBin [SAMRecord.java:1524-1531] with getAlignmentEnd [:591-598]; cigar = [(len, op)]"""
+    beg = pos - 1
+    end = 0 if flag & 4 else pos + sum(l for l, o in cigar if o in 'MDN=X') - 1
+    if end <= 0:
+        end = beg + 1
+    return reg2bin(beg, end)
+
+
+_NYBBLE = {c: i for i, c in enumerate('=ACMGRSVTWYHKDBN')}
+_NYBBLE.update({c.lower(): i for c, i in list(_NYBBLE.items()) if c != '='})
+_NYBBLE['.'] = 15
+
+
+def bam_record(ref_id, pos, name, mapq, flag, cigar, mate_ref_id, mate_pos, tlen, bases, quals, tags=b''):
+    """one BAM record as BAMRecordView lays it out (src/main/java/htsjdk/samtools/cram/encoding/reader/BAMRecordView.java:70-241):
+    block_size refID pos-1 l_read_name mapq bin n_cigar flag l_seq next_refID next_pos-1 tlen name\\0 cigar seq(4 bit) qual tags;
+    quals == b'' -> l_seq bytes 0xFF.  A base outside =ACMGRSVTWYHKDBN (any case) or '.': ValueError (IllegalArgumentException)."""
+    import struct
+    ops = 'MIDNSHP=X'
+    body = struct.pack('<iiBBHHHiiii', ref_id, pos - 1, len(name) + 1, mapq & 0xFF, indexing_bin(pos, flag, cigar) & 0xFFFF, len(cigar) & 0xFFFF,
+                       flag & 0xFFFF, len(bases), mate_ref_id, mate_pos - 1, tlen)
+    body += bytes(name) + b'\0' + b''.join(struct.pack('<I', (l << 4) | ops.index(o)) for l, o in cigar)
+    nyb = []
+    for b in bytes(bases):
+        if chr(b) not in _NYBBLE:
+            raise ValueError('Bad  byte passed to charToCompressedBase: %d' % b)
+        nyb.append(_NYBBLE[chr(b)])
+    if len(nyb) & 1:
+        nyb.append(0)
+    body += bytes((nyb[i] << 4) | nyb[i + 1] for i in range(0, len(nyb), 2))
+    body += bytes(quals) if len(quals) else b'\xff' * len(bases)
+    body += bytes(tags)
+    return struct.pack('<i', len(body)) + body
+
+
+def bam_parse(rec):
+    """the inverse, for one record with its block_size prefix -> dict (pos / mate_pos 1-based, bases ASCII upper case)"""
+    import struct
+    bs, ref, pos, lname, mapq, bin_, ncig, flag, lseq, mref, mpos, tlen = struct.unpack('<iiiBBHHHiiii', rec[:36])
+    o = 36
+    name = rec[o:o + lname - 1]; o += lname
+    cig = [((w >> 4), 'MIDNSHP=X'[w & 15]) for w in struct.unpack('<%dI' % ncig, rec[o:o + 4 * ncig])]; o += 4 * ncig
+    sq = rec[o:o + (lseq + 1) // 2]; o += (lseq + 1) // 2
+    bases = bytes(ord('=ACMGRSVTWYHKDBN'[(sq[i >> 1] >> (0 if i & 1 else 4)) & 15]) for i in range(lseq))
+    quals = rec[o:o + lseq]; o += lseq
+    return dict(block_size=bs, ref_id=ref, pos=pos + 1, name=name, mapq=mapq, bin=bin_, flag=flag, cigar=cig, mate_ref_id=mref,
+                mate_pos=mpos + 1, tlen=tlen, bases=bases, quals=quals, tags=rec[o:4 + bs])

@@ -149,3 +149,40 @@ def test_mate_linking_matches_jar(G):
         assert [int(x) for x in nf] == [s['nf'] for s in sc], c['tag']
         linked += int((cf == 4).sum())
     assert linked == 10
+
+
+def _feat_triples(feats):
+    """golden feature json -> (op, pos, length) as cigar_from_features takes them"""
+    out = []
+    for f in feats or []:
+        op = f[0]
+        ln = len(base64.b64decode(f[2])) if op in ('S', 'I') else f[2] if op in ('D', 'N', 'H', 'P') else 1
+        out.append((op, f[1], ln))
+    return out
+
+
+def test_cigar_rebuild_and_bam_records_match_jar(G):
+    """Cram2SamRecordFactory.getCigar2 over the features the jar's reader read back, and the BAM record cramtools'
+    BAMRecordView lays out for every record (bin, 4-bit bases, missing qualities as 0xFF, RG tag)"""
+    g, ref, conts = G
+    ops = set()
+    for c, rd, series in conts:
+        for i, (r, rb, sc) in enumerate(zip(c['reads'], c['read_back'], c['scalars'])):
+            cig = orec.cigar_from_features(_feat_triples(rb['features']), rb['read_length'])
+            txt = ''.join('%d%s' % e for e in cig)
+            assert txt == rb['cigar2'], (c['tag'], i, txt, rb['cigar2'])
+            ops.update(o for _, o in cig)
+            unm = bool(r['flag'] & 4)
+            paired = bool(r['flag'] & 1)
+            rec = orec.bam_record(r['ref_id'], r['pos'], r['name'].encode('latin-1'), r['mapq'], r['flag'], [] if unm else cig,
+                                  sc['mate_seq_id'] if paired else -1, sc['mate_start'] if paired else 0, sc['tlen'],
+                                  base64.b64decode(r['bases']) if r['bases'] is not None else b'',
+                                  base64.b64decode(r['quals']) if r['quals'] is not None else b'', base64.b64decode(rb['bam_tags']))
+            assert rec == base64.b64decode(rb['bam']), (c['tag'], i)
+            back = orec.bam_parse(rec)
+            assert back['pos'] == r['pos'] and back['flag'] == r['flag'] and back['bin'] == rb['bam_bin']
+            if r['bases'] is not None:
+                assert back['bases'] == base64.b64decode(r['bases']).upper().replace(b'.', b'N')
+    assert ops >= set('MIDNSHP')
+    with pytest.raises(ValueError):
+        orec.bam_record(0, 1, b'x', 0, 0, [(1, 'M')], -1, 0, 0, b'J', b'#')
