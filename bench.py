@@ -50,9 +50,9 @@ def measured_peaks():
 
 
 def ncu_traffic(kernel, n_cont):
-    """DRAM bytes of one launch of `kernel` from the committed ncu capture (profiles/r1_traffic.json), if it was taken at this size"""
+    """DRAM bytes of one launch of `kernel` from the committed ncu capture (profiles/r2_traffic.json), if it was taken at this size"""
     try:
-        with open(os.path.join(ROOT, 'profiles', 'r1_traffic.json')) as f:
+        with open(os.path.join(ROOT, 'profiles', 'r2_traffic.json')) as f:
             t = json.load(f).get(kernel)
         if t and int(t['containers_per_gpu']) == int(n_cont):
             return int(t['dram_bytes_read']) + int(t['dram_bytes_write'])
@@ -718,7 +718,7 @@ def run_ours(args):
     # contexts of the end-to-end leg: 8 on one GPU (five calls per step, each holding the host for 100+ ms: more contexts than
     # calls keep every stage busy); fewer per GPU when several ranks share the host's cores and page-locked memory
     e2e_depth = args.e2e_pipeline if args.e2e_pipeline > 0 else (8 if world == 1 else 6 if world == 2 else 4)
-    e2e = run_e2e(args, ref, rd, nu, n_e2e, world, barrier, e2e_depth, comp_hint, local)
+    e2e = None if args.no_e2e else run_e2e(args, ref, rd, nu, n_e2e, world, barrier, e2e_depth, comp_hint, local)
 
     if rank == 0:
         value = n_reads * world / (ms * 1e-3)
@@ -1118,6 +1118,7 @@ def main():
     ap.add_argument('--e2e-pipeline', type=int, default=0, help='contexts of the end-to-end leg taking consecutive steps in turn (0 = 8 on one GPU, 6 on two, 4 beyond)')
     ap.add_argument('--no-unpack', action='store_true', help='decode side: take the read features from the encoder instead of unpacking the series (row P)')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    ap.add_argument('--no-e2e', action='store_true', help='skip the end-to-end leg (profiling runs under ncu only: the line then has no e2e number)')
     ap.add_argument('--no-configs', action='store_true', help='skip the short runs of the other north_star configurations (quality models, 20 containers, fixed total)')
     ap.add_argument('--sweep-kinds', default='', help='--sweep: only these kinds (comma separated: QS,BA,RN,ITF8)')
     ap.add_argument('--sweep', action='store_true', help='BASELINE configs[1]: the rANS block sweep instead of the step benchmark')
