@@ -811,9 +811,16 @@ class E2EContext(object):
         self.back_ptr = np.ascontiguousarray(bp.reshape(-1))
         self.back_len = np.zeros(nblk, np.uint32)
         self.qs_slot = dslot[np.arange(n_cont) * NB].astype(np.int64)             # where container c's QS lands in d_back
+        self.ba_slot = dslot[np.arange(n_cont) * NB + 1].astype(np.int64)
         self.rfl = np.ones(n_reads, np.uint8)
-        self.rba = np.full(n_reads, 0xFFFFFFFFFFFFFFFF, np.uint64)
-        self.rq_new = np.zeros(n_reads, np.uint64)
+        # series table of the decode side (row P on the device): absolute addresses -- QS / BA where the block codec left them
+        # in device memory, the series the Java host inflates (FN FC FP BS DL SC RS HC PD MQ) in host memory
+        self.s_addr = np.zeros((n_cont, 12), np.uint64); self.s_len = np.zeros((n_cont, 12), np.uint64)
+        SR = self.SR = rec.Series()
+        SR.n_reads = n_reads; SR.n_containers = n_cont; SR.cont_off = inp['cont_off'].ctypes.data_as(u64p); SR.streams = None; SR.streams_len = 0
+        SR.stream_off = self.s_addr.ctypes.data_as(u64p); SR.stream_len = self.s_len.ctypes.data_as(u64p)
+        SR.read_off = vp(inp['a']['read_off'].ctypes.data); SR.rflags = vp(self.rfl.ctypes.data)
+        self.U = rec.Features(); self.u_status = np.zeros(n_cont, np.int32); self.u_mapq = np.zeros(n_reads, np.uint8)
         self.o_b = pinned_empty(n_reads * READ_LEN, np.uint8); self.o_q = pinned_empty(n_reads * READ_LEN, np.uint8)
         self.o_s = np.empty(n_reads, np.uint8); self.o_t = np.empty(n_reads, np.int32)
         N = self.N = rec.NormIn()
@@ -821,11 +828,12 @@ class E2EContext(object):
         N.cont_off = inp['cont_off'].ctypes.data_as(u64p); N.win_off = inp['win_off'].ctypes.data_as(u64p); N.win_len = inp['win_len'].ctypes.data_as(u64p)
         N.win_start0 = inp['win_s0'].ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(inp['ref'].ctypes.data); N.ref_total = inp['ref'].size
         N.pos = vp(inp['a']['pos'].ctypes.data); N.read_off = vp(inp['a']['read_off'].ctypes.data); N.rflags = vp(self.rfl.ctypes.data)
-        N.ba = vp(self.d_back.data_ptr()); N.read_ba_off = vp(self.rba.ctypes.data); N.qs = vp(self.d_back.data_ptr())
+        N.ba = None; N.qs = None                        # absolute device addresses in the unpacked read_qs_off / read_ba_off
         self.ms = {'features_encode_resident': 0.0, 'host_series_pack_resident': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0,
-                   'normalize_decode': 0.0, 'host_glue': 0.0}
+                   'features_unpack_resident': 0.0, 'normalize_decode': 0.0, 'host_glue': 0.0}
         self.h2d = self.d2h = 0
-        self.stages = (self.stage_features, self.stage_host_series, self.stage_rans_encode, self.stage_rans_decode, self.stage_normalize)
+        self.stages = (self.stage_features, self.stage_host_series, self.stage_rans_encode, self.stage_rans_decode, self.stage_unpack,
+                       self.stage_normalize)
 
     def step(self, locks=None):
         for k, stage in enumerate(self.stages):
@@ -839,7 +847,9 @@ class E2EContext(object):
         """reads (host) -> the small series and the feature arrays (host); QS / BA stay on the device"""
         ctx, inp, F, D = self.ctx, self.inp, self.F, self.D
         t0 = time.perf_counter()
-        ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(inp['R']), None, -1, inp['host_series'], C.byref(F), C.byref(D)))
+        # the feature arrays stay on the device: the host hands the series to the block layer and never looks at them
+        ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(inp['R']), None, -1, inp['host_series'] | self.rec.FEATURES_ON_DEVICE_ONLY,
+                                                           C.byref(F), C.byref(D)))
         t1 = time.perf_counter()
         self.ms['features_encode_resident'] += (t1 - t0) * 1e3
 
@@ -886,28 +896,39 @@ class E2EContext(object):
                                                     self.back_len.ctypes.data_as(u32p), self.status.ctypes.data_as(i32p)))
         self.ms['rans_decode_batch'] += (time.perf_counter() - t3) * 1e3
 
-    def stage_normalize(self):
-        """records as CramRecordReader would hand them over + the decoded QS / BA on the device -> bases and qualities (host)"""
-        from cramtools_b200._lib import u8p, u64p, i32p
-        ctx, inp, F, N = self.ctx, self.inp, self.F, self.N
-        n_reads = inp['n_reads']
-        vp = C.c_void_p
+    def stage_unpack(self):
+        """row P: the series as the decode side holds them (small ones in host memory, QS / BA on the device) -> read features,
+        left on the device"""
+        from cramtools_b200._lib import u8p, i32p
+        ctx, inp, F = self.ctx, self.inp, self.F
         t4 = time.perf_counter()
-        # score arrays sit inside the decoded QS series: per read, its offset there (the encoder's offset, moved to the QS slot)
-        rq = np.ctypeslib.as_array(C.cast(F.read_qs_off, u64p), (n_reads,))
-        delta = (self.qs_slot - self.soff[:, inp['KQS']].astype(np.int64)).astype(np.int64)
-        np.add(rq.view(np.int64).reshape(inp['n_cont'], READS_PER_CONTAINER), delta[:, None],
-               out=self.rq_new.view(np.int64).reshape(inp['n_cont'], READS_PER_CONTAINER))
-        N.read_qs_off = vp(self.rq_new.ctypes.data)
-        N.matrix = F.matrix; N.feat_off = F.feat_off; N.f_op = F.f_op; N.f_pos = F.f_pos; N.f_val = F.f_val; N.f_aux = F.f_aux
-        N.payload = F.payload; N.payload_len = F.payload_len
+        KQS, KBA = inp['KQS'], inp['KBA']
+        sa = self.s_addr
+        sa[:] = np.uint64(F.streams) + self.soff                       # F.streams: the host copy of the small series (encode side)
+        sa[:, KQS] = np.uint64(self.d_back.data_ptr()) + self.qs_slot.astype(np.uint64)
+        sa[:, KBA] = np.uint64(self.d_back.data_ptr()) + self.ba_slot.astype(np.uint64)
+        self.s_len[:] = self.slen
         t5 = time.perf_counter()
+        ctx.check(ctx.lib.cramgpu_features_unpack_resident(ctx.handle, C.byref(self.SR), C.byref(self.U), self.u_mapq.ctypes.data_as(u8p),
+                                                           self.u_status.ctypes.data_as(i32p)))
+        self.ms['features_unpack_resident'] += (time.perf_counter() - t5) * 1e3; self.ms['host_glue'] += (t5 - t4) * 1e3
+
+    def stage_normalize(self):
+        """records as CramRecordReader would hand them over (positions, lengths; the features and the decoded QS / BA are on the
+        device) -> bases and qualities (host)"""
+        from cramtools_b200._lib import u8p, u64p, i32p
+        ctx, inp, F, N, U = self.ctx, self.inp, self.F, self.N, self.U
+        n_reads = inp['n_reads']
+        t5 = time.perf_counter()
+        N.read_qs_off = U.read_qs_off; N.read_ba_off = U.read_ba_off
+        N.matrix = F.matrix; N.feat_off = U.feat_off; N.f_op = U.f_op; N.f_pos = U.f_pos; N.f_val = U.f_val; N.f_aux = U.f_aux
+        N.payload = U.payload; N.payload_len = U.payload_len
         ctx.check(ctx.lib.cramgpu_normalize_decode(ctx.handle, C.byref(N), self.o_b.ctypes.data_as(u8p), self.o_q.ctypes.data_as(u8p),
                                                    self.o_s.ctypes.data_as(u8p), self.o_t.ctypes.data_as(i32p)))
         t6 = time.perf_counter()
-        self.ms['normalize_decode'] += (t6 - t5) * 1e3; self.ms['host_glue'] += (t5 - t4) * 1e3
+        self.ms['normalize_decode'] += (t6 - t5) * 1e3
         # bytes that crossed the bus in this step
-        a, nf, nb = inp['a'], int(F.n_feat), n_reads * READ_LEN
+        a, nb = inp['a'], n_reads * READ_LEN
         KQS, KBA = inp['KQS'], inp['KBA']
         small = int(self.slen.sum() - self.slen[:, KQS].sum() - self.slen[:, KBA].sum())
         ex_bytes = self.ex_bytes
@@ -915,10 +936,11 @@ class E2EContext(object):
         self.h2d = int(2 * nb + inp['ref'].size + a['read_off'].nbytes + a['cigar_off'].nbytes + a['cigar'].nbytes + 7 * n_reads      # reads
                        + (2 + 4 + 8 + 4) * n_reads                                                                        # record fields: flag, pos, read_off, read group
                        + comp_bytes                                                                                       # compressed blocks, decode side
-                       + inp['ref'].size + 37 * n_reads + 17 * nf + int(F.payload_len))                                   # records + features, decode side
-        self.d2h = int(17 * nf + 25 * n_reads + int(F.payload_len) + small                                                # features, tables, small series
+                       + small                                                                                            # the series the host inflated, for row P
+                       + inp['ref'].size + (4 + 8 + 1) * n_reads + 8 * (n_reads + 1) + n_reads)                          # decode side: pos, read_off, rflags (twice: unpack, normaliser)
+        self.d2h = int(n_reads + 8 * inp['n_cont'] + small                                                                # force_qs, matrix, small series
                        + self.hs_down                                                                                     # record-field series the host gzips
-                       + comp_bytes + ex_bytes + 2 * nb + 5 * n_reads)
+                       + comp_bytes + ex_bytes + 2 * nb + 5 * n_reads + n_reads)                                          # blocks; bases, qualities, star, status; MAPQ
 
 
 def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device):
@@ -993,8 +1015,9 @@ def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device)
     for ln in lanes:
         for key in ln.ms:
             ln.ms[key] = 0.0
-    # one lock per call: at most one context inside each of the five calls, different calls of different steps overlap
-    locks = [threading.Lock() for _ in range(5)]
+    # one lock per call: at most one context inside each of the six calls, different calls of different steps overlap
+    permits = int(os.environ.get('CRAMGPU_E2E_PERMITS', '2'))      # contexts admitted to one call at a time
+    locks = [threading.Semaphore(permits) for _ in range(6)]
     errs = []
     dev_index = torch.cuda.current_device()
 
@@ -1027,9 +1050,10 @@ def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device)
     calls = {kk: round(sum(ln.ms[kk] for ln in lanes) / k, 2) for kk in lanes[0].ms}
     return {'value': n_reads * world / (ms * 1e-3), 'unit': UNIT, 'h2d_bytes_per_step': lanes[0].h2d, 'd2h_bytes_per_step': lanes[0].d2h,
             'ms_per_step': ms, 'containers_per_gpu': n_cont, 'steps': k, 'contexts': depth, 'calls_ms': calls,
-            'path': 'cramgpu_features_encode_resident -> cramgpu_host_series_pack_resident -> cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_normalize_decode: '
-                    'reads in and compressed blocks + restored bases/qualities out through host buffers, every copy inside the timed '
-                    'region; the rANS-coded series stay on the device between the calls'}
+            'path': 'cramgpu_features_encode_resident (feature arrays stay on the device) -> cramgpu_host_series_pack_resident -> '
+                    'cramgpu_rans_encode_batch -> cramgpu_rans_decode_batch -> cramgpu_features_unpack_resident -> cramgpu_normalize_decode: '
+                    'reads in and compressed blocks + the series the host gzips out; compressed blocks + those series in and restored '
+                    'bases/qualities out; every copy inside the timed region; QS / BA and the read features never leave the device'}
 
 
 # ------------------------------------------------------------------------------------------- configs[1]: block sweep

@@ -76,11 +76,32 @@ void prof_end(cramgpu_ctx *ctx, cudaStream_t st) { cudaEventRecord(ctx->spans.ba
 cudaError_t memcpy_pieces(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind, cudaStream_t st)
 {
     const size_t P = 16u << 20;
-    for (size_t o = 0; o < bytes; o += P) {
-        cudaError_t e = cudaMemcpyAsync((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(P, bytes - o), kind, st);
-        if (e != cudaSuccess) return e;
+    const int WINDOW = 3;
+    if (bytes <= (size_t)(WINDOW + 1) * P) {
+        for (size_t o = 0; o < bytes; o += P) {
+            cudaError_t e = cudaMemcpyAsync((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(P, bytes - o), kind, st);
+            if (e != cudaSuccess) return e;
+        }
+        return cudaSuccess;
     }
-    return cudaSuccess;
+    // A long copy is PACED: at most WINDOW pieces are handed to the copy engine ahead of the one that is moving.  The engine
+    // serves what it has been given in order, so a multi-gigabyte copy enqueued at once makes every other context's copy --
+    // however small -- wait for all of it (measured: the 0.4 GB of compressed blocks of one context waited 60 ms behind the
+    // 3.3 GB of reads of another).  The calling thread waits here instead; the host entry points are synchronous anyway.
+    cudaEvent_t ev[WINDOW];
+    for (int k = 0; k < WINDOW; k++) {
+        cudaError_t e = cudaEventCreateWithFlags(&ev[k], cudaEventDisableTiming | cudaEventBlockingSync);
+        if (e != cudaSuccess) { for (int j = 0; j < k; j++) cudaEventDestroy(ev[j]); return e; }
+    }
+    cudaError_t rc = cudaSuccess;
+    size_t i = 0;
+    for (size_t o = 0; o < bytes && rc == cudaSuccess; o += P, i++) {
+        if (i >= (size_t)WINDOW) rc = cudaEventSynchronize(ev[i % WINDOW]);
+        if (rc == cudaSuccess) rc = cudaMemcpyAsync((uint8_t *)dst + o, (const uint8_t *)src + o, std::min(P, bytes - o), kind, st);
+        if (rc == cudaSuccess) rc = cudaEventRecord(ev[i % WINDOW], st);
+    }
+    for (int k = 0; k < WINDOW; k++) cudaEventDestroy(ev[k]);
+    return rc;
 }
 
 bool host_is_pinned(const void *p)
@@ -225,6 +246,7 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
     if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
+    if (ctx->unp_in.p) cudaFree(ctx->unp_in.p);
     if (ctx->bam_scratch.p) cudaFree(ctx->bam_scratch.p);
     if (ctx->bam_cigar.p) cudaFree(ctx->bam_cigar.p);
     if (ctx->bam_out.p) cudaFree(ctx->bam_out.p);

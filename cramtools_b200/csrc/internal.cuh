@@ -68,6 +68,7 @@ struct cramgpu_ctx {
     DevPool scratch;          // carved anew by every call
     DevPool dev_in, dev_out;  // device staging of the host entry points
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
+    DevPool unp_in;                 // staged host series of cramgpu_features_unpack_resident
     DevPool rec_unp;                // results of cramgpu_features_unpack (its input series may be an encode result in rec_out)
     DevPool hs_scratch, hs_out, hs_in;   // cramgpu_host_series_pack: tables, result, staged inputs of the host variant
     DevPool bam_scratch, bam_cigar, bam_out, bam_unp, bam_pk_scratch, bam_unp_scratch;   // bam.cu: sizes/offsets, rebuilt CIGARs, packed records, unpacked arrays

@@ -2021,12 +2021,16 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     auto down = [&](size_t slot, const void *d, size_t bytes) -> cudaError_t {
         return bytes ? memcpy_pieces(po + so.off[slot], d, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
     };
-    CUDA_TRY(ctx, down(r_op, df.f_op, df.n_feat)); CUDA_TRY(ctx, down(r_pos, df.f_pos, 4 * df.n_feat));
-    CUDA_TRY(ctx, down(r_val, df.f_val, 4 * df.n_feat)); CUDA_TRY(ctx, down(r_aux, df.f_aux, 4 * df.n_feat));
-    CUDA_TRY(ctx, down(r_foff, df.feat_off, 8 * (n + 1))); CUDA_TRY(ctx, down(r_pay, df.payload, df.payload_len));
+    // CRAMGPU_FEATURES_ON_DEVICE_ONLY: a host that hands the series straight to the block layer has no use for the feature arrays
+    const bool arrays = !(dev_out && (host_series & CRAMGPU_FEATURES_ON_DEVICE_ONLY));
+    if (arrays) {
+        CUDA_TRY(ctx, down(r_op, df.f_op, df.n_feat)); CUDA_TRY(ctx, down(r_pos, df.f_pos, 4 * df.n_feat));
+        CUDA_TRY(ctx, down(r_val, df.f_val, 4 * df.n_feat)); CUDA_TRY(ctx, down(r_aux, df.f_aux, 4 * df.n_feat));
+        CUDA_TRY(ctx, down(r_foff, df.feat_off, 8 * (n + 1))); CUDA_TRY(ctx, down(r_pay, df.payload, df.payload_len));
+        CUDA_TRY(ctx, down(r_qso, df.read_qs_off, 8 * n)); CUDA_TRY(ctx, down(r_bao, df.read_ba_off, 8 * n));
+    }
     CUDA_TRY(ctx, down(r_force, df.force_qs, n)); CUDA_TRY(ctx, down(r_mtx, df.matrix, 8 * (size_t)nc));
     CUDA_TRY(ctx, down(r_soff, df.stream_off, tab)); CUDA_TRY(ctx, down(r_slen, df.stream_len, tab));
-    CUDA_TRY(ctx, down(r_qso, df.read_qs_off, 8 * n)); CUDA_TRY(ctx, down(r_bao, df.read_ba_off, 8 * n));
     for (int k = 0; k < CRAMGPU_S_COUNT; k++)
         if (((host_series >> k) & 1) && span[2 * k + 1])
             CUDA_TRY(ctx, memcpy_pieces(po + so.off[r_str] + span[2 * k], df.streams + span[2 * k], span[2 * k + 1], cudaMemcpyDeviceToHost, st));
@@ -2042,6 +2046,8 @@ static int features_encode_host(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     out->force_qs = po + so.off[r_force]; out->matrix = po + so.off[r_mtx]; out->streams = po + so.off[r_str];
     out->stream_off = (const uint64_t *)(po + so.off[r_soff]); out->stream_len = (const uint64_t *)(po + so.off[r_slen]);
     out->read_qs_off = (const uint64_t *)(po + so.off[r_qso]); out->read_ba_off = (const uint64_t *)(po + so.off[r_bao]);
+    if (!arrays) { out->f_op = nullptr; out->f_pos = out->f_val = out->f_aux = nullptr; out->feat_off = nullptr; out->payload = nullptr;
+                   out->read_qs_off = out->read_ba_off = nullptr; }
     if (fault) return ctx_fail(ctx, CRAMGPU_ERR_UNSUPPORTED, BIN_FAULT_MSG);
     return CRAMGPU_OK;
 }
@@ -2134,18 +2140,22 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     const uint32_t nc = in->n_containers;
     if (n == 0 || nc == 0) return CRAMGPU_OK;
     if (!in->read_off || !in->feat_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
-    const uint64_t nb = in->read_off[n], nf = in->feat_off[n];           // the offset tables are read here: host memory
     Stager sg;
+    // read_off is read here (host memory); feat_off / read_qs_off / read_ba_off may also be the device-resident result of
+    // cramgpu_features_unpack_resident, in which case the feature arrays are device memory too and need no extents
+    const bool foff_dev = sg.mm.kind(in->feat_off) == MEM_DEVICE;
+    const bool qso_dev = in->read_qs_off && sg.mm.kind(in->read_qs_off) == MEM_DEVICE, bao_dev = in->read_ba_off && sg.mm.kind(in->read_ba_off) == MEM_DEVICE;
+    const uint64_t nb = in->read_off[n], nf = foff_dev ? 1 : in->feat_off[n];      // device arrays are used where they are: any non-zero extent
     // extents of the side buffers in host memory: the furthest byte any record refers to (buffers in device memory are
     // used where they are, whatever their extent)
     uint64_t qs_len = 0, ba_len = 0, pay_len = 0;
     const bool qs_dev = in->qs && sg.mm.kind(in->qs) == MEM_DEVICE, ba_dev = in->ba && sg.mm.kind(in->ba) == MEM_DEVICE;
     const bool pay_dev = in->payload && sg.mm.kind(in->payload) == MEM_DEVICE;
-    if ((in->read_qs_off && !qs_dev) || (in->read_ba_off && !ba_dev))
+    if ((in->read_qs_off && !qs_dev && !qso_dev) || (in->read_ba_off && !ba_dev && !bao_dev))
         for (uint64_t r = 0; r < n; r++) {
             uint64_t len = in->read_off[r + 1] - in->read_off[r];
-            if (in->read_qs_off && !qs_dev && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
-            if (in->read_ba_off && !ba_dev && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
+            if (in->read_qs_off && !qs_dev && !qso_dev && in->read_qs_off[r] != ~0ull) qs_len = std::max(qs_len, in->read_qs_off[r] + len);
+            if (in->read_ba_off && !ba_dev && !bao_dev && in->read_ba_off[r] != ~0ull) ba_len = std::max(ba_len, in->read_ba_off[r] + len);
         }
     if (!pay_dev) pay_len = in->payload ? in->payload_len : 0;
     size_t i_ref = sg.add(in->ref, in->ref_total), i_mtx = sg.add(in->matrix, 8 * (size_t)nc), i_pos = sg.add(in->pos, 4 * n);
@@ -2171,6 +2181,8 @@ extern "C" int cramgpu_normalize_decode(cramgpu_ctx *ctx, const cramgpu_norm_in 
     dev.rflags = sg.at(D, i_rfl); dev.feat_off = (const uint64_t *)sg.at(D, i_foff); dev.f_op = sg.at(D, i_op); dev.f_pos = (const int32_t *)sg.at(D, i_fp);
     dev.f_val = (const int32_t *)sg.at(D, i_fv); dev.f_aux = (const int32_t *)sg.at(D, i_fa); dev.payload = sg.at(D, i_pay); dev.qs = sg.at(D, i_qs);
     dev.read_qs_off = (const uint64_t *)sg.at(D, i_qso); dev.ba = sg.at(D, i_ba); dev.read_ba_off = (const uint64_t *)sg.at(D, i_bao);
+    if (!in->qs && qso_dev) dev.qs = nullptr;                       // absolute device addresses in read_qs_off / read_ba_off
+    if (!in->ba && bao_dev) dev.ba = nullptr;
     uint8_t *d_b = b_dev ? bases : sg.at(D, o_bases), *d_q = q_dev ? quals : sg.at(D, o_quals);
     if (int rc = normalize_impl(ctx, &dev, d_b, d_q, sg.at(D, o_star), (int32_t *)sg.at(D, o_stat), st)) return rc;
     int32_t *d_flag = (int32_t *)sg.at(D, o_flag);
@@ -2481,6 +2493,66 @@ extern "C" int cramgpu_features_unpack_dev(cramgpu_ctx *ctx, const cramgpu_serie
     if (!ctx) return CRAMGPU_ERR_ARG;
     CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     return features_unpack_impl(ctx, in, out, d_mapq, status, stream ? (cudaStream_t)stream : ctx->stream);
+}
+
+// Host variant that leaves the features on the device: in->streams must be NULL and stream_off holds ABSOLUTE addresses, each
+// series in host memory (staged: pieces that lie next to each other travel as one copy) or in device memory (used in place).
+extern "C" int cramgpu_features_unpack_resident(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *dev_out, uint8_t *mapq,
+                                                int32_t *status)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !dev_out) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    memset(dev_out, 0, sizeof *dev_out);
+    const uint64_t n = in->n_reads;
+    const uint32_t nc = in->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (in->streams || !in->stream_off || !in->stream_len || !in->read_off || !in->rflags)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "streams must be NULL (absolute addresses in stream_off); null argument");
+    MemMap mm;
+    struct Piece { uint64_t addr, len; size_t idx; };
+    std::vector<Piece> pieces;
+    const size_t ncell = (size_t)nc * CRAMGPU_S_COUNT;
+    for (size_t i = 0; i < ncell; i++)
+        if (in->stream_len[i] && mm.kind((const void *)(uintptr_t)in->stream_off[i]) != MEM_DEVICE) pieces.push_back({in->stream_off[i], in->stream_len[i], i});
+    std::sort(pieces.begin(), pieces.end(), [](const Piece &x, const Piece &y) { return x.addr < y.addr; });
+    // runs of neighbouring pieces (gaps of alignment padding ride along)
+    struct Run { uint64_t lo, hi; size_t off; };
+    std::vector<Run> runs;
+    Carver cv;
+    for (const Piece &p : pieces) {
+        if (!runs.empty() && p.addr <= runs.back().hi + 256) runs.back().hi = std::max(runs.back().hi, p.addr + p.len);
+        else runs.push_back({p.addr, p.addr + p.len, 0});
+    }
+    for (Run &r : runs) r.off = cv.take(r.hi - r.lo + 16);
+    const bool roff_host = mm.kind(in->read_off) != MEM_DEVICE, rfl_host = mm.kind(in->rflags) != MEM_DEVICE;
+    const size_t o_roff = roff_host ? cv.take(8 * (n + 1)) : 0, o_rfl = rfl_host ? cv.take(n) : 0;
+    if (int rc = pool_reserve(ctx, ctx->unp_in, cv.off + 16)) return rc;
+    uint8_t *D = (uint8_t *)ctx->unp_in.p;
+    for (const Run &r : runs) CUDA_TRY(ctx, memcpy_pieces(D + r.off, (const void *)(uintptr_t)r.lo, r.hi - r.lo, cudaMemcpyHostToDevice, st));
+    if (roff_host) CUDA_TRY(ctx, memcpy_pieces(D + o_roff, in->read_off, 8 * (n + 1), cudaMemcpyHostToDevice, st));
+    if (rfl_host) CUDA_TRY(ctx, memcpy_pieces(D + o_rfl, in->rflags, n, cudaMemcpyHostToDevice, st));
+    std::vector<uint64_t> addr(in->stream_off, in->stream_off + ncell);
+    {
+        size_t ri = 0;
+        for (const Piece &p : pieces) {                       // pieces and runs are both in address order
+            while (p.addr >= runs[ri].hi) ri++;
+            addr[p.idx] = (uint64_t)(uintptr_t)(D + runs[ri].off + (p.addr - runs[ri].lo));
+        }
+    }
+    cramgpu_series dev = *in;
+    dev.stream_off = addr.data();
+    dev.read_off = roff_host ? (const uint64_t *)(D + o_roff) : in->read_off;
+    dev.rflags = rfl_host ? D + o_rfl : in->rflags;
+    uint8_t *d_mq = nullptr;
+    const int rc0 = features_unpack_impl(ctx, &dev, dev_out, &d_mq, status, st);
+    if (rc0 != CRAMGPU_OK && rc0 != CRAMGPU_ERR_CORRUPT && rc0 != CRAMGPU_ERR_UNSUPPORTED) return rc0;
+    if (mapq) {
+        CUDA_TRY(ctx, cudaMemcpyAsync(mapq, d_mq, n, cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    }
+    return rc0;
 }
 
 extern "C" int cramgpu_features_unpack(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t *mapq,

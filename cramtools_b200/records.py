@@ -17,6 +17,7 @@ from ._lib import CramGpuError
 u8p, u16p, u32p, i32p, i64p, u64p = (C.POINTER(t) for t in (C.c_uint8, C.c_uint16, C.c_uint32, C.c_int32, C.c_int64, C.c_uint64))
 
 SERIES = ['FN', 'FC', 'FP', 'BS', 'DL', 'BA', 'SC', 'QS', 'RS', 'HC', 'PD', 'MQ']
+FEATURES_ON_DEVICE_ONLY = 0x80000000      # cramgpu_features_encode_resident: host_series flag
 SERIES_CONTENT_ID = {'FN': 15, 'FC': 3, 'FP': 2, 'BS': 16, 'DL': 5, 'BA': 6, 'SC': 27, 'QS': 4, 'RS': 26, 'HC': 28, 'PD': 29, 'MQ': 11}
 NONE = np.uint64(0xFFFFFFFFFFFFFFFF)
 
@@ -77,6 +78,7 @@ _lib.SIGNATURES.update({
                                                     C.POINTER(HostSeries)]),
     'cramgpu_host_series_pack_dev': (C.c_int, [C.c_void_p, C.POINTER(HostFields), C.POINTER(HostSeries), u64p, u64p, C.c_void_p]),
     'cramgpu_features_unpack': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), u8p, i32p]),
+    'cramgpu_features_unpack_resident': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), u8p, i32p]),
     'cramgpu_features_unpack_dev': (C.c_int, [C.c_void_p, C.POINTER(Series), C.POINTER(Features), C.POINTER(C.c_void_p), i32p,
                                               C.c_void_p]),
     'cramgpu_parse_lossy_spec': (C.c_int, [C.c_char_p, C.POINTER(QsPolicy), C.c_int]),
@@ -208,7 +210,8 @@ def features_encode(rd, ref, spec=None, cont_off=None, ref_off=None, ref_len=Non
     return EncodedFeatures(F, n, nc)
 
 
-def features_encode_resident(rd, ref, spec=None, host_series=None, cont_off=None, ref_off=None, ref_len=None, ctx=None):
+def features_encode_resident(rd, ref, spec=None, host_series=None, cont_off=None, ref_off=None, ref_len=None, ctx=None,
+                             features_on_device_only=False):
     """cramgpu_features_encode_resident: as features_encode, but the results also stay on the device and only the series
     named in host_series (default: all but QS and BA) come back to the host.  -> (EncodedFeatures, Features with DEVICE
     pointers); the device result is valid until the next record call on ctx."""
@@ -221,6 +224,8 @@ def features_encode_resident(rd, ref, spec=None, host_series=None, cont_off=None
     mask = 0
     for name in host_series:
         mask |= 1 << SERIES.index(name)
+    if features_on_device_only:
+        mask |= FEATURES_ON_DEVICE_ONLY
     F, D = Features(), Features()
     ctx.check(ctx.lib.cramgpu_features_encode_resident(ctx.handle, C.byref(R), pol, npol, mask, C.byref(F), C.byref(D)))
     return EncodedFeatures(F, n, nc), D

@@ -330,8 +330,11 @@ typedef struct cramgpu_features {
  * back to the host (`out`) as usual, except that of `streams` only the series whose bit is set in `host_series`
  * (1u << CRAMGPU_S_x) are copied; `out->streams` keeps the device layout, the other series' bytes are left
  * unwritten.  Typical use: host_series = all but QS and BA, then cramgpu_rans_encode_batch with
- * in[i] = dev_out->streams + stream_off[c][QS].  No counterpart in the reference.
+ * in[i] = dev_out->streams + stream_off[c][QS].  With CRAMGPU_FEATURES_ON_DEVICE_ONLY or-ed into host_series the feature arrays
+ * (f_op f_pos f_val f_aux feat_off payload read_qs_off read_ba_off) are not copied to the host either (`out` holds NULL for
+ * them): a host that hands the series straight to the block layer never looks at them.  No counterpart in the reference.
  */
+#define CRAMGPU_FEATURES_ON_DEVICE_ONLY 0x80000000u
 int cramgpu_features_encode(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
                             int n_policies, cramgpu_features *out);
 int cramgpu_features_encode_resident(cramgpu_ctx *ctx, const cramgpu_reads *reads, const cramgpu_qs_policy *policies,
@@ -377,6 +380,13 @@ int cramgpu_features_unpack(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_
                             int32_t *status);
 int cramgpu_features_unpack_dev(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *out, uint8_t **d_mapq,
                                 int32_t *status, void *stream);
+/* cramgpu_features_unpack_resident: the host variant for a decode pipeline that never looks at the features itself.  in->streams
+ * must be NULL and stream_off holds ABSOLUTE addresses: a series the host inflated (gzip) lies in host memory and is staged,
+ * a series the block codec left on the device (QS, BA out of cramgpu_rans_decode_batch) is used where it is.  The features
+ * stay on the device (dev_out: device pointers, read_qs_off / read_ba_off absolute; valid until the next unpack call on ctx)
+ * and go to cramgpu_normalize_decode as they are -- with qs = ba = NULL there.  mapq (optional) and status come back to the host. */
+int cramgpu_features_unpack_resident(cramgpu_ctx *ctx, const cramgpu_series *in, cramgpu_features *dev_out, uint8_t *mapq,
+                                     int32_t *status);
 
 /* input of the decode-side normaliser: records as CramRecordReader leaves them, structure of arrays */
 typedef struct cramgpu_norm_in {

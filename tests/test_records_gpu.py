@@ -281,6 +281,38 @@ def test_resident_series_and_device_pointers(R, gpu_ctx):
                                                        star.ctypes.data_as(u8p), st.ctypes.data_as(i32p)))
     assert (st == 0).all() and (star == 0).all()
     assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
+    # ---- the decode pipeline that never sees a feature on the host: series (the small ones in host memory, QS / BA where the
+    # block codec left them on the device) -> cramgpu_features_unpack_resident -> cramgpu_normalize_decode with device pointers
+    S = R.Series()
+    sa = np.zeros((nc, 12), np.uint64)
+    sa[:] = np.uint64(host.streams.ctypes.data) + host.stream_off
+    sa[:, KQS] = np.uint64(d_streams.data_ptr()) + enc.stream_off[:, KQS]; sa[:, KBA] = np.uint64(d_streams.data_ptr()) + enc.stream_off[:, KBA]
+    sl = np.ascontiguousarray(host.stream_len, np.uint64)
+    S.n_reads = n; S.n_containers = nc; S.cont_off = co.ctypes.data_as(u64p); S.streams = None; S.streams_len = 0
+    S.stream_off = sa.ctypes.data_as(u64p); S.stream_len = sl.ctypes.data_as(u64p)
+    S.read_off = arrs['read_off'].ctypes.data; S.rflags = rfl.ctypes.data
+    U = R.Features(); ust = np.zeros(nc, np.int32); umq = np.zeros(n, np.uint8)
+    gpu_ctx.check(gpu_ctx.lib.cramgpu_features_unpack_resident(gpu_ctx.handle, C.byref(S), C.byref(U), umq.ctypes.data_as(u8p), ust.ctypes.data_as(i32p)))
+    assert (ust == 0).all() and int(U.n_feat) == int(host.n_feat)
+    mapped = (rd['flag'] & 4) == 0
+    assert (umq[mapped] == rd['mapq'][mapped]).all()
+    I.feat_off = U.feat_off; I.f_op = U.f_op; I.f_pos = U.f_pos; I.f_val = U.f_val; I.f_aux = U.f_aux; I.payload = U.payload; I.payload_len = U.payload_len
+    I.qs = None; I.ba = None; I.read_qs_off = U.read_qs_off; I.read_ba_off = U.read_ba_off
+    bases[:] = 0; quals[:] = 0
+    gpu_ctx.check(gpu_ctx.lib.cramgpu_normalize_decode(gpu_ctx.handle, C.byref(I), bases.ctypes.data_as(u8p), quals.ctypes.data_as(u8p),
+                                                       star.ctypes.data_as(u8p), st.ctypes.data_as(i32p)))
+    assert (st == 0).all() and (star == 0).all()
+    assert (bases == rd['bases']).all() and (quals == rd['quals']).all()
+    # ---- and the encode side that keeps the feature arrays on the device
+    lean, dev2 = R.features_encode_resident(rd, ref, None, cont_off=cont_off, ctx=gpu_ctx, features_on_device_only=True)
+    assert lean.f_op.size == 0 and lean.read_qs_off.size == 0 and (lean.force_qs == host.force_qs).all() and (lean.matrix == host.matrix).all()
+    assert (lean.stream_off == host.stream_off).all() and (lean.stream_len == host.stream_len).all()
+    for c in range(nc):
+        for name in R.SERIES:
+            if name not in ('QS', 'BA'):
+                assert lean.series(c, name) == host.series(c, name), (c, name)
+    from cramtools_b200 import device as dv
+    assert (dv.dev_to_numpy(gpu_ctx, int(dev2.f_op), int(host.n_feat), np.uint8) == host.f_op).all()
 
 
 def _nf_flags(enc, rd):
