@@ -246,6 +246,7 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
     if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
+    if (ctx->enc_big.p) cudaFree(ctx->enc_big.p);
     if (ctx->unp_in.p) cudaFree(ctx->unp_in.p);
     if (ctx->bam_scratch.p) cudaFree(ctx->bam_scratch.p);
     if (ctx->bam_cigar.p) cudaFree(ctx->bam_cigar.p);

@@ -43,6 +43,7 @@ struct O1Meta {
     uint8_t calpha[256];  // context rank -> byte
     uint8_t salpha[256];  // symbol rank -> byte
     uint32_t nctx, nsym;
+    uint64_t cell_off;    // where the block's nctx x nsym cells start in the count / coder-cell arrays (k_enc_layout)
 };
 
 struct DevPool {
@@ -66,6 +67,7 @@ struct cramgpu_ctx {
     std::string err;
     uint64_t launches = 0;
     DevPool scratch;          // carved anew by every call
+    DevPool enc_big;          // encoder: pair counts, coder cells and work areas, sized on the device (k_enc_layout)
     DevPool dev_in, dev_out;  // device staging of the host entry points
     DevPool rec_scratch, rec_out;   // record-feature work: counters / results (results stay valid until the next record call)
     DevPool unp_in;                 // staged host series of cramgpu_features_unpack_resident

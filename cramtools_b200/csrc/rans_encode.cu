@@ -146,8 +146,7 @@ __global__ void __launch_bounds__(256) k_hist0(const BlockDesc *__restrict__ des
 // ------------------------------------------------------------------------------------------------
 // k_prep_o1: one CTA (256 threads) per order-1 block.
 __global__ void __launch_bounds__(256) k_prep_o1(const BlockDesc *__restrict__ desc, const uint32_t *__restrict__ o1_blocks,
-                                                 const uint32_t *__restrict__ F0, O1Meta *__restrict__ meta,
-                                                 uint32_t *__restrict__ F1)
+                                                 const uint32_t *__restrict__ F0, O1Meta *__restrict__ meta)
 {
     uint32_t blk = o1_blocks[blockIdx.x];
     uint32_t j = threadIdx.x, lane = j & 31, w = j >> 5;
@@ -169,9 +168,61 @@ __global__ void __launch_bounds__(256) k_prep_o1(const BlockDesc *__restrict__ d
     if (present) m->salpha[rs] = (uint8_t)j;
     if (isctx) m->calpha[rc] = (uint8_t)j;
     if (j == 0) { m->nsym = totS; m->nctx = totC; }
-    uint32_t *f1 = F1 + (size_t)blockIdx.x * 65536;
-    for (uint32_t i = j; i < totS * totC; i += 256) f1[i] = 0;
     (void)desc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_enc_layout: one CTA.  Now that every order-1 block's alphabet is known, size its tables by what it needs instead of
+// the worst case (256 x 256 cells, a 258 KB frequency table): cell offsets of the order-1 blocks, and every block's work
+// area (table bytes first, payload growing down from the end).  totals[0] = cells, totals[1] = work bytes: the host sizes
+// the buffers from them.  A context row of the table costs at most 2 (context, run) + 4 per symbol (symbol, run, 1-2
+// bytes of frequency) + 1 (end) bytes [Frequencies.java:258-324].
+__device__ __forceinline__ unsigned long long block_excl_scan_u64(unsigned long long v, unsigned long long *s_warp, unsigned long long &total)
+{
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    unsigned long long inc = v;
+    for (int d = 1; d < 32; d <<= 1) { unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, inc, d); if (lane >= (uint32_t)d) inc += t; }
+    if (lane == 31) s_warp[w] = inc;
+    __syncthreads();
+    unsigned long long base = 0, tot = 0;
+    for (uint32_t k = 0; k < blockDim.x / 32; k++) { if (k < w) base += s_warp[k]; tot += s_warp[k]; }
+    __syncthreads();
+    total = tot;
+    return base + inc - v;
+}
+__global__ void __launch_bounds__(1024) k_enc_layout(BlockDesc *__restrict__ desc, uint32_t nblocks, O1Meta *__restrict__ meta, uint32_t n1,
+                                                     unsigned long long *__restrict__ totals)
+{
+    __shared__ unsigned long long s_warp[32];
+    unsigned long long carry = 0;
+    for (uint32_t i0 = 0; i0 < n1; i0 += 1024) {
+        const uint32_t i = i0 + threadIdx.x;
+        const unsigned long long need = i < n1 ? (((unsigned long long)meta[i].nctx * meta[i].nsym + 3ull) & ~3ull) : 0ull;
+        unsigned long long tot;
+        const unsigned long long at = block_excl_scan_u64(need, s_warp, tot);
+        if (i < n1) meta[i].cell_off = carry + at;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) totals[0] = carry;
+    carry = 0;
+    for (uint32_t i0 = 0; i0 < nblocks; i0 += 1024) {
+        const uint32_t i = i0 + threadIdx.x;
+        unsigned long long need = 0;
+        uint32_t tab_cap = 0, work_cap = 0;
+        if (i < nblocks && desc[i].order <= 1) {
+            const BlockDesc d = desc[i];
+            if (d.order == 1) { const O1Meta &m = meta[d.o1_index]; tab_cap = (m.nctx * (3u + 4u * m.nsym) + 1u + 31u) & ~15u; }
+            else tab_cap = O0_TAB_CAP;
+            const unsigned long long pay_cap = ((unsigned long long)d.in_len + d.in_len / 4 + 64 + 15) & ~15ull;
+            work_cap = (uint32_t)(tab_cap + pay_cap);
+            need = ((unsigned long long)work_cap + 255ull) & ~255ull;
+        }
+        unsigned long long tot;
+        const unsigned long long at = block_excl_scan_u64(need, s_warp, tot);
+        if (i < nblocks && desc[i].order <= 1) { desc[i].tab_cap = tab_cap; desc[i].work_cap = work_cap; desc[i].work_off = carry + at; }
+        carry += tot;
+    }
+    if (threadIdx.x == 0) totals[1] = carry;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -188,7 +239,7 @@ __global__ void __launch_bounds__(256) k_hist1(const BlockDesc *__restrict__ des
     const uint8_t *base = d_in + d.in_off;
     const uint8_t *in = base + start;
     const O1Meta *m = meta + blockIdx.x;
-    uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
+    uint32_t *g = F1 + m->cell_off;
 
     // cs[b] = (context row of byte b: cmap[b] * nsym) | (symbol rank of b: smap[b]) << 16 -- one lookup per byte gives the
     // column of this byte and the row of the next one
@@ -301,8 +352,8 @@ __global__ void __launch_bounds__(256) k_tables1(const BlockDesc *__restrict__ d
     uint32_t blk = o1_blocks[blockIdx.x];
     const BlockDesc d = desc[blk];
     const O1Meta *m = meta + blockIdx.x;
-    uint32_t *g = F1 + (size_t)blockIdx.x * 65536;
-    uint32_t *sy = tab1 + (size_t)blockIdx.x * 65536;          // compact [ctx rank][sym rank] {freq | start << 12}
+    uint32_t *g = F1 + m->cell_off;
+    uint32_t *sy = tab1 + m->cell_off;                         // compact [ctx rank][sym rank] {freq | start << 12}
     uint8_t *tab = work + d.work_off;
     uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
 
@@ -519,7 +570,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_enc(const BlockDesc *__restrict
             s.len = (k == 3) ? n - 3 * q : q;
             s.steps = n - 3 * q;
             const O1Meta *m = meta + d.o1_index;
-            s.gtab = tabs + (size_t)d.o1_index * 65536;
+            s.gtab = tabs + m->cell_off;
             s.ns_smem = (have ? m->nsym : 1) | ((have && m->nsym * m->nctx <= ENC_TAB_ENTRIES) ? 0x80000000u : 0u);
         } else {
             s.off = 0;
@@ -830,7 +881,6 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     std::vector<BlockDesc> desc(nblocks);
     std::vector<int32_t> hstatus(nblocks, 0);
     std::vector<uint32_t> o0, o1;
-    uint64_t work_total = 0;
     uint32_t max_len = 0;
     for (uint32_t i = 0; i < nblocks; i++) {
         BlockDesc &d = desc[i];
@@ -842,12 +892,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         if (d.in_len == 0) { d.order = 0xFF; continue; }                       // empty -> empty [RANS.java:60-61]
         if (ord > 1) { d.order = 0xFF; hstatus[i] = CRAMGPU_ERR_UNKNOWN_ORDER; continue; }
         if (d.in_len < 4) ord = 0;                                             // [RANS.java:63-64]
-        d.order = ord;
-        d.tab_cap = ord ? O1_TAB_CAP : O0_TAB_CAP;
-        uint64_t pay_cap = rup((uint64_t)d.in_len + d.in_len / 4 + 64, 16);
-        d.work_cap = (uint32_t)(d.tab_cap + pay_cap);
-        d.work_off = work_total;
-        work_total += rup(d.work_cap, 256);
+        d.order = ord;                       // tab_cap, work_cap, work_off: k_enc_layout, once the alphabets are known
         if (ord) { d.o1_index = (uint32_t)o1.size(); o1.push_back(i); } else o0.push_back(i);
         max_len = std::max(max_len, d.in_len);
     }
@@ -867,14 +912,12 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
     size_t o_zero_end = c.off;                                                  // [o_F0, here) is zeroed
     size_t o_syms0 = c.take(1024 * (size_t)nblocks);
     size_t o_meta = c.take(sizeof(O1Meta) * (size_t)std::max(n1, 1u));
-    size_t o_F1 = c.take(262144 * (size_t)n1 + 16);
-    size_t o_syms1 = c.take(262144 * (size_t)n1 + 16);
-    size_t o_work = c.take(work_total + 256);
+    size_t o_totals = c.take(16);
     if (int rc = pool_reserve(ctx, ctx->scratch, c.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->scratch.p;
 
     // ---- upload the plan through pinned memory
-    size_t meta_bytes = sizeof(BlockDesc) * nblocks + 4 * (size_t)(2 * n0 + 2 * n1) + 4 * (size_t)nblocks + 64;
+    size_t meta_bytes = sizeof(BlockDesc) * nblocks + 4 * (size_t)(2 * n0 + 2 * n1) + 4 * (size_t)nblocks + 512;
     if (int rc = pinned_reserve(ctx, &ctx->pin_meta, &ctx->pin_meta_cap, meta_bytes)) return rc;
     CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev));       // previous call may still be reading the pinned plan
     uint8_t *pm = (uint8_t *)ctx->pin_meta;
@@ -897,7 +940,7 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
 
     const BlockDesc *dd = (const BlockDesc *)(S + o_desc);
     uint32_t *F0 = (uint32_t *)(S + o_F0), *tlen = (uint32_t *)(S + o_tlen), *plen = (uint32_t *)(S + o_plen);
-    uint32_t *syms0 = (uint32_t *)(S + o_syms0), *syms1 = (uint32_t *)(S + o_syms1);
+    uint32_t *syms0 = (uint32_t *)(S + o_syms0);
 #ifdef CRAMGPU_TIMING_EXPERIMENTS
     const int dbg = getenv("CRAMGPU_DBG") ? atoi(getenv("CRAMGPU_DBG")) : 0;   // role-by-role timing (scripts/time_enc.py): wrong output, never in a shipped build
 #else
@@ -909,17 +952,32 @@ int rans_encode_device(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_in, 
         ctx->enc_attr_done = true;
     }
     O1Meta *meta = (O1Meta *)(S + o_meta);
-    uint32_t *F1 = (uint32_t *)(S + o_F1);
-    uint8_t *work = S + o_work;
+    uint32_t *F1 = nullptr, *syms1 = nullptr;
+    uint8_t *work = nullptr;
     const uint32_t *d_o0 = (const uint32_t *)(S + o_o0), *d_o1 = (const uint32_t *)(S + o_o1);
     const uint32_t *d_s0 = (const uint32_t *)(S + o_s0), *d_s1 = (const uint32_t *)(S + o_s1);
 
     if (n0 + n1) {
         uint32_t chunks = (max_len + HIST_CHUNK - 1) / HIST_CHUNK;
         LAUNCH(ctx, st, "k_hist0", k_hist0<<<dim3(nblocks, chunks), 256, 0, st>>>(dd, d_in, F0));
+        if (n1) LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta));
+        // The alphabets are known now: lay the tables and work areas out by what the blocks need (a quality block: 41 x 41
+        // cells and a 7 KB table, not 65 536 cells and 258 KB) and size the buffers from the totals.  One synchronisation.
+        {
+            unsigned long long *d_tot = (unsigned long long *)(S + o_totals);
+            LAUNCH(ctx, st, "k_enc_layout", k_enc_layout<<<1, 1024, 0, st>>>((BlockDesc *)(S + o_desc), nblocks, meta, n1, d_tot));
+            CUDA_TRY(ctx, cudaMemcpyAsync(pm + rup(po, 64), d_tot, 16, cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(ctx, cudaStreamSynchronize(st));
+            const uint64_t cells = ((const uint64_t *)(pm + rup(po, 64)))[0], work_total = ((const uint64_t *)(pm + rup(po, 64)))[1];
+            Carver cb;
+            const size_t b_F1 = cb.take(4 * cells + 16), b_sy = cb.take(4 * cells + 16), b_work = cb.take(work_total + 256);
+            if (int rc = pool_reserve(ctx, ctx->enc_big, cb.off)) return rc;
+            uint8_t *B = (uint8_t *)ctx->enc_big.p;
+            F1 = (uint32_t *)(B + b_F1); syms1 = (uint32_t *)(B + b_sy); work = B + b_work;
+            if (cells) CUDA_TRY(ctx, cudaMemsetAsync(F1, 0, 4 * cells, st));
+        }
         if (n1) {
             uint32_t max1 = desc[s1[0]].in_len;
-            LAUNCH(ctx, st, "k_prep_o1", k_prep_o1<<<n1, 256, 0, st>>>(dd, d_o1, F0, meta, F1));
             LAUNCH(ctx, st, "k_hist1", k_hist1<<<dim3(n1, (max1 + HIST1_CHUNK - 1) / HIST1_CHUNK), 256, 0, st>>>(dd, d_o1, d_in, meta, F1));
             LAUNCH(ctx, st, "k_tables1", k_tables1<<<n1, 256, 0, st>>>(dd, d_o1, meta, F1, syms1, work, tlen));
             ON_HP_STREAM(ctx, st, LAUNCH(ctx, hs, "k_enc1", k_enc<1><<<(n1 + 7) / 8, ENC_THREADS, ENC_SMEM(1), hs>>>(dd, d_s1, n1, d_in, syms1, meta, work, plen, d_status, dbg)));

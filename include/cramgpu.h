@@ -152,7 +152,10 @@ int cramgpu_rans_decode_batch(cramgpu_ctx *ctx, uint32_t nblocks,
  *   d_out_len       DEVICE array of nblocks u32, written by the call
  *   d_status        DEVICE array of nblocks i32, written by the call (cramgpu_status per block)
  *   stream          cudaStream_t to enqueue on (NULL = the context's own stream)
- * Work is enqueued asynchronously; results are valid once `stream` has been synchronised.
+ * Work is enqueued asynchronously; results are valid once `stream` has been synchronised.  (The ENCODER synchronises `stream`
+ * once near its start: the alphabets of the order-1 blocks are found on the device, and the frequency tables, coder cells and
+ * work areas are sized by what the blocks need -- 1 GB for 16 384 blocks where the worst case would be 12.6 GB.  The decoder,
+ * and everything the encoder enqueues after that point, is asynchronous.)
  * The context's scratch is reused by the next call on the same ctx, so calls on one ctx must be
  * stream-ordered (same stream, or synchronised in between).
  * For decode, out_cap must be >= sum over blocks of roundup16(raw size); sizes come from the prefixes,
