@@ -110,6 +110,11 @@ def jstr(v):
     return v.fields['s'] if isinstance(v, JObject) and v.cls == 'java/lang/String' else v
 
 
+def get_static(cname, fname):
+    vm.load(cname)
+    return vm.statics[(cname, fname)]
+
+
 def list_items(o):
     return o.fields['list']
 
@@ -178,6 +183,28 @@ def build(reads, ref, coordinate_sorted, tag):
         tags.append([chr(tg & 0xFF) + chr((tg >> 8) & 0xFF), b64(v.a) if isinstance(v, JArray) else int(v.fields['value']) if isinstance(v, JObject) else v])
         t = t.fields.get('next')
     out['slice_tags'] = tags
+    # SURVEY 8f-5 (the block layer around the coded series): Block.write [Block.java:272-294] of the external blocks the header
+    # gives to rANS -- method, content type, ITF8 content id / compressed size / raw size, data, CRC32 (little endian) of all of it
+    BLK = 'htsjdk/samtools/cram/structure/Block'
+    blocks = {}
+    for cid, raw in sorted(series.items()):
+        cm = comps.get(cid)
+        if not cm or cm.get('order') is None or len(raw) == 0 or len(raw) > 6000:
+            continue
+        order = 1 if cm['order'] == 'ONE' else 0
+        comp = vm.call('htsjdk/samtools/cram/io/ExternalCompression', 'rans', '([BI)[B', [jbytes(raw), order])
+        blk = new(BLK)
+        vm.call(BLK, 'setContentType', '(Lhtsjdk/samtools/cram/structure/BlockContentType;)V',
+                [blk, get_static('htsjdk/samtools/cram/structure/BlockContentType', 'EXTERNAL')])
+        vm.call(BLK, 'setContentId', '(I)V', [blk, cid])
+        vm.call(BLK, 'setMethod', '(Lhtsjdk/samtools/cram/structure/BlockCompressionMethod;)V',
+                [blk, get_static('htsjdk/samtools/cram/structure/BlockCompressionMethod', 'RANS')])
+        vm.call(BLK, 'setContent', '([B[B)V', [blk, jbytes(raw), comp])
+        baos = JObject('java/io/ByteArrayOutputStream')
+        vm.jdk_special('java/io/ByteArrayOutputStream', '<init>', '()V', [baos])
+        vm.call(BLK, 'write', '(ILjava/io/OutputStream;)V', [blk, 3, baos])
+        blocks[str(cid)] = dict(order=order, block=b64(bytes(vm.jdk_virtual('java/io/ByteArrayOutputStream', 'toByteArray', '()[B', [baos]).a)))
+    out['blocks_v3'] = blocks
 
     # ---- read it back: DataReaderFactory.buildReader + CramRecordReader.read (row P)
     imap = JObject('java/util/HashMap'); imap.fields['map'] = {}

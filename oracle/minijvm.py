@@ -890,6 +890,9 @@ class MiniJVM:
             if cn in ('java/io/DataInputStream', 'java/io/FilterInputStream'):
                 o.fields['in'] = args[1]
                 return None
+            if cn == 'java/io/FilterOutputStream':
+                o.fields['out'] = args[1]
+                return None
             if cn == 'java/io/ByteArrayOutputStream':
                 o.fields['buf'] = JArray('B', bytearray()); o.fields['count'] = 0
                 return None
