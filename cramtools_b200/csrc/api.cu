@@ -219,6 +219,7 @@ int cramgpu_init(int device, cramgpu_ctx **out)
     e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_slice, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ctx->ev_frame, cudaEventDisableTiming);
     if (e == cudaSuccess && !getenv("CRAMGPU_NO_HP_STREAM")) {
         int lo = 0, hi = 0;
         cudaDeviceGetStreamPriorityRange(&lo, &hi);
@@ -246,6 +247,10 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
     if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
+    if (ctx->frame_scratch.p) cudaFree(ctx->frame_scratch.p);
+    if (ctx->frame_out.p) cudaFree(ctx->frame_out.p);
+    if (ctx->pin_frame) cudaFreeHost(ctx->pin_frame);
+    if (ctx->ev_frame) cudaEventDestroy(ctx->ev_frame);
     if (ctx->enc_big.p) cudaFree(ctx->enc_big.p);
     if (ctx->unp_in.p) cudaFree(ctx->unp_in.p);
     if (ctx->bam_scratch.p) cudaFree(ctx->bam_scratch.p);

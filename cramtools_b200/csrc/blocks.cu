@@ -1,0 +1,238 @@
+// blocks.cu -- the CRAM v3 block layer around the coded series (the block part).
+//
+// Block.write(3, os) [htsjdk Block.java:272-294]: method | content type | ITF8 content id | ITF8 compressed size | ITF8 raw
+// size | data | CRC32 of all of it, little endian [CRC32OutputStream.java:50-51].  cramgpu_blocks_frame_dev wraps every
+// compressed block the codec left in device memory into that form, back to back, so that one copy brings a slice's blocks to
+// the Java host ready to be written -- the host neither touches the bytes again nor runs java.util.zip.CRC32 over them.
+//
+// "sizes, scan, write" like bam.cu.  The CRC of a block (up to megabytes) is not one thread's job: the framed block is cut into
+// 16 KB chunks counted from its END, a chunk into 64-byte pieces counted from its end, so that every piece but a block's first
+// and every chunk but its first is full.  A thread computes the raw CRC register of its piece (initial value 0, or ~0 for the
+// block's first piece); registers combine by crc(A || B) = shift_|B|(crc(A)) ^ crc_0(B), where shift_n -- running the register
+// through n zero bytes -- is linear: 32 column vectors per n, and only n = 64 and n = 16 384 occur.
+#include "internal.cuh"
+#include <string.h>
+
+namespace {
+
+#define FR_CHUNK 16384u
+#define FR_PIECE 64u
+#define FR_THREADS (FR_CHUNK / FR_PIECE)          // 256
+
+struct FrameArgs {
+    uint32_t nblocks;
+    const uint8_t *comp;              // base of the compressed bytes (or NULL: comp_off holds absolute addresses)
+    const uint64_t *comp_off;
+    const uint32_t *comp_len, *raw_len;
+    const int32_t *content_id;
+    const uint8_t *method, *content_type;
+    uint32_t *size;                   // framed size per block
+    const uint64_t *out_off;          // write pass
+    uint8_t *out;
+    uint32_t *chunk_crc;              // [sum of chunks] raw registers
+    const uint64_t *chunk_first;      // first chunk slot of every block
+    uint32_t shift64[32], shift16k[32];
+};
+
+__device__ __forceinline__ uint32_t itf8_bytes(uint32_t v) { return v < (1u << 7) ? 1u : v < (1u << 14) ? 2u : v < (1u << 21) ? 3u : v < (1u << 28) ? 4u : 5u; }
+// ITF8.writeUnsignedITF8 [ITF8.java:53-84]
+__device__ __forceinline__ uint32_t itf8_write(uint8_t *p, uint32_t v)
+{
+    if (v < (1u << 7)) { p[0] = (uint8_t)v; return 1; }
+    if (v < (1u << 14)) { p[0] = (uint8_t)((v >> 8) | 0x80); p[1] = (uint8_t)v; return 2; }
+    if (v < (1u << 21)) { p[0] = (uint8_t)((v >> 16) | 0xC0); p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)v; return 3; }
+    if (v < (1u << 28)) { p[0] = (uint8_t)((v >> 24) | 0xE0); p[1] = (uint8_t)(v >> 16); p[2] = (uint8_t)(v >> 8); p[3] = (uint8_t)v; return 4; }
+    p[0] = (uint8_t)(0xF0 | ((v >> 28) & 0xFF)); p[1] = (uint8_t)(v >> 20); p[2] = (uint8_t)(v >> 12); p[3] = (uint8_t)(v >> 4); p[4] = (uint8_t)v;
+    return 5;
+}
+__device__ __forceinline__ uint32_t header_bytes(const FrameArgs &a, uint32_t b) { return 2u + itf8_bytes((uint32_t)a.content_id[b]) + itf8_bytes(a.comp_len[b]) + itf8_bytes(a.raw_len[b]); }
+
+__global__ void __launch_bounds__(256) k_frame_size(FrameArgs a, uint32_t *nchunks)
+{
+    const uint32_t b = blockIdx.x * 256 + threadIdx.x;
+    if (b >= a.nblocks) return;
+    const uint32_t body = header_bytes(a, b) + a.comp_len[b];
+    a.size[b] = body + 4;
+    nchunks[b] = (body + FR_CHUNK - 1) / FR_CHUNK;
+}
+
+__device__ __forceinline__ uint32_t shift_reg(uint32_t r, const uint32_t *cols)
+{
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < 32; j++) v ^= ((r >> j) & 1u) ? cols[j] : 0u;
+    return v;
+}
+
+// grid (chunks of the longest block, nblocks); chunk index counts from the block's start, boundaries from its end
+__global__ void __launch_bounds__(FR_THREADS) k_frame_write(FrameArgs a)
+{
+    __shared__ uint32_t T[256];
+    __shared__ uint8_t hdr[20];
+    __shared__ uint32_t part[FR_THREADS];
+    __shared__ uint32_t s_hlen;
+    const uint32_t b = blockIdx.y, tid = threadIdx.x;
+    const uint32_t clen = a.comp_len[b];
+    if (tid == 0) {
+        uint32_t h = 0;
+        hdr[h++] = a.method[b]; hdr[h++] = a.content_type[b];
+        h += itf8_write(hdr + h, (uint32_t)a.content_id[b]); h += itf8_write(hdr + h, clen); h += itf8_write(hdr + h, a.raw_len[b]);
+        s_hlen = h;
+    }
+    {
+        uint32_t c = tid;
+#pragma unroll
+        for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+        T[tid] = c;
+    }
+    __syncthreads();
+    const uint32_t hlen = s_hlen, body = hlen + clen;
+    const uint32_t nch = (body + FR_CHUNK - 1) / FR_CHUNK;
+    if (blockIdx.x >= nch) return;
+    // chunk blockIdx.x covers [lo, hi) of the body; the first chunk is the short one
+    const uint32_t first_len = body - (nch - 1) * FR_CHUNK;
+    const uint32_t lo = blockIdx.x == 0 ? 0u : first_len + (blockIdx.x - 1) * FR_CHUNK, hi = blockIdx.x == 0 ? first_len : lo + FR_CHUNK;
+    const uint8_t *src = (a.comp ? a.comp : (const uint8_t *)0) + a.comp_off[b];
+    uint8_t *dst = a.out + a.out_off[b];
+    for (uint32_t p = lo + tid; p < hi; p += FR_THREADS) dst[p] = p < hlen ? hdr[p] : src[p - hlen];
+    // pieces of 64 bytes counted from the chunk's end: piece t of np covers [hi - (np - t) * 64, ...), the first one short
+    const uint32_t np = (hi - lo + FR_PIECE - 1) / FR_PIECE;
+    uint32_t reg = 0;
+    if (tid < np) {
+        const uint32_t p_hi = hi - (np - 1 - tid) * FR_PIECE, p_lo = tid == 0 ? lo : p_hi - FR_PIECE;
+        reg = (blockIdx.x == 0 && tid == 0) ? ~0u : 0u;
+        for (uint32_t p = p_lo; p < p_hi; p++) {
+            const uint32_t byte = p < hlen ? hdr[p] : src[p - hlen];
+            reg = T[(reg ^ byte) & 0xFF] ^ (reg >> 8);
+        }
+    }
+    part[tid] = reg;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t r = part[0];
+        for (uint32_t t = 1; t < np; t++) r = shift_reg(r, a.shift64) ^ part[t];
+        a.chunk_crc[a.chunk_first[b] + blockIdx.x] = r;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_frame_crc(FrameArgs a, const uint32_t *nchunks)
+{
+    const uint32_t b = blockIdx.x * 256 + threadIdx.x;
+    if (b >= a.nblocks) return;
+    const uint32_t nch = nchunks[b];
+    const uint32_t *c = a.chunk_crc + a.chunk_first[b];
+    uint32_t r = nch ? c[0] : ~0u;
+    for (uint32_t k = 1; k < nch; k++) r = shift_reg(r, a.shift16k) ^ c[k];
+    const uint32_t crc = ~r;
+    uint8_t *p = a.out + a.out_off[b] + a.size[b] - 4;
+    p[0] = (uint8_t)crc; p[1] = (uint8_t)(crc >> 8); p[2] = (uint8_t)(crc >> 16); p[3] = (uint8_t)(crc >> 24);
+}
+
+// exclusive scans (single CTA; block counts are thousands): sizes rounded up to 16 -> out_off, chunk counts -> chunk_first
+__global__ void __launch_bounds__(1024) k_frame_scan(const uint32_t *size, const uint32_t *nchunks, uint32_t n, uint64_t *out_off,
+                                                     uint64_t *chunk_first, uint32_t *max_chunks)
+{
+    uint32_t mx = 0;
+    for (uint32_t i = threadIdx.x; i < n; i += 1024) mx = max(mx, nchunks[i]);
+    mx = __reduce_max_sync(0xFFFFFFFFu, mx);
+    if ((threadIdx.x & 31) == 0) atomicMax(max_chunks, mx);
+    __shared__ unsigned long long sw[2][32];
+    __shared__ unsigned long long carry[2];
+    if (threadIdx.x < 2) carry[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint32_t i0 = 0; i0 < n; i0 += 1024) {
+        const uint32_t i = i0 + threadIdx.x;
+        unsigned long long v0 = i < n ? (((unsigned long long)size[i] + 15ull) & ~15ull) : 0ull, v1 = i < n ? nchunks[i] : 0ull;
+        unsigned long long s0 = v0, s1 = v1;
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long t0 = __shfl_up_sync(0xFFFFFFFFu, s0, d), t1 = __shfl_up_sync(0xFFFFFFFFu, s1, d);
+            if (lane >= (uint32_t)d) { s0 += t0; s1 += t1; }
+        }
+        if (lane == 31) { sw[0][w] = s0; sw[1][w] = s1; }
+        __syncthreads();
+        unsigned long long b0 = carry[0], b1 = carry[1], tot0 = 0, tot1 = 0;
+        for (uint32_t k = 0; k < 32; k++) { if (k < w) { b0 += sw[0][k]; b1 += sw[1][k]; } tot0 += sw[0][k]; tot1 += sw[1][k]; }
+        if (i < n) { out_off[i] = b0 + s0 - v0; chunk_first[i] = b1 + s1 - v1; }
+        __syncthreads();
+        if (threadIdx.x == 0) { carry[0] += tot0; carry[1] += tot1; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { out_off[n] = carry[0]; chunk_first[n] = carry[1]; }
+}
+
+// columns of shift_n: the register 1 << j run through n zero bytes
+void shift_columns(uint32_t n, uint32_t *cols)
+{
+    uint32_t T[256];
+    for (uint32_t i = 0; i < 256; i++) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c & 1) ? 0xEDB88320u ^ (c >> 1) : c >> 1; T[i] = c; }
+    for (int j = 0; j < 32; j++) {
+        uint32_t r = 1u << j;
+        for (uint32_t k = 0; k < n; k++) r = T[r & 0xFF] ^ (r >> 8);
+        cols[j] = r;
+    }
+}
+
+}  // namespace
+
+extern "C" int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_comp, const uint64_t *d_comp_off,
+                                        const uint32_t *d_comp_len, const uint32_t *d_raw_len, const int32_t *content_id,
+                                        const uint8_t *method, const uint8_t *content_type, uint8_t **d_out, uint64_t *out_len,
+                                        uint64_t **d_out_off, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!d_out || !out_len || !d_out_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    *d_out = nullptr; *out_len = 0; *d_out_off = nullptr;
+    if (nblocks == 0) return CRAMGPU_OK;
+    if (!d_comp_off || !d_comp_len || !d_raw_len || !content_id || !method || !content_type) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const size_t n = nblocks;
+    Carver cv;
+    const size_t o_id = cv.take(4 * n), o_m = cv.take(n), o_t = cv.take(n), o_size = cv.take(4 * n), o_nch = cv.take(4 * n);
+    const size_t o_off = cv.take(8 * (n + 1)), o_cf = cv.take(8 * (n + 1)), o_mx = cv.take(16);
+    if (int rc = pool_reserve(ctx, ctx->frame_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->frame_scratch.p;
+    const size_t up_bytes = rup(4 * n, 16) + 2 * rup(n, 16);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_frame, &ctx->pin_frame_cap, up_bytes + 128)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_frame));
+    uint8_t *pm = (uint8_t *)ctx->pin_frame;
+    memcpy(pm, content_id, 4 * n); memcpy(pm + rup(4 * n, 16), method, n); memcpy(pm + rup(4 * n, 16) + rup(n, 16), content_type, n);
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_id, pm, 4 * n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_m, pm + rup(4 * n, 16), n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_t, pm + rup(4 * n, 16) + rup(n, 16), n, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_frame, st));
+    FrameArgs a;
+    memset(&a, 0, sizeof a);
+    a.nblocks = nblocks; a.comp = d_comp; a.comp_off = d_comp_off; a.comp_len = d_comp_len; a.raw_len = d_raw_len;
+    a.content_id = (const int32_t *)(S + o_id); a.method = S + o_m; a.content_type = S + o_t;
+    a.size = (uint32_t *)(S + o_size); a.out_off = (const uint64_t *)(S + o_off); a.chunk_first = (const uint64_t *)(S + o_cf);
+    static uint32_t c64[32], c16k[32];
+    static bool cols_done = false;
+    if (!cols_done) { shift_columns(FR_PIECE, c64); shift_columns(FR_CHUNK, c16k); cols_done = true; }
+    memcpy(a.shift64, c64, sizeof c64); memcpy(a.shift16k, c16k, sizeof c16k);
+    uint32_t *d_nch = (uint32_t *)(S + o_nch);
+    LAUNCH(ctx, st, "k_frame_size", k_frame_size<<<(nblocks + 255) / 256, 256, 0, st>>>(a, d_nch));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_mx, 0, 16, st));
+    LAUNCH(ctx, st, "k_frame_scan", k_frame_scan<<<1, 1024, 0, st>>>(a.size, d_nch, nblocks, (uint64_t *)(S + o_off), (uint64_t *)(S + o_cf), (uint32_t *)(S + o_mx)));
+    // totals size the result buffers: bytes, chunk slots; the longest block sets the grid
+    uint64_t *tot = (uint64_t *)(pm + up_bytes);
+    CUDA_TRY(ctx, cudaMemcpyAsync(tot, S + o_off + 8 * n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(tot + 1, S + o_cf + 8 * n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(tot + 2, S + o_mx, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t total = tot[0], nchunks_total = tot[1], max_chunks = tot[2] & 0xFFFFFFFFull;
+    Carver co;
+    const size_t q_out = co.take(total + 16), q_crc = co.take(4 * nchunks_total + 16);
+    if (int rc = pool_reserve(ctx, ctx->frame_out, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->frame_out.p;
+    a.out = O + q_out; a.chunk_crc = (uint32_t *)(O + q_crc);
+    // grid.x: chunks of the longest block; CTAs beyond a block's own count leave at once
+    const uint32_t gx = (uint32_t)std::max<uint64_t>(max_chunks, 1);
+    if (nblocks > 65535) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "more than 65535 blocks in one call");
+    LAUNCH(ctx, st, "k_frame_write", k_frame_write<<<dim3(gx, nblocks), FR_THREADS, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_frame_crc", k_frame_crc<<<(nblocks + 255) / 256, 256, 0, st>>>(a, d_nch));
+    CUDA_TRY(ctx, cudaGetLastError());
+    *d_out = a.out; *out_len = total; *d_out_off = (uint64_t *)(S + o_off);
+    return CRAMGPU_OK;
+}

@@ -75,6 +75,8 @@ struct cramgpu_ctx {
     DevPool hs_scratch, hs_out, hs_in;   // cramgpu_host_series_pack: tables, result, staged inputs of the host variant
     DevPool bam_scratch, bam_cigar, bam_out, bam_unp, bam_pk_scratch, bam_unp_scratch;   // bam.cu: sizes/offsets, rebuilt CIGARs, packed records, unpacked arrays
     void *pin_bam = nullptr; size_t pin_bam_cap = 0;
+    DevPool frame_scratch, frame_out;    // blocks.cu
+    void *pin_frame = nullptr; size_t pin_frame_cap = 0; cudaEvent_t ev_frame = nullptr;
     DevPool mate_scratch;                // cramgpu_mate_link: name tables
     DevPool slice_scratch, slice_in;     // cramgpu_slice_headers: accumulators, staged inputs of the host variant
     void *pin_slice = nullptr; size_t pin_slice_cap = 0; cudaEvent_t ev_slice = nullptr;

@@ -465,3 +465,9 @@ _lib.SIGNATURES.update({
     'cramgpu_bam_pack_dev': (C.c_int, [C.c_void_p, C.POINTER(BamRecords), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p),
                                        C.c_void_p, C.c_void_p]),
 })
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_blocks_frame_dev': (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, i32p, u8p, u8p,
+                                           C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p), C.c_void_p]),
+})

@@ -655,6 +655,21 @@ int cramgpu_bam_unpack_dev(cramgpu_ctx *ctx, const uint8_t *d_bam, const uint64_
 int cramgpu_bam_pack_dev(cramgpu_ctx *ctx, const cramgpu_bam_records *in, uint8_t **d_bam, uint64_t *bam_len, uint64_t **d_rec_off,
                          int32_t *d_status, void *stream);
 
+/* ------------------------------------------------------------------ the CRAM v3 block layer (block part)
+ *
+ * Block.write(3, os) [htsjdk Block.java:272-294] for blocks whose (compressed) bytes are in device memory -- e.g. the output of
+ * cramgpu_rans_encode_dev (d_comp, d_out_off, d_out_len there): method | content type | ITF8 content id | ITF8 compressed size |
+ * ITF8 raw size | data | CRC32 of all of it, little endian [CRC32OutputStream.java:50-51].  method / content_type =
+ * BlockCompressionMethod / BlockContentType ordinals (RAW 0 GZIP 1 BZIP2 2 LZMA 3 RANS 4; EXTERNAL 4, CORE 5, ...).
+ * content_id, method, content_type: HOST arrays [nblocks]; the other inputs DEVICE arrays (d_comp NULL: d_comp_off holds absolute
+ * addresses).  Result: the framed blocks back to back, every block at a multiple of 16, in device memory owned by ctx (valid
+ * until the next call); d_out_off[i] (DEVICE, [nblocks+1]) = start of block i, its length = header + data + 4.  One stream
+ * synchronisation inside.
+ */
+int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_comp, const uint64_t *d_comp_off,
+                             const uint32_t *d_comp_len, const uint32_t *d_raw_len, const int32_t *content_id, const uint8_t *method,
+                             const uint8_t *content_type, uint8_t **d_out, uint64_t *out_len, uint64_t **d_out_off, void *stream);
+
 /* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
  *
  * Containers are independent and are dealt round-robin: the container with global ordinal g is converted by

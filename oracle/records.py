@@ -640,3 +640,17 @@ def bam_parse(rec):
     quals = rec[o:o + lseq]; o += lseq
     return dict(block_size=bs, ref_id=ref, pos=pos + 1, name=name, mapq=mapq, bin=bin_, flag=flag, cigar=cig, mate_ref_id=mref,
                 mate_pos=mpos + 1, tlen=tlen, bases=bases, quals=quals, tags=rec[o:4 + bs])
+
+
+# ---------------------------------------------------------------------------------------------- CRAM v3 blocks (the block layer)
+BLOCK_METHOD = {'RAW': 0, 'GZIP': 1, 'BZIP2': 2, 'LZMA': 3, 'RANS': 4}          # BlockCompressionMethod.ordinal()
+BLOCK_CONTENT = {'FILE_HEADER': 0, 'COMPRESSION_HEADER': 1, 'MAPPED_SLICE': 2, 'RESERVED': 3, 'EXTERNAL': 4, 'CORE': 5}
+
+
+def cram_block_v3(method, content_type, content_id, raw_len, data):
+    """Block.write(3, os) [htsjdk Block.java:272-294]: method, content type, ITF8 content id, ITF8 compressed size, ITF8 raw size,
+    the (compressed) bytes, and the CRC32 of everything before it, little endian [CRC32OutputStream.java:50-51]"""
+    import struct
+    import zlib
+    b = bytes([method, content_type]) + itf8(content_id) + itf8(len(data)) + itf8(raw_len) + bytes(data)
+    return b + struct.pack('<I', zlib.crc32(b) & 0xFFFFFFFF)

@@ -186,3 +186,18 @@ def test_cigar_rebuild_and_bam_records_match_jar(G):
     assert ops >= set('MIDNSHP')
     with pytest.raises(ValueError):
         orec.bam_record(0, 1, b'x', 0, 0, [(1, 'M')], -1, 0, 0, b'J', b'#')
+
+
+def test_block_layer_matches_jar(G):
+    """SURVEY 8f-5, the block layer: the external blocks of the rANS-coded series as the jar's Block.write(3, ...) wrote them"""
+    from oracle import rans as orans
+    g, ref, conts = G
+    n = 0
+    for c, rd, series in conts:
+        for cid, blk in c['blocks_v3'].items():
+            raw = series[int(cid)]
+            comp = orans.compress(raw, blk['order'])
+            got = orec.cram_block_v3(orec.BLOCK_METHOD['RANS'], orec.BLOCK_CONTENT['EXTERNAL'], int(cid), len(raw), comp)
+            assert got == base64.b64decode(blk['block']), (c['tag'], cid)
+            n += 1
+    assert n >= 20
