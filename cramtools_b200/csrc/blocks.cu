@@ -31,7 +31,7 @@ struct FrameArgs {
     uint8_t *out;
     uint32_t *chunk_crc;              // [sum of chunks] raw registers
     const uint64_t *chunk_first;      // first chunk slot of every block
-    uint32_t shift64[32], shift16k[32];
+    uint32_t shiftp[8][32], shift16k[32];      // shift by 64 << k bytes (k = 0..7), by 16 384 bytes
 };
 
 __device__ __forceinline__ uint32_t itf8_bytes(uint32_t v) { return v < (1u << 7) ? 1u : v < (1u << 14) ? 2u : v < (1u << 21) ? 3u : v < (1u << 28) ? 4u : 5u; }
@@ -64,14 +64,22 @@ __device__ __forceinline__ uint32_t shift_reg(uint32_t r, const uint32_t *cols)
     return v;
 }
 
-// grid (chunks of the longest block, nblocks); chunk index counts from the block's start, boundaries from its end
+// one CTA per chunk of any block (chunk_first[] says whose: a grid of blocks x chunks-of-the-longest would be mostly CTAs
+// with nothing to do); chunk index counts from the block's start, boundaries from its end
 __global__ void __launch_bounds__(FR_THREADS) k_frame_write(FrameArgs a)
 {
     __shared__ uint32_t T[256];
     __shared__ uint8_t hdr[20];
     __shared__ uint32_t part[FR_THREADS];
     __shared__ uint32_t s_hlen;
-    const uint32_t b = blockIdx.y, tid = threadIdx.x;
+    const uint32_t tid = threadIdx.x;
+    uint32_t b;
+    {
+        uint32_t lo_b = 0, hi_b = a.nblocks;                          // largest b with chunk_first[b] <= blockIdx.x
+        while (hi_b - lo_b > 1) { const uint32_t mid = (lo_b + hi_b) >> 1; if (a.chunk_first[mid] <= blockIdx.x) lo_b = mid; else hi_b = mid; }
+        b = lo_b;
+    }
+    const uint32_t ck = blockIdx.x - (uint32_t)a.chunk_first[b];
     const uint32_t clen = a.comp_len[b];
     if (tid == 0) {
         uint32_t h = 0;
@@ -88,31 +96,45 @@ __global__ void __launch_bounds__(FR_THREADS) k_frame_write(FrameArgs a)
     __syncthreads();
     const uint32_t hlen = s_hlen, body = hlen + clen;
     const uint32_t nch = (body + FR_CHUNK - 1) / FR_CHUNK;
-    if (blockIdx.x >= nch) return;
-    // chunk blockIdx.x covers [lo, hi) of the body; the first chunk is the short one
+    if (ck >= nch) return;
+    // chunk ck covers [lo, hi) of the body; the first chunk is the short one
     const uint32_t first_len = body - (nch - 1) * FR_CHUNK;
-    const uint32_t lo = blockIdx.x == 0 ? 0u : first_len + (blockIdx.x - 1) * FR_CHUNK, hi = blockIdx.x == 0 ? first_len : lo + FR_CHUNK;
+    const uint32_t lo = ck == 0 ? 0u : first_len + (ck - 1) * FR_CHUNK, hi = ck == 0 ? first_len : lo + FR_CHUNK;
     const uint8_t *src = (a.comp ? a.comp : (const uint8_t *)0) + a.comp_off[b];
     uint8_t *dst = a.out + a.out_off[b];
-    for (uint32_t p = lo + tid; p < hi; p += FR_THREADS) dst[p] = p < hlen ? hdr[p] : src[p - hlen];
-    // pieces of 64 bytes counted from the chunk's end: piece t of np covers [hi - (np - t) * 64, ...), the first one short
+    // pieces of 64 bytes counted from the chunk's end: piece t of np covers [hi - (np - t) * 64, ...), the first one short.
+    // The chunk passes through shared memory on its way out (contiguous reads and writes), a piece per 68-byte row so that the
+    // threads' byte-by-byte walks down their rows hit different banks.
+    __shared__ uint8_t stage[FR_THREADS * 68];
     const uint32_t np = (hi - lo + FR_PIECE - 1) / FR_PIECE;
+    for (uint32_t p = lo + tid; p < hi; p += FR_THREADS) {
+        const uint8_t byte = p < hlen ? hdr[p] : src[p - hlen];
+        dst[p] = byte;
+        const uint32_t d = hi - 1 - p;                                     // distance from the chunk's end
+        stage[(np - 1 - d / FR_PIECE) * 68 + (FR_PIECE - 1 - d % FR_PIECE)] = byte;
+    }
+    __syncthreads();
     uint32_t reg = 0;
     if (tid < np) {
-        const uint32_t p_hi = hi - (np - 1 - tid) * FR_PIECE, p_lo = tid == 0 ? lo : p_hi - FR_PIECE;
-        reg = (blockIdx.x == 0 && tid == 0) ? ~0u : 0u;
-        for (uint32_t p = p_lo; p < p_hi; p++) {
-            const uint32_t byte = p < hlen ? hdr[p] : src[p - hlen];
-            reg = T[(reg ^ byte) & 0xFF] ^ (reg >> 8);
-        }
+        const uint32_t first = tid == 0 ? FR_PIECE - ((hi - lo) - (np - 1) * FR_PIECE) : 0u;     // the first piece starts inside its row
+        reg = (ck == 0 && tid == 0) ? ~0u : 0u;
+        for (uint32_t i = first; i < FR_PIECE; i++) reg = T[(reg ^ stage[tid * 68 + i]) & 0xFF] ^ (reg >> 8);
     }
-    part[tid] = reg;
+    // combine as a tree over e = distance from the chunk's end: at level k the piece run ending at e (a multiple of 2^(k+1))
+    // takes in the run of 64 << k bytes before it, which is (e + 2^k); a missing left run is the empty one (register 0)
+    part[tid < np ? (np - 1 - tid) : tid] = reg;                          // part[] indexed by e; slots >= np hold 0
     __syncthreads();
-    if (tid == 0) {
-        uint32_t r = part[0];
-        for (uint32_t t = 1; t < np; t++) r = shift_reg(r, a.shift64) ^ part[t];
-        a.chunk_crc[a.chunk_first[b] + blockIdx.x] = r;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t stride = 1u << k;
+        uint32_t v = 0;
+        const bool mine = (tid & (2 * stride - 1)) == 0 && tid + stride < FR_THREADS;
+        if (mine) v = shift_reg(part[tid + stride], a.shiftp[k]) ^ part[tid];
+        __syncthreads();
+        if (mine) part[tid] = v;
+        __syncthreads();
     }
+    if (tid == 0) a.chunk_crc[blockIdx.x] = part[0];
 }
 
 __global__ void __launch_bounds__(256) k_frame_crc(FrameArgs a, const uint32_t *nchunks)
@@ -207,10 +229,9 @@ extern "C" int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, cons
     a.nblocks = nblocks; a.comp = d_comp; a.comp_off = d_comp_off; a.comp_len = d_comp_len; a.raw_len = d_raw_len;
     a.content_id = (const int32_t *)(S + o_id); a.method = S + o_m; a.content_type = S + o_t;
     a.size = (uint32_t *)(S + o_size); a.out_off = (const uint64_t *)(S + o_off); a.chunk_first = (const uint64_t *)(S + o_cf);
-    static uint32_t c64[32], c16k[32];
-    static bool cols_done = false;
-    if (!cols_done) { shift_columns(FR_PIECE, c64); shift_columns(FR_CHUNK, c16k); cols_done = true; }
-    memcpy(a.shift64, c64, sizeof c64); memcpy(a.shift16k, c16k, sizeof c16k);
+    struct Cols { uint32_t p[8][32], c16k[32]; Cols() { for (int k = 0; k < 8; k++) shift_columns(FR_PIECE << k, p[k]); shift_columns(FR_CHUNK, c16k); } };
+    static const Cols cols;                                          // computed once (thread-safe static)
+    memcpy(a.shiftp, cols.p, sizeof cols.p); memcpy(a.shift16k, cols.c16k, sizeof cols.c16k);
     uint32_t *d_nch = (uint32_t *)(S + o_nch);
     LAUNCH(ctx, st, "k_frame_size", k_frame_size<<<(nblocks + 255) / 256, 256, 0, st>>>(a, d_nch));
     CUDA_TRY(ctx, cudaMemsetAsync(S + o_mx, 0, 16, st));
@@ -227,10 +248,8 @@ extern "C" int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, cons
     if (int rc = pool_reserve(ctx, ctx->frame_out, co.off)) return rc;
     uint8_t *O = (uint8_t *)ctx->frame_out.p;
     a.out = O + q_out; a.chunk_crc = (uint32_t *)(O + q_crc);
-    // grid.x: chunks of the longest block; CTAs beyond a block's own count leave at once
-    const uint32_t gx = (uint32_t)std::max<uint64_t>(max_chunks, 1);
-    if (nblocks > 65535) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "more than 65535 blocks in one call");
-    LAUNCH(ctx, st, "k_frame_write", k_frame_write<<<dim3(gx, nblocks), FR_THREADS, 0, st>>>(a));
+    (void)max_chunks;
+    if (nchunks_total) LAUNCH(ctx, st, "k_frame_write", k_frame_write<<<(uint32_t)nchunks_total, FR_THREADS, 0, st>>>(a));
     LAUNCH(ctx, st, "k_frame_crc", k_frame_crc<<<(nblocks + 255) / 256, 256, 0, st>>>(a, d_nch));
     CUDA_TRY(ctx, cudaGetLastError());
     *d_out = a.out; *out_len = total; *d_out_off = (uint64_t *)(S + o_off);
