@@ -173,6 +173,7 @@ def workload_config(args, n_cont, note=''):
                         'decode = rANS + base/quality restoration' % (n_cont, COVERAGE),
             'containers_per_gpu': n_cont, 'reads_per_container': READS_PER_CONTAINER, 'read_len': READ_LEN,
             'unique_containers': min(UNIQUE, n_cont), 'quality_model': 'lossless',
+            'reference': 'a separate copy of the synthetic contig per tile of %d containers (no cache reuse between tiles); resident on the device' % min(UNIQUE, n_cont),
             'l2': 'inputs larger than L2 (no flush needed)' if n_cont >= 64 else 'inputs may fit L2',
             'sharding': 'containers round-robin over ranks; all-gather of compressed sizes', 'note': note}
 
@@ -301,14 +302,16 @@ class Lane(object):
             self.t_names = tile_u8(rd['names'], np.uint8, int(no_all[-1]))
             self.t_noff = up(no_all, np.uint64)
             self.t_roff = up(np.arange(n_reads + 1, dtype=np.uint64) * READ_LEN, np.uint64)
-            self.t_ref = up(ref, np.uint8)
+            # every tile of the distinct containers reads its OWN copy of the reference (separate memory: no L2 reuse between tiles)
+            self.t_ref = up(ref, np.uint8).repeat(reps).contiguous()
             self.cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
-            self.ref_off = np.zeros(n_cont, np.uint64); self.ref_len = np.full(n_cont, ref.size, np.uint64)
+            tile_of = (np.arange(n_cont) // nu).astype(np.uint64)
+            self.ref_off = tile_of * np.uint64(ref.size); self.ref_len = np.full(n_cont, ref.size, np.uint64)
             R = self.R = rec.Reads()
             R.n_reads = n_reads; R.n_containers = n_cont
             R.cont_off = self.cont_off.ctypes.data_as(u64p); R.ref_off = self.ref_off.ctypes.data_as(u64p)
             R.ref_len = self.ref_len.ctypes.data_as(u64p)
-            R.ref = vp(self.t_ref.data_ptr()); R.ref_total = ref.size
+            R.ref = vp(self.t_ref.data_ptr()); R.ref_total = self.t_ref.numel()
             R.bases = vp(self.t_bases.data_ptr()); R.quals = vp(self.t_quals.data_ptr()); R.read_off = vp(self.t_roff.data_ptr())
             R.cigar = vp(self.t_cigar.data_ptr()); R.cigar_off = vp(self.t_coff.data_ptr()); R.pos = vp(self.t_pos.data_ptr())
             R.flag = vp(self.t_flag.data_ptr()); R.mapq = vp(self.t_mapq.data_ptr()); R.rflags = None
@@ -316,7 +319,7 @@ class Lane(object):
             p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
             ws = (p.min(axis=1) - 1)
             we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
-            self.win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64); self.win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
+            self.win_off = np.tile(ws, reps)[:n_cont].astype(np.uint64) + self.ref_off; self.win_len = np.tile(we - ws, reps)[:n_cont].astype(np.uint64)
             self.win_s0 = np.tile(ws, reps)[:n_cont].astype(np.int64)
             self.slice_start = np.tile(p.min(axis=1), reps)[:n_cont].astype(np.int32)
             # the record fields in front of the read features, packed on the device (cramgpu_host_series_pack_dev)
@@ -876,7 +879,7 @@ class E2EContext(object):
         N = self.N = rec.NormIn()
         N.n_reads = n_reads; N.n_containers = n_cont
         N.cont_off = inp['cont_off'].ctypes.data_as(u64p); N.win_off = inp['win_off'].ctypes.data_as(u64p); N.win_len = inp['win_len'].ctypes.data_as(u64p)
-        N.win_start0 = inp['win_s0'].ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(inp['ref'].ctypes.data); N.ref_total = inp['ref'].size
+        N.win_start0 = inp['win_s0'].ctypes.data_as(C.POINTER(C.c_int64)); N.ref = vp(inp['d_ref'].data_ptr()); N.ref_total = inp['d_ref'].numel()
         N.pos = vp(inp['a']['pos'].ctypes.data); N.read_off = vp(inp['a']['read_off'].ctypes.data); N.rflags = vp(self.rfl.ctypes.data)
         N.ba = None; N.qs = None                        # absolute device addresses in the unpacked read_qs_off / read_ba_off
         self.ms = {'features_encode_resident': 0.0, 'host_series_pack_resident': 0.0, 'rans_encode_batch': 0.0, 'rans_decode_batch': 0.0,
@@ -983,11 +986,11 @@ class E2EContext(object):
         small = int(self.slen.sum() - self.slen[:, KQS].sum() - self.slen[:, KBA].sum())
         ex_bytes = self.ex_bytes
         comp_bytes = int(self.out_len.sum())
-        self.h2d = int(2 * nb + inp['ref'].size + a['read_off'].nbytes + a['cigar_off'].nbytes + a['cigar'].nbytes + 7 * n_reads      # reads
+        self.h2d = int(2 * nb + a['read_off'].nbytes + a['cigar_off'].nbytes + a['cigar'].nbytes + 7 * n_reads      # reads
                        + (2 + 4 + 8 + 4) * n_reads                                                                        # record fields: flag, pos, read_off, read group
                        + comp_bytes                                                                                       # compressed blocks, decode side
                        + small                                                                                            # the series the host inflated, for row P
-                       + inp['ref'].size + (4 + 8 + 1) * n_reads + 8 * (n_reads + 1) + n_reads)                          # decode side: pos, read_off, rflags (twice: unpack, normaliser)
+                       + (4 + 8 + 1) * n_reads + 8 * (n_reads + 1) + n_reads)                          # decode side: pos, read_off, rflags (twice: unpack, normaliser)
         self.d2h = int(n_reads + 8 * inp['n_cont'] + small                                                                # force_qs, matrix, small series
                        + self.hs_down                                                                                     # record-field series the host gzips
                        + comp_bytes + ex_bytes + 2 * nb + 5 * n_reads + n_reads)                                          # blocks; bases, qualities, star, status; MAPQ
@@ -1020,24 +1023,27 @@ def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device)
         return t.numpy().view(dt)
     trd = tile_reads(rd, nu, n_cont)
     n_reads = n_cont * READS_PER_CONTAINER
-    ref = pinned(ref)
+    reps = (n_cont + nu - 1) // nu
+    ref_len1 = int(ref.size)
+    # the reference is static: uploaded once, a copy per tile of containers, and handed to the calls as a device pointer
+    d_ref = torch.from_numpy(np.ascontiguousarray(ref)).to('cuda').repeat(reps).contiguous()
+    keep_pinned.append(d_ref)
     cont_off = (np.arange(n_cont + 1, dtype=np.uint64) * READS_PER_CONTAINER)
-    ref_off = np.zeros(n_cont, np.uint64); ref_len = np.full(n_cont, ref.size, np.uint64)
+    ref_off = (np.arange(n_cont) // nu).astype(np.uint64) * np.uint64(ref_len1); ref_len = np.full(n_cont, ref_len1, np.uint64)
     a = dict(bases=pinned(trd['bases']), quals=pinned(trd['quals']), read_off=pinned(trd['read_off'].astype(np.uint64)),
              cigar=pinned(trd['cigar'].astype(np.uint32)), cigar_off=pinned(trd['cigar_off'].astype(np.uint64)),
              pos=pinned(trd['pos'].astype(np.int32)), flag=pinned(trd['flag'].astype(np.uint16)), mapq=pinned(trd['mapq'].astype(np.uint8)))
     R = rec.Reads()
     R.n_reads = n_reads; R.n_containers = n_cont
     R.cont_off = cont_off.ctypes.data_as(u64p); R.ref_off = ref_off.ctypes.data_as(u64p); R.ref_len = ref_len.ctypes.data_as(u64p)
-    R.ref = vp(ref.ctypes.data); R.ref_total = ref.size
+    R.ref = vp(d_ref.data_ptr()); R.ref_total = d_ref.numel()
     for k, v in a.items():
         setattr(R, k, vp(v.ctypes.data))
     R.rflags = None
     NX = len(EXTRA); NB = 2 + NX
     rg = pinned(trd['read_group'].astype(np.int32))
     p = rd['pos'].astype(np.int64).reshape(nu, READS_PER_CONTAINER)
-    reps = (n_cont + nu - 1) // nu
-    ws = (p.min(axis=1) - 1); we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref.size)
+    ws = (p.min(axis=1) - 1); we = np.minimum(p.max(axis=1) - 1 + READ_LEN + 8, ref_len1)
     KQS, KBA = rec.SERIES.index('QS'), rec.SERIES.index('BA')
     slice_start = np.tile(p.min(axis=1), reps)[:n_cont].astype(np.int32)
     H = rec.HostFields()
@@ -1047,11 +1053,11 @@ def run_e2e(args, ref, rd, nu, n_cont, world, barrier, depth, comp_hint, device)
     H.flag = vp(a['flag'].ctypes.data); H.pos = vp(a['pos'].ctypes.data); H.read_off = vp(a['read_off'].ctypes.data); H.read_group = vp(rg.ctypes.data)
     KX = [rec.HOST_SERIES.index(nm) for nm, _ in EXTRA]
     hs_mask = sum(1 << k for k in range(len(rec.HOST_SERIES)) if k not in KX and rec.HOST_SERIES[k] != 'RN')
-    inp = dict(n_cont=n_cont, n_reads=n_reads, NB=NB, R=R, a=a, ref=ref, cont_off=cont_off, keep=[ref_off, ref_len, rg, slice_start],
+    inp = dict(n_cont=n_cont, n_reads=n_reads, NB=NB, R=R, a=a, d_ref=d_ref, cont_off=cont_off, keep=[ref_off, ref_len, rg, slice_start],
                H=H, KX=KX, hs_mask=hs_mask,
                order=np.tile(np.array([1, 1] + [o for _, o in EXTRA], np.uint8), n_cont), KQS=KQS, KBA=KBA,
                host_series=sum(1 << k for k in range(len(rec.SERIES)) if k not in (KQS, KBA)), comp_hint=comp_hint,
-               win_off=np.tile(ws, reps)[:n_cont].astype(np.uint64), win_len=np.tile(we - ws, reps)[:n_cont].astype(np.uint64),
+               win_off=np.tile(ws, reps)[:n_cont].astype(np.uint64) + ref_off, win_len=np.tile(we - ws, reps)[:n_cont].astype(np.uint64),
                win_s0=np.tile(ws, reps)[:n_cont].astype(np.int64))
     depth = max(1, depth)
     ctxs = [cramtools_b200.Context(device) for _ in range(depth)]
