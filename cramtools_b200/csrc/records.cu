@@ -1,19 +1,27 @@
 // records.cu -- per-record work of the CRAM slice hot path for sm_100a.
 //
-// Encode (one warp per read, lanes over consecutive bases so every load of bases / qualities / reference is coalesced):
-//   k_rec_walk<false>  count pass: features per read, bytes per series, substitution histogram, force-preserve flag
-//   k_rec_matrix       SubstitutionMatrix ranking per container            [SubstitutionMatrix.java:42-57,141-169]
-//   k_rec_scan         per-container exclusive scans of the 14 per-read counters
-//   k_rec_layout       absolute offsets of every (container, series) region, feature / payload bases
-//   k_rec_walk<true>   write pass: feature arrays + the series bytes       [Writer.java:180-258]
-// Both passes run the same walk over the CIGAR, restating
+// Encode: two passes over the records (count, then write) around per-container scans; in each pass a record is handled by the
+// cheapest kernel that can handle it:
+//   k_ref_norm           normalizeBase over the reference windows, once per call
+//   k_rec_simple<W, PB>  one THREAD per record, in order: classifies the record; `<len>M` records are compared with the
+//                        normalised reference as aligned words; records with several CIGAR operators and the odd ones go to lists
+//   k_rec_multi<W, PB>   the listed records, one thread per entry, all CIGAR operators (PB: quality models with base categories,
+//                        evaluated bit-parallel on groups of four bases: pb_mask / pb_planes)
+//   k_rec_walk<W>        one WARP per record (ballots, warp compaction): the fallback for region overhang and odd CIGARs
+//   k_rec_matrix         SubstitutionMatrix ranking per container            [SubstitutionMatrix.java:42-57,141-169]
+//   k_rec_scan / k_rec_layout   per-container exclusive scans of the 14 per-record counters; series-major region offsets
+//   k_rec_forced_flat / k_rec_forced_scores   the preserved score arrays under a lossy model
+//   k_rec_bin_fault      (only after a BIN treatment met a score >= 110) marks the records the reference throws for
+// All of them restate
 //   Sam2CramRecordFactory.createVariations / addSubstitutionsAndMaskedBases [Sam2CramRecordFactory.java:205-335]
 //   QualityScorePreservation.addQualityScores / addQS     (lossy/QualityScorePreservation.java:276-301,332-489)
-// Mismatch positions come from __ballot_sync; positions inside the feature list and inside each series come from
-// popc of the ballots (warp compaction), FP byte offsets from a warp prefix sum of the ITF8 lengths.
+//   Writer.write, feature part                            [Writer.java:180-258]
 //
 // Decode:
-//   k_norm             CramNormalizer.restoreReadBases / restoreQualityScores (build/CramNormalizer.java:287-434)
+//   k_unpack             series -> feature arrays: the feature part of CramRecordReader.read (row P)
+//   k_norm_simple        thread per record: stored score arrays and bases of records without features (warp-wide copies when
+//                        32 neighbouring records are contiguous); the others go to a list
+//   k_norm               the list: CramNormalizer.restoreReadBases / restoreQualityScores (build/CramNormalizer.java:287-434)
 #include "internal.cuh"
 
 #define NCNT 14
