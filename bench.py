@@ -338,6 +338,9 @@ class Lane(object):
             SI.bases = vp(self.t_bases.data_ptr()); SI.read_off = vp(self.t_roff.data_ptr()); SI.rflags = None; SI.ref_id = None
             SI.pos = vp(self.t_pos.data_ptr()); SI.flag = vp(self.t_flag.data_ptr())
             SI.scores = vp(self.t_quals.data_ptr()) if self.npol < 0 else None      # lossless: record.qualityScores = the qualities
+            SI.ref = vp(self.t_ref.data_ptr()); SI.ref_total = self.t_ref.numel()   # Slice.refMD5
+            SI.ref_off = self.ref_off.ctypes.data_as(u64p); SI.ref_len = self.ref_len.ctypes.data_as(u64p)
+            self.ref_unique = ref
             self.slice_hdr = torch.zeros(n_cont * C.sizeof(rec.SliceHeader), dtype=torch.uint8, device=dev)
             self.uniq_reads = (rd, nu)
             NHS = len(rec.HOST_SERIES)
@@ -473,7 +476,7 @@ class Lane(object):
             assert np.array_equal(got, want), 'record-field series round trip mismatch'
         # slice headers: record / base counts of every slice, and the digests of the first distinct containers against zlib
         hdr = np.frombuffer(self.slice_hdr.cpu().numpy().tobytes(), dtype=np.dtype([('seq', '<i4'), ('start', '<i4'), ('span', '<i4'), ('nrec', '<u4'),
-                                                                                   ('bases', '<u8'), ('bd', '<u4'), ('sd', '<u4')]))
+                                                                                   ('bases', '<u8'), ('bd', '<u4'), ('sd', '<u4'), ('md5', 'V16')]))
         assert (hdr['nrec'] == READS_PER_CONTAINER).all() and (hdr['bases'] == READS_PER_CONTAINER * READ_LEN).all() and (hdr['seq'] == 0).all()
         assert (hdr['start'] == self.slice_start).all(), 'slice alignment start'
         import zlib
@@ -486,6 +489,10 @@ class Lane(object):
             if lossless:
                 q = urd['quals'][lo:lo + READS_PER_CONTAINER * READ_LEN].reshape(READS_PER_CONTAINER, READ_LEN)
                 assert int(hdr['sd'][c]) == sum(zlib.crc32(x.tobytes()) for x in q) & 0xFFFFFFFF, 'SD digest'
+            import hashlib
+            s0, sp = int(hdr['start'][c]), int(hdr['span'][c])
+            refb = self.ref_unique.tobytes()
+            assert bytes(hdr['md5'][c]) == hashlib.md5(refb[s0 - 1:s0 - 1 + min(sp, len(refb) - s0 + 1)]).digest(), 'slice reference MD5'
         if self.use_unpack:
             got = np.empty(n_reads, np.uint8)
             self.ctx.check(self.ctx.lib.cramgpu_copy_to_host(self.ctx.handle, vp(got.ctypes.data), self.d_mapq, C.c_uint64(n_reads), self._sp()))
@@ -704,12 +711,12 @@ def run_ours(args):
     lanes[0].with_digests = False
     ms_dig = max_over_ranks(ms_dig)
     framing_leg = block_framing_leg(lanes[0])
-    digest_leg = {'row': 'ContainerFactory.buildSlice :138-176 (nofRecords, bases, sequenceId, alignment start/span, BD, SD)',
+    digest_leg = {'row': 'ContainerFactory.buildSlice :138-176 (nofRecords, bases, sequenceId, alignment start/span, BD, SD) + Slice.setRefMD5',
                   'ms_per_step_unpipelined_with_digests': ms_dig, 'ms_per_step_unpipelined_without': ms_unpip,
-                  'k_slice_digest_ms': round(kdig.get('k_slice_digest', 0.0), 4), 'k_slice_finish_ms': round(kdig.get('k_slice_finish', 0.0), 4),
+                  'k_slice_digest_ms': round(kdig.get('k_slice_digest', 0.0), 4), 'k_slice_finish_ms': round(kdig.get('k_slice_finish', 0.0), 4), 'k_slice_md5_ms': round(kdig.get('k_slice_md5', 0.0), 4),
                   'bytes_read_per_step': 2.0 * n_reads * READ_LEN,
                   'GBps': 2.0 * n_reads * READ_LEN / max(kdig.get('k_slice_digest', 1e9), 1e-9) / 1e6,
-                  'verified': 'record / base counts and alignment start of every slice; BD and SD of the first two slices against zlib.crc32',
+                  'verified': 'record / base counts and alignment start of every slice; BD and SD of the first two slices against zlib.crc32, their reference MD5 against hashlib',
                   'in_default_timed_step': False}
 
     # ---- the other configurations north_star names, each a short unpipelined run of the same step

@@ -32,6 +32,8 @@ struct SliceArgs {
     const uint16_t *flag;
     SliceAcc *acc;
     cramgpu_slice_header *out;
+    const uint8_t *ref;                // optional: slice reference MD5
+    const uint64_t *ref_off, *ref_len; // device copies
 };
 
 // CRC32 one byte at a time, T = the 256-entry table replicated 32 times: entry i of lane l at T[32 * i + l], so that the 32
@@ -226,7 +228,74 @@ __global__ void k_slice_finish(SliceArgs a)
         h.alignment_span = s.max_end - h.alignment_start + 1;                                       // [:174-175]
         if (h.alignment_span < 0) h.alignment_span = 0;                                             // CramSerilization.java:184-186
     }
+    for (int k = 0; k < 16; k++) h.ref_md5[k] = 0;
     a.out[c] = h;
+}
+
+// MD5 (RFC 1321) of the slice's reference span, one thread per slice: Slice.setRefMD5 [Slice.java:145-159] ->
+// SequenceUtil.calculateMD5 [SequenceUtil.java:962-966].  A slice's span is tens of kilobases: a few hundred 64-byte blocks, a
+// strictly sequential hash -- all slices of the batch run side by side.
+__constant__ uint32_t MD5_K[64] = {
+    0xd76aa478, 0xe8c7b756, 0x242070db, 0xc1bdceee, 0xf57c0faf, 0x4787c62a, 0xa8304613, 0xfd469501, 0x698098d8, 0x8b44f7af, 0xffff5bb1,
+    0x895cd7be, 0x6b901122, 0xfd987193, 0xa679438e, 0x49b40821, 0xf61e2562, 0xc040b340, 0x265e5a51, 0xe9b6c7aa, 0xd62f105d, 0x02441453,
+    0xd8a1e681, 0xe7d3fbc8, 0x21e1cde6, 0xc33707d6, 0xf4d50d87, 0x455a14ed, 0xa9e3e905, 0xfcefa3f8, 0x676f02d9, 0x8d2a4c8a, 0xfffa3942,
+    0x8771f681, 0x6d9d6122, 0xfde5380c, 0xa4beea44, 0x4bdecfa9, 0xf6bb4b60, 0xbebfbc70, 0x289b7ec6, 0xeaa127fa, 0xd4ef3085, 0x04881d05,
+    0xd9d4d039, 0xe6db99e5, 0x1fa27cf8, 0xc4ac5665, 0xf4292244, 0x432aff97, 0xab9423a7, 0xfc93a039, 0x655b59c3, 0x8f0ccc92, 0xffeff47d,
+    0x85845dd1, 0x6fa87e4f, 0xfe2ce6e0, 0xa3014314, 0x4e0811a1, 0xf7537e82, 0xbd3af235, 0x2ad7d2bb, 0xeb86d391};
+__constant__ uint8_t MD5_S[64] = {7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 7, 12, 17, 22, 5, 9, 14, 20, 5, 9, 14, 20, 5, 9, 14, 20, 5, 9, 14, 20,
+                                  4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23, 4, 11, 16, 23, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21, 6, 10, 15, 21};
+
+__device__ __forceinline__ void md5_block(uint32_t st[4], const uint32_t w[16])
+{
+    uint32_t A = st[0], B = st[1], Cc = st[2], D = st[3];
+#pragma unroll
+    for (int i = 0; i < 64; i++) {
+        uint32_t F; int g;
+        if (i < 16) { F = (B & Cc) | (~B & D); g = i; }
+        else if (i < 32) { F = (D & B) | (~D & Cc); g = (5 * i + 1) & 15; }
+        else if (i < 48) { F = B ^ Cc ^ D; g = (3 * i + 5) & 15; }
+        else { F = Cc ^ (B | ~D); g = (7 * i) & 15; }
+        F = F + A + MD5_K[i] + w[g];
+        A = D; D = Cc; Cc = B;
+        B = B + ((F << MD5_S[i]) | (F >> (32 - MD5_S[i])));
+    }
+    st[0] += A; st[1] += B; st[2] += Cc; st[3] += D;
+}
+
+__global__ void __launch_bounds__(64) k_slice_md5(SliceArgs a)
+{
+    const uint32_t c = blockIdx.x * 64 + threadIdx.x;
+    if (c >= a.n_containers) return;
+    const cramgpu_slice_header h = a.out[c];
+    if (h.sequence_id < 0 || h.alignment_start < 1) return;               // never set / "Empty slice ref md5" [:147-151]: zeros
+    const int64_t len_ref = (int64_t)a.ref_len[c];
+    int64_t span = min((int64_t)h.alignment_span, len_ref - h.alignment_start + 1);           // [:154]
+    if (span < 0) span = 0;
+    const uint8_t *p = a.ref + a.ref_off[c] + (h.alignment_start - 1);
+    uint32_t st[4] = {0x67452301u, 0xefcdab89u, 0x98badcfeu, 0x10325476u};
+    uint32_t w[16];
+    int64_t done = 0;
+    for (; done + 64 <= span; done += 64) {
+#pragma unroll
+        for (int k = 0; k < 16; k++)
+            w[k] = (uint32_t)p[done + 4 * k] | ((uint32_t)p[done + 4 * k + 1] << 8) | ((uint32_t)p[done + 4 * k + 2] << 16) | ((uint32_t)p[done + 4 * k + 3] << 24);
+        md5_block(st, w);
+    }
+    // the tail: remaining bytes, 0x80, zeros, the bit length (one or two blocks)
+    uint8_t tail[128];
+    const int rem = (int)(span - done);
+    for (int k = 0; k < 128; k++) tail[k] = 0;
+    for (int k = 0; k < rem; k++) tail[k] = p[done + k];
+    tail[rem] = 0x80;
+    const int tl = rem < 56 ? 64 : 128;
+    const uint64_t bits = (uint64_t)span * 8;
+    for (int k = 0; k < 8; k++) tail[tl - 8 + k] = (uint8_t)(bits >> (8 * k));
+    for (int b = 0; b < tl; b += 64) {
+        for (int k = 0; k < 16; k++)
+            w[k] = (uint32_t)tail[b + 4 * k] | ((uint32_t)tail[b + 4 * k + 1] << 8) | ((uint32_t)tail[b + 4 * k + 2] << 16) | ((uint32_t)tail[b + 4 * k + 3] << 24);
+        md5_block(st, w);
+    }
+    for (int k = 0; k < 16; k++) a.out[c].ref_md5[k] = (uint8_t)(st[k >> 2] >> (8 * (k & 3)));
 }
 
 }  // namespace
@@ -248,13 +317,23 @@ static int slice_impl(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slic
     if (n && !in->scores && (!in->force_qs || !in->read_qs_off || !in->streams))
         return ctx_fail(ctx, CRAMGPU_ERR_ARG, "scores == NULL needs force_qs, read_qs_off and streams");
     Carver cv;
-    const size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_acc = cv.take(sizeof(SliceAcc) * (size_t)nc);
+    const bool md5 = in->ref != nullptr;
+    if (md5 && (!in->ref_off || !in->ref_len)) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "ref needs ref_off and ref_len");
+    if (md5)
+        for (uint32_t c = 0; c < nc; c++)
+            if (in->ref_off[c] + in->ref_len[c] > in->ref_total) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "reference sequence of container %u outside ref", c);
+    const size_t up_bytes = 8 * (size_t)(nc + 1) + 16 * (size_t)nc;
+    const size_t o_cont = cv.take(up_bytes), o_acc = cv.take(sizeof(SliceAcc) * (size_t)nc);
     if (int rc = pool_reserve(ctx, ctx->slice_scratch, cv.off)) return rc;
     uint8_t *S = (uint8_t *)ctx->slice_scratch.p;
-    if (int rc = pinned_reserve(ctx, &ctx->pin_slice, &ctx->pin_slice_cap, 8 * (size_t)(nc + 1) + sizeof(cramgpu_slice_header) * (size_t)nc + 64)) return rc;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_slice, &ctx->pin_slice_cap, rup(up_bytes, 64) + sizeof(cramgpu_slice_header) * (size_t)nc + 64)) return rc;
     CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_slice));              // the previous call's upload has left the pinned buffer
     memcpy(ctx->pin_slice, in->cont_off, 8 * (size_t)(nc + 1));
-    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_cont, ctx->pin_slice, 8 * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
+    if (md5) {
+        memcpy((uint8_t *)ctx->pin_slice + 8 * (size_t)(nc + 1), in->ref_off, 8 * (size_t)nc);
+        memcpy((uint8_t *)ctx->pin_slice + 8 * (size_t)(nc + 1) + 8 * (size_t)nc, in->ref_len, 8 * (size_t)nc);
+    }
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_cont, ctx->pin_slice, md5 ? up_bytes : 8 * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
     CUDA_TRY(ctx, cudaEventRecord(ctx->ev_slice, st));
     CUDA_TRY(ctx, cudaMemsetAsync(S + o_acc, 0, sizeof(SliceAcc) * (size_t)nc, st));
     SliceArgs a;
@@ -264,12 +343,14 @@ static int slice_impl(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slic
     a.read_off = in->read_off; a.feat_off = in->feat_off; a.read_qs_off = in->read_qs_off;
     a.ref_id = in->ref_id; a.pos = in->pos; a.f_pos = in->f_pos; a.f_val = in->f_val; a.f_aux = in->f_aux; a.flag = in->flag;
     a.acc = (SliceAcc *)(S + o_acc); a.out = d_out;
+    a.ref = in->ref; a.ref_off = (const uint64_t *)(S + o_cont + 8 * (size_t)(nc + 1)); a.ref_len = a.ref_off + nc;
     if (n) {
         const dim3 grid = nc <= 65535 ? dim3((uint32_t)((max_reads + SLICE_THREADS - 1) / SLICE_THREADS), nc)
                                       : dim3((uint32_t)((n + SLICE_THREADS - 1) / SLICE_THREADS), 1);
         LAUNCH(ctx, st, "k_slice_digest", k_slice_digest<<<grid, SLICE_THREADS, 0, st>>>(a));
     }
     LAUNCH(ctx, st, "k_slice_finish", k_slice_finish<<<(nc + 127) / 128, 128, 0, st>>>(a));
+    if (md5) LAUNCH(ctx, st, "k_slice_md5", k_slice_md5<<<(nc + 63) / 64, 64, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     return CRAMGPU_OK;
 }
@@ -319,6 +400,7 @@ extern "C" int cramgpu_slice_headers(cramgpu_ctx *ctx, const cramgpu_slice_in *i
     const size_t i_id = add(in->ref_id, 4 * n), i_pos = add(in->pos, 4 * n), i_fl = add(in->flag, 2 * n);
     const size_t i_op = add(in->f_op, nf), i_fp = add(in->f_pos, 4 * nf), i_fv = add(in->f_val, 4 * nf), i_fa = add(in->f_aux, 4 * nf);
     const size_t i_fo = add(in->feat_off, 8 * (n + 1)), i_fq = add(in->force_qs, n), i_qo = add(in->read_qs_off, 8 * n);
+    const size_t i_ref = add(in->ref, in->ref ? in->ref_total : 0);
     const size_t o_out = cv.take(sizeof(cramgpu_slice_header) * (size_t)nc);
     if (int rc = pool_reserve(ctx, ctx->slice_in, cv.off + 16)) return rc;
     uint8_t *D = (uint8_t *)ctx->slice_in.p;
@@ -332,9 +414,10 @@ extern "C" int cramgpu_slice_headers(cramgpu_ctx *ctx, const cramgpu_slice_in *i
     d.f_op = (const uint8_t *)at(i_op, in->f_op); d.f_pos = (const int32_t *)at(i_fp, in->f_pos); d.f_val = (const int32_t *)at(i_fv, in->f_val);
     d.f_aux = (const int32_t *)at(i_fa, in->f_aux); d.feat_off = (const uint64_t *)at(i_fo, in->feat_off);
     d.force_qs = (const uint8_t *)at(i_fq, in->force_qs); d.read_qs_off = (const uint64_t *)at(i_qo, in->read_qs_off);
+    d.ref = (const uint8_t *)at(i_ref, in->ref);
     cramgpu_slice_header *d_out = (cramgpu_slice_header *)(D + o_out);
     if (int rc = slice_impl(ctx, &d, d_out, st)) return rc;
-    uint8_t *ph = (uint8_t *)ctx->pin_slice + rup(8 * (size_t)(nc + 1), 64);
+    uint8_t *ph = (uint8_t *)ctx->pin_slice + rup(8 * (size_t)(nc + 1) + 16 * (size_t)nc, 64);
     CUDA_TRY(ctx, cudaMemcpyAsync(ph, d_out, sizeof(cramgpu_slice_header) * (size_t)nc, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
     memcpy(out, ph, sizeof(cramgpu_slice_header) * (size_t)nc);

@@ -360,12 +360,13 @@ class SliceIn(C.Structure):
     _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('bases', C.c_void_p), ('scores', C.c_void_p),
                 ('read_off', C.c_void_p), ('rflags', C.c_void_p), ('ref_id', C.c_void_p), ('pos', C.c_void_p), ('flag', C.c_void_p),
                 ('f_op', C.c_void_p), ('f_pos', C.c_void_p), ('f_val', C.c_void_p), ('f_aux', C.c_void_p), ('feat_off', C.c_void_p),
-                ('force_qs', C.c_void_p), ('read_qs_off', C.c_void_p), ('streams', C.c_void_p)]
+                ('force_qs', C.c_void_p), ('read_qs_off', C.c_void_p), ('streams', C.c_void_p),
+                ('ref', C.c_void_p), ('ref_total', C.c_uint64), ('ref_off', u64p), ('ref_len', u64p)]
 
 
 class SliceHeader(C.Structure):
     _fields_ = [('sequence_id', C.c_int32), ('alignment_start', C.c_int32), ('alignment_span', C.c_int32), ('n_records', C.c_uint32),
-                ('bases', C.c_uint64), ('bd', C.c_uint32), ('sd', C.c_uint32)]
+                ('bases', C.c_uint64), ('bd', C.c_uint32), ('sd', C.c_uint32), ('ref_md5', C.c_uint8 * 16)]
 
 
 _lib.SIGNATURES.update({
@@ -384,7 +385,7 @@ def slice_sha_tags():
 
 
 def slice_headers(bases, read_off, pos, flag, f_op, f_val, f_aux, feat_off, scores=None, rflags=None, ref_id=None, cont_off=None,
-                  f_pos=None, force_qs=None, read_qs_off=None, streams=None, ctx=None):
+                  f_pos=None, force_qs=None, read_qs_off=None, streams=None, ref=None, ref_off=None, ref_len=None, ctx=None):
     """ContainerFactory.buildSlice's header fields and BD / SD digests [ContainerFactory.java:138-176] for every slice of a
     batch, through cramgpu_slice_headers (host buffers; `streams` / force_qs / read_qs_off: device pointers of a feature
     call when scores is None).  -> list of dicts with sequence_id, alignment_start, alignment_span, n_records, bases, tags"""
@@ -403,11 +404,15 @@ def slice_headers(bases, read_off, pos, flag, f_op, f_val, f_aux, feat_off, scor
         setattr(I, k, _vp(v))
     for k, v in (('force_qs', force_qs), ('read_qs_off', read_qs_off), ('streams', streams)):
         setattr(I, k, v if (v is None or isinstance(v, int)) else _vp(v))
+    if ref is not None:
+        refa = _arr(ref, np.uint8)
+        roff = _arr(np.zeros(nc) if ref_off is None else ref_off, np.uint64); rlen = _arr(np.full(nc, refa.size) if ref_len is None else ref_len, np.uint64)
+        I.ref = _vp(refa); I.ref_total = refa.size; I.ref_off = roff.ctypes.data_as(u64p); I.ref_len = rlen.ctypes.data_as(u64p)
     out = (SliceHeader * max(nc, 1))()
     ctx.check(ctx.lib.cramgpu_slice_headers(ctx.handle, C.byref(I), out))
     s1, s5 = slice_sha_tags()
     return [dict(sequence_id=h.sequence_id, alignment_start=h.alignment_start, alignment_span=h.alignment_span, n_records=h.n_records,
-                 bases=h.bases, bd=h.bd, sd=h.sd,
+                 bases=h.bases, bd=h.bd, sd=h.sd, ref_md5=bytes(h.ref_md5),
                  tags={'BD': struct.pack('<I', h.bd), 'SD': struct.pack('<I', h.sd), 'B5': s5, 'S5': s5, 'B1': s1, 'S1': s1})
             for h in out[:nc]]
 

@@ -559,6 +559,11 @@ typedef struct cramgpu_slice_in {
     const uint8_t *force_qs;      /* scores == NULL only */
     const uint64_t *read_qs_off;  /* scores == NULL only */
     const uint8_t *streams;       /* scores == NULL only */
+    /* slice reference MD5 (optional: ref == NULL leaves ref_md5 zero): the reference as in cramgpu_reads */
+    const uint8_t *ref;           /* reference bases, raw (as ReferenceSource hands them out); host or device in the host variant */
+    uint64_t ref_total;           /* bytes in `ref` */
+    const uint64_t *ref_off;      /* HOST [n_containers] start of the slice's reference sequence inside `ref` */
+    const uint64_t *ref_len;      /* HOST [n_containers] its length */
 } cramgpu_slice_in;
 
 typedef struct cramgpu_slice_header {
@@ -568,6 +573,9 @@ typedef struct cramgpu_slice_header {
     uint32_t n_records;           /* Slice.nofRecords */
     uint64_t bases;               /* Slice.bases */
     uint32_t bd, sd;              /* tags BD and SD */
+    uint8_t ref_md5[16];          /* Slice.refMD5 as CramSerilization.convert sets it (CramSerilization.java:184-197, Slice.setRefMD5
+                                     [Slice.java:145-159]): MD5 of the reference bases [alignmentStart - 1, + min(span, length -
+                                     alignmentStart + 1)); 16 zero bytes for a multi-reference or unplaced slice, or without `ref` */
 } cramgpu_slice_header;
 
 /* out: HOST array of n_containers headers.  _dev: every pointer but cont_off is device memory, d_out is a DEVICE array,

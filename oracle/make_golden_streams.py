@@ -183,6 +183,24 @@ def build(reads, ref, coordinate_sorted, tag):
         tags.append([chr(tg & 0xFF) + chr((tg >> 8) & 0xFF), b64(v.a) if isinstance(v, JArray) else int(v.fields['value']) if isinstance(v, JObject) else v])
         t = t.fields.get('next')
     out['slice_tags'] = tags
+    # slice reference MD5 as CramSerilization.convert sets it after buildContainer (CramSerilization.java:184-197):
+    # skipped for a multi-reference slice, MD5 of nothing for an unmapped one, else Slice.setRefMD5(reference) [Slice.java:145-159]
+    # -> SequenceUtil.calculateMD5(ref, alignmentStart - 1, min(span, ref.length - alignmentStart + 1)) [SequenceUtil.java:962-966].
+    # (SequenceUtil's static initialiser compiles a regex the interpreter's `re` cannot; calculateMD5 does not touch it.)
+    vm.skip_clinit.add('htsjdk/samtools/util/SequenceUtil')
+    SL = 'htsjdk/samtools/cram/structure/Slice'
+    if sl.fields.get('alignmentSpan', 0) < 0:
+        sl.fields['alignmentSpan'] = 0
+    sid = sl.fields.get('sequenceId')
+    if sid == -2:
+        out['ref_md5'] = None
+    else:
+        sl.fields['refMD5'] = None
+        try:
+            vm.call(SL, 'setRefMD5', '([B)V', [sl, jbytes(b'' if sid == -1 else ref)])
+        except NotImplementedError:
+            pass                     # the debug log after the assignment [Slice.java:161-175] formats with BigInteger; refMD5 is set by then
+        out['ref_md5'] = b64(bytes(sl.fields['refMD5'].a))
     # SURVEY 8f-5 (the block layer around the coded series): Block.write [Block.java:272-294] of the external blocks the header
     # gives to rANS -- method, content type, ITF8 content id / compressed size / raw size, data, CRC32 (little endian) of all of it
     BLK = 'htsjdk/samtools/cram/structure/Block'

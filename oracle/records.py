@@ -77,6 +77,18 @@ SHA512_EMPTY = bytes.fromhex('cf83e1357eefb8bdf1542850d66d8007d620e4050b5715dc83
                              '47d0d13c5d85f2b0ff8318d2877eec2f63b931bd47417a81a538327af927da3e')
 
 
+def slice_ref_md5(ref, sequence_id, alignment_start, alignment_span):
+    """Slice.refMD5 as CramSerilization.convert leaves it (CramSerilization.java:184-197; Slice.setRefMD5 [Slice.java:145-159];
+    SequenceUtil.calculateMD5 [SequenceUtil.java:962-966]): 16 zero bytes for a multi-reference slice (never set) and for an
+    unplaced one, else MD5 of ref[alignmentStart - 1 : + min(span, len(ref) - alignmentStart + 1)]"""
+    import hashlib
+    if sequence_id < 0:
+        return bytes(16)
+    ref = bytes(ref)
+    span = min(alignment_span, len(ref) - alignment_start + 1)
+    return hashlib.md5(ref[alignment_start - 1:alignment_start - 1 + max(span, 0)]).digest()
+
+
 def slice_header(rd, ex, scores):
     """ContainerFactory.buildSlice's header fields and BD / SD digests for one slice.
     rd needs ref_id besides the usual arrays; ex = extract(rd, ref); scores = quality(rd, ref, spec)[1].

@@ -201,3 +201,19 @@ def test_block_layer_matches_jar(G):
             assert got == base64.b64decode(blk['block']), (c['tag'], cid)
             n += 1
     assert n >= 20
+
+
+def test_slice_ref_md5_matches_jar(G):
+    """Slice.refMD5 as the jar's Slice.setRefMD5 computed it for the golden slices (the span reaches past the reference end in
+    two of them: the min() of [Slice.java:154] is exercised); not set for the multi-reference slice"""
+    g, ref, conts = G
+    seen = 0
+    for c, rd, series in conts:
+        s = c['slice']
+        got = orec.slice_ref_md5(ref, s['sequence_id'], s['alignment_start'], s['alignment_span'])
+        if c['ref_md5'] is None:
+            assert s['sequence_id'] == -2 and got == bytes(16)
+        else:
+            assert got == base64.b64decode(c['ref_md5']), c['tag']
+            seen += 1
+    assert seen >= 2

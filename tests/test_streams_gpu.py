@@ -174,8 +174,9 @@ def test_slice_headers_and_digests_match_jar(R, G, gpu_ctx):
     cat, cont_off = _cat(conts)
     enc = R.features_encode(cat, ref, None, cont_off=cont_off, ctx=gpu_ctx)
     got = R.slice_headers(cat['bases'], cat['read_off'], cat['pos'], cat['flag'], enc.f_op, enc.f_val, enc.f_aux, enc.feat_off,
-                          scores=cat['quals'], rflags=cat['rflags'], ref_id=cat['ref_id'], cont_off=cont_off, ctx=gpu_ctx)
+                          scores=cat['quals'], rflags=cat['rflags'], ref_id=cat['ref_id'], cont_off=cont_off, ref=ref, ctx=gpu_ctx)
     for h, (c, rd, _) in zip(got, conts):
+        assert h['ref_md5'] == (bytes(16) if c['ref_md5'] is None else base64.b64decode(c['ref_md5'])), c['tag']      # Slice.setRefMD5
         for k in ('sequence_id', 'alignment_start', 'alignment_span', 'n_records', 'bases'):
             assert h[k] == c['slice'][k], (c['tag'], k, h[k], c['slice'][k])
         assert h['tags'] == {t: base64.b64decode(v) for t, v in c['slice_tags']}, c['tag']
@@ -226,10 +227,21 @@ def test_slice_headers_parity_with_oracle(R, gpu_ctx, spec):
         want.append(orec.slice_header(sub, ex, scores))
     scores = np.concatenate(all_scores)
     keys = ('sequence_id', 'alignment_start', 'alignment_span', 'n_records', 'bases', 'bd', 'sd')
+    # every slice with its own reference sequence inside one buffer (ref_off / ref_len), the second one cut short so that the
+    # span reaches past its end
+    ref3 = np.concatenate([ref, ref[::-1].copy(), ref])
+    roff = np.array([0, ref.size, 2 * ref.size, 0], np.uint64); rlen = np.array([ref.size, ref.size, ref.size, ref.size], np.uint64)
     got = R.slice_headers(rd['bases'], rd['read_off'], pos, flag, enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, scores=scores, rflags=rfl,
-                          ref_id=ref_id, cont_off=cont_off, ctx=gpu_ctx)
+                          ref_id=ref_id, cont_off=cont_off, ref=ref3, ref_off=roff, ref_len=rlen, ctx=gpu_ctx)
     for c in range(nc):
         assert {k: got[c][k] for k in keys} == {k: want[c][k] for k in keys}, (spec, c)
+        seq = ref3[int(roff[c]):int(roff[c]) + int(rlen[c])]
+        assert got[c]['ref_md5'] == orec.slice_ref_md5(seq, want[c]['sequence_id'], want[c]['alignment_start'], want[c]['alignment_span']), (spec, c)
+    short = int(want[0]['alignment_start']) + int(want[0]['alignment_span']) // 2
+    got_s = R.slice_headers(rd['bases'], rd['read_off'], pos, flag, enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, scores=scores, rflags=rfl,
+                            ref_id=ref_id, cont_off=cont_off, ref=ref3, ref_off=roff, ref_len=np.array([short, ref.size, ref.size, ref.size], np.uint64),
+                            ctx=gpu_ctx)
+    assert got_s[0]['ref_md5'] == orec.slice_ref_md5(ref3[:short], 0, want[0]['alignment_start'], want[0]['alignment_span'])
     assert [h['sequence_id'] for h in got] == [0, 2, -2, -1]
     # the same from the device-resident result of the feature call, everything else staged from the host
     got2 = R.slice_headers(rd['bases'], rd['read_off'], pos, flag, enc.f_op, enc.f_val, enc.f_aux, enc.feat_off, scores=None, rflags=rfl,
