@@ -678,7 +678,7 @@ __global__ void __launch_bounds__(32 * DEC1_WARPS) k_dec1(const BlockDesc *__res
             // put it (or lands in the unused byte in front of the ring half when nothing is held back).
 #pragma unroll 8
             for (uint32_t u = 0; u < DEC1_CH; u++) {
-                uint32_t m[NS], xs[NS], c0[NS], f0[NS], w1[NS], xn[NS], b1[NS], xf[NS], cf[NS], rf[NS];
+                uint32_t m[NS], xs[NS], c0[NS], f0[NS], w1[NS], xn[NS], b1[NS], xf[NS], cf[NS], rf[NS], dl[NS];
                 bool a[NS], n1[NS];
 #pragma unroll
                 for (int s = 0; s < NS; s++) {
@@ -696,6 +696,7 @@ __global__ void __launch_bounds__(32 * DEC1_WARPS) k_dec1(const BlockDesc *__res
                     const uint32_t f1 = w1[s] & 0xFFFFu;
                     const uint32_t d0 = m[s] - c0[s], d1 = d0 - f0[s];
                     a[s] = d0 >= f0[s];                                            // not the first candidate
+                    dl[s] = d1;                                                    // negative exactly when it is the first
                     const uint32_t p0 = f0[s] * xs[s] + d0, p1 = f1 * xs[s] + d1;  // [Decoding.java:35-48] for either candidate
                     xn[s] = a[s] ? p1 : p0;
                     n1[s] = xn[s] < RANS_L;
@@ -706,12 +707,14 @@ __global__ void __launch_bounds__(32 * DEC1_WARPS) k_dec1(const BlockDesc *__res
                 const bool rare = __any_sync(0xFFFFFFFFu, rl);
 #pragma unroll
                 for (int s = 0; s < NS; s++) {
-                    // this lane's byte is byte (bytes taken by the lower lanes of the group) of the window Wc; one byte-permute
-                    // shifts it into the state, or leaves the state alone (selector 0x3210) when the lane does not renormalise
+                    // this lane's byte is byte (bytes taken by the lower lanes of the group) of the window Wc; one byte-permute,
+                    // predicated on the lane renormalising at all, shifts it into the state
                     const uint32_t cnt = __popc(b1[s] & lm);
-                    xf[s] = prmt_raw(xn[s], Wc[s], n1[s] ? 0x2104u + cnt : 0x3210u);
+                    const uint32_t px = prmt_raw(xn[s], Wc[s], 0x2104u + cnt);
+                    xf[s] = n1[s] ? px : xn[s];
                     cf[s] = cur[s] + __popc(b1[s] & gm);
-                    rf[s] = prmt_raw(w1[s], 0u, a[s] ? 0x4443u : 0x4442u);         // r1 or r0
+                    // r1 or r0: byte 3 or 2 of w1; the selector comes from the sign of d1 in one instruction (LEA.HI.SX32)
+                    rf[s] = prmt_raw(w1[s], 0u, 0x4443u + (uint32_t)((int32_t)dl[s] >> 31));
                 }
                 if (__builtin_expect(rare, 0)) {
 #pragma unroll
