@@ -600,6 +600,81 @@ def block_framing_leg(ln):
             'verified': 'blocks 0, 1, 2 and the last against zlib.crc32', 'in_default_timed_step': False}
 
 
+def container_assembly_leg(ln):
+    """SURVEY 8f-5, container part: whole CRAM v3 containers (container header, compression header block, slice header block with
+    the digest tags, empty core block, the rANS blocks of the step) laid out on the device -- ContainerIO.writeContainer
+    [ContainerIO.java:152-209].  Verified structurally on the first and the last container (header CRC32, size field, block
+    count, every block's CRC32, the walk ends at the container's end); CUDA-event timed."""
+    import zlib
+    torch, rec, ctx = ln.torch, ln.rec, ln.ctx
+    vp = C.c_void_p
+    ln.with_digests = True
+    ln.encode()                                        # fills ln.slice_hdr (device) beside the coded blocks
+    ln.with_digests = False
+    ln.stream.synchronize()
+    n_cont, NB = ln.n_cont, ln.NB
+    ids = [rec.SERIES_CONTENT_ID['QS'], rec.SERIES_CONTENT_ID['BA']] + [rec.HOST_SERIES_CONTENT_ID[nm] for nm, _ in EXTRA]
+    cids = np.tile(np.array([0] + ids, np.int32), n_cont)                    # per container: the (empty) core block, then the series
+    method = np.tile(np.array([0] + [4] * NB, np.uint8), n_cont); ctype = np.tile(np.array([5] + [4] * NB, np.uint8), n_cont)
+    with torch.cuda.stream(ln.stream):
+        z64 = torch.zeros(n_cont, 1, dtype=torch.int64, device=ln.dev); z32 = torch.zeros(n_cont, 1, dtype=torch.int32, device=ln.dev)
+        t_off = torch.cat([z64, ln.e_off[:-1].view(n_cont, NB)], dim=1).contiguous()
+        t_len = torch.cat([z32, ln.e_len.view(n_cont, NB)], dim=1).contiguous()
+        t_raw = torch.cat([z32, torch.from_numpy(ln.in_len.view(np.int32).reshape(n_cont, NB).copy()).to(ln.dev)], dim=1).contiguous()
+    comp_header = bytes(range(170))                    # stands for CompressionHeader.toByteArray(): opaque to the device
+    grc = (np.arange(n_cont, dtype=np.uint64) * np.uint64(10000))
+    bf = (np.arange(n_cont + 1, dtype=np.uint32) * np.uint32(NB + 1))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 1e9
+    for _ in range(3):
+        ln.stream.synchronize()
+        e0.record(ln.stream)
+        out, olen, ooff = rec.containers_assemble(ln.slice_hdr.data_ptr(), grc, [comp_header] * n_cont, bf, ln.enc_out.data_ptr(), t_off.data_ptr(),
+                                                  t_len.data_ptr(), t_raw.data_ptr(), cids, method, ctype, tags=True, ctx=ctx, stream=ln._sp())
+        e1.record(ln.stream)
+        ln.stream.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    off = ln.dv.dev_to_numpy(ctx, ooff, n_cont + 1, np.uint64)
+
+    def itf8(b, o):
+        v = b[o]
+        if v < 0x80: return v, o + 1
+        if v < 0xC0: return ((v & 0x7F) << 8) | b[o + 1], o + 2
+        if v < 0xE0: return ((v & 0x3F) << 16) | (b[o + 1] << 8) | b[o + 2], o + 3
+        if v < 0xF0: return ((v & 0x1F) << 24) | (b[o + 1] << 16) | (b[o + 2] << 8) | b[o + 3], o + 4
+        return ((v & 0x0F) << 28) | (b[o + 1] << 20) | (b[o + 2] << 12) | (b[o + 3] << 4) | (b[o + 4] & 0x0F), o + 5
+
+    def ltf8(b, o):
+        n = 0
+        while n < 8 and b[o] & (0x80 >> n): n += 1
+        v = b[o] & (0xFF >> (n + 1)) if n < 8 else 0
+        for k in range(n): v = (v << 8) | b[o + 1 + k]
+        return v, o + 1 + n
+
+    for c in (0, n_cont - 1):
+        b = ln.dv.dev_to_numpy(ctx, out + int(off[c]), int(off[c + 1] - off[c]), np.uint8).tobytes()
+        size = int.from_bytes(b[:4], 'little'); o = 4
+        for _ in range(4): _, o = itf8(b, o)
+        g, o = ltf8(b, o); _, o = ltf8(b, o)
+        nb, o = itf8(b, o); nl, o = itf8(b, o); lm, o = itf8(b, o)
+        assert g == int(grc[c]) and nb == NB + 3 and nl == 1, 'container header fields'
+        assert int.from_bytes(b[o:o + 4], 'little') == zlib.crc32(b[:o]) & 0xFFFFFFFF, 'container header CRC32'
+        o += 4
+        assert size == len(b) - o, 'container byte size'
+        first = o
+        for k in range(nb):
+            s0 = o; o += 2
+            _, o = itf8(b, o); cl, o = itf8(b, o); _, o = itf8(b, o)
+            o += cl
+            assert int.from_bytes(b[o:o + 4], 'little') == zlib.crc32(b[s0:o]) & 0xFFFFFFFF, 'block %d CRC32' % k
+            o += 4
+            if k == 0: assert o - first == lm, 'landmark'
+        assert o == len(b), 'the blocks fill the container'
+    return {'row': 'ContainerIO.writeContainer :152-209 for every container of the step (header + CRC32, compression header block, slice header block with digest tags, core, rANS blocks)',
+            'containers': int(n_cont), 'blocks': int(n_cont * (NB + 3)), 'bytes_out': int(olen), 'ms': round(best, 4), 'GBps': olen / (best * 1e-3) / 1e9,
+            'verified': 'first and last container: header fields and CRC32, byte size, landmark, the CRC32 of every block, exact length', 'in_default_timed_step': False}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -711,6 +786,7 @@ def run_ours(args):
     lanes[0].with_digests = False
     ms_dig = max_over_ranks(ms_dig)
     framing_leg = block_framing_leg(lanes[0])
+    container_leg = container_assembly_leg(lanes[0])
     digest_leg = {'row': 'ContainerFactory.buildSlice :138-176 (nofRecords, bases, sequenceId, alignment start/span, BD, SD) + Slice.setRefMD5',
                   'ms_per_step_unpipelined_with_digests': ms_dig, 'ms_per_step_unpipelined_without': ms_unpip,
                   'k_slice_digest_ms': round(kdig.get('k_slice_digest', 0.0), 4), 'k_slice_finish_ms': round(kdig.get('k_slice_finish', 0.0), 4), 'k_slice_md5_ms': round(kdig.get('k_slice_md5', 0.0), 4),
@@ -825,6 +901,7 @@ def run_ours(args):
         }
         line['slice_digests'] = digest_leg
         line['block_framing'] = framing_leg
+        line['container_assembly'] = container_leg
         line.update(extra_legs)
         if world == 1 and not args.no_cpu:
             line['cpu_baseline'] = cpu_baseline(args)

@@ -195,6 +195,181 @@ void shift_columns(uint32_t n, uint32_t *cols)
     }
 }
 
+
+// ---- the container around the blocks (container part) -------------------------------------------------------
+// ContainerIO.writeContainer [ContainerIO.java:152-209] for containers of one slice: container header | compression header
+// block | slice header block | core block | external blocks, tightly packed.  The framing kernels above run over an EXTENDED
+// block list (two more blocks per container: the compression header the Java host built, and the slice header content
+// k_cont_prepare serialises from the device-side slice header); k_cont_layout places them, k_cont_header writes the headers.
+#define CT_TAGS 1u
+
+struct ContArgs {
+    uint32_t n;                        // containers
+    uint32_t flags;
+    const cramgpu_slice_header *slices;
+    const uint64_t *grc;               // global record counter per container
+    const uint64_t *ch_off;            // compression header bytes per container (offsets into ch)
+    const uint8_t *ch;
+    const uint32_t *block_first;       // [n + 1] into the caller's block table
+    const uint8_t *comp; const uint64_t *comp_off; const uint32_t *comp_len, *raw_len;      // the caller's block table
+    const int32_t *content_id; const uint8_t *method, *content_type;
+    uint8_t *sh; uint32_t sh_stride;   // slice header content slots
+    // the extended table (absolute addresses in x_off)
+    uint64_t *x_off; uint32_t *x_len, *x_raw; int32_t *x_id; uint8_t *x_method, *x_type;
+    uint8_t sha1[20], sha512[64];
+};
+
+__device__ __forceinline__ uint32_t ltf8_bytes(uint64_t v)
+{
+    for (uint32_t n = 1; n < 9; n++) if ((v >> (7 * n)) == 0) return n;
+    return 9;
+}
+// LTF8.writeUnsignedLTF8 [LTF8.java:104-190]
+__device__ __forceinline__ uint32_t ltf8_write(uint8_t *p, uint64_t v)
+{
+    const uint32_t n = ltf8_bytes(v);
+    if (n == 9) { p[0] = 0xFF; for (int k = 0; k < 8; k++) p[1 + k] = (uint8_t)(v >> (8 * (7 - k))); return 9; }
+    for (uint32_t k = 0; k < n; k++) p[k] = (uint8_t)(v >> (8 * (n - 1 - k)));
+    p[0] |= (uint8_t)(0xFFu << (9 - n));
+    return n;
+}
+__device__ __forceinline__ uint32_t put_tag(uint8_t *p, char t0, char t1, const uint8_t *val, uint32_t len)
+{
+    // BinaryTagCodec.writeTag of a byte[] [BinaryTagCodec.java:185-228]: tag, 'B', 'c', int32 count, the bytes
+    p[0] = (uint8_t)t0; p[1] = (uint8_t)t1; p[2] = 'B'; p[3] = 'c';
+    p[4] = (uint8_t)len; p[5] = (uint8_t)(len >> 8); p[6] = (uint8_t)(len >> 16); p[7] = (uint8_t)(len >> 24);
+    for (uint32_t i = 0; i < len; i++) p[8 + i] = val[i];
+    return 8 + len;
+}
+
+// one thread per container: slice header content [SliceIO.java:76-107] and the container's rows of the extended table
+__global__ void __launch_bounds__(128) k_cont_prepare(ContArgs a)
+{
+    const uint32_t c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= a.n) return;
+    const uint32_t b0 = a.block_first[c], b1 = a.block_first[c + 1], nb = b1 - b0;     // core + external
+    const cramgpu_slice_header h = a.slices[c];
+    uint8_t *p = a.sh + (size_t)c * a.sh_stride;
+    uint32_t o = 0;
+    o += itf8_write(p + o, (uint32_t)h.sequence_id); o += itf8_write(p + o, (uint32_t)h.alignment_start);
+    o += itf8_write(p + o, (uint32_t)h.alignment_span); o += itf8_write(p + o, h.n_records);
+    o += ltf8_write(p + o, a.grc[c]);
+    o += itf8_write(p + o, nb);                                            // nofBlocks [SliceIO.java:132]
+    const uint32_t next = nb ? nb - 1 : 0;
+    o += itf8_write(p + o, next);                                          // CramArray.write: count, elements
+    for (uint32_t j = 1; j < nb; j++) o += itf8_write(p + o, (uint32_t)a.content_id[b0 + j]);
+    o += itf8_write(p + o, 0xFFFFFFFFu);                                   // embeddedRefBlockContentID = -1
+    for (int i = 0; i < 16; i++) p[o++] = h.ref_md5[i];
+    if (a.flags & CT_TAGS) {                                               // the slice's tag list: B1 S1 B5 S5 BD SD
+        uint8_t w[4];
+        o += put_tag(p + o, 'B', '1', a.sha1, 20); o += put_tag(p + o, 'S', '1', a.sha1, 20);
+        o += put_tag(p + o, 'B', '5', a.sha512, 64); o += put_tag(p + o, 'S', '5', a.sha512, 64);
+        w[0] = (uint8_t)h.bd; w[1] = (uint8_t)(h.bd >> 8); w[2] = (uint8_t)(h.bd >> 16); w[3] = (uint8_t)(h.bd >> 24);
+        o += put_tag(p + o, 'B', 'D', w, 4);
+        w[0] = (uint8_t)h.sd; w[1] = (uint8_t)(h.sd >> 8); w[2] = (uint8_t)(h.sd >> 16); w[3] = (uint8_t)(h.sd >> 24);
+        o += put_tag(p + o, 'S', 'D', w, 4);
+    }
+    const uint32_t e0 = b0 + 2 * c;
+    const uint32_t chl = (uint32_t)(a.ch_off[c + 1] - a.ch_off[c]);
+    a.x_off[e0] = (uint64_t)(uintptr_t)(a.ch + a.ch_off[c]); a.x_len[e0] = chl; a.x_raw[e0] = chl;
+    a.x_id[e0] = 0; a.x_method[e0] = 0; a.x_type[e0] = 1;                   // RAW, COMPRESSION_HEADER [ContainerIO.java:171-181]
+    a.x_off[e0 + 1] = (uint64_t)(uintptr_t)p; a.x_len[e0 + 1] = o; a.x_raw[e0 + 1] = o;
+    a.x_id[e0 + 1] = 0; a.x_method[e0 + 1] = 0; a.x_type[e0 + 1] = 2;       // RAW, MAPPED_SLICE [Block.buildNewSliceHeaderBlock]
+    for (uint32_t j = 0; j < nb; j++) {
+        const uint32_t e = e0 + 2 + j, b = b0 + j;
+        a.x_off[e] = (uint64_t)(uintptr_t)(a.comp ? a.comp : (const uint8_t *)0) + a.comp_off[b];
+        a.x_len[e] = a.comp_len[b]; a.x_raw[e] = a.raw_len[b];
+        a.x_id[e] = a.content_id[b]; a.x_method[e] = a.method[b]; a.x_type[e] = a.content_type[b];
+    }
+}
+
+struct ContLayout {
+    uint32_t n;
+    const cramgpu_slice_header *slices;
+    const uint64_t *grc;
+    const uint32_t *block_first;
+    const uint32_t *x_size;            // framed size per extended block
+    uint64_t *x_out_off;               // [next + 1]
+    uint64_t *cont_off;                // [n + 1]
+    uint32_t *hdr_len;                 // [n]
+};
+
+__device__ __forceinline__ void cont_fields(const cramgpu_slice_header &h, int32_t &seq, int32_t &start, int32_t &span)
+{
+    // ContainerFactory.buildContainer [:93-94] and calculateAlignmentBoundaries [:108-123] for one slice: a container of an
+    // unplaced slice keeps its initial -1 / -1 / 0 [Container.java:28-30]
+    seq = h.sequence_id;
+    if (seq != -1) { start = h.alignment_start; span = h.alignment_span; } else { start = -1; span = 0; }
+}
+
+// single CTA: container sizes (header + blocks, tight), their exclusive scan, then every block's place
+__global__ void __launch_bounds__(1024) k_cont_layout(ContLayout a)
+{
+    __shared__ unsigned long long sw[32];
+    __shared__ unsigned long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (uint32_t c0 = 0; c0 < a.n; c0 += 1024) {
+        const uint32_t c = c0 + threadIdx.x;
+        unsigned long long tot = 0;
+        uint32_t hl = 0;
+        if (c < a.n) {
+            const uint32_t e0 = a.block_first[c] + 2 * c, e1 = a.block_first[c + 1] + 2 * (c + 1);
+            unsigned long long body = 0;
+            for (uint32_t e = e0; e < e1; e++) body += a.x_size[e];
+            const cramgpu_slice_header h = a.slices[c];
+            int32_t seq, start, span;
+            cont_fields(h, seq, start, span);
+            hl = 4 + itf8_bytes((uint32_t)seq) + itf8_bytes((uint32_t)start) + itf8_bytes((uint32_t)span) + itf8_bytes(h.n_records) +
+                 ltf8_bytes(a.grc[c]) + ltf8_bytes(h.bases) + itf8_bytes(e1 - e0) + 1 + itf8_bytes(a.x_size[e0]) + 4;
+            a.hdr_len[c] = hl;
+            tot = hl + body;
+        }
+        unsigned long long s = tot;
+        for (int d = 1; d < 32; d <<= 1) { unsigned long long t = __shfl_up_sync(0xFFFFFFFFu, s, d); if (lane >= (uint32_t)d) s += t; }
+        if (lane == 31) sw[w] = s;
+        __syncthreads();
+        unsigned long long base = carry, all = 0;
+        for (uint32_t k = 0; k < 32; k++) { if (k < w) base += sw[k]; all += sw[k]; }
+        if (c < a.n) {
+            unsigned long long at = base + s - tot;
+            a.cont_off[c] = at;
+            at += hl;
+            const uint32_t e0 = a.block_first[c] + 2 * c, e1 = a.block_first[c + 1] + 2 * (c + 1);
+            for (uint32_t e = e0; e < e1; e++) { a.x_out_off[e] = at; at += a.x_size[e]; }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) carry += all;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { a.cont_off[a.n] = carry; a.x_out_off[a.block_first[a.n] + 2 * a.n] = carry; }
+}
+
+// one thread per container: ContainerHeaderIO.writeContainerHeader(3, ...) [ContainerHeaderIO.java:69-84]
+__global__ void __launch_bounds__(128) k_cont_header(ContLayout a, uint8_t *out)
+{
+    const uint32_t c = blockIdx.x * 128 + threadIdx.x;
+    if (c >= a.n) return;
+    const uint32_t e0 = a.block_first[c] + 2 * c, e1 = a.block_first[c + 1] + 2 * (c + 1);
+    const cramgpu_slice_header h = a.slices[c];
+    int32_t seq, start, span;
+    cont_fields(h, seq, start, span);
+    uint8_t *p = out + a.cont_off[c];
+    const uint32_t hl = a.hdr_len[c];
+    const uint32_t bytes = (uint32_t)(a.cont_off[c + 1] - a.cont_off[c] - hl);               // containerByteSize: the blocks
+    uint32_t o = 0;
+    p[o++] = (uint8_t)bytes; p[o++] = (uint8_t)(bytes >> 8); p[o++] = (uint8_t)(bytes >> 16); p[o++] = (uint8_t)(bytes >> 24);
+    o += itf8_write(p + o, (uint32_t)seq); o += itf8_write(p + o, (uint32_t)start); o += itf8_write(p + o, (uint32_t)span);
+    o += itf8_write(p + o, h.n_records); o += ltf8_write(p + o, a.grc[c]); o += ltf8_write(p + o, h.bases);
+    o += itf8_write(p + o, e1 - e0);                                       // blockCount [ContainerIO.java:183-193]
+    o += itf8_write(p + o, 1u); o += itf8_write(p + o, a.x_size[e0]);      // landmarks: the slice starts behind the compression header block
+    uint32_t r = ~0u;
+    for (uint32_t i = 0; i < o; i++) { r ^= p[i]; for (int k = 0; k < 8; k++) r = (r & 1) ? 0xEDB88320u ^ (r >> 1) : r >> 1; }
+    r = ~r;
+    p[o++] = (uint8_t)r; p[o++] = (uint8_t)(r >> 8); p[o++] = (uint8_t)(r >> 16); p[o++] = (uint8_t)(r >> 24);
+}
+
 }  // namespace
 
 extern "C" int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *d_comp, const uint64_t *d_comp_off,
@@ -253,5 +428,104 @@ extern "C" int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, cons
     LAUNCH(ctx, st, "k_frame_crc", k_frame_crc<<<(nblocks + 255) / 256, 256, 0, st>>>(a, d_nch));
     CUDA_TRY(ctx, cudaGetLastError());
     *d_out = a.out; *out_len = total; *d_out_off = (uint64_t *)(S + o_off);
+    return CRAMGPU_OK;
+}
+
+extern "C" int cramgpu_containers_assemble_dev(cramgpu_ctx *ctx, const cramgpu_container_in *in, uint8_t **d_out, uint64_t *out_len,
+                                               uint64_t **d_out_off, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!in || !d_out || !out_len || !d_out_off) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    *d_out = nullptr; *out_len = 0; *d_out_off = nullptr;
+    const uint32_t n = in->n_containers, nblocks = in->nblocks;
+    if (n == 0) return CRAMGPU_OK;
+    if (!in->d_slices || !in->global_record_counter || !in->comp_header || !in->comp_header_off || !in->block_first ||
+        !in->d_comp_off || !in->d_comp_len || !in->d_raw_len || !in->content_id || !in->method || !in->content_type)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (in->block_first[0] != 0 || in->block_first[n] != nblocks) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "block_first does not cover the block table");
+    uint32_t max_ids = 0;
+    for (uint32_t c = 0; c < n; c++) {
+        if (in->block_first[c + 1] <= in->block_first[c]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "a container needs its core block");
+        if (in->comp_header_off[c + 1] < in->comp_header_off[c]) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "comp_header_off decreases");
+        max_ids = std::max(max_ids, in->block_first[c + 1] - in->block_first[c] - 1);
+    }
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    const size_t next = (size_t)nblocks + 2 * (size_t)n, nb = nblocks;
+    const size_t ch_bytes = in->comp_header_off[n] - in->comp_header_off[0];
+    const uint32_t sh_stride = (uint32_t)rup(288 + 5 * (size_t)max_ids, 16);
+    Carver cv;
+    const size_t o_id = cv.take(4 * nb), o_m = cv.take(nb), o_t = cv.take(nb), o_bf = cv.take(4 * ((size_t)n + 1)), o_grc = cv.take(8 * (size_t)n);
+    const size_t o_cho = cv.take(8 * ((size_t)n + 1)), o_ch = cv.take(ch_bytes + 16), o_sh = cv.take((size_t)n * sh_stride);
+    const size_t x_off = cv.take(8 * next), x_len = cv.take(4 * next), x_raw = cv.take(4 * next), x_id = cv.take(4 * next);
+    const size_t x_m = cv.take(next), x_t = cv.take(next), o_size = cv.take(4 * next), o_nch = cv.take(4 * next);
+    const size_t o_off = cv.take(8 * (next + 1)), o_dummy = cv.take(8 * (next + 1)), o_cf = cv.take(8 * (next + 1)), o_mx = cv.take(16);
+    const size_t o_coff = cv.take(8 * ((size_t)n + 1)), o_hl = cv.take(4 * (size_t)n);
+    if (int rc = pool_reserve(ctx, ctx->frame_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->frame_scratch.p;
+    // small host tables -> device through page-locked staging
+    Carver pc;
+    const size_t p_id = pc.take(4 * nb, 16), p_m = pc.take(nb, 16), p_t = pc.take(nb, 16), p_bf = pc.take(4 * ((size_t)n + 1), 16);
+    const size_t p_grc = pc.take(8 * (size_t)n, 16), p_cho = pc.take(8 * ((size_t)n + 1), 16), p_ch = pc.take(ch_bytes, 16), p_tot = pc.take(32, 16);
+    if (int rc = pinned_reserve(ctx, &ctx->pin_frame, &ctx->pin_frame_cap, pc.off + 128)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_frame));
+    uint8_t *pm = (uint8_t *)ctx->pin_frame;
+    memcpy(pm + p_id, in->content_id, 4 * nb); memcpy(pm + p_m, in->method, nb); memcpy(pm + p_t, in->content_type, nb);
+    memcpy(pm + p_bf, in->block_first, 4 * ((size_t)n + 1)); memcpy(pm + p_grc, in->global_record_counter, 8 * (size_t)n);
+    {
+        uint64_t *co = (uint64_t *)(pm + p_cho);
+        for (uint32_t c = 0; c <= n; c++) co[c] = in->comp_header_off[c] - in->comp_header_off[0];
+        memcpy(pm + p_ch, in->comp_header + in->comp_header_off[0], ch_bytes);
+    }
+    auto up = [&](size_t dev_o, size_t pin_o, size_t bytes) { return bytes ? cudaMemcpyAsync(S + dev_o, pm + pin_o, bytes, cudaMemcpyHostToDevice, st) : cudaSuccess; };
+    CUDA_TRY(ctx, up(o_id, p_id, 4 * nb)); CUDA_TRY(ctx, up(o_m, p_m, nb)); CUDA_TRY(ctx, up(o_t, p_t, nb));
+    CUDA_TRY(ctx, up(o_bf, p_bf, 4 * ((size_t)n + 1))); CUDA_TRY(ctx, up(o_grc, p_grc, 8 * (size_t)n));
+    CUDA_TRY(ctx, up(o_cho, p_cho, 8 * ((size_t)n + 1))); CUDA_TRY(ctx, up(o_ch, p_ch, ch_bytes));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_frame, st));
+
+    ContArgs ca;
+    memset(&ca, 0, sizeof ca);
+    ca.n = n; ca.flags = in->flags; ca.slices = in->d_slices; ca.grc = (const uint64_t *)(S + o_grc);
+    ca.ch_off = (const uint64_t *)(S + o_cho); ca.ch = S + o_ch; ca.block_first = (const uint32_t *)(S + o_bf);
+    ca.comp = in->d_comp; ca.comp_off = in->d_comp_off; ca.comp_len = in->d_comp_len; ca.raw_len = in->d_raw_len;
+    ca.content_id = (const int32_t *)(S + o_id); ca.method = S + o_m; ca.content_type = S + o_t;
+    ca.sh = S + o_sh; ca.sh_stride = sh_stride;
+    ca.x_off = (uint64_t *)(S + x_off); ca.x_len = (uint32_t *)(S + x_len); ca.x_raw = (uint32_t *)(S + x_raw);
+    ca.x_id = (int32_t *)(S + x_id); ca.x_method = S + x_m; ca.x_type = S + x_t;
+    cramgpu_slice_sha_tags(ca.sha1, ca.sha512);
+    LAUNCH(ctx, st, "k_cont_prepare", k_cont_prepare<<<(n + 127) / 128, 128, 0, st>>>(ca));
+
+    FrameArgs a;
+    memset(&a, 0, sizeof a);
+    a.nblocks = (uint32_t)next; a.comp = nullptr; a.comp_off = ca.x_off; a.comp_len = ca.x_len; a.raw_len = ca.x_raw;
+    a.content_id = ca.x_id; a.method = ca.x_method; a.content_type = ca.x_type;
+    a.size = (uint32_t *)(S + o_size); a.out_off = (const uint64_t *)(S + o_off); a.chunk_first = (const uint64_t *)(S + o_cf);
+    struct Cols { uint32_t p[8][32], c16k[32]; Cols() { for (int k = 0; k < 8; k++) shift_columns(FR_PIECE << k, p[k]); shift_columns(FR_CHUNK, c16k); } };
+    static const Cols cols;
+    memcpy(a.shiftp, cols.p, sizeof cols.p); memcpy(a.shift16k, cols.c16k, sizeof cols.c16k);
+    uint32_t *d_nch = (uint32_t *)(S + o_nch);
+    LAUNCH(ctx, st, "k_frame_size", k_frame_size<<<((uint32_t)next + 255) / 256, 256, 0, st>>>(a, d_nch));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_mx, 0, 16, st));
+    // chunk slots of the CRC work as in cramgpu_blocks_frame_dev (its padded offsets go to a dummy); the real places are tight
+    LAUNCH(ctx, st, "k_frame_scan", k_frame_scan<<<1, 1024, 0, st>>>(a.size, d_nch, (uint32_t)next, (uint64_t *)(S + o_dummy), (uint64_t *)(S + o_cf), (uint32_t *)(S + o_mx)));
+    ContLayout cl;
+    cl.n = n; cl.slices = in->d_slices; cl.grc = ca.grc; cl.block_first = ca.block_first; cl.x_size = a.size;
+    cl.x_out_off = (uint64_t *)(S + o_off); cl.cont_off = (uint64_t *)(S + o_coff); cl.hdr_len = (uint32_t *)(S + o_hl);
+    LAUNCH(ctx, st, "k_cont_layout", k_cont_layout<<<1, 1024, 0, st>>>(cl));
+    uint64_t *tot = (uint64_t *)(pm + p_tot);
+    CUDA_TRY(ctx, cudaMemcpyAsync(tot, S + o_coff + 8 * (size_t)n, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaMemcpyAsync(tot + 1, S + o_cf + 8 * next, 8, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    const uint64_t total = tot[0], nchunks_total = tot[1];
+    Carver co;
+    const size_t q_out = co.take(total + 16), q_crc = co.take(4 * nchunks_total + 16);
+    if (int rc = pool_reserve(ctx, ctx->frame_out, co.off)) return rc;
+    uint8_t *O = (uint8_t *)ctx->frame_out.p;
+    a.out = O + q_out; a.chunk_crc = (uint32_t *)(O + q_crc);
+    if (nchunks_total) LAUNCH(ctx, st, "k_frame_write", k_frame_write<<<(uint32_t)nchunks_total, FR_THREADS, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_frame_crc", k_frame_crc<<<((uint32_t)next + 255) / 256, 256, 0, st>>>(a, d_nch));
+    LAUNCH(ctx, st, "k_cont_header", k_cont_header<<<(n + 127) / 128, 128, 0, st>>>(cl, a.out));
+    CUDA_TRY(ctx, cudaGetLastError());
+    *d_out = a.out; *out_len = total; *d_out_off = cl.cont_off;
     return CRAMGPU_OK;
 }

@@ -476,3 +476,57 @@ _lib.SIGNATURES.update({
     'cramgpu_blocks_frame_dev': (C.c_int, [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, i32p, u8p, u8p,
                                            C.POINTER(C.c_void_p), C.POINTER(C.c_uint64), C.POINTER(C.c_void_p), C.c_void_p]),
 })
+
+
+# ---------------------------------------------------------------------------------------------- CRAM v3 containers (device resident)
+CONTAINER_TAGS = 1
+
+
+class ContainerIn(C.Structure):
+    _fields_ = [('n_containers', C.c_uint32), ('flags', C.c_uint32), ('d_slices', C.c_void_p), ('global_record_counter', u64p),
+                ('comp_header', C.c_void_p), ('comp_header_off', u64p), ('block_first', C.POINTER(C.c_uint32)), ('nblocks', C.c_uint32),
+                ('d_comp', C.c_void_p), ('d_comp_off', C.c_void_p), ('d_comp_len', C.c_void_p), ('d_raw_len', C.c_void_p),
+                ('content_id', i32p), ('method', u8p), ('content_type', u8p)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_containers_assemble_dev': (C.c_int, [C.c_void_p, C.POINTER(ContainerIn), C.POINTER(C.c_void_p), C.POINTER(C.c_uint64),
+                                                  C.POINTER(C.c_void_p), C.c_void_p]),
+})
+
+
+def slice_header_array(headers):
+    """list of dicts (as slice_headers returns) -> numpy bytes of a cramgpu_slice_header array (to be placed in device memory)"""
+    arr = (SliceHeader * max(len(headers), 1))()
+    for h, d in zip(arr, headers):
+        h.sequence_id = d['sequence_id']; h.alignment_start = d['alignment_start']; h.alignment_span = d['alignment_span']
+        h.n_records = d['n_records']; h.bases = d['bases']; h.bd = d.get('bd', 0); h.sd = d.get('sd', 0)
+        md5 = d.get('ref_md5') or bytes(16)
+        for i in range(16):
+            h.ref_md5[i] = md5[i]
+    return np.frombuffer(bytes(arr), np.uint8)[:C.sizeof(SliceHeader) * len(headers)].copy()
+
+
+def containers_assemble(d_slices, global_record_counter, comp_headers, block_first, d_comp, d_comp_off, d_comp_len, d_raw_len,
+                        content_id, method, content_type, tags=True, ctx=None, stream=None):
+    """ContainerIO.writeContainer for one-slice containers through cramgpu_containers_assemble_dev.  d_*: device pointers (ints);
+    comp_headers: list of bytes (CompressionHeader.toByteArray() per container).  -> (device pointer, total bytes, device
+    pointer of the [n + 1] container offsets); the result lives in the context until the next framing call"""
+    ctx = ctx or _lib.default_context()
+    n = len(comp_headers)
+    grc = _arr(global_record_counter, np.uint64)
+    ch = _arr(np.frombuffer(b''.join(comp_headers), np.uint8) if comp_headers else np.zeros(0, np.uint8), np.uint8)
+    if ch.size == 0:
+        ch = np.zeros(1, np.uint8)
+    cho = np.concatenate([[0], np.cumsum([len(x) for x in comp_headers])]).astype(np.uint64)
+    bf = _arr(block_first, np.uint32)
+    cid = _arr(content_id, np.int32); m = _arr(method, np.uint8); t = _arr(content_type, np.uint8)
+    I = ContainerIn()
+    I.n_containers = n; I.flags = CONTAINER_TAGS if tags else 0; I.d_slices = d_slices
+    I.global_record_counter = grc.ctypes.data_as(u64p); I.comp_header = _vp(ch); I.comp_header_off = cho.ctypes.data_as(u64p)
+    I.block_first = bf.ctypes.data_as(C.POINTER(C.c_uint32)); I.nblocks = cid.size
+    I.d_comp = d_comp; I.d_comp_off = d_comp_off; I.d_comp_len = d_comp_len; I.d_raw_len = d_raw_len
+    I.content_id = cid.ctypes.data_as(i32p); I.method = m.ctypes.data_as(u8p); I.content_type = t.ctypes.data_as(u8p)
+    out, olen, ooff = C.c_void_p(), C.c_uint64(), C.c_void_p()
+    ctx.check(ctx.lib.cramgpu_containers_assemble_dev(ctx.handle, C.byref(I), C.byref(out), C.byref(olen), C.byref(ooff), stream))
+    return out.value, olen.value, ooff.value

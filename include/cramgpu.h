@@ -678,6 +678,48 @@ int cramgpu_blocks_frame_dev(cramgpu_ctx *ctx, uint32_t nblocks, const uint8_t *
                              const uint32_t *d_comp_len, const uint32_t *d_raw_len, const int32_t *content_id, const uint8_t *method,
                              const uint8_t *content_type, uint8_t **d_out, uint64_t *out_len, uint64_t **d_out_off, void *stream);
 
+/* ------------------------------------------------------------------ the CRAM v3 container (container part)
+ *
+ * ContainerIO.writeContainer [htsjdk ContainerIO.java:152-209] for containers of ONE slice (how cramtools builds them:
+ * ContainerFactory's records per slice = records per container): the bytes of every container, ready to be appended to the file --
+ *   container header   ContainerHeaderIO.writeContainerHeader(3, ..) [ContainerHeaderIO.java:69-84]: int32 size of the blocks,
+ *                      ITF8 sequence id / start / span / records, LTF8 global record counter / bases, ITF8 block count,
+ *                      landmarks (one: the slice starts behind the compression header block), CRC32 little endian.
+ *                      Sequence id, start and span are the slice's (ContainerFactory.buildContainer [:93-94],
+ *                      calculateAlignmentBoundaries [:108-123]); -1 / -1 / 0 for an unplaced slice.
+ *   compression header block   RAW, content type COMPRESSION_HEADER, the bytes of CompressionHeader.toByteArray() the Java host
+ *                      built (comp_header; the encoding maps are host business)
+ *   slice header block SliceIO.createSliceHeaderBlockContent(3, ..) [SliceIO.java:76-107] serialised on the device from the
+ *                      result of cramgpu_slice_headers_dev: ITF8 fields, LTF8 global record counter, ITF8 number of blocks,
+ *                      the content ids, embedded reference id -1, the reference MD5, and with CRAMGPU_CONTAINER_TAGS the
+ *                      content digest tags in the slice's order B1 S1 B5 S5 BD SD (BinaryTagCodec.writeTag of byte arrays)
+ *   core block, external blocks   Block.write(3, ..) as cramgpu_blocks_frame_dev, in the order of the block table: the core
+ *                      block first, then the external blocks in the order the host's Slice.external map iterates.
+ * Blocks of container c = rows [block_first[c], block_first[c+1]) of the block table (the table is cramgpu_blocks_frame_dev's).
+ * global_record_counter: Container.globalRecordCounter = Slice.globalRecordCounter (cramgpu_allgather_sizes returns it).
+ * Result: the containers back to back without padding in device memory owned by ctx (shared with cramgpu_blocks_frame_dev:
+ * valid until the next call of either); d_out_off (DEVICE, [n_containers+1]) = where container c starts -- added to the file
+ * position of the first one it is Container.offset.  One stream synchronisation inside.
+ */
+#define CRAMGPU_CONTAINER_TAGS 1u
+typedef struct cramgpu_container_in {
+    uint32_t n_containers;
+    uint32_t flags;                          /* CRAMGPU_CONTAINER_TAGS */
+    const cramgpu_slice_header *d_slices;    /* DEVICE [n_containers] */
+    const uint64_t *global_record_counter;   /* HOST [n_containers] */
+    const uint8_t *comp_header;              /* HOST: CompressionHeader.toByteArray() of every container, concatenated */
+    const uint64_t *comp_header_off;         /* HOST [n_containers+1] */
+    const uint32_t *block_first;             /* HOST [n_containers+1] */
+    uint32_t nblocks;
+    const uint8_t *d_comp;                   /* DEVICE (or NULL: d_comp_off holds absolute addresses) */
+    const uint64_t *d_comp_off;              /* DEVICE [nblocks] */
+    const uint32_t *d_comp_len, *d_raw_len;  /* DEVICE [nblocks] */
+    const int32_t *content_id;               /* HOST [nblocks] */
+    const uint8_t *method, *content_type;    /* HOST [nblocks] */
+} cramgpu_container_in;
+int cramgpu_containers_assemble_dev(cramgpu_ctx *ctx, const cramgpu_container_in *in, uint8_t **d_out, uint64_t *out_len,
+                                    uint64_t **d_out_off, void *stream);
+
 /* ------------------------------------------------------------------ multi-GPU: where this rank's containers go
  *
  * Containers are independent and are dealt round-robin: the container with global ordinal g is converted by

@@ -224,6 +224,38 @@ def build(reads, ref, coordinate_sorted, tag):
         blocks[str(cid)] = dict(order=order, block=b64(bytes(vm.jdk_virtual('java/io/ByteArrayOutputStream', 'toByteArray', '()[B', [baos]).a)))
     out['blocks_v3'] = blocks
 
+    # SURVEY 8f-5 (the container around the blocks): ContainerIO.writeContainer [ContainerIO.java:152-209] of a container holding
+    # this one slice -- container header (ContainerHeaderIO.writeContainerHeader [:69-84]: int32 byte size, ITF8 / LTF8 fields,
+    # landmarks, CRC32), compression header block (CompressionHeader.toByteArray), then SliceIO.write [:132-146]: slice header
+    # block (createSliceHeaderBlockContent [:76-107], with the content digest tags), core block, external blocks in the map's
+    # order.  The external blocks carry what the compress hook returned (the raw bytes) under the method the header chose.
+    CT = 'htsjdk/samtools/cram/structure/Container'
+    grc = {'all_reads_sorted_header': 0, 'single_ref_sorted': 162, 'unsorted_header': 6000000123}.get(tag, 7)
+    cont = new(CT)
+    cont.fields['header'] = header
+    cont.fields['nofRecords'] = len(recs)
+    cont.fields['globalRecordCounter'] = grc
+    cont.fields['bases'] = int(sl.fields.get('bases', 0))
+    cont.fields['blockCount'] = 0
+    cont.fields['slices'] = JArray('L', [sl])
+    sl.fields['globalRecordCounter'] = grc
+    if cont.fields.get('sequenceId', -1) == -1 and sl.fields.get('sequenceId', 0) != -1:          # ContainerFactory.buildContainer [:93-94]
+        cont.fields['sequenceId'] = sl.fields.get('sequenceId', 0)
+    vm.call(CF, 'calculateAlignmentBoundaries', '(L%s;)V' % CT, [cont])
+    baos = JObject('java/io/ByteArrayOutputStream')
+    vm.jdk_special('java/io/ByteArrayOutputStream', '<init>', '()V', [baos])
+    vm.call('htsjdk/samtools/cram/structure/ContainerIO', 'writeContainer',
+            '(Lhtsjdk/samtools/cram/common/Version;L%s;Ljava/io/OutputStream;)I' % CT, [G.make_factory(ref).fields['version'], cont, baos])
+    whole = bytes(vm.jdk_virtual('java/io/ByteArrayOutputStream', 'toByteArray', '()[B', [baos]).a)
+    hb = sl.fields['headerBlock']
+    out['container_v3'] = dict(bytes=b64(whole), global_record_counter=grc, byte_size=int(cont.fields['containerByteSize']),
+                               block_count=int(cont.fields['blockCount']), landmarks=[int(v) for v in cont.fields['landmarks'].a],
+                               sequence_id=int(cont.fields.get('sequenceId', 0)), alignment_start=int(cont.fields.get('alignmentStart', 0)),
+                               alignment_span=int(cont.fields.get('alignmentSpan', 0)),
+                               slice_header_content=b64(bytes(hb.fields['rawContent'].a)),
+                               content_ids=[int(v) for v in sl.fields['contentIDs'].a],
+                               compression_header=b64(bytes(vm.call(CH, 'toByteArray', '()[B', [header]).a)))
+
     # ---- read it back: DataReaderFactory.buildReader + CramRecordReader.read (row P)
     imap = JObject('java/util/HashMap'); imap.fields['map'] = {}
     for cid, raw in series.items():

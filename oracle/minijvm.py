@@ -384,7 +384,11 @@ class MiniJVM:
         if isinstance(obj, ByteBuffer):
             return cname in ('java/nio/ByteBuffer', 'java/nio/Buffer', 'java/lang/Object')
         if isinstance(obj, JArray):
-            return True
+            if cname in ('java/lang/Object', 'java/lang/Cloneable', 'java/io/Serializable'):
+                return True
+            if cname.startswith('[') and len(cname) == 2:                     # primitive array class: [B [S [I ...
+                return obj.kind == cname[1] or (obj.kind == 'Z' and cname[1] == 'B' and False)
+            return cname.startswith('[') and obj.kind in ('L', '[')         # object arrays: element types are not tracked
         while c:
             if c == cname:
                 return True
@@ -940,6 +944,8 @@ class MiniJVM:
         raise NotImplementedError('special %s.%s%s' % (cn, mn, ds))
 
     def jdk_static_call(self, cn, mn, ds, args):
+        if cn == 'java/lang/System' and mn in ('nanoTime', 'currentTimeMillis'):
+            return 0                                    # timings of the jar's own logging: never part of a result
         if cn == 'java/lang/System' and mn == 'arraycopy':
             src, sp, dst, dp, n = args
             if src is None or dst is None:
@@ -1309,7 +1315,7 @@ class MiniJVM:
                             mc = self.find_method(cmpo.cls, 'compare', '(Ljava/lang/Object;Ljava/lang/Object;)I')
                             items.sort(key=functools.cmp_to_key(lambda a, b: self.invoke(mc, [cmpo, a[0], b[0]])))
                         else:
-                            items.sort(key=lambda kv: kv[0].fields['value'] if isinstance(kv[0], JObject) else kv[0])
+                            items.sort(key=lambda kv: (kv[0].fields['value'] if 'value' in kv[0].fields else kv[0].fields['ordinal']) if isinstance(kv[0], JObject) else kv[0])   # boxed numbers / strings, else enums (Enum.compareTo = ordinal)
                     return items
                 if mn == 'put':
                     k = find(args[1]); old = mp.get(k, (None, None))
@@ -1329,9 +1335,9 @@ class MiniJVM:
                 if mn == 'clear':
                     mp.clear(); return None
                 if mn == 'values':
-                    r = JObject('java/util/ArrayList'); r.fields['list'] = [v for _, v in mp.values()]; return r
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [v for _, v in _hash_order(o, mp)]; return r
                 if mn == 'keySet':
-                    r = JObject('java/util/ArrayList'); r.fields['list'] = [k for k, _ in mp.values()]; return r
+                    r = JObject('java/util/ArrayList'); r.fields['list'] = [k for k, _ in _hash_order(o, mp)]; return r
             if 'map' in o.fields and o.cls in JDK_SETS:
                 mp = o.fields['map']
                 if mn == 'add':
@@ -1420,6 +1426,11 @@ class MiniJVM:
                 if a[0] < 0 or a[0] + 4 > b.limit:
                     self.throw('java/lang/IndexOutOfBoundsException', None)
                 struct.pack_into(fmt, arr, off + a[0], i32(a[1])); return b
+        if mn in ('putShort', 'putLong') and ds in ('(S)Ljava/nio/ByteBuffer;', '(J)Ljava/nio/ByteBuffer;'):
+            n, c = (2, 'h') if mn == 'putShort' else (8, 'q')
+            v = a[0] & ((1 << (8 * n)) - 1)
+            v = v - (1 << (8 * n)) if v >> (8 * n - 1) else v
+            b._chkw(self, n); struct.pack_into(('<' if b.order is LITTLE else '>') + c, arr, off + b.position, v); b.position += n; return b
         if mn == 'position':
             if ds == '()I':
                 return b.position
@@ -1470,6 +1481,25 @@ class MiniJVM:
 JDK_LISTS = ('java/util/ArrayList', 'java/util/LinkedList')
 JDK_MAPS = ('java/util/HashMap', 'java/util/TreeMap', 'java/util/LinkedHashMap')
 JDK_SETS = ('java/util/HashSet', 'java/util/TreeSet', 'java/util/LinkedHashSet', 'java/util/EnumSet')
+
+
+def _hash_order(o, mp):
+    """(key, value) pairs in the order a java.util.HashMap iterates them, for maps whose keys are all java.lang.Integer
+    (content id -> block / compressor: Slice.external, CompressionHeader.externalCompressors): bucket by bucket,
+    bucket = (h ^ h >>> 16) & (capacity - 1) with h = the int itself, capacity = 16 doubled while size > 0.75 capacity
+    (a map that only grew), insertion order inside a bucket.  Other maps keep insertion order (nothing pinned reads them
+    in order)."""
+    items = list(mp.values())
+    if o.cls != 'java/util/HashMap' or not items or not all(isinstance(k, JObject) and k.cls == 'java/lang/Integer' for k, _ in items):
+        return items
+    cap = 16
+    while len(items) > 0.75 * cap:
+        cap *= 2
+
+    def bucket(k):
+        h = k.fields['value'] & 0xFFFFFFFF
+        return (h ^ (h >> 16)) & (cap - 1)
+    return sorted(items, key=lambda kv: bucket(kv[0]))          # stable: insertion order inside a bucket
 
 
 def _key(v):

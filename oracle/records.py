@@ -666,3 +666,74 @@ def cram_block_v3(method, content_type, content_id, raw_len, data):
     import zlib
     b = bytes([method, content_type]) + itf8(content_id) + itf8(len(data)) + itf8(raw_len) + bytes(data)
     return b + struct.pack('<I', zlib.crc32(b) & 0xFFFFFFFF)
+
+
+# ---------------------------------------------------------------------------------------------- CRAM v3 container (the container part)
+def ltf8(v):
+    """LTF8.writeUnsignedLTF8 [htsjdk LTF8.java:104-190]: 1-9 bytes, the leading ones of the first byte count the bytes that follow"""
+    v &= (1 << 64) - 1
+    for n in range(1, 9):
+        if v >> (7 * n) == 0:
+            body = [(v >> (8 * k)) & 0xFF for k in range(n - 1, -1, -1)]
+            body[0] |= (0xFF << (9 - n)) & 0xFF
+            return bytes(body)
+    return bytes([0xFF]) + bytes((v >> (8 * k)) & 0xFF for k in range(7, -1, -1))
+
+
+def cram_array(ints):
+    """CramArray.write(int[], os): ITF8 count, then every element as ITF8"""
+    return itf8(len(ints)) + b''.join(itf8(int(v)) for v in ints)
+
+
+def bam_tag_bytes(tag, value):
+    """BinaryTagCodec.writeTag of a byte[] value [BinaryTagCodec.java:185-228, writeArray]: tag, 'B', 'c', int32 count, bytes"""
+    import struct
+    return tag.encode('latin-1') + b'Bc' + struct.pack('<i', len(value)) + bytes(value)
+
+
+def slice_header_content_v3(sequence_id, alignment_start, alignment_span, n_records, global_record_counter, content_ids, ref_md5,
+                            tags, embedded_ref_id=-1):
+    """SliceIO.createSliceHeaderBlockContent(3, slice) [SliceIO.java:76-107] with nofBlocks as SliceIO.write sets it [:132]:
+    1 (core) + the external blocks.  tags: [(name, bytes)] in the order of the slice's tag list (B1 S1 B5 S5 BD SD), or None"""
+    b = itf8(sequence_id) + itf8(alignment_start) + itf8(alignment_span) + itf8(n_records) + ltf8(global_record_counter)
+    b += itf8(1 + len(content_ids)) + cram_array(content_ids) + itf8(embedded_ref_id)
+    b += bytes(ref_md5) if ref_md5 is not None else bytes(16)
+    for name, val in (tags or []):
+        b += bam_tag_bytes(name, val)
+    return b
+
+
+def container_header_v3(byte_size, sequence_id, alignment_start, alignment_span, n_records, global_record_counter, bases,
+                        block_count, landmarks):
+    """ContainerHeaderIO.writeContainerHeader(3, ...) [ContainerHeaderIO.java:69-84]: int32 (little endian) size of the blocks,
+    ITF8 / LTF8 fields, the landmarks, and the CRC32 of those bytes, little endian"""
+    import struct
+    import zlib
+    b = struct.pack('<i', byte_size) + itf8(sequence_id) + itf8(alignment_start) + itf8(alignment_span) + itf8(n_records)
+    b += ltf8(global_record_counter) + ltf8(bases) + itf8(block_count) + cram_array(landmarks)
+    return b + struct.pack('<I', zlib.crc32(b) & 0xFFFFFFFF)
+
+
+def container_v3(slice_hdr, global_record_counter, compression_header, content_ids, ref_md5, tags, core, external):
+    """ContainerIO.writeContainer [ContainerIO.java:152-209] of a container with ONE slice (how cramtools builds them: the
+    records per slice equal the records per container): container header | compression header block | slice header block |
+    core block | external blocks.  slice_hdr: dict with sequence_id, alignment_start, alignment_span, n_records, bases;
+    core = (method, raw_len, data); external = [(content_id, method, raw_len, data)] in the order of content_ids.
+    Container fields: ContainerFactory.buildContainer [:74-100] and calculateAlignmentBoundaries [:108-123]; blockCount and
+    the landmark as writeContainer counts them [:183-197]."""
+    RAW = BLOCK_METHOD['RAW']
+    chb = cram_block_v3(RAW, BLOCK_CONTENT['COMPRESSION_HEADER'], 0, len(compression_header), compression_header)
+    shc = slice_header_content_v3(slice_hdr['sequence_id'], slice_hdr['alignment_start'], slice_hdr['alignment_span'],
+                                  slice_hdr['n_records'], global_record_counter, content_ids, ref_md5, tags)
+    blocks = chb + cram_block_v3(RAW, BLOCK_CONTENT['MAPPED_SLICE'], 0, len(shc), shc)
+    blocks += cram_block_v3(core[0], BLOCK_CONTENT['CORE'], 0, core[1], core[2])
+    for cid, method, raw_len, data in external:
+        blocks += cram_block_v3(method, BLOCK_CONTENT['EXTERNAL'], cid, raw_len, data)
+    seq = slice_hdr['sequence_id']                       # the container starts at -1 and takes the slice's id unless that is -1
+    if seq != -1:
+        start, span = slice_hdr['alignment_start'], slice_hdr['alignment_span']       # min start, max(start + span) - min start
+    else:
+        start, span = -1, 0                              # Container's initial values [Container.java:28-30]
+    hdr = container_header_v3(len(blocks), seq, start, span, slice_hdr['n_records'], global_record_counter, slice_hdr['bases'],
+                              3 + len(external), [len(chb)])
+    return hdr + blocks

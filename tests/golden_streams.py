@@ -44,3 +44,21 @@ def load():
         series = {int(k): base64.b64decode(v) for k, v in c['series'].items()}
         out.append((c, rd, series))
     return g, ref, out
+
+
+def container_parts(c, series):
+    """what a golden container is made of, for the container restatement / assembly: (slice header dict, global record counter,
+    compression header bytes, content ids in the jar's map order, tags in the slice's order, core bytes, external blocks
+    [(content id, method ordinal, raw length, bytes)] -- the bytes the stubbed compressor returned: the raw series)"""
+    from oracle import records as orec
+    cv = c['container_v3']
+    s = c['slice']
+    md5 = base64.b64decode(c['ref_md5']) if c['ref_md5'] else bytes(16)
+    tags = [(t[0], base64.b64decode(t[1])) for t in c['slice_tags']]
+    td = dict(tags)
+    hdr = dict(sequence_id=s['sequence_id'], alignment_start=s['alignment_start'], alignment_span=max(s['alignment_span'], 0),
+               n_records=s['n_records'], bases=s['bases'], ref_md5=md5,
+               bd=int.from_bytes(td['BD'], 'little'), sd=int.from_bytes(td['SD'], 'little'))
+    ids = cv['content_ids']
+    ext = [(cid, orec.BLOCK_METHOD[c['compressors'][str(cid)]['method']], len(series[cid]), series[cid]) for cid in ids]
+    return hdr, cv['global_record_counter'], base64.b64decode(cv['compression_header']), ids, tags, base64.b64decode(c['core']), ext

@@ -6,6 +6,7 @@ import re
 import pytest
 
 from cramtools_b200 import _lib
+from cramtools_b200 import records, sharding  # noqa: F401  (they register their signatures)
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 

@@ -217,3 +217,22 @@ def test_slice_ref_md5_matches_jar(G):
             assert got == base64.b64decode(c['ref_md5']), c['tag']
             seen += 1
     assert seen >= 2
+
+
+def test_container_bytes_match_jar(G):
+    """SURVEY 8f-5, the container part: ContainerIO.writeContainer of the three golden containers as the jar wrote them in the
+    mini-JVM -- container header with CRC32, compression header block, slice header block with the digest tags, core and
+    external blocks in the jar's HashMap order; LTF8 of a 6e9 record counter; the multi-reference slice"""
+    g, ref, conts = G
+    assert orec.ltf8(0) == b'\x00' and orec.ltf8(127) == b'\x7f' and orec.ltf8(128) == b'\x80\x80' and len(orec.ltf8(1 << 56)) == 9
+    for c, rd, series in conts:
+        hdr, grc, chb, ids, tags, core, ext = gs.container_parts(c, series)
+        cv = c['container_v3']
+        shc = orec.slice_header_content_v3(hdr['sequence_id'], hdr['alignment_start'], hdr['alignment_span'], hdr['n_records'], grc, ids,
+                                           hdr['ref_md5'], tags)
+        assert shc == base64.b64decode(cv['slice_header_content']), c['tag']
+        whole = orec.container_v3(hdr, grc, chb, ids, hdr['ref_md5'], tags, (0, len(core), core), ext)
+        want = base64.b64decode(cv['bytes'])
+        assert whole == want, c['tag']
+        assert int.from_bytes(want[:4], 'little') == cv['byte_size'] and cv['block_count'] == 3 + len(ids)
+        assert ids == sorted(ids)          # HashMap<Integer, Block> with fewer keys than buckets iterates in key order
