@@ -244,7 +244,7 @@ static const int8_t ILLUMINA_BIN[110] = {
     40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40, 40};
 
 enum { RC_NONE = 0, RC_ALL, RC_UNPLACED, RC_LOWER_MAPQ, RC_HIGHER_MAPQ };
-enum { BC_MATCH = 1, BC_MISMATCH, BC_FLANKING_DELETION, BC_INSERTION };
+enum { BC_MATCH = 1, BC_MISMATCH, BC_FLANKING_DELETION, BC_INSERTION, BC_LOWER_COVERAGE, BC_PILEUP };   /* the last two: parameter in bits 8..31 */
 enum { T_PRESERVE = 0, T_BIN = 1, T_DROP = 2 };
 
 typedef struct {
@@ -254,8 +254,9 @@ typedef struct {
 } qs_policy_t;
 
 /* parsePolicies / parseSinglePolicy / readTreatment [QualityScorePreservation.java:141-256].
- * Returns the number of policies (sorted: DROP, BIN, PRESERVE; stable), -1 = unknown category,
- * -2 = needs ReferenceTracks counters (X, P: not restated). */
+ * Returns the number of policies (sorted: DROP, BIN, PRESERVE; stable), -1 = unknown category.
+ * X<n> (coverage below n; reads no treatment) and P<n> (more than n mismatches piled up; then a treatment) [:210-233]
+ * become base categories BC_LOWER_COVERAGE / BC_PILEUP with n in bits 8..31. */
 int rec_oracle_parse_policies(const char *spec, qs_policy_t *out, int cap)
 {
     int n = 0;
@@ -285,7 +286,8 @@ int rec_oracle_parse_policies(const char *spec, qs_policy_t *out, int cap)
                 case 'U': p.read_cat = RC_UNPLACED; READ_TREAT(); break;
                 case '_': READ_TREAT(); break;
                 case '*': p.read_cat = RC_ALL; READ_TREAT(); break;
-                case 'X': case 'P': return -2;
+                case 'X': { int v; READ_PARAM(v); if (p.n_base_cats < 8) p.base_cat[p.n_base_cats++] = BC_LOWER_COVERAGE | (v << 8); } break;
+                case 'P': { int v; READ_PARAM(v); if (p.n_base_cats < 8) p.base_cat[p.n_base_cats++] = BC_PILEUP | (v << 8); READ_TREAT(); } break;
                 default: return -1;
                 }
                 if (!have_t) { p.treatment = T_PRESERVE; have_t = 1; }   /* null treatment -> preserve [:251-252] */
@@ -304,6 +306,121 @@ int rec_oracle_parse_policies(const char *spec, qs_policy_t *out, int cap)
     return n;
 }
 
+/* ------------------------------------------------------------------ ReferenceTracks (the X and P selectors)
+ * src/main/java/htsjdk/samtools/cram/ref/ReferenceTracks.java, literally: a window of `len` positions starting at the 1-based
+ * `position`; coverage and mismatches are Java shorts (they wrap); an index below 0 is Java's ArrayIndexOutOfBoundsException
+ * and a RuntimeException of ensureRange / moveForwardTo ends the conversion: both set `thrown` (1 = AIOOBE, 2 = "Cannot move
+ * the window backwards", 3 = "New position is beyond the reference"), after which nothing else is defined. */
+typedef struct {
+    const uint8_t *reference; int64_t ref_len;
+    int32_t position, len, thrown;
+    uint8_t *bases; int16_t *coverage, *mismatches;
+} tracks_t;
+
+tracks_t *rec_oracle_tracks_new(const uint8_t *reference, int64_t ref_len, int32_t window)        /* [:36-50] */
+{
+    tracks_t *t = calloc(1, sizeof *t);
+    t->reference = reference; t->ref_len = ref_len;
+    t->len = (int32_t)(window < ref_len ? window : ref_len);
+    t->bases = malloc((size_t)t->len + 1); t->coverage = calloc((size_t)t->len + 1, 2); t->mismatches = calloc((size_t)t->len + 1, 2);
+    t->position = 1;
+    memcpy(t->bases, reference, (size_t)t->len);                                                    /* reset() [:127-131] */
+    return t;
+}
+void rec_oracle_tracks_free(tracks_t *t) { if (t) { free(t->bases); free(t->coverage); free(t->mismatches); free(t); } }
+int32_t rec_oracle_tracks_position(const tracks_t *t) { return t->position; }
+int32_t rec_oracle_tracks_len(const tracks_t *t) { return t->len; }
+int32_t rec_oracle_tracks_thrown(const tracks_t *t) { return t->thrown; }
+const int16_t *rec_oracle_tracks_coverage(const tracks_t *t) { return t->coverage; }
+const int16_t *rec_oracle_tracks_mismatches(const tracks_t *t) { return t->mismatches; }
+
+static void tracks_move_forward_to(tracks_t *t, int32_t new_pos)                                    /* [:87-125] */
+{
+    if ((int64_t)new_pos - 1 >= t->ref_len) { t->thrown = 3; return; }
+    if (new_pos < t->position) { t->thrown = 2; return; }
+    if ((int64_t)new_pos > t->ref_len - t->len + 1) new_pos = (int32_t)(t->ref_len - t->len + 1);
+    if (new_pos == t->position) return;
+    int64_t n = t->ref_len - new_pos + 1; if (n > t->len) n = t->len;
+    memcpy(t->bases, t->reference + new_pos - 1, (size_t)n);
+    if (new_pos > t->position && t->position + t->len - new_pos > 0) {
+        for (int32_t i = 0; i < t->len; i++) {
+            if (i + new_pos - t->position < t->len) { t->coverage[i] = t->coverage[i + new_pos - t->position]; t->mismatches[i] = t->mismatches[i + new_pos - t->position]; }
+            else { t->coverage[i] = 0; t->mismatches[i] = 0; }
+        }
+    } else { memset(t->coverage, 0, 2 * (size_t)t->len); memset(t->mismatches, 0, 2 * (size_t)t->len); }
+    t->position = new_pos;
+}
+void rec_oracle_tracks_ensure_range(tracks_t *t, int32_t start, int32_t length)                     /* [:133-139] */
+{
+    if (t->thrown) return;
+    if (start < t->position) { t->thrown = 2; return; }
+    if ((int64_t)start + length > (int64_t)t->position + t->len) tracks_move_forward_to(t, start);
+}
+static uint8_t tracks_base_at(tracks_t *t, int32_t pos)                                             /* [:141-146] */
+{
+    if (pos - t->position < t->len) { if (pos - t->position < 0) { t->thrown = 1; return 0; } return t->bases[pos - t->position]; }
+    return 'N';
+}
+static int16_t tracks_coverage_at(tracks_t *t, int32_t pos)                                         /* [:148-154] */
+{
+    if (pos - t->position >= t->len) return 0;
+    if (pos - t->position < 0) { t->thrown = 1; return 0; }
+    return t->coverage[pos - t->position];
+}
+static int16_t tracks_mismatches_at(tracks_t *t, int32_t pos)                                       /* [:156-161] */
+{
+    if (pos - t->position >= t->len) return 0;
+    if (pos - t->position < 0) { t->thrown = 1; return 0; }
+    return t->mismatches[pos - t->position];
+}
+static void tracks_add(tracks_t *t, int16_t *track, int32_t pos)                                    /* addCoverage / addMismatches [:163-171] */
+{
+    if (pos - t->position < t->len) { if (pos - t->position < 0) { t->thrown = 1; return; } track[pos - t->position] = (int16_t)(track[pos - t->position] + 1); }
+}
+/* alignment end as SAMRecord.getAlignmentEnd gives it: 0 for a record with the unmapped flag */
+static int32_t sam_alignment_end(int32_t pos, uint16_t flag, const uint32_t *cigar, int64_t ncig)
+{
+    if (flag & SAM_UNMAPPED) return 0;
+    int64_t rl = 0;
+    for (int64_t c = 0; c < ncig; c++) if (consumes_ref(cigar[c] & 15)) rl += cigar[c] >> 4;
+    return (int32_t)(pos + rl - 1);
+}
+/* CramSerilization.getSpans for the records of one sequence (ref_id != -1 is the caller's business) [CramSerilization.java:60-86,
+ * AlignmentSpan.add :50-61]: union of (start, end - start).  n = 0 leaves *start = *span = 0 and returns 0. */
+int rec_oracle_span(int64_t n, const int32_t *pos, const uint16_t *flag, const uint32_t *cigar, const uint64_t *cigar_off, int32_t *start, int32_t *span)
+{
+    int have = 0; int32_t s0 = 0, sp0 = 0;
+    for (int64_t r = 0; r < n; r++) {
+        int32_t s = pos[r], sp = sam_alignment_end(pos[r], flag[r], cigar + cigar_off[r], (int64_t)(cigar_off[r + 1] - cigar_off[r])) - s;
+        if (!have) { s0 = s; sp0 = sp; have = 1; }
+        else if (s0 > s) { int32_t a = s0 + sp0, b = s + sp; sp0 = (a > b ? a : b) - s; s0 = s; }
+        else if (s0 < s) { int32_t a = s0 + sp0, b = s + sp; sp0 = (a > b ? a : b) - s0; }
+        else sp0 = sp0 > sp ? sp0 : sp;
+    }
+    *start = s0; *span = sp0;
+    return have;
+}
+/* CramSerilization.updateTracks for one record [CramSerilization.java:225-257], the inner loop's indices as they are written
+ * there: `pos` runs from readPos, and indexes the read at readPos + pos and the reference at refPos + pos */
+void rec_oracle_tracks_update(tracks_t *t, const uint8_t *rb, int64_t rlen, const uint32_t *cigar, int64_t ncig, int32_t pos)
+{
+    if (t->thrown || pos == 0) return;
+    int32_t ref_pos = pos; int64_t read_pos = 0;
+    for (int64_t c = 0; c < ncig && !t->thrown; c++) {
+        int op = cigar[c] & 15; int64_t len = cigar[c] >> 4;
+        if (consumes_ref(op)) for (int64_t e = 0; e < len; e++) tracks_add(t, t->coverage, (int32_t)(ref_pos + e));
+        if (op == OP_M || op == OP_X || op == OP_EQ) {
+            for (int64_t p = read_pos; p < len; p++) {
+                if (read_pos + p >= rlen) { t->thrown = 1; return; }
+                uint8_t read_base = rb[read_pos + p], ref_base = tracks_base_at(t, (int32_t)(ref_pos + p));
+                if (read_base != ref_base) tracks_add(t, t->mismatches, (int32_t)(ref_pos + p));
+            }
+        }
+        if (consumes_read(op)) read_pos += len;
+        if (consumes_ref(op)) ref_pos += (int32_t)len;
+    }
+}
+
 /*
  * addQualityScores for one read [QualityScorePreservation.java:276-301, 332-489].
  * scores[rlen] receives the array the reference leaves in record.qualityScores (0xFF = -1 = absent).
@@ -313,9 +430,20 @@ int rec_oracle_parse_policies(const char *spec, qs_policy_t *out, int cap)
  * the restatement goes on with entry 109 so that the other records of the batch can still be compared.
  * lossless (n_pol < 0): CramSerilization.java:160-161.
  */
+int rec_oracle_quality_t(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int has_quals, const uint32_t *cigar, int64_t ncig,
+                         int32_t pos, uint16_t flag, uint8_t mapq, const uint8_t *ref, int64_t ref_len,
+                         const qs_policy_t *pol, int n_pol, uint8_t *scores, tracks_t *t);
 int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int has_quals, const uint32_t *cigar, int64_t ncig,
                        int32_t pos, uint16_t flag, uint8_t mapq, const uint8_t *ref, int64_t ref_len,
                        const qs_policy_t *pol, int n_pol, uint8_t *scores)
+{
+    return rec_oracle_quality_t(rb, qs, rlen, has_quals, cigar, ncig, pos, flag, mapq, ref, ref_len, pol, n_pol, scores, NULL);
+}
+/* the same with the ReferenceTracks the conversion carries (t may be NULL: then X and P mask nothing); the per-base part asks
+ * the tracks for the record's range first [:397], which can move the window.  Check rec_oracle_tracks_thrown afterwards. */
+int rec_oracle_quality_t(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int has_quals, const uint32_t *cigar, int64_t ncig,
+                         int32_t pos, uint16_t flag, uint8_t mapq, const uint8_t *ref, int64_t ref_len,
+                         const qs_policy_t *pol, int n_pol, uint8_t *scores, tracks_t *t)
 {
     if (n_pol < 0) {
         if (has_quals) memcpy(scores, qs, (size_t)rlen);
@@ -348,10 +476,11 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
             continue;
         }
         if (pos == 0) continue;                                      /* NO_ALIGNMENT_START [:394-396] */
+        if (t) rec_oracle_tracks_ensure_range(t, pos, sam_alignment_end(pos, flag, cigar, ncig) - pos);     /* alSpan [:334, :397] */
         memset(mask, 0, (size_t)rlen + 1);
         for (int b = 0; b < p->n_base_cats; b++) {
             int64_t rp = 0, refp;
-            switch (p->base_cat[b]) {
+            switch (p->base_cat[b] & 0xFF) {
             case BC_FLANKING_DELETION:
                 for (int64_t c = 0; c < ncig; c++) {
                     int op = cigar[c] & 15; int64_t len = cigar[c] >> 4;
@@ -368,7 +497,7 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
                             int64_t z = refp + i - 1;                 /* tracks.baseAt(refPos + i) */
                             uint8_t tb = (z >= 0 && z < ref_len) ? ref[z] : 0;
                             int match = rb[rp + i] == tb;
-                            mask[rp + i] = (p->base_cat[b] == BC_MATCH) ? match : !match;
+                            mask[rp + i] = ((p->base_cat[b] & 0xFF) == BC_MATCH) ? match : !match;
                         }
                         rp += len;
                     }
@@ -381,6 +510,19 @@ int rec_oracle_quality(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int h
                     if (op == OP_I) for (int64_t i = 0; i < len && rp + i < rlen; i++) mask[rp + i] = 1;
                     if (consumes_read(op)) rp += len;
                 }
+                break;
+            case BC_LOWER_COVERAGE:                                  /* [:447-465]: pos starts at 1, the mask index is pos + i - 1 */
+                refp = pos;
+                for (int64_t c = 0; c < ncig && t; c++) {
+                    int op = cigar[c] & 15; int64_t len = cigar[c] >> 4;
+                    if (op == OP_M || op == OP_EQ || op == OP_X)
+                        for (int64_t i = 0; i < len && rp + i < rlen; i++) mask[rp + i] = tracks_coverage_at(t, (int32_t)(refp + i)) < (p->base_cat[b] >> 8);
+                    if (consumes_read(op)) rp += len;
+                    if (consumes_ref(op)) refp += len;
+                }
+                break;
+            case BC_PILEUP:                                          /* [:466-470]: position = alignment start + index in the read */
+                for (int64_t i = 0; i < rlen && t; i++) if (tracks_mismatches_at(t, (int32_t)(pos + i)) > (p->base_cat[b] >> 8)) mask[i] = 1;
                 break;
             }
         }
