@@ -61,6 +61,21 @@ def lib():
         L.rec_oracle_slice_header.restype = None
         L.rec_oracle_slice_header.argtypes = [_c.c_int64, u8p, u8p, i64p, u8p, i32p, i32p, u16p, u8p, i32p, i32p, i64p,
                                               _c.POINTER(SliceHeader)]
+        L.rec_oracle_tracks_new.restype = _c.c_void_p
+        L.rec_oracle_tracks_new.argtypes = [u8p, _c.c_int64, _c.c_int32]
+        L.rec_oracle_tracks_free.argtypes = [_c.c_void_p]
+        for nm in ('position', 'len', 'thrown'):
+            getattr(L, 'rec_oracle_tracks_' + nm).restype = _c.c_int32
+            getattr(L, 'rec_oracle_tracks_' + nm).argtypes = [_c.c_void_p]
+        for nm in ('coverage', 'mismatches'):
+            getattr(L, 'rec_oracle_tracks_' + nm).restype = _c.POINTER(_c.c_int16)
+            getattr(L, 'rec_oracle_tracks_' + nm).argtypes = [_c.c_void_p]
+        L.rec_oracle_tracks_ensure_range.argtypes = [_c.c_void_p, _c.c_int32, _c.c_int32]
+        L.rec_oracle_tracks_update.argtypes = [_c.c_void_p, u8p, _c.c_int64, u32p, _c.c_int64, _c.c_int32]
+        L.rec_oracle_span.restype = _c.c_int
+        L.rec_oracle_span.argtypes = [_c.c_int64, i32p, u16p, u32p, _c.POINTER(_c.c_uint64), i32p, i32p]
+        L.rec_oracle_quality_t.restype = _c.c_int
+        L.rec_oracle_quality_t.argtypes = L.rec_oracle_quality.argtypes + [_c.c_void_p]
         _done = True
     return L
 
@@ -133,8 +148,6 @@ def parse_policies(spec):
     n = lib().rec_oracle_parse_policies(spec.encode(), arr, 16)
     if n == -1:
         raise ValueError('Unknown read or base category')
-    if n == -2:
-        raise ValueError('selector needs ReferenceTracks counters (X/P): not restated')
     return arr, n
 
 
@@ -188,8 +201,10 @@ def extract(rd, ref):
     return out
 
 
-def quality(rd, ref, spec):
-    """row Q for every read.  -> (force_qs u8[n] (bit0 force, bit1 has array), scores u8[sum len] 0xFF = absent)"""
+def quality(rd, ref, spec, tracks=None, positions=None):
+    """row Q for every read.  -> (force_qs u8[n] (bit0 force, bit1 has array), scores u8[sum len] 0xFF = absent).
+    tracks: a Tracks object after .container(rd) when the model has X / P selectors (positions: list that receives the
+    window position after every record)"""
     n = len(rd['pos'])
     pol = parse_policies(spec)
     arr, npol = (None, -1) if pol is None else pol
@@ -209,10 +224,65 @@ def quality(rd, ref, spec):
         q = quals[lo:hi] if hi > lo else dummy
         cg = cigar[c0:c1] if c1 > c0 else dummyc
         sc = scores[lo:hi] if hi > lo else dummy
-        force[r] = lib().rec_oracle_quality(_p(rb, u8p), _p(q, u8p), hi - lo, 0 if (rflags[r] & 1) else 1, _p(cg, u32p),
-                                            c1 - c0, int(rd['pos'][r]), int(rd['flag'][r]), int(rd['mapq'][r]),
-                                            _p(ref, u8p), ref.size, arr, npol, _p(sc, u8p))
+        force[r] = lib().rec_oracle_quality_t(_p(rb, u8p), _p(q, u8p), hi - lo, 0 if (rflags[r] & 1) else 1, _p(cg, u32p),
+                                              c1 - c0, int(rd['pos'][r]), int(rd['flag'][r]), int(rd['mapq'][r]),
+                                              _p(ref, u8p), ref.size, arr, npol, _p(sc, u8p), None if tracks is None else tracks.h)
+        if positions is not None:
+            positions.append(tracks.position)
     return force, scores[:bases.size]
+
+
+class Tracks(object):
+    """ReferenceTracks of one reference sequence (ref/ReferenceTracks.java, restated in records_oracle.c): the coverage and
+    mismatch counters the X and P selectors read, carried from container to container as CramSerilization.convert does"""
+    THROWN = {0: None, 1: 'java/lang/ArrayIndexOutOfBoundsException', 2: 'java/lang/RuntimeException', 3: 'java/lang/RuntimeException'}
+
+    def __init__(self, ref, window=1000000):
+        self.ref = np.ascontiguousarray(ref, np.uint8)                  # kept alive: the C side holds the pointer
+        self.h = lib().rec_oracle_tracks_new(_p(self.ref, u8p), self.ref.size, int(window))
+
+    def __del__(self):
+        if getattr(self, 'h', None):
+            lib().rec_oracle_tracks_free(self.h); self.h = None
+
+    position = property(lambda self: lib().rec_oracle_tracks_position(self.h))
+    length = property(lambda self: lib().rec_oracle_tracks_len(self.h))
+    thrown = property(lambda self: lib().rec_oracle_tracks_thrown(self.h))
+    coverage = property(lambda self: np.ctypeslib.as_array(lib().rec_oracle_tracks_coverage(self.h), (self.length,)).copy())
+    mismatches = property(lambda self: np.ctypeslib.as_array(lib().rec_oracle_tracks_mismatches(self.h), (self.length,)).copy())
+
+    def container(self, rd):
+        """what CramSerilization.convert does with the tracks before it looks at a record [:121-131]: the container's span on the
+        sequence (getSpans), ensureRange, updateTracks.  rd: the container's reads (ref_id -1 = unplaced).  -> (start, span)"""
+        n = len(rd['pos'])
+        ref_id = rd.get('ref_id', np.zeros(n, np.int32))
+        keep = np.flatnonzero(np.asarray(ref_id) != -1)
+        pos = np.ascontiguousarray(np.asarray(rd['pos'])[keep], np.int32); flag = np.ascontiguousarray(np.asarray(rd['flag'])[keep], np.uint16)
+        cigar = np.ascontiguousarray(rd['cigar'], np.uint32); bases = np.ascontiguousarray(rd['bases'], np.uint8)
+        if cigar.size == 0:
+            cigar = np.zeros(1, np.uint32)
+        if bases.size == 0:
+            bases = np.zeros(1, np.uint8)
+        co = np.asarray(rd['cigar_off'])
+        sub_off = np.zeros(keep.size + 1, np.uint64)
+        pieces = []
+        for k, r in enumerate(keep):
+            pieces.append(cigar[int(co[r]):int(co[r + 1])]); sub_off[k + 1] = sub_off[k] + (int(co[r + 1]) - int(co[r]))
+        sub = np.ascontiguousarray(np.concatenate(pieces) if pieces else np.zeros(1, np.uint32), np.uint32)
+        if sub.size == 0:
+            sub = np.zeros(1, np.uint32)
+        st, sp = _c.c_int32(0), _c.c_int32(0)
+        if not lib().rec_oracle_span(keep.size, _p(pos, i32p), _p(flag, u16p), _p(sub, u32p), sub_off.ctypes.data_as(_c.POINTER(_c.c_uint64)),
+                                     _c.byref(st), _c.byref(sp)):
+            return None
+        lib().rec_oracle_tracks_ensure_range(self.h, st.value, sp.value)
+        for r in keep:
+            lo, hi = int(rd['read_off'][r]), int(rd['read_off'][r + 1])
+            c0, c1 = int(co[r]), int(co[r + 1])
+            rb = bases[lo:hi] if hi > lo else np.zeros(1, np.uint8)
+            cg = cigar[c0:c1] if c1 > c0 else np.zeros(1, np.uint32)
+            lib().rec_oracle_tracks_update(self.h, _p(np.ascontiguousarray(rb), u8p), hi - lo, _p(np.ascontiguousarray(cg), u32p), c1 - c0, int(rd['pos'][r]))
+        return st.value, sp.value
 
 
 def restore_bases(pos, rlen, ex, r, window, window_off0, matrix):
