@@ -247,6 +247,10 @@ void cramgpu_destroy(cramgpu_ctx *ctx)
     if (ctx->hs_scratch.p) cudaFree(ctx->hs_scratch.p);
     if (ctx->slice_scratch.p) cudaFree(ctx->slice_scratch.p);
     if (ctx->mate_scratch.p) cudaFree(ctx->mate_scratch.p);
+    if (ctx->trk_scratch.p) cudaFree(ctx->trk_scratch.p);
+    if (ctx->trk_own.p) cudaFree(ctx->trk_own.p);
+    if (ctx->trk_ext.p) cudaFree(ctx->trk_ext.p);
+    if (ctx->pin_trk) cudaFreeHost(ctx->pin_trk);
     if (ctx->frame_scratch.p) cudaFree(ctx->frame_scratch.p);
     if (ctx->frame_out.p) cudaFree(ctx->frame_out.p);
     if (ctx->pin_frame) cudaFreeHost(ctx->pin_frame);

@@ -78,6 +78,10 @@ struct cramgpu_ctx {
     DevPool frame_scratch, frame_out;    // blocks.cu
     void *pin_frame = nullptr; size_t pin_frame_cap = 0; cudaEvent_t ev_frame = nullptr;
     DevPool mate_scratch;                // cramgpu_mate_link: name tables
+    DevPool trk_scratch, trk_own, trk_ext;   // tracks.cu: tables, per-container count arrays, the per-base selector bytes
+    void *pin_trk = nullptr; size_t pin_trk_cap = 0;
+    bool trk_armed = false;              // trk_ext holds the bytes of the reads the next feature call with X / P selectors takes
+    uint64_t trk_reads = 0; int trk_nsel = 0; int32_t trk_kind[7] = {0}, trk_param[7] = {0};
     DevPool slice_scratch, slice_in;     // cramgpu_slice_headers: accumulators, staged inputs of the host variant
     void *pin_slice = nullptr; size_t pin_slice_cap = 0; cudaEvent_t ev_slice = nullptr;
     void *pin_hs = nullptr, *pin_hs2 = nullptr; size_t pin_hs_cap = 0, pin_hs2_cap = 0;
@@ -141,6 +145,7 @@ int ctx_fail(cramgpu_ctx *ctx, int code, const char *fmt, ...);
 int ctx_cuda(cramgpu_ctx *ctx, cudaError_t e, const char *what);
 int pool_reserve(cramgpu_ctx *ctx, DevPool &pool, size_t bytes);
 int pinned_reserve(cramgpu_ctx *ctx, void **p, size_t *cap, size_t bytes);
+int tracks_selectors(const cramgpu_qs_policy *pol, int n_pol, int32_t *kind, int32_t *param);   // tracks.cu
 
 #define CUDA_TRY(ctx, call)                                            \
     do {                                                               \

@@ -34,12 +34,15 @@ struct PolSet {
     int n;                       // < 0: lossless
     int per_base;                // any policy with base categories
     int any_bin;                 // any policy with the BIN treatment (the only one that can fault, see bin_fault)
+    int n_ext;                   // X / P selectors in all policies together (each has a bit in the per-base ext bytes)
     cramgpu_qs_policy p[MAX_POL];
+    uint8_t ext_bit[MAX_POL][8]; // policy k, base category b (an X or a P) -> its bit in the ext byte (1..7; bit 0 = "base of an M/=/X operator")
 };
 
 struct RecArgs {
     // inputs
     const uint8_t *ref, *bases, *quals;
+    const uint8_t *qs_ext;       // X / P selectors: one byte per base (same offsets as bases) from tracks.cu, else NULL
     const uint64_t *read_off, *cigar_off;
     const uint32_t *cigar;
     const int32_t *pos;
@@ -118,29 +121,32 @@ __device__ __forceinline__ bool read_in_category(const cramgpu_qs_policy &p, uin
     }
 }
 // mask value of one per-base policy at one base (QualityScorePreservation.java:398-476)
-__device__ __forceinline__ bool base_mask(const cramgpu_qs_policy &p, bool match, bool is_ins, bool dmark)
+// ext = the base's byte from tracks.cu (0 without X / P selectors), eb = the policy's row of PolSet::ext_bit
+__device__ __forceinline__ bool base_mask(const cramgpu_qs_policy &p, bool match, bool is_ins, bool dmark, uint32_t ext, const uint8_t *eb)
 {
     bool m = false;
     for (int b = 0; b < p.n_base_cats; b++) {
-        switch (p.base_cat[b]) {
+        switch (p.base_cat[b] & 0xFF) {
         case 1: m = match; break;          // MATCH: assignment for every read-consuming position
         case 2: m = !match; break;         // MISMATCH
         case 3: m = m || dmark; break;     // FLANKING_DELETION: only sets
         case 4: m = m || is_ins; break;    // INSERTION: only sets
+        case 5: if (ext & 1) m = (ext >> eb[b]) & 1; break;       // LOWER_COVERAGE: assignment for the bases of M / = / X [:447-465]
+        case 6: m = m || ((ext >> eb[b]) & 1); break;             // PILEUP: only sets [:466-470]
         }
     }
     return m;
 }
 // the score addQualityScores leaves at one base (0xFF = -1 = none), policies in their sorted order
 __device__ __forceinline__ uint8_t score_at(const PolSet &ps, uint8_t q, uint16_t flag, uint8_t mapq, int32_t pos,
-                                            bool match, bool is_ins, bool dmark, int32_t *status)
+                                            bool match, bool is_ins, bool dmark, uint32_t ext, int32_t *status)
 {
     uint8_t s = 0xFF;
     for (int k = 0; k < ps.n; k++) {
         const cramgpu_qs_policy &p = ps.p[k];
         if (!read_in_category(p, flag, mapq)) continue;
         if (p.n_base_cats == 0) { if (p.treatment != 2) s = treat(q, p.treatment, status); }
-        else if (pos != 0 && base_mask(p, match, is_ins, dmark)) s = treat(q, p.treatment, status);
+        else if (pos != 0 && base_mask(p, match, is_ins, dmark, ext, ps.ext_bit[k])) s = treat(q, p.treatment, status);
     }
     return s;
 }
@@ -463,15 +469,20 @@ __global__ void __launch_bounds__(128) k_rec_multi(RecArgs a, PolSet ps, const u
 //   match / ins / dm: base equals the RAW reference base at its position / lies in an insertion / is at or right after
 //   the start of one of the last two deletions.
 // mask of one per-base policy over a group (base_mask above, bit-parallel)
-__device__ __forceinline__ uint32_t pb_mask(const cramgpu_qs_policy &p, uint32_t match, uint32_t ins, uint32_t dm)
+// one bit per byte of a word: bit j = byte j of v is non-zero in its low bit (v holds 0x00 / 0xFF per byte)
+__device__ __forceinline__ uint32_t nibble_of(uint32_t v) { return (((v & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
+// ext: the group's four ext bytes (byte j = base j), eb: the policy's row of PolSet::ext_bit
+__device__ __forceinline__ uint32_t pb_mask(const cramgpu_qs_policy &p, uint32_t match, uint32_t ins, uint32_t dm, uint32_t ext, const uint8_t *eb)
 {
     uint32_t m = 0;
     for (int b = 0; b < p.n_base_cats; b++) {
-        switch (p.base_cat[b]) {
+        switch (p.base_cat[b] & 0xFF) {
         case 1: m = match; break;            // MATCH: assignment
         case 2: m = ~match; break;           // MISMATCH
         case 3: m |= dm; break;              // FLANKING_DELETION: only sets
         case 4: m |= ins; break;             // INSERTION: only sets
+        case 5: { const uint32_t xv = nibble_of(ext); m = (m & ~xv) | (nibble_of(ext >> eb[b]) & xv); } break;   // LOWER_COVERAGE: assignment where valid
+        case 6: m |= nibble_of(ext >> eb[b]); break;                                                              // PILEUP: only sets
         }
     }
     return m;
@@ -480,8 +491,8 @@ __device__ __forceinline__ uint32_t pb_mask(const cramgpu_qs_policy &p, uint32_t
 // appl: bit k = policy k applies to the record (its read category)
 // binany = bases that any applicable policy bins, overridden later or not (those are the ones the reference indexes the
 // binning table with)
-__device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint32_t match, uint32_t ins, uint32_t dm, uint32_t &has, uint32_t &bin,
-                                          uint32_t &binany)
+__device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint32_t match, uint32_t ins, uint32_t dm, uint32_t ext, uint32_t &has,
+                                          uint32_t &bin, uint32_t &binany)
 {
     has = 0; bin = 0; binany = 0;
     for (int k = 0; k < ps.n; k++) {
@@ -489,14 +500,12 @@ __device__ __forceinline__ void pb_planes(const PolSet &ps, uint32_t appl, uint3
         const cramgpu_qs_policy &p = ps.p[k];
         uint32_t hit;
         if (p.n_base_cats == 0) { if (p.treatment == 2) continue; hit = ~0u; }
-        else hit = pb_mask(p, match, ins, dm);
+        else hit = pb_mask(p, match, ins, dm, ext, ps.ext_bit[k]);
         has = (has & ~hit) | (p.treatment != 2 ? hit : 0u);
         bin = (bin & ~hit) | (p.treatment == 1 ? hit : 0u);
         binany |= p.treatment == 1 ? hit : 0u;
     }
 }
-// one bit per byte of a word: bit j = byte j of v is non-zero in its low bit (v holds 0x00 / 0xFF per byte)
-__device__ __forceinline__ uint32_t nibble_of(uint32_t v) { return (((v & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; }
 // bits of the deletion-flank positions d_a, d_a + 1, d_b, d_b + 1 inside the group that starts at read offset z0
 __device__ __forceinline__ uint32_t pb_dm(int32_t z0, int32_t d_a, int32_t d_b)
 {
@@ -518,6 +527,7 @@ struct PbGroup {
     uint32_t op, len;    // the operator and its length
     uint32_t rel;        // offset of bit 0 inside the operator (I and S: the base's index)
     uint32_t av;         // the bases: aligned word (M / = / X) or one byte (I, S)
+    uint32_t ext;        // the bases' ext bytes (X / P selectors), byte j = bit j; 0 without
 };
 // Walks the operators of a record: visit(PbGroup) for the read-consuming ones in groups of up to four bases, other(op, len, z)
 // for the rest (and for an empty soft clip).  M / = / X segments go by aligned words of the bases, I and S base by base
@@ -539,8 +549,9 @@ __device__ __forceinline__ void pb_walk(const RecArgs &a, uint64_t lo, uint64_t 
         else if (op == OP_I || op == OP_S) {
             for (uint32_t i = 0; i < len; i++) {
                 const int64_t rp = (int64_t)pos - 1 + aoff + i;
-                const uint8_t b = rb[z + i], tb = (rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)0;
+                const uint8_t b = rb[z + i], tb = (rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N';       // baseAt beyond the window's end [ReferenceTracks.java:141-146]
                 g.z0 = (int32_t)(z + i); g.r0 = (int32_t)(aoff + i); g.valid = 1u; g.match = b == tb ? 1u : 0u; g.ins = op == OP_I ? 1u : 0u;
+                g.ext = a.qs_ext ? a.qs_ext[lo + z + i] : 0u;
                 g.dm = pb_dm(g.z0, d_a, d_b) & 1u; g.rel = i; g.av = b;
                 visit(g);
             }
@@ -562,6 +573,12 @@ __device__ __forceinline__ void pb_walk(const RecArgs &a, uint64_t lo, uint64_t 
                     if ((g.valid >> j) & 1) rv |= (uint32_t)Rs[(int64_t)4 * k + j - sa] << (8 * j);
                 g.z0 = (int32_t)(z + 4 * k) - (int32_t)sa; g.r0 = (int32_t)(aoff + 4 * k) - (int32_t)sa;
                 g.match = nibble_of(__vcmpeq4(g.av, rv)) & g.valid; g.ins = 0; g.dm = pb_dm(g.z0, d_a, d_b); g.rel = 4 * k - sa;
+                g.ext = 0;
+                if (a.qs_ext) {
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+                        if ((g.valid >> j) & 1) g.ext |= (uint32_t)a.qs_ext[lo + z + 4 * k + j - sa] << (8 * j);
+                }
                 visit(g);
             }
         }
@@ -582,7 +599,7 @@ __device__ __forceinline__ uint8_t pb_force(const RecArgs &a, const PolSet &ps, 
             [&](const PbGroup &g) {
 #pragma unroll
                 for (int k = 0; k < MAX_POL; k++)
-                    if (k < ps.n && ps.p[k].n_base_cats) masked[k] += __popc(pb_mask(ps.p[k], g.match, g.ins, g.dm) & g.valid);
+                    if (k < ps.n && ps.p[k].n_base_cats) masked[k] += __popc(pb_mask(ps.p[k], g.match, g.ins, g.dm, g.ext, ps.ext_bit[k]) & g.valid);
             },
             [&](uint32_t, uint32_t, uint32_t) {});
     bool f = false;
@@ -661,7 +678,7 @@ __device__ __forceinline__ uint32_t perbase_read(const RecArgs &a, const PolSet 
                     uint32_t has = 0, bin = 0;
                     if (qf) {
                         uint32_t binany;
-                        pb_planes(ps, appl, g.match, g.ins, g.dm, has, bin, binany);
+                        pb_planes(ps, appl, g.match, g.ins, g.dm, g.ext, has, bin, binany);
                         has &= valid;
                         if (ps.any_bin)
                             for (uint32_t m = binany & valid; m; m &= m - 1)
@@ -912,11 +929,12 @@ __device__ __forceinline__ void walk_read(const RecArgs &a, const PolSet &ps, co
                             int64_t zi = z + i;
                             uint8_t b = in ? rb[zi] : 0;
                             int64_t rp = (int64_t)pos - 1 + aoff + i;
-                            uint8_t tb = (in && rp >= 0 && rp < ref_len) ? ref[rp] : 0;   // tracks.baseAt(refPos + i)
+                            uint8_t tb = (in && rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N';   // tracks.baseAt(refPos + i)
                             bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
+                            const uint32_t ext = (in && a.qs_ext) ? a.qs_ext[lo + zi] : 0u;
                             for (int k = 0; k < ps.n; k++)
                                 if (ps.p[k].n_base_cats) {
-                                    bool m = in && base_mask(ps.p[k], b == tb, op == OP_I, dm);
+                                    bool m = in && base_mask(ps.p[k], b == tb, op == OP_I, dm, ext, ps.ext_bit[k]);
                                     masked[k] += __popc(__ballot_sync(0xFFFFFFFFu, m));
                                 }
                         }
@@ -1017,14 +1035,14 @@ __device__ __forceinline__ void walk_read(const RecArgs &a, const PolSet &ps, co
                     int64_t zi = z + i;
                     uint8_t b = in ? (rlen ? rb[zi] : (uint8_t)'N') : 0;                      // empty bases -> 'N' x cigarLen [:218-220]
                     int64_t rp = (int64_t)pos - 1 + aoff + i;
-                    uint8_t rraw = (in && rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                    uint8_t rraw = (in && rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N';     // baseAt: 'N' beyond the window's end
                     uint8_t refb = norm_base((in && rp < ref_len) ? rraw : (uint8_t)'N');     // [:306-308]
                     bool isX = in && isM && b != refb;
                     bool hasF = in && (isX || op == OP_I || (op == OP_S && i == 0));
                     uint8_t sc = 0xFF;
                     if (q_feats && in && zi < rlen) {
                         bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
-                        sc = score_at(ps, rq[zi], flag, mapq, pos, b == rraw, op == OP_I, dm, a.status);
+                        sc = score_at(ps, rq[zi], flag, mapq, pos, b == rraw, op == OP_I, dm, a.qs_ext ? a.qs_ext[lo + zi] : 0u, a.status);
                     }
                     bool hasQ = sc < 128;                                                     // scores[i] > -1 [:290]
                     uint32_t bF = __ballot_sync(0xFFFFFFFFu, hasF), bQ = __ballot_sync(0xFFFFFFFFu, hasQ);
@@ -1217,7 +1235,7 @@ __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
     const uint8_t mapq = a.mapq[r];
     uint8_t *dst = a.streams + qoff;
     // read-level part of every base (bases not covered by a read-consuming CIGAR op see only these policies)
-    for (int64_t i = lane; i < rlen; i += 32) dst[i] = score_at(ps, rq[i], flag, mapq, 0, false, false, false, a.status);
+    for (int64_t i = lane; i < rlen; i += 32) dst[i] = score_at(ps, rq[i], flag, mapq, 0, false, false, false, 0u, a.status);
     if (!ps.per_base || pos == 0) return;
     __syncwarp();
     int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
@@ -1229,9 +1247,9 @@ __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
                 int64_t zi = z + i;
                 if (zi >= rlen) break;
                 int64_t rp = (int64_t)pos - 1 + aoff + i;
-                uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N';
                 bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
-                dst[zi] = score_at(ps, rq[zi], flag, mapq, pos, rb[zi] == tb, op == OP_I, dm, a.status);
+                dst[zi] = score_at(ps, rq[zi], flag, mapq, pos, rb[zi] == tb, op == OP_I, dm, a.qs_ext ? a.qs_ext[lo + zi] : 0u, a.status);
             }
             z += len;
         }
@@ -1242,12 +1260,12 @@ __global__ void __launch_bounds__(128) k_rec_forced_scores(RecArgs a, PolSet ps)
 // After a call whose status word says that a binned score was outside the binning table: which records?  One warp per
 // record, every base against every BIN policy that applies to it (the places where score_at calls treat with BIN), bit 7
 // of force_qs set for the records the reference throws on.  Runs only then.
-__device__ __forceinline__ bool bin_hits(const PolSet &ps, uint16_t flag, uint8_t mapq, int32_t pos, bool match, bool is_ins, bool dmark)
+__device__ __forceinline__ bool bin_hits(const PolSet &ps, uint16_t flag, uint8_t mapq, int32_t pos, bool match, bool is_ins, bool dmark, uint32_t ext)
 {
     for (int k = 0; k < ps.n; k++) {
         const cramgpu_qs_policy &p = ps.p[k];
         if (p.treatment != 1 || !read_in_category(p, flag, mapq)) continue;
-        if (p.n_base_cats == 0 || (pos != 0 && base_mask(p, match, is_ins, dmark))) return true;
+        if (p.n_base_cats == 0 || (pos != 0 && base_mask(p, match, is_ins, dmark, ext, ps.ext_bit[k]))) return true;
     }
     return false;
 }
@@ -1267,7 +1285,7 @@ __global__ void __launch_bounds__(128) k_rec_bin_fault(RecArgs a, PolSet ps)
     const uint16_t flag = a.flag[r];
     const uint8_t mapq = a.mapq[r];
     bool fault = false;
-    for (int64_t i = lane; i < rlen; i += 32) fault |= rq[i] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, 0, false, false, false);
+    for (int64_t i = lane; i < rlen; i += 32) fault |= rq[i] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, 0, false, false, false, 0u);
     if (ps.per_base && pos != 0) {
         int64_t z = 0, aoff = 0, d_a = -9, d_b = -9;
         for (uint64_t ci = a.cigar_off[r]; ci < a.cigar_off[r + 1]; ci++) {
@@ -1278,9 +1296,9 @@ __global__ void __launch_bounds__(128) k_rec_bin_fault(RecArgs a, PolSet ps)
                     int64_t zi = z + i;
                     if (zi >= rlen) break;
                     int64_t rp = (int64_t)pos - 1 + aoff + i;
-                    uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : 0;
+                    uint8_t tb = (rp >= 0 && rp < ref_len) ? ref[rp] : (uint8_t)'N';
                     bool dm = zi == d_a || zi == d_a + 1 || zi == d_b || zi == d_b + 1;
-                    fault |= rq[zi] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, pos, rb[zi] == tb, op == OP_I, dm);
+                    fault |= rq[zi] >= BIN_FAULT_Q && bin_hits(ps, flag, mapq, pos, rb[zi] == tb, op == OP_I, dm, a.qs_ext ? a.qs_ext[lo + zi] : 0u);
                 }
                 z += len;
             }
@@ -1718,7 +1736,8 @@ extern "C" int cramgpu_parse_lossy_spec(const char *spec, cramgpu_qs_policy *out
                 case 'U': p.read_cat = 2; read_treatment(); break;
                 case '_': read_treatment(); break;
                 case '*': p.read_cat = 1; read_treatment(); break;
-                case 'X': case 'P': return CRAMGPU_ERR_UNSUPPORTED;
+                case 'X': add_cat(5 | (read_param() << 8)); break;                     // lowerThanCoverage(n): reads no treatment [:210-213]
+                case 'P': add_cat(6 | (read_param() << 8)); read_treatment(); break;   // pileup(n) [:230-234]
                 default: return CRAMGPU_ERR_ARG;                        // "Unknown read or base category: " + code
                 }
                 if (!have_treatment) { p.treatment = 0; p.treat_param = 40; have_treatment = true; }
@@ -1751,7 +1770,13 @@ static int make_polset(cramgpu_ctx *ctx, const cramgpu_qs_policy *pol, int n, Po
         if (pol[k].n_base_cats < 0 || pol[k].n_base_cats > 8) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "bad policy");
         if (pol[k].n_base_cats) ps.per_base = 1;
         if (pol[k].treatment == 1) ps.any_bin = 1;
+        for (int b = 0; b < pol[k].n_base_cats; b++) {
+            const int cat = pol[k].base_cat[b] & 0xFF;
+            if (cat < 1 || cat > 6) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "bad policy");
+            if (cat >= 5) ps.ext_bit[k][b] = (uint8_t)(1 + ps.n_ext++);       // the order of tracks_selectors (tracks.cu)
+        }
     }
+    if (ps.n_ext > 7) return ctx_fail(ctx, CRAMGPU_ERR_UNSUPPORTED, "more than 7 X / P selectors in a lossy model");
     return CRAMGPU_OK;
 }
 
@@ -1788,6 +1813,17 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     }
     PolSet ps;
     if (int rc = make_polset(ctx, pol, npol, ps)) return rc;
+    // X / P selectors: the per-base bytes cramgpu_tracks_update_dev left for exactly these reads and selectors
+    const uint8_t *qs_ext = nullptr;
+    if (ps.n_ext) {
+        int32_t kind[7], param[7];
+        const int ns = tracks_selectors(pol, npol, kind, param);
+        bool same = ctx->trk_armed && ctx->trk_reads == n && ctx->trk_nsel == ns;
+        for (int e = 0; same && e < ns; e++) same = kind[e] == ctx->trk_kind[e] && param[e] == ctx->trk_param[e];
+        if (!same) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "The quality score lossy model requires reference tracks.");   // CramSerilization.java:121
+        qs_ext = (const uint8_t *)ctx->trk_ext.p;
+        ctx->trk_armed = false;
+    }
 
     Carver cv;
     size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_roff = cv.take(8 * (size_t)nc), o_rlen = cv.take(8 * (size_t)nc);
@@ -1818,6 +1854,7 @@ static int features_encode_impl(cramgpu_ctx *ctx, const cramgpu_reads *R, const 
     memset(&a, 0, sizeof a);
     a.ref = R->ref; a.bases = R->bases; a.quals = R->quals; a.read_off = R->read_off; a.cigar_off = R->cigar_off;
     a.cigar = R->cigar; a.pos = R->pos; a.flag = R->flag; a.mapq = R->mapq; a.rflags = R->rflags;
+    a.qs_ext = qs_ext;
     a.cont_off = (const uint64_t *)(S + o_cont); a.ref_off = (const uint64_t *)(S + o_roff); a.ref_len = (const uint64_t *)(S + o_rlen);
     a.n_containers = nc; a.n_reads = n;
     a.cnt = (uint32_t *)(S + o_cnt); a.force = S + o_force; a.subst = (unsigned long long *)(S + o_subst);

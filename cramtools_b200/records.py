@@ -530,3 +530,64 @@ def containers_assemble(d_slices, global_record_counter, comp_headers, block_fir
     out, olen, ooff = C.c_void_p(), C.c_uint64(), C.c_void_p()
     ctx.check(ctx.lib.cramgpu_containers_assemble_dev(ctx.handle, C.byref(I), C.byref(out), C.byref(olen), C.byref(ooff), stream))
     return out.value, olen.value, ooff.value
+
+
+# ---------------------------------------------------------------------------------------------- coverage / mismatch tracks (selectors X and P)
+_lib.SIGNATURES.update({
+    'cramgpu_tracks_create': (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32, C.POINTER(C.c_void_p)]),
+    'cramgpu_tracks_destroy': (None, [C.c_void_p, C.c_void_p]),
+    'cramgpu_tracks_position': (C.c_int64, [C.c_void_p]),
+    'cramgpu_tracks_update_dev': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(Reads), C.POINTER(QsPolicy), C.c_int, i32p, C.c_void_p]),
+})
+
+
+class ReferenceTracks(object):
+    """ref/ReferenceTracks.java for one sequence, on the device: carried from call to call like the reference carries its
+    object from container to container.  update(rd, spec, cont_off) = what CramSerilization.convert does with the tracks for a
+    batch of containers (span, ensureRange, updateTracks) plus the selector bytes the next features_encode call on the same
+    context consumes."""
+
+    def __init__(self, ref, window=0, ctx=None):
+        self.ctx = ctx or _lib.default_context()
+        ref = _arr(ref, np.uint8)
+        h = C.c_void_p()
+        self.ctx.check(self.ctx.lib.cramgpu_tracks_create(self.ctx.handle, _vp(ref), ref.size, int(window), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, 'h', None):
+            self.ctx.lib.cramgpu_tracks_destroy(self.ctx.handle, self.h); self.h = None
+
+    __del__ = close
+
+    @property
+    def position(self):
+        return int(self.ctx.lib.cramgpu_tracks_position(self.h))
+
+    def update(self, rd, spec, cont_off=None):
+        """-> per-container status list; raises CramGpuError (with .container_status) where the call fails"""
+        import torch
+        ctx = self.ctx
+        n = len(rd['pos'])
+        cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+        nc = cont_off.size - 1
+        dev = 'cuda:%d' % ctx.device if hasattr(ctx, 'device') else 'cuda:0'
+        host = dict(bases=_arr(rd['bases'], np.uint8), read_off=_arr(rd['read_off'], np.uint64), cigar=_arr(rd['cigar'], np.uint32),
+                    cigar_off=_arr(rd['cigar_off'], np.uint64), pos=_arr(rd['pos'], np.int32), flag=_arr(rd['flag'], np.uint16))
+        t = {k: torch.from_numpy(v.view(np.uint8).copy()).to(dev) for k, v in host.items()}
+        torch.cuda.synchronize()
+        R = Reads()
+        R.n_reads = n; R.n_containers = nc; R.cont_off = cont_off.ctypes.data_as(u64p)
+        for k, v in t.items():
+            setattr(R, k, v.data_ptr())
+        pol, npol = _policy_args(spec)
+        status = np.zeros(max(nc, 1), np.int32)
+        rc = ctx.lib.cramgpu_tracks_update_dev(ctx.handle, self.h, C.byref(R), pol, npol, status.ctypes.data_as(i32p), None)
+        ctx.sync()
+        self.container_status = status[:nc].tolist()
+        try:
+            ctx.check(rc)
+        except CramGpuError as e:
+            e.container_status = self.container_status
+            raise
+        return self.container_status

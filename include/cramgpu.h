@@ -225,7 +225,8 @@ typedef struct cramgpu_qs_policy {
     int32_t read_cat;      /* 0 none, 1 ALL (*), 2 UNPLACED (U), 3 LOWER_MAPPING_SCORE (m), 4 HIGHER_MAPPING_SCORE (M) */
     int32_t read_param;
     int32_t n_base_cats;   /* base categories in spec order (they overwrite one another exactly as in the reference) */
-    int32_t base_cat[8];   /* 1 MATCH (R), 2 MISMATCH (N), 3 FLANKING_DELETION (D), 4 INSERTION (I) */
+    int32_t base_cat[8];   /* 1 MATCH (R), 2 MISMATCH (N), 3 FLANKING_DELETION (D), 4 INSERTION (I); 5 LOWER_COVERAGE (X) and
+                              6 PILEUP (P) with their parameter in bits 8..31 -- these need cramgpu_tracks_update_dev first */
     int32_t treatment;     /* 0 PRESERVE, 1 BIN (Illumina 8-binning), 2 DROP */
     int32_t treat_param;
 } cramgpu_qs_policy;
@@ -233,9 +234,9 @@ typedef struct cramgpu_qs_policy {
 /*
  * Replaces QualityScorePreservation.parsePolicies(String) (lossy/QualityScorePreservation.java:167-256):
  * "-"-separated policies, sorted DROP, BIN, PRESERVE (stable).  Host only.
- * Returns the number of policies written, CRAMGPU_ERR_ARG for "Unknown read or base category", or
- * CRAMGPU_ERR_UNSUPPORTED for the X / P selectors (they need ReferenceTracks coverage / pile-up counters that
- * carry state across containers; the reference itself throws unless tracks were set up).
+ * Returns the number of policies written, or CRAMGPU_ERR_ARG for "Unknown read or base category".  The X<n> / P<n>
+ * selectors (coverage below n; more than n mismatches piled up) read ReferenceTracks counters that carry state across
+ * containers: see cramgpu_tracks_update_dev.
  */
 int cramgpu_parse_lossy_spec(const char *spec, cramgpu_qs_policy *out, int cap);
 
@@ -584,6 +585,36 @@ int cramgpu_slice_headers(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_
 int cramgpu_slice_headers_dev(cramgpu_ctx *ctx, const cramgpu_slice_in *in, cramgpu_slice_header *d_out, void *stream);
 /* the four constant tags: sha1 = B1 = S1 (20 bytes), sha512 = B5 = S5 (64 bytes) */
 void cramgpu_slice_sha_tags(uint8_t sha1[20], uint8_t sha512[64]);
+
+/* ------------------------------------------------------------------ coverage / mismatch tracks: the lossy selectors X and P
+ *
+ * The reference keeps one ReferenceTracks per sequence (src/main/java/htsjdk/samtools/cram/ref/ReferenceTracks.java) across
+ * the containers of a file: CramSerilization.convert [CramSerilization.java:112-131] moves its window to the container's span
+ * (getSpans :60-86, ensureRange) and counts the container's records into it (updateTracks :225-257: coverage of every
+ * reference position an alignment covers, mismatches of the bases of M / = / X operators, with that loop's indices as written)
+ * before QualityScorePreservation.addQS asks coverageAt(pos) < n (X<n>, lossy/QualityScorePreservation.java:447-465) and
+ * mismatchesAt(alignment start + i) > n (P<n>, :466-470) for every record.
+ *
+ * cramgpu_tracks_create      the tracks of one sequence; ref = its raw bases (HOST), window = 0 for the reference's 1 000 000.
+ * cramgpu_tracks_update_dev  everything above for a batch of containers of that sequence (reads: DEVICE arrays as
+ *     cramgpu_features_encode_dev takes them, cont_off HOST; records with pos = 0 are unplaced; ref / ref_off / ref_len unused):
+ *     container c sees the counts of containers 0..c of this call and of all earlier calls.  It leaves one byte per base in the
+ *     context; the NEXT cramgpu_features_encode* call on the context with the same reads and the same policies consumes them
+ *     (without them a model with X or P fails with "The quality score lossy model requires reference tracks.", :121).  A model
+ *     without X and P leaves the tracks untouched, as the reference does.  container_status (HOST [n_containers], may be NULL):
+ *     CRAMGPU_ERR_ARG where the reference throws ("Cannot move the window backwards", "New position is beyond the reference"),
+ *     CRAMGPU_ERR_UNSUPPORTED for a container that reaches beyond the window after the window was moved to its start (span
+ *     above the window: the reference then moves the window between records -- not modelled) or that holds a record without
+ *     bases; the first such container fails the call (nothing is left for the feature call) and the tracks stay unusable,
+ *     as after the reference's exception.  One stream synchronisation inside.
+ * cramgpu_tracks_position    ReferenceTracks.getWindowPosition() after the last call.
+ */
+typedef struct cramgpu_tracks cramgpu_tracks;
+int cramgpu_tracks_create(cramgpu_ctx *ctx, const uint8_t *ref, uint64_t ref_len, uint32_t window, cramgpu_tracks **out);
+void cramgpu_tracks_destroy(cramgpu_ctx *ctx, cramgpu_tracks *t);
+int64_t cramgpu_tracks_position(const cramgpu_tracks *t);
+int cramgpu_tracks_update_dev(cramgpu_ctx *ctx, cramgpu_tracks *t, const cramgpu_reads *reads, const cramgpu_qs_policy *pol, int n_pol,
+                              int32_t *container_status, void *stream);
 
 /* ------------------------------------------------------------------ mate linking
  *

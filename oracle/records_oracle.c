@@ -495,7 +495,7 @@ int rec_oracle_quality_t(const uint8_t *rb, const uint8_t *qs, int64_t rlen, int
                     if (consumes_read(op)) {
                         for (int64_t i = 0; i < len && rp + i < rlen; i++) {
                             int64_t z = refp + i - 1;                 /* tracks.baseAt(refPos + i) */
-                            uint8_t tb = (z >= 0 && z < ref_len) ? ref[z] : 0;
+                            uint8_t tb = t ? tracks_base_at(t, (int32_t)(refp + i)) : (z >= 0 && z < ref_len) ? ref[z] : (uint8_t)'N';   /* beyond the window: 'N' [ReferenceTracks.java:141-146] */
                             int match = rb[rp + i] == tb;
                             mask[rp + i] = ((p->base_cat[b] & 0xFF) == BC_MATCH) ? match : !match;
                         }

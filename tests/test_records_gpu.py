@@ -65,8 +65,8 @@ def test_lossy_spec_parser(R):
     assert [x.treatment for x in p] == [1, 0] and p[0].base_cat[0] == 1 and p[1].base_cat[0] == 2
     with pytest.raises(_lib.CramGpuError):
         R.QualityScorePreservation.lossyFromSpec('Z9')
-    with pytest.raises(_lib.CramGpuError):
-        R.QualityScorePreservation.lossyFromSpec('X10')
+    p = R.QualityScorePreservation.lossyFromSpec('X10-P2_8').getPreservationPolicies()       # coverage / pile-up selectors (tests/test_tracks_gpu.py)
+    assert [x.treatment for x in p] == [1, 0] and p[0].base_cat[0] == 6 | (2 << 8) and p[1].base_cat[0] == 5 | (10 << 8)
 
 
 def _sim(n_reads, n_cont, seed, unmapped_tail=0):
