@@ -105,10 +105,25 @@ __global__ void __launch_bounds__(256) k_trk_ends(TrkArgs a)
     const int32_t end = (a.flag[r] & SAM_UNMAPPED) ? 0 : (int32_t)(pos + ref_l - 1);           // SAMRecord.getAlignmentEnd
     const int64_t q = (int64_t)pos + (all_l > (int64_t)rlen ? all_l : (int64_t)rlen);             // exclusive bound of every position asked
     TrkSum *s = a.sum + c;
-    atomicMin(&s->min_start, pos); atomicMax(&s->max_start, pos); atomicMax(&s->max_end, end);
-    atomicMax(&s->max_cov, (int32_t)(pos + ref_l - 1));
-    atomicMax(&s->max_query, (int32_t)(q > 0x7FFFFFFF ? 0x7FFFFFFF : q));
-    if (has_m && rlen == 0) atomicOr(&s->flags, 1u);
+    const int32_t cov_end = (int32_t)(pos + ref_l - 1), qq = (int32_t)(q > 0x7FFFFFFF ? 0x7FFFFFFF : q);
+    const uint32_t fl = (has_m && rlen == 0) ? 1u : 0u;
+    // the records of a warp are nearly always of one container: one set of atomics per warp then (10 000 records share five words)
+    const uint32_t act = __activemask();
+    const uint32_t c0 = __shfl_sync(act, c, __ffs(act) - 1);
+    if (__all_sync(act, c == c0)) {
+        const int32_t mn = __reduce_min_sync(act, pos), mx = __reduce_max_sync(act, pos), me = __reduce_max_sync(act, end);
+        const int32_t mc = __reduce_max_sync(act, cov_end), mq = __reduce_max_sync(act, qq);
+        const uint32_t f = __reduce_or_sync(act, fl);
+        if ((threadIdx.x & 31) == (uint32_t)(__ffs(act) - 1)) {
+            atomicMin(&s->min_start, mn); atomicMax(&s->max_start, mx); atomicMax(&s->max_end, me);
+            atomicMax(&s->max_cov, mc); atomicMax(&s->max_query, mq);
+            if (f) atomicOr(&s->flags, f);
+        }
+    } else {
+        atomicMin(&s->min_start, pos); atomicMax(&s->max_start, pos); atomicMax(&s->max_end, end);
+        atomicMax(&s->max_cov, cov_end); atomicMax(&s->max_query, qq);
+        if (fl) atomicOr(&s->flags, fl);
+    }
 }
 
 // one thread per record: its counts into the container's own arrays (updateTracks, CramSerilization.java:225-257)
@@ -175,18 +190,47 @@ __global__ void __launch_bounds__(1024) k_trk_scan(TrkArgs a)
     }
 }
 
-// what container c sees at `pos`: carry + the own arrays of containers c, c-1, ... whose reach covers pos
-__device__ __forceinline__ int32_t trk_seen(const TrkArgs &a, const int32_t *carry, const int32_t *own, uint32_t c, int64_t pos)
+// The containers whose own arrays can hold a position of a record that starts at `first`: c, c-1, ... while their reach
+// (a prefix maximum) is at or beyond it -- one or two on sorted input.  Up to TRK_NEAR of them are kept in registers; a
+// record with more (deep pile-ups over many containers) takes the walk through memory for the rest.
+#define TRK_NEAR 3
+struct TrkNear { int32_t start[TRK_NEAR], len[TRK_NEAR]; int64_t off[TRK_NEAR]; int n; int64_t more; int64_t position; };
+
+__device__ __forceinline__ TrkNear trk_near(const TrkArgs &a, uint32_t c, int64_t first)
 {
-    const TrkCont *k = a.cont + c;
-    if (pos - k->position >= a.window) return 0;                            // coverageAt / mismatchesAt beyond the window [:148-161]
+    TrkNear nr;
+    nr.n = 0; nr.more = -1; nr.position = a.cont[c].position;
+#pragma unroll
+    for (int k = 0; k < TRK_NEAR; k++) { nr.start[k] = 0; nr.len[k] = 0; nr.off[k] = 0; }
+    int64_t j = c;
+    for (; j >= 0; j--) {
+        const TrkCont &kj = a.cont[j];
+        if (kj.reach < first) break;
+        if (!kj.own_len) continue;
+        if (nr.n == TRK_NEAR) { nr.more = j; break; }
+#pragma unroll
+        for (int k = 0; k < TRK_NEAR; k++)
+            if (k == nr.n) { nr.start[k] = kj.start; nr.len[k] = kj.own_len; nr.off[k] = kj.own_off; }
+        nr.n++;
+    }
+    return nr;
+}
+// what the record's container sees at `pos`: carry + the own arrays that hold pos, as a Java short
+__device__ __forceinline__ int32_t trk_seen(const TrkArgs &a, const TrkNear &nr, const int32_t *carry, const int32_t *own, int64_t pos)
+{
+    if (pos - nr.position >= a.window) return 0;                            // coverageAt / mismatchesAt beyond the window [:148-161]
     int32_t v = carry[pos];
-    for (int64_t j = c; j >= 0; j--) {
+#pragma unroll
+    for (int k = 0; k < TRK_NEAR; k++) {
+        const int64_t d = pos - nr.start[k];
+        if (d >= 0 && d < nr.len[k]) v += own[nr.off[k] + d];
+    }
+    for (int64_t j = nr.more; j >= 0; j--) {
         const TrkCont &kj = a.cont[j];
         if (kj.reach < pos) break;                                          // prefix maximum: nothing further back holds pos either
         if (kj.own_len && pos >= kj.start && pos < (int64_t)kj.start + kj.own_len) v += own[kj.own_off + (pos - kj.start)];
     }
-    return (int32_t)(int16_t)v;                                             // the tracks are Java shorts
+    return (int32_t)(int16_t)v;
 }
 
 // one warp per record: the ext byte of every base -- bit 0 = base of an M / = / X operator, bit 1 + e = selector e holds
@@ -198,17 +242,23 @@ __global__ void __launch_bounds__(128) k_trk_masks(TrkArgs a)
     const uint64_t lo = a.read_off[r];
     const int64_t rlen = (int64_t)(a.read_off[r + 1] - lo);
     uint8_t *ext = a.ext + lo;
-    for (int64_t i = lane; i < rlen; i += 32) ext[i] = 0;
     const int32_t pos = a.pos[r];
-    if (pos == 0) return;                                                   // addQS returns before the masks [:394-396]
-    const uint32_t c = trk_container_of(a.cont_off, a.n_containers, r);
-    if (!a.cont[c].ok) return;
-    __syncwarp();
+    const uint32_t c = pos ? trk_container_of(a.cont_off, a.n_containers, r) : 0u;
+    if (pos == 0 || !a.cont[c].ok) {                                        // addQS returns before the masks [:394-396] / refused container
+        for (int64_t i = lane; i < rlen; i += 32) ext[i] = 0;
+        return;
+    }
+    const TrkNear nr = trk_near(a, c, pos);
+    bool any_p = false, any_x = false;
+    for (int s = 0; s < a.n_sel; s++) { any_p |= a.sel_kind[s] == 6; any_x |= a.sel_kind[s] == 5; }
     // selector P: position = alignment start + index in the read, whatever the CIGAR says [:466-470]
     for (int64_t i = lane; i < rlen; i += 32) {
         uint8_t e = 0;
-        for (int s = 0; s < a.n_sel; s++)
-            if (a.sel_kind[s] == 6 && trk_seen(a, a.carry_mm, a.own_mm, c, (int64_t)pos + i) > a.sel_param[s]) e |= (uint8_t)(2u << s);
+        if (any_p) {
+            const int32_t m = trk_seen(a, nr, a.carry_mm, a.own_mm, (int64_t)pos + i);
+            for (int s = 0; s < a.n_sel; s++)
+                if (a.sel_kind[s] == 6 && m > a.sel_param[s]) e |= (uint8_t)(2u << s);
+        }
         ext[i] = e;
     }
     __syncwarp();
@@ -220,8 +270,11 @@ __global__ void __launch_bounds__(128) k_trk_masks(TrkArgs a)
         if (op == OP_M || op == OP_EQ || op == OP_X) {
             for (int64_t i = lane; i < len && z + i < rlen; i += 32) {
                 uint8_t e = ext[z + i] | 1;
-                for (int s = 0; s < a.n_sel; s++)
-                    if (a.sel_kind[s] == 5 && trk_seen(a, a.carry_cov, a.own_cov, c, ref_pos + i) < a.sel_param[s]) e |= (uint8_t)(2u << s);
+                if (any_x) {
+                    const int32_t v = trk_seen(a, nr, a.carry_cov, a.own_cov, ref_pos + i);
+                    for (int s = 0; s < a.n_sel; s++)
+                        if (a.sel_kind[s] == 5 && v < a.sel_param[s]) e |= (uint8_t)(2u << s);
+                }
                 ext[z + i] = e;
             }
         }
