@@ -146,6 +146,79 @@ __global__ void __launch_bounds__(256) k_mate_link(MateArgs a)
     }
 }
 
+
+// ---- decode: the pairing part of CramNormalizer.normalize (CramNormalizer.java:67-102, 236-270), the inverse of the above ----
+// next / previous links from the compression flags and NF; restoreMateInfo along every chain that starts at a record nobody
+// points to.  The reference does it record by record; what comes out is order-free except where several records point to
+// one: `previous` is then the LAST of them, and where several chains end in one record its mate is the head that came
+// last -- both are maxima over record indices.
+struct RestArgs {
+    uint64_t n_reads; uint32_t n_containers;
+    const uint64_t *cont_off;
+    const uint16_t *flag; const uint8_t *cf; uint8_t *mate_flags; int32_t *nf;
+    const int32_t *ref_id; int32_t *pos, *mate_ref_id, *mate_pos, *tlen;
+    int32_t *next, *prev, *winner;            // scratch, record indices (-1 = none)
+    int32_t *status;                          // per container
+    MateArgs m;                               // read-only view for getAlignmentEnd / computeInsertSize
+};
+__device__ __forceinline__ bool rest_linked(const RestArgs &a, uint64_t r) { return (a.flag[r] & 1) && !(a.cf[r] & 2); }   // isMultiFragment() && !isDetached()
+__device__ __forceinline__ uint32_t rest_container_of(const uint64_t *cont_off, uint32_t nc, uint64_t r)
+{
+    uint32_t lo = 0, hi = nc;
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (cont_off[mid] <= r) lo = mid; else hi = mid; }
+    return lo;
+}
+
+__global__ void __launch_bounds__(256) k_mate_rest_links(RestArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (r >= a.n_reads) return;
+    if (a.ref_id && a.ref_id[r] == -1) a.pos[r] = 0;                        // NO_ALIGNMENT_START for an unplaced record [:69-72]
+    if (!rest_linked(a, r)) { a.nf[r] = -1; a.next[r] = -1; return; }      // [:81-87] (its `previous` is dropped too: see rest_prev)
+    a.next[r] = -1;
+    if (a.cf[r] & 4) {                                                      // isHasMateDownStream() [:88-93]
+        const uint32_t c = rest_container_of(a.cont_off, a.n_containers, r);
+        const int64_t j = (int64_t)r + 1 + a.nf[r];
+        if (a.nf[r] < 0 || j >= (int64_t)a.cont_off[c + 1]) { a.status[c] = CRAMGPU_ERR_CORRUPT; return; }      // records.get() throws
+        a.next[r] = (int32_t)j;
+        atomicMax(a.prev + j, (int32_t)r);
+    }
+}
+__device__ __forceinline__ int32_t rest_prev(const RestArgs &a, uint64_t r) { return rest_linked(a, r) ? a.prev[r] : -1; }
+
+__global__ void __launch_bounds__(256) k_mate_rest_last(RestArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (r >= a.n_reads || rest_prev(a, r) != -1 || a.next[r] == -1) return;
+    int32_t cur = (int32_t)r;
+    while (a.next[cur] != -1) cur = a.next[cur];                            // next > cur: the walk ends
+    atomicMax(a.winner + cur, (int32_t)r);
+}
+
+// setNextMate [:259-266]
+__device__ __forceinline__ void rest_set_next_mate(const RestArgs &a, int32_t r, int32_t m)
+{
+    const uint16_t fm = a.flag[m];
+    uint8_t f = a.mate_flags[r];                                            // CramCompressionRecord.mateFlags [:270-283]
+    f = (fm & 0x4) ? (f | 2) : (f & ~2);                                    // setMateUnmapped(next.isSegmentUnmapped())
+    f = (fm & 0x10) ? (f | 1) : (f & ~1);                                   // setMateNegativeStrand(next.isNegativeStrand())
+    a.mate_flags[r] = f;
+    const int32_t ms = a.ref_id ? a.ref_id[m] : 0;
+    a.mate_ref_id[r] = ms;
+    a.mate_pos[r] = ms == -1 ? 0 : a.pos[m];
+}
+
+__global__ void __launch_bounds__(256) k_mate_rest_apply(RestArgs a)
+{
+    const uint64_t r = (uint64_t)blockIdx.x * 256 + threadIdx.x;
+    if (r >= a.n_reads || rest_prev(a, r) != -1 || a.next[r] == -1) return;
+    int32_t cur = (int32_t)r;
+    while (a.next[cur] != -1) { rest_set_next_mate(a, cur, a.next[cur]); cur = a.next[cur]; }      // restoreMateInfo [:236-257]
+    const int32_t tl = insert_size(a.m, r, (uint64_t)cur);
+    a.tlen[r] = tl;
+    if (a.winner[cur] == (int32_t)r) { rest_set_next_mate(a, cur, (int32_t)r); a.tlen[cur] = -tl; }
+}
+
 }  // namespace
 
 static int mate_impl(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *d_cf, int32_t *d_nf, cudaStream_t st)
@@ -248,5 +321,48 @@ extern "C" int cramgpu_mate_link(cramgpu_ctx *ctx, const cramgpu_mate_in *in, ui
     CUDA_TRY(ctx, cudaMemcpyAsync(mate_cf, D + o_cf, n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(nf, D + o_nf, 4 * n, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    return CRAMGPU_OK;
+}
+
+
+extern "C" int cramgpu_mate_restore_dev(cramgpu_ctx *ctx, const cramgpu_mate_restore *io, int32_t *d_status, void *stream)
+{
+    if (!ctx) return CRAMGPU_ERR_ARG;
+    if (!io) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    const uint64_t n = io->n_reads;
+    const uint32_t nc = io->n_containers;
+    if (n == 0 || nc == 0) return CRAMGPU_OK;
+    if (!io->cont_off || !io->flag || !io->cf || !io->mate_flags || !io->nf || !io->pos || !io->mate_ref_id || !io->mate_pos || !io->tlen || !io->read_off ||
+        !io->feat_off || !d_status)
+        return ctx_fail(ctx, CRAMGPU_ERR_ARG, "null argument");
+    if (n > 0x7FFFFFF0ull) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "too many records");
+    if (io->cont_off[0] != 0 || io->cont_off[nc] != n) return ctx_fail(ctx, CRAMGPU_ERR_ARG, "cont_off does not cover the reads");
+    CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : ctx->stream;
+    Carver cv;
+    const size_t o_cont = cv.take(8 * (size_t)(nc + 1)), o_next = cv.take(4 * n), o_prev = cv.take(4 * n), o_win = cv.take(4 * n);
+    if (int rc = pool_reserve(ctx, ctx->mate_scratch, cv.off)) return rc;
+    uint8_t *S = (uint8_t *)ctx->mate_scratch.p;
+    if (int rc = pinned_reserve(ctx, &ctx->pin_slice, &ctx->pin_slice_cap, 8 * (size_t)(nc + 1) + 64)) return rc;
+    CUDA_TRY(ctx, cudaEventSynchronize(ctx->ev_slice));
+    memcpy(ctx->pin_slice, io->cont_off, 8 * (size_t)(nc + 1));
+    CUDA_TRY(ctx, cudaMemcpyAsync(S + o_cont, ctx->pin_slice, 8 * (size_t)(nc + 1), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(ctx, cudaEventRecord(ctx->ev_slice, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_prev, 0xFF, 4 * n, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(S + o_win, 0xFF, 4 * n, st));
+    CUDA_TRY(ctx, cudaMemsetAsync(d_status, 0, 4 * (size_t)nc, st));
+    RestArgs a;
+    memset(&a, 0, sizeof a);
+    a.n_reads = n; a.n_containers = nc; a.cont_off = (const uint64_t *)(S + o_cont);
+    a.flag = io->flag; a.cf = io->cf; a.mate_flags = io->mate_flags; a.nf = io->nf; a.ref_id = io->ref_id; a.pos = io->pos;
+    a.mate_ref_id = io->mate_ref_id; a.mate_pos = io->mate_pos; a.tlen = io->tlen;
+    a.next = (int32_t *)(S + o_next); a.prev = (int32_t *)(S + o_prev); a.winner = (int32_t *)(S + o_win); a.status = d_status;
+    a.m.n_reads = n; a.m.flag = io->flag; a.m.ref_id = io->ref_id; a.m.pos = io->pos; a.m.read_off = io->read_off; a.m.feat_off = io->feat_off;
+    a.m.f_op = io->f_op; a.m.f_val = io->f_val; a.m.f_aux = io->f_aux;
+    const unsigned grid = (unsigned)((n + 255) / 256);
+    LAUNCH(ctx, st, "k_mate_rest_links", k_mate_rest_links<<<grid, 256, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_mate_rest_last", k_mate_rest_last<<<grid, 256, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_mate_rest_apply", k_mate_rest_apply<<<grid, 256, 0, st>>>(a));
+    CUDA_TRY(ctx, cudaGetLastError());
     return CRAMGPU_OK;
 }

@@ -591,3 +591,43 @@ class ReferenceTracks(object):
             e.container_status = self.container_status
             raise
         return self.container_status
+
+
+# ---------------------------------------------------------------------------------------------- decode: restore the pairing
+class MateRestore(C.Structure):
+    _fields_ = [('n_reads', C.c_uint64), ('n_containers', C.c_uint32), ('cont_off', u64p), ('flag', C.c_void_p), ('cf', C.c_void_p),
+                ('mate_flags', C.c_void_p), ('nf', C.c_void_p), ('ref_id', C.c_void_p), ('pos', C.c_void_p), ('mate_ref_id', C.c_void_p), ('mate_pos', C.c_void_p),
+                ('tlen', C.c_void_p), ('read_off', C.c_void_p), ('feat_off', C.c_void_p), ('f_op', C.c_void_p), ('f_val', C.c_void_p),
+                ('f_aux', C.c_void_p)]
+
+
+_lib.SIGNATURES.update({
+    'cramgpu_mate_restore_dev': (C.c_int, [C.c_void_p, C.POINTER(MateRestore), C.c_void_p, C.c_void_p]),
+})
+
+
+def mate_restore(flag, cf, mate_flags, nf, ref_id, pos, mate_ref_id, mate_pos, tlen, read_off, f_op, f_val, f_aux, feat_off, cont_off=None, ctx=None):
+    """The pairing part of CramNormalizer.normalize through cramgpu_mate_restore_dev (arrays staged to the device with torch).
+    -> dict(mate_flags, nf, pos, mate_ref_id, mate_pos, tlen, status)"""
+    import torch
+    ctx = ctx or _lib.default_context()
+    n = len(flag)
+    cont_off = _arr([0, n] if cont_off is None else cont_off, np.uint64)
+    nc = cont_off.size - 1
+    dev = 'cuda:%d' % ctx.device
+    host = dict(flag=_arr(flag, np.uint16), cf=_arr(cf, np.uint8), mate_flags=_arr(mate_flags, np.uint8), nf=_arr(nf, np.int32), ref_id=_arr(ref_id, np.int32), pos=_arr(pos, np.int32),
+                mate_ref_id=_arr(mate_ref_id, np.int32), mate_pos=_arr(mate_pos, np.int32), tlen=_arr(tlen, np.int32),
+                read_off=_arr(read_off, np.uint64), feat_off=_arr(feat_off, np.uint64), f_op=_arr(f_op, np.uint8), f_val=_arr(f_val, np.int32),
+                f_aux=_arr(f_aux, np.int32))
+    t = {k: torch.from_numpy(v.view(np.uint8).copy()).to(dev) for k, v in host.items()}
+    st = torch.zeros(4 * max(nc, 1), dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    I = MateRestore()
+    I.n_reads = n; I.n_containers = nc; I.cont_off = cont_off.ctypes.data_as(u64p)
+    for k, v in t.items():
+        setattr(I, k, v.data_ptr())
+    ctx.check(ctx.lib.cramgpu_mate_restore_dev(ctx.handle, C.byref(I), st.data_ptr(), None))
+    ctx.sync()
+    out = {k: t[k].cpu().numpy().view(host[k].dtype)[:n].copy() for k in ('mate_flags', 'nf', 'pos', 'mate_ref_id', 'mate_pos', 'tlen')}
+    out['status'] = st.cpu().numpy().view(np.int32)[:nc].copy()
+    return out

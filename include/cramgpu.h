@@ -650,6 +650,35 @@ typedef struct cramgpu_mate_in {
 int cramgpu_mate_link(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *mate_cf, int32_t *nf);
 int cramgpu_mate_link_dev(cramgpu_ctx *ctx, const cramgpu_mate_in *in, uint8_t *d_mate_cf, int32_t *d_nf, void *stream);
 
+/* ------------------------------------------------------------------ decode: restore the pairing (inverse of cramgpu_mate_link)
+ *
+ * The pairing part of CramNormalizer.normalize (src/main/java/htsjdk/samtools/cram/build/CramNormalizer.java:67-102, 236-270) on
+ * the records as the reader left them (cramgpu_features_unpack*): an unplaced record (ref_id -1) gets alignment start 0; a record
+ * that is not multi-fragment (flag 0x1) or is detached (cf & 2) gets nf = -1 and no links; a linked record with a mate downstream
+ * (cf & 4) points to record index + 1 + nf of its container (beyond the container: d_status[c] = CRAMGPU_ERR_CORRUPT, records.get()
+ * throws); then along every chain that starts at a record nobody points to: setNextMate (mate start, mate sequence, and in the
+ * record's mate flags -- the MF byte, CramCompressionRecord.mateFlags [:270-283] -- bit 2 mate unmapped and bit 1 mate reverse from
+ * the next record; the last record takes them from the first) and the template size of the first and last record = +-computeInsertSize [:455-470] (getAlignmentEnd from the read features).  Detached records keep
+ * the mate fields the reader gave them.  All arrays DEVICE (cont_off HOST), nf / pos / mate_* / tlen are updated in place;
+ * asynchronous on `stream`.
+ */
+typedef struct cramgpu_mate_restore {
+    uint64_t n_reads;
+    uint32_t n_containers;
+    const uint64_t *cont_off;     /* HOST [n_containers+1] */
+    const uint16_t *flag;         /* SAM flags (BF series) */
+    const uint8_t *cf;            /* compression flags (CF series) */
+    uint8_t *mate_flags;          /* MF: 1 = mate on the reverse strand, 2 = mate unmapped */
+    int32_t *nf;                  /* recordsToNextFragment (NF series; anything where cf & 4 is not set) */
+    const int32_t *ref_id;        /* sequenceId; NULL = all 0 */
+    int32_t *pos;                 /* alignmentStart */
+    int32_t *mate_ref_id, *mate_pos, *tlen;
+    const uint64_t *read_off;     /* [n_reads+1] read lengths */
+    const uint64_t *feat_off;     /* [n_reads+1] read features, as cramgpu_features */
+    const uint8_t *f_op; const int32_t *f_val, *f_aux;
+} cramgpu_mate_restore;
+int cramgpu_mate_restore_dev(cramgpu_ctx *ctx, const cramgpu_mate_restore *io, int32_t *d_status, void *stream);
+
 /* ------------------------------------------------------------------ CIGAR rebuild and BAM records
  *
  * Device-resident entry points: every pointer is DEVICE memory; results are device memory owned by the context, valid until

@@ -269,10 +269,14 @@ def build(reads, ref, coordinate_sorted, tag):
     vm.call(DRF, 'buildReader', '(Lhtsjdk/samtools/cram/encoding/reader/AbstractReader;Lhtsjdk/samtools/cram/io/BitInputStream;Ljava/util/Map;L%s;I)Lhtsjdk/samtools/cram/encoding/reader/AbstractReader;' % CH,
             [new(DRF), reader, bitin, imap, header, sl.fields.get('sequenceId')])
     back = []
+    read_crs = []
     prev_start = sl.fields.get('alignmentStart')
     for i in range(len(recs)):
         cr = new(CCR)
         vm.call(RDR, 'read', '(L%s;)V' % CCR, [reader, cr])
+        if header.fields.get('APDelta', 0):                                 # ContainerParser.getRecords [:196-198]
+            prev_start = prev_start + cr.fields.get('alignmentDelta', 0)
+            cr.fields['alignmentStart'] = prev_start
         qs = cr.fields.get('qualityScores')
         rb = cr.fields.get('readBases')
         # the CIGAR Cram2SamRecordFactory rebuilds from the read features [Cram2SamRecordFactory.java:119-225]
@@ -314,6 +318,7 @@ def build(reads, ref, coordinate_sorted, tag):
         vm.call(BV, 'setTagData', '([BII)V', [view, jbytes(tagb), 0, len(tagb)])
         bsz = vm.call(BV, 'finish', '()I', [view])
         bam_rec = bytes(view.fields['buf'].a[:bsz])
+        read_crs.append(cr)
         back.append(dict(bam=b64(bam_rec), bam_bin=bam_bin, bam_tags=b64(tagb), flags=cr.fields.get('flags', 0), cf=i8(cr.fields.get('compressionFlags', 0)) & 0xFF, seq_id=cr.fields.get('sequenceId', 0),
                          read_length=cr.fields.get('readLength', 0), alignment_delta=cr.fields.get('alignmentDelta', 0),
                          alignment_start=cr.fields.get('alignmentStart', 0),
@@ -323,6 +328,21 @@ def build(reads, ref, coordinate_sorted, tag):
                          nf=cr.fields.get('recordsToNextFragment', 0), mapq=cr.fields.get('mappingQuality', 0),
                          features=features_of(cr), cigar2=cigar2, quals=None if qs is None else b64(qs.a), bases=None if rb is None else b64(rb.a)))
     out['read_back'] = back
+    # the pairing part of the decoder (the inverse of setMateInfo): CramNormalizer.normalize [CramNormalizer.java:67-143] on the
+    # records as the reader left them -- next / previous links from CF and NF, restoreMateInfo / setNextMate / computeInsertSize
+    # [:236-270, 455-470] (it also restores bases and scores: pinned elsewhere)
+    norm = new(G.NORM, '(L%s;)V' % SFH, header0)
+    lst = JObject('java/util/ArrayList'); lst.fields['list'] = list(read_crs)
+    try:
+        vm.call(G.NORM, 'normalize', '(Ljava/util/ArrayList;[BIL%s;)V' % G.SM, [norm, lst, jbytes(ref), 0, header.fields['substitutionMatrix']])
+    except JavaThrow:
+        pass            # a record that overhangs the reference ends the base restoration [:335-434]; the pairing passes ran before it
+    idx = {id(c): k for k, c in enumerate(read_crs)}
+    out['normalized_mates'] = [dict(flags=c.fields.get('flags', 0), mate_flags=i8(c.fields.get('mateFlags', 0)) & 0xFF, mate_seq_id=c.fields.get('mateSequenceID', 0),
+                                    mate_start=c.fields.get('mateAlignmentStart', 0), tlen=c.fields.get('templateSize', 0),
+                                    nf=c.fields.get('recordsToNextFragment', 0), alignment_start=c.fields.get('alignmentStart', 0),
+                                    next=idx.get(id(c.fields.get('next')), -1), previous=idx.get(id(c.fields.get('previous')), -1))
+                               for c in read_crs]
     left = {}
     for k, (key, bis) in imap.fields['map'].items():
         left[str(int(key.fields['value']))] = bis.fields['count'] - bis.fields['pos']

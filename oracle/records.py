@@ -807,3 +807,60 @@ def container_v3(slice_hdr, global_record_counter, compression_header, content_i
     hdr = container_header_v3(len(blocks), seq, start, span, slice_hdr['n_records'], global_record_counter, slice_hdr['bases'],
                               3 + len(external), [len(chb)])
     return hdr + blocks
+
+
+# ---------------------------------------------------------------------------------------------- decode: restore pairing (inverse of set_mate_info)
+def restore_mates(flag, cf, nf, seq_id, pos, mate_flags, mate_seq_id, mate_pos, tlen, aln_end):
+    """The pairing part of CramNormalizer.normalize (src/main/java/htsjdk/samtools/cram/build/CramNormalizer.java:67-102, 236-270)
+    for the records of one container as the reader left them, in order: next / previous links from the compression flags
+    (cf: 2 = detached, 4 = mate downstream) and NF, then restoreMateInfo along every chain that starts at a record nobody
+    points to -- setNextMate (mate start, mate sequence, and in the record's MATE flags [CramCompressionRecord.java:270-283] bit
+    2 = mate unmapped, bit 1 = mate on the reverse strand: the SAM flag bits 0x8 / 0x20 are only derived from them when the
+    SAMRecord is built) and the template size of the chain's first and last record (computeInsertSize [:455-470]).
+    aln_end: CramCompressionRecord.getAlignmentEnd per record.
+    -> dict(mate_flags, pos, mate_seq_id, mate_pos, tlen, nf, next, previous); raises IndexError where records.get() would throw"""
+    n = len(flag)
+    flag = [int(x) for x in flag]; pos = [int(x) for x in pos]; seq = [int(x) for x in seq_id]
+    mseq = [int(x) for x in mate_seq_id]; mpos = [int(x) for x in mate_pos]; ts = [int(x) for x in tlen]; nf = [int(x) for x in nf]
+    mf = [int(x) for x in mate_flags]
+    nxt = [-1] * n; prv = [-1] * n
+    end = [int(x) for x in aln_end]
+    for i in range(n):
+        if seq[i] == -1:
+            if not (flag[i] & 4):
+                end[i] -= pos[i]                                             # getAlignmentEnd is asked after the start was cleared
+            pos[i] = 0                                                       # [:69-72]
+    for i in range(n):
+        if not (flag[i] & 1) or (int(cf[i]) & 2):                           # !isMultiFragment() || isDetached() [:81-87]
+            nf[i] = -1; nxt[i] = -1; prv[i] = -1
+            continue
+        if int(cf[i]) & 4:                                                   # isHasMateDownStream() [:88-93]
+            j = i + 1 + nf[i]
+            if j < 0 or j >= n:
+                raise IndexError('records.get(%d)' % j)
+            nxt[i] = j; prv[j] = i
+
+    def set_next_mate(r, m):                                                 # [:259-266]
+        mpos[r] = pos[m]
+        mf[r] = (mf[r] | 2) if flag[m] & 0x4 else (mf[r] & ~2)           # setMateUnmapped(next.isSegmentUnmapped())
+        mf[r] = (mf[r] | 1) if flag[m] & 0x10 else (mf[r] & ~1)          # setMateNegativeStrand(next.isNegativeStrand())
+        mseq[r] = seq[m]
+        if mseq[r] == -1:
+            mpos[r] = 0
+
+    def insert_size(a, b):
+        if (flag[a] & 4) or (flag[b] & 4) or seq[a] != seq[b]:
+            return 0
+        pa = end[a] if flag[a] & 0x10 else pos[a]
+        pb = end[b] if flag[b] & 0x10 else pos[b]
+        return pb - pa + (1 if pb >= pa else -1)
+    for r in range(n):                                                       # [:95-101], restoreMateInfo [:236-257]
+        if prv[r] != -1 or nxt[r] == -1:
+            continue
+        cur = r
+        while nxt[cur] != -1:
+            set_next_mate(cur, nxt[cur]); cur = nxt[cur]
+        set_next_mate(cur, r)
+        tl = insert_size(r, cur)
+        ts[r] = tl; ts[cur] = -tl
+    return dict(mate_flags=mf, pos=pos, mate_seq_id=mseq, mate_pos=mpos, tlen=ts, nf=nf, next=nxt, previous=prv)

@@ -62,3 +62,39 @@ def container_parts(c, series):
     ids = cv['content_ids']
     ext = [(cid, orec.BLOCK_METHOD[c['compressors'][str(cid)]['method']], len(series[cid]), series[cid]) for cid in ids]
     return hdr, cv['global_record_counter'], base64.b64decode(cv['compression_header']), ids, tags, base64.b64decode(c['core']), ext
+
+
+def read_back_arrays(c):
+    """the records of a golden container as the jar's reader left them (ContainerParser's alignment starts included), as
+    arrays for the pairing restoration: flag, cf, nf, ref_id, pos, mate_ref_id, mate_pos, tlen, read_len, and the read
+    features that getAlignmentEnd looks at as (f_op, f_val, f_aux, feat_off)"""
+    rb = c['read_back']
+    n = len(rb)
+    f_op, f_val, f_aux, feat_off = [], [], [], [0]
+    for r in rb:
+        for f in r['features'] or []:
+            op = f[0]
+            ln = len(base64.b64decode(f[2])) if op in ('S', 'I') else f[2] if op in ('D', 'N', 'H', 'P') else 0
+            f_op.append(ord(op)); f_val.append(ln if op in ('D', 'N', 'H', 'P') else 0); f_aux.append(ln if op in ('S', 'I') else 0)
+        feat_off.append(len(f_op))
+    return dict(flag=np.array([r['flags'] for r in rb], np.uint16), cf=np.array([r['cf'] for r in rb], np.uint8),
+                mate_flags=np.array([r['mate_flags'] for r in rb], np.uint8), nf=np.array([r['nf'] for r in rb], np.int32), ref_id=np.array([r['seq_id'] for r in rb], np.int32),
+                pos=np.array([r['alignment_start'] for r in rb], np.int32), mate_ref_id=np.array([r['mate_seq_id'] for r in rb], np.int32),
+                mate_pos=np.array([r['mate_start'] for r in rb], np.int32), tlen=np.array([r['tlen'] for r in rb], np.int32),
+                read_off=np.concatenate([[0], np.cumsum([r['read_length'] for r in rb])]).astype(np.uint64),
+                f_op=np.array(f_op, np.uint8), f_val=np.array(f_val, np.int32), f_aux=np.array(f_aux, np.int32),
+                feat_off=np.array(feat_off, np.uint64), n=n)
+
+
+def read_back_ends(a):
+    """CramCompressionRecord.getAlignmentEnd per record of read_back_arrays [CramCompressionRecord.java:160-194]"""
+    ends = []
+    for r in range(a['n']):
+        if a['flag'][r] & 4:
+            ends.append(0); continue
+        span = int(a['read_off'][r + 1] - a['read_off'][r])
+        for f in range(int(a['feat_off'][r]), int(a['feat_off'][r + 1])):
+            op = chr(a['f_op'][f])
+            span += -1 if op == 'i' else -int(a['f_aux'][f]) if op == 'S' else int(a['f_val'][f]) if op == 'D' else 0
+        ends.append(int(a['pos'][r]) + span - 1)
+    return ends

@@ -236,3 +236,19 @@ def test_container_bytes_match_jar(G):
         assert whole == want, c['tag']
         assert int.from_bytes(want[:4], 'little') == cv['byte_size'] and cv['block_count'] == 3 + len(ids)
         assert ids == sorted(ids)          # HashMap<Integer, Block> with fewer keys than buckets iterates in key order
+
+
+def test_pairing_restoration_matches_jar(G):
+    """the inverse of setMateInfo: CramNormalizer.normalize's pairing passes run in the mini-JVM on the records the jar's reader
+    read back -- links, mate fields and template sizes of the linked pairs, untouched detached records"""
+    g, ref, conts = G
+    links = 0
+    for c, rd, series in conts:
+        a = gs.read_back_arrays(c)
+        got = orec.restore_mates(a['flag'], a['cf'], a['nf'], a['ref_id'], a['pos'], a['mate_flags'], a['mate_ref_id'], a['mate_pos'], a['tlen'], gs.read_back_ends(a))
+        want = c['normalized_mates']
+        for k, key in (('mate_flags', 'mate_flags'), ('mate_seq_id', 'mate_seq_id'), ('mate_pos', 'mate_start'), ('tlen', 'tlen'), ('nf', 'nf'),
+                       ('next', 'next'), ('previous', 'previous'), ('pos', 'alignment_start')):
+            assert [int(x) for x in got[k]] == [w[key] for w in want], (c['tag'], k)
+        links += sum(1 for w in want if w['next'] >= 0)
+    assert links == 10
