@@ -11,8 +11,9 @@
 // Here a call takes a batch of containers at once.  Every container gets its OWN count arrays over its span (coverage as
 // a difference array that one CTA per container scans; mismatches by atomics), and what container c sees at a position is
 //     carry(pos) + sum over j = c, c-1, ... of own_j(pos)        as long as max query end of containers 0..j >= pos
-// (a prefix maximum, so the walk stops after one or two containers on sorted input); at the end of the call the own arrays
-// are folded into the carry arrays, which live as long as the tracks object.  The window of ReferenceTracks (1 000 000
+// (a prefix maximum, so the walk stops after one or two containers on sorted input), evaluated once per position a
+// container's records can ask about (k_trk_bits) and spread to the bases by a CIGAR walk per record (k_trk_masks); at the end
+// of the call the own arrays are folded into the carry arrays, which live as long as the tracks object.  The window of ReferenceTracks (1 000 000
 // positions that slide forward) only shows as cut-offs: a position at or beyond window start + length is neither counted
 // nor read (0), and baseAt there is 'N'; the window start per container is a scan over the containers' spans that the
 // host does between two kernels (the only synchronisation).  What is NOT modelled: a window that moves while the records
@@ -62,6 +63,9 @@ struct TrkCont {
     int64_t own_off;        // their place in the own buffers (own_len + 1 slots: the difference array needs one more)
     int32_t reach;          // prefix maximum of the last position the own arrays of containers 0..c hold
     int32_t ok;             // 0: refused, the records get no ext bytes
+    int64_t q_off;          // the container's selector bytes: one per position start .. start + q_len - 1 (what its records can ask
+    int32_t q_len;          //   about inside the window); bit 1 + e = selector e holds there, as this container sees the tracks
+    int32_t pad;
 };
 
 struct TrkArgs {
@@ -75,6 +79,7 @@ struct TrkArgs {
     int32_t *own_cov, *own_mm;
     const int32_t *carry_cov, *carry_mm;
     uint8_t *ext;
+    uint8_t *qbits;                    // selector bytes per (container, position), see TrkCont::q_off
     int n_sel; int32_t sel_kind[7], sel_param[7];        // the X (5) / P (6) selectors in policy order: bit 1 + e of the ext byte
 };
 
@@ -190,50 +195,42 @@ __global__ void __launch_bounds__(1024) k_trk_scan(TrkArgs a)
     }
 }
 
-// The containers whose own arrays can hold a position of a record that starts at `first`: c, c-1, ... while their reach
-// (a prefix maximum) is at or beyond it -- one or two on sorted input.  Up to TRK_NEAR of them are kept in registers; a
-// record with more (deep pile-ups over many containers) takes the walk through memory for the rest.
-#define TRK_NEAR 3
-struct TrkNear { int32_t start[TRK_NEAR], len[TRK_NEAR]; int64_t off[TRK_NEAR]; int n; int64_t more; int64_t position; };
-
-__device__ __forceinline__ TrkNear trk_near(const TrkArgs &a, uint32_t c, int64_t first)
+// what container c sees at `pos` (inside its window): carry + the own arrays of containers c, c-1, ... whose reach covers pos
+__device__ __forceinline__ int32_t trk_seen(const TrkArgs &a, const int32_t *carry, const int32_t *own, uint32_t c, int64_t pos)
 {
-    TrkNear nr;
-    nr.n = 0; nr.more = -1; nr.position = a.cont[c].position;
-#pragma unroll
-    for (int k = 0; k < TRK_NEAR; k++) { nr.start[k] = 0; nr.len[k] = 0; nr.off[k] = 0; }
-    int64_t j = c;
-    for (; j >= 0; j--) {
-        const TrkCont &kj = a.cont[j];
-        if (kj.reach < first) break;
-        if (!kj.own_len) continue;
-        if (nr.n == TRK_NEAR) { nr.more = j; break; }
-#pragma unroll
-        for (int k = 0; k < TRK_NEAR; k++)
-            if (k == nr.n) { nr.start[k] = kj.start; nr.len[k] = kj.own_len; nr.off[k] = kj.own_off; }
-        nr.n++;
-    }
-    return nr;
-}
-// what the record's container sees at `pos`: carry + the own arrays that hold pos, as a Java short
-__device__ __forceinline__ int32_t trk_seen(const TrkArgs &a, const TrkNear &nr, const int32_t *carry, const int32_t *own, int64_t pos)
-{
-    if (pos - nr.position >= a.window) return 0;                            // coverageAt / mismatchesAt beyond the window [:148-161]
     int32_t v = carry[pos];
-#pragma unroll
-    for (int k = 0; k < TRK_NEAR; k++) {
-        const int64_t d = pos - nr.start[k];
-        if (d >= 0 && d < nr.len[k]) v += own[nr.off[k] + d];
-    }
-    for (int64_t j = nr.more; j >= 0; j--) {
+    for (int64_t j = c; j >= 0; j--) {
         const TrkCont &kj = a.cont[j];
         if (kj.reach < pos) break;                                          // prefix maximum: nothing further back holds pos either
         if (kj.own_len && pos >= kj.start && pos < (int64_t)kj.start + kj.own_len) v += own[kj.own_off + (pos - kj.start)];
     }
-    return (int32_t)(int16_t)v;
+    return (int32_t)(int16_t)v;                                             // the tracks are Java shorts
 }
 
-// one warp per record: the ext byte of every base -- bit 0 = base of an M / = / X operator, bit 1 + e = selector e holds
+// one CTA per container: the selectors at every position its records can ask about -- coverageAt(pos) < n [:447-465],
+// mismatchesAt(pos) > n [:466-470] -- evaluated once per position instead of once per base (45 reads cover a position)
+__global__ void __launch_bounds__(256) k_trk_bits(TrkArgs a)
+{
+    const uint32_t c = blockIdx.x;
+    const TrkCont k = a.cont[c];
+    if (!k.ok) return;
+    bool any_p = false, any_x = false;
+    for (int s = 0; s < a.n_sel; s++) { any_p |= a.sel_kind[s] == 6; any_x |= a.sel_kind[s] == 5; }
+    uint8_t *q = a.qbits + k.q_off;
+    for (int32_t i = threadIdx.x; i < k.q_len; i += 256) {
+        const int64_t pos = (int64_t)k.start + i;
+        const int32_t cov = any_x ? trk_seen(a, a.carry_cov, a.own_cov, c, pos) : 0;
+        const int32_t mm = any_p ? trk_seen(a, a.carry_mm, a.own_mm, c, pos) : 0;
+        uint8_t e = 0;
+        for (int s = 0; s < a.n_sel; s++)
+            if (a.sel_kind[s] == 5 ? cov < a.sel_param[s] : mm > a.sel_param[s]) e |= (uint8_t)(2u << s);
+        q[i] = e;
+    }
+}
+
+// one warp per record: the ext byte of every base -- bit 0 = base of an M / = / X operator, bit 1 + e = selector e holds.
+// Selector P asks at alignment start + index in the read, whatever the CIGAR says; selector X at the reference position
+// of the CIGAR walk, for the bases of M / = / X only.  A position beyond the window reads as 0 counts [ReferenceTracks.java:148-161].
 __global__ void __launch_bounds__(128) k_trk_masks(TrkArgs a)
 {
     const uint32_t lane = threadIdx.x & 31;
@@ -248,38 +245,35 @@ __global__ void __launch_bounds__(128) k_trk_masks(TrkArgs a)
         for (int64_t i = lane; i < rlen; i += 32) ext[i] = 0;
         return;
     }
-    const TrkNear nr = trk_near(a, c, pos);
-    bool any_p = false, any_x = false;
-    for (int s = 0; s < a.n_sel; s++) { any_p |= a.sel_kind[s] == 6; any_x |= a.sel_kind[s] == 5; }
-    // selector P: position = alignment start + index in the read, whatever the CIGAR says [:466-470]
-    for (int64_t i = lane; i < rlen; i += 32) {
-        uint8_t e = 0;
-        if (any_p) {
-            const int32_t m = trk_seen(a, nr, a.carry_mm, a.own_mm, (int64_t)pos + i);
-            for (int s = 0; s < a.n_sel; s++)
-                if (a.sel_kind[s] == 6 && m > a.sel_param[s]) e |= (uint8_t)(2u << s);
-        }
-        ext[i] = e;
+    const TrkCont k = a.cont[c];
+    const uint8_t *q = a.qbits + k.q_off;
+    uint8_t pmask = 0, xmask = 0, xbeyond = 0;                              // beyond the window: coverage 0 < n, mismatches 0 > n never
+    for (int s = 0; s < a.n_sel; s++) {
+        if (a.sel_kind[s] == 6) pmask |= (uint8_t)(2u << s);
+        else { xmask |= (uint8_t)(2u << s); if (0 < a.sel_param[s]) xbeyond |= (uint8_t)(2u << s); }
     }
-    __syncwarp();
-    // selector X: the bases of M / = / X operators, position by the CIGAR walk [:447-465]
     int64_t z = 0, ref_pos = pos;
     for (uint64_t ci = a.cigar_off[r]; ci < a.cigar_off[r + 1]; ci++) {
         const uint32_t cw = a.cigar[ci], op = cw & 15;
         const int64_t len = cw >> 4;
-        if (op == OP_M || op == OP_EQ || op == OP_X) {
+        if (t_consumes_read(op)) {
+            const bool is_m = op == OP_M || op == OP_EQ || op == OP_X;
             for (int64_t i = lane; i < len && z + i < rlen; i += 32) {
-                uint8_t e = ext[z + i] | 1;
-                if (any_x) {
-                    const int32_t v = trk_seen(a, nr, a.carry_cov, a.own_cov, ref_pos + i);
-                    for (int s = 0; s < a.n_sel; s++)
-                        if (a.sel_kind[s] == 5 && v < a.sel_param[s]) e |= (uint8_t)(2u << s);
+                const int64_t pi = (int64_t)pos + z + i - k.start;          // selector P's position
+                uint8_t e = (pi >= 0 && pi < k.q_len) ? (q[pi] & pmask) : (uint8_t)0;
+                if (is_m) {
+                    const int64_t xi = ref_pos + i - k.start;
+                    e |= 1 | ((xi >= 0 && xi < k.q_len) ? (q[xi] & xmask) : xbeyond);
                 }
                 ext[z + i] = e;
             }
+            z += len;
         }
-        if (t_consumes_read(op)) z += len;
         if (t_consumes_ref(op)) ref_pos += len;
+    }
+    for (int64_t i = z + lane; i < rlen; i += 32) {                         // bases the CIGAR does not reach: selector P only
+        const int64_t pi = (int64_t)pos + i - k.start;
+        ext[i] = (pi >= 0 && pi < k.q_len) ? (q[pi] & pmask) : (uint8_t)0;
     }
 }
 
@@ -396,7 +390,7 @@ extern "C" int cramgpu_tracks_update_dev(cramgpu_ctx *ctx, cramgpu_tracks *t, co
 
     // ---- the window per container: CramSerilization.convert [:117-127] + ReferenceTracks.ensureRange / moveForwardTo
     TrkCont *hc = (TrkCont *)(pm + p_cont);
-    int64_t position = t->position, own_total = 0;
+    int64_t position = t->position, own_total = 0, q_total = 0;
     const int64_t W = t->window, L = (int64_t)t->ref_len;
     int32_t reach = (int32_t)0x80000000;
     int fail_code = CRAMGPU_OK;
@@ -429,20 +423,27 @@ extern "C" int cramgpu_tracks_update_dev(cramgpu_ctx *ctx, cramgpu_tracks *t, co
         k.own_len = last >= start ? (int32_t)(last - start + 1) : 0;
         k.own_off = own_total;
         own_total += (int64_t)k.own_len + 1;
+        int64_t qlast = (int64_t)s.max_query - 1 < position + W - 1 ? (int64_t)s.max_query - 1 : position + W - 1;     // asked about, and inside the window
+        k.q_len = qlast >= start ? (int32_t)(qlast - start + 1) : 0;
+        k.q_off = q_total;
+        q_total += ((int64_t)k.q_len + 15) & ~15ll;
         if (k.own_len && (int32_t)last > reach) reach = (int32_t)last;
         k.reach = reach;
     }
     if (own_total > (int64_t)1 << 31) return ctx_fail(ctx, CRAMGPU_ERR_UNSUPPORTED, "tracks: the containers of one call span more than 2^31 positions in all");
     Carver co;
     const size_t q_cov = co.take(4 * (size_t)(own_total + 1)), q_mm = co.take(4 * (size_t)(own_total + 1));
+    const size_t zero_end = co.off;
+    const size_t q_bits = co.take((size_t)q_total + 16);
     if (int rc = pool_reserve(ctx, ctx->trk_own, co.off)) return rc;
     if (int rc = pool_reserve(ctx, ctx->trk_ext, bases_len + 16)) return rc;
     uint8_t *O = (uint8_t *)ctx->trk_own.p;
-    a.own_cov = (int32_t *)(O + q_cov); a.own_mm = (int32_t *)(O + q_mm); a.ext = (uint8_t *)ctx->trk_ext.p;
-    CUDA_TRY(ctx, cudaMemsetAsync(O, 0, co.off, st));
+    a.own_cov = (int32_t *)(O + q_cov); a.own_mm = (int32_t *)(O + q_mm); a.ext = (uint8_t *)ctx->trk_ext.p; a.qbits = O + q_bits;
+    CUDA_TRY(ctx, cudaMemsetAsync(O, 0, zero_end, st));
     CUDA_TRY(ctx, cudaMemcpyAsync(S + o_cont, pm + p_cont, sizeof(TrkCont) * (size_t)nc, cudaMemcpyHostToDevice, st));
     LAUNCH(ctx, st, "k_trk_own", k_trk_own<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(a));
     LAUNCH(ctx, st, "k_trk_scan", k_trk_scan<<<nc, 1024, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_trk_bits", k_trk_bits<<<nc, 256, 0, st>>>(a));
     LAUNCH(ctx, st, "k_trk_masks", k_trk_masks<<<(unsigned)((n + 3) / 4), 128, 0, st>>>(a));
     LAUNCH(ctx, st, "k_trk_fold", k_trk_fold<<<nc, 256, 0, st>>>(a, t->d_cov, t->d_mm));
     CUDA_TRY(ctx, cudaGetLastError());
