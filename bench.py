@@ -675,6 +675,82 @@ def container_assembly_leg(ln):
             'verified': 'first and last container: header fields and CRC32, byte size, landmark, the CRC32 of every block, exact length', 'in_default_timed_step': False}
 
 
+def bam_records_leg(ln):
+    """the decoded records of the step as BAM record bytes, on the device -- CIGAR rebuilt from the unpacked read
+    features (Cram2SamRecordFactory.getCigar2), the decoder's pairing restoration (CramNormalizer.normalize), the record layout of
+    BAMRecordView -- and back again as Bam_OBA_Supplier's stripes are read (cramgpu_bam_unpack_dev).  Verified: the rebuilt CIGARs
+    are the input CIGARs where those hold only M / I / D / S (= / X come back as M by design), and unpacking the packed records
+    returns the very bases, qualities, positions and flags that went in; CUDA-event timed."""
+    torch, rec, ctx = ln.torch, ln.rec, ln.ctx
+    vp = C.c_void_p
+    ln.encode(); ln.decode()
+    ln.stream.synchronize()
+    n = ln.n_reads
+    U = ln.U
+    dev = ln.dev
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    z32 = torch.zeros(n, dtype=torch.int32, device=dev); m1 = torch.full((n,), -1, dtype=torch.int32, device=dev)
+    cf = torch.full((n,), 3, dtype=torch.uint8, device=dev); mf = torch.zeros(n, dtype=torch.uint8, device=dev)       # single-end reads: detached
+    nf = torch.full((n,), -1, dtype=torch.int32, device=dev); st_c = torch.zeros(ln.n_cont, dtype=torch.int32, device=dev)
+    st_r = torch.zeros(n, dtype=torch.int32, device=dev); st_u = torch.zeros(n, dtype=torch.int32, device=dev)
+    pos = ln.t_pos.clone()
+    cont_off = (np.arange(ln.n_cont + 1, dtype=np.uint64) * np.uint64(READS_PER_CONTAINER))
+    best = None
+    kern = {}
+    for rep in range(3):
+        ln.stream.synchronize()
+        if rep == 2:
+            ctx.profile_enable(True)                    # a third pass for the kernels' own durations
+        ev[0].record(ln.stream)
+        d_cig, d_coff, cig_len = vp(), vp(), C.c_uint64()
+        ctx.check(ctx.lib.cramgpu_cigar_rebuild_dev(ctx.handle, n, vp(ln.t_flag.data_ptr()), vp(ln.t_roff.data_ptr()), U.feat_off, U.f_op, U.f_pos,
+                                                    U.f_val, U.f_aux, C.byref(d_cig), C.byref(d_coff), C.byref(cig_len), ln._sp()))
+        ev[1].record(ln.stream)
+        M = rec.MateRestore()
+        M.n_reads = n; M.n_containers = ln.n_cont; M.cont_off = cont_off.ctypes.data_as(C.POINTER(C.c_uint64))
+        M.flag = ln.t_flag.data_ptr(); M.cf = cf.data_ptr(); M.mate_flags = mf.data_ptr(); M.nf = nf.data_ptr(); M.ref_id = z32.data_ptr()
+        M.pos = pos.data_ptr(); M.mate_ref_id = m1.data_ptr(); M.mate_pos = z32.data_ptr(); M.tlen = z32.data_ptr()
+        M.read_off = ln.t_roff.data_ptr(); M.feat_off = U.feat_off; M.f_op = U.f_op; M.f_val = U.f_val; M.f_aux = U.f_aux
+        ctx.check(ctx.lib.cramgpu_mate_restore_dev(ctx.handle, C.byref(M), vp(st_c.data_ptr()), ln._sp()))
+        ev[2].record(ln.stream)
+        B = rec.BamRecords()
+        B.n_reads = n; B.ref_id = z32.data_ptr(); B.pos = pos.data_ptr(); B.mate_ref_id = m1.data_ptr(); B.mate_pos = z32.data_ptr(); B.tlen = z32.data_ptr()
+        B.flag = ln.t_flag.data_ptr(); B.bin = None; B.mapq = ln.d_mapq.value if isinstance(ln.d_mapq, C.c_void_p) else ln.d_mapq; B.rflags = None
+        B.names = ln.t_names.data_ptr(); B.name_off = ln.t_noff.data_ptr(); B.cigar = d_cig.value; B.cigar_off = d_coff.value
+        B.bases = ln.o_bases.data_ptr(); B.quals = ln.o_quals.data_ptr(); B.read_off = ln.t_roff.data_ptr(); B.tags = None; B.tag_off = None
+        B.names_len = ln.t_names.numel(); B.cigar_len = cig_len.value; B.bases_len = ln.o_bases.numel(); B.tags_len = 0
+        d_bam, bam_len, d_roff = vp(), C.c_uint64(), vp()
+        ctx.check(ctx.lib.cramgpu_bam_pack_dev(ctx.handle, C.byref(B), C.byref(d_bam), C.byref(bam_len), C.byref(d_roff), vp(st_r.data_ptr()), ln._sp()))
+        ev[3].record(ln.stream)
+        Ub = rec.BamRecords()
+        ctx.check(ctx.lib.cramgpu_bam_unpack_dev(ctx.handle, d_bam, d_roff, n, C.byref(Ub), vp(st_u.data_ptr()), ln._sp()))
+        ev[4].record(ln.stream)
+        ln.stream.synchronize()
+        if rep == 2:
+            for name, m in ctx.profile_read():
+                kern[name] = round(kern.get(name, 0.0) + m, 4)
+            ctx.profile_enable(False)
+            break
+        t = [ev[i].elapsed_time(ev[i + 1]) for i in range(4)]
+        best = t if best is None else [min(a, b) for a, b in zip(best, t)]
+    assert int(st_c.abs().sum().item()) == 0 and int(st_r.abs().sum().item()) == 0 and int(st_u.abs().sum().item()) == 0, 'BAM leg: status'
+    # round trip: what was packed comes back
+    nb = ln.o_bases.numel()
+    got_b = ln.dv.dev_to_numpy(ctx, Ub.bases, nb, np.uint8); got_q = ln.dv.dev_to_numpy(ctx, Ub.quals, nb, np.uint8)
+    assert np.array_equal(got_b, ln.o_bases.cpu().numpy()) and np.array_equal(got_q, ln.o_quals.cpu().numpy()), 'BAM leg: bases / qualities'
+    assert np.array_equal(ln.dv.dev_to_numpy(ctx, Ub.pos, n, np.int32), ln.t_pos.cpu().numpy().view(np.int32)), 'BAM leg: positions'
+    assert np.array_equal(ln.dv.dev_to_numpy(ctx, Ub.flag, n, np.uint16), ln.t_flag.cpu().numpy().view(np.uint16)), 'BAM leg: flags'
+    # the rebuilt CIGARs against the input ones (the simulated reads use M I D S only)
+    cg = ln.dv.dev_to_numpy(ctx, d_cig.value, int(cig_len.value), np.uint32)
+    want = ln.t_cigar.cpu().numpy().view(np.uint32)
+    assert cg.size == want.size and np.array_equal(cg, want), 'BAM leg: rebuilt CIGARs'
+    total = int(bam_len.value)
+    return {'row': 'Cram2SamRecordFactory.getCigar2 :119-214 + CramNormalizer.normalize pairing :67-102 + BAMRecordView :70-241 (pack) + Bam_OBA_Supplier :45-82 (unpack) for every record of the step',
+            'reads': int(n), 'bam_bytes': total, 'ms': {'cigar_rebuild': round(best[0], 4), 'mate_restore': round(best[1], 4), 'bam_pack': round(best[2], 4), 'bam_unpack': round(best[3], 4)},
+            'kernels_ms': kern, 'bam_pack_GBps': total / (best[2] * 1e-3) / 1e9, 'bam_unpack_GBps': total / (best[3] * 1e-3) / 1e9,
+            'verified': 'rebuilt CIGARs equal the input CIGARs; packed then unpacked records return the restored bases, qualities, positions, flags', 'in_default_timed_step': False}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -787,6 +863,7 @@ def run_ours(args):
     ms_dig = max_over_ranks(ms_dig)
     framing_leg = block_framing_leg(lanes[0])
     container_leg = container_assembly_leg(lanes[0])
+    bam_leg = bam_records_leg(lanes[0]) if lanes[0].use_unpack else None
     digest_leg = {'row': 'ContainerFactory.buildSlice :138-176 (nofRecords, bases, sequenceId, alignment start/span, BD, SD) + Slice.setRefMD5',
                   'ms_per_step_unpipelined_with_digests': ms_dig, 'ms_per_step_unpipelined_without': ms_unpip,
                   'k_slice_digest_ms': round(kdig.get('k_slice_digest', 0.0), 4), 'k_slice_finish_ms': round(kdig.get('k_slice_finish', 0.0), 4), 'k_slice_md5_ms': round(kdig.get('k_slice_md5', 0.0), 4),
@@ -902,6 +979,7 @@ def run_ours(args):
         line['slice_digests'] = digest_leg
         line['block_framing'] = framing_leg
         line['container_assembly'] = container_leg
+        if bam_leg: line['bam_records'] = bam_leg
         line.update(extra_legs)
         if world == 1 and not args.no_cpu:
             line['cpu_baseline'] = cpu_baseline(args)

@@ -264,62 +264,142 @@ __global__ void __launch_bounds__(128) k_bam_size(PackArgs a)
 __device__ __forceinline__ void put_le32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
 __device__ __forceinline__ void put_le16(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); }
 
-// one warp per record, lanes over the bytes
+// copy len bytes src -> dst with the lanes of a warp, B x 32 bytes per round: all loads of a round are issued before its
+// stores (a store may alias the next load as far as the compiler knows, and a load that waits behind it costs a round trip
+// to memory -- the kernel's time is those round trips, not its bytes)
+// a byte load that is predicated instead of branched around, at a constant offset from a pointer that is computed once per
+// round: @p LDG.U8 [R + imm].  These kernels are bound by instruction issue -- 486 warp instructions per record when every
+// byte paid a 64-bit address add and every bounds check a branch with its reconvergence point (profiles/).
+template <int OFF>
+__device__ __forceinline__ uint32_t ldg_u8_if(const uint8_t *base, bool p)
+{
+    uint32_t v = 0;
+    asm("{\n .reg .pred q;\n setp.ne.u32 q, %2, 0;\n @q ld.global.nc.u8 %0, [%1+%3];\n}" : "+r"(v) : "l"(base), "r"((uint32_t)p), "n"(OFF));
+    return v;
+}
+template <int B, int J = 0>
+struct WarpCopyRound {
+    static __device__ __forceinline__ void load(uint32_t *v, const uint8_t *s, uint32_t kb, uint32_t len)
+    {
+        v[J] = ldg_u8_if<32 * J>(s, kb + 32 * J < len);
+        WarpCopyRound<B, J + 1>::load(v, s, kb, len);
+    }
+};
+template <int B>
+struct WarpCopyRound<B, B> { static __device__ __forceinline__ void load(uint32_t *, const uint8_t *, uint32_t, uint32_t) {} };
+
+// copy len bytes src -> dst with the lanes of a warp, B x 32 bytes per round: all loads of a round are issued before its
+// stores (a store may alias the next load as far as the compiler knows)
+template <int B>
+__device__ __forceinline__ void warp_copy(uint8_t *dst, const uint8_t *src, uint32_t len, uint32_t lane)
+{
+    for (uint32_t k0 = 0; k0 < len; k0 += 32 * B) {
+        const uint32_t kb = k0 + lane;
+        uint32_t v[B];
+        WarpCopyRound<B>::load(v, src + kb, kb, len);
+        uint8_t *d = dst + kb;
+#pragma unroll
+        for (int j = 0; j < B; j++) if (kb + 32 * j < len) d[32 * j] = (uint8_t)v[j];
+    }
+}
+
+// one warp per record, lanes over the bytes.  Everything the record needs is loaded before the first byte is written.
 __global__ void __launch_bounds__(128) k_bam_write(PackArgs a)
 {
-    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (r >= a.in.n_reads) return;
+    __shared__ uint8_t nyb[256];                                            // base -> nybble, 16 = not a BAM base
+    for (uint32_t i = threadIdx.x; i < 256; i += 128) nyb[i] = (uint8_t)base_nybble((uint8_t)i);
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
     const cramgpu_bam_records &R = a.in;
-    const uint64_t n0 = R.name_off[r], c0 = R.cigar_off[r], b0 = R.read_off[r];
-    const uint32_t lname = (uint32_t)(R.name_off[r + 1] - n0), ncig = (uint32_t)(R.cigar_off[r + 1] - c0), lseq = (uint32_t)(R.read_off[r + 1] - b0);
-    const uint64_t t0 = R.tags ? R.tag_off[r] : 0;
-    const uint32_t ltag = R.tags ? (uint32_t)(R.tag_off[r + 1] - t0) : 0u;
-    uint8_t *o = a.out + a.rec_off[r];
-    const uint32_t total = (uint32_t)(a.rec_off[r + 1] - a.rec_off[r]);
-    // reference length of the CIGAR -> alignment end -> bin [SAMRecord.java:591-598,1524-1531]
+    const uint8_t *const R_bases = R.bases, *const R_quals = R.quals, *const R_names = R.names;      // kernel parameters: once, not per record
+    const uint32_t *const R_cigar = R.cigar;
+    uint8_t *const out = a.out;
+    // a warp takes record after record (grid-stride): the grid is sized to fill the machine once, not one short-lived CTA per
+    // four records
+    for (uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); r < a.in.n_reads; r += (uint64_t)gridDim.x * 4) {
+    const uint64_t n0 = __ldg(R.name_off + r), c0 = __ldg(R.cigar_off + r), b0 = __ldg(R.read_off + r);
+    const uint32_t lname = (uint32_t)(__ldg(R.name_off + r + 1) - n0), ncig = (uint32_t)(__ldg(R.cigar_off + r + 1) - c0);
+    const uint32_t lseq = (uint32_t)(__ldg(R.read_off + r + 1) - b0);
+    const uint64_t t0 = R.tags ? __ldg(R.tag_off + r) : 0;
+    const uint32_t ltag = R.tags ? (uint32_t)(__ldg(R.tag_off + r + 1) - t0) : 0u;
+    const uint64_t o0 = __ldg(a.rec_off + r);
+    const uint32_t total = (uint32_t)(__ldg(a.rec_off + r + 1) - o0);
+    const int32_t pos = __ldg(R.pos + r);
+    const uint32_t flag = __ldg(R.flag + r), mapq = __ldg(R.mapq + r);
+    const int32_t ref_id = R.ref_id ? __ldg(R.ref_id + r) : 0, mref = R.mate_ref_id ? __ldg(R.mate_ref_id + r) : -1;
+    const int32_t mpos = R.mate_pos ? __ldg(R.mate_pos + r) : 0, tlen = R.tlen ? __ldg(R.tlen + r) : 0;
+    const bool noq = R.rflags && (__ldg(R.rflags + r) & CRAMGPU_RF_NO_QUALS);
+    uint8_t *o = out + o0;
+    const uint32_t nsq = (lseq + 1) / 2;
+    // ---- round 0 of every field: all of a record's loads are in flight before its first byte is written (a record then costs
+    //      two trips to memory -- offsets, data -- instead of one per field); what is longer than a round goes on below
+    const uint32_t cw0 = lane < ncig ? __ldg(R_cigar + c0 + lane) : 0u;
+    const uint32_t nm0 = ldg_u8_if<0>(R_names + n0 + lane, lane < lname);
+    const uint8_t *bp0 = R_bases + b0 + 2 * lane;
+    uint32_t h[3], l[3], q[5];
+    h[0] = ldg_u8_if<0>(bp0, 2 * lane < lseq);        l[0] = ldg_u8_if<1>(bp0, 2 * lane + 1 < lseq);
+    h[1] = ldg_u8_if<64>(bp0, 2 * lane + 64 < lseq);  l[1] = ldg_u8_if<65>(bp0, 2 * lane + 65 < lseq);
+    h[2] = ldg_u8_if<128>(bp0, 2 * lane + 128 < lseq); l[2] = ldg_u8_if<129>(bp0, 2 * lane + 129 < lseq);
+    WarpCopyRound<5>::load(q, R_quals + b0 + lane, lane, noq ? 0u : lseq);
+    // CIGAR: reference length -> alignment end -> bin [SAMRecord.java:591-598,1524-1531]
     int32_t reflen = 0;
-    for (uint32_t k = lane; k < ncig; k += 32) {
-        const uint32_t w = R.cigar[c0 + k], op = w & 15u;
-        if (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) reflen += (int32_t)(w >> 4);
-        o[36 + lname + 1 + 4 * k] = (uint8_t)w; o[36 + lname + 1 + 4 * k + 1] = (uint8_t)(w >> 8);
-        o[36 + lname + 1 + 4 * k + 2] = (uint8_t)(w >> 16); o[36 + lname + 1 + 4 * k + 3] = (uint8_t)(w >> 24);
+    for (uint32_t k0 = 0; k0 < ncig; k0 += 32) {
+        const uint32_t k = k0 + lane;
+        const uint32_t w = k0 == 0 ? cw0 : (k < ncig ? __ldg(R_cigar + c0 + k) : 0u), op = w & 15u;
+        if (k < ncig) {
+            if (op == 0 || op == 2 || op == 3 || op == 7 || op == 8) reflen += (int32_t)(w >> 4);
+            uint8_t *qq = o + 36 + lname + 1 + 4 * k;
+            qq[0] = (uint8_t)w; qq[1] = (uint8_t)(w >> 8); qq[2] = (uint8_t)(w >> 16); qq[3] = (uint8_t)(w >> 24);
+        }
     }
     for (int d = 16; d; d >>= 1) reflen += __shfl_xor_sync(0xFFFFFFFFu, reflen, d);
-    if (lane == 0) {
-        const int32_t pos = R.pos[r];
-        const uint16_t flag = R.flag[r];
+    {
+        // the 36 fixed bytes: nine little-endian words, lane k writes byte k (lanes 0-3 also bytes 32-35)
         const int32_t beg = pos - 1;
         int32_t end = (flag & 4) ? 0 : pos + reflen - 1;
         if (end <= 0) end = beg + 1;
-        put_le32(o, total - 4);
-        put_le32(o + 4, (uint32_t)(R.ref_id ? R.ref_id[r] : 0));
-        put_le32(o + 8, (uint32_t)beg);
-        o[12] = (uint8_t)(lname + 1);
-        o[13] = R.mapq[r];
-        put_le16(o + 14, reg2bin(beg, end));
-        put_le16(o + 16, ncig);
-        put_le16(o + 18, flag);
-        put_le32(o + 20, lseq);
-        put_le32(o + 24, (uint32_t)(R.mate_ref_id ? R.mate_ref_id[r] : -1));
-        put_le32(o + 28, (uint32_t)((R.mate_pos ? R.mate_pos[r] : 0) - 1));
-        put_le32(o + 32, (uint32_t)(R.tlen ? R.tlen[r] : 0));
-        o[36 + lname] = 0;
+        const uint32_t W3 = (lname + 1) | (mapq << 8) | ((uint32_t)reg2bin(beg, end) << 16), W4 = (ncig & 0xFFFFu) | (flag << 16);
+        const uint32_t wi = lane >> 2;
+        const uint32_t w = wi == 0 ? total - 4 : wi == 1 ? (uint32_t)ref_id : wi == 2 ? (uint32_t)beg : wi == 3 ? W3 : wi == 4 ? W4 : wi == 5 ? lseq
+                           : wi == 6 ? (uint32_t)mref : (uint32_t)(mpos - 1);
+        o[lane] = (uint8_t)(w >> (8 * (lane & 3)));
+        if (lane < 4) o[32 + lane] = (uint8_t)((uint32_t)tlen >> (8 * lane));
+        if (lane == 4) o[36 + lname] = 0;
     }
-    for (uint32_t k = lane; k < lname; k += 32) o[36 + k] = R.names[n0 + k];
+    if (lane < lname) o[36 + lane] = (uint8_t)nm0;
+    if (lname > 32) warp_copy<1>(o + 36 + 32, R_names + n0 + 32, lname - 32, lane);
     uint8_t *sq = o + 36 + lname + 1 + 4 * ncig;
     bool bad = false;
-    for (uint32_t k = lane; k < (lseq + 1) / 2; k += 32) {
-        uint32_t hi = base_nybble(R.bases[b0 + 2 * k]), lo = 2 * k + 1 < lseq ? base_nybble(R.bases[b0 + 2 * k + 1]) : 0u;
-        if (hi > 15 || lo > 15) { bad = true; hi = min(hi, 15u); lo = min(lo, 15u); }
-        sq[k] = (uint8_t)((hi << 4) | lo);
+    for (uint32_t k0 = 0; k0 < nsq; k0 += 96) {
+        const uint32_t kb = k0 + lane;
+        if (k0) {
+            const uint8_t *bp = R_bases + b0 + 2 * kb;
+            h[0] = ldg_u8_if<0>(bp, 2 * kb < lseq);        l[0] = ldg_u8_if<1>(bp, 2 * kb + 1 < lseq);
+            h[1] = ldg_u8_if<64>(bp, 2 * kb + 64 < lseq);  l[1] = ldg_u8_if<65>(bp, 2 * kb + 65 < lseq);
+            h[2] = ldg_u8_if<128>(bp, 2 * kb + 128 < lseq); l[2] = ldg_u8_if<129>(bp, 2 * kb + 129 < lseq);
+        }
+        uint8_t *d = sq + kb;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const uint32_t k = kb + 32 * j;
+            uint32_t hi = nyb[h[j]], lo = 2 * k + 1 < lseq ? nyb[l[j]] : 0u;
+            bad |= k < nsq && (hi > 15 || lo > 15);
+            hi = min(hi, 15u); lo = min(lo, 15u);
+            if (k < nsq) d[32 * j] = (uint8_t)((hi << 4) | lo);
+        }
     }
-    uint8_t *ql = sq + (lseq + 1) / 2;
-    const bool noq = R.rflags && (R.rflags[r] & CRAMGPU_RF_NO_QUALS);
-    for (uint32_t k = lane; k < lseq; k += 32) ql[k] = noq ? (uint8_t)0xFF : R.quals[b0 + k];
-    for (uint32_t k = lane; k < ltag; k += 32) ql[lseq + k] = R.tags[t0 + k];
+    uint8_t *ql = sq + nsq;
+    if (noq) { for (uint32_t k = lane; k < lseq; k += 32) ql[k] = 0xFF; }
+    else {
+        uint8_t *d = ql + lane;
+#pragma unroll
+        for (int j = 0; j < 5; j++) if (lane + 32 * j < lseq) d[32 * j] = (uint8_t)q[j];
+        if (lseq > 160) warp_copy<5>(ql + 160, R_quals + b0 + 160, lseq - 160, lane);
+    }
+    if (ltag) warp_copy<4>(ql + lseq, R.tags + t0, ltag, lane);
     bad = __any_sync(0xFFFFFFFFu, bad);
     if (lane == 0) a.status[r] = bad ? CRAMGPU_ERR_ARG : CRAMGPU_OK;
+    }
 }
 
 }  // namespace
@@ -352,7 +432,7 @@ extern "C" int cramgpu_bam_pack_dev(cramgpu_ctx *ctx, const cramgpu_bam_records 
     const uint64_t total = *(const uint64_t *)ctx->pin_bam;
     if (int rc = pool_reserve(ctx, ctx->bam_out, total + 16)) return rc;
     a.out = (uint8_t *)ctx->bam_out.p;
-    LAUNCH(ctx, st, "k_bam_write", k_bam_write<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_bam_write", k_bam_write<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148ull * 16), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     *d_bam = a.out; *bam_len = total; *d_rec_off = (uint64_t *)(S + o_off);
     return CRAMGPU_OK;
@@ -398,38 +478,84 @@ __global__ void __launch_bounds__(128) k_bam_scan(UnpackArgs a)
 
 __global__ void __launch_bounds__(128) k_bam_unpack(UnpackArgs a)
 {
-    const uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (r >= a.n) return;
     const uint32_t lane = threadIdx.x & 31;
-    const uint8_t *p = a.bam + a.rec_off[r];
-    const bool ok = a.status[r] == CRAMGPU_OK;
-    const uint32_t lname = (uint32_t)(a.name_off[r + 1] - a.name_off[r]), ncig = (uint32_t)(a.cigar_off[r + 1] - a.cigar_off[r]);
-    const uint32_t lseq = (uint32_t)(a.read_off[r + 1] - a.read_off[r]), ltag = (uint32_t)(a.tag_off[r + 1] - a.tag_off[r]);
+    for (uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); r < a.n; r += (uint64_t)gridDim.x * 4) {
+    const uint8_t *p = a.bam + __ldg(a.rec_off + r);
+    const bool ok = __ldg(a.status + r) == CRAMGPU_OK;
+    const uint64_t n0 = __ldg(a.name_off + r), c0 = __ldg(a.cigar_off + r), b0 = __ldg(a.read_off + r), t0 = __ldg(a.tag_off + r);
+    const uint32_t lname = (uint32_t)(__ldg(a.name_off + r + 1) - n0), ncig = (uint32_t)(__ldg(a.cigar_off + r + 1) - c0);
+    const uint32_t lseq = (uint32_t)(__ldg(a.read_off + r + 1) - b0), ltag = (uint32_t)(__ldg(a.tag_off + r + 1) - t0);
     const uint8_t *nm = p + 36, *cg = nm + lname + 1, *sq = cg + 4 * ncig, *ql = sq + (lseq + 1) / 2, *tg = ql + lseq;
-    if (lane == 0) {
-        if (ok) {
-            a.ref_id[r] = (int32_t)get_le32(p + 4); a.pos[r] = (int32_t)get_le32(p + 8) + 1; a.mapq[r] = p[13]; a.bin[r] = (uint16_t)get_le16(p + 14);
-            a.flag[r] = (uint16_t)get_le16(p + 18); a.mate_ref_id[r] = (int32_t)get_le32(p + 24); a.mate_pos[r] = (int32_t)get_le32(p + 28) + 1;
-            a.tlen[r] = (int32_t)get_le32(p + 32);
-            a.rflags[r] = (uint8_t)((lseq == 0 ? CRAMGPU_RF_NO_BASES : 0u) | ((lseq == 0 || ql[0] == 0xFF) ? CRAMGPU_RF_NO_QUALS : 0u));
-        } else {
+    if (!ok) {
+        if (lane == 0) {
             a.ref_id[r] = -1; a.pos[r] = 0; a.mapq[r] = 0; a.bin[r] = 0; a.flag[r] = 4; a.mate_ref_id[r] = -1; a.mate_pos[r] = 0; a.tlen[r] = 0;
             a.rflags[r] = CRAMGPU_RF_NO_BASES | CRAMGPU_RF_NO_QUALS;
         }
+        continue;
     }
-    if (!ok) return;
-    uint8_t *on = a.names + a.name_off[r];
-    for (uint32_t k = lane; k < lname; k += 32) on[k] = nm[k];
-    uint32_t *oc = a.cigar + a.cigar_off[r];
-    for (uint32_t k = lane; k < ncig; k += 32) oc[k] = get_le32(cg + 4 * k);
-    uint8_t *ob = a.bases + a.read_off[r], *oq = a.quals + a.read_off[r];
-    for (uint32_t k = lane; k < lseq; k += 32) {
-        const uint32_t ny = (sq[k >> 1] >> ((k & 1) ? 0 : 4)) & 15u;
-        ob[k] = (uint8_t)"=ACMGRSVTWYHKDBN"[ny];
-        oq[k] = ql[k];
+    // ---- every first-round load of the record before its first store (see k_bam_write)
+    const uint32_t hb = __ldg(p + lane), hb2 = lane < 4 ? __ldg(p + 32 + lane) : 0u;
+    const uint32_t q0 = lseq ? __ldg(ql) : 0u;
+    const uint32_t nm0 = ldg_u8_if<0>(nm + lane, lane < lname);
+    const uint8_t *cq0 = cg + 4 * lane;
+    const bool hasc = lane < ncig;
+    const uint32_t cb0 = ldg_u8_if<0>(cq0, hasc), cb1 = ldg_u8_if<1>(cq0, hasc), cb2 = ldg_u8_if<2>(cq0, hasc), cb3 = ldg_u8_if<3>(cq0, hasc);
+    uint32_t sb[5], qv[5];
+    {
+        const uint8_t *sp = sq + (lane >> 1), *qp = ql + lane;             // (lane + 32 j) >> 1 = (lane >> 1) + 16 j
+        sb[0] = ldg_u8_if<0>(sp, lane < lseq);        qv[0] = ldg_u8_if<0>(qp, lane < lseq);
+        sb[1] = ldg_u8_if<16>(sp, lane + 32 < lseq);  qv[1] = ldg_u8_if<32>(qp, lane + 32 < lseq);
+        sb[2] = ldg_u8_if<32>(sp, lane + 64 < lseq);  qv[2] = ldg_u8_if<64>(qp, lane + 64 < lseq);
+        sb[3] = ldg_u8_if<48>(sp, lane + 96 < lseq);  qv[3] = ldg_u8_if<96>(qp, lane + 96 < lseq);
+        sb[4] = ldg_u8_if<64>(sp, lane + 128 < lseq); qv[4] = ldg_u8_if<128>(qp, lane + 128 < lseq);
     }
-    uint8_t *ot = a.tags + a.tag_off[r];
-    for (uint32_t k = lane; k < ltag; k += 32) ot[k] = tg[k];
+    {
+        // the 36 fixed bytes: lane k holds byte k, lanes 0-3 also bytes 32-35; words by shuffles, and the lane that holds a
+        // field's word writes the field
+        uint32_t w = hb | (__shfl_down_sync(0xFFFFFFFFu, hb, 1) << 8) | (__shfl_down_sync(0xFFFFFFFFu, hb, 2) << 16) | (__shfl_down_sync(0xFFFFFFFFu, hb, 3) << 24);
+        const uint32_t w8 = hb2 | (__shfl_down_sync(0xFFFFFFFFu, hb2, 1) << 8) | (__shfl_down_sync(0xFFFFFFFFu, hb2, 2) << 16) | (__shfl_down_sync(0xFFFFFFFFu, hb2, 3) << 24);
+        if (lane == 4) a.ref_id[r] = (int32_t)w;
+        if (lane == 8) a.pos[r] = (int32_t)w + 1;
+        if (lane == 12) { a.mapq[r] = (uint8_t)(w >> 8); a.bin[r] = (uint16_t)(w >> 16); }
+        if (lane == 16) a.flag[r] = (uint16_t)(w >> 16);
+        if (lane == 24) a.mate_ref_id[r] = (int32_t)w;
+        if (lane == 28) a.mate_pos[r] = (int32_t)w + 1;
+        if (lane == 0) {
+            a.tlen[r] = (int32_t)w8;
+            a.rflags[r] = (uint8_t)((lseq == 0 ? CRAMGPU_RF_NO_BASES : 0u) | ((lseq == 0 || q0 == 0xFF) ? CRAMGPU_RF_NO_QUALS : 0u));
+        }
+    }
+    if (lane < lname) a.names[n0 + lane] = (uint8_t)nm0;
+    if (lname > 32) warp_copy<1>(a.names + n0 + 32, nm + 32, lname - 32, lane);
+    uint32_t *oc = a.cigar + c0;
+    if (hasc) oc[lane] = cb0 | (cb1 << 8) | (cb2 << 16) | (cb3 << 24);
+    for (uint32_t k = 32 + lane; k < ncig; k += 32) {
+        const uint8_t *q = cg + 4 * k;
+        const uint32_t b0_ = __ldg(q), b1 = __ldg(q + 1), b2 = __ldg(q + 2), b3 = __ldg(q + 3);
+        oc[k] = b0_ | (b1 << 8) | (b2 << 16) | (b3 << 24);
+    }
+    uint8_t *ob = a.bases + b0, *oq = a.quals + b0;
+    for (uint32_t k0 = 0; k0 < lseq; k0 += 160) {
+        const uint32_t kb = k0 + lane;
+        if (k0) {
+            const uint8_t *sp = sq + (kb >> 1), *qp = ql + kb;
+            sb[0] = ldg_u8_if<0>(sp, kb < lseq);        qv[0] = ldg_u8_if<0>(qp, kb < lseq);
+            sb[1] = ldg_u8_if<16>(sp, kb + 32 < lseq);  qv[1] = ldg_u8_if<32>(qp, kb + 32 < lseq);
+            sb[2] = ldg_u8_if<32>(sp, kb + 64 < lseq);  qv[2] = ldg_u8_if<64>(qp, kb + 64 < lseq);
+            sb[3] = ldg_u8_if<48>(sp, kb + 96 < lseq);  qv[3] = ldg_u8_if<96>(qp, kb + 96 < lseq);
+            sb[4] = ldg_u8_if<64>(sp, kb + 128 < lseq); qv[4] = ldg_u8_if<128>(qp, kb + 128 < lseq);
+        }
+        uint8_t *obp = ob + kb, *oqp = oq + kb;
+        const uint32_t sh = (kb & 1) ? 0u : 4u;                             // the same for every j: 32 j is even
+#pragma unroll
+        for (int j = 0; j < 5; j++) {
+            const uint32_t ny = (sb[j] >> sh) & 15u;
+            const unsigned long long tab = ny < 8 ? 0x565352474D43413Dull : 0x4E42444B48595754ull;       // "=ACMGRSV" / "TWYHKDBN" in registers
+            if (kb + 32 * j < lseq) { obp[32 * j] = (uint8_t)(tab >> (8 * (ny & 7))); oqp[32 * j] = (uint8_t)qv[j]; }
+        }
+    }
+    if (ltag) warp_copy<4>(a.tags + t0, tg, ltag, lane);
+    }
 }
 
 }  // namespace
@@ -474,7 +600,7 @@ extern "C" int cramgpu_bam_unpack_dev(cramgpu_ctx *ctx, const uint8_t *d_bam, co
     a.ref_id = i32; a.pos = i32 + n; a.mate_ref_id = i32 + 2 * n; a.mate_pos = i32 + 3 * n; a.tlen = i32 + 4 * n;
     a.flag = (uint16_t *)(S + o_u16); a.bin = a.flag + n; a.mapq = S + o_u8; a.rflags = S + o_u8 + n;
     a.names = O + q_names; a.cigar = (uint32_t *)(O + q_cig); a.bases = O + q_bases; a.quals = O + q_quals; a.tags = O + q_tags;
-    LAUNCH(ctx, st, "k_bam_unpack", k_bam_unpack<<<(uint32_t)((n + 3) / 4), 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_bam_unpack", k_bam_unpack<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148ull * 16), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     out->n_reads = n; out->ref_id = a.ref_id; out->pos = a.pos; out->mate_ref_id = a.mate_ref_id; out->mate_pos = a.mate_pos; out->tlen = a.tlen;
     out->flag = a.flag; out->bin = a.bin; out->mapq = a.mapq; out->rflags = a.rflags; out->names = a.names; out->name_off = a.name_off;
