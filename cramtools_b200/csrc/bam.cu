@@ -261,8 +261,6 @@ __global__ void __launch_bounds__(128) k_bam_size(PackArgs a)
     a.size[r] = (uint32_t)(36 + lname + 4 * ncig + (lseq + 1) / 2 + lseq + ltag);
 }
 
-__device__ __forceinline__ void put_le32(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); p[2] = (uint8_t)(v >> 16); p[3] = (uint8_t)(v >> 24); }
-__device__ __forceinline__ void put_le16(uint8_t *p, uint32_t v) { p[0] = (uint8_t)v; p[1] = (uint8_t)(v >> 8); }
 
 // copy len bytes src -> dst with the lanes of a warp, B x 32 bytes per round: all loads of a round are issued before its
 // stores (a store may alias the next load as far as the compiler knows, and a load that waits behind it costs a round trip
