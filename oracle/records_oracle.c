@@ -19,8 +19,10 @@
  * tests/golden/streams_jvm.json: the raw series ContainerFactory.buildSlice / Writer.write produced in the mini-JVM
  * (oracle/make_golden_streams.py), compared byte for byte by tests/test_oracle_streams.py.
  *
- * Per-base lossy selectors that need ReferenceTracks coverage/pile-up counters (X, P) are not restated
- * (outside BASELINE configs); R/N/D/I use "tracks present" semantics: baseAt(p) = ref[p-1].
+ * The per-base lossy selectors X and P read ReferenceTracks coverage / pile-up counters: ReferenceTracks, getSpans and
+ * updateTracks are restated literally further down (tracks_t) and pinned by tests/golden/tracks_jvm.json
+ * (oracle/make_golden_tracks.py, tests/test_oracle_tracks.py).  Without a tracks object R/N/D/I use "tracks present" semantics
+ * over the whole reference: baseAt(p) = ref[p-1], 'N' beyond its end.
  *
  * Data layout = structure of arrays, identical to the C ABI (include/cramgpu.h):
  *   reads:  bases/quals u8 concatenated, read_off[n+1]; cigar u32 BAM-packed, cigar_off[n+1];
