@@ -312,21 +312,40 @@ __global__ void __launch_bounds__(128) k_bam_write(PackArgs a)
     const uint8_t *const R_bases = R.bases, *const R_quals = R.quals, *const R_names = R.names;      // kernel parameters: once, not per record
     const uint32_t *const R_cigar = R.cigar;
     uint8_t *const out = a.out;
-    // a warp takes record after record (grid-stride): the grid is sized to fill the machine once, not one short-lived CTA per
-    // four records
-    for (uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); r < a.in.n_reads; r += (uint64_t)gridDim.x * 4) {
-    const uint64_t n0 = __ldg(R.name_off + r), c0 = __ldg(R.cigar_off + r), b0 = __ldg(R.read_off + r);
-    const uint32_t lname = (uint32_t)(__ldg(R.name_off + r + 1) - n0), ncig = (uint32_t)(__ldg(R.cigar_off + r + 1) - c0);
-    const uint32_t lseq = (uint32_t)(__ldg(R.read_off + r + 1) - b0);
-    const uint64_t t0 = R.tags ? __ldg(R.tag_off + r) : 0;
-    const uint32_t ltag = R.tags ? (uint32_t)(__ldg(R.tag_off + r + 1) - t0) : 0u;
-    const uint64_t o0 = __ldg(a.rec_off + r);
-    const uint32_t total = (uint32_t)(__ldg(a.rec_off + r + 1) - o0);
-    const int32_t pos = __ldg(R.pos + r);
-    const uint32_t flag = __ldg(R.flag + r), mapq = __ldg(R.mapq + r);
-    const int32_t ref_id = R.ref_id ? __ldg(R.ref_id + r) : 0, mref = R.mate_ref_id ? __ldg(R.mate_ref_id + r) : -1;
-    const int32_t mpos = R.mate_pos ? __ldg(R.mate_pos + r) : 0, tlen = R.tlen ? __ldg(R.tlen + r) : 0;
-    const bool noq = R.rflags && (__ldg(R.rflags + r) & CRAMGPU_RF_NO_QUALS);
+    // A CTA takes tile after tile of 32 consecutive records (grid-stride: the grid fills the machine once).  The tile's offsets and
+    // scalar fields come in with one round of coalesced loads by the whole CTA, so a record costs its warp ONE trip to memory --
+    // its data -- instead of two.
+    __shared__ uint64_t s_off[5][33];                                       // name, CIGAR, read, tag, output offsets
+    __shared__ int32_t s_i32[5][32];                                        // pos, ref id, mate ref id, mate pos, template size
+    __shared__ uint16_t s_flag[32];
+    __shared__ uint8_t s_mapq[32], s_rfl[32];
+    const uint64_t nrec = a.in.n_reads, ntiles = (nrec + 31) / 32;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * 32;
+    const uint32_t cnt = (uint32_t)(nrec - r0 < 32 ? nrec - r0 : 32);
+    __syncthreads();                                                        // the previous tile is done with the tables
+    {
+        const uint32_t t = threadIdx.x;
+        if (t <= cnt && t < 33) {
+            s_off[0][t] = __ldg(R.name_off + r0 + t); s_off[1][t] = __ldg(R.cigar_off + r0 + t); s_off[2][t] = __ldg(R.read_off + r0 + t);
+            s_off[3][t] = R.tags ? __ldg(R.tag_off + r0 + t) : 0ull; s_off[4][t] = __ldg(a.rec_off + r0 + t);
+        } else if (t >= 64 && t - 64 < cnt) {
+            const uint32_t u = t - 64;
+            s_i32[0][u] = __ldg(R.pos + r0 + u); s_i32[1][u] = R.ref_id ? __ldg(R.ref_id + r0 + u) : 0;
+            s_i32[2][u] = R.mate_ref_id ? __ldg(R.mate_ref_id + r0 + u) : -1; s_i32[3][u] = R.mate_pos ? __ldg(R.mate_pos + r0 + u) : 0;
+            s_i32[4][u] = R.tlen ? __ldg(R.tlen + r0 + u) : 0;
+            s_flag[u] = __ldg(R.flag + r0 + u); s_mapq[u] = __ldg(R.mapq + r0 + u); s_rfl[u] = R.rflags ? __ldg(R.rflags + r0 + u) : (uint8_t)0;
+        }
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x >> 5; i < cnt; i += 4) {
+    const uint64_t r = r0 + i;
+    const uint64_t n0 = s_off[0][i], c0 = s_off[1][i], b0 = s_off[2][i], t0 = s_off[3][i], o0 = s_off[4][i];
+    const uint32_t lname = (uint32_t)(s_off[0][i + 1] - n0), ncig = (uint32_t)(s_off[1][i + 1] - c0), lseq = (uint32_t)(s_off[2][i + 1] - b0);
+    const uint32_t ltag = (uint32_t)(s_off[3][i + 1] - t0), total = (uint32_t)(s_off[4][i + 1] - o0);
+    const int32_t pos = s_i32[0][i], ref_id = s_i32[1][i], mref = s_i32[2][i], mpos = s_i32[3][i], tlen = s_i32[4][i];
+    const uint32_t flag = s_flag[i], mapq = s_mapq[i];
+    const bool noq = (s_rfl[i] & CRAMGPU_RF_NO_QUALS) != 0;
     uint8_t *o = out + o0;
     const uint32_t nsq = (lseq + 1) / 2;
     // ---- round 0 of every field: all of a record's loads are in flight before its first byte is written (a record then costs
@@ -398,6 +417,7 @@ __global__ void __launch_bounds__(128) k_bam_write(PackArgs a)
     bad = __any_sync(0xFFFFFFFFu, bad);
     if (lane == 0) a.status[r] = bad ? CRAMGPU_ERR_ARG : CRAMGPU_OK;
     }
+    }
 }
 
 }  // namespace
@@ -430,7 +450,7 @@ extern "C" int cramgpu_bam_pack_dev(cramgpu_ctx *ctx, const cramgpu_bam_records 
     const uint64_t total = *(const uint64_t *)ctx->pin_bam;
     if (int rc = pool_reserve(ctx, ctx->bam_out, total + 16)) return rc;
     a.out = (uint8_t *)ctx->bam_out.p;
-    LAUNCH(ctx, st, "k_bam_write", k_bam_write<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148ull * 16), 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_bam_write", k_bam_write<<<(uint32_t)std::min<uint64_t>((n + 31) / 32, 148ull * 16), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     *d_bam = a.out; *bam_len = total; *d_rec_off = (uint64_t *)(S + o_off);
     return CRAMGPU_OK;
