@@ -497,12 +497,29 @@ __global__ void __launch_bounds__(128) k_bam_scan(UnpackArgs a)
 __global__ void __launch_bounds__(128) k_bam_unpack(UnpackArgs a)
 {
     const uint32_t lane = threadIdx.x & 31;
-    for (uint64_t r = (uint64_t)blockIdx.x * 4 + (threadIdx.x >> 5); r < a.n; r += (uint64_t)gridDim.x * 4) {
-    const uint8_t *p = a.bam + __ldg(a.rec_off + r);
-    const bool ok = __ldg(a.status + r) == CRAMGPU_OK;
-    const uint64_t n0 = __ldg(a.name_off + r), c0 = __ldg(a.cigar_off + r), b0 = __ldg(a.read_off + r), t0 = __ldg(a.tag_off + r);
-    const uint32_t lname = (uint32_t)(__ldg(a.name_off + r + 1) - n0), ncig = (uint32_t)(__ldg(a.cigar_off + r + 1) - c0);
-    const uint32_t lseq = (uint32_t)(__ldg(a.read_off + r + 1) - b0), ltag = (uint32_t)(__ldg(a.tag_off + r + 1) - t0);
+    // tiles of 32 records, their offsets through shared memory with one round of coalesced loads (see k_bam_write)
+    __shared__ uint64_t s_off[5][33];                                       // record, name, CIGAR, read, tag offsets
+    __shared__ int32_t s_st[32];
+    const uint64_t ntiles = (a.n + 31) / 32;
+    for (uint64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const uint64_t r0 = tile * 32;
+    const uint32_t cnt = (uint32_t)(a.n - r0 < 32 ? a.n - r0 : 32);
+    __syncthreads();
+    {
+        const uint32_t t = threadIdx.x;
+        if (t <= cnt && t < 33) {
+            s_off[0][t] = __ldg(a.rec_off + r0 + t); s_off[1][t] = __ldg(a.name_off + r0 + t); s_off[2][t] = __ldg(a.cigar_off + r0 + t);
+            s_off[3][t] = __ldg(a.read_off + r0 + t); s_off[4][t] = __ldg(a.tag_off + r0 + t);
+        } else if (t >= 64 && t - 64 < cnt) s_st[t - 64] = __ldg(a.status + r0 + t - 64);
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x >> 5; i < cnt; i += 4) {
+    const uint64_t r = r0 + i;
+    const uint8_t *p = a.bam + s_off[0][i];
+    const bool ok = s_st[i] == CRAMGPU_OK;
+    const uint64_t n0 = s_off[1][i], c0 = s_off[2][i], b0 = s_off[3][i], t0 = s_off[4][i];
+    const uint32_t lname = (uint32_t)(s_off[1][i + 1] - n0), ncig = (uint32_t)(s_off[2][i + 1] - c0);
+    const uint32_t lseq = (uint32_t)(s_off[3][i + 1] - b0), ltag = (uint32_t)(s_off[4][i + 1] - t0);
     const uint8_t *nm = p + 36, *cg = nm + lname + 1, *sq = cg + 4 * ncig, *ql = sq + (lseq + 1) / 2, *tg = ql + lseq;
     if (!ok) {
         if (lane == 0) {
@@ -574,6 +591,7 @@ __global__ void __launch_bounds__(128) k_bam_unpack(UnpackArgs a)
     }
     if (ltag) warp_copy<4>(a.tags + t0, tg, ltag, lane);
     }
+    }
 }
 
 }  // namespace
@@ -618,7 +636,7 @@ extern "C" int cramgpu_bam_unpack_dev(cramgpu_ctx *ctx, const uint8_t *d_bam, co
     a.ref_id = i32; a.pos = i32 + n; a.mate_ref_id = i32 + 2 * n; a.mate_pos = i32 + 3 * n; a.tlen = i32 + 4 * n;
     a.flag = (uint16_t *)(S + o_u16); a.bin = a.flag + n; a.mapq = S + o_u8; a.rflags = S + o_u8 + n;
     a.names = O + q_names; a.cigar = (uint32_t *)(O + q_cig); a.bases = O + q_bases; a.quals = O + q_quals; a.tags = O + q_tags;
-    LAUNCH(ctx, st, "k_bam_unpack", k_bam_unpack<<<(uint32_t)std::min<uint64_t>((n + 3) / 4, 148ull * 16), 128, 0, st>>>(a));
+    LAUNCH(ctx, st, "k_bam_unpack", k_bam_unpack<<<(uint32_t)std::min<uint64_t>((n + 31) / 32, 148ull * 16), 128, 0, st>>>(a));
     CUDA_TRY(ctx, cudaGetLastError());
     out->n_reads = n; out->ref_id = a.ref_id; out->pos = a.pos; out->mate_ref_id = a.mate_ref_id; out->mate_pos = a.mate_pos; out->tlen = a.tlen;
     out->flag = a.flag; out->bin = a.bin; out->mapq = a.mapq; out->rflags = a.rflags; out->names = a.names; out->name_off = a.name_off;
