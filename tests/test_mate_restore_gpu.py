@@ -110,3 +110,21 @@ def test_link_then_restore_round_trip(gpu_ctx):
     assert (got['status'] == 0).all()
     assert (got['mate_pos'] == mate).all() and (got['mate_ref_id'] == 0).all() and (got['tlen'] == tlen).all()
     assert (got['mate_flags'] == np.where(flag & 0x20, 1, 0)).all()
+
+
+def test_backward_and_out_of_container_links_are_corrupt(gpu_ctx):
+    """a link that points at or before its own record (the reference's list walk would never end) or beyond the container
+    (records.get() throws): the container is reported, its neighbours are restored"""
+    from cramtools_b200 import records as R
+    n = 12
+    z32 = np.zeros(n, np.int32)
+    a = dict(flag=np.full(n, 0x41, np.uint16), cf=np.full(n, 3, np.uint8), mate_flags=np.zeros(n, np.uint8), nf=np.full(n, -1, np.int32),
+             ref_id=z32.copy(), pos=(np.arange(n) * 10 + 1).astype(np.int32), mate_ref_id=np.full(n, -1, np.int32), mate_pos=z32.copy(), tlen=z32.copy(),
+             read_off=(np.arange(n + 1) * 50).astype(np.uint64), feat_off=np.zeros(n + 1, np.uint64), f_op=np.zeros(1, np.uint8),
+             f_val=np.zeros(1, np.int32), f_aux=np.zeros(1, np.int32))
+    a['cf'][0] = 5; a['nf'][0] = 1; a['cf'][2] = 1                     # container 0: record 0 -> record 2, fine
+    a['cf'][4] = 5; a['nf'][4] = -1                                    # container 1: points at itself
+    a['cf'][9] = 5; a['nf'][9] = 5                                     # container 2: points beyond the container
+    got = _restore(R, gpu_ctx, a, np.array([0, 4, 8, 12], np.uint64))
+    assert got['status'].tolist() == [0, _lib.ERR_CORRUPT, _lib.ERR_CORRUPT]
+    assert got['mate_pos'][0] == 21 and got['mate_pos'][2] == 1 and got['tlen'][0] == 21 and got['tlen'][2] == -21

@@ -132,3 +132,43 @@ def test_larger_batch_against_oracle(gpu_ctx):
         _check(R, gpu_ctx, ref, conts, spec, t, o, (20000, spec))
         assert t.position > 1
         t.close()
+
+
+def _unplaced(n, seed):
+    rng = np.random.default_rng(seed)
+    ln = rng.integers(20, 60, n)
+    return dict(bases=rng.choice(np.frombuffer(b'ACGTN', np.uint8), int(ln.sum())).astype(np.uint8), quals=rng.integers(2, 41, int(ln.sum())).astype(np.uint8),
+                read_off=np.concatenate([[0], np.cumsum(ln)]).astype(np.int64), cigar=np.zeros(0, np.uint32), cigar_off=np.zeros(n + 1, np.int64),
+                pos=np.zeros(n, np.int32), flag=np.full(n, 4, np.uint16), mapq=np.zeros(n, np.uint8), ref_id=np.full(n, -1, np.int32),
+                rflags=np.zeros(n, np.uint8))
+
+
+def test_unplaced_records_and_containers_leave_the_tracks_alone(G, gpu_ctx):
+    """a container of unplaced reads between placed ones, and unplaced reads at the end of a placed container: not in the spans,
+    not counted, no per-base masks (addQS returns at NO_ALIGNMENT_START)"""
+    from cramtools_b200 import records as R
+    from oracle import records as orec
+    g, ref, conts = G
+    tail, _ = _concat([conts[2], _unplaced(3, 1)])
+    tail['ref_id'] = np.concatenate([conts[2]['ref_id'], np.full(3, -1, np.int32)])
+    mixed = [conts[0], conts[1], _unplaced(5, 2), tail, conts[3]]
+    for spec in ('X3', 'P0_40-X4_8-D8'):
+        t = R.ReferenceTracks(ref, 1500, ctx=gpu_ctx); o = orec.Tracks(ref, 1500)
+        _check(R, gpu_ctx, ref, mixed, spec, t, o, (1500, spec, 'unplaced'))
+        t.close()
+
+
+def test_record_without_bases_is_refused(G, gpu_ctx):
+    from cramtools_b200 import records as R
+    g, ref, conts = G
+    c = {k: v.copy() for k, v in conts[1].items()}
+    # the third record loses its bases (SAMRecord.NULL_SEQUENCE) but keeps its CIGAR: updateTracks indexes an empty array
+    lo, hi = int(c['read_off'][2]), int(c['read_off'][3])
+    c['bases'] = np.concatenate([c['bases'][:lo], c['bases'][hi:]]); c['quals'] = np.concatenate([c['quals'][:lo], c['quals'][hi:]])
+    c['read_off'] = np.concatenate([c['read_off'][:3], c['read_off'][3:] - (hi - lo)])
+    rd, cont_off = _concat([conts[0], c])
+    t = R.ReferenceTracks(ref, 1500, ctx=gpu_ctx)
+    with pytest.raises(_lib.CramGpuError) as e:
+        t.update(rd, 'X3', cont_off)
+    assert e.value.status == _lib.ERR_UNSUPPORTED and e.value.container_status == [0, _lib.ERR_UNSUPPORTED]
+    t.close()
