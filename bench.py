@@ -271,6 +271,7 @@ class Lane(object):
         self.spec = spec
         self.pol, self.npol = rec._policy_args(spec)
         self.stream = torch.cuda.Stream(device=dev)
+        self.wait_event = None; self.d1_event = None; self.before_rans_encode = None      # set per step by run_ours' schedule
         self.side = torch.cuda.Stream(device=dev)          # the slice digests run beside the record-field and histogram kernels
         self.ev_fork, self.ev_join = torch.cuda.Event(), torch.cuda.Event()
         self.ctx = cramtools_b200.Context(dev.index)
@@ -370,6 +371,8 @@ class Lane(object):
         from cramtools_b200 import sharding
         from cramtools_b200._lib import u8p, u32p, u64p
         ctx, F, vp = self.ctx, self.F, C.c_void_p
+        if self.wait_event is not None:
+            self.stream.wait_event(self.wait_event)              # the record kernels start when that step's order-1 decode has ended
         ctx.check(ctx.lib.cramgpu_features_encode_dev(ctx.handle, C.byref(self.R), self.pol, self.npol, C.byref(F), self.soff.ctypes.data_as(u64p),
                                                       self.slen.ctypes.data_as(u64p), self._sp()))
         self.H.force_qs = F.force_qs                     # CF bit 0 comes from the quality model's decision
@@ -389,6 +392,8 @@ class Lane(object):
         v[:, 0] = base + self.soff[:, self.KQS]; w[:, 0] = self.slen[:, self.KQS]
         v[:, 1] = base + self.soff[:, self.KBA]; w[:, 1] = self.slen[:, self.KBA]
         v[:, 2:] = hbase + self.hoff[:, self.KX]; w[:, 2:] = self.hlen[:, self.KX]
+        if self.before_rans_encode is not None:
+            self.before_rans_encode()
         ctx.check(ctx.lib.cramgpu_rans_encode_dev(ctx.handle, self.nblk, None, self.in_addr.ctypes.data_as(u64p),
                                                   self.in_len.ctypes.data_as(u32p), self.order.ctypes.data_as(u8p),
                                                   vp(self.enc_out.data_ptr()), C.c_uint64(self.enc_cap), vp(self.e_off.data_ptr()),
@@ -506,6 +511,8 @@ class Lane(object):
                                                   self.c_len.ctypes.data_as(u32p), self.prefixes.ctypes.data_as(u8p),
                                                   vp(self.dec_out.data_ptr()), C.c_uint64(self.dec_out.numel()), vp(self.dd_off.data_ptr()),
                                                   vp(self.dd_len.data_ptr()), vp(self.dd_st.data_ptr()), self._sp()))
+        if self.d1_event is not None:
+            self.d1_event.record(self.stream)
         if self.use_unpack:
             # row P on the device: the read features come from the series themselves (QS / BA as just decoded, the series the
             # Java host inflates -- FN FC FP BS DL SC RS HC PD MQ -- as the encoder left them), not from the encoder's arrays
@@ -778,6 +785,13 @@ def run_ours(args):
     lanes = [Lane(i, n_cont, ref, rd, nu, dev, rank, world, groups[i], not args.no_unpack) for i in range(depth)]
     for ln in lanes:
         ln.prepare()
+    # Two schedules that were measured and are NOT the default ("pipeline arithmetic"): CRAMGPU_SERIAL_CODERS=1
+    # makes the encoder call of step j + 1 wait for the order-1 decode of step j (k_dec1 then runs at its isolated 39.8 ms, 0.0147
+    # of the roofline, but hist / tables / pack and the call's host synchronisation no longer hide beside it: 78.9 ms per step
+    # against 72.5); CRAMGPU_STAGGER=1 (three contexts) makes the record kernels of step j + 2 wait for that decode too (73.0 ms).
+    # CRAMGPU_TRACE_STEPS=1 prints when each phase of each step ended on the device.
+    stagger = depth >= 3 and bool(os.environ.get('CRAMGPU_STAGGER'))
+    serial_coders = depth >= 2 and bool(os.environ.get('CRAMGPU_SERIAL_CODERS'))
     n_reads = lanes[0].n_reads
 
     def barrier():
@@ -793,17 +807,43 @@ def run_ours(args):
             lanes[0].steps(k)
             return
         errs = []
+        trace = bool(os.environ.get('CRAMGPU_TRACE_STEPS'))
+        d1_done = [torch.cuda.Event(enable_timing=trace) for _ in range(k)]      # order-1 decode of step j has ended (device)
+        d1_sent = [threading.Event() for _ in range(k)]              # ... and its event has been recorded (host)
+        tr = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(k)] if trace else None
 
         def work(ln, i):
             try:
                 torch.cuda.set_device(local)
-                for _ in range(i, k, depth):
+                for j in range(i, k, depth):
+                    ln.wait_event = None
+                    if stagger and j >= 2:
+                        d1_sent[j - 2].wait()
+                        ln.wait_event = d1_done[j - 2]
+                    ln.d1_event = d1_done[j]
+                    ln.before_rans_encode = None
+                    if serial_coders and j >= 1:
+                        def gate(ln=ln, j=j):
+                            d1_sent[j - 1].wait()
+                            ln.stream.wait_event(d1_done[j - 1])
+                            if trace:
+                                tr[j][1].record(ln.stream)
+                        ln.before_rans_encode = gate
                     with enc_lock:
+                        if trace:
+                            tr[j][0].record(ln.stream)
                         ln.encode()
+                        if trace:
+                            tr[j][2].record(ln.stream)
                     with dec_lock:
                         ln.decode()
+                        if trace:
+                            tr[j][3].record(ln.stream)
+                    d1_sent[j].set()
             except Exception as e:      # noqa: BLE001
                 errs.append(e)
+                for ev in d1_sent:
+                    ev.set()
         th = [threading.Thread(target=work, args=(ln, i)) for i, ln in enumerate(lanes)]
         for t in th:
             t.start()
@@ -811,6 +851,13 @@ def run_ours(args):
             t.join()
         if errs:
             raise errs[0]
+        if trace and k >= 4:
+            torch.cuda.synchronize()
+            z = tr[0][0]
+            for j in range(k):
+                g = z.elapsed_time(tr[j][1]) if j >= 1 and serial_coders else float('nan')
+                sys.stderr.write('step %d lane %d: pre %.1f gate %.1f enc_end %.1f d1_end %.1f dec_end %.1f\n' % (
+                    j, j % depth, z.elapsed_time(tr[j][0]), g, z.elapsed_time(tr[j][2]), z.elapsed_time(d1_done[j]), z.elapsed_time(tr[j][3])))
 
     run_steps(args.warmup)
     barrier()
