@@ -810,6 +810,7 @@ def run_ours(args):
         trace = bool(os.environ.get('CRAMGPU_TRACE_STEPS'))
         d1_done = [torch.cuda.Event(enable_timing=trace) for _ in range(k)]      # order-1 decode of step j has ended (device)
         d1_sent = [threading.Event() for _ in range(k)]              # ... and its event has been recorded (host)
+        enc_sent = [threading.Event() for _ in range(k)]             # the encode calls of step j have returned (host)
         tr = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(k)] if trace else None
 
         def work(ln, i):
@@ -829,12 +830,15 @@ def run_ours(args):
                             if trace:
                                 tr[j][1].record(ln.stream)
                         ln.before_rans_encode = gate
+                    if (serial_coders or stagger) and j >= 1:
+                        enc_sent[j - 1].wait()                       # these schedules need the steps to encode in order
                     with enc_lock:
                         if trace:
                             tr[j][0].record(ln.stream)
                         ln.encode()
                         if trace:
                             tr[j][2].record(ln.stream)
+                    enc_sent[j].set()
                     with dec_lock:
                         ln.decode()
                         if trace:
@@ -842,7 +846,7 @@ def run_ours(args):
                     d1_sent[j].set()
             except Exception as e:      # noqa: BLE001
                 errs.append(e)
-                for ev in d1_sent:
+                for ev in d1_sent + enc_sent:
                     ev.set()
         th = [threading.Thread(target=work, args=(ln, i)) for i, ln in enumerate(lanes)]
         for t in th:
